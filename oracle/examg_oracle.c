@@ -1,0 +1,310 @@
+/*
+ * examg_oracle.c -- CPU restatement of the ExaStencils-generated V-cycle.
+ * TEST INFRASTRUCTURE ONLY (see examg_oracle.h).  Build: oracle/Makefile
+ * (gcc -O3 -fopenmp -ffp-contract=off: only the explicit fma() calls fuse).
+ *
+ * Parallelisation mirrors the reference OpenMP build of the benchmark
+ * (omp_parallelizeLoopOverDimensions = true -> `#pragma omp parallel for
+ * schedule(static)` on the outermost dimension,
+ * C/s/e/parallelization/api/omp/OMP_Loop.scala:101-110).
+ */
+#include "examg_oracle.h"
+
+#include <math.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+
+/* ---------- helpers ------------------------------------------------------ */
+
+static inline size_t og_size(const int n[3]) {
+  return (size_t)n[0] * (size_t)n[1] * (size_t)n[2];
+}
+
+/* interior range of dimension d: 1..n-2, or the single plane 0 if n == 1 (2D) */
+static inline void og_range(const int n[3], int d, int *lo, int *hi) {
+  if (n[d] == 1) { *lo = 0; *hi = 1; } else { *lo = 1; *hi = n[d] - 1; }
+}
+
+/* linear offsets of the stencil entries */
+static void og_lin_offsets(const int n[3], const og_stencil *st, ptrdiff_t *lo) {
+  for (int k = 0; k < st->nst; ++k)
+    lo[k] = (ptrdiff_t)st->off[k][0] +
+            (ptrdiff_t)n[0] * ((ptrdiff_t)st->off[k][1] +
+                               (ptrdiff_t)n[1] * (ptrdiff_t)st->off[k][2]);
+}
+
+/* index of the centre entry (diag(), C/s/e/stencil/ir/IR_StencilFunction.scala:46-60) */
+static int og_centre(const og_stencil *st) {
+  for (int k = 0; k < st->nst; ++k)
+    if (!st->off[k][0] && !st->off[k][1] && !st->off[k][2]) return k;
+  fprintf(stderr, "og: stencil without centre entry\n");
+  exit(1);
+}
+
+/* canonical A*u at node p */
+static inline double og_conv(int nst, const ptrdiff_t *lo, const double *c,
+                             const double *sf, size_t size, const double *u,
+                             size_t p) {
+  double acc;
+  if (sf) {
+    acc = sf[p] * u[(ptrdiff_t)p + lo[0]];
+    for (int k = 1; k < nst; ++k)
+      acc = fma(sf[(size_t)k * size + p], u[(ptrdiff_t)p + lo[k]], acc);
+  } else {
+    acc = c[0] * u[(ptrdiff_t)p + lo[0]];
+    for (int k = 1; k < nst; ++k) acc = fma(c[k], u[(ptrdiff_t)p + lo[k]], acc);
+  }
+  return acc;
+}
+
+#define OG_LOOP_BEGIN(n)                                         \
+  int xl, xh, yl, yh, zl, zh;                                    \
+  og_range(n, 0, &xl, &xh);                                      \
+  og_range(n, 1, &yl, &yh);                                      \
+  og_range(n, 2, &zl, &zh);                                      \
+  const int outer_is_z = (n[2] > 1);                             \
+  (void)outer_is_z;
+
+/* ---------- stencil loops ------------------------------------------------- */
+
+void og_apply(const int n[3], const og_stencil *st, const double *sf,
+              const double *u, double *out) {
+  ptrdiff_t lo[OG_MAX_ST];
+  og_lin_offsets(n, st, lo);
+  const size_t size = og_size(n);
+  const int nst = st->nst;
+  OG_LOOP_BEGIN(n)
+#pragma omp parallel for schedule(static) collapse(2)
+  for (int k = zl; k < zh; ++k)
+    for (int j = yl; j < yh; ++j) {
+      size_t row = (size_t)n[0] * ((size_t)j + (size_t)n[1] * (size_t)k);
+      for (int i = xl; i < xh; ++i)
+        out[row + i] = og_conv(nst, lo, st->coef, sf, size, u, row + i);
+    }
+}
+
+void og_residual(const int n[3], const og_stencil *st, const double *sf,
+                 const double *u, const double *rhs, double *res) {
+  ptrdiff_t lo[OG_MAX_ST];
+  og_lin_offsets(n, st, lo);
+  const size_t size = og_size(n);
+  const int nst = st->nst;
+  OG_LOOP_BEGIN(n)
+#pragma omp parallel for schedule(static) collapse(2)
+  for (int k = zl; k < zh; ++k)
+    for (int j = yl; j < yh; ++j) {
+      size_t row = (size_t)n[0] * ((size_t)j + (size_t)n[1] * (size_t)k);
+      for (int i = xl; i < xh; ++i)
+        res[row + i] = rhs[row + i] - og_conv(nst, lo, st->coef, sf, size, u, row + i);
+    }
+}
+
+void og_smooth_jacobi(const int n[3], const og_stencil *st, const double *sf,
+                      double omega, const double *u, const double *rhs,
+                      double *unext) {
+  ptrdiff_t lo[OG_MAX_ST];
+  og_lin_offsets(n, st, lo);
+  const size_t size = og_size(n);
+  const int nst = st->nst;
+  const int c = og_centre(st);
+  const double wconst = omega / st->coef[c];
+  OG_LOOP_BEGIN(n)
+#pragma omp parallel for schedule(static) collapse(2)
+  for (int k = zl; k < zh; ++k)
+    for (int j = yl; j < yh; ++j) {
+      size_t row = (size_t)n[0] * ((size_t)j + (size_t)n[1] * (size_t)k);
+      for (int i = xl; i < xh; ++i) {
+        size_t p = row + i;
+        double w = sf ? omega / sf[(size_t)c * size + p] : wconst;
+        double r = rhs[p] - og_conv(nst, lo, st->coef, sf, size, u, p);
+        unext[p] = fma(w, r, u[p]);
+      }
+    }
+}
+
+void og_smooth_rb(const int n[3], const og_stencil *st, const double *sf,
+                  double omega, double *u, const double *rhs, int color) {
+  ptrdiff_t lo[OG_MAX_ST];
+  og_lin_offsets(n, st, lo);
+  const size_t size = og_size(n);
+  const int nst = st->nst;
+  const int c = og_centre(st);
+  const double wconst = omega / st->coef[c];
+  OG_LOOP_BEGIN(n)
+#pragma omp parallel for schedule(static) collapse(2)
+  for (int k = zl; k < zh; ++k)
+    for (int j = yl; j < yh; ++j) {
+      size_t row = (size_t)n[0] * ((size_t)j + (size_t)n[1] * (size_t)k);
+      /* first i >= xl with (i + j + k) % 2 == color */
+      int i0 = xl + (((xl + j + k) & 1) != color);
+      for (int i = i0; i < xh; i += 2) {
+        size_t p = row + i;
+        double w = sf ? omega / sf[(size_t)c * size + p] : wconst;
+        double r = rhs[p] - og_conv(nst, lo, st->coef, sf, size, u, p);
+        u[p] = fma(w, r, u[p]);
+      }
+    }
+}
+
+/* ---------- reductions ---------------------------------------------------- */
+
+/* double-double accumulator: (hi, lo) += x via Knuth TwoSum */
+typedef struct { double hi, lo; } og_dd;
+
+static inline void og_dd_add(og_dd *a, double x) {
+  double s = a->hi + x;
+  double bb = s - a->hi;
+  double err = (a->hi - (s - bb)) + (x - bb);
+  a->hi = s;
+  a->lo += err;
+}
+
+static inline void og_dd_merge(og_dd *a, const og_dd *b) {
+  og_dd_add(a, b->hi);
+  a->lo += b->lo;
+}
+
+double og_dot(const int n[3], const double *a, const double *b) {
+  OG_LOOP_BEGIN(n)
+  og_dd total = {0.0, 0.0};
+#pragma omp parallel
+  {
+    og_dd part = {0.0, 0.0};
+#pragma omp for schedule(static) collapse(2) nowait
+    for (int k = zl; k < zh; ++k)
+      for (int j = yl; j < yh; ++j) {
+        size_t row = (size_t)n[0] * ((size_t)j + (size_t)n[1] * (size_t)k);
+        for (int i = xl; i < xh; ++i) og_dd_add(&part, a[row + i] * b[row + i]);
+      }
+#pragma omp critical
+    og_dd_merge(&total, &part);
+  }
+  return total.hi + total.lo;
+}
+
+double og_max_abs_diff(const int n[3], const double *a, const double *b) {
+  OG_LOOP_BEGIN(n)
+  double m = 0.0;
+#pragma omp parallel for schedule(static) collapse(2) reduction(max : m)
+  for (int k = zl; k < zh; ++k)
+    for (int j = yl; j < yh; ++j) {
+      size_t row = (size_t)n[0] * ((size_t)j + (size_t)n[1] * (size_t)k);
+      for (int i = xl; i < xh; ++i) {
+        double d = fabs(a[row + i] - b[row + i]);
+        if (d > m) m = d;
+      }
+    }
+  return m;
+}
+
+/* ---------- inter-grid transfer ------------------------------------------- */
+
+/*
+ * Full weighting: 1-D [1/4,1/2,1/4] Kronecker product
+ * (L4_DefaultRestriction.scala:29-37,63-90).  The generator normalises the sum
+ * into "coefficient x (sum of terms with that coefficient)"
+ * (C/s/e/optimization/ir/IR_SimplifyExpression.scala:579-881); restated here as
+ * groups by number of non-zero offsets m (weight 2^-(dim+m)), each group summed
+ * in lexicographic (dz,dy,dx) order, then
+ *   acc = w0*S0; acc = fma(w1,S1,acc); acc = fma(w2,S2,acc); acc = fma(w3,S3,acc).
+ */
+void og_restrict(int dim, const int nf[3], const int nc[3], double scale,
+                 const double *rf, double *rhsc) {
+  OG_LOOP_BEGIN(nc)
+  const int dzr = (dim == 3) ? 1 : 0;
+  double w[4];
+  for (int m = 0; m <= 3; ++m) w[m] = scale * ldexp(1.0, -(dim + m));
+#pragma omp parallel for schedule(static) collapse(2)
+  for (int k = zl; k < zh; ++k)
+    for (int j = yl; j < yh; ++j)
+      for (int i = xl; i < xh; ++i) {
+        double S[4] = {0.0, 0.0, 0.0, 0.0};
+        int first[4] = {1, 1, 1, 1};
+        for (int dz = -dzr; dz <= dzr; ++dz)
+          for (int dy = -1; dy <= 1; ++dy)
+            for (int dx = -1; dx <= 1; ++dx) {
+              int m = (dx != 0) + (dy != 0) + (dz != 0);
+              size_t q = (size_t)(2 * i + dx) +
+                         (size_t)nf[0] * ((size_t)(2 * j + dy) +
+                                          (size_t)nf[1] * (size_t)((dim == 3 ? 2 * k : 0) + dz));
+              if (first[m]) { S[m] = rf[q]; first[m] = 0; } else S[m] += rf[q];
+            }
+        double acc = w[0] * S[0];
+        acc = fma(w[1], S[1], acc);
+        acc = fma(w[2], S[2], acc);
+        if (dim == 3) acc = fma(w[3], S[3], acc);
+        rhsc[(size_t)i + (size_t)nc[0] * ((size_t)j + (size_t)nc[1] * (size_t)k)] = acc;
+      }
+}
+
+/*
+ * Trilinear interpolation + correction.  The generator splits the loop into
+ * 2^dim parity cases (C/s/e/stencil/ir/IR_FindStencilConvolutions.scala:122-170).
+ * Restated: s = sum of the 2^m contributing coarse values (m = number of odd
+ * fine indices) in lexicographic (z,y,x) order; uf = fma(2^-m, s, uf).
+ */
+void og_prolong_add(int dim, const int nf[3], const int nc[3], const double *uc,
+                    double *uf) {
+  OG_LOOP_BEGIN(nf)
+#pragma omp parallel for schedule(static) collapse(2)
+  for (int k = zl; k < zh; ++k)
+    for (int j = yl; j < yh; ++j)
+      for (int i = xl; i < xh; ++i) {
+        int ox = i & 1, oy = j & 1, oz = (dim == 3) ? (k & 1) : 0;
+        int ci = i >> 1, cj = j >> 1, ck = (dim == 3) ? (k >> 1) : 0;
+        double s = 0.0;
+        int first = 1;
+        for (int dz = 0; dz <= oz; ++dz)
+          for (int dy = 0; dy <= oy; ++dy)
+            for (int dx = 0; dx <= ox; ++dx) {
+              double v = uc[(size_t)(ci + dx) +
+                            (size_t)nc[0] * ((size_t)(cj + dy) + (size_t)nc[1] * (size_t)(ck + dz))];
+              if (first) { s = v; first = 0; } else s += v;
+            }
+        size_t p = (size_t)i + (size_t)nf[0] * ((size_t)j + (size_t)nf[1] * (size_t)k);
+        uf[p] = fma(ldexp(1.0, -(ox + oy + oz)), s, uf[p]);
+      }
+}
+
+/* ---------- streaming loops ----------------------------------------------- */
+
+void og_set_interior(const int n[3], double *a, double v) {
+  OG_LOOP_BEGIN(n)
+#pragma omp parallel for schedule(static) collapse(2)
+  for (int k = zl; k < zh; ++k)
+    for (int j = yl; j < yh; ++j) {
+      size_t row = (size_t)n[0] * ((size_t)j + (size_t)n[1] * (size_t)k);
+      for (int i = xl; i < xh; ++i) a[row + i] = v;
+    }
+}
+
+void og_copy_interior(const int n[3], const double *src, double *dst) {
+  OG_LOOP_BEGIN(n)
+#pragma omp parallel for schedule(static) collapse(2)
+  for (int k = zl; k < zh; ++k)
+    for (int j = yl; j < yh; ++j) {
+      size_t row = (size_t)n[0] * ((size_t)j + (size_t)n[1] * (size_t)k);
+      for (int i = xl; i < xh; ++i) dst[row + i] = src[row + i];
+    }
+}
+
+void og_axpy(const int n[3], double alpha, const double *x, double *y) {
+  OG_LOOP_BEGIN(n)
+#pragma omp parallel for schedule(static) collapse(2)
+  for (int k = zl; k < zh; ++k)
+    for (int j = yl; j < yh; ++j) {
+      size_t row = (size_t)n[0] * ((size_t)j + (size_t)n[1] * (size_t)k);
+      for (int i = xl; i < xh; ++i) y[row + i] = fma(alpha, x[row + i], y[row + i]);
+    }
+}
+
+void og_xpay(const int n[3], const double *x, double beta, double *y) {
+  OG_LOOP_BEGIN(n)
+#pragma omp parallel for schedule(static) collapse(2)
+  for (int k = zl; k < zh; ++k)
+    for (int j = yl; j < yh; ++j) {
+      size_t row = (size_t)n[0] * ((size_t)j + (size_t)n[1] * (size_t)k);
+      for (int i = xl; i < xh; ++i) y[row + i] = fma(beta, y[row + i], x[row + i]);
+    }
+}

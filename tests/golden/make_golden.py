@@ -1,0 +1,31 @@
+#!/usr/bin/env python
+"""Copies the reference's own golden stdout vectors (Testing/**/*.results) into
+tests/golden/.  Run in the build container (where /root/reference is mounted);
+the fixtures are committed because /root/reference does not exist on the GPU box.
+
+These files are data (expected residual / error histories printed with
+printWithReducedPrec, 4 significant digits), not source code.
+"""
+import os
+import shutil
+import sys
+
+REF = sys.argv[1] if len(sys.argv) > 1 else "/root/reference"
+HERE = os.path.dirname(os.path.abspath(__file__))
+
+FILES = {
+    "Poisson_2D_FD_Poisson_fromL4": "Testing/Poisson/2D_FD_Poisson_fromL4.results",
+    "Smoothers_RBGS": "Testing/Smoothers/RBGS.results",
+    "Smoothers_Jac": "Testing/Smoothers/Jac.results",
+    "SISC_3D_ConstCoeff": "Testing/SISC/3D_ConstCoeff.results",
+    "SISC_3D_VarCoeff": "Testing/SISC/3D_VarCoeff.results",
+    "SISC_2D_ConstCoeff": "Testing/SISC/2D_ConstCoeff.results",
+    "SISC_2D_VarCoeff": "Testing/SISC/2D_VarCoeff.results",
+    "Opts_seq": "Testing/Opts/seq.results",
+    "Application_OpticalFlow2D": "Testing/Application/OpticalFlow2D.results",
+}
+
+if __name__ == "__main__":
+    for name, rel in FILES.items():
+        shutil.copyfile(os.path.join(REF, rel), os.path.join(HERE, name + ".results"))
+        print("copied", rel)

@@ -1,0 +1,178 @@
+"""The reference's regression programs restated as data: configuration, initial
+fields, what is printed per iteration and the golden stdout (4 s.f.) copied from
+the reference's `.results` files (see tests/golden/README.md).
+
+Used by the oracle-vs-golden tests (CPU) and the CUDA-vs-oracle parity tests (GPU),
+so both sides run exactly the same program.
+"""
+import math
+import os
+
+import numpy as np
+
+GOLDEN_DIR = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+
+
+def golden(name):
+    with open(os.path.join(GOLDEN_DIR, name + ".results")) as f:
+        return f.read().split()
+
+
+def _grid(pos, dim):
+    """Broadcastable node-position arrays X, Y[, Z] for arrays shaped (nz, ny, nx)."""
+    x, y, z = pos
+    X = x[None, None, :]
+    Y = y[None, :, None]
+    Z = z[:, None, None]
+    return X, Y, Z
+
+
+def _set_boundary(u, vals, dim):
+    """`apply bc`: Dirichlet value on physical-boundary nodes only
+    (C/s/e/boundary/ir/IR_DirichletBC.scala:37-40)."""
+    vals = np.broadcast_to(vals, u.shape)
+    u[:, :, 0] = vals[:, :, 0]
+    u[:, :, -1] = vals[:, :, -1]
+    u[:, 0, :] = vals[:, 0, :]
+    u[:, -1, :] = vals[:, -1, :]
+    if dim == 3:
+        u[0, :, :] = vals[0, :, :]
+        u[-1, :, :] = vals[-1, :, :]
+
+
+def _interior(dim):
+    return (slice(1, -1),) * 3 if dim == 3 else (slice(None), slice(1, -1), slice(1, -1))
+
+
+class Program:
+    """One reference test program."""
+
+    def __init__(self, name, golden_name, cfg, rhs=None, bc=None, exact=None, init=None,
+                 tol=1e-5, strict=True, prints="res", print_count=True, max_it=100):
+        self.name, self.golden_name, self.cfg = name, golden_name, cfg
+        self.rhs, self.bc, self.exact, self.init = rhs, bc, exact, init
+        self.tol, self.strict, self.prints, self.print_count, self.max_it = tol, strict, prints, print_count, max_it
+
+    @property
+    def dim(self):
+        return self.cfg["dim"]
+
+    def expected(self):
+        return golden(self.golden_name)
+
+    def setup(self, solver):
+        """Fill RHS@finest, Solution@finest (interior + Dirichlet nodes) of any
+        solver exposing .max_level, .node_positions(lvl), .solution(lvl), .rhs(lvl)."""
+        lvl = solver.max_level
+        X, Y, Z = _grid(solver.node_positions(lvl), self.dim)
+        u = solver.solution(lvl)
+        f = solver.rhs(lvl)
+        inner = _interior(self.dim)
+        if self.rhs is not None:
+            f[inner] = np.broadcast_to(self.rhs(X, Y, Z), f.shape)[inner]
+        if self.init is not None:
+            u[inner] = self.init(u[inner].shape)
+        if self.bc is not None:
+            _set_boundary(u, self.bc(X, Y, Z), self.dim)
+        self._exact = None
+        if self.exact is not None:
+            self._exact = np.ascontiguousarray(np.broadcast_to(self.exact(X, Y, Z), u.shape))
+
+    def converged(self, res, init_res):
+        return res < self.tol * init_res if self.strict else res <= self.tol * init_res
+
+
+PI = math.pi
+
+# Examples/Poisson/2D_FD_Poisson_fromL4.exa4 run by Testing/Poisson/2D_FD_Poisson_fromL4.knowledge
+# (2x2 blocks x 2x2 fragments, levels 0-8  ==  global grid F=4, levels 0-8)
+POISSON_2D = Program(
+    "Poisson2D_fromL4", "Poisson_2D_FD_Poisson_fromL4",
+    dict(dim=2, F=(4, 4), min_level=0, max_level=8, op="scaled", order="bench", smoother="rbgs", omega=0.8,
+         nu_pre=3, nu_post=3, restrict_scale=1.0, cg_max_it=128, cg_rel_tol=1e-3),
+    rhs=lambda X, Y, Z: PI ** 2 * np.cos(PI * X) - 4.0 * PI ** 2 * np.sin(2.0 * PI * Y),
+    bc=lambda X, Y, Z: np.cos(PI * X) - np.sin(2.0 * PI * Y),
+    exact=lambda X, Y, Z: np.cos(PI * X) - np.sin(2.0 * PI * Y),
+    tol=1e-10, strict=False, prints="err+res", print_count=False)
+
+_quad_bc = lambda X, Y, Z: ((X * X) - ((0.5 * Y) * Y)) - ((0.5 * Z) * Z)
+
+# Testing/Smoothers/RBGS.{exa4,knowledge}: 3x3x3 blocks x 3x3x3 fragments, levels 0-6 => F=9
+SMOOTHERS_RBGS = Program(
+    "Smoothers_RBGS", "Smoothers_RBGS",
+    dict(dim=3, F=(9, 9, 9), min_level=0, max_level=6, op="unscaled", order="testing", smoother="rbgs",
+         omega=1.0, nu_pre=3, nu_post=3, restrict_scale=4.0, cg_max_it=512, cg_rel_tol=1e-3),
+    bc=_quad_bc)
+
+# Testing/Smoothers/Jac.{exa4,knowledge}
+SMOOTHERS_JAC = Program(
+    "Smoothers_Jac", "Smoothers_Jac",
+    dict(dim=3, F=(9, 9, 9), min_level=0, max_level=6, op="unscaled", order="testing", smoother="jacobi",
+         omega=0.8, nu_pre=3, nu_post=3, restrict_scale=4.0, cg_max_it=512, cg_rel_tol=1e-3),
+    bc=_quad_bc)
+
+KAPPA = 10.0
+_b3 = lambda X, Y, Z: ((X - X ** 2) * (Y - Y ** 2)) * (Z - Z ** 2)
+_b2 = lambda X, Y, Z: (X - X ** 2) * (Y - Y ** 2)
+_rhs3 = lambda X, Y, Z: (2.0 * KAPPA) * ((((X - X ** 2) * (Y - Y ** 2)) + ((X - X ** 2) * (Z - Z ** 2)))
+                                         + ((Y - Y ** 2) * (Z - Z ** 2)))
+_rhs2 = lambda X, Y, Z: (2.0 * KAPPA) * ((X - X ** 2) + (Y - Y ** 2))
+
+# Testing/SISC/3D_ConstCoeff: 2^3 blocks x 2^3 frags x fragLen 2 => F=8, levels 0-5 (256^3 cells)
+SISC_3D_CONST = Program(
+    "SISC_3D_ConstCoeff", "SISC_3D_ConstCoeff",
+    dict(dim=3, F=(8, 8, 8), min_level=0, max_level=5, op="scaled", order="testing", smoother="jacobi", omega=0.85,
+         nu_pre=3, nu_post=3, restrict_scale=1.0, cg_max_it=1024, cg_rel_tol=1e-3),
+    rhs=_rhs3, bc=lambda X, Y, Z: KAPPA * _b3(X, Y, Z), exact=lambda X, Y, Z: KAPPA * _b3(X, Y, Z),
+    prints="err")
+
+SISC_3D_VAR = Program(
+    "SISC_3D_VarCoeff", "SISC_3D_VarCoeff",
+    dict(dim=3, F=(8, 8, 8), min_level=0, max_level=5, op="varcoeff", order="testing", kappa=KAPPA,
+         smoother="jacobi", omega=0.85, nu_pre=3, nu_post=3, restrict_scale=1.0, cg_max_it=1024, cg_rel_tol=1e-3),
+    rhs=_rhs3, bc=lambda X, Y, Z: 1.0 - np.exp((-1.0 * KAPPA) * _b3(X, Y, Z)),
+    exact=lambda X, Y, Z: 1.0 - np.exp((-1.0 * KAPPA) * _b3(X, Y, Z)), prints="err")
+
+# Testing/SISC/2D_*: 2x2 blocks x 2x2 frags x fragLen 2 => F=8, levels 2-7
+SISC_2D_CONST = Program(
+    "SISC_2D_ConstCoeff", "SISC_2D_ConstCoeff",
+    dict(dim=2, F=(8, 8), min_level=2, max_level=7, op="scaled", order="testing", smoother="jacobi", omega=0.79,
+         nu_pre=3, nu_post=3, restrict_scale=1.0, cg_max_it=1024, cg_rel_tol=1e-3),
+    rhs=_rhs2, bc=lambda X, Y, Z: KAPPA * _b2(X, Y, Z), exact=lambda X, Y, Z: KAPPA * _b2(X, Y, Z),
+    prints="err")
+
+SISC_2D_VAR = Program(
+    "SISC_2D_VarCoeff", "SISC_2D_VarCoeff",
+    dict(dim=2, F=(8, 8), min_level=2, max_level=7, op="varcoeff", order="testing", kappa=KAPPA,
+         smoother="jacobi", omega=0.79, nu_pre=3, nu_post=3, restrict_scale=1.0, cg_max_it=1024, cg_rel_tol=1e-3),
+    rhs=_rhs2, bc=lambda X, Y, Z: 1.0 - np.exp((-1.0 * KAPPA) * _b2(X, Y, Z)),
+    exact=lambda X, Y, Z: 1.0 - np.exp((-1.0 * KAPPA) * _b2(X, Y, Z)), prints="err")
+
+ALL = [POISSON_2D, SMOOTHERS_RBGS, SMOOTHERS_JAC, SISC_3D_CONST, SISC_3D_VAR, SISC_2D_CONST, SISC_2D_VAR]
+
+
+def run_solve(prog, solver, printer, max_abs_err=None):
+    """Solve@finest of the program: returns the list of printed tokens.
+
+    solver: .update_residual_norm(), .vcycle(), .solution(lvl), .max_level
+    printer: printWithReducedPrec restatement (value -> str)
+    max_abs_err: callable(solution_array, exact_array) -> float (NormError / PrintError)
+    """
+    out = []
+    init_res = solver.update_residual_norm()
+    out.append(printer(init_res))
+    res = init_res
+    it = 0
+    while not (it >= prog.max_it or prog.converged(res, init_res)):
+        it += 1
+        solver.vcycle()
+        if prog.prints == "err+res":  # PrintError precedes the residual update in 2D_FD_Poisson_fromL4
+            out.append(printer(max_abs_err(solver.solution(solver.max_level), prog._exact)))
+        res = solver.update_residual_norm()
+        if prog.prints == "err":
+            out.append(printer(max_abs_err(solver.solution(solver.max_level), prog._exact)))
+        else:
+            out.append(printer(res))
+    if prog.print_count:
+        out.append(str(it))
+    return out
