@@ -1,0 +1,410 @@
+// examg_core.cu -- lifecycle, fields, stencils, host<->device copies of libexamg.
+//
+// Replaces what the reference generator prints into Global/Global_initGlobals.cpp,
+// Domain/Domain_initDomain.cpp and setupBuffers():
+//   C/s/e/domain/ir/IR_InitGeneratedDomain.scala:40-104   (rank -> block, positions)
+//   C/s/e/domain/ir/IR_ConnectFragments.scala:60-93        (neighbours, iteration offsets)
+//   C/s/e/globals/ir/IR_AllocateDataFunction.scala:64-72   (allocation)
+//   C/s/e/field/ir/IR_FieldLayout.scala:30-129             (layout; redesigned, see examg_internal.h)
+#include <cstring>
+
+#include "examg_internal.h"
+
+using namespace examg;
+
+static thread_local char g_err[512] = "";
+
+int examg::set_error(int code, const char *fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+  return code;
+}
+
+const LevelGeom *examg::geom(examg_ctx *c, int level) {
+  if (!c || level < c->cfg.min_level || level > c->cfg.max_level) return nullptr;
+  return &c->levels[level - c->cfg.min_level];
+}
+
+Field *examg::get_field(examg_ctx *c, int h) {
+  if (!c || h < 0 || h >= (int)c->fields.size() || !c->fields[h].alive) return nullptr;
+  return &c->fields[h];
+}
+
+Stencil *examg::get_stencil(examg_ctx *c, int h) {
+  if (!c || h < 0 || h >= (int)c->stencils.size()) return nullptr;
+  return &c->stencils[h];
+}
+
+GridArgs examg::grid_args(const LevelGeom &g) {
+  GridArgs a;
+  for (int d = 0; d < 3; ++d) { a.n[d] = g.n[d]; a.lo[d] = g.lo[d]; a.hi[d] = g.hi[d]; a.rlo[d] = g.rlo[d]; }
+  a.pitch = g.pitch;
+  a.plane = g.plane;
+  a.par = g.par;
+  return a;
+}
+
+StencilArgs examg::stencil_args(const LevelGeom &g, const Stencil &s) {
+  StencilArgs a;
+  a.nst = s.nst;
+  a.centre = s.centre;
+  for (int k = 0; k < EXAMG_MAX_STENCIL; ++k) { a.lin[k] = 0; a.coef[k] = 0.0; }
+  for (int k = 0; k < s.nst; ++k) {
+    a.lin[k] = (long long)s.off[k][0] + (long long)g.pitch * s.off[k][1] + g.plane * s.off[k][2];
+    a.coef[k] = s.coef[k];
+  }
+  return a;
+}
+
+extern "C" {
+
+int examg_abi_version(void) { return EXAMG_ABI_VERSION; }
+const char *examg_last_error(void) { return g_err; }
+
+examg_ctx *examg_init(const examg_config *cfg) {
+  if (!cfg || (cfg->dim != 2 && cfg->dim != 3) || cfg->min_level < 0 || cfg->max_level < cfg->min_level ||
+      cfg->max_level > 14) {
+    set_error(EXAMG_EINVAL, "examg_init: bad dimensionality or level range");
+    return nullptr;
+  }
+  int world = 1;
+  for (int d = 0; d < cfg->dim; ++d) {
+    if (cfg->block_cells[d] < 1 || cfg->num_blocks[d] < 1) {
+      set_error(EXAMG_EINVAL, "examg_init: block_cells/num_blocks must be >= 1");
+      return nullptr;
+    }
+    world *= cfg->num_blocks[d];
+  }
+  if (cfg->rank < 0 || cfg->rank >= world) {
+    // reference: "Invalid number of MPI processes" assert, IR_InitGeneratedDomain.scala:83-85
+    set_error(EXAMG_EINVAL, "examg_init: rank %d outside the %d blocks of the domain", cfg->rank, world);
+    return nullptr;
+  }
+  int ndev = 0;
+  cudaError_t e = cudaGetDeviceCount(&ndev);
+  if (e != cudaSuccess || ndev < 1) {
+    set_error(EXAMG_ECUDA, "examg_init: no CUDA device (%s); libexamg has no CPU path",
+              e == cudaSuccess ? "count 0" : cudaGetErrorString(e));
+    return nullptr;
+  }
+  if (cfg->device < 0 || cfg->device >= ndev) {
+    set_error(EXAMG_EINVAL, "examg_init: device %d of %d", cfg->device, ndev);
+    return nullptr;
+  }
+  if (cudaSetDevice(cfg->device) != cudaSuccess) {
+    set_error(EXAMG_ECUDA, "examg_init: cudaSetDevice failed");
+    return nullptr;
+  }
+  examg_ctx *c = new examg_ctx();
+  c->cfg = *cfg;
+  c->device = cfg->device;
+  c->world = world;
+  int r = cfg->rank;
+  for (int d = 0; d < 3; ++d) {
+    int nbk = d < cfg->dim ? cfg->num_blocks[d] : 1;
+    c->bidx[d] = r % nbk;
+    r /= nbk;
+    c->nb[d][0] = c->bidx[d] > 0;
+    c->nb[d][1] = c->bidx[d] < nbk - 1;
+  }
+  for (int lvl = cfg->min_level; lvl <= cfg->max_level; ++lvl) {
+    LevelGeom g;
+    for (int d = 0; d < 3; ++d) {
+      if (d < cfg->dim) {
+        int cells = cfg->block_cells[d] << lvl;
+        g.n[d] = cells + 1;
+        g.lo[d] = c->nb[d][0] ? 0 : 1;
+        g.hi[d] = c->nb[d][1] ? g.n[d] : g.n[d] - 1;
+        g.rlo[d] = 1;
+        g.goff[d] = c->bidx[d] * cells;
+        g.h[d] = (cfg->domain_hi[d] - cfg->domain_lo[d]) / (double)(cells * cfg->num_blocks[d]);
+      } else {
+        g.n[d] = 1; g.lo[d] = 0; g.hi[d] = 1; g.rlo[d] = 0; g.goff[d] = 0; g.h[d] = 1.0;
+      }
+    }
+    g.pitch = ((XPAD + g.n[0] + 1) + 15) / 16 * 16;
+    g.ay = g.n[1] + 2;
+    g.az = cfg->dim == 3 ? g.n[2] + 2 : 1;
+    g.plane = (long long)g.pitch * g.ay;
+    g.vol = g.plane * g.az;
+    g.origin = XPAD + (long long)g.pitch + (cfg->dim == 3 ? g.plane : 0);
+    g.par = (g.goff[0] + g.goff[1] + g.goff[2]) & 1;
+    c->levels.push_back(g);
+  }
+  if (cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) != cudaSuccess) {
+    set_error(EXAMG_ECUDA, "examg_init: cudaStreamCreate failed");
+    delete c;
+    return nullptr;
+  }
+  c->own_stream = true;
+  bool ok = cudaMalloc(&c->partials, sizeof(dd) * PARTIAL_CAP) == cudaSuccess &&
+            cudaMalloc(&c->red_out, sizeof(dd) * RED_SLOTS) == cudaSuccess &&
+            cudaMallocHost(&c->red_host, sizeof(dd) * RED_SLOTS) == cudaSuccess &&
+            cudaMalloc(&c->int_out, sizeof(int) * 8) == cudaSuccess &&
+            cudaMallocHost(&c->int_host, sizeof(int) * 8) == cudaSuccess;
+  if (!ok) {
+    set_error(EXAMG_ENOMEM, "examg_init: scratch allocation failed");
+    examg_finalize(c);
+    return nullptr;
+  }
+  cudaMemset(c->red_out, 0, sizeof(dd) * RED_SLOTS);
+  cudaMemset(c->int_out, 0, sizeof(int) * 8);
+  c->dev_bytes += sizeof(dd) * (PARTIAL_CAP + RED_SLOTS);
+  return c;
+}
+
+int examg_finalize(examg_ctx *c) {
+  if (!c) return set_error(EXAMG_EINVAL, "examg_finalize: null context");
+  cudaSetDevice(c->device);
+  cudaDeviceSynchronize();
+  for (auto &f : c->fields)
+    if (f.alive && f.base) cudaFree(f.base);
+  if (c->partials) cudaFree(c->partials);
+  if (c->red_out) cudaFree(c->red_out);
+  if (c->red_host) cudaFreeHost(c->red_host);
+  if (c->int_out) cudaFree(c->int_out);
+  if (c->int_host) cudaFreeHost(c->int_host);
+  if (c->own_stream && c->stream) cudaStreamDestroy(c->stream);
+  delete c;
+  return EXAMG_OK;
+}
+
+int examg_set_stream(examg_ctx *c, void *s) {
+  if (!c) return set_error(EXAMG_EINVAL, "null context");
+  EXAMG_CUDA(cudaStreamSynchronize(c->stream));
+  if (s) {
+    if (c->own_stream) cudaStreamDestroy(c->stream);
+    c->stream = (cudaStream_t)s;
+    c->own_stream = false;
+  } else if (!c->own_stream) {
+    EXAMG_CUDA(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+    c->own_stream = true;
+  }
+  return EXAMG_OK;
+}
+
+int examg_sync(examg_ctx *c) {
+  if (!c) return set_error(EXAMG_EINVAL, "null context");
+  EXAMG_CUDA(cudaStreamSynchronize(c->stream));
+  return EXAMG_OK;
+}
+
+int examg_level_dims(examg_ctx *c, int level, int n[3]) {
+  const LevelGeom *g = geom(c, level);
+  if (!g) return set_error(EXAMG_EINVAL, "examg_level_dims: level %d", level);
+  for (int d = 0; d < 3; ++d) n[d] = g->n[d];
+  return EXAMG_OK;
+}
+
+int examg_level_width(examg_ctx *c, int level, double h[3]) {
+  const LevelGeom *g = geom(c, level);
+  if (!g) return set_error(EXAMG_EINVAL, "examg_level_width: level %d", level);
+  for (int d = 0; d < 3; ++d) h[d] = g->h[d];
+  return EXAMG_OK;
+}
+
+long long examg_launch_count(examg_ctx *c) { return c ? c->launches : -1; }
+long long examg_device_bytes(examg_ctx *c) { return c ? c->dev_bytes : -1; }
+
+// ---- fields -------------------------------------------------------------------
+
+int examg_field_create(examg_ctx *c, const char *name, int level, int num_slots, int ncomp) {
+  const LevelGeom *g = geom(c, level);
+  if (!g) return set_error(EXAMG_EINVAL, "examg_field_create: level %d", level);
+  if (num_slots < 1 || num_slots > 4 || ncomp < 1 || ncomp > EXAMG_MAX_STENCIL)
+    return set_error(EXAMG_EINVAL, "examg_field_create: slots %d comps %d", num_slots, ncomp);
+  Field f;
+  f.alive = true;
+  f.name = name ? name : "";
+  f.level = level;
+  f.nslots = num_slots;
+  f.ncomp = ncomp;
+  size_t bytes = sizeof(double) * (size_t)num_slots * ncomp * g->vol;
+  cudaError_t e = cudaMalloc(&f.base, bytes);
+  if (e != cudaSuccess)
+    return set_error(EXAMG_ENOMEM, "examg_field_create(%s@%d): cudaMalloc of %zu bytes: %s", f.name.c_str(),
+                     level, bytes, cudaGetErrorString(e));
+  EXAMG_CUDA(cudaMemsetAsync(f.base, 0, bytes, c->stream));  // initFieldsWithZero
+  c->dev_bytes += (long long)bytes;
+  c->fields.push_back(f);
+  return (int)c->fields.size() - 1;
+}
+
+int examg_field_destroy(examg_ctx *c, int h) {
+  Field *f = get_field(c, h);
+  if (!f) return set_error(EXAMG_EINVAL, "examg_field_destroy: handle %d", h);
+  EXAMG_CUDA(cudaStreamSynchronize(c->stream));
+  const LevelGeom *g = geom(c, f->level);
+  c->dev_bytes -= (long long)sizeof(double) * f->nslots * f->ncomp * g->vol;
+  cudaFree(f->base);
+  f->base = nullptr;
+  f->alive = false;
+  return EXAMG_OK;
+}
+
+int examg_field_num_slots(examg_ctx *c, int h) {
+  Field *f = get_field(c, h);
+  return f ? f->nslots : set_error(EXAMG_EINVAL, "bad field %d", h);
+}
+int examg_field_active_slot(examg_ctx *c, int h) {
+  Field *f = get_field(c, h);
+  return f ? f->cur : set_error(EXAMG_EINVAL, "bad field %d", h);
+}
+int examg_field_advance(examg_ctx *c, int h) {
+  Field *f = get_field(c, h);
+  if (!f) return set_error(EXAMG_EINVAL, "bad field %d", h);
+  f->cur = (f->cur + 1) % f->nslots;
+  return EXAMG_OK;
+}
+
+int examg_field_set_bc(examg_ctx *c, int h, int kind, double value) {
+  Field *f = get_field(c, h);
+  if (!f) return set_error(EXAMG_EINVAL, "bad field %d", h);
+  if (kind != EXAMG_BC_NONE && kind != EXAMG_BC_DIRICHLET_CONST && kind != EXAMG_BC_DIRICHLET_HOST)
+    return set_error(EXAMG_EINVAL, "examg_field_set_bc: kind %d (use examg_field_set_bc_expr for programs)", kind);
+  f->bc_kind = kind;
+  f->bc_value = value;
+  f->bc_prog.clear();
+  return EXAMG_OK;
+}
+
+int examg_field_set_bc_expr(examg_ctx *c, int h, const examg_bc_op *prog, int n) {
+  Field *f = get_field(c, h);
+  if (!f) return set_error(EXAMG_EINVAL, "bad field %d", h);
+  if (!prog || n < 1 || n > 64) return set_error(EXAMG_EINVAL, "examg_field_set_bc_expr: 1..64 ops");
+  int depth = 0;  // validate the postfix program on the host so the device never has to
+  for (int i = 0; i < n; ++i) {
+    switch (prog[i].op) {
+      case EXAMG_OP_CONST: case EXAMG_OP_X: case EXAMG_OP_Y: case EXAMG_OP_Z: ++depth; break;
+      case EXAMG_OP_ADD: case EXAMG_OP_SUB: case EXAMG_OP_MUL: case EXAMG_OP_DIV:
+        if (depth < 2) return set_error(EXAMG_EINVAL, "bc program: stack underflow at op %d", i);
+        --depth; break;
+      case EXAMG_OP_NEG:
+        if (depth < 1) return set_error(EXAMG_EINVAL, "bc program: stack underflow at op %d", i);
+        break;
+      default: return set_error(EXAMG_EINVAL, "bc program: unknown op %d", prog[i].op);
+    }
+    if (depth > 16) return set_error(EXAMG_EINVAL, "bc program: stack deeper than 16");
+  }
+  if (depth != 1) return set_error(EXAMG_EINVAL, "bc program leaves %d values", depth);
+  f->bc_kind = EXAMG_BC_DIRICHLET_EXPR;
+  f->bc_prog.assign(prog, prog + n);
+  return EXAMG_OK;
+}
+
+int examg_apply_bc(examg_ctx *c, int h, int slot) {
+  Field *f = get_field(c, h);
+  if (!f) return set_error(EXAMG_EINVAL, "bad field %d", h);
+  if (slot >= f->nslots) return set_error(EXAMG_EINVAL, "bad slot %d", slot);
+  if (f->bc_kind == EXAMG_BC_NONE || f->bc_kind == EXAMG_BC_DIRICHLET_HOST) return EXAMG_OK;
+  return launch_bc(c, *f, slot);
+}
+
+static int copy_field(examg_ctx *c, int h, int slot, double *host, bool up, bool async) {
+  Field *f = get_field(c, h);
+  if (!f) return set_error(EXAMG_EINVAL, "bad field %d", h);
+  if (!host) return set_error(EXAMG_EINVAL, "null host pointer");
+  if (slot >= f->nslots) return set_error(EXAMG_EINVAL, "bad slot %d", slot);
+  const LevelGeom &g = *geom(c, f->level);
+  for (int comp = 0; comp < f->ncomp; ++comp) {
+    double *dev = field_ptr(c, f, slot, comp);
+    double *hp = host + (size_t)comp * g.n[0] * g.n[1] * g.n[2];
+    cudaMemcpy3DParms p;
+    memset(&p, 0, sizeof(p));
+    // device: rows of `pitch` doubles, `ay` rows per plane; node (0,0,0) at dev
+    cudaPitchedPtr dp = make_cudaPitchedPtr(dev, sizeof(double) * g.pitch, g.n[0], g.ay);
+    cudaPitchedPtr hpp = make_cudaPitchedPtr(hp, sizeof(double) * g.n[0], g.n[0], g.n[1]);
+    p.srcPtr = up ? hpp : dp;
+    p.dstPtr = up ? dp : hpp;
+    p.extent = make_cudaExtent(sizeof(double) * g.n[0], g.n[1], g.n[2]);
+    p.kind = up ? cudaMemcpyHostToDevice : cudaMemcpyDeviceToHost;
+    EXAMG_CUDA(cudaMemcpy3DAsync(&p, c->stream));
+  }
+  if (!async) EXAMG_CUDA(cudaStreamSynchronize(c->stream));
+  return EXAMG_OK;
+}
+
+int examg_field_upload(examg_ctx *c, int h, int slot, const double *host) {
+  return copy_field(c, h, slot, const_cast<double *>(host), true, false);
+}
+int examg_field_download(examg_ctx *c, int h, int slot, double *host) {
+  return copy_field(c, h, slot, host, false, false);
+}
+int examg_field_upload_async(examg_ctx *c, int h, int slot, const double *host) {
+  return copy_field(c, h, slot, const_cast<double *>(host), true, true);
+}
+int examg_field_download_async(examg_ctx *c, int h, int slot, double *host) {
+  return copy_field(c, h, slot, host, false, true);
+}
+
+int examg_field_fill(examg_ctx *c, int h, double value) {
+  Field *f = get_field(c, h);
+  if (!f) return set_error(EXAMG_EINVAL, "bad field %d", h);
+  const LevelGeom &g = *geom(c, f->level);
+  size_t count = (size_t)f->nslots * f->ncomp * g.vol;
+  if (value == 0.0) {
+    EXAMG_CUDA(cudaMemsetAsync(f->base, 0, sizeof(double) * count, c->stream));
+    return EXAMG_OK;
+  }
+  // cudaMemset2D-style fill through the D32 memset is not available for doubles: stage one row
+  std::vector<double> row(g.pitch, value);
+  EXAMG_CUDA(cudaMemcpyAsync(f->base, row.data(), sizeof(double) * g.pitch, cudaMemcpyHostToDevice, c->stream));
+  EXAMG_CUDA(cudaStreamSynchronize(c->stream));
+  for (size_t done = g.pitch; done < count;) {  // doubling copy
+    size_t chunk = done < count - done ? done : count - done;
+    EXAMG_CUDA(cudaMemcpyAsync(f->base + done, f->base, sizeof(double) * chunk, cudaMemcpyDeviceToDevice, c->stream));
+    done += chunk;
+  }
+  return EXAMG_OK;
+}
+
+// ---- stencils -----------------------------------------------------------------
+
+static int add_stencil(examg_ctx *c, int level, int n, const int (*off)[3], const double *coef, int cf) {
+  const LevelGeom *g = geom(c, level);
+  if (!g) return set_error(EXAMG_EINVAL, "stencil: level %d", level);
+  if (n < 1 || n > EXAMG_MAX_STENCIL || !off) return set_error(EXAMG_EINVAL, "stencil: %d entries", n);
+  Stencil s;
+  s.level = level;
+  s.nst = n;
+  s.centre = -1;
+  s.coeff_field = cf;
+  for (int k = 0; k < n; ++k) {
+    for (int d = 0; d < 3; ++d) {
+      s.off[k][d] = off[k][d];
+      if (off[k][d] < -1 || off[k][d] > 1 || (d >= c->cfg.dim && off[k][d] != 0))
+        return set_error(EXAMG_EUNSUP, "stencil: offset %d of entry %d outside the compact 3^d box", off[k][d], k);
+    }
+    s.coef[k] = coef ? coef[k] : 0.0;
+    if (!off[k][0] && !off[k][1] && !off[k][2]) s.centre = k;
+  }
+  if (s.centre < 0) return set_error(EXAMG_EINVAL, "stencil without centre entry (diag() undefined)");
+  s.is7 = false;
+  if (cf < 0 && c->cfg.dim == 3 && n == 7) {
+    int seen = 0;
+    for (int k = 0; k < n; ++k) {
+      int nz = (off[k][0] != 0) + (off[k][1] != 0) + (off[k][2] != 0);
+      if (nz <= 1) ++seen;
+    }
+    s.is7 = (seen == 7);
+  }
+  c->stencils.push_back(s);
+  return (int)c->stencils.size() - 1;
+}
+
+int examg_stencil_const(examg_ctx *c, int level, int n, const int (*off)[3], const double *coef) {
+  if (!coef) return set_error(EXAMG_EINVAL, "examg_stencil_const: null coefficients");
+  return add_stencil(c, level, n, off, coef, -1);
+}
+
+int examg_stencil_field(examg_ctx *c, int level, int n, const int (*off)[3], int cf) {
+  Field *f = get_field(c, cf);
+  if (!f || f->level != level || f->ncomp != n)
+    return set_error(EXAMG_EINVAL, "examg_stencil_field: coefficient field must live on level %d with %d components",
+                     level, n);
+  return add_stencil(c, level, n, off, nullptr, cf);
+}
+
+}  // extern "C"

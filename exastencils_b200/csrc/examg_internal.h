@@ -1,0 +1,160 @@
+// examg_internal.h -- data structures shared by the translation units of libexamg.
+// Not part of the ABI (include/examg.h is).
+#pragma once
+
+#include <cuda_runtime.h>
+
+#include <cstdarg>
+#include <cstdint>
+#include <cstdio>
+#include <string>
+#include <vector>
+
+#include "../../include/examg.h"
+
+namespace examg {
+
+// ---------------------------------------------------------------------------
+// HBM layout of one scalar component of a node field on one level
+// (replaces [pad|ghost|dup|inner|dup|ghost|pad]^d of IR_FieldLayout.scala:30-129):
+//
+//   element(i,j,k) = origin + i + pitch*(j + ay*k)       i,j,k in [-1, n_d]
+//
+//   x: XPAD = 16 doubles in front of node 0, so node 0 of every row sits on a
+//      128-byte boundary (the left ghost is element 15 of the pad); pitch is a
+//      multiple of 16 doubles -> rows are 128-byte aligned, which is what TMA
+//      (16 B) and 128-bit vector accesses need.
+//   y,z: one ghost row/plane per side (z only in 3D).
+// ---------------------------------------------------------------------------
+constexpr int XPAD = 16;
+
+struct LevelGeom {
+  int n[3];        // local nodes per dim incl. duplicate/boundary nodes (n[2] = 1 in 2D)
+  int lo[3], hi[3];  // loop range [lo,hi): physical-boundary nodes excluded
+  int rlo[3];      // reduction range lower bound (shared nodes counted once)
+  int goff[3];     // global node index of local node 0
+  int pitch, ay, az;
+  long long plane;  // pitch*ay
+  long long vol;    // pitch*ay*az  (elements per component)
+  long long origin; // element offset of node (0,0,0)
+  double h[3];
+  int par;         // (goff[0]+goff[1]+goff[2]) & 1 : local -> global colour
+};
+
+// Passed by value to kernels.
+struct GridArgs {
+  int n[3];
+  int lo[3], hi[3];
+  int rlo[3];
+  int pitch;
+  long long plane;
+  int par;
+};
+
+struct StencilArgs {
+  int nst;
+  int centre;
+  long long lin[EXAMG_MAX_STENCIL];
+  double coef[EXAMG_MAX_STENCIL];
+};
+
+struct Field {
+  bool alive = false;
+  std::string name;
+  int level = 0, nslots = 1, ncomp = 1, cur = 0;
+  double *base = nullptr;  // nslots*ncomp*vol doubles
+  int bc_kind = EXAMG_BC_NONE;
+  double bc_value = 0.0;
+  std::vector<examg_bc_op> bc_prog;
+};
+
+struct Stencil {
+  int level = 0, nst = 0, centre = 0;
+  int off[EXAMG_MAX_STENCIL][3];
+  double coef[EXAMG_MAX_STENCIL];
+  int coeff_field = -1;  // -1: constant coefficients
+  bool is7 = false;      // 3D 7-point constant stencil (fast path)
+};
+
+struct dd { double hi, lo; };
+
+}  // namespace examg
+
+struct examg_ctx {
+  examg_config cfg;
+  int device = 0;
+  int bidx[3] = {0, 0, 0};  // block index of this rank
+  int world = 1;
+  bool nb[3][2];  // neighbour present on the -/+ side of dim d
+  std::vector<examg::LevelGeom> levels;  // index level - min_level
+  std::vector<examg::Field> fields;
+  std::vector<examg::Stencil> stencils;
+  cudaStream_t stream = nullptr;
+  bool own_stream = false;
+  long long launches = 0;
+  long long dev_bytes = 0;
+  // reduction scratch: per-block partials + final result
+  examg::dd *partials = nullptr;  // PARTIAL_CAP
+  examg::dd *red_out = nullptr;   // RED_SLOTS results on device
+  examg::dd *red_host = nullptr;  // pinned mirror
+  int *int_out = nullptr;         // device ints (cg iterations)
+  int *int_host = nullptr;        // pinned
+  struct examg_comm *comm = nullptr;
+};
+
+namespace examg {
+
+constexpr int PARTIAL_CAP = 1 << 15;
+constexpr int RED_SLOTS = 8;
+
+int set_error(int code, const char *fmt, ...);
+const LevelGeom *geom(examg_ctx *c, int level);
+Field *get_field(examg_ctx *c, int h);
+Stencil *get_stencil(examg_ctx *c, int h);
+inline double *field_ptr(examg_ctx *c, const Field *f, int slot, int comp = 0) {
+  const LevelGeom &g = c->levels[f->level - c->cfg.min_level];
+  if (slot < 0) slot = f->cur;
+  return f->base + ((long long)slot * f->ncomp + comp) * g.vol + g.origin;
+}
+GridArgs grid_args(const LevelGeom &g);
+StencilArgs stencil_args(const LevelGeom &g, const Stencil &s);
+
+// global (all-rank) sum of a device dd partial written to c->red_out[slot]; returns hi+lo
+int finish_sum(examg_ctx *c, int slot, double *out);
+
+#define EXAMG_CUDA(expr)                                                              \
+  do {                                                                                \
+    cudaError_t e__ = (expr);                                                         \
+    if (e__ != cudaSuccess)                                                           \
+      return examg::set_error(EXAMG_ECUDA, "%s:%d %s: %s", __FILE__, __LINE__, #expr, \
+                              cudaGetErrorString(e__));                               \
+  } while (0)
+
+#define EXAMG_LAUNCH_CHECK(c)                                                        \
+  do {                                                                               \
+    (c)->launches++;                                                                 \
+    cudaError_t e__ = cudaGetLastError();                                            \
+    if (e__ != cudaSuccess)                                                          \
+      return examg::set_error(EXAMG_ECUDA, "%s:%d launch: %s", __FILE__, __LINE__,   \
+                              cudaGetErrorString(e__));                              \
+  } while (0)
+
+// ---- internal launchers (defined in the kernel translation units) -----------
+int launch_apply(examg_ctx *c, const Stencil &s, const double *u, double *out);
+int launch_residual(examg_ctx *c, const Stencil &s, const double *u, const double *rhs, double *res,
+                    int red_slot /* <0: no norm */);
+int launch_jacobi(examg_ctx *c, const Stencil &s, double omega, const double *u, const double *rhs,
+                  double *unext);
+int launch_rb(examg_ctx *c, const Stencil &s, double omega, double *u, const double *rhs, int color);
+int launch_restrict(examg_ctx *c, int lvl_fine, double scale, const double *rf, double *rhsc);
+int launch_prolong(examg_ctx *c, int lvl_fine, const double *uc, double *uf);
+int launch_dot(examg_ctx *c, int level, const double *a, const double *b, int red_slot);
+int launch_maxdiff(examg_ctx *c, int level, const double *a, const double *b, int red_slot);
+enum { STREAM_SET = 0, STREAM_COPY = 1, STREAM_AXPY = 2, STREAM_XPAY = 3 };
+int launch_stream_op(examg_ctx *c, int level, int op, double alpha, const double *x, double *y);
+int launch_bc(examg_ctx *c, const Field &f, int slot);
+int launch_cg(examg_ctx *c, const Stencil &s, double *u, const double *rhs, double *res, double *p,
+              double *ap, int max_it, double rel_tol);
+int do_exchange(examg_ctx *c, const Field &f, int slot);
+
+}  // namespace examg

@@ -1,0 +1,369 @@
+// examg_kernels.cu -- generic (any compact stencil, 2D/3D, constant or
+// stencil-field coefficients) kernels of libexamg: A*u, residual (+ fused
+// sum of squares), Jacobi, one red-black colour, dot/max reductions, streaming
+// loops and the Dirichlet boundary update.
+//
+// Arithmetic contract (bit-identical to oracle/examg_oracle.c; built with
+// --fmad=false so only the explicit fma() calls fuse):
+//   A*u      : acc = c0*u0; acc = fma(ck, uk, acc), k = 1..nst-1 in declaration order
+//   residual : r = rhs - acc
+//   smoother : u' = fma(omega/diag, rhs - acc, u)
+//   sums     : double-double accumulation of the rounded products
+// Reference loops these replace: Benchmark/Poisson3D/3D_FD_Poisson_fromL4.exa4:113-125,
+// 204-218; Testing/SISC/3D_VarCoeff.exa4 (Smoother, UpResidual); iteration space
+// C/s/e/baseExt/ir/IR_LoopOverPointsInOneFragment.scala:86-125.
+#include "examg_device.cuh"
+
+namespace examg {
+
+enum { M_APPLY = 0, M_RESIDUAL = 1, M_RESNORM = 2, M_JACOBI = 3, M_RB = 4 };
+
+template <int NST, bool VAR>
+__device__ __forceinline__ double conv(const StencilArgs &st, const double *__restrict__ sf, long long sfvol,
+                                       const double *u, long long p) {
+  const int nst = NST > 0 ? NST : st.nst;
+  double acc;
+  if (VAR) {
+    acc = sf[p] * u[p + st.lin[0]];
+#pragma unroll
+    for (int k = 1; k < nst; ++k) acc = fma(sf[k * sfvol + p], u[p + st.lin[k]], acc);
+  } else {
+    acc = st.coef[0] * u[p + st.lin[0]];
+#pragma unroll
+    for (int k = 1; k < nst; ++k) acc = fma(st.coef[k], u[p + st.lin[k]], acc);
+  }
+  return acc;
+}
+
+// One kernel for the five loop shapes.  For M_RB, `u` and `out` alias.
+template <int MODE, int NST, bool VAR>
+__global__ void __launch_bounds__(256)
+k_stencil(const GridArgs g, const __grid_constant__ StencilArgs st, const double *__restrict__ sf,
+          long long sfvol, const double *u, const double *__restrict__ rhs, double *out, double w, int color,
+          int kz, dd *__restrict__ partials) {
+  const int tx = blockIdx.x * blockDim.x + threadIdx.x;
+  const int z0 = g.lo[2] + blockIdx.z * kz;
+  const int z1 = min(z0 + kz, g.hi[2]);
+  dd part = {0.0, 0.0};
+  for (int j = g.lo[1] + blockIdx.y * blockDim.y + threadIdx.y; j < g.hi[1]; j += gridDim.y * blockDim.y) {
+    for (int k = z0; k < z1; ++k) {
+      int i;
+      if (MODE == M_RB) {
+        const int first = g.lo[0] + ((g.lo[0] + j + k + g.par + color) & 1);
+        i = first + 2 * tx;
+      } else {
+        i = g.lo[0] + tx;
+      }
+      if (i < g.hi[0]) {
+        const long long p = i + (long long)g.pitch * j + g.plane * k;
+        const double acc = conv<NST, VAR>(st, sf, sfvol, u, p);
+        if (MODE == M_APPLY) {
+          out[p] = acc;
+        } else if (MODE == M_RESIDUAL || MODE == M_RESNORM) {
+          const double r = rhs[p] - acc;
+          out[p] = r;
+          if (MODE == M_RESNORM && i >= g.rlo[0] && j >= g.rlo[1] && k >= g.rlo[2]) dd_add(part, r * r);
+        } else {
+          const double ww = VAR ? w / sf[st.centre * sfvol + p] : w;  // w = omega (VAR) or omega/diag
+          const double r = rhs[p] - acc;
+          out[p] = fma(ww, r, u[p]);
+        }
+      }
+    }
+  }
+  if (MODE == M_RESNORM) {
+    part = dd_block_reduce(part);
+    if (threadIdx.x == 0 && threadIdx.y == 0)
+      partials[blockIdx.x + gridDim.x * (blockIdx.y + gridDim.y * blockIdx.z)] = part;
+  }
+}
+
+// merges the per-block partials in index order; one block
+__global__ void __launch_bounds__(1024) k_final_sum(const dd *__restrict__ partials, int n, dd *out) {
+  dd v = {0.0, 0.0};
+  for (int i = threadIdx.x; i < n; i += blockDim.x) dd_merge(v, partials[i]);
+  v = dd_block_reduce(v);
+  if (threadIdx.x == 0) *out = v;
+}
+
+__global__ void __launch_bounds__(1024) k_final_max(const dd *__restrict__ partials, int n, dd *out) {
+  double v = 0.0;
+  for (int i = threadIdx.x; i < n; i += blockDim.x) v = fmax(v, partials[i].hi);
+  v = max_block_reduce(v);
+  if (threadIdx.x == 0) { out->hi = v; out->lo = 0.0; }
+}
+
+enum { R_DOT = 0, R_MAXDIFF = 1 };
+template <int KIND>
+__global__ void __launch_bounds__(256)
+k_reduce(const GridArgs g, const double *__restrict__ a, const double *__restrict__ b, int kz,
+         dd *__restrict__ partials) {
+  const int i = (KIND == R_DOT ? max(g.lo[0], g.rlo[0]) : g.lo[0]) + blockIdx.x * blockDim.x + threadIdx.x;
+  const int zlo = KIND == R_DOT ? max(g.lo[2], g.rlo[2]) : g.lo[2];
+  const int ylo = KIND == R_DOT ? max(g.lo[1], g.rlo[1]) : g.lo[1];
+  const int z0 = zlo + blockIdx.z * kz;
+  const int z1 = min(z0 + kz, g.hi[2]);
+  dd part = {0.0, 0.0};
+  double m = 0.0;
+  for (int j = ylo + blockIdx.y * blockDim.y + threadIdx.y; j < g.hi[1]; j += gridDim.y * blockDim.y)
+    for (int k = z0; k < z1; ++k)
+      if (i < g.hi[0]) {
+        const long long p = i + (long long)g.pitch * j + g.plane * k;
+        if (KIND == R_DOT) dd_add(part, a[p] * b[p]);
+        else m = fmax(m, fabs(a[p] - b[p]));
+      }
+  const int bid = blockIdx.x + gridDim.x * (blockIdx.y + gridDim.y * blockIdx.z);
+  if (KIND == R_DOT) {
+    part = dd_block_reduce(part);
+    if (threadIdx.x == 0 && threadIdx.y == 0) partials[bid] = part;
+  } else {
+    m = max_block_reduce(m);
+    if (threadIdx.x == 0 && threadIdx.y == 0) { partials[bid].hi = m; partials[bid].lo = 0.0; }
+  }
+}
+
+template <int OP>
+__global__ void __launch_bounds__(256)
+k_stream(const GridArgs g, double alpha, const double *__restrict__ x, double *__restrict__ y, int kz) {
+  const int i = g.lo[0] + blockIdx.x * blockDim.x + threadIdx.x;
+  const int z0 = g.lo[2] + blockIdx.z * kz;
+  const int z1 = min(z0 + kz, g.hi[2]);
+  if (i >= g.hi[0]) return;
+  for (int j = g.lo[1] + blockIdx.y * blockDim.y + threadIdx.y; j < g.hi[1]; j += gridDim.y * blockDim.y)
+    for (int k = z0; k < z1; ++k) {
+      const long long p = i + (long long)g.pitch * j + g.plane * k;
+      if (OP == STREAM_SET) y[p] = alpha;
+      else if (OP == STREAM_COPY) y[p] = x[p];
+      else if (OP == STREAM_AXPY) y[p] = fma(alpha, x[p], y[p]);
+      else y[p] = fma(alpha, y[p], x[p]);
+    }
+}
+
+// ---- Dirichlet boundary update -------------------------------------------------
+struct BcProg {
+  int n;
+  int op[64];
+  double val[64];
+};
+
+__device__ __forceinline__ double bc_eval(const BcProg &pr, double x, double y, double z) {
+  double stk[16];
+  int sp = 0;
+  for (int q = 0; q < pr.n; ++q) {
+    switch (pr.op[q]) {
+      case EXAMG_OP_CONST: stk[sp++] = pr.val[q]; break;
+      case EXAMG_OP_X: stk[sp++] = x; break;
+      case EXAMG_OP_Y: stk[sp++] = y; break;
+      case EXAMG_OP_Z: stk[sp++] = z; break;
+      case EXAMG_OP_ADD: --sp; stk[sp - 1] = stk[sp - 1] + stk[sp]; break;
+      case EXAMG_OP_SUB: --sp; stk[sp - 1] = stk[sp - 1] - stk[sp]; break;
+      case EXAMG_OP_MUL: --sp; stk[sp - 1] = stk[sp - 1] * stk[sp]; break;
+      case EXAMG_OP_DIV: --sp; stk[sp - 1] = stk[sp - 1] / stk[sp]; break;
+      case EXAMG_OP_NEG: stk[sp - 1] = -stk[sp - 1]; break;
+    }
+  }
+  return stk[0];
+}
+
+struct BcArgs {
+  int n[3];
+  int goff[3];
+  double h[3], x0[3];
+  int pitch;
+  long long plane;
+  int face_mask;  // bit 2*d+s set: face on side s of dim d is a physical boundary
+  int dim;
+};
+
+// blockIdx.y = face id (2*d + side).  vf_boundaryPosition = node position
+// i*h + lo (C/s/e/grid/ir/IR_VF_NodePosition.scala:109-111).
+__global__ void __launch_bounds__(256)
+k_dirichlet(const BcArgs a, const __grid_constant__ BcProg pr, int use_prog, double value, double *f) {
+  const int face = blockIdx.y;
+  if (!((a.face_mask >> face) & 1)) return;
+  const int d = face >> 1, side = face & 1;
+  const int da = d == 0 ? 1 : 0;             // first in-face dim
+  const int db = d == 2 ? 1 : 2;             // second in-face dim (extent 1 in 2D)
+  const int na = a.n[da], nb = a.n[db];
+  const long long total = (long long)na * nb;
+  for (long long t = blockIdx.x * (long long)blockDim.x + threadIdx.x; t < total;
+       t += (long long)gridDim.x * blockDim.x) {
+    int idx[3];
+    idx[d] = side ? a.n[d] - 1 : 0;
+    idx[da] = (int)(t % na);
+    idx[db] = (int)(t / na);
+    double v = value;
+    if (use_prog) {
+      // x = i*h + domain_lo
+      const double x = (double)(a.goff[0] + idx[0]) * a.h[0] + a.x0[0];
+      const double y = (double)(a.goff[1] + idx[1]) * a.h[1] + a.x0[1];
+      const double z = a.dim == 3 ? (double)(a.goff[2] + idx[2]) * a.h[2] + a.x0[2] : 0.0;
+      v = bc_eval(pr, x, y, z);
+    }
+    f[idx[0] + (long long)a.pitch * idx[1] + a.plane * idx[2]] = v;
+  }
+}
+
+// ---- launchers -----------------------------------------------------------------
+
+template <int MODE>
+static int launch_stencil(examg_ctx *c, const Stencil &s, const double *u, const double *rhs, double *out,
+                          double omega, int color, int red_slot) {
+  const LevelGeom &g = *geom(c, s.level);
+  const GridArgs ga = grid_args(g);
+  const StencilArgs sa = stencil_args(g, s);
+  const bool var = s.coeff_field >= 0;
+  const double *sf = nullptr;
+  if (var) sf = field_ptr(c, &c->fields[s.coeff_field], 0, 0);
+  int ex = g.hi[0] - g.lo[0], ey = g.hi[1] - g.lo[1], ez = g.hi[2] - g.lo[2];
+  if (ex <= 0 || ey <= 0 || ez <= 0) {
+    if (MODE == M_RESNORM) {
+      EXAMG_CUDA(cudaMemsetAsync(c->red_out + red_slot, 0, sizeof(dd), c->stream));
+    }
+    return EXAMG_OK;
+  }
+  if (MODE == M_RB) ex = (ex + 1) / 2;
+  const Shape sh = make_shape(ex, ey, ez);
+  double w = omega;
+  if (!var && (MODE == M_JACOBI || MODE == M_RB)) w = omega / s.coef[s.centre];
+#define EXAMG_GO(NST, VAR)                                                                         \
+  k_stencil<MODE, NST, VAR><<<sh.grid, sh.block, 0, c->stream>>>(ga, sa, sf, g.vol, u, rhs, out, w, \
+                                                                  color, sh.kz, c->partials)
+  if (var) {
+    switch (s.nst) {
+      case 5: EXAMG_GO(5, true); break;
+      case 7: EXAMG_GO(7, true); break;
+      case 9: EXAMG_GO(9, true); break;
+      case 27: EXAMG_GO(27, true); break;
+      default: EXAMG_GO(0, true); break;
+    }
+  } else {
+    switch (s.nst) {
+      case 5: EXAMG_GO(5, false); break;
+      case 7: EXAMG_GO(7, false); break;
+      case 9: EXAMG_GO(9, false); break;
+      case 27: EXAMG_GO(27, false); break;
+      default: EXAMG_GO(0, false); break;
+    }
+  }
+#undef EXAMG_GO
+  EXAMG_LAUNCH_CHECK(c);
+  if (MODE == M_RESNORM) {
+    k_final_sum<<<1, 1024, 0, c->stream>>>(c->partials, sh.nblocks, c->red_out + red_slot);
+    EXAMG_LAUNCH_CHECK(c);
+  }
+  return EXAMG_OK;
+}
+
+int launch_apply(examg_ctx *c, const Stencil &s, const double *u, double *out) {
+  return launch_stencil<M_APPLY>(c, s, u, nullptr, out, 0.0, 0, -1);
+}
+int launch_residual_generic(examg_ctx *c, const Stencil &s, const double *u, const double *rhs, double *res,
+                            int red_slot) {
+  if (red_slot >= 0) return launch_stencil<M_RESNORM>(c, s, u, rhs, res, 0.0, 0, red_slot);
+  return launch_stencil<M_RESIDUAL>(c, s, u, rhs, res, 0.0, 0, -1);
+}
+int launch_jacobi_generic(examg_ctx *c, const Stencil &s, double omega, const double *u, const double *rhs,
+                          double *unext) {
+  return launch_stencil<M_JACOBI>(c, s, u, rhs, unext, omega, 0, -1);
+}
+int launch_rb_generic(examg_ctx *c, const Stencil &s, double omega, double *u, const double *rhs, int color) {
+  return launch_stencil<M_RB>(c, s, u, rhs, u, omega, color, -1);
+}
+
+static int launch_reduce(examg_ctx *c, int level, const double *a, const double *b, int red_slot, int kind) {
+  const LevelGeom &g = *geom(c, level);
+  const GridArgs ga = grid_args(g);
+  int xlo = g.lo[0], ylo = g.lo[1], zlo = g.lo[2];
+  if (kind == R_DOT) {
+    xlo = g.lo[0] > g.rlo[0] ? g.lo[0] : g.rlo[0];
+    ylo = g.lo[1] > g.rlo[1] ? g.lo[1] : g.rlo[1];
+    zlo = g.lo[2] > g.rlo[2] ? g.lo[2] : g.rlo[2];
+  }
+  const int ex = g.hi[0] - xlo, ey = g.hi[1] - ylo, ez = g.hi[2] - zlo;
+  if (ex <= 0 || ey <= 0 || ez <= 0) {
+    EXAMG_CUDA(cudaMemsetAsync(c->red_out + red_slot, 0, sizeof(dd), c->stream));
+    return EXAMG_OK;
+  }
+  const Shape sh = make_shape(ex, ey, ez);
+  if (kind == R_DOT) {
+    k_reduce<R_DOT><<<sh.grid, sh.block, 0, c->stream>>>(ga, a, b, sh.kz, c->partials);
+    EXAMG_LAUNCH_CHECK(c);
+    k_final_sum<<<1, 1024, 0, c->stream>>>(c->partials, sh.nblocks, c->red_out + red_slot);
+  } else {
+    k_reduce<R_MAXDIFF><<<sh.grid, sh.block, 0, c->stream>>>(ga, a, b, sh.kz, c->partials);
+    EXAMG_LAUNCH_CHECK(c);
+    k_final_max<<<1, 1024, 0, c->stream>>>(c->partials, sh.nblocks, c->red_out + red_slot);
+  }
+  EXAMG_LAUNCH_CHECK(c);
+  return EXAMG_OK;
+}
+
+int launch_dot(examg_ctx *c, int level, const double *a, const double *b, int red_slot) {
+  return launch_reduce(c, level, a, b, red_slot, R_DOT);
+}
+int launch_maxdiff(examg_ctx *c, int level, const double *a, const double *b, int red_slot) {
+  return launch_reduce(c, level, a, b, red_slot, R_MAXDIFF);
+}
+
+int launch_stream_op(examg_ctx *c, int level, int op, double alpha, const double *x, double *y) {
+  const LevelGeom &g = *geom(c, level);
+  const GridArgs ga = grid_args(g);
+  const int ex = g.hi[0] - g.lo[0], ey = g.hi[1] - g.lo[1], ez = g.hi[2] - g.lo[2];
+  if (ex <= 0 || ey <= 0 || ez <= 0) return EXAMG_OK;
+  const Shape sh = make_shape(ex, ey, ez);
+  switch (op) {
+    case STREAM_SET: k_stream<STREAM_SET><<<sh.grid, sh.block, 0, c->stream>>>(ga, alpha, x, y, sh.kz); break;
+    case STREAM_COPY: k_stream<STREAM_COPY><<<sh.grid, sh.block, 0, c->stream>>>(ga, alpha, x, y, sh.kz); break;
+    case STREAM_AXPY: k_stream<STREAM_AXPY><<<sh.grid, sh.block, 0, c->stream>>>(ga, alpha, x, y, sh.kz); break;
+    default: k_stream<STREAM_XPAY><<<sh.grid, sh.block, 0, c->stream>>>(ga, alpha, x, y, sh.kz); break;
+  }
+  EXAMG_LAUNCH_CHECK(c);
+  return EXAMG_OK;
+}
+
+int launch_bc(examg_ctx *c, const Field &f, int slot) {
+  const LevelGeom &g = *geom(c, f.level);
+  BcArgs a;
+  int mask = 0;
+  for (int d = 0; d < 3; ++d) {
+    a.n[d] = g.n[d];
+    a.goff[d] = g.goff[d];
+    a.h[d] = g.h[d];
+    a.x0[d] = d < c->cfg.dim ? c->cfg.domain_lo[d] : 0.0;
+    if (d < c->cfg.dim) {
+      if (!c->nb[d][0]) mask |= 1 << (2 * d);
+      if (!c->nb[d][1]) mask |= 1 << (2 * d + 1);
+    }
+  }
+  if (!mask) return EXAMG_OK;
+  a.pitch = g.pitch;
+  a.plane = g.plane;
+  a.face_mask = mask;
+  a.dim = c->cfg.dim;
+  BcProg pr;
+  pr.n = 0;
+  const int use_prog = f.bc_kind == EXAMG_BC_DIRICHLET_EXPR;
+  if (use_prog) {
+    pr.n = (int)f.bc_prog.size();
+    for (int q = 0; q < pr.n; ++q) { pr.op[q] = f.bc_prog[q].op; pr.val[q] = f.bc_prog[q].value; }
+  }
+  long long maxface = 1;
+  for (int d = 0; d < c->cfg.dim; ++d) {
+    long long fsz = 1;
+    for (int e = 0; e < c->cfg.dim; ++e)
+      if (e != d) fsz *= g.n[e];
+    if (fsz > maxface) maxface = fsz;
+  }
+  int gx = (int)((maxface + 255) / 256);
+  if (gx > 1024) gx = 1024;
+  dim3 grid(gx, 2 * c->cfg.dim, 1);
+  for (int comp = 0; comp < f.ncomp; ++comp) {
+    k_dirichlet<<<grid, 256, 0, c->stream>>>(a, pr, use_prog, f.bc_value,
+                                             field_ptr(c, &f, slot, comp));
+    EXAMG_LAUNCH_CHECK(c);
+  }
+  return EXAMG_OK;
+}
+
+}  // namespace examg

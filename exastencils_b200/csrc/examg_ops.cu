@@ -1,0 +1,179 @@
+// examg_ops.cu -- C-ABI entry points of the hot path (argument checking, slot
+// resolution, dispatch to the kernel launchers).  One entry per `loop over`
+// shape of the L4 programs; see include/examg.h for the reference lines.
+#include <cmath>
+
+#include "examg_internal.h"
+
+using namespace examg;
+
+namespace examg {
+// generic launchers (examg_kernels.cu, examg_transfer.cu)
+int launch_residual_generic(examg_ctx *c, const Stencil &s, const double *u, const double *rhs, double *res, int red_slot);
+int launch_jacobi_generic(examg_ctx *c, const Stencil &s, double omega, const double *u, const double *rhs, double *unext);
+int launch_rb_generic(examg_ctx *c, const Stencil &s, double omega, double *u, const double *rhs, int color);
+int launch_restrict_generic(examg_ctx *c, int lvl_fine, double scale, const double *rf, double *rhsc);
+int launch_prolong_generic(examg_ctx *c, int lvl_fine, const double *uc, double *uf);
+// 3D 7-point constant-coefficient fast path (examg_fast7.cu)
+bool fast7_usable(examg_ctx *c, const Stencil &s);
+int fast7_residual(examg_ctx *c, const Stencil &s, const double *u, const double *rhs, double *res, int red_slot);
+int fast7_rb(examg_ctx *c, const Stencil &s, double omega, double *u, const double *rhs, int color);
+
+int launch_residual(examg_ctx *c, const Stencil &s, const double *u, const double *rhs, double *res, int red_slot) {
+  if (fast7_usable(c, s)) return fast7_residual(c, s, u, rhs, res, red_slot);
+  return launch_residual_generic(c, s, u, rhs, res, red_slot);
+}
+int launch_jacobi(examg_ctx *c, const Stencil &s, double omega, const double *u, const double *rhs, double *unext) {
+  return launch_jacobi_generic(c, s, omega, u, rhs, unext);
+}
+int launch_rb(examg_ctx *c, const Stencil &s, double omega, double *u, const double *rhs, int color) {
+  if (fast7_usable(c, s)) return fast7_rb(c, s, omega, u, rhs, color);
+  return launch_rb_generic(c, s, omega, u, rhs, color);
+}
+int launch_restrict(examg_ctx *c, int lvl_fine, double scale, const double *rf, double *rhsc) {
+  return launch_restrict_generic(c, lvl_fine, scale, rf, rhsc);
+}
+int launch_prolong(examg_ctx *c, int lvl_fine, const double *uc, double *uf) {
+  return launch_prolong_generic(c, lvl_fine, uc, uf);
+}
+}  // namespace examg
+
+#define GET_FIELD(var, h)                                                   \
+  Field *var = get_field(c, h);                                             \
+  if (!var) return set_error(EXAMG_EINVAL, "%s: bad field handle %d", __func__, h)
+#define GET_STENCIL(var, h)                                                 \
+  Stencil *var = get_stencil(c, h);                                         \
+  if (!var) return set_error(EXAMG_EINVAL, "%s: bad stencil handle %d", __func__, h)
+#define CHECK_SLOT(f, slot) \
+  if ((slot) >= (f)->nslots) return set_error(EXAMG_EINVAL, "%s: slot %d of %d", __func__, slot, (f)->nslots)
+#define CHECK_LEVEL(f, lvl) \
+  if ((f)->level != (lvl)) return set_error(EXAMG_EINVAL, "%s: field %s lives on level %d, not %d", __func__, (f)->name.c_str(), (f)->level, lvl)
+
+extern "C" {
+
+int examg_apply(examg_ctx *c, int A, int u, int u_slot, int out) {
+  GET_STENCIL(s, A); GET_FIELD(fu, u); GET_FIELD(fo, out);
+  CHECK_SLOT(fu, u_slot); CHECK_LEVEL(fu, s->level); CHECK_LEVEL(fo, s->level);
+  if (fu == fo) return set_error(EXAMG_EINVAL, "examg_apply: in-place application");
+  return launch_apply(c, *s, field_ptr(c, fu, u_slot), field_ptr(c, fo, -1));
+}
+
+int examg_residual(examg_ctx *c, int A, int u, int u_slot, int rhs, int res, double *norm2_out) {
+  GET_STENCIL(s, A); GET_FIELD(fu, u); GET_FIELD(fr, rhs); GET_FIELD(fo, res);
+  CHECK_SLOT(fu, u_slot); CHECK_LEVEL(fu, s->level); CHECK_LEVEL(fr, s->level); CHECK_LEVEL(fo, s->level);
+  if (fu == fo) return set_error(EXAMG_EINVAL, "examg_residual: Residual aliases Solution");
+  int rc = launch_residual(c, *s, field_ptr(c, fu, u_slot), field_ptr(c, fr, -1), field_ptr(c, fo, -1),
+                           norm2_out ? 0 : -1);
+  if (rc || !norm2_out) return rc;
+  return finish_sum(c, 0, norm2_out);
+}
+
+int examg_smooth_jacobi(examg_ctx *c, int A, int u, int rhs, double omega, int nsweeps) {
+  GET_STENCIL(s, A); GET_FIELD(fu, u); GET_FIELD(fr, rhs);
+  CHECK_LEVEL(fu, s->level); CHECK_LEVEL(fr, s->level);
+  if (fu->nslots < 2) return set_error(EXAMG_EINVAL, "examg_smooth_jacobi: Solution needs 2 slots");
+  for (int it = 0; it < nsweeps; ++it) {
+    int rc = do_exchange(c, *fu, fu->cur);
+    if (rc) return rc;
+    const int nxt = (fu->cur + 1) % fu->nslots;
+    rc = launch_jacobi(c, *s, omega, field_ptr(c, fu, fu->cur), field_ptr(c, fr, -1), field_ptr(c, fu, nxt));
+    if (rc) return rc;
+    fu->cur = nxt;  // advance Solution
+  }
+  return EXAMG_OK;
+}
+
+int examg_smooth_rb_color(examg_ctx *c, int A, int u, int rhs, double omega, int color) {
+  GET_STENCIL(s, A); GET_FIELD(fu, u); GET_FIELD(fr, rhs);
+  CHECK_LEVEL(fu, s->level); CHECK_LEVEL(fr, s->level);
+  if (color != 0 && color != 1) return set_error(EXAMG_EINVAL, "examg_smooth_rb_color: colour %d", color);
+  int rc = do_exchange(c, *fu, fu->cur);
+  if (rc) return rc;
+  return launch_rb(c, *s, omega, field_ptr(c, fu, -1), field_ptr(c, fr, -1), color);
+}
+
+int examg_smooth_rbgs(examg_ctx *c, int A, int u, int rhs, double omega, int nsweeps) {
+  for (int it = 0; it < nsweeps; ++it)
+    for (int color = 0; color < 2; ++color) {
+      int rc = examg_smooth_rb_color(c, A, u, rhs, omega, color);
+      if (rc) return rc;
+    }
+  return EXAMG_OK;
+}
+
+int examg_restrict(examg_ctx *c, int res_fine, int rhs_coarse, double scale) {
+  GET_FIELD(ff, res_fine); GET_FIELD(fc, rhs_coarse);
+  if (fc->level != ff->level - 1) return set_error(EXAMG_EINVAL, "examg_restrict: levels %d -> %d", ff->level, fc->level);
+  int rc = do_exchange(c, *ff, ff->cur);  // communicate Residual
+  if (rc) return rc;
+  return launch_restrict(c, ff->level, scale, field_ptr(c, ff, -1), field_ptr(c, fc, -1));
+}
+
+int examg_prolong_add(examg_ctx *c, int u_coarse, int uc_slot, int u_fine, int uf_slot) {
+  GET_FIELD(fc, u_coarse); GET_FIELD(ff, u_fine);
+  CHECK_SLOT(fc, uc_slot); CHECK_SLOT(ff, uf_slot);
+  if (fc->level != ff->level - 1) return set_error(EXAMG_EINVAL, "examg_prolong_add: levels %d -> %d", fc->level, ff->level);
+  return launch_prolong(c, ff->level, field_ptr(c, fc, uc_slot), field_ptr(c, ff, uf_slot));
+}
+
+int examg_dot(examg_ctx *c, int a, int a_slot, int b, int b_slot, double *out) {
+  GET_FIELD(fa, a); GET_FIELD(fb, b);
+  CHECK_SLOT(fa, a_slot); CHECK_SLOT(fb, b_slot); CHECK_LEVEL(fb, fa->level);
+  if (!out) return set_error(EXAMG_EINVAL, "examg_dot: null output");
+  int rc = launch_dot(c, fa->level, field_ptr(c, fa, a_slot), field_ptr(c, fb, b_slot), 0);
+  if (rc) return rc;
+  return finish_sum(c, 0, out);
+}
+
+int examg_max_abs_diff(examg_ctx *c, int a, int a_slot, int b, int b_slot, double *out) {
+  GET_FIELD(fa, a); GET_FIELD(fb, b);
+  CHECK_SLOT(fa, a_slot); CHECK_SLOT(fb, b_slot); CHECK_LEVEL(fb, fa->level);
+  if (!out) return set_error(EXAMG_EINVAL, "examg_max_abs_diff: null output");
+  int rc = launch_maxdiff(c, fa->level, field_ptr(c, fa, a_slot), field_ptr(c, fb, b_slot), 1);
+  if (rc) return rc;
+  EXAMG_CUDA(cudaMemcpyAsync(c->red_host + 1, c->red_out + 1, sizeof(dd), cudaMemcpyDeviceToHost, c->stream));
+  EXAMG_CUDA(cudaStreamSynchronize(c->stream));
+  *out = c->red_host[1].hi;  // per-block maximum; the host process group takes the max over blocks
+  return EXAMG_OK;
+}
+
+int examg_set(examg_ctx *c, int f, int slot, double value) {
+  GET_FIELD(ff, f); CHECK_SLOT(ff, slot);
+  return launch_stream_op(c, ff->level, STREAM_SET, value, nullptr, field_ptr(c, ff, slot));
+}
+int examg_copy(examg_ctx *c, int src, int src_slot, int dst, int dst_slot) {
+  GET_FIELD(fs, src); GET_FIELD(fd, dst);
+  CHECK_SLOT(fs, src_slot); CHECK_SLOT(fd, dst_slot); CHECK_LEVEL(fd, fs->level);
+  return launch_stream_op(c, fs->level, STREAM_COPY, 0.0, field_ptr(c, fs, src_slot), field_ptr(c, fd, dst_slot));
+}
+int examg_axpy(examg_ctx *c, double alpha, int x, int x_slot, int y, int y_slot) {
+  GET_FIELD(fx, x); GET_FIELD(fy, y);
+  CHECK_SLOT(fx, x_slot); CHECK_SLOT(fy, y_slot); CHECK_LEVEL(fy, fx->level);
+  return launch_stream_op(c, fx->level, STREAM_AXPY, alpha, field_ptr(c, fx, x_slot), field_ptr(c, fy, y_slot));
+}
+int examg_xpay(examg_ctx *c, int x, int x_slot, double beta, int y, int y_slot) {
+  GET_FIELD(fx, x); GET_FIELD(fy, y);
+  CHECK_SLOT(fx, x_slot); CHECK_SLOT(fy, y_slot); CHECK_LEVEL(fy, fx->level);
+  return launch_stream_op(c, fx->level, STREAM_XPAY, beta, field_ptr(c, fx, x_slot), field_ptr(c, fy, y_slot));
+}
+
+int examg_exchange(examg_ctx *c, int field, int slot) {
+  GET_FIELD(f, field); CHECK_SLOT(f, slot);
+  return do_exchange(c, *f, slot < 0 ? f->cur : slot);
+}
+
+int examg_cg_coarse(examg_ctx *c, int A, int u, int rhs, int res, int p, int ap, int max_it, double rel_tol,
+                    int *iters_out) {
+  GET_STENCIL(s, A); GET_FIELD(fu, u); GET_FIELD(fr, rhs); GET_FIELD(fres, res); GET_FIELD(fp, p); GET_FIELD(fap, ap);
+  CHECK_LEVEL(fu, s->level); CHECK_LEVEL(fr, s->level); CHECK_LEVEL(fres, s->level);
+  CHECK_LEVEL(fp, s->level); CHECK_LEVEL(fap, s->level);
+  int rc = launch_cg(c, *s, field_ptr(c, fu, -1), field_ptr(c, fr, -1), field_ptr(c, fres, -1), field_ptr(c, fp, -1),
+                     field_ptr(c, fap, -1), max_it, rel_tol);
+  if (rc || !iters_out) return rc;
+  EXAMG_CUDA(cudaMemcpyAsync(c->int_host, c->int_out, sizeof(int), cudaMemcpyDeviceToHost, c->stream));
+  EXAMG_CUDA(cudaStreamSynchronize(c->stream));
+  *iters_out = c->int_host[0];
+  return EXAMG_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,226 @@
+/*
+ * examg.h -- C ABI of libexamg, the B200-native runtime behind the geometric-
+ * multigrid V-cycle that the ExaStencils generator emits.
+ *
+ * The reference has no FFI for this path: its generator prints every loop nest
+ * inline.  The conventions this boundary mirrors (paths relative to the
+ * reference root, C/s/e = Compiler/src/exastencils):
+ *   - kernel wrappers are `extern "C"` functions taking plain pointers, ints
+ *     and scalars            C/s/e/parallelization/api/cuda/CUDA_Kernel.scala:546-632
+ *   - generateCInterface wraps all generated functions in extern "C"
+ *                            C/s/e/baseExt/ir/IR_FunctionCollection.scala:52-66
+ *   - get<name>/set<name> copy loops between a caller-owned dense array and
+ *     the internal field     C/s/e/interfacing/ir/IR_CopyToExternalField.scala:30-90
+ *   - errors abort (IR_Assert -> exit(1); CUDA_CheckError)
+ *                            C/s/e/parallelization/api/cuda/CUDA_Error.scala:39-68
+ * Here every entry point returns 0 on success and a negative EXAMG_E* code on
+ * failure; examg_last_error() holds the message.  The emitted host code wraps
+ * calls in a check-and-exit(1) macro, which reproduces the reference behaviour
+ * (INTEGRATION.md).
+ *
+ * Ownership: the library owns all device memory (layout, padding and ghost
+ * layers are its business); callers hold integer handles.  Host pointers passed
+ * to upload/download/norm outputs stay caller-owned and are never retained.
+ * Threading: single caller thread per context; calls are stream-ordered on the
+ * context's stream and return before completion unless they have host outputs.
+ *
+ * One context = one block (= one fragment) of the rectangular domain on one
+ * GPU:  domain_rect_numBlocks_{x,y,z} blocks, rank -> block index x-fastest
+ * (C/s/e/domain/ir/IR_InitGeneratedDomain.scala:41-47).
+ */
+#ifndef EXAMG_H
+#define EXAMG_H
+
+#include <stddef.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define EXAMG_ABI_VERSION 1
+#define EXAMG_MAX_STENCIL 27
+
+/* error codes */
+#define EXAMG_OK 0
+#define EXAMG_EINVAL (-1)  /* bad argument / handle                       */
+#define EXAMG_ECUDA (-2)   /* CUDA runtime error (message has the string) */
+#define EXAMG_ENOMEM (-3)
+#define EXAMG_ESTATE (-4)  /* call not valid in this state                */
+#define EXAMG_EUNSUP (-5)  /* combination not supported                   */
+
+typedef struct examg_ctx examg_ctx;
+
+/* ---- lifecycle: initGlobals + initDomain + setupBuffers / destroyGlobals ----
+ * (C/s/e/domain/ir/IR_InitGeneratedDomain.scala:78-104,
+ *  C/s/e/globals/ir/IR_AllocateDataFunction.scala:64-72) */
+typedef struct {
+  int dim;              /* Knowledge.dimensionality: 2 or 3                        */
+  int min_level;        /* Knowledge.minLevel                                      */
+  int max_level;        /* Knowledge.maxLevel                                      */
+  int block_cells[3];   /* cells per block and dim at level 0 =
+                           domain_rect_numFragsPerBlock_d * domain_fragmentLength_d */
+  int num_blocks[3];    /* domain_rect_numBlocks_{x,y,z}                           */
+  int rank;             /* this block: mpi rank, x-fastest over num_blocks         */
+  int device;           /* CUDA device ordinal (cuda_deviceId)                     */
+  double domain_lo[3];  /* Domain global< lo to hi >                               */
+  double domain_hi[3];
+} examg_config;
+
+int examg_abi_version(void);
+const char *examg_last_error(void);
+examg_ctx *examg_init(const examg_config *cfg); /* NULL on failure */
+int examg_finalize(examg_ctx *ctx);
+/* Use an existing cudaStream_t (passed as void*) for all work; NULL = own stream. */
+int examg_set_stream(examg_ctx *ctx, void *cuda_stream);
+int examg_sync(examg_ctx *ctx);
+/* local node counts n[d] (duplicate layers included, ghosts excluded) of a level */
+int examg_level_dims(examg_ctx *ctx, int level, int n[3]);
+/* grid width vf_gridWidth_d of a level (C/s/e/domain/ir/IR_DomainFromAABB.scala:31-40) */
+int examg_level_width(examg_ctx *ctx, int level, double h[3]);
+
+/* ---- fields (Field Name< domain, Layout, BC >[slots]@level) -----------------
+ * Node-localised, one duplicate layer, one ghost layer per side
+ * (Layout NodeWithComm; C/s/e/field/ir/IR_FieldLayout.scala:30-129).
+ * ncomp > 1 gives the SoA component dimension of stencil-field coefficients. */
+int examg_field_create(examg_ctx *ctx, const char *name, int level, int num_slots, int ncomp);
+int examg_field_destroy(examg_ctx *ctx, int field);
+int examg_field_num_slots(examg_ctx *ctx, int field);
+int examg_field_active_slot(examg_ctx *ctx, int field);          /* currentSlot              */
+int examg_field_advance(examg_ctx *ctx, int field);              /* `advance F` IR_Slot.scala:33-62 */
+
+/* Boundary conditions (third template argument of the field declaration).
+ * Dirichlet on node fields writes the value into the boundary nodes (the
+ * duplicate layer of blocks without a neighbour; IR_DirichletBC.scala:37-40). */
+enum {
+  EXAMG_BC_NONE = 0,
+  EXAMG_BC_DIRICHLET_CONST = 1, /* value                                             */
+  EXAMG_BC_DIRICHLET_EXPR = 2,  /* postfix program over vf_boundaryPosition_{x,y,z}  */
+  EXAMG_BC_DIRICHLET_HOST = 3   /* boundary nodes keep what upload() wrote           */
+};
+/* postfix (RPN) program for boundary expressions -- what the kernel printer
+ * lowers `vf_boundaryPosition_x ** 2 - 0.5 * ...` to.  Evaluated in double with
+ * exactly the association of the program (no contraction). */
+enum {
+  EXAMG_OP_CONST = 0, /* push value */
+  EXAMG_OP_X = 1, EXAMG_OP_Y = 2, EXAMG_OP_Z = 3, /* push node position */
+  EXAMG_OP_ADD = 4, EXAMG_OP_SUB = 5, EXAMG_OP_MUL = 6, EXAMG_OP_DIV = 7, EXAMG_OP_NEG = 8
+};
+typedef struct { int op; double value; } examg_bc_op;
+int examg_field_set_bc(examg_ctx *ctx, int field, int kind, double value);
+int examg_field_set_bc_expr(examg_ctx *ctx, int field, const examg_bc_op *prog, int n_ops);
+/* applyBCs<F>_<lvl>(slot)  (C/s/e/boundary/ir/IR_ApplyBCFunction.scala:53-105); slot < 0 = active */
+int examg_apply_bc(examg_ctx *ctx, int field, int slot);
+
+/* set<name>/get<name>: dense caller array [comp][nz][ny][nx], x fastest, local
+ * nodes incl. duplicate/boundary nodes, no ghosts.  Synchronous. */
+int examg_field_upload(examg_ctx *ctx, int field, int slot, const double *host);
+int examg_field_download(examg_ctx *ctx, int field, int slot, double *host);
+/* same, asynchronous on the context stream (host must be pinned to overlap) */
+int examg_field_upload_async(examg_ctx *ctx, int field, int slot, const double *host);
+int examg_field_download_async(examg_ctx *ctx, int field, int slot, double *host);
+/* whole allocation (ghosts, padding, all slots) := value (initFieldsWithZero) */
+int examg_field_fill(examg_ctx *ctx, int field, double value);
+
+/* ---- stencils ---------------------------------------------------------------
+ * Stencil Name@lvl { [dx,dy,dz] => coeff ... }: entries in declaration order.
+ * Stencil fields take their coefficients from a field with ncomp = n_entries
+ * (StencilField; C/s/e/operator/ir/IR_StencilField.scala). */
+int examg_stencil_const(examg_ctx *ctx, int level, int n_entries, const int (*offsets)[3],
+                        const double *coeffs);
+int examg_stencil_field(examg_ctx *ctx, int level, int n_entries, const int (*offsets)[3],
+                        int coeff_field);
+
+/* ---- hot path: one entry point per `loop over` shape -------------------------
+ * Iteration space of every loop: all local nodes except physical-boundary nodes
+ * (C/s/e/baseExt/ir/IR_LoopOverPointsInOneFragment.scala:86-101); reductions
+ * count nodes shared between blocks once (:116-125).  slot < 0 = active slot. */
+
+/* out = A * u */
+int examg_apply(examg_ctx *ctx, int stencil, int u, int u_slot, int out);
+/* Residual = RHS - A * Solution; if norm2_out != NULL also returns the global
+ * sum of Residual^2 (fused reduction; synchronises)                         */
+int examg_residual(examg_ctx *ctx, int stencil, int u, int u_slot, int rhs, int res,
+                   double *norm2_out);
+/* nsweeps x { communicate; Solution<next> = Solution<active> + omega/diag(A) *
+ * (RHS - A*Solution<active>); advance }   (needs 2 slots)                  */
+int examg_smooth_jacobi(examg_ctx *ctx, int stencil, int u, int rhs, double omega, int nsweeps);
+/* nsweeps x color with {(i0+i1+i2)%2}: colour 0 then colour 1, each
+ * { communicate; Solution += omega/diag(A)*(RHS - A*Solution); apply bc }
+ * (C/s/e/baseExt/l4/L4_ColorLoops.scala:44-70).  The library may fuse colours
+ * and sweeps; results are identical to the unfused order.                   */
+int examg_smooth_rbgs(examg_ctx *ctx, int stencil, int u, int rhs, double omega, int nsweeps);
+/* a single colour half-sweep (the unfused form) */
+int examg_smooth_rb_color(examg_ctx *ctx, int stencil, int u, int rhs, double omega, int color);
+/* RHS@coarser = scale * NodeRestriction * Residual
+ * (C/s/e/operator/l4/L4_DefaultRestriction.scala:29-90)                     */
+int examg_restrict(examg_ctx *ctx, int res_fine, int rhs_coarse, double scale);
+/* Solution += NodeProlongation@coarser * Solution@coarser
+ * (C/s/e/operator/l4/L4_DefaultProlongation.scala:30-45)                    */
+int examg_prolong_add(examg_ctx *ctx, int u_coarse, int u_coarse_slot, int u_fine, int u_fine_slot);
+/* loop over F with reduction(+: x) { x += a * b }; global over all blocks */
+int examg_dot(examg_ctx *ctx, int a, int a_slot, int b, int b_slot, double *out);
+/* max |a - b| over the loop points (PrintError / NormError) */
+int examg_max_abs_diff(examg_ctx *ctx, int a, int a_slot, int b, int b_slot, double *out);
+/* streaming loops on the loop points */
+int examg_set(examg_ctx *ctx, int f, int slot, double value);
+int examg_copy(examg_ctx *ctx, int src, int src_slot, int dst, int dst_slot);
+int examg_axpy(examg_ctx *ctx, double alpha, int x, int x_slot, int y, int y_slot); /* y += alpha*x */
+int examg_xpay(examg_ctx *ctx, int x, int x_slot, double beta, int y, int y_slot);  /* y = x + beta*y */
+/* exch<F>_<lvl>(slot): duplicate-layer sync then ghost-layer exchange, one
+ * dimension after the other (C/s/e/communication/ir/IR_CommunicateFunction.scala:412-470) */
+int examg_exchange(examg_ctx *ctx, int field, int slot);
+/* mgCycle@coarsest: un-preconditioned CG, stops at ||r|| <= rel_tol*||r0|| or
+ * max_it (Benchmark/Poisson3D/3D_FD_Poisson_fromL4.exa4:152-201).
+ * Runs entirely on the device; *iters_out (nullable) synchronises.          */
+int examg_cg_coarse(examg_ctx *ctx, int stencil, int u, int rhs, int res, int p, int ap,
+                    int max_it, double rel_tol, int *iters_out);
+
+/* ---- whole cycle: Solve@finest / mgCycle@lvl as one library object -----------
+ * (C/s/e/solver/l3/L3_SolverForEquation.scala:259-395).  Creates the field set
+ * of the L4 programs on every level (Solution[slots], RHS, Residual and, on the
+ * coarsest level, cgTmp0/cgTmp1) and runs the level loop without host
+ * round-trips (captured into a CUDA graph).                                  */
+enum { EXAMG_SMOOTH_JACOBI = 0, EXAMG_SMOOTH_RBGS = 1 };
+typedef struct {
+  int smoother;          /* EXAMG_SMOOTH_*                                       */
+  double omega;          /* solver_smoother_damping                              */
+  int nu_pre, nu_post;   /* solver_smoother_numPre / numPost                     */
+  double restrict_scale; /* 1, or 4 for `4.0 * RestrictionStencil` programs      */
+  int cg_max_it;         /* solver_cgs_maxNumIts                                 */
+  double cg_rel_tol;     /* solver_cgs_targetResReduction                        */
+  const int *stencils;   /* stencil handle per level, index level - min_level   */
+} examg_cycle_desc;
+typedef struct examg_solver examg_solver;
+examg_solver *examg_solver_create(examg_ctx *ctx, const examg_cycle_desc *desc);
+int examg_solver_destroy(examg_solver *s);
+/* field handles of a level: which = 0 Solution, 1 RHS, 2 Residual, 3 cgTmp0, 4 cgTmp1 */
+enum { EXAMG_F_SOLUTION = 0, EXAMG_F_RHS = 1, EXAMG_F_RESIDUAL = 2, EXAMG_F_CGTMP0 = 3, EXAMG_F_CGTMP1 = 4 };
+int examg_solver_field(examg_solver *s, int level, int which);
+/* mgCycle@level (level < 0: finest); asynchronous */
+int examg_solver_vcycle(examg_solver *s, int level);
+/* n x mgCycle@finest followed by one residual+norm; *norm_out = ||Residual||_2 */
+int examg_solver_cycles(examg_solver *s, int n, double *norm_out);
+/* Residual@finest = RHS - A*Solution; *norm_out = sqrt(global sum r^2) */
+int examg_solver_residual_norm(examg_solver *s, double *norm_out);
+/* CG iterations of the most recent coarse solve (synchronises) */
+int examg_solver_last_cg_iters(examg_solver *s, int *iters_out);
+
+/* ---- multi-GPU plumbing (one process per GPU) ---------------------------------
+ * Peers are wired by exchanging opaque blobs through the host's process group
+ * (torch.distributed / MPI): every rank exports a blob, all blobs are gathered
+ * and imported.  After that `communicate` writes faces directly into the
+ * neighbours' ghost layers over NVLink.                                       */
+int examg_comm_blob_size(examg_ctx *ctx);
+int examg_comm_export(examg_ctx *ctx, void *blob);
+int examg_comm_import(examg_ctx *ctx, const void *all_blobs, int world);
+
+/* ---- observability ------------------------------------------------------------ */
+/* kernels launched by this context since init (bench.py's gpu_launches) */
+long long examg_launch_count(examg_ctx *ctx);
+/* bytes of device memory held by this context */
+long long examg_device_bytes(examg_ctx *ctx);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* EXAMG_H */
