@@ -1,0 +1,335 @@
+#!/usr/bin/env python
+"""bench.py -- 3D Poisson V-cycle throughput (DoF-cycles/s) on N B200s.
+
+Workload (BASELINE.json configs[1]): Benchmark/Poisson3D 7-point constant-coefficient
+Poisson, V(2,2) red-black Gauss-Seidel (omega 0.8), CG coarse solve, 512^3 cells per
+GPU (levels 2..9 as in Benchmark/Poisson3D/3D_FD_Poisson_fromL4_CUDA.knowledge), double
+precision, Dirichlet data x^2 - y^2/2 - z^2/2, RHS = 0.  N > 1: weak scaling, one block
+of 512^3 cells per GPU (domain_rect_numBlocks 2x1x1, 2x2x1, 2x2x2).
+
+A step = one mgCycle@finest + the outer-loop residual and its L2 norm
+(Solve@finest's loop body, ...fromL4.exa4:135-149).  Prints ONE JSON line.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+BLOCKS = {1: (1, 1, 1), 2: (2, 1, 1), 4: (2, 2, 1), 8: (2, 2, 2)}
+NU_PRE = NU_POST = 2
+OMEGA = 0.8
+MIN_LEVEL = 2
+# algorithmic bytes per fine-grid point (DESIGN.md "Byte model")
+BYTES_RBGS_SWEEP = 24.0
+BYTES_RESIDUAL = 24.0
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        with open(p) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured"
+    return 6650.0, "fallback"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed region."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.rows, self.proc = index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append(line.strip())
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        self.t.join(timeout=2)
+        sm, mx, reasons = [], None, set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            c = [x.strip() for x in r.split(",")]
+            if len(c) < 7:
+                continue
+            try:
+                sm.append(float(c[0]))
+                mx = float(c[1])
+            except ValueError:
+                continue
+            for nm, v in zip(names, c[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(nm)
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": mx, "reasons": sorted(reasons),
+                "samples": len(sm)}
+
+
+def set_benchmark_problem(prog):
+    """Solution@finest = Dirichlet data on the boundary, 0 inside; RHS = 0 (Benchmark/Poisson3D)."""
+    from exastencils_b200 import runtime as rt
+    f = prog.f_solution[prog.max_level]
+    bc = [(rt.OP_X, 0), (rt.OP_X, 0), (rt.OP_MUL, 0),
+          (rt.OP_CONST, 0.5), (rt.OP_Y, 0), (rt.OP_MUL, 0), (rt.OP_Y, 0), (rt.OP_MUL, 0), (rt.OP_SUB, 0),
+          (rt.OP_CONST, 0.5), (rt.OP_Z, 0), (rt.OP_MUL, 0), (rt.OP_Z, 0), (rt.OP_MUL, 0), (rt.OP_SUB, 0)]
+    prog.ctx.field_set_bc_expr(f, bc)
+    prog.ctx.fill(f, 0.0)
+    prog.ctx.apply_bc(f)
+    prog.ctx.fill(prog.f_rhs[prog.max_level], 0.0)
+
+
+def run_reference(args):
+    """--impl reference: the CPU restatement of the reference's generated C++/OpenMP solver
+    (oracle/, kind "port": the generator needs a JVM, absent here) on the host cores."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    from oracle import oracle as og
+    og.build()
+    level = args.cpu_level
+    ncores = os.cpu_count() or 1
+    s = og.Solver(3, (1, 1, 1), MIN_LEVEL, level, op=og.OP_LAPLACE_SCALED, order=og.ORDER_BENCH,
+                  smoother=og.SMOOTH_RBGS, omega=OMEGA, nu_pre=NU_PRE, nu_post=NU_POST, cg_max_it=128, cg_rel_tol=1e-3)
+    _oracle_problem(s, level)
+    for _ in range(args.warmup):
+        s.vcycle()
+        s.update_residual_norm()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        s.vcycle()
+        s.update_residual_norm()
+    dt = time.perf_counter() - t0
+    n = (1 << level) - 1
+    dof = float(n) ** 3
+    val = dof * args.steps / dt
+    sample = "%d V(2,2) cycles + residual norm at %d^3 cells on one host (OpenMP, %d threads)" % (
+        args.steps, 1 << level, ncores)
+    line = {"impl": "reference", "metric": "3D Poisson V-cycle DoF-cycles/s", "value": val, "unit": "DoF-cycles/s",
+            "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": workload_config(args.gpus, args.level),
+            "cpu_baseline": {"value": val, "unit": "DoF-cycles/s", "cores": ncores, "kind": "port", "sample": sample},
+            "e2e": {"value": val, "unit": "DoF-cycles/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line))
+
+
+def _oracle_problem(s, level):
+    import numpy as np
+    x, y, z = s.node_positions(level)
+    X, Y, Z = x[None, None, :], y[None, :, None], z[:, None, None]
+    u = s.solution(level)
+    u[...] = ((X * X) - ((0.5 * Y) * Y)) - ((0.5 * Z) * Z)
+    u[1:-1, 1:-1, 1:-1] = 0.0
+
+
+def workload_config(n_gpus, level):
+    return {"workload": "Benchmark/Poisson3D 7-point constant-coefficient, V(2,2) RBGS omega=0.8, CG coarse solve, "
+                        "%d^3 cells per GPU, levels %d..%d" % (1 << level, MIN_LEVEL, level),
+            "blocks": list(BLOCKS[n_gpus]), "cells_per_gpu": (1 << level) ** 3, "smoother": "rbgs", "nu_pre": NU_PRE,
+            "nu_post": NU_POST, "l2_policy": "inputs larger than L2 (3 fields x %.2f GB on the finest level)"
+            % (8.0 * ((1 << level) + 1) ** 3 / 1e9)}
+
+
+def cpu_baseline(args):
+    """Bounded sample of the same workload on the host cores with the oracle (kind "port")."""
+    from oracle import oracle as og
+    og.build()
+    level = args.cpu_level
+    ncores = os.cpu_count() or 1
+    s = og.Solver(3, (1, 1, 1), MIN_LEVEL, level, op=og.OP_LAPLACE_SCALED, order=og.ORDER_BENCH,
+                  smoother=og.SMOOTH_RBGS, omega=OMEGA, nu_pre=NU_PRE, nu_post=NU_POST, cg_max_it=128, cg_rel_tol=1e-3)
+    _oracle_problem(s, level)
+    s.vcycle()
+    s.update_residual_norm()
+    reps = args.cpu_cycles
+    t0 = time.perf_counter()
+    for _ in range(reps):
+        s.vcycle()
+        s.update_residual_norm()
+    dt = time.perf_counter() - t0
+    s.close()
+    dof = float((1 << level) - 1) ** 3
+    return {"value": dof * reps / dt, "unit": "DoF-cycles/s", "cores": ncores, "kind": "port",
+            "sample": "%d V(2,2) cycles + residual norm at %d^3 cells (OpenMP, %d threads, %.1f s)" % (
+                reps, 1 << level, ncores, dt)}
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="examg", choices=["examg", "reference"])
+    ap.add_argument("--level", type=int, default=9, help="finest level per GPU (9 = 512^3 cells)")
+    ap.add_argument("--cpu-level", type=int, default=9)
+    ap.add_argument("--cpu-cycles", type=int, default=3)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    if args.gpus not in BLOCKS:
+        raise SystemExit("--gpus must be 1, 2, 4 or 8")
+    if args.impl == "reference":
+        return run_reference(args)
+
+    import torch
+    from exastencils_b200 import MultigridProgram
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    if world != args.gpus:
+        raise SystemExit("--gpus %d but WORLD_SIZE %d (launch with torch.distributed.run)" % (args.gpus, world))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: libexamg has no CPU path")
+    torch.cuda.set_device(local_rank)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    stream = torch.cuda.Stream()
+    level = args.level
+    prog = MultigridProgram(3, (1, 1, 1), MIN_LEVEL, level, op="scaled", order="bench", smoother="rbgs", omega=OMEGA,
+                            nu_pre=NU_PRE, nu_post=NU_POST, cg_max_it=128, cg_rel_tol=1e-3,
+                            num_blocks=BLOCKS[world], rank=rank, device=local_rank, stream=stream.cuda_stream)
+    if world > 1:
+        from exastencils_b200.distributed import wire_peers
+        wire_peers(prog.ctx, dist)
+    set_benchmark_problem(prog)
+    ctx = prog.ctx
+    nb = BLOCKS[world]
+    dof = 1.0
+    for d in range(3):
+        dof *= (nb[d] << level) - 1
+
+    def barrier():
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # ---- device-resident throughput ------------------------------------------------
+    with torch.cuda.stream(stream):
+        for _ in range(args.warmup):
+            prog.cycles(1)
+        barrier()
+        sampler = ClockSampler(local_rank)
+        if rank == 0:
+            sampler.start()
+        l0 = ctx.launch_count()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(stream)
+        for _ in range(args.steps):
+            res = prog.cycles(1)
+        e1.record(stream)
+        barrier()
+        ms = e0.elapsed_time(e1)
+        launches = ctx.launch_count() - l0
+        clocks = sampler.stop() if rank == 0 else None
+    if dist is not None:
+        t = torch.tensor([ms], device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
+    value = dof * args.steps / (ms * 1e-3)
+
+    # ---- end to end through the C ABI with host buffers -----------------------------
+    # every step: H2D of the step's input (RHS@finest, pinned), one cycle + residual norm, D2H of the norm
+    shape = ctx.shape(level)
+    rhs_host = torch.zeros(shape, dtype=torch.float64).pin_memory()
+    h2d = rhs_host.numel() * 8
+    set_benchmark_problem(prog)
+    with torch.cuda.stream(stream):
+        for _ in range(args.warmup):
+            ctx.upload_async(prog.f_rhs[level], rhs_host.data_ptr())
+            prog.cycles(1)
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(stream)
+        for _ in range(args.steps):
+            ctx.upload_async(prog.f_rhs[level], rhs_host.data_ptr())
+            res_e2e = prog.cycles(1)  # synchronises: the norm is read back on the host
+        e1.record(stream)
+        barrier()
+        ms_e2e = e0.elapsed_time(e1)
+    if dist is not None:
+        t = torch.tensor([ms_e2e], device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms_e2e = float(t.item())
+    e2e = {"value": dof * args.steps / (ms_e2e * 1e-3), "unit": "DoF-cycles/s", "h2d_bytes_per_step": h2d,
+           "d2h_bytes_per_step": 16, "ms_per_step": ms_e2e / args.steps,
+           "what": "per step: RHS@finest H2D from pinned memory, mgCycle + residual, norm D2H"}
+
+    # ---- roofline of the dominant kernel (RBGS sweeps on the finest level), timed alone ----
+    peak, peak_kind = peaks()
+    A, u, f = prog.stencil[level], prog.f_solution[level], prog.f_rhs[level]
+    n_loc = ctx.dims(level)
+    pts = float(n_loc[0] - 2) * (n_loc[1] - 2) * (n_loc[2] - 2) if world == 1 else float(n_loc[0]) * n_loc[1] * n_loc[2]
+    reps = max(5, args.steps)
+    with torch.cuda.stream(stream):
+        for _ in range(3):
+            ctx.smooth_rbgs(A, u, f, OMEGA, NU_PRE)
+        torch.cuda.synchronize()
+        l1 = ctx.launch_count()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(stream)
+        for _ in range(reps):
+            ctx.smooth_rbgs(A, u, f, OMEGA, NU_PRE)
+        e1.record(stream)
+        torch.cuda.synchronize()
+        ms_k = e0.elapsed_time(e1) / reps
+        k_launches = (ctx.launch_count() - l1) // reps
+        e0.record(stream)
+        for _ in range(reps):
+            ctx.residual(A, u, f, prog.f_residual[level])
+        e1.record(stream)
+        torch.cuda.synchronize()
+        ms_r = e0.elapsed_time(e1) / reps
+    alg_bytes = BYTES_RBGS_SWEEP * NU_PRE * pts
+    achieved = alg_bytes / (ms_k * 1e-3) / 1e9
+    roofline = {"bound": "hbm", "kernel": "RBGS smoother, %d sweeps on the finest level (%d launch(es))" % (NU_PRE, k_launches),
+                "achieved": achieved, "peak": peak, "peak_kind": peak_kind + " (MEASURED_PEAKS.json hbm_gbs, burst)",
+                "unit": "GB/s", "frac": achieved / peak, "traffic": None,
+                "algorithmic_bytes_per_launch_group": alg_bytes, "ms": ms_k,
+                "residual": {"achieved": BYTES_RESIDUAL * pts / (ms_r * 1e-3) / 1e9, "ms": ms_r,
+                             "frac": BYTES_RESIDUAL * pts / (ms_r * 1e-3) / 1e9 / peak}}
+    traffic_file = os.path.join(ROOT, "profiles", "traffic.json")
+    if os.path.exists(traffic_file):
+        with open(traffic_file) as fh:
+            roofline["traffic"] = json.load(fh).get("rbgs_bytes_per_launch_group")
+
+    cb = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        cb = cpu_baseline(args)
+
+    if rank == 0:
+        line = {"metric": "3D Poisson V-cycle DoF-cycles/s", "value": value, "unit": "DoF-cycles/s",
+                "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps,
+                "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
+                "data": "synthetic", "config": workload_config(world, level), "e2e": e2e,
+                "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline, "cpu_baseline": cb,
+                "final_residual": res, "device_bytes": ctx.device_bytes()}
+        print(json.dumps(line))
+    prog.close()
+    if dist is not None:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,12 @@
+"""exastencils_b200 -- host side of libexamg, the B200-native runtime behind the
+geometric-multigrid V-cycle the ExaStencils generator emits.
+
+  runtime.py  ctypes binding of the C ABI (include/examg.h)
+  program.py  the generated solver's leveled functions (Solve, mgCycle, ResNorm ...)
+  csrc/       CUDA sources of libexamg.so (sm_100a), built in-tree into lib/
+
+There is no CPU implementation in this package; the CPU oracle lives in oracle/ and is
+test infrastructure only.
+"""
+from .runtime import ExaMGError, Context, build, lib  # noqa: F401
+from .program import MultigridProgram, laplace_stencil  # noqa: F401

@@ -166,11 +166,13 @@ def run_solve(prog, solver, printer, max_abs_err=None):
     while not (it >= prog.max_it or prog.converged(res, init_res)):
         it += 1
         solver.vcycle()
+        # a GPU solver downloads its Solution (get<name>()); the oracle aliases its own array
+        fetch = getattr(solver, "fetch_solution", None) or (lambda: solver.solution(solver.max_level))
         if prog.prints == "err+res":  # PrintError precedes the residual update in 2D_FD_Poisson_fromL4
-            out.append(printer(max_abs_err(solver.solution(solver.max_level), prog._exact)))
+            out.append(printer(max_abs_err(fetch(), prog._exact)))
         res = solver.update_residual_norm()
         if prog.prints == "err":
-            out.append(printer(max_abs_err(solver.solution(solver.max_level), prog._exact)))
+            out.append(printer(max_abs_err(fetch(), prog._exact)))
         else:
             out.append(printer(res))
     if prog.print_count:

@@ -1,0 +1,81 @@
+"""CPU-side checks of the drop-in boundary: libexamg.so builds, loads, exports every
+symbol include/examg.h declares, the ctypes binding covers all of them, and the
+product path fails loudly (no CPU fallback) when there is no CUDA device."""
+import ctypes
+import os
+import re
+
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+@pytest.fixture(scope="module")
+def built():
+    import exastencils_b200
+    exastencils_b200.build()
+    return exastencils_b200
+
+
+def _declared_symbols():
+    text = open(os.path.join(ROOT, "include", "examg.h")).read()
+    text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
+    return sorted(set(re.findall(r"\b(examg_[a-z0-9_]+)\s*\(", text)))
+
+
+def test_header_symbols_exported(built):
+    from exastencils_b200 import runtime as rt
+    syms = _declared_symbols()
+    assert len(syms) >= 45
+    L = ctypes.CDLL(rt.LIB_PATH)
+    missing = [s for s in syms if not hasattr(L, s)]
+    assert not missing, "declared in examg.h but not exported: %s" % missing
+
+
+def test_binding_covers_header(built):
+    from exastencils_b200 import runtime as rt
+    assert sorted(rt.SIGNATURES) == _declared_symbols()
+    assert rt.lib().examg_abi_version() == 1
+
+
+def test_header_cites_reference():
+    text = open(os.path.join(ROOT, "include", "examg.h")).read()
+    assert text.count(".scala:") >= 15
+
+
+def test_no_cpu_fallback(built):
+    """Without a GPU the product path must raise, not compute on the CPU."""
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("GPU present")
+    from exastencils_b200 import runtime as rt, MultigridProgram
+    with pytest.raises(rt.ExaMGError, match="no CUDA device"):
+        rt.Context(3, 1, 3)
+    with pytest.raises(rt.ExaMGError):
+        MultigridProgram(3, (1, 1, 1), 1, 3)
+
+
+def test_product_does_not_import_oracle():
+    pkg = os.path.join(ROOT, "exastencils_b200")
+    for dirpath, _, files in os.walk(pkg):
+        for fn in files:
+            if fn.endswith((".py", ".cu", ".cuh", ".h", ".cpp")):
+                src = open(os.path.join(dirpath, fn)).read()
+                assert not re.search(r"^\s*(from|import)\s+oracle|#include\s+\".*oracle|dlopen.*oracle|CDLL.*oracle",
+                                     src, flags=re.M), fn
+
+
+def test_laplace_stencil_matches_oracle(oracle):
+    """Generation-time stencil constants of the host side equal the oracle's."""
+    from exastencils_b200 import laplace_stencil
+    for dim, F, lvl, op, order in [(3, (1, 1, 1), 5, oracle.OP_LAPLACE_SCALED, oracle.ORDER_BENCH),
+                                   (2, (4, 4), 6, oracle.OP_LAPLACE_SCALED, oracle.ORDER_TESTING),
+                                   (3, (9, 9, 9), 2, oracle.OP_LAPLACE_UNSCALED, oracle.ORDER_TESTING)]:
+        s = oracle.Solver(dim, F, lvl, lvl, op=op, order=order)
+        st = s.stencil(lvl)
+        h = [1.0 / (F[d] << lvl) if d < dim else 1.0 for d in range(3)]
+        offs, coefs = laplace_stencil(dim, h, scaled=(op == oracle.OP_LAPLACE_SCALED),
+                                      order="bench" if order == oracle.ORDER_BENCH else "testing")
+        assert offs == st.offsets()
+        assert coefs == st.coeffs()
+        s.close()

@@ -1,0 +1,263 @@
+"""CUDA-vs-oracle parity of every hot-path kernel, through the C ABI (libexamg.so).
+
+Bar: fields bit-exact (the kernels and the oracle share one floating-point
+association, DESIGN.md "Arithmetic contract"); reductions within 1e-14 relative
+(double-double sums make them order-insensitive; only the final rounding can differ).
+Sizes are small enough for the oracle to finish in well under a second each; ragged
+(non power-of-two) and degenerate (no interior point) grids are included.
+"""
+import itertools
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+RTOL_SUM = 1e-14
+
+
+def _ctx(dim, cells, lvl_lo, lvl_hi):
+    from exastencils_b200 import runtime as rt
+    return rt.Context(dim, lvl_lo, lvl_hi, block_cells=cells)
+
+
+def _rand(shape, seed):
+    rng = np.random.default_rng(seed)
+    return rng.uniform(-1.0, 1.0, size=shape)
+
+
+def _stencil_offsets(dim, npts):
+    if npts in (5, 7):
+        offs = [(0, 0, 0)]
+        for d in range(dim):
+            for s in (-1, 1):
+                o = [0, 0, 0]
+                o[d] = s
+                offs.append(tuple(o))
+        return offs
+    rng = range(-1, 2)
+    if dim == 2:
+        offs = [(dx, dy, 0) for dy in rng for dx in rng]
+    else:
+        offs = [(dx, dy, dz) for dz in rng for dy in rng for dx in rng]
+    # centre first is not required; keep lexicographic order to exercise `centre` lookup
+    return offs
+
+
+CASES = [
+    # dim, cells per dim at level 0, level, stencil points
+    (2, (1, 1), 5, 5), (2, (3, 5), 3, 5), (2, (4, 4), 4, 9), (2, (1, 1), 1, 9),
+    (3, (1, 1, 1), 4, 7), (3, (3, 2, 5), 2, 7), (3, (9, 9, 9), 1, 7), (3, (1, 1, 1), 3, 27), (3, (5, 3, 2), 2, 27),
+    (3, (1, 1, 1), 1, 7), (3, (1, 1, 1), 0, 7), (2, (1, 1), 0, 5),
+    (3, (1, 1, 1), 6, 7),   # 65^3: several blocks per dimension, z-marching
+    (2, (1, 1), 9, 5),      # 513^2
+]
+
+
+@pytest.mark.parametrize("dim,cells,lvl,npts", CASES)
+@pytest.mark.parametrize("var", [False, True], ids=["const", "stencilfield"])
+def test_stencil_loops(dim, cells, lvl, npts, var, oracle):
+    og = oracle
+    ctx = _ctx(dim, cells, lvl, lvl)
+    shape = ctx.shape(lvl)
+    offs = _stencil_offsets(dim, npts)
+    seed = hash((dim, cells, lvl, npts, var)) % (2 ** 31)
+    coef = _rand(len(offs), seed)
+    centre = offs.index((0, 0, 0))
+    coef[centre] = 4.0 + abs(coef[centre])
+    u, rhs = _rand(shape, seed + 1), _rand(shape, seed + 2)
+    sf = None
+    if var:
+        sf = _rand((len(offs),) + shape, seed + 3)
+        sf[centre] = 4.0 + np.abs(sf[centre])
+        sf = np.ascontiguousarray(sf)
+        cf = ctx.field_create("coef", lvl, 1, len(offs))
+        ctx.upload(cf, sf)
+        A = ctx.stencil_field(lvl, offs, cf)
+    else:
+        A = ctx.stencil_const(lvl, offs, coef)
+    st = og.Stencil.make(offs, coef)
+    fu = ctx.field_create("u", lvl, 2, 1)
+    ff = ctx.field_create("rhs", lvl, 1, 1)
+    fo = ctx.field_create("out", lvl, 1, 1)
+    ctx.upload(fu, u, 0)
+    ctx.upload(fu, u, 1)
+    ctx.upload(ff, rhs)
+    sentinel = _rand(shape, seed + 4)
+
+    def ref3(a):
+        return a.reshape((1,) + a.shape) if a.ndim == 2 else a
+
+    # A*u
+    ctx.upload(fo, sentinel)
+    ctx.apply(A, fu, fo)
+    exp = sentinel.copy()
+    got = ctx.download(fo, lvl)
+    e = og.apply(st, u, sf)
+    inner = (Ellipsis,) + tuple(slice(1, -1) for _ in range(dim))
+    exp[inner] = e[inner]
+    assert np.array_equal(got, exp)
+    # residual + fused norm
+    ctx.upload(fo, sentinel)
+    n2 = ctx.residual(A, fu, ff, fo, norm=True)
+    e = og.residual(st, u, rhs, sf)
+    exp = sentinel.copy()
+    exp[inner] = e[inner]
+    assert np.array_equal(ctx.download(fo, lvl), exp)
+    n2_ref = og.dot(e, e)
+    assert abs(n2 - n2_ref) <= RTOL_SUM * abs(n2_ref)
+    # Jacobi (slot 0 -> slot 1, advance)
+    omega = 0.8
+    ctx.smooth_jacobi(A, fu, ff, omega, 1)
+    assert ctx.field_active_slot(fu) == 1
+    e = og.smooth_jacobi(st, omega, u, rhs, sf)
+    assert np.array_equal(ctx.download(fu, lvl), e)
+    ctx.field_advance(fu)
+    assert ctx.field_active_slot(fu) == 0
+    # red-black colours in place
+    e = u.copy()
+    for color in (0, 1, 1, 0):
+        ctx.smooth_rb_color(A, fu, ff, omega, color)
+        og.smooth_rb(st, omega, e, rhs, color, sf)
+        assert np.array_equal(ctx.download(fu, lvl), e), "colour %d" % color
+    ctx.smooth_rbgs(A, fu, ff, omega, 2)
+    for _ in range(2):
+        og.smooth_rb(st, omega, e, rhs, 0, sf)
+        og.smooth_rb(st, omega, e, rhs, 1, sf)
+    assert np.array_equal(ctx.download(fu, lvl), e)
+    ctx.close()
+
+
+@pytest.mark.parametrize("dim,cells,lvl", [(2, (1, 1), 5), (2, (3, 5), 3), (3, (1, 1, 1), 4), (3, (3, 2, 5), 2),
+                                           (3, (9, 9, 9), 1), (3, (1, 1, 1), 1), (2, (1, 1), 1), (3, (1, 1, 1), 6),
+                                           (2, (1, 1), 9)])
+def test_transfer(dim, cells, lvl, oracle):
+    og = oracle
+    ctx = _ctx(dim, cells, lvl - 1, lvl)
+    fs, cs = ctx.shape(lvl), ctx.shape(lvl - 1)
+    seed = 77 + lvl
+    rf, uc, uf, sent = _rand(fs, seed), _rand(cs, seed + 1), _rand(fs, seed + 2), _rand(cs, seed + 3)
+    f_rf = ctx.field_create("Residual", lvl)
+    f_rc = ctx.field_create("RHS", lvl - 1)
+    f_uc = ctx.field_create("Solution", lvl - 1)
+    f_uf = ctx.field_create("Solution", lvl)
+    inner = (Ellipsis,) + tuple(slice(1, -1) for _ in range(dim))
+    for scale in (1.0, 4.0):
+        ctx.upload(f_rf, rf)
+        ctx.upload(f_rc, sent)
+        ctx.restrict(f_rf, f_rc, scale)
+        e = og.restrict(dim, rf, cs, scale)
+        exp = sent.copy()
+        exp[inner] = e[inner]
+        assert np.array_equal(ctx.download(f_rc, lvl - 1), exp)
+    ctx.upload(f_uc, uc)
+    ctx.upload(f_uf, uf)
+    ctx.prolong_add(f_uc, f_uf)
+    e = og.prolong_add(dim, uc, uf.copy())
+    assert np.array_equal(ctx.download(f_uf, lvl), e)
+    ctx.close()
+
+
+@pytest.mark.parametrize("dim,cells,lvl", [(2, (3, 5), 3), (3, (3, 2, 5), 2), (3, (1, 1, 1), 6), (2, (1, 1), 10),
+                                           (3, (1, 1, 1), 0)])
+def test_streaming_and_reductions(dim, cells, lvl, oracle):
+    og = oracle
+    ctx = _ctx(dim, cells, lvl, lvl)
+    shape = ctx.shape(lvl)
+    a, b = _rand(shape, 5), _rand(shape, 6) * 1e3
+    fa, fb = ctx.field_create("a", lvl), ctx.field_create("b", lvl)
+    ctx.upload(fa, a)
+    ctx.upload(fb, b)
+    d = ctx.dot(fa, fb)
+    dr = og.dot(a, b)
+    assert abs(d - dr) <= RTOL_SUM * max(abs(dr), 1e-300)
+    assert ctx.max_abs_diff(fa, fb) == og.max_abs_diff(a, b)
+    ctx.axpy(0.37, fa, fb)
+    og.axpy(0.37, a, b)
+    assert np.array_equal(ctx.download(fb, lvl), b)
+    ctx.xpay(fa, -1.25, fb)
+    og.xpay(a, -1.25, b)
+    assert np.array_equal(ctx.download(fb, lvl), b)
+    ctx.copy(fa, fb)
+    inner = (Ellipsis,) + tuple(slice(1, -1) for _ in range(dim))
+    b[inner] = a[inner]
+    assert np.array_equal(ctx.download(fb, lvl), b)
+    ctx.set(fb, 2.5)
+    b[inner] = 2.5
+    assert np.array_equal(ctx.download(fb, lvl), b)
+    ctx.fill(fb, -3.0)
+    assert np.array_equal(ctx.download(fb, lvl), np.full(shape, -3.0))
+    ctx.close()
+
+
+def test_dot_cancellation(oracle):
+    """Ill-conditioned sum: the double-double accumulation must keep the small terms."""
+    og = oracle
+    lvl = 5
+    ctx = _ctx(3, (1, 1, 1), lvl, lvl)
+    shape = ctx.shape(lvl)
+    a = _rand(shape, 11)
+    b = np.ones(shape)
+    a[1, 1, 1], a[-2, -2, -2] = 1e17, -1e17
+    fa, fb = ctx.field_create("a", lvl), ctx.field_create("b", lvl)
+    ctx.upload(fa, a)
+    ctx.upload(fb, b)
+    d, dr = ctx.dot(fa, fb), og.dot(a, b)
+    assert abs(d - dr) <= 1e-12 * abs(dr)
+    ctx.close()
+
+
+@pytest.mark.parametrize("dim", [2, 3])
+def test_dirichlet_bc(dim):
+    """apply bc: constant and expression Dirichlet values on all physical-boundary nodes."""
+    from exastencils_b200 import runtime as rt
+    lvl = 4
+    ctx = _ctx(dim, (3, 2, 1)[:dim], lvl, lvl)
+    shape = ctx.shape(lvl)
+    u = _rand(shape, 3)
+    f = ctx.field_create("Solution", lvl)
+    ctx.upload(f, u)
+    ctx.field_set_bc(f, rt.BC_DIRICHLET_CONST, 1.5)
+    ctx.apply_bc(f)
+    exp = u.copy()
+    exp[..., 0] = exp[..., -1] = 1.5
+    exp[..., 0, :] = exp[..., -1, :] = 1.5
+    if dim == 3:
+        exp[0] = exp[-1] = 1.5
+    assert np.array_equal(ctx.download(f, lvl), exp)
+    # vf_boundaryPosition_x ** 2 - 0.5 * vf_boundaryPosition_y ** 2 - 0.5 * vf_boundaryPosition_z ** 2
+    prog = [(rt.OP_X, 0), (rt.OP_X, 0), (rt.OP_MUL, 0),
+            (rt.OP_CONST, 0.5), (rt.OP_Y, 0), (rt.OP_MUL, 0), (rt.OP_Y, 0), (rt.OP_MUL, 0), (rt.OP_SUB, 0),
+            (rt.OP_CONST, 0.5), (rt.OP_Z, 0), (rt.OP_MUL, 0), (rt.OP_Z, 0), (rt.OP_MUL, 0), (rt.OP_SUB, 0)]
+    ctx.field_set_bc_expr(f, prog)
+    ctx.apply_bc(f)
+    nx, ny, nz = ctx.dims(lvl)
+    h = ctx.width(lvl)
+    X = (np.arange(nx) * h[0])[None, None, :]
+    Y = (np.arange(ny) * h[1])[None, :, None]
+    Z = (np.arange(nz) * h[2])[:, None, None] if dim == 3 else np.zeros((1, 1, 1))
+    vals = np.broadcast_to(((X * X) - ((0.5 * Y) * Y)) - ((0.5 * Z) * Z), (nz, ny, nx)).reshape(shape)
+    exp = u.copy()
+    exp[..., 0], exp[..., -1] = vals[..., 0], vals[..., -1]
+    exp[..., 0, :], exp[..., -1, :] = vals[..., 0, :], vals[..., -1, :]
+    if dim == 3:
+        exp[0], exp[-1] = vals[0], vals[-1]
+    assert np.array_equal(ctx.download(f, lvl), exp)
+    with pytest.raises(rt.ExaMGError):
+        ctx.field_set_bc_expr(f, [(rt.OP_ADD, 0)])
+    ctx.close()
+
+
+def test_error_convention():
+    from exastencils_b200 import runtime as rt
+    ctx = _ctx(3, (1, 1, 1), 1, 3)
+    with pytest.raises(rt.ExaMGError):
+        ctx.field_create("x", 7)
+    f3, f2 = ctx.field_create("a", 3), ctx.field_create("b", 2)
+    with pytest.raises(rt.ExaMGError):
+        ctx.dot(f3, f2)
+    with pytest.raises(rt.ExaMGError):
+        ctx.stencil_const(3, [(1, 0, 0)], [1.0])  # no centre entry
+    with pytest.raises(rt.ExaMGError):
+        ctx.upload(99, np.zeros(ctx.shape(3)))
+    ctx.close()

@@ -1,0 +1,135 @@
+"""Whole-solver parity on the GPU: the reference's regression programs run through
+libexamg must (a) print the reference's golden stdout (4 s.f., tests/golden/) and
+(b) match the CPU oracle -- Solution fields bit-for-bit after every V-cycle,
+residual norms within 1e-12 relative (the tolerance BASELINE.json's north_star states).
+Both host modes are covered: the library cycle (CUDA graph) and the call-by-call
+sequence the generator back-end emits.
+"""
+import numpy as np
+import pytest
+
+import programs
+from oracle_driver import make_oracle_solver
+
+pytestmark = pytest.mark.gpu
+
+RTOL_NORM = 1e-12
+
+
+def make_gpu_solver(cfg, mode="library", **override):
+    from exastencils_b200 import MultigridProgram
+    c = dict(cfg)
+    c.update(override)
+    return MultigridProgram(c["dim"], tuple(c["F"]), c["min_level"], c["max_level"], op=c["op"], order=c["order"],
+                            kappa=c.get("kappa", 0.0), smoother=c["smoother"], omega=c["omega"], nu_pre=c["nu_pre"],
+                            nu_post=c["nu_post"], restrict_scale=c["restrict_scale"], cg_max_it=c["cg_max_it"],
+                            cg_rel_tol=c["cg_rel_tol"], mode=mode)
+
+
+def _setup_pair(prog, mode, **override):
+    ref = make_oracle_solver(prog.cfg, **override)
+    gpu = make_gpu_solver(prog.cfg, mode, **override)
+    prog.setup(ref)
+    ref.sync_slots()
+    prog.setup(gpu)
+    if prog.cfg["op"] == "varcoeff":  # identical operator data on both sides
+        for lvl in range(ref.min_level, ref.max_level + 1):
+            gpu.coeff(lvl)[...] = ref.coeff(lvl).reshape(gpu.coeff(lvl).shape)
+    gpu.sync_slots()
+    return ref, gpu
+
+
+@pytest.mark.parametrize("mode", ["library", "calls"])
+@pytest.mark.parametrize("prog", [programs.POISSON_2D, programs.SISC_2D_CONST, programs.SISC_2D_VAR,
+                                  programs.SMOOTHERS_RBGS, programs.SMOOTHERS_JAC], ids=lambda p: p.name)
+def test_golden_stdout(prog, mode, oracle):
+    """Same printed history as the reference's .results file."""
+    if mode == "calls" and prog.dim == 3:
+        pytest.skip("call-by-call mode is covered in 2D and by test_oracle_parity")
+    gpu = make_gpu_solver(prog.cfg, mode)
+    prog.setup(gpu)
+    if prog.cfg["op"] == "varcoeff":
+        ref = make_oracle_solver(prog.cfg)
+        for lvl in range(ref.min_level, ref.max_level + 1):
+            gpu.coeff(lvl)[...] = ref.coeff(lvl).reshape(gpu.coeff(lvl).shape)
+        ref.close()
+    gpu.sync_slots()
+    out = programs.run_solve(prog, gpu, oracle.print_reduced_prec, oracle.max_abs_diff)
+    gpu.close()
+    assert out == prog.expected()
+
+
+@pytest.mark.parametrize("prog", [programs.SISC_3D_CONST, programs.SISC_3D_VAR], ids=lambda p: p.name)
+def test_golden_stdout_3d_sisc(prog, oracle):
+    """256^3-cell SISC programs (the reference's own CUDA target is tested on these)."""
+    gpu = make_gpu_solver(prog.cfg, "library")
+    prog.setup(gpu)
+    if prog.cfg["op"] == "varcoeff":
+        ref = make_oracle_solver(prog.cfg)
+        for lvl in range(ref.min_level, ref.max_level + 1):
+            gpu.coeff(lvl)[...] = ref.coeff(lvl).reshape(gpu.coeff(lvl).shape)
+        ref.close()
+    gpu.sync_slots()
+    out = programs.run_solve(prog, gpu, oracle.print_reduced_prec, oracle.max_abs_diff)
+    gpu.close()
+    assert out == prog.expected()
+
+
+SMALL = dict(max_level=4)
+
+
+@pytest.mark.parametrize("mode", ["library", "calls"])
+@pytest.mark.parametrize("prog,override", [
+    (programs.POISSON_2D, dict(max_level=6)),
+    (programs.SISC_2D_VAR, dict(max_level=6)),
+    (programs.SMOOTHERS_RBGS, dict(max_level=3)),
+    (programs.SMOOTHERS_JAC, dict(max_level=3)),
+    (programs.SISC_3D_CONST, dict(max_level=3)),
+    (programs.SISC_3D_VAR, dict(max_level=3)),
+    (programs.SMOOTHERS_RBGS, dict(max_level=3, nu_pre=2, nu_post=2, omega=0.8)),   # V(2,2), north-star smoother
+    (programs.SMOOTHERS_JAC, dict(max_level=3, nu_pre=2, nu_post=1)),                # odd sweep count: slot parity flips
+], ids=lambda v: v.name if hasattr(v, "name") else "-".join("%s%s" % kv for kv in v.items()))
+def test_oracle_parity(prog, override, mode, oracle):
+    ref, gpu = _setup_pair(prog, mode, **override)
+    lvl = ref.max_level
+    r_ref, r_gpu = ref.update_residual_norm(), gpu.update_residual_norm()
+    assert abs(r_gpu - r_ref) <= RTOL_NORM * r_ref
+    assert np.array_equal(gpu.fetch_residual(), ref.residual(lvl).reshape(gpu.ctx.shape(lvl)))
+    for cyc in range(4):
+        ref.vcycle()
+        gpu.vcycle()
+        assert gpu.last_cg_iters() == ref.last_cg_iters(), "CG iteration count, cycle %d" % cyc
+        assert np.array_equal(gpu.fetch_solution(), ref.solution(lvl).reshape(gpu.ctx.shape(lvl))), "cycle %d" % cyc
+        r_ref, r_gpu = ref.update_residual_norm(), gpu.update_residual_norm()
+        assert abs(r_gpu - r_ref) <= RTOL_NORM * r_ref
+    # coarse levels too (restriction / coarse solution of the last cycle)
+    for l in range(ref.min_level, lvl):
+        assert np.array_equal(gpu.fetch_rhs(l), ref.rhs(l).reshape(gpu.ctx.shape(l))), "RHS@%d" % l
+        assert np.array_equal(gpu.fetch_solution(l), ref.solution(l).reshape(gpu.ctx.shape(l))), "Solution@%d" % l
+    gpu.close()
+    ref.close()
+
+
+def test_benchmark_program_properties(oracle):
+    """Benchmark/Poisson3D (config 2) at a size the oracle cannot check quickly:
+    size-independent properties.  The Dirichlet data x^2 - y^2/2 - z^2/2 is harmonic and
+    quadratic, so the 7-point discrete solution equals it: the error must fall to rounding
+    level and the residual must contract by > 10x per V(2,2) cycle."""
+    from exastencils_b200 import MultigridProgram, runtime as rt
+    lvl = 7  # 129^3
+    gpu = MultigridProgram(3, (1, 1, 1), 2, lvl, op="scaled", order="bench", smoother="rbgs", omega=0.8, nu_pre=2,
+                           nu_post=2, cg_max_it=128, cg_rel_tol=1e-3)
+    f = gpu.f_solution[lvl]
+    prog = [(rt.OP_X, 0), (rt.OP_X, 0), (rt.OP_MUL, 0),
+            (rt.OP_CONST, 0.5), (rt.OP_Y, 0), (rt.OP_MUL, 0), (rt.OP_Y, 0), (rt.OP_MUL, 0), (rt.OP_SUB, 0),
+            (rt.OP_CONST, 0.5), (rt.OP_Z, 0), (rt.OP_MUL, 0), (rt.OP_Z, 0), (rt.OP_MUL, 0), (rt.OP_SUB, 0)]
+    gpu.ctx.field_set_bc_expr(f, prog)
+    gpu.ctx.apply_bc(f)
+    hist = gpu.Solve(max_it=20, target_reduction=1e-10)
+    assert len(hist) <= 12
+    for a, b in zip(hist[:-2], hist[1:-1]):
+        assert b < 0.1 * a
+    x, y, z = gpu.node_positions(lvl)
+    exact = (x[None, None, :] ** 2 - 0.5 * y[None, :, None] ** 2) - 0.5 * z[:, None, None] ** 2
+    assert np.max(np.abs(gpu.fetch_solution() - exact)) < 1e-9
+    gpu.close()
