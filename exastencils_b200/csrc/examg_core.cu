@@ -125,11 +125,11 @@ examg_ctx *examg_init(const examg_config *cfg) {
       }
     }
     g.pitch = ((XPAD + g.n[0] + 1) + 15) / 16 * 16;
-    g.ay = g.n[1] + 2;
-    g.az = cfg->dim == 3 ? g.n[2] + 2 : 1;
+    g.ay = g.n[1] + 2 * GHOST;
+    g.az = cfg->dim == 3 ? g.n[2] + 2 * GHOST : 1;
     g.plane = (long long)g.pitch * g.ay;
     g.vol = g.plane * g.az;
-    g.origin = XPAD + (long long)g.pitch + (cfg->dim == 3 ? g.plane : 0);
+    g.origin = XPAD + (long long)g.pitch * GHOST + (cfg->dim == 3 ? g.plane * GHOST : 0);
     g.par = (g.goff[0] + g.goff[1] + g.goff[2]) & 1;
     c->levels.push_back(g);
   }
@@ -160,7 +160,10 @@ int examg_finalize(examg_ctx *c) {
   cudaSetDevice(c->device);
   cudaDeviceSynchronize();
   for (auto &f : c->fields)
-    if (f.alive && f.base) cudaFree(f.base);
+    if (f.alive) {
+      for (int sl = 0; sl < f.nslots; ++sl) cudaFree(f.slot[sl]);
+      if (f.shadow) cudaFree(f.shadow);
+    }
   if (c->partials) cudaFree(c->partials);
   if (c->red_out) cudaFree(c->red_out);
   if (c->red_host) cudaFreeHost(c->red_host);
@@ -221,13 +224,17 @@ int examg_field_create(examg_ctx *c, const char *name, int level, int num_slots,
   f.level = level;
   f.nslots = num_slots;
   f.ncomp = ncomp;
-  size_t bytes = sizeof(double) * (size_t)num_slots * ncomp * g->vol;
-  cudaError_t e = cudaMalloc(&f.base, bytes);
-  if (e != cudaSuccess)
-    return set_error(EXAMG_ENOMEM, "examg_field_create(%s@%d): cudaMalloc of %zu bytes: %s", f.name.c_str(),
-                     level, bytes, cudaGetErrorString(e));
-  EXAMG_CUDA(cudaMemsetAsync(f.base, 0, bytes, c->stream));  // initFieldsWithZero
-  c->dev_bytes += (long long)bytes;
+  size_t bytes = sizeof(double) * (size_t)ncomp * g->vol;
+  for (int sl = 0; sl < num_slots; ++sl) {
+    cudaError_t e = cudaMalloc(&f.slot[sl], bytes);
+    if (e != cudaSuccess) {
+      for (int q = 0; q < sl; ++q) cudaFree(f.slot[q]);
+      return set_error(EXAMG_ENOMEM, "examg_field_create(%s@%d): cudaMalloc of %zu bytes: %s", f.name.c_str(),
+                       level, bytes, cudaGetErrorString(e));
+    }
+    EXAMG_CUDA(cudaMemsetAsync(f.slot[sl], 0, bytes, c->stream));  // initFieldsWithZero
+    c->dev_bytes += (long long)bytes;
+  }
   c->fields.push_back(f);
   return (int)c->fields.size() - 1;
 }
@@ -237,9 +244,16 @@ int examg_field_destroy(examg_ctx *c, int h) {
   if (!f) return set_error(EXAMG_EINVAL, "examg_field_destroy: handle %d", h);
   EXAMG_CUDA(cudaStreamSynchronize(c->stream));
   const LevelGeom *g = geom(c, f->level);
-  c->dev_bytes -= (long long)sizeof(double) * f->nslots * f->ncomp * g->vol;
-  cudaFree(f->base);
-  f->base = nullptr;
+  for (int sl = 0; sl < f->nslots; ++sl) {
+    c->dev_bytes -= (long long)sizeof(double) * f->ncomp * g->vol;
+    cudaFree(f->slot[sl]);
+    f->slot[sl] = nullptr;
+  }
+  if (f->shadow) {
+    c->dev_bytes -= (long long)sizeof(double) * f->ncomp * g->vol;
+    cudaFree(f->shadow);
+    f->shadow = nullptr;
+  }
   f->alive = false;
   return EXAMG_OK;
 }
@@ -343,19 +357,22 @@ int examg_field_fill(examg_ctx *c, int h, double value) {
   Field *f = get_field(c, h);
   if (!f) return set_error(EXAMG_EINVAL, "bad field %d", h);
   const LevelGeom &g = *geom(c, f->level);
-  size_t count = (size_t)f->nslots * f->ncomp * g.vol;
-  if (value == 0.0) {
-    EXAMG_CUDA(cudaMemsetAsync(f->base, 0, sizeof(double) * count, c->stream));
-    return EXAMG_OK;
-  }
-  // cudaMemset2D-style fill through the D32 memset is not available for doubles: stage one row
+  const size_t count = (size_t)f->ncomp * g.vol;
   std::vector<double> row(g.pitch, value);
-  EXAMG_CUDA(cudaMemcpyAsync(f->base, row.data(), sizeof(double) * g.pitch, cudaMemcpyHostToDevice, c->stream));
-  EXAMG_CUDA(cudaStreamSynchronize(c->stream));
-  for (size_t done = g.pitch; done < count;) {  // doubling copy
-    size_t chunk = done < count - done ? done : count - done;
-    EXAMG_CUDA(cudaMemcpyAsync(f->base + done, f->base, sizeof(double) * chunk, cudaMemcpyDeviceToDevice, c->stream));
-    done += chunk;
+  for (int sl = 0; sl < f->nslots; ++sl) {
+    double *base = f->slot[sl];
+    if (value == 0.0) {
+      EXAMG_CUDA(cudaMemsetAsync(base, 0, sizeof(double) * count, c->stream));
+      continue;
+    }
+    // no 64-bit memset in the runtime API: stage one row, then doubling device copies
+    EXAMG_CUDA(cudaMemcpyAsync(base, row.data(), sizeof(double) * g.pitch, cudaMemcpyHostToDevice, c->stream));
+    EXAMG_CUDA(cudaStreamSynchronize(c->stream));
+    for (size_t done = g.pitch; done < count;) {
+      size_t chunk = done < count - done ? done : count - done;
+      EXAMG_CUDA(cudaMemcpyAsync(base + done, base, sizeof(double) * chunk, cudaMemcpyDeviceToDevice, c->stream));
+      done += chunk;
+    }
   }
   return EXAMG_OK;
 }

@@ -30,6 +30,20 @@ struct examg_solver {
   std::map<std::vector<int>, Graph> graphs;  // keyed by the active slots of Solution on entry
 };
 
+// (active slot, shadow parity) of a Solution field, as recorded in the graph keys
+static void restore_state(Field &f, int state) {
+  const int cur = state >> 1;
+  const bool swapped = state & 1;
+  if (f.swapped != swapped) {  // the buffers of the slot that was active while sweeping are exchanged
+    // fused sweeps only run on single-slot (RBGS) fields, so the slot in question is slot[f.cur]
+    double *t = f.slot[f.cur];
+    f.slot[f.cur] = f.shadow;
+    f.shadow = t;
+    f.swapped = swapped;
+  }
+  f.cur = cur;
+}
+
 static int lv(examg_solver *s, int level) { return level - s->c->cfg.min_level; }
 
 static int smooth(examg_solver *s, int level, int n) {
@@ -133,7 +147,7 @@ int examg_solver_vcycle(examg_solver *s, int level) {
   if (!s->use_graph || level != c->cfg.max_level) return vcycle_rec(s, level);
 
   std::vector<int> key;
-  for (int h : s->sol) key.push_back(c->fields[h].cur);
+  for (int h : s->sol) key.push_back(c->fields[h].cur * 2 + (c->fields[h].swapped ? 1 : 0));
   auto it = s->graphs.find(key);
   if (it == s->graphs.end()) {
     // capture mgCycle@finest for this slot configuration
@@ -150,13 +164,13 @@ int examg_solver_vcycle(examg_solver *s, int level) {
     if (e != cudaSuccess) return set_error(EXAMG_ECUDA, "cudaGraphInstantiate: %s", cudaGetErrorString(e));
     g.launches = c->launches - l0;
     c->launches = l0;  // nothing ran yet
-    for (int h : s->sol) g.exit_slots.push_back(c->fields[h].cur);
-    for (size_t i = 0; i < s->sol.size(); ++i) c->fields[s->sol[i]].cur = key[i];
+    for (int h : s->sol) g.exit_slots.push_back(c->fields[h].cur * 2 + (c->fields[h].swapped ? 1 : 0));
+    for (size_t i = 0; i < s->sol.size(); ++i) restore_state(c->fields[s->sol[i]], key[i]);
     it = s->graphs.emplace(key, g).first;
   }
   EXAMG_CUDA(cudaGraphLaunch(it->second.exec, c->stream));
   c->launches += it->second.launches;
-  for (size_t i = 0; i < s->sol.size(); ++i) c->fields[s->sol[i]].cur = it->second.exit_slots[i];
+  for (size_t i = 0; i < s->sol.size(); ++i) restore_state(c->fields[s->sol[i]], it->second.exit_slots[i]);
   return EXAMG_OK;
 }
 

@@ -24,9 +24,13 @@ namespace examg {
 //      128-byte boundary (the left ghost is element 15 of the pad); pitch is a
 //      multiple of 16 doubles -> rows are 128-byte aligned, which is what TMA
 //      (16 B) and 128-bit vector accesses need.
-//   y,z: one ghost row/plane per side (z only in 3D).
+//   y,z: GHOST ghost rows/planes per side (z only in 3D).  Two layers, because one
+//      fused red+black sweep needs a 2-deep halo (one exchange per sweep instead
+//      of one per colour; the B200 form of the reference's contraction loops,
+//      C/s/e/baseExt/ir/IR_ContractingLoop.scala:48-90).
 // ---------------------------------------------------------------------------
 constexpr int XPAD = 16;
+constexpr int GHOST = 2;
 
 struct LevelGeom {
   int n[3];        // local nodes per dim incl. duplicate/boundary nodes (n[2] = 1 in 2D)
@@ -62,7 +66,9 @@ struct Field {
   bool alive = false;
   std::string name;
   int level = 0, nslots = 1, ncomp = 1, cur = 0;
-  double *base = nullptr;  // nslots*ncomp*vol doubles
+  double *slot[4] = {nullptr, nullptr, nullptr, nullptr};  // one allocation of ncomp*vol doubles per slot
+  double *shadow = nullptr;  // second buffer of the active slot for out-of-place fused sweeps (lazy)
+  bool swapped = false;      // slot[cur] and shadow have been exchanged an odd number of times
   int bc_kind = EXAMG_BC_NONE;
   double bc_value = 0.0;
   std::vector<examg_bc_op> bc_prog;
@@ -114,7 +120,7 @@ Stencil *get_stencil(examg_ctx *c, int h);
 inline double *field_ptr(examg_ctx *c, const Field *f, int slot, int comp = 0) {
   const LevelGeom &g = c->levels[f->level - c->cfg.min_level];
   if (slot < 0) slot = f->cur;
-  return f->base + ((long long)slot * f->ncomp + comp) * g.vol + g.origin;
+  return f->slot[slot] + (long long)comp * g.vol + g.origin;
 }
 GridArgs grid_args(const LevelGeom &g);
 StencilArgs stencil_args(const LevelGeom &g, const Stencil &s);

@@ -18,6 +18,8 @@ int launch_prolong_generic(examg_ctx *c, int lvl_fine, const double *uc, double 
 bool fast7_usable(examg_ctx *c, const Stencil &s);
 int fast7_residual(examg_ctx *c, const Stencil &s, const double *u, const double *rhs, double *res, int red_slot);
 int fast7_rb(examg_ctx *c, const Stencil &s, double omega, double *u, const double *rhs, int color);
+bool fused_rb_usable(examg_ctx *c, const Stencil &s, const Field &fu);
+int launch_rb_fused(examg_ctx *c, const Stencil &s, double omega, Field &fu, const double *rhs);
 
 int launch_residual(examg_ctx *c, const Stencil &s, const double *u, const double *rhs, double *res, int red_slot) {
   if (fast7_usable(c, s)) return fast7_residual(c, s, u, rhs, res, red_slot);
@@ -87,12 +89,28 @@ int examg_smooth_rb_color(examg_ctx *c, int A, int u, int rhs, double omega, int
   GET_STENCIL(s, A); GET_FIELD(fu, u); GET_FIELD(fr, rhs);
   CHECK_LEVEL(fu, s->level); CHECK_LEVEL(fr, s->level);
   if (color != 0 && color != 1) return set_error(EXAMG_EINVAL, "examg_smooth_rb_color: colour %d", color);
+  for (int k = 0; k < s->nst; ++k)
+    if (k != s->centre && ((s->off[k][0] + s->off[k][1] + s->off[k][2]) & 1) == 0)
+      return set_error(EXAMG_EUNSUP, "examg_smooth_rb: two colours do not decouple this stencil (entry [%d,%d,%d] "
+                       "couples points of one colour); use a star stencil or Jacobi", s->off[k][0], s->off[k][1], s->off[k][2]);
   int rc = do_exchange(c, *fu, fu->cur);
   if (rc) return rc;
   return launch_rb(c, *s, omega, field_ptr(c, fu, -1), field_ptr(c, fr, -1), color);
 }
 
 int examg_smooth_rbgs(examg_ctx *c, int A, int u, int rhs, double omega, int nsweeps) {
+  {
+    GET_STENCIL(s, A); GET_FIELD(fu, u); GET_FIELD(fr, rhs);
+    CHECK_LEVEL(fu, s->level); CHECK_LEVEL(fr, s->level);
+    if (fused_rb_usable(c, *s, *fu)) {  // both colours of a sweep in one pass over HBM
+      for (int it = 0; it < nsweeps; ++it) {
+        int rc = do_exchange(c, *fu, fu->cur);
+        if (rc) return rc;
+        if ((rc = launch_rb_fused(c, *s, omega, *fu, field_ptr(c, fr, -1)))) return rc;
+      }
+      return EXAMG_OK;
+    }
+  }
   for (int it = 0; it < nsweeps; ++it)
     for (int color = 0; color < 2; ++color) {
       int rc = examg_smooth_rb_color(c, A, u, rhs, omega, color);

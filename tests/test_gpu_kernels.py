@@ -51,6 +51,8 @@ CASES = [
     (3, (1, 1, 1), 1, 7), (3, (1, 1, 1), 0, 7), (2, (1, 1), 0, 5),
     (3, (1, 1, 1), 6, 7),   # 65^3: several blocks per dimension, z-marching
     (2, (1, 1), 9, 5),      # 513^2
+    (3, (5, 3, 2), 5, 7),   # 161 x 97 x 65: ragged tile edges of the fused red-black sweep
+    (3, (1, 1, 1), 7, 7),   # 129^3: several tiles and z-segments per CTA
 ]
 
 
@@ -114,7 +116,15 @@ def test_stencil_loops(dim, cells, lvl, npts, var, oracle):
     assert np.array_equal(ctx.download(fu, lvl), e)
     ctx.field_advance(fu)
     assert ctx.field_active_slot(fu) == 0
-    # red-black colours in place
+    # red-black colours in place.  Two colours decouple only star stencils: with diagonal
+    # entries same-coloured points are coupled, the reference's own OpenMP loop races there,
+    # and libexamg refuses rather than give order-dependent results.
+    if npts in (9, 27):
+        from exastencils_b200 import runtime as rt
+        with pytest.raises(rt.ExaMGError, match="colour"):
+            ctx.smooth_rb_color(A, fu, ff, omega, 0)
+        ctx.close()
+        return
     e = u.copy()
     for color in (0, 1, 1, 0):
         ctx.smooth_rb_color(A, fu, ff, omega, color)
