@@ -30,6 +30,11 @@ struct examg_solver {
   std::map<std::vector<int>, Graph> graphs;  // keyed by the active slots of Solution on entry
 };
 
+namespace examg {
+bool fused_rb_usable(examg_ctx *c, const Stencil &s, const Field &fu);
+int ensure_shadow(examg_ctx *c, Field &fu);
+}
+
 // (active slot, shadow parity) of a Solution field, as recorded in the graph keys
 static void restore_state(Field &f, int state) {
   const int cur = state >> 1;
@@ -150,6 +155,13 @@ int examg_solver_vcycle(examg_solver *s, int level) {
   for (int h : s->sol) key.push_back(c->fields[h].cur * 2 + (c->fields[h].swapped ? 1 : 0));
   auto it = s->graphs.find(key);
   if (it == s->graphs.end()) {
+    // allocations cannot be captured: create the shadow buffers of the fused sweeps first
+    if (s->desc.smoother == EXAMG_SMOOTH_RBGS)
+      for (size_t i = 0; i < s->sol.size(); ++i)
+        if (fused_rb_usable(c, *get_stencil(c, s->stencils[i]), c->fields[s->sol[i]])) {
+          int rc = ensure_shadow(c, c->fields[s->sol[i]]);
+          if (rc) return rc;
+        }
     // capture mgCycle@finest for this slot configuration
     const long long l0 = c->launches;
     cudaGraph_t graph = nullptr;

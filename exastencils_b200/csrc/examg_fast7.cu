@@ -10,8 +10,8 @@
 // Design (B200):
 //   * out of place: reads Solution, writes the shadow buffer, buffers are swapped afterwards
 //     (so a tile may read its 2-deep halo from neighbours that are being rewritten)
-//   * each CTA owns an x-y tile (60 x 32 outputs, 64 x 36 with the halo) and marches in z;
-//     TMA (cp.async.bulk.tensor.3d) brings one 64x36 plane per step into a ring of 6 planes
+//   * each CTA owns an x-y tile (60 x 30 outputs, 64 x 34 with the halo) and marches in z;
+//     TMA (cp.async.bulk.tensor.3d) brings one 64x34 plane per step into a ring of 6 planes
 //     in shared memory, completion tracked by mbarriers, two planes prefetched ahead
 //   * 2.5-D wavefront: at step t colour 0 is applied in place (in shared memory) to plane
 //     t-1 and colour 1 to plane t-3; the skew of two planes makes the stages of one step
@@ -36,27 +36,25 @@ namespace examg {
 
 constexpr int FS = 2;                 // fused half-sweeps (colour 0, colour 1)
 constexpr int FW = 64;                // tile width in shared memory (x)
-constexpr int FH = 36;                // tile height in shared memory (y)
+constexpr int FH = 34;                // tile height in shared memory (y)
 constexpr int FR = 2 * FS + 2;        // ring depth (planes)
 constexpr int FOW = FW - 2 * FS;      // 60 output columns
-constexpr int FOH = FH - 2 * FS;      // 32 output rows
+constexpr int FOH = FH - 2 * FS;      // 30 output rows
 constexpr int FNT = 256;              // threads per CTA
 constexpr int FPLANE = FW * FH;       // doubles per plane
 constexpr int FITEMS = ((FH - 2) / 2) * (FW / 32);  // warp items per stage: row pairs x 32-wide chunks
-constexpr size_t FSMEM = sizeof(double) * FPLANE * FR + 128;
+constexpr int FNI = (FITEMS + FNT / 32 - 1) / (FNT / 32);  // items per warp and stage (4)
+constexpr size_t FSMEM = sizeof(double) * FPLANE * FR + 8 * FR;
 
 struct FusedArgs {
   int n[3];
-  int ulo[FS][3], uhi[FS][3];  // update bounds per stage (local node coordinates)
+  int ulo[3], uhi[3];  // update bounds (local node coordinates), same for both colours
   int pitch;
   long long plane;
   int tiles_x, tiles_y;
   int nzp;                     // output planes 0..nzp-1
   long long units;             // tiles * nzp
   int par;
-  int soff[7];                 // in-plane shared-memory offset of stencil entry k
-  int sdz[7];                  // dz of entry k
-  int centre;
   double coef[7];
   double w;                    // omega / diag
 };
@@ -88,12 +86,20 @@ __device__ __forceinline__ void tma_load_plane(void *dst, const CUtensorMap *tm,
       : "memory");
 }
 
+// Declaration orders of the 7-point stencils in the reference's programs (the order fixes the
+// floating-point association): 0 = centre,-x,+x,-y,+y,-z,+z (Benchmark/Poisson3D, Examples/Poisson),
+// 1 = centre,+x,-x,+y,-y,+z,-z (Testing/Smoothers, Testing/SISC, Testing/Opts).
+__device__ constexpr int ORD_DX[2][7] = {{0, -1, 1, 0, 0, 0, 0}, {0, 1, -1, 0, 0, 0, 0}};
+__device__ constexpr int ORD_DY[2][7] = {{0, 0, 0, -1, 1, 0, 0}, {0, 0, 0, 1, -1, 0, 0}};
+__device__ constexpr int ORD_DZ[2][7] = {{0, 0, 0, 0, 0, -1, 1}, {0, 0, 0, 0, 0, 1, -1}};
+
+template <int ORD>
 __global__ void __launch_bounds__(FNT, 2)
 k_rb_fused(const __grid_constant__ CUtensorMap tm_in, const __grid_constant__ FusedArgs a,
            const double *__restrict__ rhs, double *__restrict__ uout) {
-  extern __shared__ unsigned char smem_raw[];
-  double *ring = reinterpret_cast<double *>((reinterpret_cast<uintptr_t>(smem_raw) + 127) & ~uintptr_t(127));
-  __shared__ uint64_t full[FR];
+  // dynamic shared memory only (starts 1024-byte aligned): ring of FR planes, then the mbarriers
+  extern __shared__ __align__(1024) double ring[];
+  uint64_t *full = reinterpret_cast<uint64_t *>(ring + FPLANE * FR);
 
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   if (tid == 0) {
@@ -102,10 +108,15 @@ k_rb_fused(const __grid_constant__ CUtensorMap tm_in, const __grid_constant__ Fu
   }
   __syncthreads();
 
+  double coef[7];
+#pragma unroll
+  for (int k = 0; k < 7; ++k) coef[k] = a.coef[k];
+  const double w = a.w;
+
   // this CTA's share of the (tile, plane) units
   const long long u0 = a.units * blockIdx.x / gridDim.x;
   const long long u1 = a.units * (blockIdx.x + 1) / gridDim.x;
-  long long loads = 0;  // planes loaded so far by this CTA (ring position / mbarrier phase)
+  int loads = 0;  // planes loaded so far by this CTA, modulo 2*FR (ring position and mbarrier phase)
 
   for (long long ub = u0; ub < u1;) {
     const int tile = (int)(ub / a.nzp);
@@ -115,79 +126,131 @@ k_rb_fused(const __grid_constant__ CUtensorMap tm_in, const __grid_constant__ Fu
     ub = seg_end;
     const int ox = FOW * (tile % a.tiles_x), oy = FOH * (tile / a.tiles_x);  // first output node of the tile
     const int t0 = za - FS, tl = zb - 1 + FS;  // first / last plane loaded
-    const long long kbase = loads - t0;       // ring position of plane z is kbase + z
     // array coordinates of the tile corner (TMA zero-fills outside the allocation)
     const int cx = ox - FS + XPAD, cy = oy - FS + GHOST;
+
+    // per-thread item geometry (fixed for the segment): the lane owns the column pair (xb, xb+1) of row y
+    int ibase[FNI], iflag[FNI];  // smem offset; parity | valid(x=xb)<<1 | valid(xb+1)<<2
+    const double *irhs[FNI];     // rhs at (xb, y) of plane 0
+#pragma unroll
+    for (int it = 0; it < FNI; ++it) {
+      const int item = warp + it * (FNT / 32);
+      // a warp item is 2 rows x 32 columns.  64-bit shared-memory accesses are served per
+      // half-warp: lanes 0-7 take row y, lanes 8-15 row y+1 of one 16-column group, whose
+      // colour points sit in complementary 8-byte bank pairs -> conflict-free
+      const int rp = item / (FW / 32), ch = item % (FW / 32);
+      const int y = 1 + 2 * rp + ((lane >> 3) & 1);
+      const int xb = 32 * ch + 16 * (lane >> 4) + 2 * (lane & 7);
+      const int lx = ox - FS + xb, ly = oy - FS + y;
+      const bool rowok = ly >= a.ulo[1] && ly < a.uhi[1];
+      const bool v0 = rowok && xb >= 1 && lx >= a.ulo[0] && lx < a.uhi[0];
+      const bool v1 = rowok && xb + 1 <= FW - 2 && lx + 1 >= a.ulo[0] && lx + 1 < a.uhi[0];
+      ibase[it] = y * FW + xb;
+      irhs[it] = rhs + (lx + a.pitch * ly);
+      iflag[it] = ((lx + ly + a.par) & 1) | (v0 ? 2 : 0) | (v1 ? 4 : 0);
+    }
 
     if (tid == 0) {
       asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
       for (int z = t0; z <= min(t0 + 1, tl); ++z) {
-        const int sl = (int)((kbase + z) % FR);
+        const int k = (loads + z - t0) % (2 * FR), sl = k % FR;
         mbar_expect_tx(&full[sl], FPLANE * 8);
         tma_load_plane(ring + sl * FPLANE, &tm_in, cx, cy, z + GHOST, &full[sl]);
       }
     }
+    // rhs values of the next step are fetched one step ahead into registers (rqn), so the
+    // L2/HBM latency of those loads is covered by a whole step of work
+    double rq[FS][FNI], rqn[FS][FNI];
+#pragma unroll
+    for (int s = 0; s < FS; ++s)
+#pragma unroll
+      for (int it = 0; it < FNI; ++it) rq[s][it] = 0.0;
+
+    int kt = loads;  // ring counter of plane t (mod 2*FR)
     for (int t = t0; t <= zb - 1 + 2 * FS; ++t) {
-      if (t <= tl) {
-        const long long k = kbase + t;
-        mbar_wait(&full[k % FR], (uint32_t)((k / FR) & 1));
-      }
-      // ---- stages: colour s-1 on plane t-(2s-1) -------------------------------------
+      // ---- (1) rhs prefetch for step t+1: stage s works on plane t+1-(2s-1), colour parity (t+1-s)&1
 #pragma unroll
       for (int s = 1; s <= FS; ++s) {
-        const int zs = t - (2 * s - 1);
-        if (zs < za - (FS - s) || zs >= zb + (FS - s)) continue;
-        if (zs < a.ulo[s - 1][2] || zs >= a.uhi[s - 1][2]) continue;
-        const int color = (s - 1) & 1;
-        const int pc = (int)((kbase + zs) % FR) * FPLANE;
-        const int dm = (int)((kbase + zs - 1) % FR) * FPLANE - pc;
-        const int dp = (int)((kbase + zs + 1) % FR) * FPLANE - pc;
-        int nb[7];
+        const int zs = t + 1 - (2 * s - 1);
+        const bool zok = zs >= za - (FS - s) && zs < zb + (FS - s) && zs >= a.ulo[2] && zs < a.uhi[2];
+        if (zok) {
+          const long long zoff = a.plane * zs;  // uniform
 #pragma unroll
-        for (int k = 0; k < 7; ++k) nb[k] = a.soff[k] + (a.sdz[k] > 0 ? dp : (a.sdz[k] < 0 ? dm : 0));
-        const double *rz = rhs + a.plane * zs;
-        for (int item = warp; item < FITEMS; item += FNT / 32) {
-          const int rp = item / (FW / 32), ch = item % (FW / 32);
-          const int y = 1 + 2 * rp + (lane >> 4);
-          const int xb = 32 * ch + 2 * (lane & 15);
-          const int ly = oy - FS + y;
-          const int q = (ox - FS + xb + ly + zs + a.par + color) & 1;
-          const int x = xb + q, lx = ox - FS + x;
-          const bool ok = x >= 1 && x <= FW - 2 && lx >= a.ulo[s - 1][0] && lx < a.uhi[s - 1][0] &&
-                          ly >= a.ulo[s - 1][1] && ly < a.uhi[s - 1][1];
-          if (ok) {
-            double *pt = ring + pc + y * FW + x;
-            const double f = __ldg(rz + lx + (long long)a.pitch * ly);
-            double acc = a.coef[0] * pt[nb[0]];
-#pragma unroll
-            for (int k = 1; k < 7; ++k) acc = fma(a.coef[k], pt[nb[k]], acc);
-            const double r = f - acc;
-            *pt = fma(a.w, r, *pt);
+          for (int it = 0; it < FNI; ++it) {
+            const int q = (iflag[it] + t + 1 - s) & 1;
+            const bool ok = (iflag[it] >> (1 + q)) & 1;
+            rqn[s - 1][it] = ok ? __ldg(irhs[it] + zoff + q) : 0.0;
           }
         }
       }
-      // ---- plane t-2S is final: write the tile's 60x32 outputs -------------------------
+      if (t <= tl) mbar_wait(&full[kt % FR], (uint32_t)(kt >= FR));
+      // ---- (2) stages: colour s-1 on plane t-(2s-1); all loads first, then all stores ----
+      double nv[FS][FNI];
+      int addr[FS][FNI];
+#pragma unroll
+      for (int s = 1; s <= FS; ++s) {
+        const int zs = t - (2 * s - 1);
+        const bool zok = zs >= za - (FS - s) && zs < zb + (FS - s) && zs >= a.ulo[2] && zs < a.uhi[2];
+#pragma unroll
+        for (int it = 0; it < FNI; ++it) addr[s - 1][it] = -1;
+        if (zok) {
+          // ring slots of planes zs-1, zs, zs+1 (kt is the counter of plane t)
+          const int kc = (kt + 2 * FR - (2 * s - 1)) % (2 * FR);
+          const int pc = (kc % FR) * FPLANE;
+          const int dm = ((kc + FR - 1) % FR) * FPLANE - pc;
+          const int dp = ((kc + 1) % FR) * FPLANE - pc;
+#pragma unroll
+          for (int it = 0; it < FNI; ++it) {
+            const int q = (iflag[it] + t - s) & 1;
+            const bool ok = (iflag[it] >> (1 + q)) & 1;
+            const int ad = pc + ibase[it] + q;
+            const double *pt = ring + ad;  // all seven neighbours are inside the ring for every lane
+            const double *pm = pt + dm, *pp = pt + dp;
+            double v[7];
+#pragma unroll
+            for (int k = 0; k < 7; ++k)
+              v[k] = (ORD_DZ[ORD][k] == 0 ? pt : (ORD_DZ[ORD][k] < 0 ? pm : pp))[ORD_DX[ORD][k] + FW * ORD_DY[ORD][k]];
+            double acc = coef[0] * v[0];
+#pragma unroll
+            for (int k = 1; k < 7; ++k) acc = fma(coef[k], v[k], acc);
+            const double r = rq[s - 1][it] - acc;
+            nv[s - 1][it] = fma(w, r, v[0]);
+            addr[s - 1][it] = ok ? ad : -1;
+          }
+        }
+      }
+#pragma unroll
+      for (int s = 0; s < FS; ++s)
+#pragma unroll
+        for (int it = 0; it < FNI; ++it)
+          if (addr[s][it] >= 0) ring[addr[s][it]] = nv[s][it];
+      // ---- (3) plane t-2S is final: write the tile's outputs (one row per warp iteration) ---
       const int zf = t - 2 * FS;
       if (zf >= za && zf < zb) {
-        const double *src = ring + (int)((kbase + zf) % FR) * FPLANE;
-        double *dst = uout + a.plane * zf;
-        for (int e = tid; e < FOW * FOH; e += FNT) {
-          const int r = e / FOW, col = e - r * FOW;
-          const int lx = ox + col, ly = oy + r;
-          if (lx < a.n[0] && ly < a.n[1]) dst[lx + (long long)a.pitch * ly] = src[(r + FS) * FW + col + FS];
+        const double *src = ring + ((kt + 2 * FR - 2 * FS) % FR) * FPLANE + FS * FW + FS;
+        double *dst = uout + a.plane * zf + ox + (long long)a.pitch * oy;
+        const int wlim = min(FOW, a.n[0] - ox), hlim = min(FOH, a.n[1] - oy);
+        for (int r = warp; r < hlim; r += FNT / 32) {
+          if (lane < wlim) dst[(long long)a.pitch * r + lane] = src[r * FW + lane];
+          if (lane + 32 < wlim) dst[(long long)a.pitch * r + lane + 32] = src[r * FW + lane + 32];
         }
       }
       __syncthreads();
       // the slot of plane t-2S is free now: prefetch plane t+2 into it
       if (tid == 0 && t + 2 <= tl) {
-        const long long k = kbase + t + 2;
-        const int sl = (int)(k % FR);
+        const int sl = (kt + 2) % FR;
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
         mbar_expect_tx(&full[sl], FPLANE * 8);
         tma_load_plane(ring + sl * FPLANE, &tm_in, cx, cy, t + 2 + GHOST, &full[sl]);
       }
+#pragma unroll
+      for (int s = 0; s < FS; ++s)
+#pragma unroll
+        for (int it = 0; it < FNI; ++it) rq[s][it] = rqn[s][it];
+      kt = (kt + 1) % (2 * FR);
     }
-    loads += tl - t0 + 1;
+    loads = (loads + tl - t0 + 1) % (2 * FR);
+    // kt ran past tl (no loads for t > tl): the next segment continues at `loads`
   }
 }
 
@@ -222,6 +285,21 @@ static int make_plane_map(const LevelGeom &g, double *base, CUtensorMap *tm) {
   return EXAMG_OK;
 }
 
+// 0 / 1: one of the two known declaration orders; -1: something else (generic kernels)
+static int stencil_order(const Stencil &s) {
+  static const int dx[2][7] = {{0, -1, 1, 0, 0, 0, 0}, {0, 1, -1, 0, 0, 0, 0}};
+  static const int dy[2][7] = {{0, 0, 0, -1, 1, 0, 0}, {0, 0, 0, 1, -1, 0, 0}};
+  static const int dz[2][7] = {{0, 0, 0, 0, 0, -1, 1}, {0, 0, 0, 0, 0, 1, -1}};
+  if (s.nst != 7) return -1;
+  for (int o = 0; o < 2; ++o) {
+    bool same = true;
+    for (int k = 0; k < 7; ++k)
+      same = same && s.off[k][0] == dx[o][k] && s.off[k][1] == dy[o][k] && s.off[k][2] == dz[o][k];
+    if (same) return o;
+  }
+  return -1;
+}
+
 static bool fused_enabled() {
   static int v = -1;
   if (v < 0) {
@@ -235,34 +313,43 @@ static bool fused_enabled() {
 constexpr int FUSED_MIN_N = 65;
 
 bool fused_rb_usable(examg_ctx *c, const Stencil &s, const Field &fu) {
-  if (!fused_enabled() || !s.is7 || c->cfg.dim != 3 || fu.ncomp != 1) return false;
+  if (!fused_enabled() || !s.is7 || c->cfg.dim != 3 || fu.ncomp != 1 || stencil_order(s) < 0) return false;
   if (c->world > 1) return false;  // multi-block: colour sweeps + exchange (examg_comm.cu)
   const LevelGeom &g = *geom(c, s.level);
   return g.n[0] >= FUSED_MIN_N && g.n[1] >= FUSED_MIN_N && g.n[2] >= FUSED_MIN_N;
 }
 
+// Allocates the second buffer of a field (not capturable: call before graph capture).
+int ensure_shadow(examg_ctx *c, Field &fu) {
+  static bool attr_set = false;
+  if (!attr_set) {
+    EXAMG_CUDA(cudaFuncSetAttribute(k_rb_fused<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)FSMEM));
+    EXAMG_CUDA(cudaFuncSetAttribute(k_rb_fused<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)FSMEM));
+    attr_set = true;
+  }
+  if (fu.shadow) return EXAMG_OK;
+  const LevelGeom &g = *geom(c, fu.level);
+  const size_t bytes = sizeof(double) * (size_t)g.vol;
+  cudaError_t e = cudaMalloc(&fu.shadow, bytes);
+  if (e != cudaSuccess) return set_error(EXAMG_ENOMEM, "shadow buffer of %s@%d: %s", fu.name.c_str(), fu.level, cudaGetErrorString(e));
+  EXAMG_CUDA(cudaMemset(fu.shadow, 0, bytes));
+  c->dev_bytes += (long long)bytes;
+  return EXAMG_OK;
+}
+
 // One full sweep: colour 0 then colour 1.  Swaps fu.slot[cur] with the shadow buffer.
 int launch_rb_fused(examg_ctx *c, const Stencil &s, double omega, Field &fu, const double *rhs) {
   const LevelGeom &g = *geom(c, s.level);
-  if (!fu.shadow) {
-    const size_t bytes = sizeof(double) * (size_t)g.vol;
-    cudaError_t e = cudaMalloc(&fu.shadow, bytes);
-    if (e != cudaSuccess) return set_error(EXAMG_ENOMEM, "shadow buffer of %s@%d: %s", fu.name.c_str(), fu.level, cudaGetErrorString(e));
-    EXAMG_CUDA(cudaMemsetAsync(fu.shadow, 0, bytes, c->stream));
-    c->dev_bytes += (long long)bytes;
-  }
-  static bool attr_set = false;
-  if (!attr_set) {
-    EXAMG_CUDA(cudaFuncSetAttribute(k_rb_fused, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)FSMEM));
-    attr_set = true;
-  }
+  int rc0 = ensure_shadow(c, fu);
+  if (rc0) return rc0;
   CUtensorMap tm;
   int rc = make_plane_map(g, fu.slot[fu.cur], &tm);
   if (rc) return rc;
   FusedArgs a;
   for (int d = 0; d < 3; ++d) {
     a.n[d] = g.n[d];
-    for (int st = 0; st < FS; ++st) { a.ulo[st][d] = g.lo[d]; a.uhi[st][d] = g.hi[d]; }
+    a.ulo[d] = g.lo[d];
+    a.uhi[d] = g.hi[d];
   }
   a.pitch = g.pitch;
   a.plane = g.plane;
@@ -271,12 +358,8 @@ int launch_rb_fused(examg_ctx *c, const Stencil &s, double omega, Field &fu, con
   a.nzp = g.n[2];
   a.units = (long long)a.tiles_x * a.tiles_y * a.nzp;
   a.par = g.par;
-  a.centre = s.centre;
-  for (int k = 0; k < 7; ++k) {
-    a.soff[k] = s.off[k][0] + FW * s.off[k][1];
-    a.sdz[k] = s.off[k][2];
-    a.coef[k] = s.coef[k];
-  }
+  for (int k = 0; k < 7; ++k) a.coef[k] = s.coef[k];
+  const int ord = stencil_order(s);
   a.w = omega / s.coef[s.centre];
   int dev = 0, nsm = 148;
   cudaGetDevice(&dev);
@@ -285,7 +368,10 @@ int launch_rb_fused(examg_ctx *c, const Stencil &s, double omega, Field &fu, con
   const long long min_units = 24;  // at least this many planes per CTA (4 are restart overhead)
   if (grid > a.units / min_units) grid = a.units / min_units;
   if (grid < 1) grid = 1;
-  k_rb_fused<<<(int)grid, FNT, FSMEM, c->stream>>>(tm, a, rhs, fu.shadow + g.origin);
+  if (ord == 0)
+    k_rb_fused<0><<<(int)grid, FNT, FSMEM, c->stream>>>(tm, a, rhs, fu.shadow + g.origin);
+  else
+    k_rb_fused<1><<<(int)grid, FNT, FSMEM, c->stream>>>(tm, a, rhs, fu.shadow + g.origin);
   EXAMG_LAUNCH_CHECK(c);
   double *t = fu.slot[fu.cur];
   fu.slot[fu.cur] = fu.shadow;

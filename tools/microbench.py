@@ -1,0 +1,79 @@
+#!/usr/bin/env python
+"""Per-kernel timings of libexamg on one GPU (CUDA events on the launching stream).
+
+  python tools/microbench.py --level 9 [--reps 10]
+
+Prints one line per loop shape: ms, points/s, algorithmic GB/s and the fraction of the
+measured HBM peak (MEASURED_PEAKS.json).  Development tool; bench.py is the contract.
+"""
+import argparse
+import json
+import os
+import sys
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--level", type=int, default=9)
+    ap.add_argument("--reps", type=int, default=10)
+    ap.add_argument("--nu", type=int, default=2)
+    args = ap.parse_args()
+    import torch
+    from exastencils_b200 import MultigridProgram
+    peak = 6650.0
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        peak = float(json.load(open(p))["hbm_gbs"])
+    stream = torch.cuda.Stream()
+    L = args.level
+    prog = MultigridProgram(3, (1, 1, 1), 2, L, smoother="rbgs", omega=0.8, nu_pre=args.nu, nu_post=args.nu,
+                            stream=stream.cuda_stream)
+    ctx = prog.ctx
+    n = ctx.dims(L)
+    pts = float(n[0] - 2) * (n[1] - 2) * (n[2] - 2)
+    A, u, f, r = prog.stencil[L], prog.f_solution[L], prog.f_rhs[L], prog.f_residual[L]
+    uc, fc = prog.f_solution[L - 1], prog.f_rhs[L - 1]
+
+    def timeit(name, fn, bytes_per_pt, npts=pts):
+        with torch.cuda.stream(stream):
+            for _ in range(3):
+                fn()
+            torch.cuda.synchronize()
+            l0 = ctx.launch_count()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(stream)
+            for _ in range(args.reps):
+                fn()
+            e1.record(stream)
+            torch.cuda.synchronize()
+            ms = e0.elapsed_time(e1) / args.reps
+            nl = (ctx.launch_count() - l0) / args.reps
+        gbs = bytes_per_pt * npts / (ms * 1e-3) / 1e9
+        print("%-34s %8.3f ms  %6.1f launches  %8.1f GB/s alg  %5.1f%% of %.0f" % (name, ms, nl, gbs, 100 * gbs / peak,
+                                                                              peak), flush=True)
+
+    timeit("rbgs 1 sweep (24 B/pt)", lambda: ctx.smooth_rbgs(A, u, f, 0.8, 1), 24.0)
+    timeit("rbgs %d sweeps (24 B/pt/sweep)" % args.nu, lambda: ctx.smooth_rbgs(A, u, f, 0.8, args.nu), 24.0 * args.nu)
+    timeit("rb one colour (12 B/pt)", lambda: ctx.smooth_rb_color(A, u, f, 0.8, 0), 12.0)
+    timeit("residual (24 B/pt)", lambda: ctx.residual(A, u, f, r), 24.0)
+    timeit("residual + norm (24 B/pt)", lambda: ctx.residual(A, u, f, r, norm=True), 24.0)
+    timeit("restrict (9 B/fine pt)", lambda: ctx.restrict(r, fc), 9.0)
+    timeit("prolong+correct (17 B/fine pt)", lambda: ctx.prolong_add(uc, u), 17.0)
+    timeit("dot (16 B/pt)", lambda: ctx.dot(r, r), 16.0)
+    timeit("set coarse (8 B/coarse pt)", lambda: ctx.set(uc, 0.0), 1.0)
+    # whole cycle: (4 sweeps*24 + 24 + 9 + 17) * 8/7 per finest point
+    cyc_bytes = ((2 * args.nu) * 24.0 + 24 + 9 + 17) * 8.0 / 7.0
+    timeit("V(%d,%d) cycle (%.1f B/pt)" % (args.nu, args.nu, cyc_bytes), lambda: prog.vcycle(), cyc_bytes)
+    timeit("V cycle + residual norm", lambda: prog.cycles(1), cyc_bytes + 24.0)
+    # coarse part alone: mgCycle@(L-1)
+    prog2 = prog
+    timeit("mgCycle@%d (coarse part)" % (L - 1), lambda: prog2.ctx.L.examg_solver_vcycle(prog2._solver, L - 1), cyc_bytes,
+           npts=pts / 8)
+    prog.close()
+
+
+if __name__ == "__main__":
+    main()
