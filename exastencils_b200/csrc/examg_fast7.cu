@@ -29,6 +29,7 @@
 #include <cuda.h>
 
 #include <map>
+#include <type_traits>
 
 #include "examg_device.cuh"
 
@@ -100,6 +101,7 @@ k_rb_fused(const __grid_constant__ CUtensorMap tm_in, const __grid_constant__ Fu
   // dynamic shared memory only (starts 1024-byte aligned): ring of FR planes, then the mbarriers
   extern __shared__ __align__(1024) double ring[];
   uint64_t *full = reinterpret_cast<uint64_t *>(ring + FPLANE * FR);
+  char *ringb = reinterpret_cast<char *>(ring);
 
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   if (tid == 0) {
@@ -112,6 +114,8 @@ k_rb_fused(const __grid_constant__ CUtensorMap tm_in, const __grid_constant__ Fu
 #pragma unroll
   for (int k = 0; k < 7; ++k) coef[k] = a.coef[k];
   const double w = a.w;
+  const long long plane8 = a.plane * 8;
+  const long long pitch8 = (long long)a.pitch * 8;
 
   // this CTA's share of the (tile, plane) units
   const long long u0 = a.units * blockIdx.x / gridDim.x;
@@ -129,26 +133,40 @@ k_rb_fused(const __grid_constant__ CUtensorMap tm_in, const __grid_constant__ Fu
     // array coordinates of the tile corner (TMA zero-fills outside the allocation)
     const int cx = ox - FS + XPAD, cy = oy - FS + GHOST;
 
-    // per-thread item geometry (fixed for the segment): the lane owns the column pair (xb, xb+1) of row y
-    int ibase[FNI], iflag[FNI];  // smem offset; parity | valid(x=xb)<<1 | valid(xb+1)<<2
-    const double *irhs[FNI];     // rhs at (xb, y) of plane 0
+    // ---- per-thread item geometry, fixed for the segment ------------------------------
+    // A warp item is 2 rows x 32 columns; the lane owns the column pair (xb, xb+1) of one row.
+    // 64-bit shared-memory accesses are served per half-warp: lanes 0-7 take row y, lanes 8-15
+    // row y+1 of one 16-column group; their colour points sit in complementary 8-byte bank
+    // pairs, so every access is conflict-free.
+    // Colour of (x,y,z) is (x+y+z+par)&1.  At step t = t0+rel stage 2 (colour 1, plane t-3)
+    // updates x = xb + (e ^ rel&1) and stage 1 (colour 0, plane t-1) the other column, with
+    // e = (xb+y+par+t0)&1.  "A" = column xb+e, "B" = column xb+(e^1).
+    uint32_t offA[FNI], offB[FNI];    // byte offset of the point inside a plane of the ring
+    uint32_t roffA[FNI], roffB[FNI];  // byte offset of the point inside a plane of rhs
+    uint32_t okmask = 0;              // bit 2*it: A may be updated, bit 2*it+1: B
 #pragma unroll
     for (int it = 0; it < FNI; ++it) {
       const int item = warp + it * (FNT / 32);
-      // a warp item is 2 rows x 32 columns.  64-bit shared-memory accesses are served per
-      // half-warp: lanes 0-7 take row y, lanes 8-15 row y+1 of one 16-column group, whose
-      // colour points sit in complementary 8-byte bank pairs -> conflict-free
       const int rp = item / (FW / 32), ch = item % (FW / 32);
       const int y = 1 + 2 * rp + ((lane >> 3) & 1);
       const int xb = 32 * ch + 16 * (lane >> 4) + 2 * (lane & 7);
       const int lx = ox - FS + xb, ly = oy - FS + y;
+      const int e = (lx + ly + a.par + t0) & 1;
       const bool rowok = ly >= a.ulo[1] && ly < a.uhi[1];
       const bool v0 = rowok && xb >= 1 && lx >= a.ulo[0] && lx < a.uhi[0];
       const bool v1 = rowok && xb + 1 <= FW - 2 && lx + 1 >= a.ulo[0] && lx + 1 < a.uhi[0];
-      ibase[it] = y * FW + xb;
-      irhs[it] = rhs + (lx + a.pitch * ly);
-      iflag[it] = ((lx + ly + a.par) & 1) | (v0 ? 2 : 0) | (v1 ? 4 : 0);
+      offA[it] = (uint32_t)(y * FW + xb + e) * 8u;
+      offB[it] = (uint32_t)(y * FW + xb + (e ^ 1)) * 8u;
+      const int g = lx + a.pitch * ly;
+      roffA[it] = (uint32_t)(g + e) * 8u;
+      roffB[it] = (uint32_t)(g + (e ^ 1)) * 8u;
+      okmask |= ((e ? v1 : v0) ? 1u : 0u) << (2 * it);
+      okmask |= ((e ? v0 : v1) ? 1u : 0u) << (2 * it + 1);
     }
+    // output rows of this warp: r = warp, warp+8, ...; two 32-column chunks
+    const uint32_t so_off = (uint32_t)((FS + warp) * FW + FS + lane) * 8u;
+    const int wlim = min(FOW, a.n[0] - ox), hlim = min(FOH, a.n[1] - oy);
+    char *const dst0 = reinterpret_cast<char *>(uout + ox + lane) + pitch8 * (oy + warp);
 
     if (tid == 0) {
       asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
@@ -158,99 +176,116 @@ k_rb_fused(const __grid_constant__ CUtensorMap tm_in, const __grid_constant__ Fu
         tma_load_plane(ring + sl * FPLANE, &tm_in, cx, cy, z + GHOST, &full[sl]);
       }
     }
-    // rhs values of the next step are fetched one step ahead into registers (rqn), so the
-    // L2/HBM latency of those loads is covered by a whole step of work
-    double rq[FS][FNI], rqn[FS][FNI];
+    // rhs values are fetched one step ahead into registers: step parity 0 consumes rq0 and fills
+    // rq1, parity 1 the other way round, so no copies are needed
+    double rq0[FS][FNI], rq1[FS][FNI];
 #pragma unroll
     for (int s = 0; s < FS; ++s)
 #pragma unroll
-      for (int it = 0; it < FNI; ++it) rq[s][it] = 0.0;
+      for (int it = 0; it < FNI; ++it) rq0[s][it] = rq1[s][it] = 0.0;
 
     int kt = loads;  // ring counter of plane t (mod 2*FR)
-    for (int t = t0; t <= zb - 1 + 2 * FS; ++t) {
-      // ---- (1) rhs prefetch for step t+1: stage s works on plane t+1-(2s-1), colour parity (t+1-s)&1
+
+    auto step = [&](auto parity, const int t) {
+      constexpr int P = decltype(parity)::value;
+      double(&rcur)[FS][FNI] = P ? rq1 : rq0;
+      double(&rnxt)[FS][FNI] = P ? rq0 : rq1;
+      // ---- (1) rhs prefetch for step t+1 (relative parity P^1) --------------------------
 #pragma unroll
       for (int s = 1; s <= FS; ++s) {
         const int zs = t + 1 - (2 * s - 1);
         const bool zok = zs >= za - (FS - s) && zs < zb + (FS - s) && zs >= a.ulo[2] && zs < a.uhi[2];
         if (zok) {
-          const long long zoff = a.plane * zs;  // uniform
+          const bool useA = (s == 2) == ((P ^ 1) == 0);
+          const char *rz = reinterpret_cast<const char *>(rhs) + plane8 * zs;  // uniform
 #pragma unroll
           for (int it = 0; it < FNI; ++it) {
-            const int q = (iflag[it] + t + 1 - s) & 1;
-            const bool ok = (iflag[it] >> (1 + q)) & 1;
-            rqn[s - 1][it] = ok ? __ldg(irhs[it] + zoff + q) : 0.0;
+            const bool ok = (okmask >> (2 * it + (useA ? 0 : 1))) & 1u;
+            const uint32_t ro = useA ? roffA[it] : roffB[it];
+            rnxt[s - 1][it] = ok ? __ldg(reinterpret_cast<const double *>(rz + ro)) : 0.0;
           }
         }
       }
-      if (t <= tl) mbar_wait(&full[kt % FR], (uint32_t)(kt >= FR));
+      const int slot_t = kt >= FR ? kt - FR : kt;
+      if (t <= tl) mbar_wait(&full[slot_t], (uint32_t)(kt >= FR));
       // ---- (2) stages: colour s-1 on plane t-(2s-1); all loads first, then all stores ----
       double nv[FS][FNI];
-      int addr[FS][FNI];
+      uint32_t sa[FS][FNI];
+      bool act[FS];
 #pragma unroll
       for (int s = 1; s <= FS; ++s) {
         const int zs = t - (2 * s - 1);
-        const bool zok = zs >= za - (FS - s) && zs < zb + (FS - s) && zs >= a.ulo[2] && zs < a.uhi[2];
-#pragma unroll
-        for (int it = 0; it < FNI; ++it) addr[s - 1][it] = -1;
-        if (zok) {
-          // ring slots of planes zs-1, zs, zs+1 (kt is the counter of plane t)
-          const int kc = (kt + 2 * FR - (2 * s - 1)) % (2 * FR);
-          const int pc = (kc % FR) * FPLANE;
-          const int dm = ((kc + FR - 1) % FR) * FPLANE - pc;
-          const int dp = ((kc + 1) % FR) * FPLANE - pc;
+        act[s - 1] = zs >= za - (FS - s) && zs < zb + (FS - s) && zs >= a.ulo[2] && zs < a.uhi[2];
+        if (act[s - 1]) {
+          const bool useA = (s == 2) == (P == 0);
+          int sc = slot_t - (2 * s - 1);  // ring slots of planes zs, zs-1, zs+1
+          if (sc < 0) sc += FR;
+          const int sm = sc == 0 ? FR - 1 : sc - 1, sp = sc == FR - 1 ? 0 : sc + 1;
+          const char *pcb = ringb + sc * (FPLANE * 8);
+          const int dm = (sm - sc) * (FPLANE * 8), dp = (sp - sc) * (FPLANE * 8);
 #pragma unroll
           for (int it = 0; it < FNI; ++it) {
-            const int q = (iflag[it] + t - s) & 1;
-            const bool ok = (iflag[it] >> (1 + q)) & 1;
-            const int ad = pc + ibase[it] + q;
-            const double *pt = ring + ad;  // all seven neighbours are inside the ring for every lane
-            const double *pm = pt + dm, *pp = pt + dp;
+            const uint32_t off = useA ? offA[it] : offB[it];
+            const char *pt = pcb + off;  // all seven neighbours are inside the ring for every lane
             double v[7];
 #pragma unroll
-            for (int k = 0; k < 7; ++k)
-              v[k] = (ORD_DZ[ORD][k] == 0 ? pt : (ORD_DZ[ORD][k] < 0 ? pm : pp))[ORD_DX[ORD][k] + FW * ORD_DY[ORD][k]];
+            for (int k = 0; k < 7; ++k) {
+              const int d = (ORD_DX[ORD][k] + FW * ORD_DY[ORD][k]) * 8;
+              const char *q = ORD_DZ[ORD][k] == 0 ? pt : (ORD_DZ[ORD][k] < 0 ? pt + dm : pt + dp);
+              v[k] = *reinterpret_cast<const double *>(q + d);
+            }
             double acc = coef[0] * v[0];
 #pragma unroll
             for (int k = 1; k < 7; ++k) acc = fma(coef[k], v[k], acc);
-            const double r = rq[s - 1][it] - acc;
+            const double r = rcur[s - 1][it] - acc;
             nv[s - 1][it] = fma(w, r, v[0]);
-            addr[s - 1][it] = ok ? ad : -1;
+            sa[s - 1][it] = (uint32_t)(sc * (FPLANE * 8)) + off;
           }
         }
       }
 #pragma unroll
       for (int s = 0; s < FS; ++s)
+        if (act[s]) {
+          const bool useA = (s == 1) == (P == 0);
 #pragma unroll
-        for (int it = 0; it < FNI; ++it)
-          if (addr[s][it] >= 0) ring[addr[s][it]] = nv[s][it];
-      // ---- (3) plane t-2S is final: write the tile's outputs (one row per warp iteration) ---
+          for (int it = 0; it < FNI; ++it)
+            if ((okmask >> (2 * it + (useA ? 0 : 1))) & 1u) *reinterpret_cast<double *>(ringb + sa[s][it]) = nv[s][it];
+        }
+      // ---- (3) plane t-2S is final: write the tile's outputs -----------------------------
       const int zf = t - 2 * FS;
       if (zf >= za && zf < zb) {
-        const double *src = ring + ((kt + 2 * FR - 2 * FS) % FR) * FPLANE + FS * FW + FS;
-        double *dst = uout + a.plane * zf + ox + (long long)a.pitch * oy;
-        const int wlim = min(FOW, a.n[0] - ox), hlim = min(FOH, a.n[1] - oy);
-        for (int r = warp; r < hlim; r += FNT / 32) {
-          if (lane < wlim) dst[(long long)a.pitch * r + lane] = src[r * FW + lane];
-          if (lane + 32 < wlim) dst[(long long)a.pitch * r + lane + 32] = src[r * FW + lane + 32];
+        int sf = slot_t - 2 * FS;
+        if (sf < 0) sf += FR;
+        const char *src = ringb + sf * (FPLANE * 8) + so_off;
+        char *dst = dst0 + plane8 * zf;
+#pragma unroll
+        for (int i = 0; i < (FOH + FNT / 32 - 1) / (FNT / 32); ++i) {
+          const int r = warp + i * (FNT / 32);
+          if (r < hlim) {
+            const double *sr = reinterpret_cast<const double *>(src + i * (FNT / 32) * FW * 8);
+            double *dr = reinterpret_cast<double *>(dst + pitch8 * (i * (FNT / 32)));
+            if (lane < wlim) dr[0] = sr[0];
+            if (lane + 32 < wlim) dr[32] = sr[32];
+          }
         }
       }
       __syncthreads();
       // the slot of plane t-2S is free now: prefetch plane t+2 into it
       if (tid == 0 && t + 2 <= tl) {
-        const int sl = (kt + 2) % FR;
+        const int sl = slot_t + 2 >= FR ? slot_t + 2 - FR : slot_t + 2;
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
         mbar_expect_tx(&full[sl], FPLANE * 8);
         tma_load_plane(ring + sl * FPLANE, &tm_in, cx, cy, t + 2 + GHOST, &full[sl]);
       }
-#pragma unroll
-      for (int s = 0; s < FS; ++s)
-#pragma unroll
-        for (int it = 0; it < FNI; ++it) rq[s][it] = rqn[s][it];
-      kt = (kt + 1) % (2 * FR);
+      kt = kt + 1 == 2 * FR ? 0 : kt + 1;
+    };
+
+    const int tend = zb - 1 + 2 * FS;
+    for (int t = t0; t <= tend; t += 2) {
+      step(std::integral_constant<int, 0>{}, t);
+      if (t + 1 <= tend) step(std::integral_constant<int, 1>{}, t + 1);
     }
     loads = (loads + tl - t0 + 1) % (2 * FR);
-    // kt ran past tl (no loads for t > tl): the next segment continues at `loads`
   }
 }
 
