@@ -1,63 +1,61 @@
-// examg_fast7.cu -- 3D 7-point constant-coefficient fast path: one full red-black
-// Gauss-Seidel sweep (colour 0 then colour 1) per pass over HBM.
+// examg_fast7.cu -- 3D 7-point constant-coefficient fast path: S red-black half-sweeps
+// (S = 2: one full sweep, S = 4: two sweeps) per pass over HBM.
 //
-// Reference loop being replaced (two passes per sweep, each a masked full-grid loop):
+// Reference loops being replaced (two masked full-grid passes per sweep):
 //   color with { (i0+i1+i2)%2, communicate; loop over Solution { Solution += omega/diag(A) *
 //   (RHS - A*Solution) }; apply bc }         Benchmark/Poisson3D/3D_FD_Poisson_fromL4.exa4:204-213
 //   colour order / duplication               C/s/e/baseExt/l4/L4_ColorLoops.scala:44-70
 //   temporal blocking precedent              C/s/e/baseExt/ir/IR_ContractingLoop.scala:48-90,131-195
 //
-// Design (B200):
-//   * out of place: reads Solution, writes the shadow buffer, buffers are swapped afterwards
-//     (so a tile may read its 2-deep halo from neighbours that are being rewritten)
-//   * each CTA owns an x-y tile (60 x 30 outputs, 64 x 34 with the halo) and marches in z;
-//     TMA (cp.async.bulk.tensor.3d) brings one 64x34 plane per step into a ring of 6 planes
-//     in shared memory, completion tracked by mbarriers, two planes prefetched ahead
-//   * 2.5-D wavefront: at step t colour 0 is applied in place (in shared memory) to plane
-//     t-1 and colour 1 to plane t-3; the skew of two planes makes the stages of one step
-//     independent, so there is one __syncthreads per plane; plane t-4 is final and is
-//     written back with coalesced stores
-//   * lanes 0-15 / 16-31 of a warp take the colour points of two adjacent rows: the 64-bit
-//     shared-memory accesses of a warp then cover complementary 8-byte slots -> no bank conflict
-//   * work = (tile, plane) pairs split evenly over a persistent grid of 2 CTAs per SM
-//     (stream-K style), so there is no tail wave; restart cost is 4 planes per segment
-// HBM traffic per point and sweep: 8*1.2 (Solution incl. halo) + 8*1.1 (RHS) + 8 (write)
-// = 26.4 B against 24 B algorithmic (32 B for two element-granular colour passes, and
-// 48 B measured for them because a 32-byte sector holds both colours).
+// Design (B200), "register-window wavefront":
+//   * out of place: reads Solution, writes the shadow buffer; the two are swapped afterwards
+//   * a CTA (512 threads, one per SM, persistent) owns an x-y tile of 64 x 32 nodes (S-deep halo
+//     included) and marches in z.  TMA (cp.async.bulk.tensor.3d) stages plane t of Solution and
+//     RHS in a 4-deep shared-memory ring (mbarrier completion, three planes in flight).
+//   * every thread owns a 2 x 2 block of the plane and keeps a window of S+2 planes of it in
+//     registers.  Half-sweep s (colour (s-1)&1) works on plane t-s, one plane behind half-sweep
+//     s-1: the z neighbours and two of the four in-plane neighbours are the thread's own
+//     registers, the other two come from the neighbouring threads through a colour-compressed
+//     exchange buffer in shared memory that half-sweep s-1 filled one step earlier (double
+//     buffered: one __syncthreads per plane).  The update is Gauss-Seidel in place -- in the
+//     register window.
+//   * plane t-S is final after half-sweep S and is written with 128-bit stores
+//   * work = (tile, plane) units split evenly over the grid; a segment start costs 2S planes
+// HBM traffic per point (S = 2): 8/0.82 (Solution with halo) + 8/0.82 (RHS) + 8 (write) = 27.5 B
+// against 24 B algorithmic; S = 4: 8/0.66 * 2 + 8 = 32.4 B against 48 B.
 //
 // Arithmetic is the contract of examg_kernels.cu (bit-identical to the unfused order).
 #include <cuda.h>
 
-#include <map>
 #include <type_traits>
 
 #include "examg_device.cuh"
 
 namespace examg {
 
-constexpr int FS = 2;                 // fused half-sweeps (colour 0, colour 1)
-constexpr int FW = 64;                // tile width in shared memory (x)
-constexpr int FH = 34;                // tile height in shared memory (y)
-constexpr int FR = 2 * FS + 2;        // ring depth (planes)
-constexpr int FOW = FW - 2 * FS;      // 60 output columns
-constexpr int FOH = FH - 2 * FS;      // 30 output rows
-constexpr int FNT = 256;              // threads per CTA
-constexpr int FPLANE = FW * FH;       // doubles per plane
-constexpr int FITEMS = ((FH - 2) / 2) * (FW / 32);  // warp items per stage: row pairs x 32-wide chunks
-constexpr int FNI = (FITEMS + FNT / 32 - 1) / (FNT / 32);  // items per warp and stage (4)
-constexpr size_t FSMEM = sizeof(double) * FPLANE * FR + 8 * FR;
+constexpr int RW = 64;                 // tile width (x), = 2 * warp size
+constexpr int RH = 32;                 // tile height (y), = 2 * warps per CTA
+constexpr int RNT = 512;               // threads per CTA
+constexpr int RD = 4;                  // depth of the TMA ring (planes)
+constexpr int RPLANE = RW * RH;        // doubles per staged plane
+constexpr int RXB = (RH + 2) * 32 + 32;  // doubles per exchange buffer: rows -1..RH of 32, 16 pad each end
+constexpr int ROFF_RING = 1024;        // bytes in front of the ring: mbarriers + landing zone of row -1 reads
 
-struct FusedArgs {
+template <int S>
+constexpr size_t rbw_smem() { return ROFF_RING + sizeof(double) * (2 * RD * RPLANE + (S - 1) * 2 * RXB); }
+
+struct RbwArgs {
   int n[3];
-  int ulo[3], uhi[3];  // update bounds (local node coordinates), same for both colours
+  int ulo[3], uhi[3];  // update bounds (local node coordinates) of the last half-sweep
+  int elo[3], ehi[3];  // 1: neighbour block on that side; half-sweep s also updates S-s layers beyond
   int pitch;
   long long plane;
-  int tiles_x, tiles_y;
-  int nzp;                     // output planes 0..nzp-1
-  long long units;             // tiles * nzp
+  int tiles_x;
+  int nzp;             // output planes 0..nzp-1
+  long long units;     // tiles * nzp
   int par;
   double coef[7];
-  double w;                    // omega / diag
+  double w;            // omega / diag
 };
 
 __device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -87,25 +85,48 @@ __device__ __forceinline__ void tma_load_plane(void *dst, const CUtensorMap *tm,
       : "memory");
 }
 
-// Declaration orders of the 7-point stencils in the reference's programs (the order fixes the
-// floating-point association): 0 = centre,-x,+x,-y,+y,-z,+z (Benchmark/Poisson3D, Examples/Poisson),
+// One point update.  ORD = declaration order of the stencil entries, which fixes the
+// floating-point association: 0 = centre,-x,+x,-y,+y,-z,+z (Benchmark/Poisson3D, Examples/Poisson),
 // 1 = centre,+x,-x,+y,-y,+z,-z (Testing/Smoothers, Testing/SISC, Testing/Opts).
-__device__ constexpr int ORD_DX[2][7] = {{0, -1, 1, 0, 0, 0, 0}, {0, 1, -1, 0, 0, 0, 0}};
-__device__ constexpr int ORD_DY[2][7] = {{0, 0, 0, -1, 1, 0, 0}, {0, 0, 0, 1, -1, 0, 0}};
-__device__ constexpr int ORD_DZ[2][7] = {{0, 0, 0, 0, 0, -1, 1}, {0, 0, 0, 0, 0, 1, -1}};
-
 template <int ORD>
-__global__ void __launch_bounds__(FNT, 2)
-k_rb_fused(const __grid_constant__ CUtensorMap tm_in, const __grid_constant__ FusedArgs a,
-           const double *__restrict__ rhs, double *__restrict__ uout) {
-  // dynamic shared memory only (starts 1024-byte aligned): ring of FR planes, then the mbarriers
-  extern __shared__ __align__(1024) double ring[];
-  uint64_t *full = reinterpret_cast<uint64_t *>(ring + FPLANE * FR);
-  char *ringb = reinterpret_cast<char *>(ring);
+__device__ __forceinline__ double rb_update(double c, double xm, double xp, double ym, double yp, double zm, double zp,
+                                            double f, const double (&coef)[7], double w) {
+  double acc = coef[0] * c;
+  if (ORD == 0) {
+    acc = fma(coef[1], xm, acc);
+    acc = fma(coef[2], xp, acc);
+    acc = fma(coef[3], ym, acc);
+    acc = fma(coef[4], yp, acc);
+    acc = fma(coef[5], zm, acc);
+    acc = fma(coef[6], zp, acc);
+  } else {
+    acc = fma(coef[1], xp, acc);
+    acc = fma(coef[2], xm, acc);
+    acc = fma(coef[3], yp, acc);
+    acc = fma(coef[4], ym, acc);
+    acc = fma(coef[5], zp, acc);
+    acc = fma(coef[6], zm, acc);
+  }
+  const double r = f - acc;
+  return fma(w, r, c);
+}
+
+template <int S, int ORD>
+__global__ void __launch_bounds__(RNT, 1)
+k_rbw(const __grid_constant__ CUtensorMap tm_u, const __grid_constant__ CUtensorMap tm_f,
+      const __grid_constant__ RbwArgs a, double *__restrict__ uout) {
+  constexpr int NW = S + 2;  // planes in the register window: t-S-1 .. t
+  static_assert(S == 2 || S == 4, "S half-sweeps");
+  extern __shared__ __align__(1024) unsigned char smem[];
+  uint64_t *full = reinterpret_cast<uint64_t *>(smem);
+  double *ring_u = reinterpret_cast<double *>(smem + ROFF_RING);
+  double *ring_f = ring_u + RD * RPLANE;
+  double *xbuf = ring_f + RD * RPLANE;  // [(s-1)*2 + plane parity][RXB], s = 1..S-1
 
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int x0 = 2 * lane, y0 = 2 * warp;  // the thread's 2x2 block inside the tile
   if (tid == 0) {
-    for (int i = 0; i < FR; ++i) mbar_init(&full[i], 1);
+    for (int i = 0; i < RD; ++i) mbar_init(&full[i], 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   __syncthreads();
@@ -116,11 +137,13 @@ k_rb_fused(const __grid_constant__ CUtensorMap tm_in, const __grid_constant__ Fu
   const double w = a.w;
   const long long plane8 = a.plane * 8;
   const long long pitch8 = (long long)a.pitch * 8;
+  const int ld_off = y0 * RW + x0;           // (x0, y0) inside a staged plane
+  const int x_off = 16 + (y0 + 1) * 32 + lane;  // (row y0, column pair `lane`) inside an exchange buffer
 
   // this CTA's share of the (tile, plane) units
   const long long u0 = a.units * blockIdx.x / gridDim.x;
   const long long u1 = a.units * (blockIdx.x + 1) / gridDim.x;
-  int loads = 0;  // planes loaded so far by this CTA, modulo 2*FR (ring position and mbarrier phase)
+  uint32_t kt = 0;  // planes loaded so far, modulo 2*RD: ring slot kt & 3, mbarrier phase kt >> 2
 
   for (long long ub = u0; ub < u1;) {
     const int tile = (int)(ub / a.nzp);
@@ -128,164 +151,135 @@ k_rb_fused(const __grid_constant__ CUtensorMap tm_in, const __grid_constant__ Fu
     const long long seg_end = min(u1, (long long)(tile + 1) * a.nzp);
     const int zb = za + (int)(seg_end - ub);
     ub = seg_end;
-    const int ox = FOW * (tile % a.tiles_x), oy = FOH * (tile / a.tiles_x);  // first output node of the tile
-    const int t0 = za - FS, tl = zb - 1 + FS;  // first / last plane loaded
+    const int ox = (RW - 2 * S) * (tile % a.tiles_x), oy = (RH - 2 * S) * (tile / a.tiles_x);  // first output node
+    const int gx = ox - S + x0, gy = oy - S + y0;  // local node coordinates of the thread's block
+    // Colour of node (x,y,z) is (x+y+z+par)&1; x0, y0 are even, so the colour pattern of the 2x2
+    // block depends on the plane only.  Steps are numbered K = t - t0 with (t0 + bp) even: at odd K
+    // every half-sweep updates the diagonal (0,0),(1,1) of its plane, at even K the anti-diagonal.
+    const int bp = (ox + oy + a.par) & 1;
+    int t0 = za - S;
+    t0 -= (t0 + bp) & 1;
+    const int tl = zb - 1 + S;  // last plane loaded = last step
     // array coordinates of the tile corner (TMA zero-fills outside the allocation)
-    const int cx = ox - FS + XPAD, cy = oy - FS + GHOST;
+    const int cx = ox - S + XPAD, cy = oy - S + GHOST;
 
-    // ---- per-thread item geometry, fixed for the segment ------------------------------
-    // A warp item is 2 rows x 32 columns; the lane owns the column pair (xb, xb+1) of one row.
-    // 64-bit shared-memory accesses are served per half-warp: lanes 0-7 take row y, lanes 8-15
-    // row y+1 of one 16-column group; their colour points sit in complementary 8-byte bank
-    // pairs, so every access is conflict-free.
-    // Colour of (x,y,z) is (x+y+z+par)&1.  At step t = t0+rel stage 2 (colour 1, plane t-3)
-    // updates x = xb + (e ^ rel&1) and stage 1 (colour 0, plane t-1) the other column, with
-    // e = (xb+y+par+t0)&1.  "A" = column xb+e, "B" = column xb+(e^1).
-    uint32_t offA[FNI], offB[FNI];    // byte offset of the point inside a plane of the ring
-    uint32_t roffA[FNI], roffB[FNI];  // byte offset of the point inside a plane of rhs
-    uint32_t okmask = 0;              // bit 2*it: A may be updated, bit 2*it+1: B
+    // update masks: bit 4*(s-1)+j, j = jx + 2*jy
+    uint32_t mk = 0;
 #pragma unroll
-    for (int it = 0; it < FNI; ++it) {
-      const int item = warp + it * (FNT / 32);
-      const int rp = item / (FW / 32), ch = item % (FW / 32);
-      const int y = 1 + 2 * rp + ((lane >> 3) & 1);
-      const int xb = 32 * ch + 16 * (lane >> 4) + 2 * (lane & 7);
-      const int lx = ox - FS + xb, ly = oy - FS + y;
-      const int e = (lx + ly + a.par + t0) & 1;
-      const bool rowok = ly >= a.ulo[1] && ly < a.uhi[1];
-      const bool v0 = rowok && xb >= 1 && lx >= a.ulo[0] && lx < a.uhi[0];
-      const bool v1 = rowok && xb + 1 <= FW - 2 && lx + 1 >= a.ulo[0] && lx + 1 < a.uhi[0];
-      offA[it] = (uint32_t)(y * FW + xb + e) * 8u;
-      offB[it] = (uint32_t)(y * FW + xb + (e ^ 1)) * 8u;
-      const int g = lx + a.pitch * ly;
-      roffA[it] = (uint32_t)(g + e) * 8u;
-      roffB[it] = (uint32_t)(g + (e ^ 1)) * 8u;
-      okmask |= ((e ? v1 : v0) ? 1u : 0u) << (2 * it);
-      okmask |= ((e ? v0 : v1) ? 1u : 0u) << (2 * it + 1);
+    for (int s = 1; s <= S; ++s) {
+      const int e = S - s;
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const int xx = gx + (j & 1), yy = gy + (j >> 1);
+        const bool ok = xx >= a.ulo[0] - e * a.elo[0] && xx < a.uhi[0] + e * a.ehi[0] &&
+                        yy >= a.ulo[1] - e * a.elo[1] && yy < a.uhi[1] + e * a.ehi[1];
+        mk |= (ok ? 1u : 0u) << (4 * (s - 1) + j);
+      }
     }
-    // output rows of this warp: r = warp, warp+8, ...; two 32-column chunks
-    const uint32_t so_off = (uint32_t)((FS + warp) * FW + FS + lane) * 8u;
-    const int wlim = min(FOW, a.n[0] - ox), hlim = min(FOH, a.n[1] - oy);
-    char *const dst0 = reinterpret_cast<char *>(uout + ox + lane) + pitch8 * (oy + warp);
+    const bool xst = x0 >= S && x0 < RW - S && gx < a.n[0];
+    const bool st0 = xst && y0 >= S && y0 < RH - S && gy < a.n[1];
+    const bool st1 = xst && y0 >= S && y0 < RH - S && gy + 1 < a.n[1];
+    char *const dst = reinterpret_cast<char *>(uout + gx) + pitch8 * gy;
 
+    auto issue = [&](int z, uint32_t k) {
+      const int sl = k & (RD - 1);
+      mbar_expect_tx(&full[sl], 2 * RPLANE * 8);
+      tma_load_plane(ring_u + sl * RPLANE, &tm_u, cx, cy, z + GHOST, &full[sl]);
+      tma_load_plane(ring_f + sl * RPLANE, &tm_f, cx, cy, z + GHOST, &full[sl]);
+    };
     if (tid == 0) {
       asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-      for (int z = t0; z <= min(t0 + 1, tl); ++z) {
-        const int k = (loads + z - t0) % (2 * FR), sl = k % FR;
-        mbar_expect_tx(&full[sl], FPLANE * 8);
-        tma_load_plane(ring + sl * FPLANE, &tm_in, cx, cy, z + GHOST, &full[sl]);
-      }
+      for (int i = 0; i < RD - 1; ++i)
+        if (t0 + i <= tl) issue(t0 + i, kt + i);
     }
-    // rhs values are fetched one step ahead into registers: step parity 0 consumes rq0 and fills
-    // rq1, parity 1 the other way round, so no copies are needed
-    double rq0[FS][FNI], rq1[FS][FNI];
-#pragma unroll
-    for (int s = 0; s < FS; ++s)
-#pragma unroll
-      for (int it = 0; it < FNI; ++it) rq0[s][it] = rq1[s][it] = 0.0;
 
-    int kt = loads;  // ring counter of plane t (mod 2*FR)
-
-    auto step = [&](auto parity, const int t) {
-      constexpr int P = decltype(parity)::value;
-      double(&rcur)[FS][FNI] = P ? rq1 : rq0;
-      double(&rnxt)[FS][FNI] = P ? rq0 : rq1;
-      // ---- (1) rhs prefetch for step t+1 (relative parity P^1) --------------------------
+    double u[NW][4], f[NW][4];  // [plane slot][jx + 2*jy]
 #pragma unroll
-      for (int s = 1; s <= FS; ++s) {
-        const int zs = t + 1 - (2 * s - 1);
-        const bool zok = zs >= za - (FS - s) && zs < zb + (FS - s) && zs >= a.ulo[2] && zs < a.uhi[2];
+    for (int q = 0; q < NW; ++q)
+#pragma unroll
+      for (int j = 0; j < 4; ++j) u[q][j] = f[q][j] = 0.0;
+
+    auto step = [&](auto kc, const int t) {
+      constexpr int K = decltype(kc)::value;
+      constexpr bool DIAG = (K & 1) != 0;
+      constexpr int P0 = DIAG ? 0 : 1, P1 = DIAG ? 3 : 2;  // updated points in row y0 / row y0+1
+      constexpr int Q0 = DIAG ? 1 : 0, Q1 = DIAG ? 2 : 3;  // the other point of row y0 / row y0+1
+      const int slot_t = kt & (RD - 1);
+      mbar_wait(&full[slot_t], kt >> 2);
+      {
+        const double2 *pu = reinterpret_cast<const double2 *>(ring_u + slot_t * RPLANE + ld_off);
+        const double2 *pf = reinterpret_cast<const double2 *>(ring_f + slot_t * RPLANE + ld_off);
+        const double2 a0 = pu[0], a1 = pu[RW / 2], b0 = pf[0], b1 = pf[RW / 2];
+        u[K][0] = a0.x; u[K][1] = a0.y; u[K][2] = a1.x; u[K][3] = a1.y;
+        f[K][0] = b0.x; f[K][1] = b0.y; f[K][2] = b1.x; f[K][3] = b1.y;
+      }
+#pragma unroll
+      for (int s = 1; s <= S; ++s) {
+        const int c = (K + NW - s) % NW, cm = (K + NW - s - 1) % NW, cp = (K + NW - s + 1) % NW;
+        const int pp = (K + NW - s) & 1;
+        const int p = t - s, e = S - s;
+        const bool zok = p >= a.ulo[2] - e * a.elo[2] && p < a.uhi[2] + e * a.ehi[2];
         if (zok) {
-          const bool useA = (s == 2) == ((P ^ 1) == 0);
-          const char *rz = reinterpret_cast<const char *>(rhs) + plane8 * zs;  // uniform
-#pragma unroll
-          for (int it = 0; it < FNI; ++it) {
-            const bool ok = (okmask >> (2 * it + (useA ? 0 : 1))) & 1u;
-            const uint32_t ro = useA ? roffA[it] : roffB[it];
-            rnxt[s - 1][it] = ok ? __ldg(reinterpret_cast<const double *>(rz + ro)) : 0.0;
+          // neighbours owned by other threads: row y0 -> (ex0 in x, ey0 at y0-1), row y0+1 -> (ex1, ey1 at y0+2)
+          double ex0, ey0, ex1, ey1;
+          if (s == 1) {  // original values: the staged plane t-1
+            const double *pl = ring_u + ((slot_t + RD - 1) & (RD - 1)) * RPLANE + ld_off;
+            ex0 = pl[DIAG ? -1 : 2];
+            ey0 = pl[-RW + (DIAG ? 0 : 1)];
+            ex1 = pl[RW + (DIAG ? 2 : -1)];
+            ey1 = pl[2 * RW + (DIAG ? 1 : 0)];
+          } else {  // what half-sweep s-1 published for this plane one step ago
+            const double *xb = xbuf + ((s - 2) * 2 + pp) * RXB + x_off;
+            ex0 = xb[DIAG ? -1 : 1];
+            ey0 = xb[-32];
+            ex1 = xb[32 + (DIAG ? 1 : -1)];
+            ey1 = xb[64];
           }
+          const double n0 = rb_update<ORD>(u[c][P0], DIAG ? ex0 : u[c][Q0], DIAG ? u[c][Q0] : ex0, ey0, u[c][Q1],
+                                           u[cm][P0], u[cp][P0], f[c][P0], coef, w);
+          const double n1 = rb_update<ORD>(u[c][P1], DIAG ? u[c][Q1] : ex1, DIAG ? ex1 : u[c][Q1], u[c][Q0], ey1,
+                                           u[cm][P1], u[cp][P1], f[c][P1], coef, w);
+          if ((mk >> (4 * (s - 1) + P0)) & 1u) u[c][P0] = n0;
+          if ((mk >> (4 * (s - 1) + P1)) & 1u) u[c][P1] = n1;
+        }
+        if (s < S) {  // publish this colour of the plane for half-sweep s+1 (also where nothing was updated)
+          double *xw = xbuf + ((s - 1) * 2 + pp) * RXB + x_off;
+          xw[0] = u[c][P0];
+          xw[32] = u[c][P1];
         }
       }
-      const int slot_t = kt >= FR ? kt - FR : kt;
-      if (t <= tl) mbar_wait(&full[slot_t], (uint32_t)(kt >= FR));
-      // ---- (2) stages: colour s-1 on plane t-(2s-1); all loads first, then all stores ----
-      double nv[FS][FNI];
-      uint32_t sa[FS][FNI];
-      bool act[FS];
-#pragma unroll
-      for (int s = 1; s <= FS; ++s) {
-        const int zs = t - (2 * s - 1);
-        act[s - 1] = zs >= za - (FS - s) && zs < zb + (FS - s) && zs >= a.ulo[2] && zs < a.uhi[2];
-        if (act[s - 1]) {
-          const bool useA = (s == 2) == (P == 0);
-          int sc = slot_t - (2 * s - 1);  // ring slots of planes zs, zs-1, zs+1
-          if (sc < 0) sc += FR;
-          const int sm = sc == 0 ? FR - 1 : sc - 1, sp = sc == FR - 1 ? 0 : sc + 1;
-          const char *pcb = ringb + sc * (FPLANE * 8);
-          const int dm = (sm - sc) * (FPLANE * 8), dp = (sp - sc) * (FPLANE * 8);
-#pragma unroll
-          for (int it = 0; it < FNI; ++it) {
-            const uint32_t off = useA ? offA[it] : offB[it];
-            const char *pt = pcb + off;  // all seven neighbours are inside the ring for every lane
-            double v[7];
-#pragma unroll
-            for (int k = 0; k < 7; ++k) {
-              const int d = (ORD_DX[ORD][k] + FW * ORD_DY[ORD][k]) * 8;
-              const char *q = ORD_DZ[ORD][k] == 0 ? pt : (ORD_DZ[ORD][k] < 0 ? pt + dm : pt + dp);
-              v[k] = *reinterpret_cast<const double *>(q + d);
-            }
-            double acc = coef[0] * v[0];
-#pragma unroll
-            for (int k = 1; k < 7; ++k) acc = fma(coef[k], v[k], acc);
-            const double r = rcur[s - 1][it] - acc;
-            nv[s - 1][it] = fma(w, r, v[0]);
-            sa[s - 1][it] = (uint32_t)(sc * (FPLANE * 8)) + off;
-          }
-        }
-      }
-#pragma unroll
-      for (int s = 0; s < FS; ++s)
-        if (act[s]) {
-          const bool useA = (s == 1) == (P == 0);
-#pragma unroll
-          for (int it = 0; it < FNI; ++it)
-            if ((okmask >> (2 * it + (useA ? 0 : 1))) & 1u) *reinterpret_cast<double *>(ringb + sa[s][it]) = nv[s][it];
-        }
-      // ---- (3) plane t-2S is final: write the tile's outputs -----------------------------
-      const int zf = t - 2 * FS;
+      // plane t-S is final
+      const int zf = t - S;
       if (zf >= za && zf < zb) {
-        int sf = slot_t - 2 * FS;
-        if (sf < 0) sf += FR;
-        const char *src = ringb + sf * (FPLANE * 8) + so_off;
-        char *dst = dst0 + plane8 * zf;
-#pragma unroll
-        for (int i = 0; i < (FOH + FNT / 32 - 1) / (FNT / 32); ++i) {
-          const int r = warp + i * (FNT / 32);
-          if (r < hlim) {
-            const double *sr = reinterpret_cast<const double *>(src + i * (FNT / 32) * FW * 8);
-            double *dr = reinterpret_cast<double *>(dst + pitch8 * (i * (FNT / 32)));
-            if (lane < wlim) dr[0] = sr[0];
-            if (lane + 32 < wlim) dr[32] = sr[32];
-          }
-        }
+        const int c = (K + NW - S) % NW;
+        char *d = dst + plane8 * zf;
+        if (st0) *reinterpret_cast<double2 *>(d) = make_double2(u[c][0], u[c][1]);
+        if (st1) *reinterpret_cast<double2 *>(d + pitch8) = make_double2(u[c][2], u[c][3]);
       }
       __syncthreads();
-      // the slot of plane t-2S is free now: prefetch plane t+2 into it
-      if (tid == 0 && t + 2 <= tl) {
-        const int sl = slot_t + 2 >= FR ? slot_t + 2 - FR : slot_t + 2;
+      // the slot of plane t-1 is free now: prefetch plane t+3 into it
+      if (tid == 0 && t + RD - 1 <= tl) {
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-        mbar_expect_tx(&full[sl], FPLANE * 8);
-        tma_load_plane(ring + sl * FPLANE, &tm_in, cx, cy, t + 2 + GHOST, &full[sl]);
+        issue(t + RD - 1, kt + RD - 1);
       }
-      kt = kt + 1 == 2 * FR ? 0 : kt + 1;
+      kt = (kt + 1) & (2 * RD - 1);
     };
 
-    const int tend = zb - 1 + 2 * FS;
-    for (int t = t0; t <= tend; t += 2) {
+    for (int t = t0; t <= tl; t += NW) {
       step(std::integral_constant<int, 0>{}, t);
-      if (t + 1 <= tend) step(std::integral_constant<int, 1>{}, t + 1);
+      if (t + 1 > tl) break;
+      step(std::integral_constant<int, 1>{}, t + 1);
+      if (t + 2 > tl) break;
+      step(std::integral_constant<int, 2>{}, t + 2);
+      if (t + 3 > tl) break;
+      step(std::integral_constant<int, 3>{}, t + 3);
+      if (NW > 4) {
+        if (t + 4 > tl) break;
+        step(std::integral_constant<int, 4 % NW>{}, t + 4);
+        if (t + 5 > tl) break;
+        step(std::integral_constant<int, 5 % NW>{}, t + 5);
+      }
     }
-    loads = (loads + tl - t0 + 1) % (2 * FR);
   }
 }
 
@@ -307,15 +301,16 @@ static EncodeTiledFn encode_fn() {
   return fn;
 }
 
-static int make_plane_map(const LevelGeom &g, double *base, CUtensorMap *tm) {
+static int make_plane_map(const LevelGeom &g, const double *base, CUtensorMap *tm) {
   EncodeTiledFn fn = encode_fn();
   if (!fn) return set_error(EXAMG_ECUDA, "cuTensorMapEncodeTiled entry point not available");
   const cuuint64_t dims[3] = {(cuuint64_t)g.pitch, (cuuint64_t)g.ay, (cuuint64_t)g.az};
   const cuuint64_t strides[2] = {(cuuint64_t)g.pitch * 8, (cuuint64_t)g.plane * 8};
-  const cuuint32_t box[3] = {FW, FH, 1};
+  const cuuint32_t box[3] = {RW, RH, 1};
   const cuuint32_t estr[3] = {1, 1, 1};
-  CUresult r = fn(tm, CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 3, base, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
-                  CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  CUresult r = fn(tm, CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 3, const_cast<double *>(base), dims, strides, box, estr,
+                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) return set_error(EXAMG_ECUDA, "cuTensorMapEncodeTiled failed (%d)", (int)r);
   return EXAMG_OK;
 }
@@ -335,13 +330,22 @@ static int stencil_order(const Stencil &s) {
   return -1;
 }
 
+static int env_flag(const char *name, int dflt) {
+  const char *e = getenv(name);
+  return e && e[0] ? atoi(e) : dflt;
+}
+
 static bool fused_enabled() {
   static int v = -1;
-  if (v < 0) {
-    const char *e = getenv("EXAMG_NO_FUSED");
-    v = (e && e[0] == '1') ? 0 : 1;
-  }
+  if (v < 0) v = env_flag("EXAMG_NO_FUSED", 0) ? 0 : 1;
   return v == 1;
+}
+
+// largest number of half-sweeps fused into one pass (EXAMG_FUSE_HALF_SWEEPS = 2 or 4)
+static int max_half_sweeps() {
+  static int v = -1;
+  if (v < 0) v = env_flag("EXAMG_FUSE_HALF_SWEEPS", 4) >= 4 ? 4 : 2;
+  return v;
 }
 
 // smallest level extent for which the tiled kernel pays off (below: a few hundred KB per sweep)
@@ -358,8 +362,10 @@ bool fused_rb_usable(examg_ctx *c, const Stencil &s, const Field &fu) {
 int ensure_shadow(examg_ctx *c, Field &fu) {
   static bool attr_set = false;
   if (!attr_set) {
-    EXAMG_CUDA(cudaFuncSetAttribute(k_rb_fused<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)FSMEM));
-    EXAMG_CUDA(cudaFuncSetAttribute(k_rb_fused<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)FSMEM));
+    EXAMG_CUDA(cudaFuncSetAttribute(k_rbw<2, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)rbw_smem<2>()));
+    EXAMG_CUDA(cudaFuncSetAttribute(k_rbw<2, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)rbw_smem<2>()));
+    EXAMG_CUDA(cudaFuncSetAttribute(k_rbw<4, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)rbw_smem<4>()));
+    EXAMG_CUDA(cudaFuncSetAttribute(k_rbw<4, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)rbw_smem<4>()));
     attr_set = true;
   }
   if (fu.shadow) return EXAMG_OK;
@@ -372,26 +378,28 @@ int ensure_shadow(examg_ctx *c, Field &fu) {
   return EXAMG_OK;
 }
 
-// One full sweep: colour 0 then colour 1.  Swaps fu.slot[cur] with the shadow buffer.
-int launch_rb_fused(examg_ctx *c, const Stencil &s, double omega, Field &fu, const double *rhs) {
+// nhalf/2 full sweeps (colour 0, colour 1, ...) in one pass.  Swaps fu.slot[cur] with the shadow buffer.
+template <int S>
+static int launch_rbw(examg_ctx *c, const Stencil &s, double omega, Field &fu, const double *rhs) {
   const LevelGeom &g = *geom(c, s.level);
-  int rc0 = ensure_shadow(c, fu);
-  if (rc0) return rc0;
-  CUtensorMap tm;
-  int rc = make_plane_map(g, fu.slot[fu.cur], &tm);
+  CUtensorMap tm_u, tm_f;
+  int rc = make_plane_map(g, fu.slot[fu.cur], &tm_u);
   if (rc) return rc;
-  FusedArgs a;
+  if ((rc = make_plane_map(g, rhs - g.origin, &tm_f))) return rc;
+  RbwArgs a;
   for (int d = 0; d < 3; ++d) {
     a.n[d] = g.n[d];
     a.ulo[d] = g.lo[d];
     a.uhi[d] = g.hi[d];
+    a.elo[d] = c->nb[d][0] ? 1 : 0;
+    a.ehi[d] = c->nb[d][1] ? 1 : 0;
   }
   a.pitch = g.pitch;
   a.plane = g.plane;
-  a.tiles_x = (g.n[0] + FOW - 1) / FOW;
-  a.tiles_y = (g.n[1] + FOH - 1) / FOH;
+  a.tiles_x = (g.n[0] + (RW - 2 * S) - 1) / (RW - 2 * S);
+  const int tiles_y = (g.n[1] + (RH - 2 * S) - 1) / (RH - 2 * S);
   a.nzp = g.n[2];
-  a.units = (long long)a.tiles_x * a.tiles_y * a.nzp;
+  a.units = (long long)a.tiles_x * tiles_y * a.nzp;
   a.par = g.par;
   for (int k = 0; k < 7; ++k) a.coef[k] = s.coef[k];
   const int ord = stencil_order(s);
@@ -399,20 +407,33 @@ int launch_rb_fused(examg_ctx *c, const Stencil &s, double omega, Field &fu, con
   int dev = 0, nsm = 148;
   cudaGetDevice(&dev);
   cudaDeviceGetAttribute(&nsm, cudaDevAttrMultiProcessorCount, dev);
-  long long grid = 2LL * nsm;
-  const long long min_units = 24;  // at least this many planes per CTA (4 are restart overhead)
+  long long grid = nsm;
+  const long long min_units = 6 * S;  // at least this many planes per CTA (2S are restart overhead)
   if (grid > a.units / min_units) grid = a.units / min_units;
   if (grid < 1) grid = 1;
   if (ord == 0)
-    k_rb_fused<0><<<(int)grid, FNT, FSMEM, c->stream>>>(tm, a, rhs, fu.shadow + g.origin);
+    k_rbw<S, 0><<<(int)grid, RNT, rbw_smem<S>(), c->stream>>>(tm_u, tm_f, a, fu.shadow + g.origin);
   else
-    k_rb_fused<1><<<(int)grid, FNT, FSMEM, c->stream>>>(tm, a, rhs, fu.shadow + g.origin);
+    k_rbw<S, 1><<<(int)grid, RNT, rbw_smem<S>(), c->stream>>>(tm_u, tm_f, a, fu.shadow + g.origin);
   EXAMG_LAUNCH_CHECK(c);
   double *t = fu.slot[fu.cur];
   fu.slot[fu.cur] = fu.shadow;
   fu.shadow = t;
   fu.swapped = !fu.swapped;
   return EXAMG_OK;
+}
+
+// nsweeps full sweeps; returns the number of sweeps done by one launch through *done
+int launch_rb_fused(examg_ctx *c, const Stencil &s, double omega, Field &fu, const double *rhs, int nsweeps,
+                    int *done) {
+  int rc = ensure_shadow(c, fu);
+  if (rc) return rc;
+  if (nsweeps >= 2 && max_half_sweeps() >= 4) {
+    *done = 2;
+    return launch_rbw<4>(c, s, omega, fu, rhs);
+  }
+  *done = 1;
+  return launch_rbw<2>(c, s, omega, fu, rhs);
 }
 
 bool fast7_usable(examg_ctx *c, const Stencil &s) { (void)c; (void)s; return false; }

@@ -19,7 +19,7 @@ bool fast7_usable(examg_ctx *c, const Stencil &s);
 int fast7_residual(examg_ctx *c, const Stencil &s, const double *u, const double *rhs, double *res, int red_slot);
 int fast7_rb(examg_ctx *c, const Stencil &s, double omega, double *u, const double *rhs, int color);
 bool fused_rb_usable(examg_ctx *c, const Stencil &s, const Field &fu);
-int launch_rb_fused(examg_ctx *c, const Stencil &s, double omega, Field &fu, const double *rhs);
+int launch_rb_fused(examg_ctx *c, const Stencil &s, double omega, Field &fu, const double *rhs, int nsweeps, int *done);
 
 int launch_residual(examg_ctx *c, const Stencil &s, const double *u, const double *rhs, double *res, int red_slot) {
   if (fast7_usable(c, s)) return fast7_residual(c, s, u, rhs, res, red_slot);
@@ -102,11 +102,12 @@ int examg_smooth_rbgs(examg_ctx *c, int A, int u, int rhs, double omega, int nsw
   {
     GET_STENCIL(s, A); GET_FIELD(fu, u); GET_FIELD(fr, rhs);
     CHECK_LEVEL(fu, s->level); CHECK_LEVEL(fr, s->level);
-    if (fused_rb_usable(c, *s, *fu)) {  // both colours of a sweep in one pass over HBM
-      for (int it = 0; it < nsweeps; ++it) {
-        int rc = do_exchange(c, *fu, fu->cur);
+    if (fused_rb_usable(c, *s, *fu)) {  // both colours of one or two sweeps in one pass over HBM
+      for (int it = 0; it < nsweeps;) {
+        int rc = do_exchange(c, *fu, fu->cur), done = 0;
         if (rc) return rc;
-        if ((rc = launch_rb_fused(c, *s, omega, *fu, field_ptr(c, fr, -1)))) return rc;
+        if ((rc = launch_rb_fused(c, *s, omega, *fu, field_ptr(c, fr, -1), nsweeps - it, &done))) return rc;
+        it += done;
       }
       return EXAMG_OK;
     }
