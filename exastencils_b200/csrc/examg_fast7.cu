@@ -20,9 +20,15 @@
 //     buffered: one __syncthreads per plane).  The update is Gauss-Seidel in place -- in the
 //     register window.
 //   * plane t-S is final after half-sweep S and is written with 128-bit stores
-//   * work = (tile, plane) units split evenly over the grid; a segment start costs 2S planes
-// HBM traffic per point (S = 2): 8/0.82 (Solution with halo) + 8/0.82 (RHS) + 8 (write) = 27.5 B
-// against 24 B algorithmic; S = 4: 8/0.66 * 2 + 8 = 32.4 B against 48 B.
+//   * schedule: full waves in which CTA b marches through the whole z column of tile
+//     wave*grid + b -- adjacent tiles advance side by side, so the halo two tiles share is read
+//     from HBM once and found in the 126 MB L2 by the other (measured: 89% of the copy roofline
+//     against 60% with a stream-K split) -- then the remaining tiles*planes units are
+//     split evenly over the grid; a segment start costs 2S planes
+// HBM traffic per point (S = 2) with the halo served from L2: 8 + 8 + 8 = 24 B, the algorithmic
+// minimum; without L2 sharing 8/0.82 * 2 + 8 = 27.5 B.  S = 4: 24 B for 48 B of algorithmic work.
+// Tried and dropped (profiles/r01_notes.md): L2 prefetch ahead of the ring (evicts the shared
+// halo lines), a loose lockstep between neighbouring CTAs (no gain over free-running).
 //
 // Arithmetic is the contract of examg_kernels.cu (bit-identical to the unfused order).
 #include <cuda.h>
@@ -50,10 +56,10 @@ struct RbwArgs {
   int elo[3], ehi[3];  // 1: neighbour block on that side; half-sweep s also updates S-s layers beyond
   int pitch;
   long long plane;
-  int tiles_x;
+  int tiles_x, tiles;
   int nzp;             // output planes 0..nzp-1
-  long long units;     // tiles * nzp
   int par;
+  int pf;              // planes ahead of the TMA loads that are prefetched into L2 (0: none)
   double coef[7];
   double w;            // omega / diag
 };
@@ -83,6 +89,11 @@ __device__ __forceinline__ void tma_load_plane(void *dst, const CUtensorMap *tm,
       "cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];"
       ::"r"(smem_u32(dst)), "l"((uint64_t)tm), "r"(x), "r"(y), "r"(z), "r"(smem_u32(bar))
       : "memory");
+}
+
+__device__ __forceinline__ void tma_prefetch_plane(const CUtensorMap *tm, int x, int y, int z) {
+  asm volatile("cp.async.bulk.prefetch.tensor.3d.L2.global.tile [%0, {%1, %2, %3}];"
+               ::"l"((uint64_t)tm), "r"(x), "r"(y), "r"(z) : "memory");
 }
 
 // One point update.  ORD = declaration order of the stencil entries, which fixes the
@@ -140,17 +151,31 @@ k_rbw(const __grid_constant__ CUtensorMap tm_u, const __grid_constant__ CUtensor
   const int ld_off = y0 * RW + x0;           // (x0, y0) inside a staged plane
   const int x_off = 16 + (y0 + 1) * 32 + lane;  // (row y0, column pair `lane`) inside an exchange buffer
 
-  // this CTA's share of the (tile, plane) units
-  const long long u0 = a.units * blockIdx.x / gridDim.x;
-  const long long u1 = a.units * (blockIdx.x + 1) / gridDim.x;
+  // Schedule: `nfull` waves in which every CTA marches through the whole z column of one tile
+  // (tile = wave * gridDim + blockIdx: neighbouring tiles run side by side at the same z, so the
+  // halo they share is read from HBM once and found in L2 by the other), then the remaining
+  // tiles * planes units are split evenly over the grid.
+  const int G = gridDim.x, bid = blockIdx.x;
+  const int nfull = a.tiles / G;
+  const long long rem_units = (long long)(a.tiles - nfull * G) * a.nzp;
+  const long long u1 = rem_units * (bid + 1) / G;
+  long long ub = rem_units * bid / G;
   uint32_t kt = 0;  // planes loaded so far, modulo 2*RD: ring slot kt & 3, mbarrier phase kt >> 2
-
-  for (long long ub = u0; ub < u1;) {
-    const int tile = (int)(ub / a.nzp);
-    const int za = (int)(ub - (long long)tile * a.nzp);
-    const long long seg_end = min(u1, (long long)(tile + 1) * a.nzp);
-    const int zb = za + (int)(seg_end - ub);
-    ub = seg_end;
+  for (int seg = 0;; ++seg) {
+    int tile, za, zb;
+    if (seg < nfull) {
+      tile = seg * G + bid;
+      za = 0;
+      zb = a.nzp;
+    } else {
+      if (ub >= u1) break;
+      const int rt = (int)(ub / a.nzp);
+      tile = nfull * G + rt;
+      za = (int)(ub - (long long)rt * a.nzp);
+      const long long seg_end = min(u1, (long long)(rt + 1) * a.nzp);
+      zb = za + (int)(seg_end - ub);
+      ub = seg_end;
+    }
     const int ox = (RW - 2 * S) * (tile % a.tiles_x), oy = (RH - 2 * S) * (tile / a.tiles_x);  // first output node
     const int gx = ox - S + x0, gy = oy - S + y0;  // local node coordinates of the thread's block
     // Colour of node (x,y,z) is (x+y+z+par)&1; x0, y0 are even, so the colour pattern of the 2x2
@@ -191,6 +216,11 @@ k_rbw(const __grid_constant__ CUtensorMap tm_u, const __grid_constant__ CUtensor
       asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
       for (int i = 0; i < RD - 1; ++i)
         if (t0 + i <= tl) issue(t0 + i, kt + i);
+      for (int i = RD - 1; i < RD - 1 + a.pf; ++i)
+        if (t0 + i <= tl) {
+          tma_prefetch_plane(&tm_u, cx, cy, t0 + i + GHOST);
+          tma_prefetch_plane(&tm_f, cx, cy, t0 + i + GHOST);
+        }
     }
 
     double u[NW][4], f[NW][4];  // [plane slot][jx + 2*jy]
@@ -257,10 +287,16 @@ k_rbw(const __grid_constant__ CUtensorMap tm_u, const __grid_constant__ CUtensor
         if (st1) *reinterpret_cast<double2 *>(d + pitch8) = make_double2(u[c][2], u[c][3]);
       }
       __syncthreads();
-      // the slot of plane t-1 is free now: prefetch plane t+3 into it
+      // The slot of plane t-1 is free now: prefetch plane t+3 into it.  Every generic-proxy read of
+      // the slot has returned its data before its thread arrived at the barrier above (the values
+      // were consumed by this step's arithmetic), so no proxy fence is needed -- a fence here would
+      // also make the TMA issue wait for this thread's outstanding global accesses.
       if (tid == 0 && t + RD - 1 <= tl) {
-        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
         issue(t + RD - 1, kt + RD - 1);
+        if (a.pf > 0 && t + RD - 1 + a.pf <= tl) {
+          tma_prefetch_plane(&tm_u, cx, cy, t + RD - 1 + a.pf + GHOST);
+          tma_prefetch_plane(&tm_f, cx, cy, t + RD - 1 + a.pf + GHOST);
+        }
       }
       kt = (kt + 1) & (2 * RD - 1);
     };
@@ -301,6 +337,25 @@ static EncodeTiledFn encode_fn() {
   return fn;
 }
 
+static int env_flag(const char *name, int dflt) {
+  const char *e = getenv(name);
+  return e && e[0] ? atoi(e) : dflt;
+}
+
+// L2 promotion of the TMA loads: 0 none, 1 64 B, 2 128 B, 3 256 B
+static int l2_promotion() {
+  static int v = -1;
+  if (v < 0) v = env_flag("EXAMG_TMA_L2PROMO", 1) & 3;
+  return v;
+}
+
+// planes prefetched into L2 ahead of the shared-memory ring
+static int tma_prefetch() {
+  static int v = -1;
+  if (v < 0) v = env_flag("EXAMG_TMA_PREFETCH", 0);
+  return v;
+}
+
 static int make_plane_map(const LevelGeom &g, const double *base, CUtensorMap *tm) {
   EncodeTiledFn fn = encode_fn();
   if (!fn) return set_error(EXAMG_ECUDA, "cuTensorMapEncodeTiled entry point not available");
@@ -309,7 +364,7 @@ static int make_plane_map(const LevelGeom &g, const double *base, CUtensorMap *t
   const cuuint32_t box[3] = {RW, RH, 1};
   const cuuint32_t estr[3] = {1, 1, 1};
   CUresult r = fn(tm, CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 3, const_cast<double *>(base), dims, strides, box, estr,
-                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, (CUtensorMapL2promotion)l2_promotion(),
                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) return set_error(EXAMG_ECUDA, "cuTensorMapEncodeTiled failed (%d)", (int)r);
   return EXAMG_OK;
@@ -328,11 +383,6 @@ static int stencil_order(const Stencil &s) {
     if (same) return o;
   }
   return -1;
-}
-
-static int env_flag(const char *name, int dflt) {
-  const char *e = getenv(name);
-  return e && e[0] ? atoi(e) : dflt;
 }
 
 static bool fused_enabled() {
@@ -399,8 +449,10 @@ static int launch_rbw(examg_ctx *c, const Stencil &s, double omega, Field &fu, c
   a.tiles_x = (g.n[0] + (RW - 2 * S) - 1) / (RW - 2 * S);
   const int tiles_y = (g.n[1] + (RH - 2 * S) - 1) / (RH - 2 * S);
   a.nzp = g.n[2];
-  a.units = (long long)a.tiles_x * tiles_y * a.nzp;
+  a.tiles = a.tiles_x * tiles_y;
+  const long long units = (long long)a.tiles * a.nzp;
   a.par = g.par;
+  a.pf = tma_prefetch();
   for (int k = 0; k < 7; ++k) a.coef[k] = s.coef[k];
   const int ord = stencil_order(s);
   a.w = omega / s.coef[s.centre];
@@ -409,7 +461,7 @@ static int launch_rbw(examg_ctx *c, const Stencil &s, double omega, Field &fu, c
   cudaDeviceGetAttribute(&nsm, cudaDevAttrMultiProcessorCount, dev);
   long long grid = nsm;
   const long long min_units = 6 * S;  // at least this many planes per CTA (2S are restart overhead)
-  if (grid > a.units / min_units) grid = a.units / min_units;
+  if (grid > units / min_units) grid = units / min_units;
   if (grid < 1) grid = 1;
   if (ord == 0)
     k_rbw<S, 0><<<(int)grid, RNT, rbw_smem<S>(), c->stream>>>(tm_u, tm_f, a, fu.shadow + g.origin);

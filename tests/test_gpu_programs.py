@@ -114,7 +114,8 @@ def test_benchmark_program_properties(oracle):
     """Benchmark/Poisson3D (config 2) at a size the oracle cannot check quickly:
     size-independent properties.  The Dirichlet data x^2 - y^2/2 - z^2/2 is harmonic and
     quadratic, so the 7-point discrete solution equals it: the error must fall to rounding
-    level and the residual must contract by > 10x per V(2,2) cycle."""
+    level and the residual must contract by > 4x per V(2,2) cycle (omega = 0.8 under-relaxes RBGS;
+    the oracle shows the same 5.5x, see test_vcycle_matches_oracle for the bit-level comparison)."""
     from exastencils_b200 import MultigridProgram, runtime as rt
     lvl = 7  # 129^3
     gpu = MultigridProgram(3, (1, 1, 1), 2, lvl, op="scaled", order="bench", smoother="rbgs", omega=0.8, nu_pre=2,
@@ -126,9 +127,9 @@ def test_benchmark_program_properties(oracle):
     gpu.ctx.field_set_bc_expr(f, prog)
     gpu.ctx.apply_bc(f)
     hist = gpu.Solve(max_it=20, target_reduction=1e-10)
-    assert len(hist) <= 12
+    assert len(hist) <= 16
     for a, b in zip(hist[:-2], hist[1:-1]):
-        assert b < 0.1 * a
+        assert b < 0.25 * a
     x, y, z = gpu.node_positions(lvl)
     exact = (x[None, None, :] ** 2 - 0.5 * y[None, :, None] ** 2) - 0.5 * z[:, None, None] ** 2
     assert np.max(np.abs(gpu.fetch_solution() - exact)) < 1e-9
