@@ -25,6 +25,7 @@ struct examg_solver {
   std::vector<int> stencils;          // per level
   std::vector<int> sol, rhs, res;     // field handles per level
   int cg_p = -1, cg_ap = -1;
+  int coarse_top = -1;                // mgCycle@level for level <= coarse_top is one single-CTA kernel
   bool use_graph = true;
   struct Graph { cudaGraphExec_t exec; long long launches; std::vector<int> exit_slots; };
   std::map<std::vector<int>, Graph> graphs;  // keyed by the active slots of Solution on entry
@@ -33,6 +34,10 @@ struct examg_solver {
 namespace examg {
 bool fused_rb_usable(examg_ctx *c, const Stencil &s, const Field &fu);
 int ensure_shadow(examg_ctx *c, Field &fu);
+// single-CTA coarse sub-cycle (examg_coarse.cu)
+int coarse_cycle_top(examg_ctx *c, const examg_cycle_desc &d, const int *stencils, const int *sol, int max_top);
+int launch_coarse_cycle(examg_ctx *c, const examg_cycle_desc &d, int top, const int *stencils, const int *sol,
+                        const int *rhs, const int *res, int cg_p, int cg_ap);
 }
 
 // (active slot, shadow parity) of a Solution field, as recorded in the graph keys
@@ -64,6 +69,9 @@ static int vcycle_rec(examg_solver *s, int level) {
   if (level == c->cfg.min_level)
     return examg_cg_coarse(c, s->stencils[l], s->sol[l], s->rhs[l], s->res[l], s->cg_p, s->cg_ap,
                            s->desc.cg_max_it, s->desc.cg_rel_tol, nullptr);
+  if (level <= s->coarse_top)
+    return launch_coarse_cycle(c, s->desc, level, s->stencils.data(), s->sol.data(), s->rhs.data(), s->res.data(),
+                               s->cg_p, s->cg_ap);
   int rc;
   if ((rc = smooth(s, level, s->desc.nu_pre))) return rc;
   if ((rc = examg_residual(c, s->stencils[l], s->sol[l], -1, s->rhs[l], s->res[l], nullptr))) return rc;
@@ -112,6 +120,7 @@ examg_solver *examg_solver_create(examg_ctx *c, const examg_cycle_desc *d) {
   s->cg_ap = examg_field_create(c, "cgTmp1", c->cfg.min_level, 1, 1);
   if (s->cg_p < 0 || s->cg_ap < 0) { delete s; return nullptr; }
   examg_field_set_bc(c, s->cg_p, EXAMG_BC_DIRICHLET_CONST, 0.0);
+  s->coarse_top = coarse_cycle_top(c, s->desc, s->stencils.data(), s->sol.data(), c->cfg.max_level);
   const char *ng = getenv("EXAMG_NO_GRAPH");
   s->use_graph = !(ng && ng[0] == '1');
   return s;

@@ -12,28 +12,11 @@
 // Reference loops these replace: Benchmark/Poisson3D/3D_FD_Poisson_fromL4.exa4:113-125,
 // 204-218; Testing/SISC/3D_VarCoeff.exa4 (Smoother, UpResidual); iteration space
 // C/s/e/baseExt/ir/IR_LoopOverPointsInOneFragment.scala:86-125.
-#include "examg_device.cuh"
+#include "examg_point_ops.cuh"
 
 namespace examg {
 
 enum { M_APPLY = 0, M_RESIDUAL = 1, M_RESNORM = 2, M_JACOBI = 3, M_RB = 4 };
-
-template <int NST, bool VAR>
-__device__ __forceinline__ double conv(const StencilArgs &st, const double *__restrict__ sf, long long sfvol,
-                                       const double *u, long long p) {
-  const int nst = NST > 0 ? NST : st.nst;
-  double acc;
-  if (VAR) {
-    acc = sf[p] * u[p + st.lin[0]];
-#pragma unroll
-    for (int k = 1; k < nst; ++k) acc = fma(sf[k * sfvol + p], u[p + st.lin[k]], acc);
-  } else {
-    acc = st.coef[0] * u[p + st.lin[0]];
-#pragma unroll
-    for (int k = 1; k < nst; ++k) acc = fma(st.coef[k], u[p + st.lin[k]], acc);
-  }
-  return acc;
-}
 
 // One kernel for the five loop shapes.  For M_RB, `u` and `out` alias.
 template <int MODE, int NST, bool VAR>

@@ -14,7 +14,7 @@
 //                 fine indices) in lexicographic (dz,dy,dx) order; uf = fma(2^-m, s, uf)
 #include <cstdlib>
 
-#include "examg_device.cuh"
+#include "examg_point_ops.cuh"
 
 namespace examg {
 
@@ -29,22 +29,7 @@ k_restrict(const GridArgs gc, int fpitch, long long fplane, double w0, double w1
   for (int j = gc.lo[1] + blockIdx.y * blockDim.y + threadIdx.y; j < gc.hi[1]; j += gridDim.y * blockDim.y)
     for (int k = z0; k < z1; ++k) {
       const long long q = 2 * i + (long long)fpitch * (2 * j) + (DIM == 3 ? fplane * (2 * k) : 0);
-      double S[4];
-      bool first[4] = {true, true, true, true};
-#pragma unroll
-      for (int dz = (DIM == 3 ? -1 : 0); dz <= (DIM == 3 ? 1 : 0); ++dz)
-#pragma unroll
-        for (int dy = -1; dy <= 1; ++dy)
-#pragma unroll
-          for (int dx = -1; dx <= 1; ++dx) {
-            const int m = (dx != 0) + (dy != 0) + (dz != 0);
-            const double v = rf[q + dx + (long long)fpitch * dy + fplane * dz];
-            if (first[m]) { S[m] = v; first[m] = false; } else S[m] += v;
-          }
-      double acc = w0 * S[0];
-      acc = fma(w1, S[1], acc);
-      acc = fma(w2, S[2], acc);
-      if (DIM == 3) acc = fma(w3, S[3], acc);
+      const double acc = restrict_point<DIM>(rf, q, fpitch, fplane, w0, w1, w2, w3);
       rhsc[i + (long long)gc.pitch * j + gc.plane * k] = acc;
     }
 }
@@ -56,28 +41,12 @@ k_prolong(const GridArgs gf, int cpitch, long long cplane, const double *__restr
   const int z0 = gf.lo[2] + blockIdx.z * kz;
   const int z1 = min(z0 + kz, gf.hi[2]);
   if (i >= gf.hi[0]) return;
-  const int ox = i & 1, ci = i >> 1;
-  for (int j = gf.lo[1] + blockIdx.y * blockDim.y + threadIdx.y; j < gf.hi[1]; j += gridDim.y * blockDim.y) {
-    const int oy = j & 1, cj = j >> 1;
+  for (int j = gf.lo[1] + blockIdx.y * blockDim.y + threadIdx.y; j < gf.hi[1]; j += gridDim.y * blockDim.y)
     for (int k = z0; k < z1; ++k) {
-      const int oz = DIM == 3 ? (k & 1) : 0, ck = DIM == 3 ? (k >> 1) : 0;
-      const long long q = ci + (long long)cpitch * cj + cplane * ck;
-      double s = 0.0;
-      bool first = true;
-      for (int dz = 0; dz <= oz; ++dz)
-        for (int dy = 0; dy <= oy; ++dy)
-          for (int dx = 0; dx <= ox; ++dx) {
-            const double v = uc[q + dx + (long long)cpitch * dy + cplane * dz];
-            if (first) { s = v; first = false; } else s += v;
-          }
-      const int m = ox + oy + oz;
-      const double wgt = m == 0 ? 1.0 : (m == 1 ? 0.5 : (m == 2 ? 0.25 : 0.125));
       const long long p = i + (long long)gf.pitch * j + gf.plane * k;
-      uf[p] = fma(wgt, s, uf[p]);
+      uf[p] = prolong_point<DIM>(uc, cpitch, cplane, i, j, k, uf[p]);
     }
-  }
 }
-
 
 // 3D fast path of the prolongation: one thread per coarse cell (ci, cj) marching over coarse
 // planes; it owns the 2x2 fine points (2ci..2ci+1, 2cj..2cj+1) of the fine planes 2ck and 2ck+1,
