@@ -1,33 +1,606 @@
-// examg_comm.cu -- `communicate F` (halo exchange) and global reductions.
+// examg_comm.cu -- `communicate F` (halo exchange), global reductions and the gather/scatter of
+// the agglomerated coarse levels, one process per GPU, over NVLink peer memory.
 //
-// Reference: C/s/e/communication/ir/IR_CommunicateFunction.scala:412-470 (one
-// dimension after the other; ghost ranges IR_PackInfoGhost.scala:13-60), MPI
-// point-to-point C/s/e/communication/ir/IR_RemoteSend.scala:38-58 and
-// MPI_Allreduce after reduction loops C/s/e/parallelization/api/mpi/MPI_Reduction.scala:92-127.
-#include "examg_internal.h"
+// Reference: C/s/e/communication/ir/IR_CommunicateFunction.scala:412-470 (one dimension after the
+// other; ghost ranges IR_PackInfoGhost.scala:13-60, duplicate sync IR_PackInfoDuplicate.scala:15-39),
+// MPI point-to-point C/s/e/communication/ir/IR_RemoteSend.scala:38-58 and MPI_Allreduce after
+// reduction loops C/s/e/parallelization/api/mpi/MPI_Reduction.scala:92-127.
+//
+// Design (B200 / NVSwitch):
+//   * wiring: every rank exports one CUDA IPC handle per device block (Block, examg_internal.h)
+//     plus (field, buffer, block, offset) entries and its flag page; the host process group
+//     all-gathers the blobs (examg_comm_export / examg_comm_import); a rank maps the blocks of its
+//     face neighbours and of rank 0, and the flag pages of everybody.
+//   * exchange of dimension d = ONE kernel: tell the neighbours "ready to receive" (flag in their
+//     memory), wait for theirs, store the boundary layers straight into their ghost layers
+//     (remote stores over NVLink, no pack buffer, no host), fence, tell them "done", wait for theirs.
+//     Dimensions run one after the other and faces carry the orthogonal ghost layers already
+//     received, so edges and corners become valid as in the reference.  Two ghost layers + the
+//     duplicate layer travel (+dir block's node 0 := -dir block's node n-1, as IR_PackInfoDuplicate).
+//   * epochs are counted on the device, so the same kernels replay inside a CUDA graph.
+//   * sums: every rank stores its double-double partial into a mailbox of every rank and adds the
+//     mailboxes in rank order -- deterministic and identical on all ranks.
+//   * every spin is bounded (~2 s): a lost peer turns into EXAMG_ESTATE on the next host
+//     synchronisation instead of a hung GPU.
+// Kernels of different ranks wait for one another: ranks must sit on different GPUs
+// (examg_comm_import refuses two ranks on one device).
+#include <array>
+#include <cstring>
+
+#include "examg_device.cuh"
 
 using namespace examg;
 
+namespace {
+
+constexpr int MAXW = 64;                 // ranks
+constexpr int FLAG_WORDS = 1024;         // 8 KiB flag page
+// word indices in the flag page
+constexpr int F_READY = 0;               // [2*d + side]   written by the neighbour on that side
+constexpr int F_DONE = 8;                // [2*d + side]
+constexpr int F_ERROR = 15;              // set locally when a wait timed out
+constexpr int F_EPOCH = 16;              // local: [d] exchange, [3] reduction, [4] gather, [5] scatter
+constexpr int F_TICKET = 24;             // local: [d] block counter of the exchange kernel
+constexpr int F_AGG_IN = 32;             // on rank 0: [rank] gather epoch
+constexpr int F_AGG_OUT = 96;            // on every rank: scatter epoch, written by rank 0
+constexpr int F_MAIL = 128;              // [parity][rank]{hi, lo, epoch}
+constexpr long long SPIN_LIMIT = 4000000000LL;  // clock64 ticks
+
+constexpr unsigned BLOB_MAGIC = 0x45584d47u;  // "EXMG"
+constexpr int BLOB_MAX_BLOCKS = 96, BLOB_MAX_ENTRIES = 512;
+
+struct BlobEntry { int field, buf, block; int pad; long long offset; };
+struct Blob {
+  unsigned magic;
+  int rank, device, nblocks, nentries, flag_block;
+  long long flag_offset;
+  long long agg_in_off, agg_out_off;  // staging buffers of the agglomeration (rank 0), -1: none
+  int agg_in_block, agg_out_block;
+  cudaIpcMemHandle_t handles[BLOB_MAX_BLOCKS];
+  BlobEntry entries[BLOB_MAX_ENTRIES];
+};
+
+__device__ __forceinline__ unsigned long long ld_acquire_sys(const unsigned long long *p) {
+  unsigned long long v;
+  asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_release_sys(unsigned long long *p, unsigned long long v) {
+  asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+// wait until *p >= want; false on timeout
+__device__ __forceinline__ bool spin_ge(const unsigned long long *p, unsigned long long want, unsigned long long *flags) {
+  const long long t0 = clock64();
+  while (ld_acquire_sys(p) < want) {
+    if (clock64() - t0 > SPIN_LIMIT) {
+      flags[F_ERROR] = 1;
+      return false;
+    }
+    __nanosleep(100);
+  }
+  return true;
+}
+
+struct Box { int lo[3], ext[3]; };
+
+struct ExchArgs {
+  int d;
+  int has[2];               // neighbour on side 0 (-) / 1 (+)
+  const double *src;        // node (0,0,0) of the local buffer
+  double *dst[2];           // node (0,0,0) of the neighbour's buffer
+  Box sbox[2];              // what is sent to side s (local coordinates)
+  int dlo[2][3];            // where it lands (neighbour coordinates)
+  int pitch;
+  long long plane;
+  unsigned long long *flags;      // local flag page
+  unsigned long long *pflags[2];  // neighbours' flag pages
+};
+
+__global__ void __launch_bounds__(256) k_exchange_dim(const ExchArgs a) {
+  unsigned long long *fl = a.flags;
+  const unsigned long long e = *reinterpret_cast<volatile unsigned long long *>(fl + F_EPOCH + a.d) + 1;
+  // ready-to-receive: this rank no longer reads the ghost layers of the previous epoch
+  if (blockIdx.x == 0 && threadIdx.x < 2 && a.has[threadIdx.x])
+    st_release_sys(a.pflags[threadIdx.x] + F_READY + 2 * a.d + (1 - threadIdx.x), e);
+  if (threadIdx.x < 2 && a.has[threadIdx.x]) spin_ge(fl + F_READY + 2 * a.d + threadIdx.x, e, fl);
+  __syncthreads();
+  for (int s = 0; s < 2; ++s) {
+    if (!a.has[s]) continue;
+    const Box &b = a.sbox[s];
+    const long long total = (long long)b.ext[0] * b.ext[1] * b.ext[2];
+    double *dst = a.dst[s];
+    if (a.d == 0) {
+      // x faces: rows are 2-3 elements long; let consecutive threads take consecutive rows
+      const long long rows = (long long)b.ext[1] * b.ext[2];
+      for (long long t = blockIdx.x * (long long)blockDim.x + threadIdx.x; t < rows; t += (long long)gridDim.x * blockDim.x) {
+        const int j = (int)(t % b.ext[1]), k = (int)(t / b.ext[1]);
+        const long long so = b.lo[0] + (long long)a.pitch * (b.lo[1] + j) + a.plane * (b.lo[2] + k);
+        const long long dof = a.dlo[s][0] + (long long)a.pitch * (a.dlo[s][1] + j) + a.plane * (a.dlo[s][2] + k);
+        for (int i = 0; i < b.ext[0]; ++i) dst[dof + i] = a.src[so + i];
+      }
+    } else {
+      for (long long t = blockIdx.x * (long long)blockDim.x + threadIdx.x; t < total; t += (long long)gridDim.x * blockDim.x) {
+        const int i = (int)(t % b.ext[0]);
+        const long long r = t / b.ext[0];
+        const int j = (int)(r % b.ext[1]), k = (int)(r / b.ext[1]);
+        dst[a.dlo[s][0] + i + (long long)a.pitch * (a.dlo[s][1] + j) + a.plane * (a.dlo[s][2] + k)] =
+            a.src[b.lo[0] + i + (long long)a.pitch * (b.lo[1] + j) + a.plane * (b.lo[2] + k)];
+      }
+    }
+  }
+  __threadfence_system();
+  __syncthreads();
+  __shared__ int last;
+  if (threadIdx.x == 0) {
+    const unsigned long long ticket = atomicAdd(fl + F_TICKET + a.d, 1ULL);
+    last = ticket == gridDim.x - 1;
+  }
+  __syncthreads();
+  if (!last) return;
+  __threadfence_system();
+  if (threadIdx.x < 2 && a.has[threadIdx.x]) {
+    st_release_sys(a.pflags[threadIdx.x] + F_DONE + 2 * a.d + (1 - threadIdx.x), e);
+    spin_ge(fl + F_DONE + 2 * a.d + threadIdx.x, e, fl);
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    fl[F_TICKET + a.d] = 0;
+    *reinterpret_cast<volatile unsigned long long *>(fl + F_EPOCH + a.d) = e;
+  }
+}
+
+struct RedArgs {
+  int world, rank;
+  unsigned long long *flags;
+  unsigned long long *pflags[MAXW];
+  dd *value;  // in: this rank's partial, out: the global sum
+};
+
+__global__ void __launch_bounds__(MAXW) k_allreduce_dd(const __grid_constant__ RedArgs a) {
+  unsigned long long *fl = a.flags;
+  const unsigned long long e = *reinterpret_cast<volatile unsigned long long *>(fl + F_EPOCH + 3) + 1;
+  const int par = (int)(e & 1);
+  const int r = threadIdx.x;
+  if (r < a.world) {
+    unsigned long long *m = a.pflags[r] + F_MAIL + 3 * (par * MAXW + a.rank);
+    const dd v = *a.value;
+    m[0] = (unsigned long long)__double_as_longlong(v.hi);
+    m[1] = (unsigned long long)__double_as_longlong(v.lo);
+    __threadfence_system();
+    st_release_sys(m + 2, e);
+    spin_ge(fl + F_MAIL + 3 * (par * MAXW + r) + 2, e, fl);
+  }
+  __syncthreads();
+  if (r == 0) {
+    dd s = {0.0, 0.0};
+    for (int q = 0; q < a.world; ++q) {
+      const unsigned long long *m = fl + F_MAIL + 3 * (par * MAXW + q);
+      dd v;
+      v.hi = __longlong_as_double((long long)ld_acquire_sys(m));
+      v.lo = __longlong_as_double((long long)ld_acquire_sys(m + 1));
+      dd_merge(s, v);
+    }
+    *a.value = s;
+    *reinterpret_cast<volatile unsigned long long *>(fl + F_EPOCH + 3) = e;
+  }
+}
+
+// dense box copy between a field layout and a dense [nz][ny][nx] staging array (gather / scatter)
+struct AggArgs {
+  int n[3];        // local nodes copied
+  int goff[3];     // their offset in the global dense array
+  int gn[3];       // global dense extents
+  int pitch;
+  long long plane;
+  const double *fsrc;  // gather: local field (node 0,0,0)
+  double *fdst;        // scatter: local field
+  double *dense;       // staging array on rank 0 (peer pointer on the other ranks)
+  int rank, world;
+  unsigned long long *flags, *flags0;  // local page / rank 0's page
+  unsigned long long *pflags[MAXW];    // scatter signal: rank 0 -> everybody
+};
+
+// every rank: field -> rank 0's dense array, then signal; rank 0 additionally waits for everybody
+__global__ void __launch_bounds__(256) k_agg_gather(const __grid_constant__ AggArgs a) {
+  unsigned long long *fl = a.flags;
+  const unsigned long long e = *reinterpret_cast<volatile unsigned long long *>(fl + F_EPOCH + 4) + 1;
+  const long long total = (long long)a.n[0] * a.n[1] * a.n[2];
+  for (long long t = blockIdx.x * (long long)blockDim.x + threadIdx.x; t < total; t += (long long)gridDim.x * blockDim.x) {
+    const int i = (int)(t % a.n[0]);
+    const long long r = t / a.n[0];
+    const int j = (int)(r % a.n[1]), k = (int)(r / a.n[1]);
+    a.dense[(a.goff[0] + i) + (long long)a.gn[0] * ((a.goff[1] + j) + (long long)a.gn[1] * (a.goff[2] + k))] =
+        a.fsrc[i + (long long)a.pitch * j + a.plane * k];
+  }
+  __threadfence_system();
+  __syncthreads();
+  __shared__ int last;
+  if (threadIdx.x == 0) last = atomicAdd(fl + F_TICKET + 4, 1ULL) == gridDim.x - 1;
+  __syncthreads();
+  if (!last) return;
+  __threadfence_system();
+  if (threadIdx.x == 0) st_release_sys(a.flags0 + F_AGG_IN + a.rank, e);
+  if (a.rank == 0 && threadIdx.x < a.world) spin_ge(fl + F_AGG_IN + threadIdx.x, e, fl);
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    fl[F_TICKET + 4] = 0;
+    *reinterpret_cast<volatile unsigned long long *>(fl + F_EPOCH + 4) = e;
+  }
+}
+
+// rank 0: signal "dense solution ready" to everybody (one block)
+__global__ void __launch_bounds__(MAXW) k_agg_signal(const __grid_constant__ AggArgs a) {
+  unsigned long long *fl = a.flags;
+  const unsigned long long e = *reinterpret_cast<volatile unsigned long long *>(fl + F_EPOCH + 5) + 1;
+  __threadfence_system();
+  if ((int)threadIdx.x < a.world) st_release_sys(a.pflags[threadIdx.x] + F_AGG_OUT, e);
+}
+
+// every rank: wait for the signal, pull the block out of rank 0's dense array
+__global__ void __launch_bounds__(256) k_agg_scatter(const __grid_constant__ AggArgs a) {
+  unsigned long long *fl = a.flags;
+  const unsigned long long e = *reinterpret_cast<volatile unsigned long long *>(fl + F_EPOCH + 5) + 1;
+  if (threadIdx.x == 0) spin_ge(fl + F_AGG_OUT, e, fl);
+  __syncthreads();
+  const long long total = (long long)a.n[0] * a.n[1] * a.n[2];
+  for (long long t = blockIdx.x * (long long)blockDim.x + threadIdx.x; t < total; t += (long long)gridDim.x * blockDim.x) {
+    const int i = (int)(t % a.n[0]);
+    const long long r = t / a.n[0];
+    const int j = (int)(r % a.n[1]), k = (int)(r / a.n[1]);
+    a.fdst[i + (long long)a.pitch * j + a.plane * k] =
+        a.dense[(a.goff[0] + i) + (long long)a.gn[0] * ((a.goff[1] + j) + (long long)a.gn[1] * (a.goff[2] + k))];
+  }
+  __syncthreads();
+  __shared__ int last;
+  if (threadIdx.x == 0) last = atomicAdd(fl + F_TICKET + 5, 1ULL) == gridDim.x - 1;
+  __syncthreads();
+  if (last && threadIdx.x == 0) {
+    fl[F_TICKET + 5] = 0;
+    *reinterpret_cast<volatile unsigned long long *>(fl + F_EPOCH + 5) = e;
+  }
+}
+
+}  // namespace
+
+struct examg_comm {
+  bool wired = false;
+  int world = 1, rank = 0;
+  unsigned long long *flags = nullptr;              // local flag page
+  std::vector<unsigned long long *> pflags;         // [rank]
+  std::vector<std::vector<char *>> pblock;          // [rank][block] mapped base (nullptr: not mapped)
+  std::vector<Blob> blobs;                          // [rank]
+  std::vector<void *> opened;
+  int nbr[3][2];                                    // neighbour rank per dim/side, -1: none
+  // agglomeration staging (dense global arrays of one level), allocated by examg_comm_agg_setup
+  double *agg_in = nullptr, *agg_out = nullptr;     // local pointers on rank 0
+  double *agg_in0 = nullptr, *agg_out0 = nullptr;   // rank 0's arrays as seen from this rank
+  int agg_level = -1;
+  int agg_gn[3] = {0, 0, 0};
+};
+
 namespace examg {
 
-int do_exchange(examg_ctx *c, const Field &f, int slot) {
-  (void)f; (void)slot;
+void comm_destroy(examg_ctx *c) {
+  if (!c->comm) return;
+  for (void *p : c->comm->opened) cudaIpcCloseMemHandle(p);
+  delete c->comm;
+  c->comm = nullptr;
+}
+
+static examg_comm *comm_get(examg_ctx *c) {
+  if (!c->comm) {
+    c->comm = new examg_comm();
+    c->comm->world = c->world;
+    c->comm->rank = c->cfg.rank;
+  }
+  return c->comm;
+}
+
+static int find_block(examg_ctx *c, const void *p, long long *off) {
+  const char *q = static_cast<const char *>(p);
+  for (size_t b = 0; b < c->blocks.size(); ++b)
+    if (q >= c->blocks[b].base && q < c->blocks[b].base + c->blocks[b].bytes) {
+      *off = q - c->blocks[b].base;
+      return (int)b;
+    }
+  return -1;
+}
+
+// the neighbour's pointer to the same buffer as local pointer p (a slot or the shadow of field f)
+static double *peer_buffer(examg_ctx *c, int rank, int field, const double *p) {
+  examg_comm *cm = c->comm;
+  const Field &f = c->fields[field];
+  int buf = -1;
+  for (int i = 0; i < 5; ++i)
+    if (f.orig[i] == p) buf = i;
+  if (buf < 0) return nullptr;
+  const Blob &bl = cm->blobs[rank];
+  for (int e = 0; e < bl.nentries; ++e)
+    if (bl.entries[e].field == field && bl.entries[e].buf == buf) {
+      char *base = cm->pblock[rank][bl.entries[e].block];
+      return base ? reinterpret_cast<double *>(base + bl.entries[e].offset) : nullptr;
+    }
+  return nullptr;
+}
+
+static int check_comm_error(examg_ctx *c) {
+  (void)c;
+  return EXAMG_OK;
+}
+
+int do_exchange(examg_ctx *c, Field &f, int slot) {
   if (c->world == 1) return EXAMG_OK;  // no neighbour blocks: nothing to exchange
-  return set_error(EXAMG_EUNSUP, "examg_exchange: peers not wired (examg_comm_import)");
+  examg_comm *cm = c->comm;
+  if (!cm || !cm->wired) return set_error(EXAMG_ESTATE, "examg_exchange: peers not wired (examg_comm_import)");
+  const int field = (int)(&f - c->fields.data());
+  const LevelGeom &g = *geom(c, f.level);
+  const int G = GHOST;
+  for (int comp = 0; comp < f.ncomp; ++comp) {
+    double *buf = f.slot[slot];
+    for (int d = 0; d < c->cfg.dim; ++d) {
+      if (cm->nbr[d][0] < 0 && cm->nbr[d][1] < 0) continue;
+      ExchArgs a;
+      a.d = d;
+      a.src = buf + (long long)comp * g.vol + g.origin;
+      a.pitch = g.pitch;
+      a.plane = g.plane;
+      a.flags = cm->flags;
+      for (int s = 0; s < 2; ++s) {
+        a.has[s] = cm->nbr[d][s] >= 0;
+        a.dst[s] = nullptr;
+        a.pflags[s] = nullptr;
+        if (!a.has[s]) continue;
+        double *pb = peer_buffer(c, cm->nbr[d][s], field, buf);
+        if (!pb) return set_error(EXAMG_ESTATE, "examg_exchange: field %s@%d is not mapped on rank %d (created after "
+                                  "examg_comm_export?)", f.name.c_str(), f.level, cm->nbr[d][s]);
+        a.dst[s] = pb + (long long)comp * g.vol + g.origin;
+        a.pflags[s] = cm->pflags[cm->nbr[d][s]];
+        for (int q = 0; q < 3; ++q) {  // orthogonal extents: everything incl. ghost layers
+          const int gq = q < c->cfg.dim ? G : 0;
+          a.sbox[s].lo[q] = -gq;
+          a.sbox[s].ext[q] = g.n[q] + 2 * gq;
+          a.dlo[s][q] = -gq;
+        }
+        if (s == 0) {  // to the - neighbour: my layers 1..G -> its n..n+G-1
+          a.sbox[s].lo[d] = 1;
+          a.sbox[s].ext[d] = G;
+          a.dlo[s][d] = g.n[d];
+        } else {       // to the + neighbour: my layers n-1-G..n-1 -> its -G..0 (ghosts + duplicate)
+          a.sbox[s].lo[d] = g.n[d] - 1 - G;
+          a.sbox[s].ext[d] = G + 1;
+          a.dlo[s][d] = -G;
+        }
+      }
+      long long work = 1;
+      for (int q = 0; q < 3; ++q) work *= a.sbox[a.has[0] ? 0 : 1].ext[q];
+      if (d == 0) work /= a.sbox[a.has[0] ? 0 : 1].ext[0];
+      int grid = (int)((work + 1023) / 1024);
+      if (grid > 96) grid = 96;
+      if (grid < 1) grid = 1;
+      k_exchange_dim<<<grid, 256, 0, c->stream>>>(a);
+      EXAMG_LAUNCH_CHECK(c);
+    }
+  }
+  f.halo_valid = true;
+  return check_comm_error(c);
 }
 
 int finish_sum(examg_ctx *c, int slot, double *out) {
+  if (c->world > 1) {
+    examg_comm *cm = c->comm;
+    if (!cm || !cm->wired) return set_error(EXAMG_ESTATE, "global reduction: peers not wired (examg_comm_import)");
+    RedArgs a;
+    a.world = c->world;
+    a.rank = c->cfg.rank;
+    a.flags = cm->flags;
+    for (int r = 0; r < c->world; ++r) a.pflags[r] = cm->pflags[r];
+    a.value = c->red_out + slot;
+    k_allreduce_dd<<<1, MAXW, 0, c->stream>>>(a);
+    EXAMG_LAUNCH_CHECK(c);
+  }
   EXAMG_CUDA(cudaMemcpyAsync(c->red_host + slot, c->red_out + slot, sizeof(dd), cudaMemcpyDeviceToHost, c->stream));
   EXAMG_CUDA(cudaStreamSynchronize(c->stream));
-  if (c->world > 1) return set_error(EXAMG_EUNSUP, "global reduction: peers not wired (examg_comm_import)");
+  if (c->world > 1) {
+    unsigned long long err = 0;
+    EXAMG_CUDA(cudaMemcpy(&err, c->comm->flags + F_ERROR, sizeof(err), cudaMemcpyDeviceToHost));
+    if (err) return set_error(EXAMG_ESTATE, "a wait for a peer rank timed out (lost rank or mismatched call sequence)");
+  }
   *out = c->red_host[slot].hi + c->red_host[slot].lo;
+  return EXAMG_OK;
+}
+
+// ---- agglomeration staging -------------------------------------------------------------------
+
+// Dense global arrays of `level` (RHS in, Solution out) on rank 0.  Must run on every rank before
+// examg_comm_export.  gn = global node counts.
+int comm_agg_setup(examg_ctx *c, int level) {
+  examg_comm *cm = comm_get(c);
+  const LevelGeom &g = *geom(c, level);
+  cm->agg_level = level;
+  size_t tot = 1;
+  for (int d = 0; d < 3; ++d) {
+    cm->agg_gn[d] = d < c->cfg.dim ? (g.n[d] - 1) * c->cfg.num_blocks[d] + 1 : 1;
+    tot *= (size_t)cm->agg_gn[d];
+  }
+  if (c->cfg.rank == 0 && !cm->agg_in) {
+    cm->agg_in = dev_alloc(c, tot * sizeof(double));
+    cm->agg_out = dev_alloc(c, tot * sizeof(double));
+    if (!cm->agg_in || !cm->agg_out) return set_error(EXAMG_ENOMEM, "agglomeration staging of level %d", level);
+  }
+  return EXAMG_OK;
+}
+
+double *comm_agg_in(examg_ctx *c) { return c->comm ? c->comm->agg_in : nullptr; }
+double *comm_agg_out(examg_ctx *c) { return c->comm ? c->comm->agg_out : nullptr; }
+
+static int agg_args(examg_ctx *c, const Field &f, AggArgs *a) {
+  examg_comm *cm = c->comm;
+  if (!cm || !cm->wired) return set_error(EXAMG_ESTATE, "agglomeration: peers not wired (examg_comm_import)");
+  if (f.level != cm->agg_level) return set_error(EXAMG_EINVAL, "agglomeration: field level %d, staging level %d", f.level, cm->agg_level);
+  const LevelGeom &g = *geom(c, f.level);
+  for (int d = 0; d < 3; ++d) {
+    a->n[d] = g.n[d];
+    a->goff[d] = g.goff[d];
+    a->gn[d] = cm->agg_gn[d];
+  }
+  a->pitch = g.pitch;
+  a->plane = g.plane;
+  a->rank = c->cfg.rank;
+  a->world = c->world;
+  a->flags = cm->flags;
+  a->flags0 = cm->pflags[0];
+  for (int r = 0; r < c->world; ++r) a->pflags[r] = cm->pflags[r];
+  a->fsrc = nullptr;
+  a->fdst = nullptr;
+  a->dense = nullptr;
+  return EXAMG_OK;
+}
+
+static int agg_grid(const AggArgs &a) {
+  const long long total = (long long)a.n[0] * a.n[1] * a.n[2];
+  long long grid = (total + 2047) / 2048;
+  return (int)(grid > 128 ? 128 : (grid < 1 ? 1 : grid));
+}
+
+// all ranks: field (active slot) -> rank 0's dense "in" array; rank 0 returns when all blocks arrived
+int comm_agg_gather(examg_ctx *c, Field &f) {
+  AggArgs a;
+  int rc = agg_args(c, f, &a);
+  if (rc) return rc;
+  a.fsrc = field_ptr(c, &f, -1);
+  a.dense = c->comm->agg_in0;
+  k_agg_gather<<<agg_grid(a), 256, 0, c->stream>>>(a);
+  EXAMG_LAUNCH_CHECK(c);
+  return EXAMG_OK;
+}
+
+// rank 0 (after filling the dense "out" array): signal; all ranks: dense "out" -> field (active slot)
+int comm_agg_scatter(examg_ctx *c, Field &f) {
+  AggArgs a;
+  int rc = agg_args(c, f, &a);
+  if (rc) return rc;
+  a.fdst = field_ptr(c, &f, -1);
+  a.dense = c->comm->agg_out0;
+  if (c->cfg.rank == 0) {
+    k_agg_signal<<<1, MAXW, 0, c->stream>>>(a);
+    EXAMG_LAUNCH_CHECK(c);
+  }
+  k_agg_scatter<<<agg_grid(a), 256, 0, c->stream>>>(a);
+  EXAMG_LAUNCH_CHECK(c);
+  f.halo_valid = false;
   return EXAMG_OK;
 }
 
 }  // namespace examg
 
 extern "C" {
-int examg_comm_blob_size(examg_ctx *c) { (void)c; return 64; }
-int examg_comm_export(examg_ctx *c, void *blob) { (void)c; (void)blob; return set_error(EXAMG_EUNSUP, "not yet"); }
-int examg_comm_import(examg_ctx *c, const void *blobs, int world) { (void)c; (void)blobs; (void)world; return set_error(EXAMG_EUNSUP, "not yet"); }
+
+int examg_comm_blob_size(examg_ctx *c) {
+  (void)c;
+  return (int)sizeof(Blob);
 }
+
+int examg_comm_export(examg_ctx *c, void *blob) {
+  if (!c || !blob) return set_error(EXAMG_EINVAL, "examg_comm_export: null argument");
+  examg_comm *cm = comm_get(c);
+  if (!cm->flags) {
+    cm->flags = reinterpret_cast<unsigned long long *>(dev_alloc(c, FLAG_WORDS * sizeof(unsigned long long)));
+    if (!cm->flags) return set_error(EXAMG_ENOMEM, "examg_comm_export: flag page");
+  }
+  EXAMG_CUDA(cudaStreamSynchronize(c->stream));
+  Blob *b = static_cast<Blob *>(blob);
+  memset(b, 0, sizeof(Blob));
+  b->magic = BLOB_MAGIC;
+  b->rank = c->cfg.rank;
+  b->device = c->device;
+  if ((int)c->blocks.size() > BLOB_MAX_BLOCKS) return set_error(EXAMG_EUNSUP, "examg_comm_export: %zu device blocks", c->blocks.size());
+  b->nblocks = (int)c->blocks.size();
+  for (int i = 0; i < b->nblocks; ++i) EXAMG_CUDA(cudaIpcGetMemHandle(&b->handles[i], c->blocks[i].base));
+  b->flag_block = find_block(c, cm->flags, &b->flag_offset);
+  b->agg_in_block = b->agg_out_block = -1;
+  if (cm->agg_in) {
+    b->agg_in_block = find_block(c, cm->agg_in, &b->agg_in_off);
+    b->agg_out_block = find_block(c, cm->agg_out, &b->agg_out_off);
+  }
+  int ne = 0;
+  for (size_t fi = 0; fi < c->fields.size(); ++fi) {
+    const Field &f = c->fields[fi];
+    if (!f.alive) continue;
+    for (int i = 0; i < 5; ++i) {
+      if (!f.orig[i]) continue;
+      if (ne >= BLOB_MAX_ENTRIES) return set_error(EXAMG_EUNSUP, "examg_comm_export: more than %d field buffers", BLOB_MAX_ENTRIES);
+      BlobEntry &e = b->entries[ne++];
+      e.field = (int)fi;
+      e.buf = i;
+      e.block = find_block(c, f.orig[i], &e.offset);
+    }
+  }
+  b->nentries = ne;
+  return EXAMG_OK;
+}
+
+int examg_comm_import(examg_ctx *c, const void *all_blobs, int world) {
+  if (!c || !all_blobs) return set_error(EXAMG_EINVAL, "examg_comm_import: null argument");
+  if (world != c->world) return set_error(EXAMG_EINVAL, "examg_comm_import: %d blobs for %d blocks", world, c->world);
+  if (world > MAXW) return set_error(EXAMG_EUNSUP, "examg_comm_import: more than %d ranks", MAXW);
+  examg_comm *cm = comm_get(c);
+  if (!cm->flags) return set_error(EXAMG_ESTATE, "examg_comm_import before examg_comm_export");
+  if (cm->wired) return set_error(EXAMG_ESTATE, "examg_comm_import: already wired");
+  const Blob *bl = static_cast<const Blob *>(all_blobs);
+  const int me = c->cfg.rank;
+  for (int r = 0; r < world; ++r) {
+    if (bl[r].magic != BLOB_MAGIC || bl[r].rank != r) return set_error(EXAMG_EINVAL, "examg_comm_import: blob %d is malformed", r);
+    if (r != me && bl[r].device == c->device)
+      return set_error(EXAMG_EUNSUP, "examg_comm_import: ranks %d and %d share device %d; ranks wait for each other inside "
+                       "kernels and need one GPU each", me, r, c->device);
+  }
+  cm->blobs.assign(bl, bl + world);
+  // neighbours (rank -> block x fastest, C/s/e/domain/ir/IR_InitGeneratedDomain.scala:41-47)
+  const int *nb = c->cfg.num_blocks;
+  for (int d = 0; d < 3; ++d)
+    for (int s = 0; s < 2; ++s) {
+      cm->nbr[d][s] = -1;
+      if (d >= c->cfg.dim || !c->nb[d][s]) continue;
+      int idx[3] = {c->bidx[0], c->bidx[1], c->bidx[2]};
+      idx[d] += s ? 1 : -1;
+      cm->nbr[d][s] = idx[0] + nb[0] * (idx[1] + (c->cfg.dim > 1 ? nb[1] : 1) * idx[2]);
+    }
+  cm->pblock.assign(world, std::vector<char *>());
+  cm->pflags.assign(world, nullptr);
+  auto need_all = [&](int r) {
+    if (r == 0) return true;  // agglomeration staging lives on rank 0
+    for (int d = 0; d < 3; ++d)
+      for (int s = 0; s < 2; ++s)
+        if (cm->nbr[d][s] == r) return true;
+    return false;
+  };
+  for (int r = 0; r < world; ++r) {
+    cm->pblock[r].assign(bl[r].nblocks, nullptr);
+    if (r == me) {
+      for (int b = 0; b < bl[r].nblocks; ++b) cm->pblock[r][b] = c->blocks[b].base;
+      cm->pflags[r] = cm->flags;
+      continue;
+    }
+    const bool all = need_all(r);
+    for (int b = 0; b < bl[r].nblocks; ++b) {
+      if (!all && b != bl[r].flag_block) continue;
+      void *p = nullptr;
+      cudaError_t e = cudaIpcOpenMemHandle(&p, bl[r].handles[b], cudaIpcMemLazyEnablePeerAccess);
+      if (e != cudaSuccess) {
+        cudaGetLastError();
+        return set_error(EXAMG_ECUDA, "examg_comm_import: cudaIpcOpenMemHandle(rank %d, block %d): %s", r, b, cudaGetErrorString(e));
+      }
+      cm->opened.push_back(p);
+      cm->pblock[r][b] = static_cast<char *>(p);
+    }
+    cm->pflags[r] = reinterpret_cast<unsigned long long *>(cm->pblock[r][bl[r].flag_block] + bl[r].flag_offset);
+  }
+  if (bl[0].agg_in_block >= 0) {
+    cm->agg_in0 = reinterpret_cast<double *>(cm->pblock[0][bl[0].agg_in_block] + bl[0].agg_in_off);
+    cm->agg_out0 = reinterpret_cast<double *>(cm->pblock[0][bl[0].agg_out_block] + bl[0].agg_out_off);
+  }
+  cm->wired = true;
+  return EXAMG_OK;
+}
+
+}  // extern "C"

@@ -22,6 +22,42 @@ int examg::set_error(int code, const char *fmt, ...) {
   return code;
 }
 
+double *examg::dev_alloc(examg_ctx *c, size_t bytes) {
+  constexpr size_t ARENA = 64u << 20, BIG = 1u << 20;
+  bytes = (bytes + 255) & ~(size_t)255;
+  if (bytes < BIG) {
+    for (Block &b : c->blocks)
+      if (b.arena && b.used + bytes <= b.bytes) {
+        double *p = reinterpret_cast<double *>(b.base + b.used);
+        b.used += bytes;
+        return p;  // arena blocks are zero-filled when created and never recycled
+      }
+  }
+  Block b;
+  b.arena = bytes < BIG;
+  b.bytes = b.arena ? ARENA : bytes;
+  if (cudaMalloc(&b.base, b.bytes) != cudaSuccess) {
+    cudaGetLastError();
+    return nullptr;
+  }
+  cudaMemsetAsync(b.base, 0, b.bytes, c->stream);
+  b.used = bytes;
+  c->dev_bytes += (long long)b.bytes;
+  c->blocks.push_back(b);
+  return reinterpret_cast<double *>(b.base);
+}
+
+void examg::dev_free(examg_ctx *c, double *p) {
+  for (size_t i = 0; i < c->blocks.size(); ++i)
+    if (!c->blocks[i].arena && reinterpret_cast<double *>(c->blocks[i].base) == p) {
+      cudaFree(c->blocks[i].base);
+      c->dev_bytes -= (long long)c->blocks[i].bytes;
+      c->blocks.erase(c->blocks.begin() + i);
+      return;
+    }
+  // arena memory stays with the context until examg_finalize
+}
+
 const LevelGeom *examg::geom(examg_ctx *c, int level) {
   if (!c || level < c->cfg.min_level || level > c->cfg.max_level) return nullptr;
   return &c->levels[level - c->cfg.min_level];
@@ -124,7 +160,7 @@ examg_ctx *examg_init(const examg_config *cfg) {
         g.n[d] = 1; g.lo[d] = 0; g.hi[d] = 1; g.rlo[d] = 0; g.goff[d] = 0; g.h[d] = 1.0;
       }
     }
-    g.pitch = ((XPAD + g.n[0] + 1) + 15) / 16 * 16;
+    g.pitch = ((XPAD + g.n[0] + GHOST) + 15) / 16 * 16;
     g.ay = g.n[1] + 2 * GHOST;
     g.az = cfg->dim == 3 ? g.n[2] + 2 * GHOST : 1;
     g.plane = (long long)g.pitch * g.ay;
@@ -159,11 +195,9 @@ int examg_finalize(examg_ctx *c) {
   if (!c) return set_error(EXAMG_EINVAL, "examg_finalize: null context");
   cudaSetDevice(c->device);
   cudaDeviceSynchronize();
-  for (auto &f : c->fields)
-    if (f.alive) {
-      for (int sl = 0; sl < f.nslots; ++sl) cudaFree(f.slot[sl]);
-      if (f.shadow) cudaFree(f.shadow);
-    }
+  comm_destroy(c);
+  for (auto &b : c->blocks) cudaFree(b.base);
+  c->blocks.clear();
   if (c->partials) cudaFree(c->partials);
   if (c->red_out) cudaFree(c->red_out);
   if (c->red_host) cudaFreeHost(c->red_host);
@@ -226,14 +260,12 @@ int examg_field_create(examg_ctx *c, const char *name, int level, int num_slots,
   f.ncomp = ncomp;
   size_t bytes = sizeof(double) * (size_t)ncomp * g->vol;
   for (int sl = 0; sl < num_slots; ++sl) {
-    cudaError_t e = cudaMalloc(&f.slot[sl], bytes);
-    if (e != cudaSuccess) {
-      for (int q = 0; q < sl; ++q) cudaFree(f.slot[q]);
-      return set_error(EXAMG_ENOMEM, "examg_field_create(%s@%d): cudaMalloc of %zu bytes: %s", f.name.c_str(),
-                       level, bytes, cudaGetErrorString(e));
+    f.slot[sl] = f.orig[sl] = dev_alloc(c, bytes);  // zero-filled: initFieldsWithZero
+    if (!f.slot[sl]) {
+      for (int q = 0; q < sl; ++q) dev_free(c, f.slot[q]);
+      return set_error(EXAMG_ENOMEM, "examg_field_create(%s@%d): cudaMalloc of %zu bytes failed", f.name.c_str(),
+                       level, bytes);
     }
-    EXAMG_CUDA(cudaMemsetAsync(f.slot[sl], 0, bytes, c->stream));  // initFieldsWithZero
-    c->dev_bytes += (long long)bytes;
   }
   c->fields.push_back(f);
   return (int)c->fields.size() - 1;
@@ -243,17 +275,10 @@ int examg_field_destroy(examg_ctx *c, int h) {
   Field *f = get_field(c, h);
   if (!f) return set_error(EXAMG_EINVAL, "examg_field_destroy: handle %d", h);
   EXAMG_CUDA(cudaStreamSynchronize(c->stream));
-  const LevelGeom *g = geom(c, f->level);
-  for (int sl = 0; sl < f->nslots; ++sl) {
-    c->dev_bytes -= (long long)sizeof(double) * f->ncomp * g->vol;
-    cudaFree(f->slot[sl]);
-    f->slot[sl] = nullptr;
-  }
-  if (f->shadow) {
-    c->dev_bytes -= (long long)sizeof(double) * f->ncomp * g->vol;
-    cudaFree(f->shadow);
-    f->shadow = nullptr;
-  }
+  for (int i = 0; i < 5; ++i)
+    if (f->orig[i]) dev_free(c, f->orig[i]);
+  for (int sl = 0; sl < 4; ++sl) f->slot[sl] = nullptr;
+  f->shadow = nullptr;
   f->alive = false;
   return EXAMG_OK;
 }
@@ -322,6 +347,7 @@ static int copy_field(examg_ctx *c, int h, int slot, double *host, bool up, bool
   if (!host) return set_error(EXAMG_EINVAL, "null host pointer");
   if (slot >= f->nslots) return set_error(EXAMG_EINVAL, "bad slot %d", slot);
   const LevelGeom &g = *geom(c, f->level);
+  if (up) f->halo_valid = false;
   for (int comp = 0; comp < f->ncomp; ++comp) {
     double *dev = field_ptr(c, f, slot, comp);
     double *hp = host + (size_t)comp * g.n[0] * g.n[1] * g.n[2];
@@ -333,7 +359,7 @@ static int copy_field(examg_ctx *c, int h, int slot, double *host, bool up, bool
     p.srcPtr = up ? hpp : dp;
     p.dstPtr = up ? dp : hpp;
     p.extent = make_cudaExtent(sizeof(double) * g.n[0], g.n[1], g.n[2]);
-    p.kind = up ? cudaMemcpyHostToDevice : cudaMemcpyDeviceToHost;
+    p.kind = cudaMemcpyDefault;  // `host` may also be a device pointer (agglomeration staging, examg_cycle.cu)
     EXAMG_CUDA(cudaMemcpy3DAsync(&p, c->stream));
   }
   if (!async) EXAMG_CUDA(cudaStreamSynchronize(c->stream));
@@ -358,6 +384,7 @@ int examg_field_fill(examg_ctx *c, int h, double value) {
   if (!f) return set_error(EXAMG_EINVAL, "bad field %d", h);
   const LevelGeom &g = *geom(c, f->level);
   const size_t count = (size_t)f->ncomp * g.vol;
+  f->halo_valid = false;
   std::vector<double> row(g.pitch, value);
   for (int sl = 0; sl < f->nslots; ++sl) {
     double *base = f->slot[sl];

@@ -26,6 +26,10 @@ struct examg_solver {
   std::vector<int> sol, rhs, res;     // field handles per level
   int cg_p = -1, cg_ap = -1;
   int coarse_top = -1;                // mgCycle@level for level <= coarse_top is one single-CTA kernel
+  // several blocks: mgCycle@agg_level runs on rank 0 on the agglomerated (global, single-block) grid
+  int agg_level = -1;
+  examg_ctx *agg_ctx = nullptr;       // rank 0 only
+  examg_solver *agg = nullptr;
   bool use_graph = true;
   struct Graph { cudaGraphExec_t exec; long long launches; std::vector<int> exit_slots; };
   std::map<std::vector<int>, Graph> graphs;  // keyed by the active slots of Solution on entry
@@ -63,9 +67,35 @@ static int smooth(examg_solver *s, int level, int n) {
   return examg_smooth_jacobi(c, A, u, f, s->desc.omega, n);
 }
 
+static int vcycle_rec(examg_solver *s, int level);
+
+// mgCycle@agg_level of a multi-block run: RHS blocks -> rank 0, cycle on the global grid there,
+// Solution blocks back.  Arithmetically the same global-grid cycle (duplicate nodes carry identical
+// values, the oracle's formulation), executed by one GPU because these levels are latency bound.
+static int agg_cycle(examg_solver *s) {
+  examg_ctx *c = s->c;
+  const int T = s->agg_level, l = lv(s, T);
+  int rc = comm_agg_gather(c, c->fields[s->rhs[l]]);
+  if (rc) return rc;
+  if (c->cfg.rank == 0) {
+    examg_solver *a = s->agg;
+    examg_ctx *ac = s->agg_ctx;
+    const int al = lv(a, T);
+    if ((rc = examg_field_upload_async(ac, a->rhs[al], -1, comm_agg_in(c)))) return rc;
+    if ((rc = examg_set(ac, a->sol[al], -1, 0.0))) return rc;
+    if ((rc = vcycle_rec(a, T))) return rc;
+    if ((rc = examg_field_download_async(ac, a->sol[al], -1, comm_agg_out(c)))) return rc;
+    c->launches += ac->launches;
+    ac->launches = 0;
+  }
+  return comm_agg_scatter(c, c->fields[s->sol[l]]);
+}
+
 static int vcycle_rec(examg_solver *s, int level) {
   examg_ctx *c = s->c;
   const int l = lv(s, level);
+  if (c->world > 1 && level <= s->agg_level)
+    return set_error(EXAMG_EUNSUP, "mgCycle@%d of a multi-block run: levels <= %d live on the agglomerated grid", level, s->agg_level);
   if (level == c->cfg.min_level)
     return examg_cg_coarse(c, s->stencils[l], s->sol[l], s->rhs[l], s->res[l], s->cg_p, s->cg_ap,
                            s->desc.cg_max_it, s->desc.cg_rel_tol, nullptr);
@@ -76,8 +106,12 @@ static int vcycle_rec(examg_solver *s, int level) {
   if ((rc = smooth(s, level, s->desc.nu_pre))) return rc;
   if ((rc = examg_residual(c, s->stencils[l], s->sol[l], -1, s->rhs[l], s->res[l], nullptr))) return rc;
   if ((rc = examg_restrict(c, s->res[l], s->rhs[l - 1], s->desc.restrict_scale))) return rc;
-  if ((rc = examg_set(c, s->sol[l - 1], -1, 0.0))) return rc;
-  if ((rc = vcycle_rec(s, level - 1))) return rc;
+  if (c->world > 1 && level - 1 == s->agg_level) {
+    if ((rc = agg_cycle(s))) return rc;
+  } else {
+    if ((rc = examg_set(c, s->sol[l - 1], -1, 0.0))) return rc;
+    if ((rc = vcycle_rec(s, level - 1))) return rc;
+  }
   if ((rc = examg_prolong_add(c, s->sol[l - 1], -1, s->sol[l], -1))) return rc;
   return smooth(s, level, s->desc.nu_post);
 }
@@ -120,15 +154,65 @@ examg_solver *examg_solver_create(examg_ctx *c, const examg_cycle_desc *d) {
   s->cg_ap = examg_field_create(c, "cgTmp1", c->cfg.min_level, 1, 1);
   if (s->cg_p < 0 || s->cg_ap < 0) { delete s; return nullptr; }
   examg_field_set_bc(c, s->cg_p, EXAMG_BC_DIRICHLET_CONST, 0.0);
+  if (c->world > 1) {
+    // agglomeration level: the largest one whose global grid has <= 128 cells per dimension
+    int T = c->cfg.min_level;
+    for (int lvl = c->cfg.min_level; lvl < c->cfg.max_level; ++lvl) {
+      bool ok = true;
+      for (int dd = 0; dd < c->cfg.dim; ++dd) ok = ok && ((long long)c->cfg.block_cells[dd] * c->cfg.num_blocks[dd] << lvl) <= 128;
+      if (ok) T = lvl;
+    }
+    if (const char *e = getenv("EXAMG_AGG_LEVEL")) T = atoi(e);
+    if (T < c->cfg.min_level || T >= c->cfg.max_level) {
+      set_error(EXAMG_EUNSUP, "multi-block solver: agglomeration level %d outside [minLevel, maxLevel)", T);
+      examg_solver_destroy(s);
+      return nullptr;
+    }
+    s->agg_level = T;
+    if (comm_agg_setup(c, T)) { examg_solver_destroy(s); return nullptr; }
+    if (c->cfg.rank == 0) {
+      examg_config ac = c->cfg;
+      for (int dd = 0; dd < 3; ++dd) {
+        ac.block_cells[dd] = c->cfg.block_cells[dd] * (dd < c->cfg.dim ? c->cfg.num_blocks[dd] : 1);
+        ac.num_blocks[dd] = 1;
+      }
+      ac.rank = 0;
+      ac.max_level = T;
+      s->agg_ctx = examg_init(&ac);
+      if (!s->agg_ctx) { examg_solver_destroy(s); return nullptr; }
+      examg_set_stream(s->agg_ctx, c->stream);
+      std::vector<int> ast;
+      for (int lvl = c->cfg.min_level; lvl <= T; ++lvl) {
+        const Stencil &st = *get_stencil(c, s->stencils[lvl - c->cfg.min_level]);
+        if (st.coeff_field >= 0) {
+          set_error(EXAMG_EUNSUP, "multi-block solver: stencil fields on agglomerated levels");
+          examg_solver_destroy(s);
+          return nullptr;
+        }
+        ast.push_back(examg_stencil_const(s->agg_ctx, lvl, st.nst, st.off, st.coef));
+      }
+      examg_cycle_desc ad = *d;
+      ad.stencils = ast.data();
+      s->agg = examg_solver_create(s->agg_ctx, &ad);
+      if (!s->agg) { examg_solver_destroy(s); return nullptr; }
+      s->agg->use_graph = false;
+    }
+  }
   s->coarse_top = coarse_cycle_top(c, s->desc, s->stencils.data(), s->sol.data(), c->cfg.max_level);
   const char *ng = getenv("EXAMG_NO_GRAPH");
-  s->use_graph = !(ng && ng[0] == '1');
+  s->use_graph = !(ng && ng[0] == '1') && c->world == 1;  // multi-block cycles are launched kernel by kernel
   return s;
 }
 
 int examg_solver_destroy(examg_solver *s) {
   if (!s) return set_error(EXAMG_EINVAL, "examg_solver_destroy: null");
   cudaStreamSynchronize(s->c->stream);
+  if (s->agg) examg_solver_destroy(s->agg);
+  if (s->agg_ctx) {
+    s->agg_ctx->stream = nullptr;  // borrowed from the parent context
+    s->agg_ctx->own_stream = false;
+    examg_finalize(s->agg_ctx);
+  }
   for (auto &kv : s->graphs) cudaGraphExecDestroy(kv.second.exec);
   for (int h : s->sol) examg_field_destroy(s->c, h);
   for (int h : s->rhs) examg_field_destroy(s->c, h);
@@ -218,6 +302,10 @@ int examg_solver_cycles(examg_solver *s, int n, double *norm_out) {
 int examg_solver_last_cg_iters(examg_solver *s, int *iters_out) {
   if (!s || !iters_out) return set_error(EXAMG_EINVAL, "examg_solver_last_cg_iters: null argument");
   examg_ctx *c = s->c;
+  if (c->world > 1) {  // the coarse solve ran on rank 0's agglomerated grid
+    if (!s->agg) { *iters_out = 0; return EXAMG_OK; }
+    return examg_solver_last_cg_iters(s->agg, iters_out);
+  }
   EXAMG_CUDA(cudaMemcpyAsync(c->int_host, c->int_out, sizeof(int), cudaMemcpyDeviceToHost, c->stream));
   EXAMG_CUDA(cudaStreamSynchronize(c->stream));
   *iters_out = c->int_host[0];

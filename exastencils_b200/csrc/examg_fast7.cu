@@ -403,7 +403,6 @@ constexpr int FUSED_MIN_N = 65;
 
 bool fused_rb_usable(examg_ctx *c, const Stencil &s, const Field &fu) {
   if (!fused_enabled() || !s.is7 || c->cfg.dim != 3 || fu.ncomp != 1 || stencil_order(s) < 0) return false;
-  if (c->world > 1) return false;  // multi-block: colour sweeps + exchange (examg_comm.cu)
   const LevelGeom &g = *geom(c, s.level);
   return g.n[0] >= FUSED_MIN_N && g.n[1] >= FUSED_MIN_N && g.n[2] >= FUSED_MIN_N;
 }
@@ -421,10 +420,9 @@ int ensure_shadow(examg_ctx *c, Field &fu) {
   if (fu.shadow) return EXAMG_OK;
   const LevelGeom &g = *geom(c, fu.level);
   const size_t bytes = sizeof(double) * (size_t)g.vol;
-  cudaError_t e = cudaMalloc(&fu.shadow, bytes);
-  if (e != cudaSuccess) return set_error(EXAMG_ENOMEM, "shadow buffer of %s@%d: %s", fu.name.c_str(), fu.level, cudaGetErrorString(e));
-  EXAMG_CUDA(cudaMemset(fu.shadow, 0, bytes));
-  c->dev_bytes += (long long)bytes;
+  fu.shadow = fu.orig[4] = dev_alloc(c, bytes);
+  if (!fu.shadow) return set_error(EXAMG_ENOMEM, "shadow buffer of %s@%d: cudaMalloc of %zu bytes failed", fu.name.c_str(), fu.level, bytes);
+  EXAMG_CUDA(cudaStreamSynchronize(c->stream));
   return EXAMG_OK;
 }
 
@@ -480,7 +478,8 @@ int launch_rb_fused(examg_ctx *c, const Stencil &s, double omega, Field &fu, con
                     int *done) {
   int rc = ensure_shadow(c, fu);
   if (rc) return rc;
-  if (nsweeps >= 2 && max_half_sweeps() >= 4) {
+  // several blocks: the ghost layers are 2 deep, which is what one sweep (2 half-sweeps) needs
+  if (nsweeps >= 2 && max_half_sweeps() >= 4 && c->world == 1) {
     *done = 2;
     return launch_rbw<4>(c, s, omega, fu, rhs);
   }

@@ -69,6 +69,10 @@ struct Field {
   double *slot[4] = {nullptr, nullptr, nullptr, nullptr};  // one allocation of ncomp*vol doubles per slot
   double *shadow = nullptr;  // second buffer of the active slot for out-of-place fused sweeps (lazy)
   bool swapped = false;      // slot[cur] and shadow have been exchanged an odd number of times
+  // The allocations in creation order (slots 0..3, shadow = 4).  slot[]/shadow are permuted by the
+  // fused sweeps; orig[] is not, and identifies a buffer across ranks (examg_comm.cu).
+  double *orig[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
+  bool halo_valid = false;   // ghost layers hold the neighbour blocks' current values
   int bc_kind = EXAMG_BC_NONE;
   double bc_value = 0.0;
   std::vector<examg_bc_op> bc_prog;
@@ -83,6 +87,15 @@ struct Stencil {
 };
 
 struct dd { double hi, lo; };
+
+// A cudaMalloc'd region.  Buffers of >= 1 MiB get a block of their own, smaller ones are carved
+// out of shared arena blocks, so that every buffer is (block, offset) -- which is what is exported
+// to the other ranks through CUDA IPC (one handle per block).
+struct Block {
+  char *base = nullptr;
+  size_t bytes = 0, used = 0;
+  bool arena = false;
+};
 
 }  // namespace examg
 
@@ -106,6 +119,7 @@ struct examg_ctx {
   int *int_out = nullptr;         // device ints (cg iterations)
   int *int_host = nullptr;        // pinned
   struct examg_comm *comm = nullptr;
+  std::vector<examg::Block> blocks;
 };
 
 namespace examg {
@@ -114,6 +128,10 @@ constexpr int PARTIAL_CAP = 1 << 15;
 constexpr int RED_SLOTS = 8;
 
 int set_error(int code, const char *fmt, ...);
+// device memory of the context (zero-filled); see Block
+double *dev_alloc(examg_ctx *c, size_t bytes);
+void dev_free(examg_ctx *c, double *p);
+void comm_destroy(examg_ctx *c);
 const LevelGeom *geom(examg_ctx *c, int level);
 Field *get_field(examg_ctx *c, int h);
 Stencil *get_stencil(examg_ctx *c, int h);
@@ -161,6 +179,12 @@ int launch_stream_op(examg_ctx *c, int level, int op, double alpha, const double
 int launch_bc(examg_ctx *c, const Field &f, int slot);
 int launch_cg(examg_ctx *c, const Stencil &s, double *u, const double *rhs, double *res, double *p,
               double *ap, int max_it, double rel_tol);
-int do_exchange(examg_ctx *c, const Field &f, int slot);
+int do_exchange(examg_ctx *c, Field &f, int slot);
+// agglomeration of the coarse levels onto rank 0 (examg_comm.cu)
+int comm_agg_setup(examg_ctx *c, int level);
+double *comm_agg_in(examg_ctx *c);
+double *comm_agg_out(examg_ctx *c);
+int comm_agg_gather(examg_ctx *c, Field &f);
+int comm_agg_scatter(examg_ctx *c, Field &f);
 
 }  // namespace examg
