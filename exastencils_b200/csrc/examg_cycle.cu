@@ -154,6 +154,14 @@ examg_solver *examg_solver_create(examg_ctx *c, const examg_cycle_desc *d) {
   s->cg_ap = examg_field_create(c, "cgTmp1", c->cfg.min_level, 1, 1);
   if (s->cg_p < 0 || s->cg_ap < 0) { delete s; return nullptr; }
   examg_field_set_bc(c, s->cg_p, EXAMG_BC_DIRICHLET_CONST, 0.0);
+  // second buffers of the fused sweeps: now, so that they are part of what examg_comm_export publishes
+  if (d->smoother == EXAMG_SMOOTH_RBGS)
+    for (int l = 0; l < nl; ++l)
+      if (fused_rb_usable(c, *get_stencil(c, s->stencils[l]), c->fields[s->sol[l]]) &&
+          ensure_shadow(c, c->fields[s->sol[l]])) {
+        examg_solver_destroy(s);
+        return nullptr;
+      }
   if (c->world > 1) {
     // agglomeration level: the largest one whose global grid has <= 128 cells per dimension
     int T = c->cfg.min_level;
