@@ -212,7 +212,7 @@ def main():
                             num_blocks=BLOCKS[world], rank=rank, device=local_rank, stream=stream.cuda_stream)
     if world > 1:
         from exastencils_b200.distributed import wire_peers
-        wire_peers(prog.ctx, dist)
+        wire_peers(prog.ctx, dist, device="cuda:%d" % local_rank)
     set_benchmark_problem(prog)
     ctx = prog.ctx
     nb = BLOCKS[world]
