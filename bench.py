@@ -5,7 +5,7 @@ Workload (BASELINE.json configs[1]): Benchmark/Poisson3D 7-point constant-coeffi
 Poisson, V(2,2) red-black Gauss-Seidel (omega 0.8), CG coarse solve, 512^3 cells per
 GPU (levels 2..9 as in Benchmark/Poisson3D/3D_FD_Poisson_fromL4_CUDA.knowledge), double
 precision, Dirichlet data x^2 - y^2/2 - z^2/2, RHS = 0.  N > 1: weak scaling, one block
-of 512^3 cells per GPU (domain_rect_numBlocks 2x1x1, 2x2x1, 2x2x2).
+of 512^3 cells per GPU (domain_rect_numBlocks 1x1x2, 1x2x2, 1x2x4, domain [0,nbx]x[0,nby]x[0,nbz]).
 
 A step = one mgCycle@finest + the outer-loop residual and its L2 norm
 (Solve@finest's loop body, ...fromL4.exa4:135-149).  Prints ONE JSON line.
@@ -21,7 +21,10 @@ import time
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
-BLOCKS = {1: (1, 1, 1), 2: (2, 1, 1), 4: (2, 2, 1), 8: (2, 2, 2)}
+# domain_rect_numBlocks_{x,y,z}: z and y are split first -- their faces are contiguous rows, which NVLink peer
+# stores move at full speed; the domain grows with the block grid ([0,nbx]x[0,nby]x[0,nbz]), so the mesh width and
+# with it the operator stay those of the 1-GPU problem (weak scaling of the same isotropic problem)
+BLOCKS = {1: (1, 1, 1), 2: (1, 1, 2), 4: (1, 2, 2), 8: (1, 2, 4)}
 NU_PRE = NU_POST = 2
 OMEGA = 0.8
 MIN_LEVEL = 2
@@ -209,7 +212,8 @@ def main():
     level = args.level
     prog = MultigridProgram(3, (1, 1, 1), MIN_LEVEL, level, op="scaled", order="bench", smoother="rbgs", omega=OMEGA,
                             nu_pre=NU_PRE, nu_post=NU_POST, cg_max_it=128, cg_rel_tol=1e-3,
-                            num_blocks=BLOCKS[world], rank=rank, device=local_rank, stream=stream.cuda_stream)
+                            num_blocks=BLOCKS[world], rank=rank, device=local_rank, stream=stream.cuda_stream,
+                            domain_hi=tuple(float(b) for b in BLOCKS[world]))
     if world > 1:
         from exastencils_b200.distributed import wire_peers
         wire_peers(prog.ctx, dist, device="cuda:%d" % local_rank)

@@ -15,7 +15,7 @@
 //     memory), wait for theirs, store the boundary layers straight into their ghost layers
 //     (remote stores over NVLink, no pack buffer, no host), fence, tell them "done", wait for theirs.
 //     Dimensions run one after the other and faces carry the orthogonal ghost layers already
-//     received, so edges and corners become valid as in the reference.  Two ghost layers + the
+//     received, so edges and corners become valid as in the reference.  `depth` ghost layers + the
 //     duplicate layer travel (+dir block's node 0 := -dir block's node n-1, as IR_PackInfoDuplicate).
 //   * epochs are counted on the device, so the same kernels replay inside a CUDA graph.
 //   * sums: every rank stores its double-double partial into a mailbox of every rank and adds the
@@ -328,13 +328,14 @@ static int check_comm_error(examg_ctx *c) {
   return EXAMG_OK;
 }
 
-int do_exchange(examg_ctx *c, Field &f, int slot) {
+int do_exchange(examg_ctx *c, Field &f, int slot, int depth) {
   if (c->world == 1) return EXAMG_OK;  // no neighbour blocks: nothing to exchange
   examg_comm *cm = c->comm;
   if (!cm || !cm->wired) return set_error(EXAMG_ESTATE, "examg_exchange: peers not wired (examg_comm_import)");
   const int field = (int)(&f - c->fields.data());
   const LevelGeom &g = *geom(c, f.level);
-  const int G = GHOST;
+  if (depth < 1 || depth > GHOST) return set_error(EXAMG_EINVAL, "examg_exchange: depth %d", depth);
+  const int G = depth;
   for (int comp = 0; comp < f.ncomp; ++comp) {
     double *buf = f.slot[slot];
     for (int d = 0; d < c->cfg.dim; ++d) {
@@ -381,7 +382,7 @@ int do_exchange(examg_ctx *c, Field &f, int slot) {
       EXAMG_LAUNCH_CHECK(c);
     }
   }
-  f.halo_valid = true;
+  f.halo_depth = depth;
   return check_comm_error(c);
 }
 
@@ -487,7 +488,7 @@ int comm_agg_scatter(examg_ctx *c, Field &f) {
   }
   k_agg_scatter<<<agg_grid(a), 256, 0, c->stream>>>(a);
   EXAMG_LAUNCH_CHECK(c);
-  f.halo_valid = false;
+  f.halo_depth = 0;
   return EXAMG_OK;
 }
 

@@ -341,13 +341,13 @@ int examg_apply_bc(examg_ctx *c, int h, int slot) {
   return launch_bc(c, *f, slot);
 }
 
-static int copy_field(examg_ctx *c, int h, int slot, double *host, bool up, bool async) {
+static int copy_field(examg_ctx *c, int h, int slot, double *host, bool up, bool async, bool device_side = false) {
   Field *f = get_field(c, h);
   if (!f) return set_error(EXAMG_EINVAL, "bad field %d", h);
   if (!host) return set_error(EXAMG_EINVAL, "null host pointer");
   if (slot >= f->nslots) return set_error(EXAMG_EINVAL, "bad slot %d", slot);
   const LevelGeom &g = *geom(c, f->level);
-  if (up) f->halo_valid = false;
+  if (up) f->halo_depth = 0;
   for (int comp = 0; comp < f->ncomp; ++comp) {
     double *dev = field_ptr(c, f, slot, comp);
     double *hp = host + (size_t)comp * g.n[0] * g.n[1] * g.n[2];
@@ -359,12 +359,21 @@ static int copy_field(examg_ctx *c, int h, int slot, double *host, bool up, bool
     p.srcPtr = up ? hpp : dp;
     p.dstPtr = up ? dp : hpp;
     p.extent = make_cudaExtent(sizeof(double) * g.n[0], g.n[1], g.n[2]);
-    p.kind = cudaMemcpyDefault;  // `host` may also be a device pointer (agglomeration staging, examg_cycle.cu)
+    p.kind = device_side ? cudaMemcpyDeviceToDevice : (up ? cudaMemcpyHostToDevice : cudaMemcpyDeviceToHost);
     EXAMG_CUDA(cudaMemcpy3DAsync(&p, c->stream));
   }
   if (!async) EXAMG_CUDA(cudaStreamSynchronize(c->stream));
   return EXAMG_OK;
 }
+
+}  // extern "C"
+
+// dense device array <-> field (agglomeration staging, examg_cycle.cu); asynchronous, capturable
+int examg::copy_field_device(examg_ctx *c, int h, int slot, double *dense, bool to_field) {
+  return copy_field(c, h, slot, dense, to_field, true, true);
+}
+
+extern "C" {
 
 int examg_field_upload(examg_ctx *c, int h, int slot, const double *host) {
   return copy_field(c, h, slot, const_cast<double *>(host), true, false);
@@ -384,7 +393,7 @@ int examg_field_fill(examg_ctx *c, int h, double value) {
   if (!f) return set_error(EXAMG_EINVAL, "bad field %d", h);
   const LevelGeom &g = *geom(c, f->level);
   const size_t count = (size_t)f->ncomp * g.vol;
-  f->halo_valid = false;
+  f->halo_depth = 0;
   std::vector<double> row(g.pitch, value);
   for (int sl = 0; sl < f->nslots; ++sl) {
     double *base = f->slot[sl];

@@ -81,10 +81,10 @@ static int agg_cycle(examg_solver *s) {
     examg_solver *a = s->agg;
     examg_ctx *ac = s->agg_ctx;
     const int al = lv(a, T);
-    if ((rc = examg_field_upload_async(ac, a->rhs[al], -1, comm_agg_in(c)))) return rc;
+    if ((rc = copy_field_device(ac, a->rhs[al], -1, comm_agg_in(c), true))) return rc;
     if ((rc = examg_set(ac, a->sol[al], -1, 0.0))) return rc;
     if ((rc = vcycle_rec(a, T))) return rc;
-    if ((rc = examg_field_download_async(ac, a->sol[al], -1, comm_agg_out(c)))) return rc;
+    if ((rc = copy_field_device(ac, a->sol[al], -1, comm_agg_out(c), false))) return rc;
     c->launches += ac->launches;
     ac->launches = 0;
   }
@@ -208,7 +208,7 @@ examg_solver *examg_solver_create(examg_ctx *c, const examg_cycle_desc *d) {
   }
   s->coarse_top = coarse_cycle_top(c, s->desc, s->stencils.data(), s->sol.data(), c->cfg.max_level);
   const char *ng = getenv("EXAMG_NO_GRAPH");
-  s->use_graph = !(ng && ng[0] == '1') && c->world == 1;  // multi-block cycles are launched kernel by kernel
+  s->use_graph = !(ng && ng[0] == '1');
   return s;
 }
 
@@ -245,6 +245,27 @@ int examg_solver_field(examg_solver *s, int level, int which) {
   return set_error(EXAMG_EINVAL, "examg_solver_field: no field %d on level %d", which, level);
 }
 
+// State that decides which kernels a cycle launches and on which buffers: (active slot, shadow
+// parity) of every Solution field -- of the agglomerated solver too -- and how many ghost layers
+// of every RHS field are valid (a cycle skips the RHS exchange when they already are).
+static void cycle_state(examg_solver *s, std::vector<int> &key) {
+  examg_ctx *c = s->c;
+  for (int h : s->sol) key.push_back(c->fields[h].cur * 2 + (c->fields[h].swapped ? 1 : 0));
+  for (int h : s->rhs) key.push_back(c->fields[h].halo_depth);
+  for (int h : s->sol) key.push_back(c->fields[h].halo_depth);
+  for (int h : s->res) key.push_back(c->fields[h].halo_depth);
+  if (s->agg) cycle_state(s->agg, key);
+}
+
+static void restore_cycle_state(examg_solver *s, const std::vector<int> &key, size_t &pos) {
+  examg_ctx *c = s->c;
+  for (int h : s->sol) restore_state(c->fields[h], key[pos++]);
+  for (int h : s->rhs) c->fields[h].halo_depth = key[pos++];
+  for (int h : s->sol) c->fields[h].halo_depth = key[pos++];
+  for (int h : s->res) c->fields[h].halo_depth = key[pos++];
+  if (s->agg) restore_cycle_state(s->agg, key, pos);
+}
+
 int examg_solver_vcycle(examg_solver *s, int level) {
   if (!s) return set_error(EXAMG_EINVAL, "null solver");
   examg_ctx *c = s->c;
@@ -253,17 +274,11 @@ int examg_solver_vcycle(examg_solver *s, int level) {
   if (!s->use_graph || level != c->cfg.max_level) return vcycle_rec(s, level);
 
   std::vector<int> key;
-  for (int h : s->sol) key.push_back(c->fields[h].cur * 2 + (c->fields[h].swapped ? 1 : 0));
+  cycle_state(s, key);
   auto it = s->graphs.find(key);
   if (it == s->graphs.end()) {
-    // allocations cannot be captured: create the shadow buffers of the fused sweeps first
-    if (s->desc.smoother == EXAMG_SMOOTH_RBGS)
-      for (size_t i = 0; i < s->sol.size(); ++i)
-        if (fused_rb_usable(c, *get_stencil(c, s->stencils[i]), c->fields[s->sol[i]])) {
-          int rc = ensure_shadow(c, c->fields[s->sol[i]]);
-          if (rc) return rc;
-        }
-    // capture mgCycle@finest for this slot configuration
+    // capture mgCycle@finest for this state (allocations cannot be captured: the shadow buffers of the
+    // fused sweeps were created with the solver)
     const long long l0 = c->launches;
     cudaGraph_t graph = nullptr;
     EXAMG_CUDA(cudaStreamBeginCapture(c->stream, cudaStreamCaptureModeThreadLocal));
@@ -277,13 +292,15 @@ int examg_solver_vcycle(examg_solver *s, int level) {
     if (e != cudaSuccess) return set_error(EXAMG_ECUDA, "cudaGraphInstantiate: %s", cudaGetErrorString(e));
     g.launches = c->launches - l0;
     c->launches = l0;  // nothing ran yet
-    for (int h : s->sol) g.exit_slots.push_back(c->fields[h].cur * 2 + (c->fields[h].swapped ? 1 : 0));
-    for (size_t i = 0; i < s->sol.size(); ++i) restore_state(c->fields[s->sol[i]], key[i]);
+    cycle_state(s, g.exit_slots);
+    size_t pos = 0;
+    restore_cycle_state(s, key, pos);
     it = s->graphs.emplace(key, g).first;
   }
   EXAMG_CUDA(cudaGraphLaunch(it->second.exec, c->stream));
   c->launches += it->second.launches;
-  for (size_t i = 0; i < s->sol.size(); ++i) restore_state(c->fields[s->sol[i]], it->second.exit_slots[i]);
+  size_t pos = 0;
+  restore_cycle_state(s, it->second.exit_slots, pos);
   return EXAMG_OK;
 }
 

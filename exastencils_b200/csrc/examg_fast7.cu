@@ -473,13 +473,15 @@ static int launch_rbw(examg_ctx *c, const Stencil &s, double omega, Field &fu, c
   return EXAMG_OK;
 }
 
+// sweeps the next launch will fuse (1 or 2)
+int rb_fused_plan(int nsweeps) { return nsweeps >= 2 && max_half_sweeps() >= 4 ? 2 : 1; }
+
 // nsweeps full sweeps; returns the number of sweeps done by one launch through *done
 int launch_rb_fused(examg_ctx *c, const Stencil &s, double omega, Field &fu, const double *rhs, int nsweeps,
                     int *done) {
   int rc = ensure_shadow(c, fu);
   if (rc) return rc;
-  // several blocks: the ghost layers are 2 deep, which is what one sweep (2 half-sweeps) needs
-  if (nsweeps >= 2 && max_half_sweeps() >= 4 && c->world == 1) {
+  if (rb_fused_plan(nsweeps) == 2) {
     *done = 2;
     return launch_rbw<4>(c, s, omega, fu, rhs);
   }

@@ -24,13 +24,13 @@ namespace examg {
 //      128-byte boundary (the left ghost is element 15 of the pad); pitch is a
 //      multiple of 16 doubles -> rows are 128-byte aligned, which is what TMA
 //      (16 B) and 128-bit vector accesses need.
-//   y,z: GHOST ghost rows/planes per side (z only in 3D).  Two layers, because one
-//      fused red+black sweep needs a 2-deep halo (one exchange per sweep instead
-//      of one per colour; the B200 form of the reference's contraction loops,
-//      C/s/e/baseExt/ir/IR_ContractingLoop.scala:48-90).
+//   y,z: GHOST ghost rows/planes per side (z only in 3D).  Four layers, because two
+//      fused red+black sweeps (4 half-sweeps) need a 4-deep halo: one exchange per
+//      two sweeps instead of one per colour; the B200 form of the reference's
+//      contraction loops, C/s/e/baseExt/ir/IR_ContractingLoop.scala:48-90.
 // ---------------------------------------------------------------------------
 constexpr int XPAD = 16;
-constexpr int GHOST = 2;
+constexpr int GHOST = 4;
 
 struct LevelGeom {
   int n[3];        // local nodes per dim incl. duplicate/boundary nodes (n[2] = 1 in 2D)
@@ -72,7 +72,7 @@ struct Field {
   // The allocations in creation order (slots 0..3, shadow = 4).  slot[]/shadow are permuted by the
   // fused sweeps; orig[] is not, and identifies a buffer across ranks (examg_comm.cu).
   double *orig[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
-  bool halo_valid = false;   // ghost layers hold the neighbour blocks' current values
+  int halo_depth = 0;        // this many ghost layers hold the neighbour blocks' current values
   int bc_kind = EXAMG_BC_NONE;
   double bc_value = 0.0;
   std::vector<examg_bc_op> bc_prog;
@@ -179,8 +179,10 @@ int launch_stream_op(examg_ctx *c, int level, int op, double alpha, const double
 int launch_bc(examg_ctx *c, const Field &f, int slot);
 int launch_cg(examg_ctx *c, const Stencil &s, double *u, const double *rhs, double *res, double *p,
               double *ap, int max_it, double rel_tol);
-int do_exchange(examg_ctx *c, Field &f, int slot);
+// communicate: `depth` ghost layers (+ the duplicate layer) per side, 1 <= depth <= GHOST
+int do_exchange(examg_ctx *c, Field &f, int slot, int depth = 1);
 // agglomeration of the coarse levels onto rank 0 (examg_comm.cu)
+int copy_field_device(examg_ctx *c, int field, int slot, double *dense, bool to_field);
 int comm_agg_setup(examg_ctx *c, int level);
 double *comm_agg_in(examg_ctx *c);
 double *comm_agg_out(examg_ctx *c);

@@ -20,6 +20,7 @@ int fast7_residual(examg_ctx *c, const Stencil &s, const double *u, const double
 int fast7_rb(examg_ctx *c, const Stencil &s, double omega, double *u, const double *rhs, int color);
 bool fused_rb_usable(examg_ctx *c, const Stencil &s, const Field &fu);
 int launch_rb_fused(examg_ctx *c, const Stencil &s, double omega, Field &fu, const double *rhs, int nsweeps, int *done);
+int rb_fused_plan(int nsweeps);
 
 int launch_residual(examg_ctx *c, const Stencil &s, const double *u, const double *rhs, double *res, int red_slot) {
   if (fast7_usable(c, s)) return fast7_residual(c, s, u, rhs, res, red_slot);
@@ -59,7 +60,7 @@ int examg_apply(examg_ctx *c, int A, int u, int u_slot, int out) {
   if (fu == fo) return set_error(EXAMG_EINVAL, "examg_apply: in-place application");
   int rc = do_exchange(c, *fu, u_slot < 0 ? fu->cur : u_slot);
   if (rc) return rc;
-  fo->halo_valid = false;
+  fo->halo_depth = 0;
   return launch_apply(c, *s, field_ptr(c, fu, u_slot), field_ptr(c, fo, -1));
 }
 
@@ -69,7 +70,7 @@ int examg_residual(examg_ctx *c, int A, int u, int u_slot, int rhs, int res, dou
   if (fu == fo) return set_error(EXAMG_EINVAL, "examg_residual: Residual aliases Solution");
   int rc = do_exchange(c, *fu, u_slot < 0 ? fu->cur : u_slot);  // communicate Solution
   if (rc) return rc;
-  fo->halo_valid = false;
+  fo->halo_depth = 0;
   rc = launch_residual(c, *s, field_ptr(c, fu, u_slot), field_ptr(c, fr, -1), field_ptr(c, fo, -1),
                            norm2_out ? 0 : -1);
   if (rc || !norm2_out) return rc;
@@ -87,7 +88,7 @@ int examg_smooth_jacobi(examg_ctx *c, int A, int u, int rhs, double omega, int n
     rc = launch_jacobi(c, *s, omega, field_ptr(c, fu, fu->cur), field_ptr(c, fr, -1), field_ptr(c, fu, nxt));
     if (rc) return rc;
     fu->cur = nxt;  // advance Solution
-    fu->halo_valid = false;
+    fu->halo_depth = 0;
   }
   return EXAMG_OK;
 }
@@ -102,7 +103,7 @@ int examg_smooth_rb_color(examg_ctx *c, int A, int u, int rhs, double omega, int
                        "couples points of one colour); use a star stencil or Jacobi", s->off[k][0], s->off[k][1], s->off[k][2]);
   int rc = do_exchange(c, *fu, fu->cur);
   if (rc) return rc;
-  fu->halo_valid = false;
+  fu->halo_depth = 0;
   return launch_rb(c, *s, omega, field_ptr(c, fu, -1), field_ptr(c, fr, -1), color);
 }
 
@@ -112,13 +113,15 @@ int examg_smooth_rbgs(examg_ctx *c, int A, int u, int rhs, double omega, int nsw
     CHECK_LEVEL(fu, s->level); CHECK_LEVEL(fr, s->level);
     if (fused_rb_usable(c, *s, *fu)) {  // both colours of one or two sweeps in one pass over HBM
       for (int it = 0; it < nsweeps;) {
-        int rc = do_exchange(c, *fu, fu->cur), done = 0;
+        // one launch does `plan` sweeps = 2*plan half-sweeps: that many ghost layers of Solution and one
+        // less of RHS (the redundant updates in the ghost layers read RHS there)
+        const int plan = rb_fused_plan(nsweeps - it);
+        int rc = do_exchange(c, *fu, fu->cur, 2 * plan), done = 0;
         if (rc) return rc;
-            // the redundant update of the first ghost layer reads RHS there
-        if (c->world > 1 && !fr->halo_valid && (rc = do_exchange(c, *fr, fr->cur))) return rc;
+        if (c->world > 1 && fr->halo_depth < 2 * plan - 1 && (rc = do_exchange(c, *fr, fr->cur, 2 * plan - 1))) return rc;
         if ((rc = launch_rb_fused(c, *s, omega, *fu, field_ptr(c, fr, -1), nsweeps - it, &done))) return rc;
         it += done;
-        fu->halo_valid = false;
+        fu->halo_depth = 0;
       }
       return EXAMG_OK;
     }
@@ -136,7 +139,7 @@ int examg_restrict(examg_ctx *c, int res_fine, int rhs_coarse, double scale) {
   if (fc->level != ff->level - 1) return set_error(EXAMG_EINVAL, "examg_restrict: levels %d -> %d", ff->level, fc->level);
   int rc = do_exchange(c, *ff, ff->cur);  // communicate Residual
   if (rc) return rc;
-  fc->halo_valid = false;
+  fc->halo_depth = 0;
   return launch_restrict(c, ff->level, scale, field_ptr(c, ff, -1), field_ptr(c, fc, -1));
 }
 
@@ -144,7 +147,7 @@ int examg_prolong_add(examg_ctx *c, int u_coarse, int uc_slot, int u_fine, int u
   GET_FIELD(fc, u_coarse); GET_FIELD(ff, u_fine);
   CHECK_SLOT(fc, uc_slot); CHECK_SLOT(ff, uf_slot);
   if (fc->level != ff->level - 1) return set_error(EXAMG_EINVAL, "examg_prolong_add: levels %d -> %d", fc->level, ff->level);
-  ff->halo_valid = false;
+  ff->halo_depth = 0;
   return launch_prolong(c, ff->level, field_ptr(c, fc, uc_slot), field_ptr(c, ff, uf_slot));
 }
 
@@ -171,25 +174,25 @@ int examg_max_abs_diff(examg_ctx *c, int a, int a_slot, int b, int b_slot, doubl
 
 int examg_set(examg_ctx *c, int f, int slot, double value) {
   GET_FIELD(ff, f); CHECK_SLOT(ff, slot);
-  ff->halo_valid = false;
+  ff->halo_depth = 0;
   return launch_stream_op(c, ff->level, STREAM_SET, value, nullptr, field_ptr(c, ff, slot));
 }
 int examg_copy(examg_ctx *c, int src, int src_slot, int dst, int dst_slot) {
   GET_FIELD(fs, src); GET_FIELD(fd, dst);
   CHECK_SLOT(fs, src_slot); CHECK_SLOT(fd, dst_slot); CHECK_LEVEL(fd, fs->level);
-  fd->halo_valid = false;
+  fd->halo_depth = 0;
   return launch_stream_op(c, fs->level, STREAM_COPY, 0.0, field_ptr(c, fs, src_slot), field_ptr(c, fd, dst_slot));
 }
 int examg_axpy(examg_ctx *c, double alpha, int x, int x_slot, int y, int y_slot) {
   GET_FIELD(fx, x); GET_FIELD(fy, y);
   CHECK_SLOT(fx, x_slot); CHECK_SLOT(fy, y_slot); CHECK_LEVEL(fy, fx->level);
-  fy->halo_valid = false;
+  fy->halo_depth = 0;
   return launch_stream_op(c, fx->level, STREAM_AXPY, alpha, field_ptr(c, fx, x_slot), field_ptr(c, fy, y_slot));
 }
 int examg_xpay(examg_ctx *c, int x, int x_slot, double beta, int y, int y_slot) {
   GET_FIELD(fx, x); GET_FIELD(fy, y);
   CHECK_SLOT(fx, x_slot); CHECK_SLOT(fy, y_slot); CHECK_LEVEL(fy, fx->level);
-  fy->halo_valid = false;
+  fy->halo_depth = 0;
   return launch_stream_op(c, fx->level, STREAM_XPAY, beta, field_ptr(c, fx, x_slot), field_ptr(c, fy, y_slot));
 }
 

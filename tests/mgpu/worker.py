@@ -22,8 +22,9 @@ def main():
     ap.add_argument("--level", type=int, default=7)
     ap.add_argument("--min-level", type=int, default=2)
     ap.add_argument("--cycles", type=int, default=3)
-    ap.add_argument("--nu", type=int, default=2)
+    ap.add_argument("--sweeps", type=int, default=2, help="nu_pre = nu_post")
     ap.add_argument("--smoother", default="rbgs")
+    ap.add_argument("--blocks", default="", help="domain_rect_numBlocks as x,y,z (default: x first)")
     args = ap.parse_args()
     import torch
     import torch.distributed as dist
@@ -34,10 +35,11 @@ def main():
     local = int(os.environ.get("LOCAL_RANK", rank))
     torch.cuda.set_device(local)
     dist.init_process_group("nccl", device_id=torch.device("cuda", local))
-    nb = BLOCK_GRIDS[world]
+    nb = tuple(int(v) for v in args.blocks.split(",")) if args.blocks else BLOCK_GRIDS[world]
+    assert nb[0] * nb[1] * nb[2] == world
     L = args.level
     prog = MultigridProgram(3, (1, 1, 1), args.min_level, L, op="scaled", order="bench", smoother=args.smoother,
-                            omega=0.8, nu_pre=args.nu, nu_post=args.nu, cg_max_it=128, cg_rel_tol=1e-3,
+                            omega=0.8, nu_pre=args.sweeps, nu_post=args.sweeps, cg_max_it=128, cg_rel_tol=1e-3,
                             num_blocks=nb, rank=rank, device=local)
     wire_peers(prog.ctx, dist, device="cuda:%d" % local)
 
@@ -63,7 +65,7 @@ def main():
         og.build()
         ref = og.Solver(3, nb, args.min_level, L, op=og.OP_LAPLACE_SCALED, order=og.ORDER_BENCH,
                         smoother=og.SMOOTH_RBGS if args.smoother == "rbgs" else og.SMOOTH_JACOBI, omega=0.8,
-                        nu_pre=args.nu, nu_post=args.nu, cg_max_it=128, cg_rel_tol=1e-3)
+                        nu_pre=args.sweeps, nu_post=args.sweeps, cg_max_it=128, cg_rel_tol=1e-3)
         ref.solution(L)[...] = u0
         ref.rhs(L)[...] = f0
         ref.sync_slots()
