@@ -1,0 +1,28 @@
+"""Multi-GPU parity: needs >= 2 GPUs (skipped on a single-GPU box).  One rank per GPU runs
+tests/mgpu/worker.py: the Benchmark/Poisson3D program on a 2- or 8-block domain against the oracle's
+run on the global grid -- fields bit-exact, residual norms within 1e-13."""
+import os
+import subprocess
+import sys
+
+import pytest
+
+pytestmark = pytest.mark.gpu
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _ngpus():
+    import torch
+    return torch.cuda.device_count() if torch.cuda.is_available() else 0
+
+
+@pytest.mark.parametrize("world,blocks,level", [(2, "2,1,1", 7), (2, "1,1,2", 7), (4, "1,2,2", 7), (8, "2,2,2", 6),
+                                                (8, "1,2,4", 6)])
+def test_blocks_match_global_oracle(world, blocks, level):
+    if _ngpus() < world:
+        pytest.skip("needs %d GPUs" % world)
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", str(world),
+           "--master-addr", "127.0.0.1", "--master-port", str(29700 + world), os.path.join(ROOT, "tests", "mgpu", "worker.py"),
+           "--level", str(level), "--cycles", "3", "--blocks", blocks]
+    out = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
+    assert out.returncode == 0 and "MGPU PARITY OK" in out.stdout, out.stdout[-3000:] + out.stderr[-3000:]
