@@ -181,7 +181,7 @@ def cpu_baseline(args):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--steps", type=int, default=30)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="examg", choices=["examg", "reference"])
     ap.add_argument("--level", type=int, default=9, help="finest level per GPU (9 = 512^3 cells)")
@@ -231,12 +231,12 @@ def main():
 
     # ---- device-resident throughput ------------------------------------------------
     with torch.cuda.stream(stream):
+        sampler = ClockSampler(local_rank)
+        if rank == 0:
+            sampler.start()  # samples cover the warm-up and both timed regions (nvidia-smi needs ~100 ms per sample)
         for _ in range(args.warmup):
             prog.cycles(1)
         barrier()
-        sampler = ClockSampler(local_rank)
-        if rank == 0:
-            sampler.start()
         l0 = ctx.launch_count()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record(stream)
@@ -246,7 +246,6 @@ def main():
         barrier()
         ms = e0.elapsed_time(e1)
         launches = ctx.launch_count() - l0
-        clocks = sampler.stop() if rank == 0 else None
     if dist is not None:
         t = torch.tensor([ms], device="cuda")
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
@@ -276,6 +275,7 @@ def main():
         t = torch.tensor([ms_e2e], device="cuda")
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         ms_e2e = float(t.item())
+    clocks = sampler.stop() if rank == 0 else None
     e2e = {"value": dof * args.steps / (ms_e2e * 1e-3), "unit": "DoF-cycles/s", "h2d_bytes_per_step": h2d,
            "d2h_bytes_per_step": 16, "ms_per_step": ms_e2e / args.steps,
            "what": "per step: RHS@finest H2D from pinned memory, mgCycle + residual, norm D2H"}

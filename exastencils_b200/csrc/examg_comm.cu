@@ -92,6 +92,11 @@ struct ExchArgs {
   int dlo[2][3];            // where it lands (neighbour coordinates)
   int pitch;
   long long plane;
+  // d >= 1: whole rows travel (x pad included), so a face is `nchunks` runs of `len2` double2
+  long long soff[2], doff[2];  // first element of the runs, relative to src / dst[s]
+  long long len2[2];
+  int nchunks;
+  long long cstride;           // elements between runs
   unsigned long long *flags;      // local flag page
   unsigned long long *pflags[2];  // neighbours' flag pages
 };
@@ -107,7 +112,6 @@ __global__ void __launch_bounds__(256) k_exchange_dim(const ExchArgs a) {
   for (int s = 0; s < 2; ++s) {
     if (!a.has[s]) continue;
     const Box &b = a.sbox[s];
-    const long long total = (long long)b.ext[0] * b.ext[1] * b.ext[2];
     double *dst = a.dst[s];
     if (a.d == 0) {
       // x faces: rows are 2-3 elements long; let consecutive threads take consecutive rows
@@ -119,12 +123,26 @@ __global__ void __launch_bounds__(256) k_exchange_dim(const ExchArgs a) {
         for (int i = 0; i < b.ext[0]; ++i) dst[dof + i] = a.src[so + i];
       }
     } else {
-      for (long long t = blockIdx.x * (long long)blockDim.x + threadIdx.x; t < total; t += (long long)gridDim.x * blockDim.x) {
-        const int i = (int)(t % b.ext[0]);
-        const long long r = t / b.ext[0];
-        const int j = (int)(r % b.ext[1]), k = (int)(r / b.ext[1]);
-        dst[a.dlo[s][0] + i + (long long)a.pitch * (a.dlo[s][1] + j) + a.plane * (a.dlo[s][2] + k)] =
-            a.src[b.lo[0] + i + (long long)a.pitch * (b.lo[1] + j) + a.plane * (b.lo[2] + k)];
+      // y / z faces: runs of whole rows, 128-bit accesses, four independent loads per thread in flight
+      const long long n2 = a.len2[s] * a.nchunks;
+      const long long stride = (long long)gridDim.x * blockDim.x;
+      const double *sb = a.src + a.soff[s];
+      double *db = dst + a.doff[s];
+      for (long long t0 = blockIdx.x * (long long)blockDim.x + threadIdx.x; t0 < n2; t0 += 4 * stride) {
+        double2 v[4];
+        long long off[4];
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          const long long t = t0 + q * stride;
+          if (t < n2) {
+            const long long ch = a.nchunks == 1 ? 0 : t / a.len2[s];
+            off[q] = ch * a.cstride + 2 * (t - ch * a.len2[s]);
+            v[q] = *reinterpret_cast<const double2 *>(sb + off[q]);
+          }
+        }
+#pragma unroll
+        for (int q = 0; q < 4; ++q)
+          if (t0 + q * stride < n2) *reinterpret_cast<double2 *>(db + off[q]) = v[q];
       }
     }
   }
@@ -372,11 +390,37 @@ int do_exchange(examg_ctx *c, Field &f, int slot, int depth) {
           a.dlo[s][d] = -G;
         }
       }
-      long long work = 1;
-      for (int q = 0; q < 3; ++q) work *= a.sbox[a.has[0] ? 0 : 1].ext[q];
-      if (d == 0) work /= a.sbox[a.has[0] ? 0 : 1].ext[0];
-      int grid = (int)((work + 1023) / 1024);
-      if (grid > 96) grid = 96;
+      long long work;  // threads' worth of work
+      a.nchunks = 1;
+      a.cstride = 0;
+      for (int s = 0; s < 2; ++s) a.soff[s] = a.doff[s] = a.len2[s] = 0;
+      if (d == 0) {
+        work = (long long)a.sbox[a.has[0] ? 0 : 1].ext[1] * a.sbox[a.has[0] ? 0 : 1].ext[2];
+      } else {
+        // whole rows: from the first row of the allocation's y range (d == 2) resp. of the sent layers (d == 1)
+        const int gy = GHOST, gz = c->cfg.dim == 3 ? GHOST : 0;
+        for (int s = 0; s < 2; ++s) {
+          if (!a.has[s]) continue;
+          const int lo = a.sbox[s].lo[d], ext = a.sbox[s].ext[d], dlo = a.dlo[s][d];
+          if (d == 2 || c->cfg.dim == 2) {  // last dimension: one run of `ext` planes (rows in 2D)
+            const long long unit = d == 2 ? g.plane : g.pitch;
+            const long long first = d == 2 ? -(long long)XPAD - (long long)g.pitch * gy : -(long long)XPAD;
+            a.soff[s] = first + unit * lo;
+            a.doff[s] = first + unit * dlo;
+            a.len2[s] = unit * ext / 2;
+            a.nchunks = 1;
+          } else {  // d == 1 in 3D: `ext` rows in every plane (ghost planes included)
+            a.soff[s] = -(long long)XPAD + (long long)g.pitch * lo - g.plane * gz;
+            a.doff[s] = -(long long)XPAD + (long long)g.pitch * dlo - g.plane * gz;
+            a.len2[s] = (long long)g.pitch * ext / 2;
+            a.nchunks = g.n[2] + 2 * gz;
+            a.cstride = g.plane;
+          }
+        }
+        work = (a.len2[0] > a.len2[1] ? a.len2[0] : a.len2[1]) * a.nchunks / 4;
+      }
+      int grid = (int)((work + 255) / 256);
+      if (grid > 592) grid = 592;
       if (grid < 1) grid = 1;
       k_exchange_dim<<<grid, 256, 0, c->stream>>>(a);
       EXAMG_LAUNCH_CHECK(c);
