@@ -83,25 +83,32 @@ __device__ __forceinline__ bool spin_ge(const unsigned long long *p, unsigned lo
 
 struct Box { int lo[3], ext[3]; };
 
-struct ExchArgs {
-  int d;
-  int has[2];               // neighbour on side 0 (-) / 1 (+)
+constexpr int EXF = 4;  // face copies (field components) per exchange kernel
+
+struct FaceCopy {
   const double *src;        // node (0,0,0) of the local buffer
-  double *dst[2];           // node (0,0,0) of the neighbour's buffer
-  Box sbox[2];              // what is sent to side s (local coordinates)
-  int dlo[2][3];            // where it lands (neighbour coordinates)
-  int pitch;
-  long long plane;
+  double *dst[2];           // node (0,0,0) of the neighbour's buffer on side 0 (-) / 1 (+)
+  Box sbox[2];              // d == 0: what is sent to side s (local coordinates) ...
+  int dlo[2][3];            //         ... and where it lands (neighbour coordinates)
   // d >= 1: whole rows travel (x pad included), so a face is `nchunks` runs of `len2` double2
   long long soff[2], doff[2];  // first element of the runs, relative to src / dst[s]
   long long len2[2];
   int nchunks;
-  long long cstride;           // elements between runs
+  long long cstride;        // elements between runs
+  int pitch;
+  long long plane;
+};
+
+struct ExchArgs {
+  int d;
+  int has[2];               // neighbour on side 0 (-) / 1 (+)
+  int nf;
+  FaceCopy f[EXF];
   unsigned long long *flags;      // local flag page
   unsigned long long *pflags[2];  // neighbours' flag pages
 };
 
-__global__ void __launch_bounds__(256) k_exchange_dim(const ExchArgs a) {
+__global__ void __launch_bounds__(256) k_exchange_dim(const __grid_constant__ ExchArgs a) {
   unsigned long long *fl = a.flags;
   const unsigned long long e = *reinterpret_cast<volatile unsigned long long *>(fl + F_EPOCH + a.d) + 1;
   // ready-to-receive: this rank no longer reads the ghost layers of the previous epoch
@@ -109,40 +116,43 @@ __global__ void __launch_bounds__(256) k_exchange_dim(const ExchArgs a) {
     st_release_sys(a.pflags[threadIdx.x] + F_READY + 2 * a.d + (1 - threadIdx.x), e);
   if (threadIdx.x < 2 && a.has[threadIdx.x]) spin_ge(fl + F_READY + 2 * a.d + threadIdx.x, e, fl);
   __syncthreads();
-  for (int s = 0; s < 2; ++s) {
-    if (!a.has[s]) continue;
-    const Box &b = a.sbox[s];
-    double *dst = a.dst[s];
-    if (a.d == 0) {
-      // x faces: rows are 2-3 elements long; let consecutive threads take consecutive rows
-      const long long rows = (long long)b.ext[1] * b.ext[2];
-      for (long long t = blockIdx.x * (long long)blockDim.x + threadIdx.x; t < rows; t += (long long)gridDim.x * blockDim.x) {
-        const int j = (int)(t % b.ext[1]), k = (int)(t / b.ext[1]);
-        const long long so = b.lo[0] + (long long)a.pitch * (b.lo[1] + j) + a.plane * (b.lo[2] + k);
-        const long long dof = a.dlo[s][0] + (long long)a.pitch * (a.dlo[s][1] + j) + a.plane * (a.dlo[s][2] + k);
-        for (int i = 0; i < b.ext[0]; ++i) dst[dof + i] = a.src[so + i];
-      }
-    } else {
-      // y / z faces: runs of whole rows, 128-bit accesses, four independent loads per thread in flight
-      const long long n2 = a.len2[s] * a.nchunks;
-      const long long stride = (long long)gridDim.x * blockDim.x;
-      const double *sb = a.src + a.soff[s];
-      double *db = dst + a.doff[s];
-      for (long long t0 = blockIdx.x * (long long)blockDim.x + threadIdx.x; t0 < n2; t0 += 4 * stride) {
-        double2 v[4];
-        long long off[4];
-#pragma unroll
-        for (int q = 0; q < 4; ++q) {
-          const long long t = t0 + q * stride;
-          if (t < n2) {
-            const long long ch = a.nchunks == 1 ? 0 : t / a.len2[s];
-            off[q] = ch * a.cstride + 2 * (t - ch * a.len2[s]);
-            v[q] = *reinterpret_cast<const double2 *>(sb + off[q]);
-          }
+  for (int fi = 0; fi < a.nf; ++fi) {
+    const FaceCopy &fc = a.f[fi];
+    for (int s = 0; s < 2; ++s) {
+      if (!a.has[s]) continue;
+      double *dst = fc.dst[s];
+      if (a.d == 0) {
+        // x faces: rows are a few elements long; consecutive threads take consecutive rows
+        const Box &b = fc.sbox[s];
+        const long long rows = (long long)b.ext[1] * b.ext[2];
+        for (long long t = blockIdx.x * (long long)blockDim.x + threadIdx.x; t < rows; t += (long long)gridDim.x * blockDim.x) {
+          const int j = (int)(t % b.ext[1]), k = (int)(t / b.ext[1]);
+          const long long so = b.lo[0] + (long long)fc.pitch * (b.lo[1] + j) + fc.plane * (b.lo[2] + k);
+          const long long dof = fc.dlo[s][0] + (long long)fc.pitch * (fc.dlo[s][1] + j) + fc.plane * (fc.dlo[s][2] + k);
+          for (int i = 0; i < b.ext[0]; ++i) dst[dof + i] = fc.src[so + i];
         }
+      } else {
+        // y / z faces: runs of whole rows, 128-bit accesses, four independent loads per thread in flight
+        const long long n2 = fc.len2[s] * fc.nchunks;
+        const long long stride = (long long)gridDim.x * blockDim.x;
+        const double *sb = fc.src + fc.soff[s];
+        double *db = dst + fc.doff[s];
+        for (long long t0 = blockIdx.x * (long long)blockDim.x + threadIdx.x; t0 < n2; t0 += 4 * stride) {
+          double2 v[4];
+          long long off[4];
 #pragma unroll
-        for (int q = 0; q < 4; ++q)
-          if (t0 + q * stride < n2) *reinterpret_cast<double2 *>(db + off[q]) = v[q];
+          for (int q = 0; q < 4; ++q) {
+            const long long t = t0 + q * stride;
+            if (t < n2) {
+              const long long ch = fc.nchunks == 1 ? 0 : t / fc.len2[s];
+              off[q] = ch * fc.cstride + 2 * (t - ch * fc.len2[s]);
+              v[q] = *reinterpret_cast<const double2 *>(sb + off[q]);
+            }
+          }
+#pragma unroll
+          for (int q = 0; q < 4; ++q)
+            if (t0 + q * stride < n2) *reinterpret_cast<double2 *>(db + off[q]) = v[q];
+        }
       }
     }
   }
@@ -341,93 +351,110 @@ static double *peer_buffer(examg_ctx *c, int rank, int field, const double *p) {
   return nullptr;
 }
 
-static int check_comm_error(examg_ctx *c) {
-  (void)c;
-  return EXAMG_OK;
-}
-
-int do_exchange(examg_ctx *c, Field &f, int slot, int depth) {
+// One `communicate` of up to two fields (e.g. Solution and RHS in front of a fused sweep): one
+// kernel and one handshake per dimension for all of them.
+int do_exchange_many(examg_ctx *c, Field *const *fs, const int *slots, const int *depths, int nfields) {
   if (c->world == 1) return EXAMG_OK;  // no neighbour blocks: nothing to exchange
   examg_comm *cm = c->comm;
   if (!cm || !cm->wired) return set_error(EXAMG_ESTATE, "examg_exchange: peers not wired (examg_comm_import)");
-  const int field = (int)(&f - c->fields.data());
-  const LevelGeom &g = *geom(c, f.level);
-  if (depth < 1 || depth > GHOST) return set_error(EXAMG_EINVAL, "examg_exchange: depth %d", depth);
-  const int G = depth;
-  for (int comp = 0; comp < f.ncomp; ++comp) {
-    double *buf = f.slot[slot];
-    for (int d = 0; d < c->cfg.dim; ++d) {
-      if (cm->nbr[d][0] < 0 && cm->nbr[d][1] < 0) continue;
-      ExchArgs a;
-      a.d = d;
-      a.src = buf + (long long)comp * g.vol + g.origin;
-      a.pitch = g.pitch;
-      a.plane = g.plane;
-      a.flags = cm->flags;
-      for (int s = 0; s < 2; ++s) {
-        a.has[s] = cm->nbr[d][s] >= 0;
-        a.dst[s] = nullptr;
-        a.pflags[s] = nullptr;
-        if (!a.has[s]) continue;
-        double *pb = peer_buffer(c, cm->nbr[d][s], field, buf);
-        if (!pb) return set_error(EXAMG_ESTATE, "examg_exchange: field %s@%d is not mapped on rank %d (created after "
-                                  "examg_comm_export?)", f.name.c_str(), f.level, cm->nbr[d][s]);
-        a.dst[s] = pb + (long long)comp * g.vol + g.origin;
-        a.pflags[s] = cm->pflags[cm->nbr[d][s]];
-        for (int q = 0; q < 3; ++q) {  // orthogonal extents: everything incl. ghost layers
-          const int gq = q < c->cfg.dim ? G : 0;
-          a.sbox[s].lo[q] = -gq;
-          a.sbox[s].ext[q] = g.n[q] + 2 * gq;
-          a.dlo[s][q] = -gq;
-        }
-        if (s == 0) {  // to the - neighbour: my layers 1..G -> its n..n+G-1
-          a.sbox[s].lo[d] = 1;
-          a.sbox[s].ext[d] = G;
-          a.dlo[s][d] = g.n[d];
-        } else {       // to the + neighbour: my layers n-1-G..n-1 -> its -G..0 (ghosts + duplicate)
-          a.sbox[s].lo[d] = g.n[d] - 1 - G;
-          a.sbox[s].ext[d] = G + 1;
-          a.dlo[s][d] = -G;
-        }
-      }
-      long long work;  // threads' worth of work
-      a.nchunks = 1;
-      a.cstride = 0;
-      for (int s = 0; s < 2; ++s) a.soff[s] = a.doff[s] = a.len2[s] = 0;
-      if (d == 0) {
-        work = (long long)a.sbox[a.has[0] ? 0 : 1].ext[1] * a.sbox[a.has[0] ? 0 : 1].ext[2];
-      } else {
-        // whole rows: from the first row of the allocation's y range (d == 2) resp. of the sent layers (d == 1)
-        const int gy = GHOST, gz = c->cfg.dim == 3 ? GHOST : 0;
-        for (int s = 0; s < 2; ++s) {
-          if (!a.has[s]) continue;
-          const int lo = a.sbox[s].lo[d], ext = a.sbox[s].ext[d], dlo = a.dlo[s][d];
-          if (d == 2 || c->cfg.dim == 2) {  // last dimension: one run of `ext` planes (rows in 2D)
-            const long long unit = d == 2 ? g.plane : g.pitch;
-            const long long first = d == 2 ? -(long long)XPAD - (long long)g.pitch * gy : -(long long)XPAD;
-            a.soff[s] = first + unit * lo;
-            a.doff[s] = first + unit * dlo;
-            a.len2[s] = unit * ext / 2;
-            a.nchunks = 1;
-          } else {  // d == 1 in 3D: `ext` rows in every plane (ghost planes included)
-            a.soff[s] = -(long long)XPAD + (long long)g.pitch * lo - g.plane * gz;
-            a.doff[s] = -(long long)XPAD + (long long)g.pitch * dlo - g.plane * gz;
-            a.len2[s] = (long long)g.pitch * ext / 2;
-            a.nchunks = g.n[2] + 2 * gz;
-            a.cstride = g.plane;
-          }
-        }
-        work = (a.len2[0] > a.len2[1] ? a.len2[0] : a.len2[1]) * a.nchunks / 4;
-      }
+  for (int d = 0; d < c->cfg.dim; ++d) {
+    if (cm->nbr[d][0] < 0 && cm->nbr[d][1] < 0) continue;
+    ExchArgs a;
+    a.d = d;
+    a.flags = cm->flags;
+    a.nf = 0;
+    long long work = 0;  // threads' worth of work
+    for (int s = 0; s < 2; ++s) {
+      a.has[s] = cm->nbr[d][s] >= 0;
+      a.pflags[s] = a.has[s] ? cm->pflags[cm->nbr[d][s]] : nullptr;
+    }
+    auto flush = [&]() -> int {
+      if (a.nf == 0) return EXAMG_OK;
       int grid = (int)((work + 255) / 256);
       if (grid > 592) grid = 592;
       if (grid < 1) grid = 1;
       k_exchange_dim<<<grid, 256, 0, c->stream>>>(a);
       EXAMG_LAUNCH_CHECK(c);
+      a.nf = 0;
+      work = 0;
+      return EXAMG_OK;
+    };
+    for (int q = 0; q < nfields; ++q) {
+      Field &f = *fs[q];
+      const int field = (int)(&f - c->fields.data());
+      const LevelGeom &g = *geom(c, f.level);
+      const int G = depths[q];
+      if (G < 1 || G > GHOST) return set_error(EXAMG_EINVAL, "examg_exchange: depth %d", G);
+      double *buf = f.slot[slots[q]];
+      for (int comp = 0; comp < f.ncomp; ++comp) {
+        if (a.nf == EXF) {
+          int rc = flush();
+          if (rc) return rc;
+        }
+        FaceCopy &fc = a.f[a.nf++];
+        fc.src = buf + (long long)comp * g.vol + g.origin;
+        fc.pitch = g.pitch;
+        fc.plane = g.plane;
+        fc.nchunks = 1;
+        fc.cstride = 0;
+        for (int s = 0; s < 2; ++s) {
+          fc.dst[s] = nullptr;
+          fc.soff[s] = fc.doff[s] = fc.len2[s] = 0;
+          if (!a.has[s]) continue;
+          double *pb = peer_buffer(c, cm->nbr[d][s], field, buf);
+          if (!pb) return set_error(EXAMG_ESTATE, "examg_exchange: field %s@%d is not mapped on rank %d (created after "
+                                    "examg_comm_export?)", f.name.c_str(), f.level, cm->nbr[d][s]);
+          fc.dst[s] = pb + (long long)comp * g.vol + g.origin;
+          for (int w = 0; w < 3; ++w) {  // orthogonal extents: everything incl. ghost layers
+            const int gw = w < c->cfg.dim ? G : 0;
+            fc.sbox[s].lo[w] = -gw;
+            fc.sbox[s].ext[w] = g.n[w] + 2 * gw;
+            fc.dlo[s][w] = -gw;
+          }
+          if (s == 0) {  // to the - neighbour: my layers 1..G -> its n..n+G-1
+            fc.sbox[s].lo[d] = 1;
+            fc.sbox[s].ext[d] = G;
+            fc.dlo[s][d] = g.n[d];
+          } else {       // to the + neighbour: my layers n-1-G..n-1 -> its -G..0 (ghosts + duplicate)
+            fc.sbox[s].lo[d] = g.n[d] - 1 - G;
+            fc.sbox[s].ext[d] = G + 1;
+            fc.dlo[s][d] = -G;
+          }
+          if (d == 0) {
+            work += (long long)fc.sbox[s].ext[1] * fc.sbox[s].ext[2];
+            continue;
+          }
+          // whole rows: from the first row of the allocation's y range (last dim) resp. of the sent layers
+          const int gy = GHOST, gz = c->cfg.dim == 3 ? GHOST : 0;
+          const int lo = fc.sbox[s].lo[d], ext = fc.sbox[s].ext[d], dlo = fc.dlo[s][d];
+          if (d == 2 || c->cfg.dim == 2) {  // last dimension: one run of `ext` planes (rows in 2D)
+            const long long unit = d == 2 ? g.plane : g.pitch;
+            const long long first = d == 2 ? -(long long)XPAD - (long long)g.pitch * gy : -(long long)XPAD;
+            fc.soff[s] = first + unit * lo;
+            fc.doff[s] = first + unit * dlo;
+            fc.len2[s] = unit * ext / 2;
+            fc.nchunks = 1;
+          } else {  // d == 1 in 3D: `ext` rows in every plane (ghost planes included)
+            fc.soff[s] = -(long long)XPAD + (long long)g.pitch * lo - g.plane * gz;
+            fc.doff[s] = -(long long)XPAD + (long long)g.pitch * dlo - g.plane * gz;
+            fc.len2[s] = (long long)g.pitch * ext / 2;
+            fc.nchunks = g.n[2] + 2 * gz;
+            fc.cstride = g.plane;
+          }
+          work += fc.len2[s] * fc.nchunks / 4;
+        }
+      }
     }
+    int rc = flush();
+    if (rc) return rc;
   }
-  f.halo_depth = depth;
-  return check_comm_error(c);
+  for (int q = 0; q < nfields; ++q) fs[q]->halo_depth = depths[q];
+  return EXAMG_OK;
+}
+
+int do_exchange(examg_ctx *c, Field &f, int slot, int depth) {
+  Field *fp = &f;
+  return do_exchange_many(c, &fp, &slot, &depth, 1);
 }
 
 int finish_sum(examg_ctx *c, int slot, double *out) {

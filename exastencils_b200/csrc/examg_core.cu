@@ -75,7 +75,7 @@ Stencil *examg::get_stencil(examg_ctx *c, int h) {
 
 GridArgs examg::grid_args(const LevelGeom &g) {
   GridArgs a;
-  for (int d = 0; d < 3; ++d) { a.n[d] = g.n[d]; a.lo[d] = g.lo[d]; a.hi[d] = g.hi[d]; a.rlo[d] = g.rlo[d]; }
+  for (int d = 0; d < 3; ++d) { a.n[d] = g.n[d]; a.lo[d] = g.lo[d]; a.hi[d] = g.hi[d]; a.rlo[d] = g.rlo[d]; a.rhi[d] = g.hi[d]; }
   a.pitch = g.pitch;
   a.plane = g.plane;
   a.par = g.par;

@@ -49,7 +49,7 @@ struct LevelGeom {
 struct GridArgs {
   int n[3];
   int lo[3], hi[3];
-  int rlo[3];
+  int rlo[3], rhi[3];  // reduction range (shared nodes counted once, no redundantly computed ghost nodes)
   int pitch;
   long long plane;
   int par;
@@ -166,7 +166,10 @@ int finish_sum(examg_ctx *c, int slot, double *out);
 // ---- internal launchers (defined in the kernel translation units) -----------
 int launch_apply(examg_ctx *c, const Stencil &s, const double *u, double *out);
 int launch_residual(examg_ctx *c, const Stencil &s, const double *u, const double *rhs, double *res,
-                    int red_slot /* <0: no norm */);
+                    int red_slot /* <0: no norm */, int extend = 0);
+// Residual = RHS - A*Solution incl. `communicate Solution`; extend > 0: also on that many layers of the
+// neighbour blocks' nodes (then Residual needs no exchange before the restriction)
+int residual_op(examg_ctx *c, int A, int u, int u_slot, int rhs, int res, double *norm2_out, int extend);
 int launch_jacobi(examg_ctx *c, const Stencil &s, double omega, const double *u, const double *rhs,
                   double *unext);
 int launch_rb(examg_ctx *c, const Stencil &s, double omega, double *u, const double *rhs, int color);
@@ -181,6 +184,8 @@ int launch_cg(examg_ctx *c, const Stencil &s, double *u, const double *rhs, doub
               double *ap, int max_it, double rel_tol);
 // communicate: `depth` ghost layers (+ the duplicate layer) per side, 1 <= depth <= GHOST
 int do_exchange(examg_ctx *c, Field &f, int slot, int depth = 1);
+// several fields in one handshake per dimension
+int do_exchange_many(examg_ctx *c, Field *const *fs, const int *slots, const int *depths, int nfields);
 // agglomeration of the coarse levels onto rank 0 (examg_comm.cu)
 int copy_field_device(examg_ctx *c, int field, int slot, double *dense, bool to_field);
 int comm_agg_setup(examg_ctx *c, int level);

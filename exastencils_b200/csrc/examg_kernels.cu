@@ -45,7 +45,9 @@ k_stencil(const GridArgs g, const __grid_constant__ StencilArgs st, const double
         } else if (MODE == M_RESIDUAL || MODE == M_RESNORM) {
           const double r = rhs[p] - acc;
           out[p] = r;
-          if (MODE == M_RESNORM && i >= g.rlo[0] && j >= g.rlo[1] && k >= g.rlo[2]) dd_add(part, r * r);
+          if (MODE == M_RESNORM && i >= g.rlo[0] && j >= g.rlo[1] && k >= g.rlo[2] && i < g.rhi[0] && j < g.rhi[1] &&
+              k < g.rhi[2])
+            dd_add(part, r * r);
         } else {
           const double ww = VAR ? w / sf[st.centre * sfvol + p] : w;  // w = omega (VAR) or omega/diag
           const double r = rhs[p] - acc;
@@ -191,14 +193,19 @@ k_dirichlet(const BcArgs a, const __grid_constant__ BcProg pr, int use_prog, dou
 
 template <int MODE>
 static int launch_stencil(examg_ctx *c, const Stencil &s, const double *u, const double *rhs, double *out,
-                          double omega, int color, int red_slot) {
+                          double omega, int color, int red_slot, int extend = 0) {
   const LevelGeom &g = *geom(c, s.level);
-  const GridArgs ga = grid_args(g);
+  GridArgs ga = grid_args(g);
+  // `extend` layers of the neighbour blocks' nodes are computed redundantly (saves their exchange)
+  for (int d = 0; d < c->cfg.dim && extend > 0; ++d) {
+    if (c->nb[d][0]) ga.lo[d] -= extend;
+    if (c->nb[d][1]) ga.hi[d] += extend;
+  }
   const StencilArgs sa = stencil_args(g, s);
   const bool var = s.coeff_field >= 0;
   const double *sf = nullptr;
   if (var) sf = field_ptr(c, &c->fields[s.coeff_field], 0, 0);
-  int ex = g.hi[0] - g.lo[0], ey = g.hi[1] - g.lo[1], ez = g.hi[2] - g.lo[2];
+  int ex = ga.hi[0] - ga.lo[0], ey = ga.hi[1] - ga.lo[1], ez = ga.hi[2] - ga.lo[2];
   if (ex <= 0 || ey <= 0 || ez <= 0) {
     if (MODE == M_RESNORM) {
       EXAMG_CUDA(cudaMemsetAsync(c->red_out + red_slot, 0, sizeof(dd), c->stream));
@@ -242,9 +249,9 @@ int launch_apply(examg_ctx *c, const Stencil &s, const double *u, double *out) {
   return launch_stencil<M_APPLY>(c, s, u, nullptr, out, 0.0, 0, -1);
 }
 int launch_residual_generic(examg_ctx *c, const Stencil &s, const double *u, const double *rhs, double *res,
-                            int red_slot) {
-  if (red_slot >= 0) return launch_stencil<M_RESNORM>(c, s, u, rhs, res, 0.0, 0, red_slot);
-  return launch_stencil<M_RESIDUAL>(c, s, u, rhs, res, 0.0, 0, -1);
+                            int red_slot, int extend) {
+  if (red_slot >= 0) return launch_stencil<M_RESNORM>(c, s, u, rhs, res, 0.0, 0, red_slot, extend);
+  return launch_stencil<M_RESIDUAL>(c, s, u, rhs, res, 0.0, 0, -1, extend);
 }
 int launch_jacobi_generic(examg_ctx *c, const Stencil &s, double omega, const double *u, const double *rhs,
                           double *unext) {

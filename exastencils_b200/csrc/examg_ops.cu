@@ -9,7 +9,7 @@ using namespace examg;
 
 namespace examg {
 // generic launchers (examg_kernels.cu, examg_transfer.cu)
-int launch_residual_generic(examg_ctx *c, const Stencil &s, const double *u, const double *rhs, double *res, int red_slot);
+int launch_residual_generic(examg_ctx *c, const Stencil &s, const double *u, const double *rhs, double *res, int red_slot, int extend);
 int launch_jacobi_generic(examg_ctx *c, const Stencil &s, double omega, const double *u, const double *rhs, double *unext);
 int launch_rb_generic(examg_ctx *c, const Stencil &s, double omega, double *u, const double *rhs, int color);
 int launch_restrict_generic(examg_ctx *c, int lvl_fine, double scale, const double *rf, double *rhsc);
@@ -22,9 +22,10 @@ bool fused_rb_usable(examg_ctx *c, const Stencil &s, const Field &fu);
 int launch_rb_fused(examg_ctx *c, const Stencil &s, double omega, Field &fu, const double *rhs, int nsweeps, int *done);
 int rb_fused_plan(int nsweeps);
 
-int launch_residual(examg_ctx *c, const Stencil &s, const double *u, const double *rhs, double *res, int red_slot) {
+int launch_residual(examg_ctx *c, const Stencil &s, const double *u, const double *rhs, double *res, int red_slot,
+                    int extend) {
   if (fast7_usable(c, s)) return fast7_residual(c, s, u, rhs, res, red_slot);
-  return launch_residual_generic(c, s, u, rhs, res, red_slot);
+  return launch_residual_generic(c, s, u, rhs, res, red_slot, extend);
 }
 int launch_jacobi(examg_ctx *c, const Stencil &s, double omega, const double *u, const double *rhs, double *unext) {
   return launch_jacobi_generic(c, s, omega, u, rhs, unext);
@@ -52,6 +53,28 @@ int launch_prolong(examg_ctx *c, int lvl_fine, const double *uc, double *uf) {
 #define CHECK_LEVEL(f, lvl) \
   if ((f)->level != (lvl)) return set_error(EXAMG_EINVAL, "%s: field %s lives on level %d, not %d", __func__, (f)->name.c_str(), (f)->level, lvl)
 
+int examg::residual_op(examg_ctx *c, int A, int u, int u_slot, int rhs, int res, double *norm2_out, int extend) {
+  GET_STENCIL(s, A); GET_FIELD(fu, u); GET_FIELD(fr, rhs); GET_FIELD(fo, res);
+  CHECK_SLOT(fu, u_slot); CHECK_LEVEL(fu, s->level); CHECK_LEVEL(fr, s->level); CHECK_LEVEL(fo, s->level);
+  if (fu == fo) return set_error(EXAMG_EINVAL, "examg_residual: Residual aliases Solution");
+  if (c->world == 1) extend = 0;
+  const int us = u_slot < 0 ? fu->cur : u_slot;
+  int rc;
+  if (extend > 0 && fr->halo_depth < extend) {  // communicate Solution (and RHS where its ghost layers are stale)
+    Field *fs[2] = {fu, fr};
+    const int slots[2] = {us, fr->cur}, depths[2] = {extend + 1, extend};
+    rc = do_exchange_many(c, fs, slots, depths, 2);
+  } else {
+    rc = do_exchange(c, *fu, us, extend + 1);
+  }
+  if (rc) return rc;
+  rc = launch_residual(c, *s, field_ptr(c, fu, u_slot), field_ptr(c, fr, -1), field_ptr(c, fo, -1),
+                       norm2_out ? 0 : -1, extend);
+  fo->halo_depth = extend;
+  if (rc || !norm2_out) return rc;
+  return finish_sum(c, 0, norm2_out);
+}
+
 extern "C" {
 
 int examg_apply(examg_ctx *c, int A, int u, int u_slot, int out) {
@@ -65,16 +88,7 @@ int examg_apply(examg_ctx *c, int A, int u, int u_slot, int out) {
 }
 
 int examg_residual(examg_ctx *c, int A, int u, int u_slot, int rhs, int res, double *norm2_out) {
-  GET_STENCIL(s, A); GET_FIELD(fu, u); GET_FIELD(fr, rhs); GET_FIELD(fo, res);
-  CHECK_SLOT(fu, u_slot); CHECK_LEVEL(fu, s->level); CHECK_LEVEL(fr, s->level); CHECK_LEVEL(fo, s->level);
-  if (fu == fo) return set_error(EXAMG_EINVAL, "examg_residual: Residual aliases Solution");
-  int rc = do_exchange(c, *fu, u_slot < 0 ? fu->cur : u_slot);  // communicate Solution
-  if (rc) return rc;
-  fo->halo_depth = 0;
-  rc = launch_residual(c, *s, field_ptr(c, fu, u_slot), field_ptr(c, fr, -1), field_ptr(c, fo, -1),
-                           norm2_out ? 0 : -1);
-  if (rc || !norm2_out) return rc;
-  return finish_sum(c, 0, norm2_out);
+  return residual_op(c, A, u, u_slot, rhs, res, norm2_out, 0);
 }
 
 int examg_smooth_jacobi(examg_ctx *c, int A, int u, int rhs, double omega, int nsweeps) {
@@ -116,9 +130,15 @@ int examg_smooth_rbgs(examg_ctx *c, int A, int u, int rhs, double omega, int nsw
         // one launch does `plan` sweeps = 2*plan half-sweeps: that many ghost layers of Solution and one
         // less of RHS (the redundant updates in the ghost layers read RHS there)
         const int plan = rb_fused_plan(nsweeps - it);
-        int rc = do_exchange(c, *fu, fu->cur, 2 * plan), done = 0;
+        int rc, done = 0;
+        if (c->world > 1 && fr->halo_depth < 2 * plan - 1) {  // Solution and RHS in one handshake
+          Field *fs[2] = {fu, fr};
+          const int slots[2] = {fu->cur, fr->cur}, depths[2] = {2 * plan, 2 * plan - 1};
+          rc = do_exchange_many(c, fs, slots, depths, 2);
+        } else {
+          rc = do_exchange(c, *fu, fu->cur, 2 * plan);
+        }
         if (rc) return rc;
-        if (c->world > 1 && fr->halo_depth < 2 * plan - 1 && (rc = do_exchange(c, *fr, fr->cur, 2 * plan - 1))) return rc;
         if ((rc = launch_rb_fused(c, *s, omega, *fu, field_ptr(c, fr, -1), nsweeps - it, &done))) return rc;
         it += done;
         fu->halo_depth = 0;
@@ -137,7 +157,7 @@ int examg_smooth_rbgs(examg_ctx *c, int A, int u, int rhs, double omega, int nsw
 int examg_restrict(examg_ctx *c, int res_fine, int rhs_coarse, double scale) {
   GET_FIELD(ff, res_fine); GET_FIELD(fc, rhs_coarse);
   if (fc->level != ff->level - 1) return set_error(EXAMG_EINVAL, "examg_restrict: levels %d -> %d", ff->level, fc->level);
-  int rc = do_exchange(c, *ff, ff->cur);  // communicate Residual
+  int rc = ff->halo_depth >= 1 ? EXAMG_OK : do_exchange(c, *ff, ff->cur);  // communicate Residual
   if (rc) return rc;
   fc->halo_depth = 0;
   return launch_restrict(c, ff->level, scale, field_ptr(c, ff, -1), field_ptr(c, fc, -1));
