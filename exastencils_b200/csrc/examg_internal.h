@@ -120,6 +120,8 @@ struct examg_ctx {
   int *int_host = nullptr;        // pinned
   struct examg_comm *comm = nullptr;
   std::vector<examg::Block> blocks;
+  double *stage = nullptr;        // dense staging array of host <-> field transfers
+  size_t stage_doubles = 0;
 };
 
 namespace examg {

@@ -221,6 +221,11 @@ int examg_exchange(examg_ctx *c, int field, int slot) {
   return do_exchange(c, *f, slot < 0 ? f->cur : slot);
 }
 
+int examg_exchange_depth(examg_ctx *c, int field, int slot, int depth) {
+  GET_FIELD(f, field); CHECK_SLOT(f, slot);
+  return do_exchange(c, *f, slot < 0 ? f->cur : slot, depth);
+}
+
 int examg_cg_coarse(examg_ctx *c, int A, int u, int rhs, int res, int p, int ap, int max_it, double rel_tol,
                     int *iters_out) {
   GET_STENCIL(s, A); GET_FIELD(fu, u); GET_FIELD(fr, rhs); GET_FIELD(fres, res); GET_FIELD(fp, p); GET_FIELD(fap, ap);

@@ -98,6 +98,7 @@ SIGNATURES = {
     "examg_axpy": (C.c_int, [C.c_void_p, C.c_double, C.c_int, C.c_int, C.c_int, C.c_int]),
     "examg_xpay": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_double, C.c_int, C.c_int]),
     "examg_exchange": (C.c_int, [C.c_void_p, C.c_int, C.c_int]),
+    "examg_exchange_depth": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int]),
     "examg_cg_coarse": (C.c_int, [C.c_void_p] + [C.c_int] * 7 + [C.c_double, _ip]),
     "examg_solver_create": (C.c_void_p, [C.c_void_p, C.POINTER(CycleDesc)]),
     "examg_solver_destroy": (C.c_int, [C.c_void_p]),
@@ -313,8 +314,8 @@ class Context:
     def xpay(self, x, beta, y, x_slot=-1, y_slot=-1):
         check(self.L.examg_xpay(self.h, x, x_slot, beta, y, y_slot))
 
-    def exchange(self, f, slot=-1):
-        check(self.L.examg_exchange(self.h, f, slot))
+    def exchange(self, f, slot=-1, depth=1):
+        check(self.L.examg_exchange_depth(self.h, f, slot, depth))
 
     def cg_coarse(self, A, u, rhs, res, p, ap, max_it, rel_tol, want_iters=True):
         its = C.c_int()

@@ -169,6 +169,9 @@ int examg_xpay(examg_ctx *ctx, int x, int x_slot, double beta, int y, int y_slot
 /* exch<F>_<lvl>(slot): duplicate-layer sync then ghost-layer exchange, one
  * dimension after the other (C/s/e/communication/ir/IR_CommunicateFunction.scala:412-470) */
 int examg_exchange(examg_ctx *ctx, int field, int slot);
+/* same with `depth` ghost layers per side (1..4): what a sweep that fuses depth/2 red-black sweeps consumes
+ * (the contraction extents of C/s/e/baseExt/ir/IR_ContractingLoop.scala:48-90) */
+int examg_exchange_depth(examg_ctx *ctx, int field, int slot, int depth);
 /* mgCycle@coarsest: un-preconditioned CG, stops at ||r|| <= rel_tol*||r0|| or
  * max_it (Benchmark/Poisson3D/3D_FD_Poisson_fromL4.exa4:152-201).
  * Runs entirely on the device; *iters_out (nullable) synchronises.          */
