@@ -44,18 +44,28 @@ int launch_coarse_cycle(examg_ctx *c, const examg_cycle_desc &d, int top, const 
                         const int *rhs, const int *res, int cg_p, int cg_ap);
 }
 
-// (active slot, shadow parity) of a Solution field, as recorded in the graph keys
+// State of a Solution field as recorded in the graph keys: the active slot and which allocation
+// (index into Field::orig) every slot and the shadow currently point at -- the fused sweeps
+// exchange buffers instead of copying (RBGS: slot <-> shadow, Jacobi with an even number of sweeps:
+// slot <-> slot).
+static int field_state(const Field &f) {
+  auto index_of = [&](const double *p) {
+    for (int i = 0; i < 5; ++i)
+      if (p && f.orig[i] == p) return i;
+    return 0;
+  };
+  int code = f.cur, mult = 4;
+  for (int i = 0; i < 4; ++i, mult *= 5) code += mult * index_of(f.slot[i]);
+  return code + mult * index_of(f.shadow);
+}
+
 static void restore_state(Field &f, int state) {
-  const int cur = state >> 1;
-  const bool swapped = state & 1;
-  if (f.swapped != swapped) {  // the buffers of the slot that was active while sweeping are exchanged
-    // fused sweeps only run on single-slot (RBGS) fields, so the slot in question is slot[f.cur]
-    double *t = f.slot[f.cur];
-    f.slot[f.cur] = f.shadow;
-    f.shadow = t;
-    f.swapped = swapped;
-  }
-  f.cur = cur;
+  f.cur = state % 4;
+  state /= 4;
+  for (int i = 0; i < 4; ++i, state /= 5)
+    if (f.slot[i]) f.slot[i] = f.orig[state % 5];
+  if (f.shadow) f.shadow = f.orig[state % 5];
+  f.swapped = f.shadow && f.shadow != f.orig[4];
 }
 
 static int lv(examg_solver *s, int level) { return level - s->c->cfg.min_level; }
@@ -246,12 +256,12 @@ int examg_solver_field(examg_solver *s, int level, int which) {
   return set_error(EXAMG_EINVAL, "examg_solver_field: no field %d on level %d", which, level);
 }
 
-// State that decides which kernels a cycle launches and on which buffers: (active slot, shadow
-// parity) of every Solution field -- of the agglomerated solver too -- and how many ghost layers
+// State that decides which kernels a cycle launches and on which buffers: (active slot, buffer
+// permutation) of every Solution field -- of the agglomerated solver too -- and how many ghost layers
 // of every RHS field are valid (a cycle skips the RHS exchange when they already are).
 static void cycle_state(examg_solver *s, std::vector<int> &key) {
   examg_ctx *c = s->c;
-  for (int h : s->sol) key.push_back(c->fields[h].cur * 2 + (c->fields[h].swapped ? 1 : 0));
+  for (int h : s->sol) key.push_back(field_state(c->fields[h]));
   for (int h : s->rhs) key.push_back(c->fields[h].halo_depth);
   for (int h : s->sol) key.push_back(c->fields[h].halo_depth);
   for (int h : s->res) key.push_back(c->fields[h].halo_depth);

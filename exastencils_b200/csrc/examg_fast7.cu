@@ -319,6 +319,12 @@ k_rbw(const __grid_constant__ CUtensorMap tm_u, const __grid_constant__ CUtensor
   }
 }
 
+}  // namespace examg
+
+#include "examg_jac7.cuh"
+
+namespace examg {
+
 // ---- host side -------------------------------------------------------------------
 
 typedef CUresult (*EncodeTiledFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *,
@@ -487,6 +493,99 @@ int launch_rb_fused(examg_ctx *c, const Stencil &s, double omega, Field &fu, con
   }
   *done = 1;
   return launch_rbw<2>(c, s, omega, fu, rhs);
+}
+
+// ---- Jacobi: S sweeps per pass (examg_jac7.cuh) ------------------------------------
+
+// largest number of Jacobi sweeps fused into one pass (EXAMG_JAC_FUSE_SWEEPS = 1..3; 0: generic kernel)
+static int max_jac_sweeps() {
+  static int v = -1;
+  if (v < 0) {
+    v = env_flag("EXAMG_JAC_FUSE_SWEEPS", 3);
+    v = v < 0 ? 0 : v > 3 ? 3 : v;
+  }
+  return v;
+}
+
+bool fused_jac_usable(examg_ctx *c, const Stencil &s, const Field &fu) {
+  return max_jac_sweeps() > 0 && fu.nslots == 2 && fused_rb_usable(c, s, fu);
+}
+
+// sweeps the next launch will fuse
+int jac_fused_plan(int nsweeps) {
+  const int m = max_jac_sweeps();
+  if (nsweeps <= m) return nsweeps;
+  return nsweeps == m + 1 && m == 3 ? 2 : m;  // 4 = 2 + 2 rather than 3 + 1
+}
+
+template <int S>
+static int launch_jacw(examg_ctx *c, const Stencil &s, double omega, Field &fu, const double *rhs) {
+  static bool attr_set = false;
+  if (!attr_set) {
+    EXAMG_CUDA(cudaFuncSetAttribute(k_jacw<S, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)jacw_smem<S>()));
+    EXAMG_CUDA(cudaFuncSetAttribute(k_jacw<S, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)jacw_smem<S>()));
+    attr_set = true;
+  }
+  const LevelGeom &g = *geom(c, s.level);
+  const int nxt = (fu.cur + 1) % 2;
+  CUtensorMap tm_u, tm_f;
+  int rc = make_plane_map(g, fu.slot[fu.cur], &tm_u);
+  if (rc) return rc;
+  if ((rc = make_plane_map(g, rhs - g.origin, &tm_f))) return rc;
+  RbwArgs a;
+  for (int d = 0; d < 3; ++d) {
+    a.n[d] = g.n[d];
+    a.ulo[d] = g.lo[d];
+    a.uhi[d] = g.hi[d];
+    a.elo[d] = c->nb[d][0] ? 1 : 0;
+    a.ehi[d] = c->nb[d][1] ? 1 : 0;
+  }
+  a.pitch = g.pitch;
+  a.plane = g.plane;
+  a.tiles_x = (g.n[0] + jacw_iw<S>() - 1) / jacw_iw<S>();
+  const int tiles_y = (g.n[1] + jacw_ih<S>() - 1) / jacw_ih<S>();
+  a.nzp = g.n[2];
+  a.tiles = a.tiles_x * tiles_y;
+  const long long units = (long long)a.tiles * a.nzp;
+  a.par = g.par;
+  a.pf = 0;
+  for (int k = 0; k < 7; ++k) a.coef[k] = s.coef[k];
+  const int ord = stencil_order(s);
+  a.w = omega / s.coef[s.centre];
+  int dev = 0, nsm = 148;
+  cudaGetDevice(&dev);
+  cudaDeviceGetAttribute(&nsm, cudaDevAttrMultiProcessorCount, dev);
+  long long grid = nsm;
+  const long long min_units = 8 * S;  // at least this many planes per CTA (2S are restart overhead)
+  if (grid > units / min_units) grid = units / min_units;
+  if (grid < 1) grid = 1;
+  if (ord == 0)
+    k_jacw<S, 0><<<(int)grid, RNT, jacw_smem<S>(), c->stream>>>(tm_u, tm_f, a, fu.slot[nxt] + g.origin);
+  else
+    k_jacw<S, 1><<<(int)grid, RNT, jacw_smem<S>(), c->stream>>>(tm_u, tm_f, a, fu.slot[nxt] + g.origin);
+  EXAMG_LAUNCH_CHECK(c);
+  if (S & 1) {
+    fu.cur = nxt;  // advance Solution an odd number of times
+  } else {
+    // an even number of `advance`s: the active slot stays, the result sits in the other buffer.
+    // Exchange the two buffers (Solution<next> then holds the input of the pass, not the last-but-one sweep).
+    double *t = fu.slot[fu.cur];
+    fu.slot[fu.cur] = fu.slot[nxt];
+    fu.slot[nxt] = t;
+  }
+  return EXAMG_OK;
+}
+
+// up to nsweeps Jacobi sweeps in one launch; *done = sweeps done
+int launch_jac_fused(examg_ctx *c, const Stencil &s, double omega, Field &fu, const double *rhs, int nsweeps,
+                     int *done) {
+  const int plan = jac_fused_plan(nsweeps);
+  *done = plan;
+  switch (plan) {
+    case 1: return launch_jacw<1>(c, s, omega, fu, rhs);
+    case 2: return launch_jacw<2>(c, s, omega, fu, rhs);
+    default: return launch_jacw<3>(c, s, omega, fu, rhs);
+  }
 }
 
 bool fast7_usable(examg_ctx *c, const Stencil &s) { (void)c; (void)s; return false; }

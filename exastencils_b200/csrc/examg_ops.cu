@@ -21,6 +21,9 @@ int fast7_rb(examg_ctx *c, const Stencil &s, double omega, double *u, const doub
 bool fused_rb_usable(examg_ctx *c, const Stencil &s, const Field &fu);
 int launch_rb_fused(examg_ctx *c, const Stencil &s, double omega, Field &fu, const double *rhs, int nsweeps, int *done);
 int rb_fused_plan(int nsweeps);
+bool fused_jac_usable(examg_ctx *c, const Stencil &s, const Field &fu);
+int launch_jac_fused(examg_ctx *c, const Stencil &s, double omega, Field &fu, const double *rhs, int nsweeps, int *done);
+int jac_fused_plan(int nsweeps);
 
 int launch_residual(examg_ctx *c, const Stencil &s, const double *u, const double *rhs, double *res, int red_slot,
                     int extend) {
@@ -95,6 +98,25 @@ int examg_smooth_jacobi(examg_ctx *c, int A, int u, int rhs, double omega, int n
   GET_STENCIL(s, A); GET_FIELD(fu, u); GET_FIELD(fr, rhs);
   CHECK_LEVEL(fu, s->level); CHECK_LEVEL(fr, s->level);
   if (fu->nslots < 2) return set_error(EXAMG_EINVAL, "examg_smooth_jacobi: Solution needs 2 slots");
+  if (fused_jac_usable(c, *s, *fu)) {  // up to three sweeps in one pass over HBM (examg_jac7.cuh)
+    for (int it = 0; it < nsweeps;) {
+      // `plan` sweeps need that many ghost layers of Solution and one less of RHS (redundant updates there)
+      const int plan = jac_fused_plan(nsweeps - it);
+      int rc, done = 0;
+      if (c->world > 1 && plan > 1 && fr->halo_depth < plan - 1) {
+        Field *fs[2] = {fu, fr};
+        const int slots[2] = {fu->cur, fr->cur}, depths[2] = {plan, plan - 1};
+        rc = do_exchange_many(c, fs, slots, depths, 2);
+      } else {
+        rc = do_exchange(c, *fu, fu->cur, plan);
+      }
+      if (rc) return rc;
+      if ((rc = launch_jac_fused(c, *s, omega, *fu, field_ptr(c, fr, -1), nsweeps - it, &done))) return rc;
+      it += done;
+      fu->halo_depth = 0;
+    }
+    return EXAMG_OK;
+  }
   for (int it = 0; it < nsweeps; ++it) {
     int rc = do_exchange(c, *fu, fu->cur);
     if (rc) return rc;

@@ -271,3 +271,42 @@ def test_error_convention():
     with pytest.raises(rt.ExaMGError):
         ctx.upload(99, np.zeros(ctx.shape(3)))
     ctx.close()
+
+
+_ORDERS = {
+    # declaration order of the stencil entries = floating-point association (DESIGN.md "Arithmetic contract")
+    "bench": [(0, 0, 0), (-1, 0, 0), (1, 0, 0), (0, -1, 0), (0, 1, 0), (0, 0, -1), (0, 0, 1)],
+    "testing": [(0, 0, 0), (1, 0, 0), (-1, 0, 0), (0, 1, 0), (0, -1, 0), (0, 0, 1), (0, 0, -1)],
+}
+
+
+@pytest.mark.parametrize("cells,lvl", [((1, 1, 1), 6), ((5, 3, 2), 5), ((1, 1, 1), 7), ((3, 1, 2), 6)])
+@pytest.mark.parametrize("order", ["bench", "testing"])
+def test_jacobi_temporal_blocking(cells, lvl, order, oracle):
+    """nu Jacobi sweeps with `advance` in between (Testing/Opts/tempBlock.exa4:144-153): libexamg does up to three
+    per pass over HBM (examg_jac7.cuh); fields must be bit-identical to nu separate sweeps of the oracle."""
+    og = oracle
+    ctx = _ctx(3, cells, lvl, lvl)
+    shape = ctx.shape(lvl)
+    offs = _ORDERS[order]
+    seed = 1000 * lvl + 10 * sum(cells) + (order == "testing")
+    coef = _rand(7, seed)
+    coef[0] = 4.0 + abs(coef[0])
+    A = ctx.stencil_const(lvl, offs, coef)
+    st = og.Stencil.make(offs, coef)
+    fu = ctx.field_create("u", lvl, 2, 1)
+    ff = ctx.field_create("rhs", lvl, 1, 1)
+    u, rhs = _rand(shape, seed + 1), _rand(shape, seed + 2)
+    ctx.upload(ff, rhs)
+    omega = 0.8
+    for nu in (2, 3, 4, 5, 1, 7):
+        ctx.upload(fu, u, 0)
+        ctx.upload(fu, u, 1)
+        cur = ctx.field_active_slot(fu)
+        ctx.smooth_jacobi(A, fu, ff, omega, nu)
+        assert ctx.field_active_slot(fu) == (cur + nu) % 2
+        e = u
+        for _ in range(nu):
+            e = og.smooth_jacobi(st, omega, e, rhs, None)
+        assert np.array_equal(ctx.download(fu, lvl), e), "nu = %d" % nu
+    ctx.close()

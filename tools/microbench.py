@@ -81,6 +81,19 @@ def main():
     timeit("mgCycle@%d (coarse part)" % (L - 1), lambda: prog2.ctx.L.examg_solver_vcycle(prog2._solver, L - 1), cyc_bytes,
            npts=pts / 8)
     prog.close()
+    if args.level > 9:
+        return
+    # Jacobi (two Solution slots): 1, 2 and 3 sweeps per pass over HBM
+    jp = MultigridProgram(3, (1, 1, 1), 2, L, smoother="jacobi", omega=0.8, nu_pre=args.nu, nu_post=args.nu,
+                          stream=stream.cuda_stream)
+    set_benchmark_problem(jp)
+    ctx = jp.ctx
+    A, u, f = jp.stencil[L], jp.f_solution[L], jp.f_rhs[L]
+    for nu in (1, 2, 3, 4):
+        timeit("jacobi %d sweeps (24 B/pt/sweep)" % nu, lambda: ctx.smooth_jacobi(A, u, f, 0.8, nu), 24.0 * nu)
+    set_benchmark_problem(jp)
+    timeit("Jacobi V(%d,%d) cycle (%.1f B/pt)" % (args.nu, args.nu, cyc_bytes), lambda: jp.vcycle(), cyc_bytes)
+    jp.close()
 
 
 if __name__ == "__main__":
