@@ -144,6 +144,44 @@ void og_solver_vcycle(og_solver *s, int lvl);
 /* number of CG iterations done by the most recent coarse solve */
 int og_solver_last_cg_iters(const og_solver *s);
 
+
+/* ---- optical flow: 2D cell-centred, two coupled unknowns, 2x2 block smoother ------------------
+ * (examg_oracle_optflow.c; Benchmark/OptFlow2D/2D_FD_OptFlow.exa4, Testing/Application/OpticalFlow2D.exa4).
+ * Dense arrays: (ny+2) x (nx+2), one ghost cell per side. */
+void ogf_neumann(int nx, int ny, double *a);
+void ogf_apply(int nx, int ny, const double L[5], double a2, const double *cuu, const double *cuv,
+               const double *cvv, const double *u, const double *v, double *ou, double *ov);
+void ogf_residual(int nx, int ny, const double L[5], double a2, const double *cuu, const double *cuv,
+                  const double *cvv, const double *u, const double *v, const double *fu, const double *fv,
+                  double *ru, double *rv);
+void ogf_smooth_color(int nx, int ny, const double L[5], double a2, const double *cuu, const double *cuv,
+                      const double *cvv, double *u, double *v, const double *fu, const double *fv,
+                      double relax, int color);
+void ogf_restrict(int nxc, int nyc, const double *fine, double *coarse);
+void ogf_prolong_add(int nxc, int nyc, const double *coarse, double *fine);
+double ogf_dot2(int nx, int ny, const double *a, const double *b, const double *c, const double *d);
+
+typedef struct {
+  int F[2];              /* cells per dim at level 0 */
+  int min_level, max_level;
+  double alpha;          /* Globals { Val alpha } */
+  double relax;          /* solve locally relax ... */
+  int nu_pre, nu_post;
+  int cg_max_it;
+  double cg_rel_tol;
+} ogf_config;
+enum { OGF_U = 0, OGF_V, OGF_RHS_U, OGF_RHS_V, OGF_RES_U, OGF_RES_V, OGF_CUU, OGF_CUV, OGF_CVV, OGF_IMG0, OGF_IMG1 };
+typedef struct ogf_solver ogf_solver;
+ogf_solver *ogf_solver_create(const ogf_config *cfg);
+void ogf_solver_destroy(ogf_solver *s);
+void ogf_solver_dims(const ogf_solver *s, int lvl, int n[2]);
+double *ogf_solver_field(ogf_solver *s, int lvl, int which);
+void ogf_solver_init_images(ogf_solver *s);   /* initImgs@finest */
+void ogf_solver_init_fields(ogf_solver *s);   /* apply bc to the images, initGradients@all, rhs */
+double ogf_solver_update_residual_norm(ogf_solver *s, int lvl);
+void ogf_solver_vcycle(ogf_solver *s, int lvl);
+int ogf_solver_last_cg_iters(const ogf_solver *s);
+
 /* printWithReducedPrec (C/s/e/util/ir/IR_ResolvePrintWithReducedPrec.scala:33-78):
  * formats like std::cout with precision p (default float notation). */
 void og_print_reduced_prec(double v, char *buf, size_t buflen);

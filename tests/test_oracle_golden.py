@@ -43,3 +43,29 @@ def test_print_reduced_prec(oracle):
     assert p(5.55e-12) == "6e-12"
     assert p(5.55e-11) == "5.5e-11" or p(5.55e-11) == "5.6e-11"
     assert p(5.554e-10) == "5.55e-10"
+
+
+def optflow_history(solver, fmt, max_it=128, reduction=1e-5):
+    """doSolve@finest of Testing/Application/OpticalFlow2D.exa4: printed residual norms."""
+    r0 = solver.update_residual_norm()
+    out, r, it = [fmt(r0)], r0, 0
+    while it < max_it and r > reduction * r0:
+        it += 1
+        solver.vcycle()
+        r = solver.update_residual_norm()
+        out.append(fmt(r))
+    return out
+
+
+def test_golden_optical_flow_2d(oracle):
+    """Testing/Application/OpticalFlow2D.{exa4,knowledge,results}: levels 2..8, V(3,3) red-black 2x2 block smoother,
+    CG on 4x4 cells; pins examg_oracle_optflow.c."""
+    import os
+    from oracle import optflow
+    s = optflow.Solver((1, 1), 2, 8, alpha=1.0, relax=1.0, nu_pre=3, nu_post=3, cg_max_it=128, cg_rel_tol=1e-3)
+    s.init_images()
+    s.init_fields()
+    got = optflow_history(s, oracle.print_reduced_prec)
+    s.close()
+    path = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "Application_OpticalFlow2D.results")
+    assert got == open(path).read().split()
