@@ -247,7 +247,25 @@ long long examg_device_bytes(examg_ctx *c) { return c ? c->dev_bytes : -1; }
 
 // ---- fields -------------------------------------------------------------------
 
+static int field_create(examg_ctx *c, const char *name, int level, int num_slots, int ncomp, int loc);
+
 int examg_field_create(examg_ctx *c, const char *name, int level, int num_slots, int ncomp) {
+  return field_create(c, name, level, num_slots, ncomp, 0);
+}
+
+int examg_field_create_cell(examg_ctx *c, const char *name, int level, int num_slots, int ncomp) {
+  if (c && c->world > 1) return set_error(EXAMG_EUNSUP, "examg_field_create_cell: cell fields are single-block so far");
+  return field_create(c, name, level, num_slots, ncomp, 1);
+}
+
+int examg_level_cells(examg_ctx *c, int level, int n[3]) {
+  const LevelGeom *g = geom(c, level);
+  if (!g || !n) return set_error(EXAMG_EINVAL, "examg_level_cells: level %d", level);
+  for (int d = 0; d < 3; ++d) n[d] = d < c->cfg.dim ? g->n[d] - 1 : 1;
+  return EXAMG_OK;
+}
+
+static int field_create(examg_ctx *c, const char *name, int level, int num_slots, int ncomp, int loc) {
   const LevelGeom *g = geom(c, level);
   if (!g) return set_error(EXAMG_EINVAL, "examg_field_create: level %d", level);
   if (num_slots < 1 || num_slots > 4 || ncomp < 1 || ncomp > EXAMG_MAX_STENCIL)
@@ -258,6 +276,7 @@ int examg_field_create(examg_ctx *c, const char *name, int level, int num_slots,
   f.level = level;
   f.nslots = num_slots;
   f.ncomp = ncomp;
+  f.loc = loc;
   size_t bytes = sizeof(double) * (size_t)ncomp * g->vol;
   for (int sl = 0; sl < num_slots; ++sl) {
     f.slot[sl] = f.orig[sl] = dev_alloc(c, bytes);  // zero-filled: initFieldsWithZero
@@ -301,7 +320,12 @@ int examg_field_advance(examg_ctx *c, int h) {
 int examg_field_set_bc(examg_ctx *c, int h, int kind, double value) {
   Field *f = get_field(c, h);
   if (!f) return set_error(EXAMG_EINVAL, "bad field %d", h);
-  if (kind != EXAMG_BC_NONE && kind != EXAMG_BC_DIRICHLET_CONST && kind != EXAMG_BC_DIRICHLET_HOST)
+  if (kind == EXAMG_BC_NEUMANN && f->loc != 1)
+    return set_error(EXAMG_EUNSUP, "examg_field_set_bc: Neumann is implemented for cell-localised fields");
+  if (f->loc == 1 && kind != EXAMG_BC_NONE && kind != EXAMG_BC_NEUMANN)
+    return set_error(EXAMG_EUNSUP, "examg_field_set_bc: cell-localised fields take None or Neumann");
+  if (kind != EXAMG_BC_NONE && kind != EXAMG_BC_DIRICHLET_CONST && kind != EXAMG_BC_DIRICHLET_HOST &&
+      kind != EXAMG_BC_NEUMANN)
     return set_error(EXAMG_EINVAL, "examg_field_set_bc: kind %d (use examg_field_set_bc_expr for programs)", kind);
   f->bc_kind = kind;
   f->bc_value = value;
@@ -338,6 +362,7 @@ int examg_apply_bc(examg_ctx *c, int h, int slot) {
   if (!f) return set_error(EXAMG_EINVAL, "bad field %d", h);
   if (slot >= f->nslots) return set_error(EXAMG_EINVAL, "bad slot %d", slot);
   if (f->bc_kind == EXAMG_BC_NONE || f->bc_kind == EXAMG_BC_DIRICHLET_HOST) return EXAMG_OK;
+  if (f->loc == 1) return launch_bc_cell(c, *f, slot);
   return launch_bc(c, *f, slot);
 }
 
@@ -348,7 +373,9 @@ static int copy_field(examg_ctx *c, int h, int slot, double *host, bool up, bool
   if (slot >= f->nslots) return set_error(EXAMG_EINVAL, "bad slot %d", slot);
   const LevelGeom &g = *geom(c, f->level);
   if (up) f->halo_depth = 0;
-  const size_t dense = (size_t)g.n[0] * g.n[1] * g.n[2];
+  int e[3];  // dense extents: nodes, or cells of a cell-localised field
+  for (int d = 0; d < 3; ++d) e[d] = g.n[d] - (f->loc == 1 && d < c->cfg.dim ? 1 : 0);
+  const size_t dense = (size_t)e[0] * e[1] * e[2];
   // Large host transfers go through a dense device staging array: one flat copy over PCIe at full
   // rate (a pitched 3D copy of 4 KB rows reaches ~60% of it), then a device-side 3D copy into /
   // out of the padded layout.
@@ -370,11 +397,11 @@ static int copy_field(examg_ctx *c, int h, int slot, double *host, bool up, bool
     cudaMemcpy3DParms p;
     memset(&p, 0, sizeof(p));
     // device: rows of `pitch` doubles, `ay` rows per plane; node (0,0,0) at dev
-    cudaPitchedPtr dp = make_cudaPitchedPtr(dev, sizeof(double) * g.pitch, g.n[0], g.ay);
-    cudaPitchedPtr hpp = make_cudaPitchedPtr(other, sizeof(double) * g.n[0], g.n[0], g.n[1]);
+    cudaPitchedPtr dp = make_cudaPitchedPtr(dev, sizeof(double) * g.pitch, e[0], g.ay);
+    cudaPitchedPtr hpp = make_cudaPitchedPtr(other, sizeof(double) * e[0], e[0], e[1]);
     p.srcPtr = up ? hpp : dp;
     p.dstPtr = up ? dp : hpp;
-    p.extent = make_cudaExtent(sizeof(double) * g.n[0], g.n[1], g.n[2]);
+    p.extent = make_cudaExtent(sizeof(double) * e[0], e[1], e[2]);
     p.kind = (device_side || stage) ? cudaMemcpyDeviceToDevice : (up ? cudaMemcpyHostToDevice : cudaMemcpyDeviceToHost);
     EXAMG_CUDA(cudaMemcpy3DAsync(&p, c->stream));
     if (stage && !up) EXAMG_CUDA(cudaMemcpyAsync(hp, stage, dense * sizeof(double), cudaMemcpyDeviceToHost, c->stream));

@@ -72,6 +72,7 @@ struct Field {
   // The allocations in creation order (slots 0..3, shadow = 4).  slot[]/shadow are permuted by the
   // fused sweeps; orig[] is not, and identifies a buffer across ranks (examg_comm.cu).
   double *orig[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
+  int loc = 0;               // 0: node-localised, 1: cell-localised (n-1 cells per dim, ghost cells at -1 and n-1)
   int halo_depth = 0;        // this many ghost layers hold the neighbour blocks' current values
   int bc_kind = EXAMG_BC_NONE;
   double bc_value = 0.0;
@@ -84,6 +85,14 @@ struct Stencil {
   double coef[EXAMG_MAX_STENCIL];
   int coeff_field = -1;  // -1: constant coefficients
   bool is7 = false;      // 3D 7-point constant stencil (fast path)
+};
+
+// [c_uu + a2*L, c_uv; c_uv, c_vv + a2*L] on two cell fields (the optical-flow operator, examg_optflow.cu)
+struct System2 {
+  int level = 0;
+  double a2 = 1.0;
+  int cuu = -1, cuv = -1, cvv = -1;
+  double L[5];
 };
 
 struct dd { double hi, lo; };
@@ -108,6 +117,7 @@ struct examg_ctx {
   std::vector<examg::LevelGeom> levels;  // index level - min_level
   std::vector<examg::Field> fields;
   std::vector<examg::Stencil> stencils;
+  std::vector<examg::System2> systems;
   cudaStream_t stream = nullptr;
   bool own_stream = false;
   long long launches = 0;
@@ -182,6 +192,7 @@ int launch_maxdiff(examg_ctx *c, int level, const double *a, const double *b, in
 enum { STREAM_SET = 0, STREAM_COPY = 1, STREAM_AXPY = 2, STREAM_XPAY = 3 };
 int launch_stream_op(examg_ctx *c, int level, int op, double alpha, const double *x, double *y);
 int launch_bc(examg_ctx *c, const Field &f, int slot);
+int launch_bc_cell(examg_ctx *c, const Field &f, int slot);  // Neumann ghost cells (examg_optflow.cu)
 int launch_cg(examg_ctx *c, const Stencil &s, double *u, const double *rhs, double *res, double *p,
               double *ap, int max_it, double rel_tol);
 // communicate: `depth` ghost layers (+ the duplicate layer) per side, 1 <= depth <= GHOST

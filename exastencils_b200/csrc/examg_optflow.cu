@@ -1,0 +1,666 @@
+// examg_optflow.cu -- the coupled two-unknown system of the optical-flow programs on 2D cell-centred fields:
+// red-black 2x2 block smoother (`solve locally`), residual (+ fused norm), cell restriction / prolongation,
+// Neumann ghost cells, coupled CG on the coarsest level, and the whole cycle as one object.
+//
+// Reference loops being replaced (Benchmark/OptFlow2D/2D_FD_OptFlow.exa4; Vec2 form:
+// Testing/Application/OpticalFlow2D.exa4):
+//   smoother     :144-161 / :216-231   repeat with { colour 0, colour 1; communicate u, v; loop over u { solve
+//                locally relax r { u => uuSten*u + uvSten*v + alpha*alpha*Laplace*u == rhs_u; v => ... } }; apply bc }
+//                C/s/e/solver/ir/IR_LocalSolve.scala:88-236, IR_LocalDirectInvert.scala:44-140
+//   residual     :167-177   residual_u = rhs_u - (uuSten*u + uvSten*v + alpha**2 * (Laplace*u)); apply bc
+//   restriction  :180-188   rhs@coarser = RestrictionCell * residual   (L4_DefaultRestriction.scala:40-47: [1/2,1/2]^d)
+//   correction   :204-214   u += ProlongationCell@coarser * u@coarser  (L4_DefaultProlongation.scala:30-45: piecewise
+//                constant); apply bc
+//   coarse CG    :234-335
+//   Neumann      C/s/e/boundary/ir/IR_NeumannBC.scala:70-80 (ghost cell = adjacent inner cell), faces in the order
+//                -x,+x,-y,+y over the full orthogonal extent (IR_ApplyBCFunction.scala:53-85) => ghost (i,j) = cell
+//                (clamp i, clamp j), corners included
+//
+// Design (B200): every kernel that writes a Neumann field also writes the ghost cells next to the cells it
+// updates, so `apply bc` costs no launch and no pass; the two unknowns are processed together (the reference
+// makes one loop per unknown for residual/restriction/correction); the cycle is one CUDA graph.
+// Arithmetic: oracle/examg_oracle_optflow.c header ("Arithmetic contract"); fields are bit-identical.
+// Layout: cell (i,j) of a cell field sits where node (i,j) of a node field of the level does, i.e.
+// n-1 cells use the n-node allocation; ghost cells are elements -1 and n_cells.
+#include <cmath>
+#include <map>
+
+#include "examg_cg.cuh"
+
+using namespace examg;
+
+namespace examg {
+
+struct OfArgs {
+  int nx, ny, pitch;
+  double L[5];
+  double a2;
+  const double *cuu, *cuv, *cvv;
+};
+
+// store a cell of a Neumann field together with the ghost cells that mirror it
+__device__ __forceinline__ void store_neumann(double *a, int i, int j, int nx, int ny, int pitch, double val) {
+  const long long p = i + (long long)pitch * j;
+  a[p] = val;
+  const int gi = i == 0 ? -1 : (i == nx - 1 ? nx : i), gj = j == 0 ? -1 : (j == ny - 1 ? ny : j);
+  const bool ex = i == 0 || i == nx - 1, ey = j == 0 || j == ny - 1;
+  if (ex) a[gi + (long long)pitch * j] = val;
+  if (ey) a[i + (long long)pitch * gj] = val;
+  if (ex && ey) a[gi + (long long)pitch * gj] = val;
+}
+
+__device__ __forceinline__ double of_lap(const double (&L)[5], const double *w, long long p, int pitch) {
+  double acc = L[0] * w[p];
+  acc = fma(L[1], w[p - 1], acc);
+  acc = fma(L[2], w[p + 1], acc);
+  acc = fma(L[3], w[p - pitch], acc);
+  acc = fma(L[4], w[p + pitch], acc);
+  return acc;
+}
+
+__device__ __forceinline__ double of_off(const double (&L)[5], const double *w, long long p, int pitch) {
+  double acc = L[1] * w[p - 1];
+  acc = fma(L[2], w[p + 1], acc);
+  acc = fma(L[3], w[p - pitch], acc);
+  acc = fma(L[4], w[p + pitch], acc);
+  return acc;
+}
+
+// the 2x2 local solve at one cell
+__device__ __forceinline__ void of_local_solve(const OfArgs &a, const double *u, const double *v, const double *fu,
+                                               const double *fv, long long p, double relax, double keep, double &nu,
+                                               double &nv) {
+  const double f0 = fu[p] - a.a2 * of_off(a.L, u, p, a.pitch);
+  const double f1 = fv[p] - a.a2 * of_off(a.L, v, p, a.pitch);
+  const double a01 = a.cuv[p];
+  const double a00 = fma(a.a2, a.L[0], a.cuu[p]), a11 = fma(a.a2, a.L[0], a.cvv[p]);
+  const double det = a00 * a11 - a01 * a01;
+  const double su = (a11 * f0 - a01 * f1) / det;
+  const double sv = (a00 * f1 - a01 * f0) / det;
+  nu = u[p] * keep + relax * su;
+  nv = v[p] * keep + relax * sv;
+}
+
+// ghost (i,j) = cell (clamp i, clamp j): the result of the four face loops in the reference's order
+__global__ void __launch_bounds__(256) k_of_neumann(double *a, int nx, int ny, int pitch) {
+  const int t = blockIdx.x * blockDim.x + threadIdx.x;
+  const int per = 2 * (nx + 2) + 2 * ny;
+  if (t >= per) return;
+  int i, j;
+  if (t < nx + 2) { i = t - 1; j = -1; }
+  else if (t < 2 * (nx + 2)) { i = t - (nx + 2) - 1; j = ny; }
+  else if (t < 2 * (nx + 2) + ny) { i = -1; j = t - 2 * (nx + 2); }
+  else { i = nx; j = t - 2 * (nx + 2) - ny; }
+  const int ci = min(max(i, 0), nx - 1), cj = min(max(j, 0), ny - 1);
+  a[i + (long long)pitch * j] = a[ci + (long long)pitch * cj];
+}
+
+// one colour of the block smoother; thread per updated cell
+__global__ void __launch_bounds__(256)
+k_of_smooth_color(const OfArgs a, double *__restrict__ u, double *__restrict__ v, const double *__restrict__ fu,
+                  const double *__restrict__ fv, double relax, int color) {
+  const int j = blockIdx.y * blockDim.y + threadIdx.y;
+  if (j >= a.ny) return;
+  const int i = 2 * (blockIdx.x * blockDim.x + threadIdx.x) + ((j + color) & 1);
+  if (i >= a.nx) return;
+  const long long p = i + (long long)a.pitch * j;
+  double nu, nv;
+  of_local_solve(a, u, v, fu, fv, p, relax, 1.0 - relax, nu, nv);
+  store_neumann(u, i, j, a.nx, a.ny, a.pitch, nu);
+  store_neumann(v, i, j, a.nx, a.ny, a.pitch, nv);
+}
+
+// residual of both unknowns (+ sum of squares); thread per cell, rows by grid stride
+template <bool NORM>
+__global__ void __launch_bounds__(256)
+k_of_residual(const OfArgs a, const double *__restrict__ u, const double *__restrict__ v, const double *__restrict__ fu,
+              const double *__restrict__ fv, double *__restrict__ ru, double *__restrict__ rv, dd *partials) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  dd part = {0.0, 0.0};
+  for (int j = blockIdx.y * blockDim.y + threadIdx.y; j < a.ny; j += gridDim.y * blockDim.y) {
+    if (i >= a.nx) break;
+    const long long p = i + (long long)a.pitch * j;
+    const double r0 = fu[p] - fma(a.a2, of_lap(a.L, u, p, a.pitch), fma(a.cuv[p], v[p], a.cuu[p] * u[p]));
+    const double r1 = fv[p] - fma(a.a2, of_lap(a.L, v, p, a.pitch), fma(a.cvv[p], v[p], a.cuv[p] * u[p]));
+    store_neumann(ru, i, j, a.nx, a.ny, a.pitch, r0);
+    store_neumann(rv, i, j, a.nx, a.ny, a.pitch, r1);
+    if (NORM) {
+      dd_add(part, r0 * r0);
+      dd_add(part, r1 * r1);
+    }
+  }
+  if (NORM) {
+    part = dd_block_reduce(part);
+    if (threadIdx.x == 0 && threadIdx.y == 0) partials[blockIdx.x + gridDim.x * blockIdx.y] = part;
+  }
+}
+
+__global__ void __launch_bounds__(1024) k_of_final_sum(const dd *__restrict__ partials, int n, dd *out) {
+  dd v = {0.0, 0.0};
+  for (int i = threadIdx.x; i < n; i += blockDim.x) dd_merge(v, partials[i]);
+  v = dd_block_reduce(v);
+  if (threadIdx.x == 0) *out = v;
+}
+
+struct Pair {
+  const double *src[3];
+  double *dst[3];
+};
+
+// coarse = 0.25 * (((f00 + f10) + f01) + f11) for up to three fields (blockIdx.z)
+__global__ void __launch_bounds__(256) k_of_restrict(const Pair pr, int nxc, int nyc, int pitch_f, int pitch_c) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  const double *__restrict__ f = pr.src[blockIdx.z];
+  double *__restrict__ cdst = pr.dst[blockIdx.z];
+  for (int j = blockIdx.y * blockDim.y + threadIdx.y; j < nyc; j += gridDim.y * blockDim.y) {
+    if (i >= nxc) break;
+    const long long q = 2 * i + (long long)pitch_f * (2 * j);
+    const double2 lo = *reinterpret_cast<const double2 *>(f + q);
+    const double2 hi = *reinterpret_cast<const double2 *>(f + q + pitch_f);
+    cdst[i + (long long)pitch_c * j] = 0.25 * (((lo.x + lo.y) + hi.x) + hi.y);
+  }
+}
+
+// fine += coarse(parent) for up to three fields; thread per coarse cell; Neumann ghosts refreshed
+__global__ void __launch_bounds__(256) k_of_prolong_add(const Pair pr, int nxc, int nyc, int pitch_f, int pitch_c) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  const double *__restrict__ cs = pr.src[blockIdx.z];
+  double *__restrict__ f = pr.dst[blockIdx.z];
+  const int nxf = 2 * nxc, nyf = 2 * nyc;
+  for (int j = blockIdx.y * blockDim.y + threadIdx.y; j < nyc; j += gridDim.y * blockDim.y) {
+    if (i >= nxc) break;
+    const double cv = cs[i + (long long)pitch_c * j];
+    const long long q = 2 * i + (long long)pitch_f * (2 * j);
+    double2 lo = *reinterpret_cast<double2 *>(f + q);
+    double2 hi = *reinterpret_cast<double2 *>(f + q + pitch_f);
+    lo.x += cv; lo.y += cv; hi.x += cv; hi.y += cv;
+    const bool edge = i == 0 || i == nxc - 1 || j == 0 || j == nyc - 1;
+    if (!edge) {
+      *reinterpret_cast<double2 *>(f + q) = lo;
+      *reinterpret_cast<double2 *>(f + q + pitch_f) = hi;
+    } else {
+      store_neumann(f, 2 * i, 2 * j, nxf, nyf, pitch_f, lo.x);
+      store_neumann(f, 2 * i + 1, 2 * j, nxf, nyf, pitch_f, lo.y);
+      store_neumann(f, 2 * i, 2 * j + 1, nxf, nyf, pitch_f, hi.x);
+      store_neumann(f, 2 * i + 1, 2 * j + 1, nxf, nyf, pitch_f, hi.y);
+    }
+  }
+}
+
+// InitFields: Ix, Iy, It -> IxIx, IxIy, IyIy and rhs (images carry valid Neumann ghosts)
+__global__ void __launch_bounds__(256)
+k_of_init(const double *__restrict__ img0, const double *__restrict__ img1, int nx, int ny, int pitch, double gx1,
+          double gx0, double gy1, double gy0, double *__restrict__ cuu, double *__restrict__ cuv,
+          double *__restrict__ cvv, double *__restrict__ fu, double *__restrict__ fv) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  for (int j = blockIdx.y * blockDim.y + threadIdx.y; j < ny; j += gridDim.y * blockDim.y) {
+    if (i >= nx) break;
+    const long long p = i + (long long)pitch * j;
+    const double ix = fma(gx0, img0[p], gx1 * img0[p + 1]);  // GradX: [1,0] then [0,0]
+    const double iy = fma(gy0, img0[p], gy1 * img0[p + pitch]);
+    const double it = img1[p] - img0[p];
+    cuu[p] = ix * ix;
+    cuv[p] = ix * iy;
+    cvv[p] = iy * iy;
+    fu[p] = -ix * it;
+    fv[p] = -iy * it;
+  }
+}
+
+// mgCycle@coarsest: the coupled CG, whole solve in one CTA (the grid has a few dozen cells)
+__global__ void __launch_bounds__(1024)
+k_of_cg(const OfArgs a, double *u, double *v, const double *fu, const double *fv, double *ru, double *rv, double *pu,
+        double *pv, double *apu, double *apv, int max_it, double rel_tol, int *iters_out) {
+  const int total = a.nx * a.ny, tid = threadIdx.x, nt = blockDim.x;
+  dd part = {0.0, 0.0};
+  for (int t = tid; t < total; t += nt) {
+    const int i = t % a.nx, j = t / a.nx;
+    const long long p = i + (long long)a.pitch * j;
+    const double r0 = fu[p] - fma(a.a2, of_lap(a.L, u, p, a.pitch), fma(a.cuv[p], v[p], a.cuu[p] * u[p]));
+    const double r1 = fv[p] - fma(a.a2, of_lap(a.L, v, p, a.pitch), fma(a.cvv[p], v[p], a.cuv[p] * u[p]));
+    store_neumann(ru, i, j, a.nx, a.ny, a.pitch, r0);
+    store_neumann(rv, i, j, a.nx, a.ny, a.pitch, r1);
+    store_neumann(pu, i, j, a.nx, a.ny, a.pitch, r0);
+    store_neumann(pv, i, j, a.nx, a.ny, a.pitch, r1);
+    dd_add(part, r0 * r0);
+    dd_add(part, r1 * r1);
+  }
+  double curRes = sqrt(cg_sum(part));
+  const double initRes = curRes;
+  int iters = 0;
+  for (int step = 0; step < max_it; ++step) {
+    iters = step + 1;
+    dd n0 = {0.0, 0.0}, n1 = {0.0, 0.0}, d0 = {0.0, 0.0}, d1 = {0.0, 0.0};
+    for (int t = tid; t < total; t += nt) {
+      const int i = t % a.nx, j = t / a.nx;
+      const long long p = i + (long long)a.pitch * j;
+      const double au = fma(a.a2, of_lap(a.L, pu, p, a.pitch), fma(a.cuv[p], pv[p], a.cuu[p] * pu[p]));
+      const double av = fma(a.a2, of_lap(a.L, pv, p, a.pitch), fma(a.cvv[p], pv[p], a.cuv[p] * pu[p]));
+      apu[p] = au;
+      apv[p] = av;
+      dd_add(n0, ru[p] * ru[p]);
+      dd_add(n1, rv[p] * rv[p]);
+      dd_add(d0, pu[p] * au);
+      dd_add(d1, pv[p] * av);
+    }
+    const double nom = cg_sum(n0) + cg_sum(n1);
+    const double den = cg_sum(d0) + cg_sum(d1);
+    const double alpha = nom / den;
+    dd pr = {0.0, 0.0};
+    for (int t = tid; t < total; t += nt) {
+      const int i = t % a.nx, j = t / a.nx;
+      const long long p = i + (long long)a.pitch * j;
+      store_neumann(u, i, j, a.nx, a.ny, a.pitch, fma(alpha, pu[p], u[p]));
+      store_neumann(v, i, j, a.nx, a.ny, a.pitch, fma(alpha, pv[p], v[p]));
+      const double r0 = fma(-alpha, apu[p], ru[p]), r1 = fma(-alpha, apv[p], rv[p]);
+      store_neumann(ru, i, j, a.nx, a.ny, a.pitch, r0);
+      store_neumann(rv, i, j, a.nx, a.ny, a.pitch, r1);
+      dd_add(pr, r0 * r0);
+      dd_add(pr, r1 * r1);
+    }
+    const double nextRes = sqrt(cg_sum(pr));
+    if (nextRes <= rel_tol * initRes) break;
+    const double beta = (nextRes * nextRes) / (curRes * curRes);
+    for (int t = tid; t < total; t += nt) {
+      const int i = t % a.nx, j = t / a.nx;
+      const long long p = i + (long long)a.pitch * j;
+      store_neumann(pu, i, j, a.nx, a.ny, a.pitch, fma(beta, pu[p], ru[p]));
+      store_neumann(pv, i, j, a.nx, a.ny, a.pitch, fma(beta, pv[p], rv[p]));
+    }
+    curRes = nextRes;
+    __syncthreads();
+  }
+  if (tid == 0 && iters_out) *iters_out = iters;
+}
+
+// ---- host side ---------------------------------------------------------------------
+
+static System2 *get_system(examg_ctx *c, int h) {
+  if (!c || h < 0 || h >= (int)c->systems.size()) return nullptr;
+  return &c->systems[h];
+}
+
+static Field *cell_field(examg_ctx *c, int h, int level) {
+  Field *f = get_field(c, h);
+  if (!f || f->loc != 1 || f->level != level || f->ncomp != 1) return nullptr;
+  return f;
+}
+
+static OfArgs of_args(examg_ctx *c, const System2 &s) {
+  const LevelGeom &g = *geom(c, s.level);
+  OfArgs a;
+  a.nx = g.n[0] - 1;
+  a.ny = g.n[1] - 1;
+  a.pitch = g.pitch;
+  for (int k = 0; k < 5; ++k) a.L[k] = s.L[k];
+  a.a2 = s.a2;
+  a.cuu = field_ptr(c, &c->fields[s.cuu], -1);
+  a.cuv = field_ptr(c, &c->fields[s.cuv], -1);
+  a.cvv = field_ptr(c, &c->fields[s.cvv], -1);
+  return a;
+}
+
+static dim3 rows_grid(int nx, int ny, dim3 block, int nz = 1) {
+  int gx = (nx + block.x - 1) / block.x, gy = (ny + block.y - 1) / block.y;
+  const int cap = 148 * 16;  // rows beyond that are covered by the grid stride
+  if (gx * gy * nz > cap) gy = cap / (gx * nz) > 0 ? cap / (gx * nz) : 1;
+  return dim3(gx, gy, nz);
+}
+
+int launch_bc_cell(examg_ctx *c, const Field &f, int slot) {
+  if (c->cfg.dim != 2) return set_error(EXAMG_EUNSUP, "apply bc: cell-localised fields are 2D so far");
+  const LevelGeom &g = *geom(c, f.level);
+  const int nx = g.n[0] - 1, ny = g.n[1] - 1, per = 2 * (nx + 2) + 2 * ny;
+  for (int comp = 0; comp < f.ncomp; ++comp) {
+    k_of_neumann<<<(per + 255) / 256, 256, 0, c->stream>>>(field_ptr(c, &f, slot, comp), nx, ny, g.pitch);
+    EXAMG_LAUNCH_CHECK(c);
+  }
+  return EXAMG_OK;
+}
+
+#define OF_SYS(var, h)                  \
+  System2 *var = get_system(c, h);      \
+  if (!var) return set_error(EXAMG_EINVAL, "%s: bad system handle %d", __func__, h)
+#define OF_FIELD(var, h, lvl)                \
+  Field *var = cell_field(c, h, lvl);        \
+  if (!var) return set_error(EXAMG_EINVAL, "%s: field %d is not a scalar cell field of level %d", __func__, h, lvl)
+
+}  // namespace examg
+
+extern "C" {
+
+int examg_system2_create(examg_ctx *c, const examg_system2_desc *d) {
+  if (!c || !d) return set_error(EXAMG_EINVAL, "examg_system2_create: null argument");
+  if (c->cfg.dim != 2) return set_error(EXAMG_EUNSUP, "examg_system2_create: 2D programs only");
+  Stencil *st = get_stencil(c, d->laplace);
+  if (!st || st->coeff_field >= 0 || st->nst != 5)
+    return set_error(EXAMG_EINVAL, "examg_system2_create: laplace must be a constant 5-point stencil");
+  static const int want[5][2] = {{0, 0}, {-1, 0}, {1, 0}, {0, -1}, {0, 1}};
+  for (int k = 0; k < 5; ++k)
+    if (st->off[k][0] != want[k][0] || st->off[k][1] != want[k][1] || st->off[k][2] != 0)
+      return set_error(EXAMG_EUNSUP, "examg_system2_create: stencil entries must be declared centre,-x,+x,-y,+y");
+  const LevelGeom &g = *geom(c, st->level);
+  if (g.n[0] < 3 || g.n[1] < 3) return set_error(EXAMG_EUNSUP, "examg_system2_create: fewer than 2 cells per dimension");
+  System2 s;
+  s.level = st->level;
+  s.a2 = d->scale;
+  for (int k = 0; k < 5; ++k) s.L[k] = st->coef[k];
+  const int hs[3] = {d->c_uu, d->c_uv, d->c_vv};
+  for (int k = 0; k < 3; ++k)
+    if (!cell_field(c, hs[k], s.level))
+      return set_error(EXAMG_EINVAL, "examg_system2_create: coefficient %d is not a scalar cell field of level %d", k, s.level);
+  s.cuu = d->c_uu;
+  s.cuv = d->c_uv;
+  s.cvv = d->c_vv;
+  c->systems.push_back(s);
+  return (int)c->systems.size() - 1;
+}
+
+int examg_system2_residual(examg_ctx *c, int sys, int u, int v, int rhs_u, int rhs_v, int res_u, int res_v,
+                           double *norm2_out) {
+  OF_SYS(s, sys);
+  OF_FIELD(fu, u, s->level); OF_FIELD(fv, v, s->level); OF_FIELD(bu, rhs_u, s->level); OF_FIELD(bv, rhs_v, s->level);
+  OF_FIELD(ru, res_u, s->level); OF_FIELD(rv, res_v, s->level);
+  const OfArgs a = of_args(c, *s);
+  const dim3 block(64, 4), grid = rows_grid(a.nx, a.ny, block);
+  if (norm2_out) {
+    k_of_residual<true><<<grid, block, 0, c->stream>>>(a, field_ptr(c, fu, -1), field_ptr(c, fv, -1), field_ptr(c, bu, -1),
+                                                       field_ptr(c, bv, -1), field_ptr(c, ru, -1), field_ptr(c, rv, -1),
+                                                       c->partials);
+    EXAMG_LAUNCH_CHECK(c);
+    k_of_final_sum<<<1, 1024, 0, c->stream>>>(c->partials, (int)(grid.x * grid.y), c->red_out);
+    EXAMG_LAUNCH_CHECK(c);
+    return finish_sum(c, 0, norm2_out);
+  }
+  k_of_residual<false><<<grid, block, 0, c->stream>>>(a, field_ptr(c, fu, -1), field_ptr(c, fv, -1), field_ptr(c, bu, -1),
+                                                      field_ptr(c, bv, -1), field_ptr(c, ru, -1), field_ptr(c, rv, -1),
+                                                      nullptr);
+  EXAMG_LAUNCH_CHECK(c);
+  return EXAMG_OK;
+}
+
+int examg_system2_smooth_rb_color(examg_ctx *c, int sys, int u, int v, int rhs_u, int rhs_v, double relax, int color) {
+  OF_SYS(s, sys);
+  OF_FIELD(fu, u, s->level); OF_FIELD(fv, v, s->level); OF_FIELD(bu, rhs_u, s->level); OF_FIELD(bv, rhs_v, s->level);
+  if (color != 0 && color != 1) return set_error(EXAMG_EINVAL, "examg_system2_smooth_rb_color: colour %d", color);
+  const OfArgs a = of_args(c, *s);
+  const dim3 block(64, 4), grid((a.nx / 2 + 1 + block.x - 1) / block.x, (a.ny + block.y - 1) / block.y);
+  k_of_smooth_color<<<grid, block, 0, c->stream>>>(a, field_ptr(c, fu, -1), field_ptr(c, fv, -1), field_ptr(c, bu, -1),
+                                                   field_ptr(c, bv, -1), relax, color);
+  EXAMG_LAUNCH_CHECK(c);
+  return EXAMG_OK;
+}
+
+int examg_system2_smooth_rb(examg_ctx *c, int sys, int u, int v, int rhs_u, int rhs_v, double relax, int nsweeps) {
+  for (int it = 0; it < nsweeps; ++it)
+    for (int color = 0; color < 2; ++color) {
+      int rc = examg_system2_smooth_rb_color(c, sys, u, v, rhs_u, rhs_v, relax, color);
+      if (rc) return rc;
+    }
+  return EXAMG_OK;
+}
+
+static int cell_transfer(examg_ctx *c, const int *src, const int *dst, int n, bool restrict_op, const char *who) {
+  if (n < 1 || n > 3) return set_error(EXAMG_EINVAL, "%s: 1..3 fields", who);
+  Pair pr;
+  int lf = -1, lc = -1;
+  for (int k = 0; k < n; ++k) {
+    Field *fs = get_field(c, src[k]), *fd = get_field(c, dst[k]);
+    if (!fs || !fd || fs->loc != 1 || fd->loc != 1) return set_error(EXAMG_EINVAL, "%s: not a cell field", who);
+    const int fine = restrict_op ? fs->level : fd->level, coarse = restrict_op ? fd->level : fs->level;
+    if (coarse != fine - 1 || (lf >= 0 && fine != lf)) return set_error(EXAMG_EINVAL, "%s: levels %d -> %d", who, fs->level, fd->level);
+    lf = fine;
+    lc = coarse;
+    pr.src[k] = field_ptr(c, fs, -1);
+    pr.dst[k] = field_ptr(c, fd, -1);
+  }
+  if (c->cfg.dim != 2) return set_error(EXAMG_EUNSUP, "%s: 2D only", who);
+  const LevelGeom &gf = *geom(c, lf), &gc = *geom(c, lc);
+  const int nxc = gc.n[0] - 1, nyc = gc.n[1] - 1;
+  const dim3 block(64, 4), grid = rows_grid(nxc, nyc, block, n);
+  if (restrict_op)
+    k_of_restrict<<<grid, block, 0, c->stream>>>(pr, nxc, nyc, gf.pitch, gc.pitch);
+  else
+    k_of_prolong_add<<<grid, block, 0, c->stream>>>(pr, nxc, nyc, gf.pitch, gc.pitch);
+  EXAMG_LAUNCH_CHECK(c);
+  return EXAMG_OK;
+}
+
+int examg_restrict_cell(examg_ctx *c, const int *fine, const int *coarse, int nfields) {
+  return cell_transfer(c, fine, coarse, nfields, true, "examg_restrict_cell");
+}
+
+int examg_prolong_add_cell(examg_ctx *c, const int *coarse, const int *fine, int nfields) {
+  return cell_transfer(c, coarse, fine, nfields, false, "examg_prolong_add_cell");
+}
+
+int examg_system2_cg_coarse(examg_ctx *c, int sys, const int *fields, int max_it, double rel_tol, int *iters_out) {
+  OF_SYS(s, sys);
+  if (!fields) return set_error(EXAMG_EINVAL, "examg_system2_cg_coarse: null field list");
+  double *p[10];
+  for (int k = 0; k < 10; ++k) {
+    Field *f = cell_field(c, fields[k], s->level);
+    if (!f) return set_error(EXAMG_EINVAL, "examg_system2_cg_coarse: field %d (#%d) is not a cell field of level %d", fields[k], k, s->level);
+    p[k] = field_ptr(c, f, -1);
+  }
+  const OfArgs a = of_args(c, *s);
+  int nt = 32;
+  while (nt < 1024 && nt < a.nx * a.ny) nt <<= 1;
+  k_of_cg<<<1, nt, 0, c->stream>>>(a, p[0], p[1], p[2], p[3], p[4], p[5], p[6], p[7], p[8], p[9], max_it, rel_tol, c->int_out);
+  EXAMG_LAUNCH_CHECK(c);
+  if (iters_out) {
+    EXAMG_CUDA(cudaMemcpyAsync(c->int_host, c->int_out, sizeof(int), cudaMemcpyDeviceToHost, c->stream));
+    EXAMG_CUDA(cudaStreamSynchronize(c->stream));
+    *iters_out = c->int_host[0];
+  }
+  return EXAMG_OK;
+}
+
+}  // extern "C"
+
+// ---- the whole program: InitFields / doSolve@finest / mgCycle@all -----------------------------
+
+struct examg_optflow {
+  examg_ctx *c = nullptr;
+  examg_optflow_desc desc;
+  int nlev = 0;
+  std::vector<int> f[9];   // per level: u, v, rhs_u, rhs_v, residual_u, residual_v, IxIx, IxIy, IyIy
+  std::vector<int> sys;    // per level
+  int img0 = -1, img1 = -1;
+  int cg[4] = {-1, -1, -1, -1};  // cgTmp0_u, cgTmp0_v, cgTmp1_u, cgTmp1_v @coarsest
+  cudaGraphExec_t graph = nullptr;
+  long long graph_launches = 0;
+};
+
+namespace {
+
+int of_lv(examg_optflow *o, int level) { return level - o->c->cfg.min_level; }
+
+int of_zero(examg_ctx *c, int h) {  // u@coarser = 0; apply bc: the whole allocation, ghosts included
+  Field *f = get_field(c, h);
+  const LevelGeom &g = *geom(c, f->level);
+  EXAMG_CUDA(cudaMemsetAsync(f->slot[f->cur], 0, sizeof(double) * (size_t)g.vol, c->stream));
+  c->launches++;
+  return EXAMG_OK;
+}
+
+int of_vcycle_rec(examg_optflow *o, int level) {
+  examg_ctx *c = o->c;
+  const int l = of_lv(o, level);
+  if (level == c->cfg.min_level) {
+    const int fl[10] = {o->f[0][l], o->f[1][l], o->f[2][l], o->f[3][l], o->f[4][l], o->f[5][l],
+                        o->cg[0], o->cg[1], o->cg[2], o->cg[3]};
+    return examg_system2_cg_coarse(c, o->sys[l], fl, o->desc.cg_max_it, o->desc.cg_rel_tol, nullptr);
+  }
+  int rc;
+  if ((rc = examg_system2_smooth_rb(c, o->sys[l], o->f[0][l], o->f[1][l], o->f[2][l], o->f[3][l], o->desc.relax,
+                                    o->desc.nu_pre))) return rc;
+  if ((rc = examg_system2_residual(c, o->sys[l], o->f[0][l], o->f[1][l], o->f[2][l], o->f[3][l], o->f[4][l],
+                                   o->f[5][l], nullptr))) return rc;
+  const int res[2] = {o->f[4][l], o->f[5][l]}, rhsc[2] = {o->f[2][l - 1], o->f[3][l - 1]};
+  if ((rc = examg_restrict_cell(c, res, rhsc, 2))) return rc;
+  if ((rc = of_zero(c, o->f[0][l - 1])) || (rc = of_zero(c, o->f[1][l - 1]))) return rc;
+  if ((rc = of_vcycle_rec(o, level - 1))) return rc;
+  const int uc[2] = {o->f[0][l - 1], o->f[1][l - 1]}, uf[2] = {o->f[0][l], o->f[1][l]};
+  if ((rc = examg_prolong_add_cell(c, uc, uf, 2))) return rc;
+  return examg_system2_smooth_rb(c, o->sys[l], o->f[0][l], o->f[1][l], o->f[2][l], o->f[3][l], o->desc.relax,
+                                 o->desc.nu_post);
+}
+
+}  // namespace
+
+extern "C" {
+
+examg_optflow *examg_optflow_create(examg_ctx *c, const examg_optflow_desc *d) {
+  if (!c || !d) { set_error(EXAMG_EINVAL, "examg_optflow_create: null argument"); return nullptr; }
+  if (c->cfg.dim != 2 || c->world != 1) {
+    set_error(EXAMG_EUNSUP, "examg_optflow_create: 2D single-block programs only");
+    return nullptr;
+  }
+  examg_optflow *o = new examg_optflow;
+  o->c = c;
+  o->desc = *d;
+  o->nlev = c->cfg.max_level - c->cfg.min_level + 1;
+  static const char *names[9] = {"u", "v", "rhs_u", "rhs_v", "residual_u", "residual_v", "IxIx", "IxIy", "IyIy"};
+  static const int offs[5][3] = {{0, 0, 0}, {-1, 0, 0}, {1, 0, 0}, {0, -1, 0}, {0, 1, 0}};
+  bool ok = true;
+  for (int level = c->cfg.min_level; level <= c->cfg.max_level && ok; ++level) {
+    for (int k = 0; k < 9; ++k) {
+      const int h = examg_field_create_cell(c, names[k], level, 1, 1);
+      ok = ok && h >= 0;
+      o->f[k].push_back(h);
+      // u, v, residual_u, residual_v: Neumann; rhs and the coefficients: None
+      if (ok && (k < 2 || k == 4 || k == 5)) examg_field_set_bc(c, h, EXAMG_BC_NEUMANN, 0.0);
+    }
+    if (!ok) break;
+    // Stencil Laplace@all (Benchmark/OptFlow2D/2D_FD_OptFlow.exa4:75-81)
+    const LevelGeom &g = *geom(c, level);
+    const double hx2 = g.h[0] * g.h[0], hy2 = g.h[1] * g.h[1];
+    const double coef[5] = {2.0 / hx2 + 2.0 / hy2, -1.0 / hx2, -1.0 / hx2, -1.0 / hy2, -1.0 / hy2};
+    const int st = examg_stencil_const(c, level, 5, offs, coef);
+    examg_system2_desc sd;
+    sd.laplace = st;
+    sd.scale = d->alpha * d->alpha;  // alpha ** 2
+    sd.c_uu = o->f[6].back();
+    sd.c_uv = o->f[7].back();
+    sd.c_vv = o->f[8].back();
+    const int sh = st >= 0 ? examg_system2_create(c, &sd) : -1;
+    ok = ok && sh >= 0;
+    o->sys.push_back(sh);
+  }
+  if (ok) {
+    o->img0 = examg_field_create_cell(c, "img0", c->cfg.max_level, 1, 1);
+    o->img1 = examg_field_create_cell(c, "img1", c->cfg.max_level, 1, 1);
+    ok = o->img0 >= 0 && o->img1 >= 0;
+    static const char *cgn[4] = {"cgTmp0_u", "cgTmp0_v", "cgTmp1_u", "cgTmp1_v"};
+    for (int k = 0; k < 4 && ok; ++k) {
+      o->cg[k] = examg_field_create_cell(c, cgn[k], c->cfg.min_level, 1, 1);
+      ok = o->cg[k] >= 0;
+    }
+    if (ok) {
+      examg_field_set_bc(c, o->img0, EXAMG_BC_NEUMANN, 0.0);
+      examg_field_set_bc(c, o->img1, EXAMG_BC_NEUMANN, 0.0);
+      examg_field_set_bc(c, o->cg[0], EXAMG_BC_NEUMANN, 0.0);
+      examg_field_set_bc(c, o->cg[1], EXAMG_BC_NEUMANN, 0.0);
+    }
+  }
+  if (!ok) {
+    delete o;  // fields stay with the context and are released by examg_finalize
+    return nullptr;
+  }
+  return o;
+}
+
+int examg_optflow_destroy(examg_optflow *o) {
+  if (!o) return EXAMG_OK;
+  if (o->graph) cudaGraphExecDestroy(o->graph);
+  delete o;
+  return EXAMG_OK;
+}
+
+int examg_optflow_field(examg_optflow *o, int level, int which) {
+  if (!o) return set_error(EXAMG_EINVAL, "null optflow object");
+  examg_ctx *c = o->c;
+  if (which == EXAMG_OF_IMG0) return o->img0;
+  if (which == EXAMG_OF_IMG1) return o->img1;
+  if (level < c->cfg.min_level || level > c->cfg.max_level || which < 0 || which > EXAMG_OF_IMG1)
+    return set_error(EXAMG_EINVAL, "examg_optflow_field: level %d which %d", level, which);
+  return o->f[which][of_lv(o, level)];
+}
+
+int examg_optflow_init_fields(examg_optflow *o) {
+  if (!o) return set_error(EXAMG_EINVAL, "null optflow object");
+  examg_ctx *c = o->c;
+  int rc;
+  if ((rc = examg_apply_bc(c, o->img0, -1)) || (rc = examg_apply_bc(c, o->img1, -1))) return rc;
+  const int L = c->cfg.max_level, l = of_lv(o, L);
+  const LevelGeom &g = *geom(c, L);
+  const int nx = g.n[0] - 1, ny = g.n[1] - 1;
+  const dim3 block(64, 4), grid = rows_grid(nx, ny, block);
+  auto ptr = [&](int h) { return field_ptr(c, &c->fields[h], -1); };
+  k_of_init<<<grid, block, 0, c->stream>>>(ptr(o->img0), ptr(o->img1), nx, ny, g.pitch, 1.0 / g.h[0], -1.0 / g.h[0],
+                                           1.0 / g.h[1], -1.0 / g.h[1], ptr(o->f[6][l]), ptr(o->f[7][l]),
+                                           ptr(o->f[8][l]), ptr(o->f[2][l]), ptr(o->f[3][l]));
+  EXAMG_LAUNCH_CHECK(c);
+  for (int level = L - 1; level >= c->cfg.min_level; --level) {  // initGradients@(all but finest)
+    const int k = of_lv(o, level);
+    const int fine[3] = {o->f[6][k + 1], o->f[7][k + 1], o->f[8][k + 1]}, coarse[3] = {o->f[6][k], o->f[7][k], o->f[8][k]};
+    if ((rc = examg_restrict_cell(c, fine, coarse, 3))) return rc;
+  }
+  return EXAMG_OK;
+}
+
+int examg_optflow_vcycle(examg_optflow *o, int level) {
+  if (!o) return set_error(EXAMG_EINVAL, "null optflow object");
+  examg_ctx *c = o->c;
+  if (level < 0) level = c->cfg.max_level;
+  if (level < c->cfg.min_level || level > c->cfg.max_level) return set_error(EXAMG_EINVAL, "examg_optflow_vcycle: level %d", level);
+  if (level != c->cfg.max_level) return of_vcycle_rec(o, level);
+  if (!o->graph) {  // everything is in place: one graph serves every cycle
+    const long long l0 = c->launches;
+    cudaGraph_t graph = nullptr;
+    EXAMG_CUDA(cudaStreamBeginCapture(c->stream, cudaStreamCaptureModeThreadLocal));
+    const int rc = of_vcycle_rec(o, level);
+    const cudaError_t e = cudaStreamEndCapture(c->stream, &graph);
+    if (rc) { if (graph) cudaGraphDestroy(graph); return rc; }
+    if (e != cudaSuccess) return set_error(EXAMG_ECUDA, "graph capture of mgCycle failed: %s", cudaGetErrorString(e));
+    const cudaError_t e2 = cudaGraphInstantiate(&o->graph, graph, 0);
+    cudaGraphDestroy(graph);
+    if (e2 != cudaSuccess) return set_error(EXAMG_ECUDA, "cudaGraphInstantiate: %s", cudaGetErrorString(e2));
+    o->graph_launches = c->launches - l0;
+    c->launches = l0;
+  }
+  EXAMG_CUDA(cudaGraphLaunch(o->graph, c->stream));
+  c->launches += o->graph_launches;
+  return EXAMG_OK;
+}
+
+int examg_optflow_residual_norm(examg_optflow *o, double *norm_out) {
+  if (!o || !norm_out) return set_error(EXAMG_EINVAL, "examg_optflow_residual_norm: null argument");
+  const int l = of_lv(o, o->c->cfg.max_level);
+  double n2 = 0.0;
+  const int rc = examg_system2_residual(o->c, o->sys[l], o->f[0][l], o->f[1][l], o->f[2][l], o->f[3][l], o->f[4][l],
+                                        o->f[5][l], &n2);
+  if (rc) return rc;
+  *norm_out = std::sqrt(n2);
+  return EXAMG_OK;
+}
+
+int examg_optflow_cycles(examg_optflow *o, int n, double *norm_out) {
+  for (int i = 0; i < n; ++i) {
+    const int rc = examg_optflow_vcycle(o, -1);
+    if (rc) return rc;
+  }
+  return norm_out ? examg_optflow_residual_norm(o, norm_out) : EXAMG_OK;
+}
+
+int examg_optflow_last_cg_iters(examg_optflow *o, int *iters_out) {
+  if (!o || !iters_out) return set_error(EXAMG_EINVAL, "examg_optflow_last_cg_iters: null argument");
+  examg_ctx *c = o->c;
+  EXAMG_CUDA(cudaMemcpyAsync(c->int_host, c->int_out, sizeof(int), cudaMemcpyDeviceToHost, c->stream));
+  EXAMG_CUDA(cudaStreamSynchronize(c->stream));
+  *iters_out = c->int_host[0];
+  return EXAMG_OK;
+}
+
+}  // extern "C"

@@ -21,6 +21,7 @@ MAX_STENCIL = 27
 BC_NONE, BC_DIRICHLET_CONST, BC_DIRICHLET_EXPR, BC_DIRICHLET_HOST = 0, 1, 2, 3
 OP_CONST, OP_X, OP_Y, OP_Z, OP_ADD, OP_SUB, OP_MUL, OP_DIV, OP_NEG = range(9)
 SMOOTH_JACOBI, SMOOTH_RBGS = 0, 1
+BC_NEUMANN = 4
 F_SOLUTION, F_RHS, F_RESIDUAL, F_CGTMP0, F_CGTMP1 = range(5)
 
 
@@ -42,6 +43,15 @@ class CycleDesc(C.Structure):
     _fields_ = [("smoother", C.c_int), ("omega", C.c_double), ("nu_pre", C.c_int), ("nu_post", C.c_int),
                 ("restrict_scale", C.c_double), ("cg_max_it", C.c_int), ("cg_rel_tol", C.c_double),
                 ("stencils", C.POINTER(C.c_int))]
+
+
+class System2Desc(C.Structure):
+    _fields_ = [("laplace", C.c_int), ("scale", C.c_double), ("c_uu", C.c_int), ("c_uv", C.c_int), ("c_vv", C.c_int)]
+
+
+class OptFlowDesc(C.Structure):
+    _fields_ = [("alpha", C.c_double), ("relax", C.c_double), ("nu_pre", C.c_int), ("nu_post", C.c_int),
+                ("cg_max_it", C.c_int), ("cg_rel_tol", C.c_double)]
 
 
 def build(force=False, verbose=False):
@@ -107,6 +117,23 @@ SIGNATURES = {
     "examg_solver_cycles": (C.c_int, [C.c_void_p, C.c_int, _dp]),
     "examg_solver_residual_norm": (C.c_int, [C.c_void_p, _dp]),
     "examg_solver_last_cg_iters": (C.c_int, [C.c_void_p, _ip]),
+    "examg_field_create_cell": (C.c_int, [C.c_void_p, C.c_char_p, C.c_int, C.c_int, C.c_int]),
+    "examg_level_cells": (C.c_int, [C.c_void_p, C.c_int, _ip]),
+    "examg_system2_create": (C.c_int, [C.c_void_p, C.POINTER(System2Desc)]),
+    "examg_system2_residual": (C.c_int, [C.c_void_p] + [C.c_int] * 7 + [_dp]),
+    "examg_system2_smooth_rb": (C.c_int, [C.c_void_p] + [C.c_int] * 5 + [C.c_double, C.c_int]),
+    "examg_system2_smooth_rb_color": (C.c_int, [C.c_void_p] + [C.c_int] * 5 + [C.c_double, C.c_int]),
+    "examg_restrict_cell": (C.c_int, [C.c_void_p, _ip, _ip, C.c_int]),
+    "examg_prolong_add_cell": (C.c_int, [C.c_void_p, _ip, _ip, C.c_int]),
+    "examg_system2_cg_coarse": (C.c_int, [C.c_void_p, C.c_int, _ip, C.c_int, C.c_double, _ip]),
+    "examg_optflow_create": (C.c_void_p, [C.c_void_p, C.POINTER(OptFlowDesc)]),
+    "examg_optflow_destroy": (C.c_int, [C.c_void_p]),
+    "examg_optflow_field": (C.c_int, [C.c_void_p, C.c_int, C.c_int]),
+    "examg_optflow_init_fields": (C.c_int, [C.c_void_p]),
+    "examg_optflow_vcycle": (C.c_int, [C.c_void_p, C.c_int]),
+    "examg_optflow_cycles": (C.c_int, [C.c_void_p, C.c_int, _dp]),
+    "examg_optflow_residual_norm": (C.c_int, [C.c_void_p, _dp]),
+    "examg_optflow_last_cg_iters": (C.c_int, [C.c_void_p, _ip]),
     "examg_comm_blob_size": (C.c_int, [C.c_void_p]),
     "examg_comm_export": (C.c_int, [C.c_void_p, C.c_void_p]),
     "examg_comm_import": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int]),
@@ -205,6 +232,23 @@ class Context:
     # -- fields
     def field_create(self, name, level, num_slots=1, ncomp=1):
         return check(self.L.examg_field_create(self.h, name.encode(), level, num_slots, ncomp))
+
+    def field_create_cell(self, name, level, num_slots=1, ncomp=1):
+        return check(self.L.examg_field_create_cell(self.h, name.encode(), level, num_slots, ncomp))
+
+    def cells(self, level):
+        n = (C.c_int * 3)()
+        check(self.L.examg_level_cells(self.h, level, n))
+        return n[0], n[1], n[2]
+
+    def cell_shape(self, level):
+        nx, ny, nz = self.cells(level)
+        return (nz, ny, nx)
+
+    def download_cells(self, f, level, slot=-1):
+        out = np.empty(self.cell_shape(level), dtype=np.float64)
+        check(self.L.examg_field_download(self.h, f, slot, _ptr(out)))
+        return out
 
     def field_destroy(self, f):
         check(self.L.examg_field_destroy(self.h, f))
@@ -321,4 +365,38 @@ class Context:
         its = C.c_int()
         check(self.L.examg_cg_coarse(self.h, A, u, rhs, res, p, ap, max_it, rel_tol,
                                      C.byref(its) if want_iters else None))
+        return its.value
+
+    # -- coupled two-unknown systems on cell fields (optical flow)
+    @staticmethod
+    def _ints(v):
+        return (C.c_int * len(v))(*[int(x) for x in v])
+
+    def system2_create(self, laplace, scale, c_uu, c_uv, c_vv):
+        d = System2Desc(laplace, scale, c_uu, c_uv, c_vv)
+        return check(self.L.examg_system2_create(self.h, C.byref(d)))
+
+    def system2_residual(self, sys, u, v, rhs_u, rhs_v, res_u, res_v, norm=False):
+        if norm:
+            n2 = C.c_double()
+            check(self.L.examg_system2_residual(self.h, sys, u, v, rhs_u, rhs_v, res_u, res_v, C.byref(n2)))
+            return n2.value
+        check(self.L.examg_system2_residual(self.h, sys, u, v, rhs_u, rhs_v, res_u, res_v, None))
+
+    def system2_smooth_rb(self, sys, u, v, rhs_u, rhs_v, relax=1.0, nsweeps=1):
+        check(self.L.examg_system2_smooth_rb(self.h, sys, u, v, rhs_u, rhs_v, relax, nsweeps))
+
+    def system2_smooth_rb_color(self, sys, u, v, rhs_u, rhs_v, relax, color):
+        check(self.L.examg_system2_smooth_rb_color(self.h, sys, u, v, rhs_u, rhs_v, relax, color))
+
+    def restrict_cell(self, fine, coarse):
+        check(self.L.examg_restrict_cell(self.h, self._ints(fine), self._ints(coarse), len(fine)))
+
+    def prolong_add_cell(self, coarse, fine):
+        check(self.L.examg_prolong_add_cell(self.h, self._ints(coarse), self._ints(fine), len(fine)))
+
+    def system2_cg_coarse(self, sys, fields, max_it, rel_tol, want_iters=True):
+        its = C.c_int()
+        check(self.L.examg_system2_cg_coarse(self.h, sys, self._ints(fields), max_it, rel_tol,
+                                             C.byref(its) if want_iters else None))
         return its.value

@@ -83,6 +83,11 @@ int examg_level_width(examg_ctx *ctx, int level, double h[3]);
  * (Layout NodeWithComm; C/s/e/field/ir/IR_FieldLayout.scala:30-129).
  * ncomp > 1 gives the SoA component dimension of stencil-field coefficients. */
 int examg_field_create(examg_ctx *ctx, const char *name, int level, int num_slots, int ncomp);
+/* Cell-localised field (Layout< Real, Cell >: duplicateLayers 0, ghostLayers 1): n-1 cells per
+ * dimension where the level has n nodes; upload/download move the dense cell array, no ghosts.
+ * 2D, single block so far. */
+int examg_field_create_cell(examg_ctx *ctx, const char *name, int level, int num_slots, int ncomp);
+int examg_level_cells(examg_ctx *ctx, int level, int n[3]);
 int examg_field_destroy(examg_ctx *ctx, int field);
 int examg_field_num_slots(examg_ctx *ctx, int field);
 int examg_field_active_slot(examg_ctx *ctx, int field);          /* currentSlot              */
@@ -95,7 +100,9 @@ enum {
   EXAMG_BC_NONE = 0,
   EXAMG_BC_DIRICHLET_CONST = 1, /* value                                             */
   EXAMG_BC_DIRICHLET_EXPR = 2,  /* postfix program over vf_boundaryPosition_{x,y,z}  */
-  EXAMG_BC_DIRICHLET_HOST = 3   /* boundary nodes keep what upload() wrote           */
+  EXAMG_BC_DIRICHLET_HOST = 3,  /* boundary nodes keep what upload() wrote           */
+  EXAMG_BC_NEUMANN = 4          /* cell fields, order 1: ghost cell = adjacent inner cell
+                                   (C/s/e/boundary/ir/IR_NeumannBC.scala:70-80)       */
 };
 /* postfix (RPN) program for boundary expressions -- what the kernel printer
  * lowers `vf_boundaryPosition_x ** 2 - 0.5 * ...` to.  Evaluated in double with
@@ -207,6 +214,57 @@ int examg_solver_cycles(examg_solver *s, int n, double *norm_out);
 int examg_solver_residual_norm(examg_solver *s, double *norm_out);
 /* CG iterations of the most recent coarse solve (synchronises) */
 int examg_solver_last_cg_iters(examg_solver *s, int *iters_out);
+
+/* ---- coupled two-unknown systems on cell fields: the optical-flow programs -----------------
+ * (Benchmark/OptFlow2D/2D_FD_OptFlow.exa4, Testing/Application/OpticalFlow2D.exa4)
+ *   A = [ c_uu + scale*L   c_uv          ]   L = constant 5-point stencil (declared centre,-x,+x,-y,+y),
+ *       [ c_uv             c_vv + scale*L ]   c_* = cell fields (uuSten, uvSten = vuSten, vvSten)
+ * All loops run over all cells; Neumann ghost cells of the written fields are refreshed by the same
+ * kernel (`apply bc` costs no launch).                                                          */
+typedef struct {
+  int laplace;          /* stencil handle; fixes the level */
+  double scale;         /* alpha ** 2 */
+  int c_uu, c_uv, c_vv; /* cell-field handles */
+} examg_system2_desc;
+int examg_system2_create(examg_ctx *ctx, const examg_system2_desc *desc);
+/* residual_u = rhs_u - A_u(u,v); residual_v alike; apply bc; *norm2_out (nullable) = sum of both squares */
+int examg_system2_residual(examg_ctx *ctx, int sys, int u, int v, int rhs_u, int rhs_v, int res_u, int res_v,
+                           double *norm2_out);
+/* nsweeps x { colour 0, colour 1: loop over u { solve locally relax r { u => A_u == rhs_u; v => A_v == rhs_v } };
+ * apply bc }  (C/s/e/solver/ir/IR_LocalSolve.scala:88-236, IR_LocalDirectInvert.scala:44-140)   */
+int examg_system2_smooth_rb(examg_ctx *ctx, int sys, int u, int v, int rhs_u, int rhs_v, double relax, int nsweeps);
+int examg_system2_smooth_rb_color(examg_ctx *ctx, int sys, int u, int v, int rhs_u, int rhs_v, double relax,
+                                  int color);
+/* coarse[k] = RestrictionCell * fine[k] (mean of the 2^d children), k < nfields <= 3
+ * (C/s/e/operator/l4/L4_DefaultRestriction.scala:40-47)                                         */
+int examg_restrict_cell(examg_ctx *ctx, const int *fine, const int *coarse, int nfields);
+/* fine[k] += ProlongationCell * coarse[k] (piecewise constant); apply bc
+ * (C/s/e/operator/l4/L4_DefaultProlongation.scala:30-45)                                        */
+int examg_prolong_add_cell(examg_ctx *ctx, const int *coarse, const int *fine, int nfields);
+/* mgCycle@coarsest of the optical-flow programs: CG on both unknowns.  fields = { u, v, rhs_u, rhs_v,
+ * residual_u, residual_v, cgTmp0_u, cgTmp0_v, cgTmp1_u, cgTmp1_v }; runs on the device.        */
+int examg_system2_cg_coarse(examg_ctx *ctx, int sys, const int *fields, int max_it, double rel_tol, int *iters_out);
+
+/* whole program: InitFields / mgCycle@all / doSolve@finest as one library object */
+typedef struct {
+  double alpha;          /* Globals { Val alpha }              */
+  double relax;          /* solve locally relax ...            */
+  int nu_pre, nu_post;   /* repeat 3 times                     */
+  int cg_max_it;         /* 128                                */
+  double cg_rel_tol;     /* 0.001                              */
+} examg_optflow_desc;
+typedef struct examg_optflow examg_optflow;
+examg_optflow *examg_optflow_create(examg_ctx *ctx, const examg_optflow_desc *desc);
+int examg_optflow_destroy(examg_optflow *o);
+enum { EXAMG_OF_U = 0, EXAMG_OF_V = 1, EXAMG_OF_RHS_U = 2, EXAMG_OF_RHS_V = 3, EXAMG_OF_RES_U = 4, EXAMG_OF_RES_V = 5,
+       EXAMG_OF_IXIX = 6, EXAMG_OF_IXIY = 7, EXAMG_OF_IYIY = 8, EXAMG_OF_IMG0 = 9, EXAMG_OF_IMG1 = 10 };
+int examg_optflow_field(examg_optflow *o, int level, int which);
+/* after img0/img1 were uploaded: apply bc to the images, initGradients@all, rhs@finest */
+int examg_optflow_init_fields(examg_optflow *o);
+int examg_optflow_vcycle(examg_optflow *o, int level);              /* mgCycle@level (< 0: finest) */
+int examg_optflow_cycles(examg_optflow *o, int n, double *norm_out); /* n cycles + residual norm    */
+int examg_optflow_residual_norm(examg_optflow *o, double *norm_out);
+int examg_optflow_last_cg_iters(examg_optflow *o, int *iters_out);
 
 /* ---- multi-GPU plumbing (one process per GPU) ---------------------------------
  * Peers are wired by exchanging opaque blobs through the host's process group
