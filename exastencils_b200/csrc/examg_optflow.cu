@@ -24,12 +24,21 @@
 // n-1 cells use the n-node allocation; ghost cells are elements -1 and n_cells.
 #include <cmath>
 #include <map>
+#include <type_traits>
+#include <utility>
+#include <vector>
 
 #include "examg_cg.cuh"
 
 using namespace examg;
 
 namespace examg {
+
+// fn(integral_constant<K>) for K = 0, 1, ... until it returns false
+template <int... Ks, class F>
+__device__ __forceinline__ bool of_steps(std::integer_sequence<int, Ks...>, F &&fn) {
+  return (fn(std::integral_constant<int, Ks>{}) && ...);
+}
 
 struct OfArgs {
   int nx, ny, pitch;
@@ -74,9 +83,10 @@ __device__ __forceinline__ void of_local_solve(const OfArgs &a, const double *u,
   const double f1 = fv[p] - a.a2 * of_off(a.L, v, p, a.pitch);
   const double a01 = a.cuv[p];
   const double a00 = fma(a.a2, a.L[0], a.cuu[p]), a11 = fma(a.a2, a.L[0], a.cvv[p]);
-  const double det = a00 * a11 - a01 * a01;
-  const double su = (a11 * f0 - a01 * f1) / det;
-  const double sv = (a00 * f1 - a01 * f0) / det;
+  const double rdet = 1.0 / (a00 * a11 - a01 * a01);
+  const double i00 = rdet * a11, i01 = -(rdet * a01), i11 = rdet * a00;
+  const double su = i00 * f0 + i01 * f1;
+  const double sv = i01 * f0 + i11 * f1;
   nu = u[p] * keep + relax * su;
   nv = v[p] * keep + relax * sv;
 }
@@ -207,6 +217,143 @@ k_of_init(const double *__restrict__ img0, const double *__restrict__ img1, int 
   }
 }
 
+
+// ---- fused red-black block smoother: S half-sweeps (S/2 sweeps) per pass over HBM ---------------------
+// "Warp-private wavefront": a warp owns a strip of 64 cells in x (S-deep halo each side included) and
+// marches in y; a lane owns two adjacent cells (one of each colour) and keeps S+2 rows of u, v and S+1
+// rows of the five read-only arrays (rhs_u, rhs_v, IxIx, IxIy, IyIy) in registers.  Half-sweep s works on
+// row t-s, one row behind half-sweep s-1: the y neighbours are the lane's own registers, the x neighbours
+// its other cell and one warp shuffle.  No shared memory, no block-wide barrier; 128-bit coalesced loads
+// (512 B per row, array and warp) issued one row ahead.  Out of place (u, v -> second buffers, exchanged
+// afterwards), because neighbouring strips read each other's halo.  Neumann boundaries = clamped
+// neighbour access; the ghost cells of the result are written with the cells they mirror.
+// HBM traffic per cell: 7 reads + 2 writes = 72 B per pass for S/2 sweeps of 80 B algorithmic each
+// (halo columns come from L2: adjacent strips run in the same CTA).
+template <int S>
+__global__ void __launch_bounds__(128)
+k_of_rbw(const OfArgs a, const double *__restrict__ u, const double *__restrict__ v, const double *__restrict__ fu,
+         const double *__restrict__ fv, double *__restrict__ uo, double *__restrict__ vo, double relax, int seg_rows,
+         int nstrips) {
+  constexpr int NW = S + 2, IW = 64 - 2 * S;
+  const int lane = threadIdx.x & 31;
+  const int strip = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (strip >= nstrips) return;  // whole warp
+  const int nx = a.nx, ny = a.ny, pitch = a.pitch;
+  const int ox = IW * strip, x0 = ox - S + 2 * lane;  // x0 even: cell A = (x0, .), cell B = (x0+1, .)
+  const int za = blockIdx.y * seg_rows, zb = min(ny, za + seg_rows);
+  int t0 = za - S;
+  t0 -= t0 & 1;  // even: at odd steps every half-sweep updates cell A of its row, at even steps cell B
+  const int tl = zb - 1 + S;
+  const bool inx = x0 >= 0 && x0 < nx;
+  const bool west_edge = x0 == 0, east_edge = x0 + 1 == nx - 1;
+  const bool st = inx && x0 >= ox && x0 < ox + IW;
+  const double keep = 1.0 - relax, a2 = a.a2;
+  const double L0 = a.L[0], L1 = a.L[1], L2 = a.L[2], L3 = a.L[3], L4 = a.L[4];
+
+  double uw[NW][2], vw[NW][2], cf[NW][5][2];  // cf: rhs_u, rhs_v and the inverse of the cell's 2x2 block: I00, I01, I11
+#pragma unroll
+  for (int q = 0; q < NW; ++q) {
+    uw[q][0] = uw[q][1] = vw[q][0] = vw[q][1] = 0.0;
+#pragma unroll
+    for (int k = 0; k < 5; ++k) cf[q][k][0] = cf[q][k][1] = 0.0;
+  }
+  double2 nx_u, nx_v, nx_c[5];  // row t+1, in flight
+  auto fetch = [&](int r) {
+    if (inx && r >= 0 && r < ny && r <= tl) {
+      const long long p = x0 + (long long)pitch * r;
+      nx_u = *reinterpret_cast<const double2 *>(u + p);
+      nx_v = *reinterpret_cast<const double2 *>(v + p);
+      nx_c[0] = __ldg(reinterpret_cast<const double2 *>(fu + p));
+      nx_c[1] = __ldg(reinterpret_cast<const double2 *>(fv + p));
+      nx_c[2] = __ldg(reinterpret_cast<const double2 *>(a.cuu + p));
+      nx_c[3] = __ldg(reinterpret_cast<const double2 *>(a.cuv + p));
+      nx_c[4] = __ldg(reinterpret_cast<const double2 *>(a.cvv + p));
+    } else {
+      nx_u = nx_v = make_double2(0.0, 0.0);
+#pragma unroll
+      for (int k = 0; k < 5; ++k) nx_c[k] = make_double2(0.0, 0.0);
+    }
+  };
+  fetch(t0);
+
+  auto step = [&](auto kc, const int t) {
+    constexpr int K = decltype(kc)::value;
+    constexpr int X = (K & 1) ? 0 : 1;  // the cell every half-sweep updates at this step
+    uw[K][0] = nx_u.x; uw[K][1] = nx_u.y; vw[K][0] = nx_v.x; vw[K][1] = nx_v.y;
+    cf[K][0][0] = nx_c[0].x; cf[K][0][1] = nx_c[0].y; cf[K][1][0] = nx_c[1].x; cf[K][1][1] = nx_c[1].y;
+    {  // the block inverse depends on the coefficients only: once per cell and pass, off the critical path
+      const double a00x = fma(a2, L0, nx_c[2].x), a11x = fma(a2, L0, nx_c[4].x), a01x = nx_c[3].x;
+      const double a00y = fma(a2, L0, nx_c[2].y), a11y = fma(a2, L0, nx_c[4].y), a01y = nx_c[3].y;
+      const double rx = 1.0 / (a00x * a11x - a01x * a01x), ry = 1.0 / (a00y * a11y - a01y * a01y);
+      cf[K][2][0] = rx * a11x; cf[K][3][0] = -(rx * a01x); cf[K][4][0] = rx * a00x;
+      cf[K][2][1] = ry * a11y; cf[K][3][1] = -(ry * a01y); cf[K][4][1] = ry * a00y;
+    }
+    fetch(t + 1);
+#pragma unroll
+    for (int s = 1; s <= S; ++s) {
+      const int c = (K + NW - s) % NW, cm = (K + NW - s - 1) % NW, cp = (K + NW - s + 1) % NW;
+      const int r = t - s;
+      // x neighbour owned by the adjacent lane: A's west = B of lane-1, B's east = A of lane+1
+      const double su = X == 0 ? __shfl_up_sync(0xffffffffu, uw[c][1], 1) : __shfl_down_sync(0xffffffffu, uw[c][0], 1);
+      const double sv = X == 0 ? __shfl_up_sync(0xffffffffu, vw[c][1], 1) : __shfl_down_sync(0xffffffffu, vw[c][0], 1);
+      if (inx && r >= 0 && r < ny) {
+        const double cu = uw[c][X], cv = vw[c][X];
+        double uwst, uest, vwst, vest;
+        if (X == 0) {
+          uwst = west_edge ? cu : su; vwst = west_edge ? cv : sv;
+          uest = uw[c][1]; vest = vw[c][1];
+        } else {
+          uwst = uw[c][0]; vwst = vw[c][0];
+          uest = east_edge ? cu : su; vest = east_edge ? cv : sv;
+        }
+        const double usth = r == 0 ? cu : uw[cm][X], vsth = r == 0 ? cv : vw[cm][X];
+        const double unth = r == ny - 1 ? cu : uw[cp][X], vnth = r == ny - 1 ? cv : vw[cp][X];
+        double o0 = L1 * uwst;
+        o0 = fma(L2, uest, o0);
+        o0 = fma(L3, usth, o0);
+        o0 = fma(L4, unth, o0);
+        double o1 = L1 * vwst;
+        o1 = fma(L2, vest, o1);
+        o1 = fma(L3, vsth, o1);
+        o1 = fma(L4, vnth, o1);
+        const double f0 = cf[c][0][X] - a2 * o0, f1 = cf[c][1][X] - a2 * o1;
+        const double nu = cf[c][2][X] * f0 + cf[c][3][X] * f1;
+        const double nv = cf[c][3][X] * f0 + cf[c][4][X] * f1;
+        uw[c][X] = cu * keep + relax * nu;
+        vw[c][X] = cv * keep + relax * nv;
+      }
+    }
+    const int zf = t - S;
+    if (st && zf >= za && zf < zb) {
+      const int c = (K + NW - S) % NW;
+      const double2 ru = make_double2(uw[c][0], uw[c][1]), rv = make_double2(vw[c][0], vw[c][1]);
+      const long long p = x0 + (long long)pitch * zf;
+      *reinterpret_cast<double2 *>(uo + p) = ru;
+      *reinterpret_cast<double2 *>(vo + p) = rv;
+      // Neumann ghost cells mirror the cells just written
+      if (west_edge) { uo[p - 1] = ru.x; vo[p - 1] = rv.x; }
+      if (east_edge) { uo[p + 2] = ru.y; vo[p + 2] = rv.y; }
+      if (zf == 0 || zf == ny - 1) {
+        const long long g = p + (zf == 0 ? -(long long)pitch : (long long)pitch);
+        *reinterpret_cast<double2 *>(uo + g) = ru;
+        *reinterpret_cast<double2 *>(vo + g) = rv;
+        if (west_edge) { uo[g - 1] = ru.x; vo[g - 1] = rv.x; }
+        if (east_edge) { uo[g + 2] = ru.y; vo[g + 2] = rv.y; }
+      }
+    }
+  };
+
+  for (int t = t0; t <= tl; t += NW) {
+    const bool more = of_steps(std::make_integer_sequence<int, NW>{}, [&](auto kc) {
+      constexpr int K = decltype(kc)::value;
+      if (t + K > tl) return false;
+      step(kc, t + K);
+      return true;
+    });
+    if (!more) break;
+  }
+}
+
 // mgCycle@coarsest: the coupled CG, whole solve in one CTA (the grid has a few dozen cells)
 __global__ void __launch_bounds__(1024)
 k_of_cg(const OfArgs a, double *u, double *v, const double *fu, const double *fv, double *ru, double *rv, double *pu,
@@ -318,6 +465,65 @@ int launch_bc_cell(examg_ctx *c, const Field &f, int slot) {
   return EXAMG_OK;
 }
 
+int ensure_shadow(examg_ctx *c, Field &fu);  // examg_fast7.cu
+
+// sweeps fused into one pass (EXAMG_OF_FUSE_SWEEPS = 0..3; 0: one kernel per colour)
+static int of_max_sweeps() {
+  static int v = -1;
+  if (v < 0) {
+    const char *e = getenv("EXAMG_OF_FUSE_SWEEPS");
+    v = e ? atoi(e) : 3;
+    v = v < 0 ? 0 : v > 3 ? 3 : v;
+  }
+  return v;
+}
+
+static bool of_fused_usable(examg_ctx *c, const System2 &s) {
+  const LevelGeom &g = *geom(c, s.level);
+  const int nx = g.n[0] - 1, ny = g.n[1] - 1;
+  return of_max_sweeps() > 0 && nx % 2 == 0 && nx >= 128 && ny >= 16;
+}
+
+template <int S>
+static int launch_of_rbw_s(examg_ctx *c, const OfArgs &a, const double *u, const double *v, const double *bu,
+                           const double *bv, double *uo, double *vo, double relax) {
+  constexpr int IW = 64 - 2 * S;
+  const int nstrips = (a.nx + IW - 1) / IW;
+  const int gx = (nstrips + 3) / 4;
+  // rows per segment: enough CTAs for a few waves, but segments long against their 2S warm-up rows
+  int nseg = (148 * 12 + gx - 1) / gx;
+  const int max_seg = a.ny / (16 * S) > 0 ? a.ny / (16 * S) : 1;
+  if (nseg > max_seg) nseg = max_seg;
+  const int seg_rows = (a.ny + nseg - 1) / nseg;
+  nseg = (a.ny + seg_rows - 1) / seg_rows;
+  k_of_rbw<S><<<dim3(gx, nseg), 128, 0, c->stream>>>(a, u, v, bu, bv, uo, vo, relax, seg_rows, nstrips);
+  EXAMG_LAUNCH_CHECK(c);
+  return EXAMG_OK;
+}
+
+// `sweeps` red-black sweeps in one pass; exchanges the buffers of u and v with their second buffers
+static int launch_of_rbw(examg_ctx *c, const System2 &s, Field &fu, Field &fv, const double *bu, const double *bv,
+                         double relax, int sweeps) {
+  const LevelGeom &g = *geom(c, s.level);
+  const OfArgs a = of_args(c, s);
+  const double *u = field_ptr(c, &fu, -1), *v = field_ptr(c, &fv, -1);
+  double *uo = fu.shadow + g.origin, *vo = fv.shadow + g.origin;
+  int rc;
+  switch (sweeps) {
+    case 1: rc = launch_of_rbw_s<2>(c, a, u, v, bu, bv, uo, vo, relax); break;
+    case 2: rc = launch_of_rbw_s<4>(c, a, u, v, bu, bv, uo, vo, relax); break;
+    default: rc = launch_of_rbw_s<6>(c, a, u, v, bu, bv, uo, vo, relax); break;
+  }
+  if (rc) return rc;
+  for (Field *f : {&fu, &fv}) {
+    double *t = f->slot[f->cur];
+    f->slot[f->cur] = f->shadow;
+    f->shadow = t;
+    f->swapped = !f->swapped;
+  }
+  return EXAMG_OK;
+}
+
 #define OF_SYS(var, h)                  \
   System2 *var = get_system(c, h);      \
   if (!var) return set_error(EXAMG_EINVAL, "%s: bad system handle %d", __func__, h)
@@ -392,6 +598,21 @@ int examg_system2_smooth_rb_color(examg_ctx *c, int sys, int u, int v, int rhs_u
 }
 
 int examg_system2_smooth_rb(examg_ctx *c, int sys, int u, int v, int rhs_u, int rhs_v, double relax, int nsweeps) {
+  {
+    OF_SYS(s, sys);
+    OF_FIELD(fu, u, s->level); OF_FIELD(fv, v, s->level); OF_FIELD(bu, rhs_u, s->level); OF_FIELD(bv, rhs_v, s->level);
+    if (of_fused_usable(c, *s) && fu != fv) {  // up to three sweeps per pass over HBM
+      int rc;
+      if ((rc = ensure_shadow(c, *fu)) || (rc = ensure_shadow(c, *fv))) return rc;
+      for (int it = 0; it < nsweeps;) {
+        int plan = of_max_sweeps();
+        if (plan > nsweeps - it) plan = nsweeps - it;
+        if ((rc = launch_of_rbw(c, *s, *fu, *fv, field_ptr(c, bu, -1), field_ptr(c, bv, -1), relax, plan))) return rc;
+        it += plan;
+      }
+      return EXAMG_OK;
+    }
+  }
   for (int it = 0; it < nsweeps; ++it)
     for (int color = 0; color < 2; ++color) {
       int rc = examg_system2_smooth_rb_color(c, sys, u, v, rhs_u, rhs_v, relax, color);
@@ -468,8 +689,8 @@ struct examg_optflow {
   std::vector<int> sys;    // per level
   int img0 = -1, img1 = -1;
   int cg[4] = {-1, -1, -1, -1};  // cgTmp0_u, cgTmp0_v, cgTmp1_u, cgTmp1_v @coarsest
-  cudaGraphExec_t graph = nullptr;
-  long long graph_launches = 0;
+  struct Graph { cudaGraphExec_t exec = nullptr; long long launches = 0; std::vector<int> exit_state; };
+  std::map<std::vector<int>, Graph> graphs;  // keyed by which buffer of u, v is active on every level
 };
 
 namespace {
@@ -482,6 +703,27 @@ int of_zero(examg_ctx *c, int h) {  // u@coarser = 0; apply bc: the whole alloca
   EXAMG_CUDA(cudaMemsetAsync(f->slot[f->cur], 0, sizeof(double) * (size_t)g.vol, c->stream));
   c->launches++;
   return EXAMG_OK;
+}
+
+std::vector<int> of_state(examg_optflow *o) {
+  std::vector<int> key;
+  for (int k = 0; k < 2; ++k)
+    for (int h : o->f[k]) key.push_back(o->c->fields[h].swapped ? 1 : 0);
+  return key;
+}
+
+void of_restore(examg_optflow *o, const std::vector<int> &key) {
+  size_t pos = 0;
+  for (int k = 0; k < 2; ++k)
+    for (int h : o->f[k]) {
+      Field &f = o->c->fields[h];
+      if ((f.swapped ? 1 : 0) != key[pos++]) {
+        double *t = f.slot[f.cur];
+        f.slot[f.cur] = f.shadow;
+        f.shadow = t;
+        f.swapped = !f.swapped;
+      }
+    }
 }
 
 int of_vcycle_rec(examg_optflow *o, int level) {
@@ -547,6 +789,9 @@ examg_optflow *examg_optflow_create(examg_ctx *c, const examg_optflow_desc *d) {
     const int sh = st >= 0 ? examg_system2_create(c, &sd) : -1;
     ok = ok && sh >= 0;
     o->sys.push_back(sh);
+    // second buffers of the fused sweeps: now, graph capture cannot allocate
+    if (ok && of_fused_usable(c, c->systems[sh]))
+      ok = ensure_shadow(c, c->fields[o->f[0].back()]) == EXAMG_OK && ensure_shadow(c, c->fields[o->f[1].back()]) == EXAMG_OK;
   }
   if (ok) {
     o->img0 = examg_field_create_cell(c, "img0", c->cfg.max_level, 1, 1);
@@ -573,7 +818,8 @@ examg_optflow *examg_optflow_create(examg_ctx *c, const examg_optflow_desc *d) {
 
 int examg_optflow_destroy(examg_optflow *o) {
   if (!o) return EXAMG_OK;
-  if (o->graph) cudaGraphExecDestroy(o->graph);
+  for (auto &kv : o->graphs)
+    if (kv.second.exec) cudaGraphExecDestroy(kv.second.exec);
   delete o;
   return EXAMG_OK;
 }
@@ -616,7 +862,10 @@ int examg_optflow_vcycle(examg_optflow *o, int level) {
   if (level < 0) level = c->cfg.max_level;
   if (level < c->cfg.min_level || level > c->cfg.max_level) return set_error(EXAMG_EINVAL, "examg_optflow_vcycle: level %d", level);
   if (level != c->cfg.max_level) return of_vcycle_rec(o, level);
-  if (!o->graph) {  // everything is in place: one graph serves every cycle
+  // one graph per buffer state (the fused sweeps exchange u, v with their second buffers)
+  const std::vector<int> key = of_state(o);
+  auto it = o->graphs.find(key);
+  if (it == o->graphs.end()) {
     const long long l0 = c->launches;
     cudaGraph_t graph = nullptr;
     EXAMG_CUDA(cudaStreamBeginCapture(c->stream, cudaStreamCaptureModeThreadLocal));
@@ -624,14 +873,19 @@ int examg_optflow_vcycle(examg_optflow *o, int level) {
     const cudaError_t e = cudaStreamEndCapture(c->stream, &graph);
     if (rc) { if (graph) cudaGraphDestroy(graph); return rc; }
     if (e != cudaSuccess) return set_error(EXAMG_ECUDA, "graph capture of mgCycle failed: %s", cudaGetErrorString(e));
-    const cudaError_t e2 = cudaGraphInstantiate(&o->graph, graph, 0);
+    examg_optflow::Graph g;
+    const cudaError_t e2 = cudaGraphInstantiate(&g.exec, graph, 0);
     cudaGraphDestroy(graph);
     if (e2 != cudaSuccess) return set_error(EXAMG_ECUDA, "cudaGraphInstantiate: %s", cudaGetErrorString(e2));
-    o->graph_launches = c->launches - l0;
-    c->launches = l0;
+    g.launches = c->launches - l0;
+    c->launches = l0;  // nothing ran yet
+    g.exit_state = of_state(o);
+    of_restore(o, key);
+    it = o->graphs.emplace(key, g).first;
   }
-  EXAMG_CUDA(cudaGraphLaunch(o->graph, c->stream));
-  c->launches += o->graph_launches;
+  EXAMG_CUDA(cudaGraphLaunch(it->second.exec, c->stream));
+  c->launches += it->second.launches;
+  of_restore(o, it->second.exit_state);
   return EXAMG_OK;
 }
 

@@ -16,8 +16,9 @@
  *                       C/s/e/boundary/ir/IR_ApplyBCFunction.scala:53-85
  *   local solve         C/s/e/solver/ir/IR_LocalSolve.scala:88-236 (unknowns at the cell -> matrix,
  *                       everything else -> right-hand side), IR_LocalDirectInvert.scala:44-140
- *                       (write back u*(1-relax) + relax*u_new), 2x2 system by cofactors
- *                       (C/s/e/solver/ir/IR_SolveMatrixSystem.scala, compile-time branch)
+ *                       (write back u*(1-relax) + relax*u_new), 2x2 system by the explicit inverse
+ *                       (C/s/e/solver/ir/IR_SolveMatrixSystem.scala compile-time branch ->
+ *                       IR_CompiletimeMatOps.scala:796-803)
  *   cell restriction    [1/2,1/2]^d, prolongation = transpose * 2^d = piecewise constant:
  *                       C/s/e/operator/l4/L4_DefaultRestriction.scala:40-47,
  *                       L4_DefaultProlongation.scala:30-45
@@ -33,7 +34,10 @@
  *   smoother at one cell:
  *     o(w)  = Lw*w_w, then fma(Le,..), fma(Ls,..), fma(Ln,..)       (off-centre part)
  *     f0 = rhs_u - a2*o(u); f1 = rhs_v - a2*o(v); A00 = fma(a2,Lc,cuu); A11 = fma(a2,Lc,cvv); A01 = A10 = cuv
- *     det = A00*A11 - A01*A10;  nu = (A11*f0 - A01*f1)/det;  nv = (A00*f1 - A10*f0)/det
+ *     the 2x2 inverse as the generator's compile-time branch writes it
+ *     (C/s/e/baseExt/ir/IR_MatOperations/IR_CompiletimeMatOps.scala:796-803):
+ *     rdet = 1/(A00*A11 - A01*A10); I00 = rdet*A11; I01 = I10 = -(rdet*A01); I11 = rdet*A00
+ *     nu = I00*f0 + I01*f1;  nv = I10*f0 + I11*f1          (products rounded, then added)
  *     u = u*(1-relax) + relax*nu;  v alike
  *   sums: double-double, as in examg_oracle.c
  */
@@ -121,9 +125,10 @@ void ogf_smooth_color(int nx, int ny, const double L[5], double a2, const double
       const double f0 = fu[p] - a2 * ogf_off(L, u, p, sy);
       const double f1 = fv[p] - a2 * ogf_off(L, v, p, sy);
       const double a00 = fma(a2, L[0], cuu[p]), a11 = fma(a2, L[0], cvv[p]), a01 = cuv[p];
-      const double det = a00 * a11 - a01 * a01;
-      const double nu = (a11 * f0 - a01 * f1) / det;
-      const double nv = (a00 * f1 - a01 * f0) / det;
+      const double rdet = 1.0 / (a00 * a11 - a01 * a01);
+      const double i00 = rdet * a11, i01 = -(rdet * a01), i11 = rdet * a00;
+      const double nu = i00 * f0 + i01 * f1;
+      const double nv = i01 * f0 + i11 * f1;
       u[p] = u[p] * keep + relax * nu;
       v[p] = v[p] * keep + relax * nv;
     }
