@@ -115,8 +115,13 @@ static int vcycle_rec(examg_solver *s, int level) {
   int rc;
   if ((rc = smooth(s, level, s->desc.nu_pre))) return rc;
   // several blocks: the residual of the first ghost layer is computed here too, so the restriction needs no exchange
-  if ((rc = residual_op(c, s->stencils[l], s->sol[l], -1, s->rhs[l], s->res[l], nullptr, 1))) return rc;
-  if ((rc = examg_restrict(c, s->res[l], s->rhs[l - 1], s->desc.restrict_scale))) return rc;
+  // (on large 3D constant-coefficient levels residual and restriction are one pass and Residual is not materialised)
+  rc = residual_restrict_op(c, s->stencils[l], s->sol[l], s->rhs[l], s->rhs[l - 1], s->desc.restrict_scale);
+  if (rc < 0) return rc;
+  if (rc == 1) {
+    if ((rc = residual_op(c, s->stencils[l], s->sol[l], -1, s->rhs[l], s->res[l], nullptr, 1))) return rc;
+    if ((rc = examg_restrict(c, s->res[l], s->rhs[l - 1], s->desc.restrict_scale))) return rc;
+  }
   if (c->world > 1 && level - 1 == s->agg_level) {
     if ((rc = agg_cycle(s))) return rc;
   } else {

@@ -377,7 +377,7 @@ static int make_plane_map(const LevelGeom &g, const double *base, CUtensorMap *t
 }
 
 // 0 / 1: one of the two known declaration orders; -1: something else (generic kernels)
-static int stencil_order(const Stencil &s) {
+int stencil_order(const Stencil &s) {
   static const int dx[2][7] = {{0, -1, 1, 0, 0, 0, 0}, {0, 1, -1, 0, 0, 0, 0}};
   static const int dy[2][7] = {{0, 0, 0, -1, 1, 0, 0}, {0, 0, 0, 1, -1, 0, 0}};
   static const int dz[2][7] = {{0, 0, 0, 0, 0, -1, 1}, {0, 0, 0, 0, 0, 1, -1}};
@@ -586,16 +586,6 @@ int launch_jac_fused(examg_ctx *c, const Stencil &s, double omega, Field &fu, co
     case 2: return launch_jacw<2>(c, s, omega, fu, rhs);
     default: return launch_jacw<3>(c, s, omega, fu, rhs);
   }
-}
-
-bool fast7_usable(examg_ctx *c, const Stencil &s) { (void)c; (void)s; return false; }
-int fast7_residual(examg_ctx *c, const Stencil &s, const double *u, const double *rhs, double *res, int red_slot) {
-  (void)c; (void)s; (void)u; (void)rhs; (void)res; (void)red_slot;
-  return set_error(EXAMG_EUNSUP, "fast7_residual");
-}
-int fast7_rb(examg_ctx *c, const Stencil &s, double omega, double *u, const double *rhs, int color) {
-  (void)c; (void)s; (void)omega; (void)u; (void)rhs; (void)color;
-  return set_error(EXAMG_EUNSUP, "fast7_rb");
 }
 
 }  // namespace examg

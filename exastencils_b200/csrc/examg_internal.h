@@ -182,6 +182,8 @@ int launch_residual(examg_ctx *c, const Stencil &s, const double *u, const doubl
 // Residual = RHS - A*Solution incl. `communicate Solution`; extend > 0: also on that many layers of the
 // neighbour blocks' nodes (then Residual needs no exchange before the restriction)
 int residual_op(examg_ctx *c, int A, int u, int u_slot, int rhs, int res, double *norm2_out, int extend);
+// fused residual + restriction (examg_resrestrict.cu); 1 = not covered, run the two loops
+int residual_restrict_op(examg_ctx *c, int A, int u, int rhs, int rhs_coarse, double scale);
 int launch_jacobi(examg_ctx *c, const Stencil &s, double omega, const double *u, const double *rhs,
                   double *unext);
 int launch_rb(examg_ctx *c, const Stencil &s, double omega, double *u, const double *rhs, int color);

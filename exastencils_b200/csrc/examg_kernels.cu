@@ -28,12 +28,33 @@ k_stencil(const GridArgs g, const __grid_constant__ StencilArgs st, const double
   const int z0 = g.lo[2] + blockIdx.z * kz;
   const int z1 = min(z0 + kz, g.hi[2]);
   dd part = {0.0, 0.0};
-  // Sum of squares: the (non-negative) squares of up to four consecutive planes are added in plain double
-  // before they enter the double-double sum -- relative error <= 4 ulp, far inside the 1e-14 the tests
-  // allow -- so that the loop-carried TwoSum chain is paid once per four points.
+  // Sum of squares: the (non-negative) squares of up to eight consecutive planes are added in plain double
+  // before they enter the double-double sum -- relative error <= 8 ulp, far inside the 1e-14 the tests
+  // allow -- so that the loop-carried TwoSum chain is paid once per eight points, and without a
+  // data-dependent branch in the plane loop.
   double sq = 0.0;
-  int nsq = 0;
   for (int j = g.lo[1] + blockIdx.y * blockDim.y + threadIdx.y; j < g.hi[1]; j += gridDim.y * blockDim.y) {
+    if (MODE == M_RESNORM) {
+      // the plane loop in chunks of eight without a data-dependent branch inside (the compiler pipelines it
+      // like the plain residual loop); one TwoSum per chunk
+      const int i = g.lo[0] + tx;
+      if (i < g.hi[0]) {
+        const bool cnt_ij = i >= g.rlo[0] && i < g.rhi[0] && j >= g.rlo[1] && j < g.rhi[1];
+        const int cz0 = cnt_ij ? max(z0, g.rlo[2]) : z1, cz1 = min(z1, g.rhi[2]);
+        for (int kb = z0; kb < z1; kb += 8) {
+          const int ke = min(kb + 8, z1);
+          for (int k = kb; k < ke; ++k) {
+            const long long p = i + (long long)g.pitch * j + g.plane * k;
+            const double r = rhs[p] - conv<NST, VAR>(st, sf, sfvol, u, p);
+            out[p] = r;
+            sq += (k >= cz0 && k < cz1) ? r * r : 0.0;
+          }
+          dd_add(part, sq);
+          sq = 0.0;
+        }
+      }
+      continue;
+    }
     for (int k = z0; k < z1; ++k) {
       int i;
       if (MODE == M_RB) {
@@ -47,14 +68,8 @@ k_stencil(const GridArgs g, const __grid_constant__ StencilArgs st, const double
         const double acc = conv<NST, VAR>(st, sf, sfvol, u, p);
         if (MODE == M_APPLY) {
           out[p] = acc;
-        } else if (MODE == M_RESIDUAL || MODE == M_RESNORM) {
-          const double r = rhs[p] - acc;
-          out[p] = r;
-          if (MODE == M_RESNORM && i >= g.rlo[0] && j >= g.rlo[1] && k >= g.rlo[2] && i < g.rhi[0] && j < g.rhi[1] &&
-              k < g.rhi[2]) {
-            sq += r * r;
-            if (++nsq == 4) { dd_add(part, sq); sq = 0.0; nsq = 0; }
-          }
+        } else if (MODE == M_RESIDUAL) {
+          out[p] = rhs[p] - acc;
         } else {
           const double ww = VAR ? w / sf[st.centre * sfvol + p] : w;  // w = omega (VAR) or omega/diag
           const double r = rhs[p] - acc;
@@ -64,7 +79,7 @@ k_stencil(const GridArgs g, const __grid_constant__ StencilArgs st, const double
     }
   }
   if (MODE == M_RESNORM) {
-    if (nsq > 0) dd_add(part, sq);
+    dd_add(part, sq);
     part = dd_block_reduce(part);
     if (threadIdx.x == 0 && threadIdx.y == 0)
       partials[blockIdx.x + gridDim.x * (blockIdx.y + gridDim.y * blockIdx.z)] = part;

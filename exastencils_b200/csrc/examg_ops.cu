@@ -14,27 +14,23 @@ int launch_jacobi_generic(examg_ctx *c, const Stencil &s, double omega, const do
 int launch_rb_generic(examg_ctx *c, const Stencil &s, double omega, double *u, const double *rhs, int color);
 int launch_restrict_generic(examg_ctx *c, int lvl_fine, double scale, const double *rf, double *rhsc);
 int launch_prolong_generic(examg_ctx *c, int lvl_fine, const double *uc, double *uf);
-// 3D 7-point constant-coefficient fast path (examg_fast7.cu)
-bool fast7_usable(examg_ctx *c, const Stencil &s);
-int fast7_residual(examg_ctx *c, const Stencil &s, const double *u, const double *rhs, double *res, int red_slot);
-int fast7_rb(examg_ctx *c, const Stencil &s, double omega, double *u, const double *rhs, int color);
 bool fused_rb_usable(examg_ctx *c, const Stencil &s, const Field &fu);
 int launch_rb_fused(examg_ctx *c, const Stencil &s, double omega, Field &fu, const double *rhs, int nsweeps, int *done);
 int rb_fused_plan(int nsweeps);
 bool fused_jac_usable(examg_ctx *c, const Stencil &s, const Field &fu);
 int launch_jac_fused(examg_ctx *c, const Stencil &s, double omega, Field &fu, const double *rhs, int nsweeps, int *done);
 int jac_fused_plan(int nsweeps);
+bool residual_restrict_usable(examg_ctx *c, const Stencil &s);
+int launch_residual_restrict(examg_ctx *c, const Stencil &s, const double *u, const double *rhs, double *rhsc, double scale);
 
 int launch_residual(examg_ctx *c, const Stencil &s, const double *u, const double *rhs, double *res, int red_slot,
                     int extend) {
-  if (fast7_usable(c, s)) return fast7_residual(c, s, u, rhs, res, red_slot);
   return launch_residual_generic(c, s, u, rhs, res, red_slot, extend);
 }
 int launch_jacobi(examg_ctx *c, const Stencil &s, double omega, const double *u, const double *rhs, double *unext) {
   return launch_jacobi_generic(c, s, omega, u, rhs, unext);
 }
 int launch_rb(examg_ctx *c, const Stencil &s, double omega, double *u, const double *rhs, int color) {
-  if (fast7_usable(c, s)) return fast7_rb(c, s, omega, u, rhs, color);
   return launch_rb_generic(c, s, omega, u, rhs, color);
 }
 int launch_restrict(examg_ctx *c, int lvl_fine, double scale, const double *rf, double *rhsc) {
@@ -78,6 +74,27 @@ int examg::residual_op(examg_ctx *c, int A, int u, int u_slot, int rhs, int res,
   return finish_sum(c, 0, norm2_out);
 }
 
+// RHS@coarser = scale * Restriction * (RHS - A*Solution) without materialising Residual (examg_resrestrict.cu);
+// returns 1 if the combination is not covered (the caller then runs the two separate loops)
+int examg::residual_restrict_op(examg_ctx *c, int A, int u, int rhs, int rhs_coarse, double scale) {
+  GET_STENCIL(s, A); GET_FIELD(fu, u); GET_FIELD(fr, rhs); GET_FIELD(fc, rhs_coarse);
+  CHECK_LEVEL(fu, s->level); CHECK_LEVEL(fr, s->level); CHECK_LEVEL(fc, s->level - 1);
+  if (!residual_restrict_usable(c, *s) || fu->ncomp != 1) return 1;
+  int rc;
+  if (c->world > 1) {  // the residual is needed one layer beyond the block: Solution 2 layers, RHS 1
+    if (fr->halo_depth < 1) {
+      Field *fs[2] = {fu, fr};
+      const int slots[2] = {fu->cur, fr->cur}, depths[2] = {2, 1};
+      rc = do_exchange_many(c, fs, slots, depths, 2);
+    } else {
+      rc = do_exchange(c, *fu, fu->cur, 2);
+    }
+    if (rc) return rc;
+  }
+  fc->halo_depth = 0;
+  return launch_residual_restrict(c, *s, field_ptr(c, fu, -1), field_ptr(c, fr, -1), field_ptr(c, fc, -1), scale);
+}
+
 extern "C" {
 
 int examg_apply(examg_ctx *c, int A, int u, int u_slot, int out) {
@@ -92,6 +109,13 @@ int examg_apply(examg_ctx *c, int A, int u, int u_slot, int out) {
 
 int examg_residual(examg_ctx *c, int A, int u, int u_slot, int rhs, int res, double *norm2_out) {
   return residual_op(c, A, u, u_slot, rhs, res, norm2_out, 0);
+}
+
+int examg_residual_restrict(examg_ctx *c, int A, int u, int rhs, int res, int rhs_coarse, double scale) {
+  int rc = residual_restrict_op(c, A, u, rhs, rhs_coarse, scale);
+  if (rc != 1) return rc;
+  if ((rc = residual_op(c, A, u, -1, rhs, res, nullptr, 1))) return rc;
+  return examg_restrict(c, res, rhs_coarse, scale);
 }
 
 int examg_smooth_jacobi(examg_ctx *c, int A, int u, int rhs, double omega, int nsweeps) {

@@ -100,6 +100,7 @@ SIGNATURES = {
     "examg_smooth_rbgs": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_double, C.c_int]),
     "examg_smooth_rb_color": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_double, C.c_int]),
     "examg_restrict": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_double]),
+    "examg_residual_restrict": (C.c_int, [C.c_void_p] + [C.c_int] * 5 + [C.c_double]),
     "examg_prolong_add": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int]),
     "examg_dot": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, _dp]),
     "examg_max_abs_diff": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, _dp]),
@@ -332,6 +333,9 @@ class Context:
 
     def restrict(self, res_fine, rhs_coarse, scale=1.0):
         check(self.L.examg_restrict(self.h, res_fine, rhs_coarse, scale))
+
+    def residual_restrict(self, A, u, rhs, res, rhs_coarse, scale=1.0):
+        check(self.L.examg_residual_restrict(self.h, A, u, rhs, res, rhs_coarse, scale))
 
     def prolong_add(self, u_coarse, u_fine, uc_slot=-1, uf_slot=-1):
         check(self.L.examg_prolong_add(self.h, u_coarse, uc_slot, u_fine, uf_slot))

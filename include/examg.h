@@ -161,6 +161,11 @@ int examg_smooth_rb_color(examg_ctx *ctx, int stencil, int u, int rhs, double om
 /* RHS@coarser = scale * NodeRestriction * Residual
  * (C/s/e/operator/l4/L4_DefaultRestriction.scala:29-90)                     */
 int examg_restrict(examg_ctx *ctx, int res_fine, int rhs_coarse, double scale);
+/* UpResidual + Restriction of mgCycle in one call: RHS@coarser = scale * NodeRestriction * (RHS - A * Solution).
+ * On large 3D constant-coefficient levels this is ONE pass over the fine grid and Residual is left untouched
+ * (inside mgCycle it only feeds the restriction, Benchmark/Poisson3D/3D_FD_Poisson_fromL4.exa4:216-224);
+ * otherwise the two loops run one after the other and Residual is written.                       */
+int examg_residual_restrict(examg_ctx *ctx, int stencil, int u, int rhs, int res, int rhs_coarse, double scale);
 /* Solution += NodeProlongation@coarser * Solution@coarser
  * (C/s/e/operator/l4/L4_DefaultProlongation.scala:30-45)                    */
 int examg_prolong_add(examg_ctx *ctx, int u_coarse, int u_coarse_slot, int u_fine, int u_fine_slot);

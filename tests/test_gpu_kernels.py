@@ -310,3 +310,35 @@ def test_jacobi_temporal_blocking(cells, lvl, order, oracle):
             e = og.smooth_jacobi(st, omega, e, rhs, None)
         assert np.array_equal(ctx.download(fu, lvl), e), "nu = %d" % nu
     ctx.close()
+
+
+@pytest.mark.parametrize("cells,lvl", [((1, 1, 1), 6), ((5, 3, 2), 5), ((1, 1, 1), 7), ((3, 1, 2), 6), ((1, 1, 1), 4)])
+@pytest.mark.parametrize("order", ["bench", "testing"])
+def test_residual_restrict_fused(cells, lvl, order, oracle):
+    """UpResidual + Restriction of mgCycle as one pass (examg_resrestrict.cu): RHS@coarser must be bit-identical to
+    the two separate loops of the oracle (Benchmark/Poisson3D/3D_FD_Poisson_fromL4.exa4:216-224)."""
+    og = oracle
+    ctx = _ctx(3, cells, lvl - 1, lvl)
+    fs, cs = ctx.shape(lvl), ctx.shape(lvl - 1)
+    offs = _ORDERS[order]
+    seed = 2000 * lvl + 10 * sum(cells) + (order == "testing")
+    coef = _rand(7, seed)
+    coef[0] = 4.0 + abs(coef[0])
+    A = ctx.stencil_const(lvl, offs, coef)
+    st = og.Stencil.make(offs, coef)
+    fu, ff, fr = ctx.field_create("u", lvl), ctx.field_create("rhs", lvl), ctx.field_create("res", lvl)
+    fc = ctx.field_create("rhs", lvl - 1)
+    u, rhs, sent = _rand(fs, seed + 1), _rand(fs, seed + 2), _rand(cs, seed + 3)
+    ctx.upload(fu, u)
+    ctx.upload(ff, rhs)
+    inner = (Ellipsis,) + tuple(slice(1, -1) for _ in range(3))
+    for scale in (1.0, 4.0):
+        ctx.upload(fc, sent)
+        ctx.residual_restrict(A, fu, ff, fr, fc, scale)
+        r = np.zeros(fs)
+        r[inner] = og.residual(st, u, rhs, None)[inner]  # Residual has Dirichlet 0 on the boundary
+        e = og.restrict(3, r, cs, scale)
+        exp = sent.copy()
+        exp[inner] = e[inner]
+        assert np.array_equal(ctx.download(fc, lvl - 1), exp)
+    ctx.close()
