@@ -204,6 +204,11 @@ int examg_finalize(examg_ctx *c) {
   if (c->int_out) cudaFree(c->int_out);
   if (c->int_host) cudaFreeHost(c->int_host);
   if (c->own_stream && c->stream) cudaStreamDestroy(c->stream);
+  if (c->copy_stream) cudaStreamDestroy(c->copy_stream);
+  for (int b = 0; b < 2; ++b) {
+    if (c->up_h2d[b]) cudaEventDestroy(c->up_h2d[b]);
+    if (c->up_d2d[b]) cudaEventDestroy(c->up_d2d[b]);
+  }
   delete c;
   return EXAMG_OK;
 }
@@ -430,6 +435,70 @@ int examg_field_upload_async(examg_ctx *c, int h, int slot, const double *host) 
 }
 int examg_field_download_async(examg_ctx *c, int h, int slot, double *host) {
   return copy_field(c, h, slot, host, false, true);
+}
+
+// Pipelined upload: _begin starts the host -> device copy of the NEXT input on the library's copy stream (the
+// host array must be pinned and stay untouched until _finish), _finish orders the device-side scatter into
+// the field with the kernels of the main stream.  Between the two calls the main stream can compute.
+int examg_field_upload_begin(examg_ctx *c, int h, int slot, const double *host) {
+  Field *f = get_field(c, h);
+  if (!f || !host) return set_error(EXAMG_EINVAL, "examg_field_upload_begin: bad field %d or null host pointer", h);
+  if (slot >= f->nslots) return set_error(EXAMG_EINVAL, "bad slot %d", slot);
+  if (c->up_pending) return set_error(EXAMG_ESTATE, "examg_field_upload_begin: an upload is already in flight");
+  const LevelGeom &g = *geom(c, f->level);
+  size_t dense = 1;
+  for (int d = 0; d < 3; ++d) dense *= (size_t)(g.n[d] - (f->loc == 1 && d < c->cfg.dim ? 1 : 0));
+  const size_t need = dense * f->ncomp;
+  if (!c->copy_stream) {
+    EXAMG_CUDA(cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking));
+    for (int b = 0; b < 2; ++b) {
+      EXAMG_CUDA(cudaEventCreateWithFlags(&c->up_h2d[b], cudaEventDisableTiming));
+      EXAMG_CUDA(cudaEventCreateWithFlags(&c->up_d2d[b], cudaEventDisableTiming));
+    }
+  }
+  const int b = c->up_turn;
+  if (c->up_doubles[b] < need) {
+    EXAMG_CUDA(cudaStreamSynchronize(c->stream));
+    EXAMG_CUDA(cudaStreamSynchronize(c->copy_stream));
+    if (c->up_stage[b]) dev_free(c, c->up_stage[b]);
+    c->up_stage[b] = dev_alloc(c, need * sizeof(double));
+    c->up_doubles[b] = c->up_stage[b] ? need : 0;
+    if (!c->up_stage[b]) return set_error(EXAMG_ENOMEM, "examg_field_upload_begin: staging array of %zu bytes", need * sizeof(double));
+  } else {
+    EXAMG_CUDA(cudaStreamWaitEvent(c->copy_stream, c->up_d2d[b], 0));  // the scatter that last read this array
+  }
+  EXAMG_CUDA(cudaMemcpyAsync(c->up_stage[b], host, need * sizeof(double), cudaMemcpyHostToDevice, c->copy_stream));
+  EXAMG_CUDA(cudaEventRecord(c->up_h2d[b], c->copy_stream));
+  c->up_field = h;
+  c->up_slot = slot;
+  c->up_pending = true;
+  return EXAMG_OK;
+}
+
+int examg_field_upload_finish(examg_ctx *c) {
+  if (!c || !c->up_pending) return set_error(EXAMG_ESTATE, "examg_field_upload_finish: no upload in flight");
+  Field *f = get_field(c, c->up_field);
+  if (!f) return set_error(EXAMG_EINVAL, "examg_field_upload_finish: field %d vanished", c->up_field);
+  const int b = c->up_turn;
+  const LevelGeom &g = *geom(c, f->level);
+  int e[3];
+  for (int d = 0; d < 3; ++d) e[d] = g.n[d] - (f->loc == 1 && d < c->cfg.dim ? 1 : 0);
+  const size_t dense = (size_t)e[0] * e[1] * e[2];
+  EXAMG_CUDA(cudaStreamWaitEvent(c->stream, c->up_h2d[b], 0));
+  for (int comp = 0; comp < f->ncomp; ++comp) {
+    cudaMemcpy3DParms p;
+    memset(&p, 0, sizeof(p));
+    p.srcPtr = make_cudaPitchedPtr(c->up_stage[b] + (size_t)comp * dense, sizeof(double) * e[0], e[0], e[1]);
+    p.dstPtr = make_cudaPitchedPtr(field_ptr(c, f, c->up_slot, comp), sizeof(double) * g.pitch, e[0], g.ay);
+    p.extent = make_cudaExtent(sizeof(double) * e[0], e[1], e[2]);
+    p.kind = cudaMemcpyDeviceToDevice;
+    EXAMG_CUDA(cudaMemcpy3DAsync(&p, c->stream));
+  }
+  EXAMG_CUDA(cudaEventRecord(c->up_d2d[b], c->stream));
+  f->halo_depth = 0;
+  c->up_turn ^= 1;
+  c->up_pending = false;
+  return EXAMG_OK;
 }
 
 int examg_field_fill(examg_ctx *c, int h, double value) {

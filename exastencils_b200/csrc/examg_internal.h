@@ -132,6 +132,14 @@ struct examg_ctx {
   std::vector<examg::Block> blocks;
   double *stage = nullptr;        // dense staging array of host <-> field transfers
   size_t stage_doubles = 0;
+  // pipelined upload (examg_field_upload_begin / _finish): the H2D copy runs on its own stream into one of two
+  // staging arrays while the main stream computes; only the device-side scatter is ordered with the kernels
+  cudaStream_t copy_stream = nullptr;
+  cudaEvent_t up_h2d[2] = {nullptr, nullptr}, up_d2d[2] = {nullptr, nullptr};
+  double *up_stage[2] = {nullptr, nullptr};
+  size_t up_doubles[2] = {0, 0};
+  int up_turn = 0, up_field = -1, up_slot = -1;
+  bool up_pending = false;
 };
 
 namespace examg {

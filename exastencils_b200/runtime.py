@@ -91,6 +91,8 @@ SIGNATURES = {
     "examg_field_download": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_void_p]),
     "examg_field_upload_async": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_void_p]),
     "examg_field_download_async": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_void_p]),
+    "examg_field_upload_begin": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_void_p]),
+    "examg_field_upload_finish": (C.c_int, [C.c_void_p]),
     "examg_field_fill": (C.c_int, [C.c_void_p, C.c_int, C.c_double]),
     "examg_stencil_const": (C.c_int, [C.c_void_p, C.c_int, C.c_int, _off_t, _dp]),
     "examg_stencil_field": (C.c_int, [C.c_void_p, C.c_int, C.c_int, _off_t, C.c_int]),
@@ -290,6 +292,12 @@ class Context:
 
     def download_async(self, f, host_ptr, slot=-1):
         check(self.L.examg_field_download_async(self.h, f, slot, C.c_void_p(host_ptr)))
+
+    def upload_begin(self, f, host_ptr, slot=-1):
+        check(self.L.examg_field_upload_begin(self.h, f, slot, C.c_void_p(host_ptr)))
+
+    def upload_finish(self):
+        check(self.L.examg_field_upload_finish(self.h))
 
     def fill(self, f, value):
         check(self.L.examg_field_fill(self.h, f, value))

@@ -125,6 +125,12 @@ int examg_field_download(examg_ctx *ctx, int field, int slot, double *host);
 /* same, asynchronous on the context stream (host must be pinned to overlap) */
 int examg_field_upload_async(examg_ctx *ctx, int field, int slot, const double *host);
 int examg_field_download_async(examg_ctx *ctx, int field, int slot, double *host);
+/* Pipelined upload for solve loops that take a new input every step: _begin starts the host -> device
+ * copy on the library's own copy stream (host must be pinned and stay valid until _finish returns),
+ * _finish orders the scatter into the field with the kernels of the context stream.  Kernels issued
+ * between the two calls overlap the PCIe transfer.  One upload in flight at a time.              */
+int examg_field_upload_begin(examg_ctx *ctx, int field, int slot, const double *host);
+int examg_field_upload_finish(examg_ctx *ctx);
 /* whole allocation (ghosts, padding, all slots) := value (initFieldsWithZero) */
 int examg_field_fill(examg_ctx *ctx, int field, double value);
 

@@ -342,3 +342,24 @@ def test_residual_restrict_fused(cells, lvl, order, oracle):
         exp[inner] = e[inner]
         assert np.array_equal(ctx.download(fc, lvl - 1), exp)
     ctx.close()
+
+
+def test_pipelined_upload():
+    """examg_field_upload_begin/_finish: the copy-stream transfer lands in the field exactly like examg_field_upload,
+    for node and cell fields, alternating between the two staging arrays."""
+    import torch
+    ctx = _ctx(3, (1, 1, 1), 5, 6)
+    f6, f5 = ctx.field_create("a", 6), ctx.field_create("b", 5, 1, 3)
+    for it in range(4):
+        lvl, f, nc = (6, f6, 1) if it % 2 == 0 else (5, f5, 3)
+        shape = ((nc,) if nc > 1 else ()) + ctx.shape(lvl)
+        host = torch.from_numpy(_rand(shape, 40 + it)).pin_memory()
+        ctx.upload_begin(f, host.data_ptr())
+        ctx.set(f6 if f is f5 else f5, 1.0)  # unrelated work on the main stream in between
+        ctx.upload_finish()
+        got = ctx.download(f, lvl, ncomp=nc)
+        assert np.array_equal(got, host.numpy())
+    from exastencils_b200 import runtime as rt
+    with pytest.raises(rt.ExaMGError):
+        ctx.upload_finish()
+    ctx.close()
