@@ -94,6 +94,28 @@ def main():
     set_benchmark_problem(jp)
     timeit("Jacobi V(%d,%d) cycle (%.1f B/pt)" % (args.nu, args.nu, cyc_bytes), lambda: jp.vcycle(), cyc_bytes)
     jp.close()
+    # 27-point stencil field (BASELINE config 3's operator shape) one level down: Jacobi sweep and residual read
+    # 27 coefficients + Solution + RHS and write one value = 240 B per point
+    import numpy as np
+    from exastencils_b200 import runtime as rt
+    L3 = L - 1
+    c3 = rt.Context(3, L3, L3, block_cells=(1, 1, 1))
+    c3.set_stream(stream.cuda_stream)
+    ctx = c3
+    n3 = c3.dims(L3)
+    pts3 = float(n3[0] - 2) * (n3[1] - 2) * (n3[2] - 2)
+    offs = [(dx, dy, dz) for dz in (-1, 0, 1) for dy in (-1, 0, 1) for dx in (-1, 0, 1)]
+    cf = c3.field_create("coef", L3, 1, 27)
+    rng = np.random.default_rng(1)
+    coef = rng.uniform(-1.0, 1.0, size=(27,) + c3.shape(L3))
+    coef[13] = 30.0 + np.abs(coef[13])
+    c3.upload(cf, coef)
+    del coef
+    A27 = c3.stencil_field(L3, offs, cf)
+    u3, f3, r3 = c3.field_create("u", L3, 2, 1), c3.field_create("f", L3), c3.field_create("r", L3)
+    timeit("27-pt stencil-field Jacobi (240 B/pt) @%d" % L3, lambda: c3.smooth_jacobi(A27, u3, f3, 0.8, 1), 240.0, npts=pts3)
+    timeit("27-pt stencil-field residual (240 B/pt)", lambda: c3.residual(A27, u3, f3, r3), 240.0, npts=pts3)
+    c3.close()
 
 
 if __name__ == "__main__":
