@@ -363,3 +363,38 @@ def test_pipelined_upload():
     with pytest.raises(rt.ExaMGError):
         ctx.upload_finish()
     ctx.close()
+
+
+@pytest.mark.parametrize("cells,lvl", [((1, 1, 1), 6), ((5, 3, 2), 5)])
+@pytest.mark.parametrize("npts,order", [(27, "lex"), (7, "testing")])
+def test_jacobi_stencil_field_sweeps(cells, lvl, npts, order, oracle):
+    """Stencil-field Jacobi, nu sweeps with `advance` (Testing/SISC/3D_VarCoeff.exa4 `Smoother`; BASELINE config 3's
+    27-point operator shape) against nu sweeps of the oracle, bit for bit."""
+    og = oracle
+    ctx = _ctx(3, cells, lvl, lvl)
+    shape = ctx.shape(lvl)
+    offs = _stencil_offsets(3, 27) if npts == 27 else _ORDERS[order]
+    centre = offs.index((0, 0, 0))
+    seed = 3000 * lvl + 10 * sum(cells) + npts
+    sf = _rand((npts,) + shape, seed)
+    sf[centre] = (8.0 if npts == 7 else 30.0) + np.abs(sf[centre])
+    sf = np.ascontiguousarray(sf)
+    cf = ctx.field_create("coef", lvl, 1, npts)
+    ctx.upload(cf, sf)
+    A = ctx.stencil_field(lvl, offs, cf)
+    st = og.Stencil.make(offs, np.zeros(npts))
+    fu = ctx.field_create("u", lvl, 2, 1)
+    ff = ctx.field_create("rhs", lvl, 1, 1)
+    u, rhs = _rand(shape, seed + 1), _rand(shape, seed + 2)
+    ctx.upload(ff, rhs)
+    for nu in (2, 3):
+        ctx.upload(fu, u, 0)
+        ctx.upload(fu, u, 1)
+        cur = ctx.field_active_slot(fu)
+        ctx.smooth_jacobi(A, fu, ff, 0.85, nu)
+        assert ctx.field_active_slot(fu) == (cur + nu) % 2
+        e = u
+        for _ in range(nu):
+            e = og.smooth_jacobi(st, 0.85, e, rhs, sf)
+        assert np.array_equal(ctx.download(fu, lvl), e), "nu = %d" % nu
+    ctx.close()
