@@ -191,6 +191,8 @@ examg_ctx *examg_init(const examg_config *cfg) {
   return c;
 }
 
+static int fold_timer(examg::Timer &t, bool wait);
+
 int examg_finalize(examg_ctx *c) {
   if (!c) return set_error(EXAMG_EINVAL, "examg_finalize: null context");
   cudaSetDevice(c->device);
@@ -204,6 +206,10 @@ int examg_finalize(examg_ctx *c) {
   if (c->int_out) cudaFree(c->int_out);
   if (c->int_host) cudaFreeHost(c->int_host);
   if (c->own_stream && c->stream) cudaStreamDestroy(c->stream);
+  for (auto &kv : c->timers) {
+    fold_timer(kv.second, false);
+    if (kv.second.start) cudaEventDestroy(kv.second.start);
+  }
   if (c->copy_stream) cudaStreamDestroy(c->copy_stream);
   for (int b = 0; b < 2; ++b) {
     if (c->up_h2d[b]) cudaEventDestroy(c->up_h2d[b]);
@@ -244,6 +250,74 @@ int examg_level_width(examg_ctx *c, int level, double h[3]) {
   const LevelGeom *g = geom(c, level);
   if (!g) return set_error(EXAMG_EINVAL, "examg_level_width: level %d", level);
   for (int d = 0; d < 3; ++d) h[d] = g->h[d];
+  return EXAMG_OK;
+}
+
+// ---- timers: startTimer("x") / stopTimer("x") / getTotalTime("x") / printAllTimers() ------------
+// (C/s/e/timing/ir/IR_GetTime.scala:33-63, IR_PrintAllTimers.scala:38-70).  The reference stops a host stopwatch
+// after a device synchronisation; here both ends are CUDA events on the context stream, so timing neither
+// synchronises nor measures host overhead.  Nested starts of one name count once, as in the reference.
+static int fold_timer(Timer &t, bool wait) {
+  size_t keep = 0;
+  for (size_t i = 0; i < t.done.size(); ++i) {
+    if (wait) cudaEventSynchronize(t.done[i].second);
+    float ms = 0.f;
+    if (cudaEventElapsedTime(&ms, t.done[i].first, t.done[i].second) == cudaSuccess) {
+      t.total_ms += ms;
+      cudaEventDestroy(t.done[i].first);
+      cudaEventDestroy(t.done[i].second);
+    } else {
+      cudaGetLastError();  // not finished yet
+      t.done[keep++] = t.done[i];
+    }
+  }
+  t.done.resize(keep);
+  return EXAMG_OK;
+}
+
+int examg_timer_start(examg_ctx *c, const char *name) {
+  if (!c || !name) return set_error(EXAMG_EINVAL, "examg_timer_start: null argument");
+  Timer &t = c->timers[name];
+  if (t.depth++ > 0) return EXAMG_OK;
+  EXAMG_CUDA(cudaEventCreate(&t.start));
+  EXAMG_CUDA(cudaEventRecord(t.start, c->stream));
+  return EXAMG_OK;
+}
+
+int examg_timer_stop(examg_ctx *c, const char *name) {
+  if (!c || !name) return set_error(EXAMG_EINVAL, "examg_timer_stop: null argument");
+  auto it = c->timers.find(name);
+  if (it == c->timers.end() || it->second.depth == 0) return set_error(EXAMG_ESTATE, "stopTimer(\"%s\") without startTimer", name);
+  Timer &t = it->second;
+  if (--t.depth > 0) return EXAMG_OK;
+  cudaEvent_t stop;
+  EXAMG_CUDA(cudaEventCreate(&stop));
+  EXAMG_CUDA(cudaEventRecord(stop, c->stream));
+  t.done.push_back({t.start, stop});
+  t.start = nullptr;
+  t.count++;
+  if (t.done.size() > 256) fold_timer(t, false);
+  return EXAMG_OK;
+}
+
+int examg_timer_total_ms(examg_ctx *c, const char *name, double *total_ms, long long *count) {
+  if (!c || !name || !total_ms) return set_error(EXAMG_EINVAL, "examg_timer_total_ms: null argument");
+  auto it = c->timers.find(name);
+  if (it == c->timers.end()) return set_error(EXAMG_EINVAL, "getTotalTime(\"%s\"): unknown timer", name);
+  fold_timer(it->second, true);
+  *total_ms = it->second.total_ms;
+  if (count) *count = it->second.count;
+  return EXAMG_OK;
+}
+
+int examg_timer_print_all(examg_ctx *c) {
+  if (!c) return set_error(EXAMG_EINVAL, "null context");
+  for (auto &kv : c->timers) {
+    fold_timer(kv.second, true);
+    // the reference prints "Mean mean total time for Timer <name>: <ms>" per timer (one rank: mean = total)
+    printf("Mean mean total time for Timer %s: %g\n", kv.first.c_str(), kv.second.total_ms);
+  }
+  fflush(stdout);
   return EXAMG_OK;
 }
 

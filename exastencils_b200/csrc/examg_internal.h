@@ -7,6 +7,7 @@
 #include <cstdarg>
 #include <cstdint>
 #include <cstdio>
+#include <map>
 #include <string>
 #include <vector>
 
@@ -95,6 +96,15 @@ struct System2 {
   double L[5];
 };
 
+// startTimer / stopTimer of the L4 programs, measured on the device (CUDA events on the context stream)
+struct Timer {
+  cudaEvent_t start = nullptr;                           // open measurement
+  std::vector<std::pair<cudaEvent_t, cudaEvent_t>> done; // closed, not yet folded into total_ms
+  double total_ms = 0.0;
+  long long count = 0;
+  int depth = 0;                                         // nested startTimer calls (reference: entries counter)
+};
+
 struct dd { double hi, lo; };
 
 // A cudaMalloc'd region.  Buffers of >= 1 MiB get a block of their own, smaller ones are carved
@@ -130,6 +140,7 @@ struct examg_ctx {
   int *int_host = nullptr;        // pinned
   struct examg_comm *comm = nullptr;
   std::vector<examg::Block> blocks;
+  std::map<std::string, examg::Timer> timers;
   double *stage = nullptr;        // dense staging array of host <-> field transfers
   size_t stage_doubles = 0;
   // pipelined upload (examg_field_upload_begin / _finish): the H2D copy runs on its own stream into one of two

@@ -140,6 +140,10 @@ SIGNATURES = {
     "examg_comm_blob_size": (C.c_int, [C.c_void_p]),
     "examg_comm_export": (C.c_int, [C.c_void_p, C.c_void_p]),
     "examg_comm_import": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int]),
+    "examg_timer_start": (C.c_int, [C.c_void_p, C.c_char_p]),
+    "examg_timer_stop": (C.c_int, [C.c_void_p, C.c_char_p]),
+    "examg_timer_total_ms": (C.c_int, [C.c_void_p, C.c_char_p, _dp, C.POINTER(C.c_longlong)]),
+    "examg_timer_print_all": (C.c_int, [C.c_void_p]),
     "examg_launch_count": (C.c_longlong, [C.c_void_p]),
     "examg_device_bytes": (C.c_longlong, [C.c_void_p]),
 }
@@ -225,6 +229,17 @@ class Context:
 
     def sync(self):
         check(self.L.examg_sync(self.h))
+
+    def timer_start(self, name):
+        check(self.L.examg_timer_start(self.h, name.encode()))
+
+    def timer_stop(self, name):
+        check(self.L.examg_timer_stop(self.h, name.encode()))
+
+    def timer_total_ms(self, name):
+        ms, n = C.c_double(), C.c_longlong()
+        check(self.L.examg_timer_total_ms(self.h, name.encode(), C.byref(ms), C.byref(n)))
+        return ms.value, n.value
 
     def launch_count(self):
         return self.L.examg_launch_count(self.h)

@@ -287,6 +287,14 @@ int examg_comm_export(examg_ctx *ctx, void *blob);
 int examg_comm_import(examg_ctx *ctx, const void *all_blobs, int world);
 
 /* ---- observability ------------------------------------------------------------ */
+/* startTimer("name") / stopTimer("name") / getTotalTime("name") / printAllTimers() of the L4 programs
+ * (C/s/e/timing/ir/IR_GetTime.scala:33-63, IR_PrintAllTimers.scala:38-70).  Measured with CUDA events on the
+ * context stream: asynchronous; examg_timer_total_ms waits for the measurements it reports.  Do not start or
+ * stop a timer inside a region that the library captures into a CUDA graph (examg_solver_vcycle).        */
+int examg_timer_start(examg_ctx *ctx, const char *name);
+int examg_timer_stop(examg_ctx *ctx, const char *name);
+int examg_timer_total_ms(examg_ctx *ctx, const char *name, double *total_ms, long long *count);
+int examg_timer_print_all(examg_ctx *ctx);
 /* kernels launched by this context since init (bench.py's gpu_launches) */
 long long examg_launch_count(examg_ctx *ctx);
 /* bytes of device memory held by this context */

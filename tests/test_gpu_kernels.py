@@ -398,3 +398,26 @@ def test_jacobi_stencil_field_sweeps(cells, lvl, npts, order, oracle):
             e = og.smooth_jacobi(st, 0.85, e, rhs, sf)
         assert np.array_equal(ctx.download(fu, lvl), e), "nu = %d" % nu
     ctx.close()
+
+
+def test_timers():
+    """startTimer / stopTimer / getTotalTime (C/s/e/timing/ir/IR_GetTime.scala): device-side, nested starts count once."""
+    from exastencils_b200 import runtime as rt
+    ctx = _ctx(3, (1, 1, 1), 6, 6)
+    f = ctx.field_create("a", 6)
+    ctx.timer_start("solve")
+    ctx.timer_start("solve")
+    for _ in range(10):
+        ctx.set(f, 1.0)
+    ctx.timer_stop("solve")
+    ctx.timer_stop("solve")
+    ctx.timer_start("solve")
+    ctx.set(f, 2.0)
+    ctx.timer_stop("solve")
+    ms, n = ctx.timer_total_ms("solve")
+    assert n == 2 and 0.0 < ms < 1000.0
+    with pytest.raises(rt.ExaMGError):
+        ctx.timer_stop("solve")
+    with pytest.raises(rt.ExaMGError):
+        ctx.timer_total_ms("nope")
+    ctx.close()
