@@ -322,6 +322,7 @@ k_rbw(const __grid_constant__ CUtensorMap tm_u, const __grid_constant__ CUtensor
 }  // namespace examg
 
 #include "examg_jac7.cuh"
+#include "examg_jacv.cuh"
 
 namespace examg {
 
@@ -585,6 +586,109 @@ int launch_jac_fused(examg_ctx *c, const Stencil &s, double omega, Field &fu, co
     case 1: return launch_jacw<1>(c, s, omega, fu, rhs);
     case 2: return launch_jacw<2>(c, s, omega, fu, rhs);
     default: return launch_jacw<3>(c, s, omega, fu, rhs);
+  }
+}
+
+// ---- stencil-field Jacobi: two sweeps per pass, coefficients read once (examg_jacv.cuh) ----------
+
+// 3D view of a field with `ncomp` components stacked in z (component k, plane z = plane k * az + z), box bw x bh x 1
+static int make_box_map(const LevelGeom &g, const double *base, int ncomp, int bw, int bh, CUtensorMap *tm) {
+  EncodeTiledFn fn = encode_fn();
+  if (!fn) return set_error(EXAMG_ECUDA, "cuTensorMapEncodeTiled entry point not available");
+  const cuuint64_t dims[3] = {(cuuint64_t)g.pitch, (cuuint64_t)g.ay, (cuuint64_t)g.az * ncomp};
+  const cuuint64_t strides[2] = {(cuuint64_t)g.pitch * 8, (cuuint64_t)g.plane * 8};
+  const cuuint32_t box[3] = {(cuuint32_t)bw, (cuuint32_t)bh, 1};
+  const cuuint32_t estr[3] = {1, 1, 1};
+  CUresult r = fn(tm, CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 3, const_cast<double *>(base), dims, strides, box, estr,
+                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, (CUtensorMapL2promotion)l2_promotion(),
+                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) return set_error(EXAMG_ECUDA, "cuTensorMapEncodeTiled (box %d x %d) failed (%d)", bw, bh, (int)r);
+  return EXAMG_OK;
+}
+
+// 27 lexicographic (dx fastest): 2; 7-point in declaration order 0 / 1: 0 / 1; anything else: -1
+static int jacv_shape(const Stencil &s) {
+  if (s.nst == 7) return stencil_order(s);
+  if (s.nst != 27) return -1;
+  for (int k = 0; k < 27; ++k)
+    if (s.off[k][0] != k % 3 - 1 || s.off[k][1] != (k / 3) % 3 - 1 || s.off[k][2] != k / 9 - 1) return -1;
+  return 2;
+}
+
+// EXAMG_JACV_FUSE: 0 = generic kernels only, 1 = 27-point (default), 2 = 27- and 7-point
+static int jacv_mode() {
+  static int v = -1;
+  if (v < 0) v = env_flag("EXAMG_JACV_FUSE", 1);
+  return v;
+}
+
+constexpr int JACV_MIN_N = 33;
+
+bool fused_jacv_usable(examg_ctx *c, const Stencil &s, const Field &fu) {
+  if (!fused_enabled() || jacv_mode() <= 0 || c->cfg.dim != 3 || s.coeff_field < 0 || fu.ncomp != 1 ||
+      fu.nslots != 2 || c->world != 1)
+    return false;
+  const int shape = jacv_shape(s);
+  if (shape < 0 || (shape < 2 && jacv_mode() < 2)) return false;
+  const LevelGeom &g = *geom(c, s.level);
+  return g.n[0] >= JACV_MIN_N && g.n[1] >= JACV_MIN_N && g.n[2] >= JACV_MIN_N;
+}
+
+template <int NST, int ORD>
+static int launch_jacv(examg_ctx *c, const Stencil &s, double omega, Field &fu, const double *rhs) {
+  static bool attr_set = false;
+  if (!attr_set) {
+    EXAMG_CUDA(cudaFuncSetAttribute(k_jacv2<NST, ORD>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)jacv_smem<NST>()));
+    attr_set = true;
+  }
+  const LevelGeom &g = *geom(c, s.level);
+  const Field &cf = c->fields[s.coeff_field];
+  const int nxt = (fu.cur + 1) % 2;
+  CUtensorMap tm_u, tm_c;
+  int rc = make_box_map(g, fu.slot[fu.cur], 1, VUW, VUH, &tm_u);
+  if (rc) return rc;
+  if ((rc = make_box_map(g, cf.slot[0], NST, VCW, VH, &tm_c))) return rc;
+  RbwArgs a;
+  for (int d = 0; d < 3; ++d) {
+    a.n[d] = g.n[d];
+    a.ulo[d] = g.lo[d];
+    a.uhi[d] = g.hi[d];
+    a.elo[d] = a.ehi[d] = 0;  // single block (fused_jacv_usable)
+  }
+  a.pitch = g.pitch;
+  a.plane = g.plane;
+  a.tiles_x = (g.n[0] + VIW - 1) / VIW;
+  const int tiles_y = (g.n[1] + VIH - 1) / VIH;
+  a.nzp = g.n[2];
+  a.tiles = a.tiles_x * tiles_y;
+  const long long units = (long long)a.tiles * a.nzp;
+  a.par = g.az;  // planes per component of the stacked view
+  a.pf = 0;
+  for (int k = 0; k < 7; ++k) a.coef[k] = 0.0;
+  a.w = omega;  // the diagonal varies: omega / diag is formed per point
+  int dev = 0, nsm = 148;
+  cudaGetDevice(&dev);
+  cudaDeviceGetAttribute(&nsm, cudaDevAttrMultiProcessorCount, dev);
+  long long grid = nsm;
+  const long long min_units = 12;  // at least this many planes per CTA (2 are restart overhead)
+  if (grid > units / min_units) grid = units / min_units;
+  if (grid < 1) grid = 1;
+  k_jacv2<NST, ORD><<<(int)grid, VNT, jacv_smem<NST>(), c->stream>>>(tm_u, tm_c, a, rhs, fu.slot[nxt] + g.origin);
+  EXAMG_LAUNCH_CHECK(c);
+  // two `advance`s: the active slot stays, the result sits in the other buffer -> exchange the two buffers
+  double *t = fu.slot[fu.cur];
+  fu.slot[fu.cur] = fu.slot[nxt];
+  fu.slot[nxt] = t;
+  return EXAMG_OK;
+}
+
+// exactly two Jacobi sweeps with stencil-field coefficients in one launch
+int launch_jacv_fused(examg_ctx *c, const Stencil &s, double omega, Field &fu, const double *rhs) {
+  switch (jacv_shape(s)) {
+    case 2: return launch_jacv<27, 0>(c, s, omega, fu, rhs);
+    case 0: return launch_jacv<7, 0>(c, s, omega, fu, rhs);
+    case 1: return launch_jacv<7, 1>(c, s, omega, fu, rhs);
+    default: return set_error(EXAMG_EUNSUP, "launch_jacv_fused: stencil shape not covered");
   }
 }
 

@@ -20,6 +20,8 @@ int rb_fused_plan(int nsweeps);
 bool fused_jac_usable(examg_ctx *c, const Stencil &s, const Field &fu);
 int launch_jac_fused(examg_ctx *c, const Stencil &s, double omega, Field &fu, const double *rhs, int nsweeps, int *done);
 int jac_fused_plan(int nsweeps);
+bool fused_jacv_usable(examg_ctx *c, const Stencil &s, const Field &fu);
+int launch_jacv_fused(examg_ctx *c, const Stencil &s, double omega, Field &fu, const double *rhs);
 bool residual_restrict_usable(examg_ctx *c, const Stencil &s);
 int launch_residual_restrict(examg_ctx *c, const Stencil &s, const double *u, const double *rhs, double *rhsc, double scale);
 
@@ -141,7 +143,15 @@ int examg_smooth_jacobi(examg_ctx *c, int A, int u, int rhs, double omega, int n
     }
     return EXAMG_OK;
   }
-  for (int it = 0; it < nsweeps; ++it) {
+  int it0 = 0;
+  if (fused_jacv_usable(c, *s, *fu)) {  // stencil-field coefficients: pairs of sweeps read them once (examg_jacv.cuh)
+    for (; it0 + 2 <= nsweeps; it0 += 2) {
+      int rc = launch_jacv_fused(c, *s, omega, *fu, field_ptr(c, fr, -1));
+      if (rc) return rc;
+      fu->halo_depth = 0;
+    }
+  }
+  for (int it = it0; it < nsweeps; ++it) {
     int rc = do_exchange(c, *fu, fu->cur);
     if (rc) return rc;
     const int nxt = (fu->cur + 1) % fu->nslots;

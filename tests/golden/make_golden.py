@@ -23,6 +23,10 @@ FILES = {
     "SISC_2D_VarCoeff": "Testing/SISC/2D_VarCoeff.results",
     "Opts_seq": "Testing/Opts/seq.results",
     "Application_OpticalFlow2D": "Testing/Application/OpticalFlow2D.results",
+    "BC_2D_Polynomial": "Testing/BC/2D_Polynomial.results",
+    "BC_2D_Trigonometric": "Testing/BC/2D_Trigonometric.results",
+    "BC_3D_Polynomial": "Testing/BC/3D_Polynomial.results",
+    "BC_3D_Trigonometric": "Testing/BC/3D_Trigonometric.results",
 }
 
 if __name__ == "__main__":

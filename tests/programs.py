@@ -148,6 +148,21 @@ SISC_2D_VAR = Program(
     rhs=_rhs2, bc=lambda X, Y, Z: 1.0 - np.exp((-1.0 * KAPPA) * _b2(X, Y, Z)),
     exact=lambda X, Y, Z: 1.0 - np.exp((-1.0 * KAPPA) * _b2(X, Y, Z)), prints="err")
 
+# Testing/BC/{2D,3D}_{Polynomial,Trigonometric}.{exa4,knowledge}: the Smoothers/Jac cycle (unscaled stencil,
+# omega = 0.8 Jacobi, V(3,3), CG) on 2^d blocks x 2^d fragments => F=4, levels 0-6, with a non-trivial Dirichlet
+# expression on the finest level; prints the initial residual, then NormError_0 (max |u - exact|) per cycle.
+_BC_CFG3 = dict(dim=3, F=(4, 4, 4), min_level=0, max_level=6, op="unscaled", order="testing", smoother="jacobi",
+                omega=0.8, nu_pre=3, nu_post=3, restrict_scale=4.0, cg_max_it=512, cg_rel_tol=1e-3)
+_BC_CFG2 = dict(_BC_CFG3, dim=2, F=(4, 4))
+_poly2 = lambda X, Y, Z: (X * X) - (Y * Y) + 0.0 * Z
+_trig2 = lambda X, Y, Z: np.sin(PI * X) * np.sinh(PI * Y) + 0.0 * Z
+_trig3 = lambda X, Y, Z: (np.sin(PI * X) * np.sin(PI * Y)) * np.sinh((math.sqrt(2.0) * PI) * Z)
+BC_2D_POLY = Program("BC_2D_Polynomial", "BC_2D_Polynomial", _BC_CFG2, bc=_poly2, exact=_poly2, prints="err")
+BC_2D_TRIG = Program("BC_2D_Trigonometric", "BC_2D_Trigonometric", _BC_CFG2, bc=_trig2, exact=_trig2, prints="err")
+BC_3D_POLY = Program("BC_3D_Polynomial", "BC_3D_Polynomial", _BC_CFG3, bc=_quad_bc, exact=_quad_bc, prints="err")
+BC_3D_TRIG = Program("BC_3D_Trigonometric", "BC_3D_Trigonometric", _BC_CFG3, bc=_trig3, exact=_trig3, prints="err")
+BC_PROGRAMS = [BC_2D_POLY, BC_2D_TRIG, BC_3D_POLY, BC_3D_TRIG]
+
 ALL = [POISSON_2D, SMOOTHERS_RBGS, SMOOTHERS_JAC, SISC_3D_CONST, SISC_3D_VAR, SISC_2D_CONST, SISC_2D_VAR]
 
 

@@ -41,7 +41,8 @@ def _setup_pair(prog, mode, **override):
 
 @pytest.mark.parametrize("mode", ["library", "calls"])
 @pytest.mark.parametrize("prog", [programs.POISSON_2D, programs.SISC_2D_CONST, programs.SISC_2D_VAR,
-                                  programs.SMOOTHERS_RBGS, programs.SMOOTHERS_JAC], ids=lambda p: p.name)
+                                  programs.SMOOTHERS_RBGS, programs.SMOOTHERS_JAC, programs.BC_2D_POLY,
+                                  programs.BC_2D_TRIG], ids=lambda p: p.name)
 def test_golden_stdout(prog, mode, oracle):
     """Same printed history as the reference's .results file."""
     if mode == "calls" and prog.dim == 3:
@@ -59,9 +60,11 @@ def test_golden_stdout(prog, mode, oracle):
     assert out == prog.expected()
 
 
-@pytest.mark.parametrize("prog", [programs.SISC_3D_CONST, programs.SISC_3D_VAR], ids=lambda p: p.name)
+@pytest.mark.parametrize("prog", [programs.SISC_3D_CONST, programs.SISC_3D_VAR, programs.BC_3D_POLY,
+                                  programs.BC_3D_TRIG], ids=lambda p: p.name)
 def test_golden_stdout_3d_sisc(prog, oracle):
-    """256^3-cell SISC programs (the reference's own CUDA target is tested on these)."""
+    """256^3-cell programs: Testing/SISC (the reference's own CUDA target is tested on these) and Testing/BC
+    (polynomial and sin*sin*sinh Dirichlet data)."""
     gpu = make_gpu_solver(prog.cfg, "library")
     prog.setup(gpu)
     if prog.cfg["op"] == "varcoeff":
