@@ -88,6 +88,68 @@ class ClockSampler:
                 "samples": len(sm)}
 
 
+KAPPA = 10.0  # getCoefficient of Testing/SISC/3D_VarCoeff.exa4
+
+# --workload: poisson7 = BASELINE configs[1] (the bench contract), varcoef27 = configs[2] (27-point stencil field,
+# damped Jacobi with pairs of sweeps fused into one pass over the coefficients; 1 GPU)
+WORKLOADS = {
+    "poisson7": dict(op="scaled", order="bench", smoother="rbgs", omega=OMEGA, kappa=0.0, bytes_sweep=24.0,
+                     bytes_residual=24.0),
+    "varcoef27": dict(op="varcoeff27", order="testing", smoother="jacobi", omega=0.85, kappa=KAPPA,
+                      bytes_sweep=240.0, bytes_residual=240.0),
+}
+
+
+def _bump(rt, op):  # X - X * X
+    return [(op, 0), (op, 0), (op, 0), (rt.OP_MUL, 0), (rt.OP_SUB, 0)]
+
+
+def set_varcoef_problem(prog):
+    """Testing/SISC/3D_VarCoeff.exa4 on the 27-point operator: RHS = 2 kappa ((x-x^2)(y-y^2) + (x-x^2)(z-z^2) +
+    (y-y^2)(z-z^2)), Dirichlet data 1 - exp(-kappa (x-x^2)(y-y^2)(z-z^2)), Solution = 0 inside; all on the device."""
+    from exastencils_b200 import runtime as rt
+    ctx, lvl = prog.ctx, prog.max_level
+    bx, by, bz = _bump(rt, rt.OP_X), _bump(rt, rt.OP_Y), _bump(rt, rt.OP_Z)
+    mul, add = [(rt.OP_MUL, 0)], [(rt.OP_ADD, 0)]
+    rhs = [(rt.OP_CONST, 2.0 * KAPPA)] + bx + by + mul + bx + bz + mul + add + by + bz + mul + add + mul
+    ctx.field_eval(prog.f_rhs[lvl], rhs)
+    bc = ([(rt.OP_CONST, 1.0), (rt.OP_CONST, -1.0 * KAPPA)] + bx + by + mul + bz + mul + mul +
+          [(rt.OP_EXP, 0), (rt.OP_SUB, 0)])
+    f = prog.f_solution[lvl]
+    ctx.field_set_bc_expr(f, bc)
+    ctx.fill(f, 0.0)
+    ctx.apply_bc(f)
+
+
+def set_problem(prog, workload):
+    if workload == "varcoef27":
+        set_varcoef_problem(prog)
+    else:
+        set_benchmark_problem(prog)
+
+
+def _oracle_solver(og, workload, level):
+    w = WORKLOADS[workload]
+    if workload == "varcoef27":
+        s = og.Solver(3, (1, 1, 1), MIN_LEVEL, level, op=og.OP_VARCOEFF27, order=og.ORDER_TESTING, kappa=KAPPA,
+                      smoother=og.SMOOTH_JACOBI, omega=w["omega"], nu_pre=NU_PRE, nu_post=NU_POST, cg_max_it=128,
+                      cg_rel_tol=1e-3)
+        import numpy as np
+        x, y, z = s.node_positions(level)
+        X, Y, Z = x[None, None, :], y[None, :, None], z[:, None, None]
+        bx, by, bz = X - X * X, Y - Y * Y, Z - Z * Z
+        s.rhs(level)[...] = (2.0 * KAPPA) * (((bx * by) + (bx * bz)) + (by * bz))
+        u = s.solution(level)
+        u[...] = 1.0 - np.exp((-1.0 * KAPPA) * ((bx * by) * bz))
+        u[1:-1, 1:-1, 1:-1] = 0.0
+        s.sync_slots()
+        return s
+    s = og.Solver(3, (1, 1, 1), MIN_LEVEL, level, op=og.OP_LAPLACE_SCALED, order=og.ORDER_BENCH,
+                  smoother=og.SMOOTH_RBGS, omega=OMEGA, nu_pre=NU_PRE, nu_post=NU_POST, cg_max_it=128, cg_rel_tol=1e-3)
+    _oracle_problem(s, level)
+    return s
+
+
 def set_benchmark_problem(prog):
     """Solution@finest = Dirichlet data on the boundary, 0 inside; RHS = 0 (Benchmark/Poisson3D)."""
     from exastencils_b200 import runtime as rt
@@ -111,9 +173,7 @@ def run_reference(args):
     og.build()
     level = args.cpu_level
     ncores = os.cpu_count() or 1
-    s = og.Solver(3, (1, 1, 1), MIN_LEVEL, level, op=og.OP_LAPLACE_SCALED, order=og.ORDER_BENCH,
-                  smoother=og.SMOOTH_RBGS, omega=OMEGA, nu_pre=NU_PRE, nu_post=NU_POST, cg_max_it=128, cg_rel_tol=1e-3)
-    _oracle_problem(s, level)
+    s = _oracle_solver(og, args.workload, level)
     for _ in range(args.warmup):
         s.vcycle()
         s.update_residual_norm()
@@ -130,7 +190,7 @@ def run_reference(args):
     line = {"impl": "reference", "metric": "3D Poisson V-cycle DoF-cycles/s", "value": val, "unit": "DoF-cycles/s",
             "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-            "config": workload_config(args.gpus, args.level),
+            "config": workload_config(args.gpus, args.level, args.workload),
             "cpu_baseline": {"value": val, "unit": "DoF-cycles/s", "cores": ncores, "kind": "port", "sample": sample},
             "e2e": {"value": val, "unit": "DoF-cycles/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
@@ -146,7 +206,14 @@ def _oracle_problem(s, level):
     u[1:-1, 1:-1, 1:-1] = 0.0
 
 
-def workload_config(n_gpus, level):
+def workload_config(n_gpus, level, workload="poisson7"):
+    if workload == "varcoef27":
+        return {"workload": "3D 27-point variable-coefficient Poisson (stencil field, coefficient exp(10 (x-x^2)(y-y^2)"
+                            "(z-z^2))), V(2,2) damped Jacobi omega=0.85 with pairs of sweeps fused into one pass, CG "
+                            "coarse solve, %d^3 cells, levels %d..%d" % (1 << level, MIN_LEVEL, level),
+                "blocks": [1, 1, 1], "cells_per_gpu": (1 << level) ** 3, "smoother": "jacobi", "nu_pre": NU_PRE,
+                "nu_post": NU_POST, "l2_policy": "inputs larger than L2 (27 coefficient components x %.2f GB on the "
+                "finest level)" % (8.0 * ((1 << level) + 1) ** 3 / 1e9)}
     return {"workload": "Benchmark/Poisson3D 7-point constant-coefficient, V(2,2) RBGS omega=0.8, CG coarse solve, "
                         "%d^3 cells per GPU, levels %d..%d" % (1 << level, MIN_LEVEL, level),
             "blocks": list(BLOCKS[n_gpus]), "cells_per_gpu": (1 << level) ** 3, "smoother": "rbgs", "nu_pre": NU_PRE,
@@ -160,9 +227,7 @@ def cpu_baseline(args):
     og.build()
     level = args.cpu_level
     ncores = os.cpu_count() or 1
-    s = og.Solver(3, (1, 1, 1), MIN_LEVEL, level, op=og.OP_LAPLACE_SCALED, order=og.ORDER_BENCH,
-                  smoother=og.SMOOTH_RBGS, omega=OMEGA, nu_pre=NU_PRE, nu_post=NU_POST, cg_max_it=128, cg_rel_tol=1e-3)
-    _oracle_problem(s, level)
+    s = _oracle_solver(og, args.workload, level)
     s.vcycle()
     s.update_residual_norm()
     reps = args.cpu_cycles
@@ -184,13 +249,22 @@ def main():
     ap.add_argument("--steps", type=int, default=30)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="examg", choices=["examg", "reference"])
-    ap.add_argument("--level", type=int, default=9, help="finest level per GPU (9 = 512^3 cells)")
-    ap.add_argument("--cpu-level", type=int, default=9)
+    ap.add_argument("--workload", default="poisson7", choices=sorted(WORKLOADS))
+    ap.add_argument("--level", type=int, default=None, help="finest level per GPU (9 = 512^3 cells; default 9, "
+                    "varcoef27: 8)")
+    ap.add_argument("--cpu-level", type=int, default=None)
     ap.add_argument("--cpu-cycles", type=int, default=3)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
     if args.gpus not in BLOCKS:
         raise SystemExit("--gpus must be 1, 2, 4 or 8")
+    wl = WORKLOADS[args.workload]
+    if args.level is None:
+        args.level = 8 if args.workload == "varcoef27" else 9
+    if args.cpu_level is None:
+        args.cpu_level = min(args.level, 8) if args.workload == "varcoef27" else 9
+    if args.workload == "varcoef27" and args.gpus != 1:
+        raise SystemExit("--workload varcoef27 runs on one GPU (stencil fields are single-block so far)")
     if args.impl == "reference":
         return run_reference(args)
 
@@ -210,14 +284,14 @@ def main():
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     stream = torch.cuda.Stream()
     level = args.level
-    prog = MultigridProgram(3, (1, 1, 1), MIN_LEVEL, level, op="scaled", order="bench", smoother="rbgs", omega=OMEGA,
-                            nu_pre=NU_PRE, nu_post=NU_POST, cg_max_it=128, cg_rel_tol=1e-3,
+    prog = MultigridProgram(3, (1, 1, 1), MIN_LEVEL, level, op=wl["op"], order=wl["order"], smoother=wl["smoother"],
+                            omega=wl["omega"], kappa=wl["kappa"], nu_pre=NU_PRE, nu_post=NU_POST, cg_max_it=128, cg_rel_tol=1e-3,
                             num_blocks=BLOCKS[world], rank=rank, device=local_rank, stream=stream.cuda_stream,
                             domain_hi=tuple(float(b) for b in BLOCKS[world]))
     if world > 1:
         from exastencils_b200.distributed import wire_peers
         wire_peers(prog.ctx, dist, device="cuda:%d" % local_rank)
-    set_benchmark_problem(prog)
+    set_problem(prog, args.workload)
     ctx = prog.ctx
     nb = BLOCKS[world]
     dof = 1.0
@@ -257,7 +331,9 @@ def main():
     shape = ctx.shape(level)
     rhs_host = torch.zeros(shape, dtype=torch.float64).pin_memory()
     h2d = rhs_host.numel() * 8
-    set_benchmark_problem(prog)
+    set_problem(prog, args.workload)
+    if args.workload == "varcoef27":  # the step's input: the RHS the device just assembled, staged in pinned memory
+        rhs_host.copy_(torch.from_numpy(ctx.download(prog.f_rhs[level], level)))
     with torch.cuda.stream(stream):
         # software pipeline through the ABI's upload_begin/_finish: the PCIe transfer of step i+1's input runs on
         # the library's copy stream while step i computes; every step still moves its own 1.08 GB
@@ -293,15 +369,19 @@ def main():
     n_loc = ctx.dims(level)
     pts = float(n_loc[0] - 2) * (n_loc[1] - 2) * (n_loc[2] - 2) if world == 1 else float(n_loc[0]) * n_loc[1] * n_loc[2]
     reps = max(5, args.steps)
+    if args.workload == "varcoef27":
+        smooth = lambda: ctx.smooth_jacobi(A, u, f, wl["omega"], NU_PRE)
+    else:
+        smooth = lambda: ctx.smooth_rbgs(A, u, f, OMEGA, NU_PRE)
     with torch.cuda.stream(stream):
         for _ in range(3):
-            ctx.smooth_rbgs(A, u, f, OMEGA, NU_PRE)
+            smooth()
         torch.cuda.synchronize()
         l1 = ctx.launch_count()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record(stream)
         for _ in range(reps):
-            ctx.smooth_rbgs(A, u, f, OMEGA, NU_PRE)
+            smooth()
         e1.record(stream)
         torch.cuda.synchronize()
         ms_k = e0.elapsed_time(e1) / reps
@@ -312,18 +392,20 @@ def main():
         e1.record(stream)
         torch.cuda.synchronize()
         ms_r = e0.elapsed_time(e1) / reps
-    alg_bytes = BYTES_RBGS_SWEEP * NU_PRE * pts
+    alg_bytes = wl["bytes_sweep"] * NU_PRE * pts
     achieved = alg_bytes / (ms_k * 1e-3) / 1e9
-    roofline = {"bound": "hbm", "kernel": "RBGS smoother, %d sweeps on the finest level (%d launch(es))" % (NU_PRE, k_launches),
+    kname = "damped Jacobi on the 27-point stencil field" if args.workload == "varcoef27" else "RBGS smoother"
+    roofline = {"bound": "hbm", "kernel": "%s, %d sweeps on the finest level (%d launch(es))" % (kname, NU_PRE, k_launches),
                 "achieved": achieved, "peak": peak, "peak_kind": peak_kind + " (MEASURED_PEAKS.json hbm_gbs, burst)",
                 "unit": "GB/s", "frac": achieved / peak, "traffic": None,
                 "algorithmic_bytes_per_launch_group": alg_bytes, "ms": ms_k,
-                "residual": {"achieved": BYTES_RESIDUAL * pts / (ms_r * 1e-3) / 1e9, "ms": ms_r,
-                             "frac": BYTES_RESIDUAL * pts / (ms_r * 1e-3) / 1e9 / peak}}
+                "residual": {"achieved": wl["bytes_residual"] * pts / (ms_r * 1e-3) / 1e9, "ms": ms_r,
+                             "frac": wl["bytes_residual"] * pts / (ms_r * 1e-3) / 1e9 / peak}}
     traffic_file = os.path.join(ROOT, "profiles", "traffic.json")
     if os.path.exists(traffic_file):
         with open(traffic_file) as fh:
-            roofline["traffic"] = json.load(fh).get("rbgs_bytes_per_launch_group")
+            roofline["traffic"] = json.load(fh).get("jacv27_bytes_per_launch_group" if args.workload == "varcoef27"
+                                                    else "rbgs_bytes_per_launch_group")
 
     cb = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
@@ -333,7 +415,7 @@ def main():
         line = {"metric": "3D Poisson V-cycle DoF-cycles/s", "value": value, "unit": "DoF-cycles/s",
                 "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps,
                 "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
-                "data": "synthetic", "config": workload_config(world, level), "e2e": e2e,
+                "data": "synthetic", "config": workload_config(world, level, args.workload), "e2e": e2e,
                 "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline, "cpu_baseline": cb,
                 "final_residual": res, "device_bytes": ctx.device_bytes()}
         print(json.dumps(line))

@@ -412,28 +412,51 @@ int examg_field_set_bc(examg_ctx *c, int h, int kind, double value) {
   return EXAMG_OK;
 }
 
+// validates a postfix program on the host so the device never has to; ncomp > 0 allows EXAMG_OP_COMP
+static int check_program(const char *who, const examg_bc_op *prog, int n, int ncomp) {
+  if (!prog || n < 1 || n > 64) return set_error(EXAMG_EINVAL, "%s: 1..64 ops", who);
+  int depth = 0;
+  for (int i = 0; i < n; ++i) {
+    switch (prog[i].op) {
+      case EXAMG_OP_COMP:
+        if (ncomp <= 0 || prog[i].value < 0 || prog[i].value >= ncomp || prog[i].value != (int)prog[i].value)
+          return set_error(EXAMG_EINVAL, "%s: op %d reads component %g of %d", who, i, prog[i].value, ncomp);
+        ++depth; break;
+      case EXAMG_OP_CONST: case EXAMG_OP_X: case EXAMG_OP_Y: case EXAMG_OP_Z: ++depth; break;
+      case EXAMG_OP_ADD: case EXAMG_OP_SUB: case EXAMG_OP_MUL: case EXAMG_OP_DIV:
+        if (depth < 2) return set_error(EXAMG_EINVAL, "%s: stack underflow at op %d", who, i);
+        --depth; break;
+      case EXAMG_OP_NEG: case EXAMG_OP_EXP: case EXAMG_OP_SIN: case EXAMG_OP_COS: case EXAMG_OP_SINH:
+      case EXAMG_OP_SQRT:
+        if (depth < 1) return set_error(EXAMG_EINVAL, "%s: stack underflow at op %d", who, i);
+        break;
+      default: return set_error(EXAMG_EINVAL, "%s: unknown op %d", who, prog[i].op);
+    }
+    if (depth > 16) return set_error(EXAMG_EINVAL, "%s: stack deeper than 16", who);
+  }
+  if (depth != 1) return set_error(EXAMG_EINVAL, "%s: program leaves %d values", who, depth);
+  return EXAMG_OK;
+}
+
 int examg_field_set_bc_expr(examg_ctx *c, int h, const examg_bc_op *prog, int n) {
   Field *f = get_field(c, h);
   if (!f) return set_error(EXAMG_EINVAL, "bad field %d", h);
-  if (!prog || n < 1 || n > 64) return set_error(EXAMG_EINVAL, "examg_field_set_bc_expr: 1..64 ops");
-  int depth = 0;  // validate the postfix program on the host so the device never has to
-  for (int i = 0; i < n; ++i) {
-    switch (prog[i].op) {
-      case EXAMG_OP_CONST: case EXAMG_OP_X: case EXAMG_OP_Y: case EXAMG_OP_Z: ++depth; break;
-      case EXAMG_OP_ADD: case EXAMG_OP_SUB: case EXAMG_OP_MUL: case EXAMG_OP_DIV:
-        if (depth < 2) return set_error(EXAMG_EINVAL, "bc program: stack underflow at op %d", i);
-        --depth; break;
-      case EXAMG_OP_NEG:
-        if (depth < 1) return set_error(EXAMG_EINVAL, "bc program: stack underflow at op %d", i);
-        break;
-      default: return set_error(EXAMG_EINVAL, "bc program: unknown op %d", prog[i].op);
-    }
-    if (depth > 16) return set_error(EXAMG_EINVAL, "bc program: stack deeper than 16");
-  }
-  if (depth != 1) return set_error(EXAMG_EINVAL, "bc program leaves %d values", depth);
+  int rc = check_program("bc program", prog, n, 0);
+  if (rc) return rc;
   f->bc_kind = EXAMG_BC_DIRICHLET_EXPR;
   f->bc_prog.assign(prog, prog + n);
   return EXAMG_OK;
+}
+
+int examg_field_eval(examg_ctx *c, int h, int slot, int comp, const examg_bc_op *prog, int n) {
+  Field *f = get_field(c, h);
+  if (!f) return set_error(EXAMG_EINVAL, "bad field %d", h);
+  if (slot >= f->nslots) return set_error(EXAMG_EINVAL, "examg_field_eval: slot %d of %d", slot, f->nslots);
+  if (comp < 0 || comp >= f->ncomp) return set_error(EXAMG_EINVAL, "examg_field_eval: component %d of %d", comp, f->ncomp);
+  if (f->loc != 0) return set_error(EXAMG_EUNSUP, "examg_field_eval: node-localised fields only");
+  int rc = check_program("examg_field_eval", prog, n, f->ncomp);
+  if (rc) return rc;
+  return launch_field_eval(c, *f, slot, comp, prog, n);
 }
 
 int examg_apply_bc(examg_ctx *c, int h, int slot) {

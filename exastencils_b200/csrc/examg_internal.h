@@ -213,6 +213,7 @@ int launch_maxdiff(examg_ctx *c, int level, const double *a, const double *b, in
 enum { STREAM_SET = 0, STREAM_COPY = 1, STREAM_AXPY = 2, STREAM_XPAY = 3 };
 int launch_stream_op(examg_ctx *c, int level, int op, double alpha, const double *x, double *y);
 int launch_bc(examg_ctx *c, const Field &f, int slot);
+int launch_field_eval(examg_ctx *c, const Field &f, int slot, int comp, const examg_bc_op *prog, int n);
 int launch_bc_cell(examg_ctx *c, const Field &f, int slot);  // Neumann ghost cells (examg_optflow.cu)
 int launch_cg(examg_ctx *c, const Stencil &s, double *u, const double *rhs, double *res, double *p,
               double *ap, int max_it, double rel_tol);

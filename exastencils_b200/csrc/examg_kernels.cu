@@ -154,12 +154,20 @@ struct BcProg {
   double val[64];
 };
 
-__device__ __forceinline__ double bc_eval(const BcProg &pr, double x, double y, double z) {
+// comp0 / vol: component 0 of the field being written at this node and the component stride (EXAMG_OP_COMP)
+__device__ __forceinline__ double bc_eval(const BcProg &pr, double x, double y, double z,
+                                          const double *comp0 = nullptr, long long vol = 0) {
   double stk[16];
   int sp = 0;
   for (int q = 0; q < pr.n; ++q) {
     switch (pr.op[q]) {
       case EXAMG_OP_CONST: stk[sp++] = pr.val[q]; break;
+      case EXAMG_OP_COMP: stk[sp++] = comp0[(long long)pr.val[q] * vol]; break;
+      case EXAMG_OP_EXP: stk[sp - 1] = exp(stk[sp - 1]); break;
+      case EXAMG_OP_SIN: stk[sp - 1] = sin(stk[sp - 1]); break;
+      case EXAMG_OP_COS: stk[sp - 1] = cos(stk[sp - 1]); break;
+      case EXAMG_OP_SINH: stk[sp - 1] = sinh(stk[sp - 1]); break;
+      case EXAMG_OP_SQRT: stk[sp - 1] = sqrt(stk[sp - 1]); break;
       case EXAMG_OP_X: stk[sp++] = x; break;
       case EXAMG_OP_Y: stk[sp++] = y; break;
       case EXAMG_OP_Z: stk[sp++] = z; break;
@@ -209,6 +217,21 @@ k_dirichlet(const BcArgs a, const __grid_constant__ BcProg pr, int use_prog, dou
       v = bc_eval(pr, x, y, z);
     }
     f[idx[0] + (long long)a.pitch * idx[1] + a.plane * idx[2]] = v;
+  }
+}
+
+// loop over F { F[comp] = <expr>(vf_nodePosition) } on the local nodes and one ghost layer
+__global__ void __launch_bounds__(256)
+k_field_eval(const BcArgs a, const __grid_constant__ BcProg pr, double *f0, long long vol, int comp) {
+  const int ex = a.n[0] + 2, ey = a.n[1] + 2, ez = a.dim == 3 ? a.n[2] + 2 : 1;
+  const long long total = (long long)ex * ey * ez;
+  for (long long t = blockIdx.x * (long long)blockDim.x + threadIdx.x; t < total; t += (long long)gridDim.x * blockDim.x) {
+    const int i = (int)(t % ex) - 1, j = (int)((t / ex) % ey) - 1, k = a.dim == 3 ? (int)(t / ((long long)ex * ey)) - 1 : 0;
+    const double x = (double)(a.goff[0] + i) * a.h[0] + a.x0[0];
+    const double y = (double)(a.goff[1] + j) * a.h[1] + a.x0[1];
+    const double z = a.dim == 3 ? (double)(a.goff[2] + k) * a.h[2] + a.x0[2] : 0.0;
+    const long long p = i + (long long)a.pitch * j + a.plane * k;
+    f0[(long long)comp * vol + p] = bc_eval(pr, x, y, z, f0 + p, vol);
   }
 }
 
@@ -331,6 +354,30 @@ int launch_stream_op(examg_ctx *c, int level, int op, double alpha, const double
     case STREAM_AXPY: k_stream<STREAM_AXPY><<<sh.grid, sh.block, 0, c->stream>>>(ga, alpha, x, y, sh.kz); break;
     default: k_stream<STREAM_XPAY><<<sh.grid, sh.block, 0, c->stream>>>(ga, alpha, x, y, sh.kz); break;
   }
+  EXAMG_LAUNCH_CHECK(c);
+  return EXAMG_OK;
+}
+
+int launch_field_eval(examg_ctx *c, const Field &f, int slot, int comp, const examg_bc_op *prog, int n) {
+  const LevelGeom &g = *geom(c, f.level);
+  BcArgs a;
+  for (int d = 0; d < 3; ++d) {
+    a.n[d] = g.n[d];
+    a.goff[d] = g.goff[d];
+    a.h[d] = g.h[d];
+    a.x0[d] = d < c->cfg.dim ? c->cfg.domain_lo[d] : 0.0;
+  }
+  a.pitch = g.pitch;
+  a.plane = g.plane;
+  a.face_mask = 0;
+  a.dim = c->cfg.dim;
+  BcProg pr;
+  pr.n = n;
+  for (int q = 0; q < n; ++q) { pr.op[q] = prog[q].op; pr.val[q] = prog[q].value; }
+  const long long total = (long long)(g.n[0] + 2) * (g.n[1] + 2) * (c->cfg.dim == 3 ? g.n[2] + 2 : 1);
+  long long blocks = (total + 255) / 256;
+  if (blocks > 148 * 16) blocks = 148 * 16;
+  k_field_eval<<<(int)blocks, 256, 0, c->stream>>>(a, pr, field_ptr(c, &f, slot, 0), g.vol, comp);
   EXAMG_LAUNCH_CHECK(c);
   return EXAMG_OK;
 }

@@ -45,6 +45,43 @@ def laplace_stencil(dim, h, scaled=True, order="bench"):
     return offsets, coeffs
 
 
+def varcoeff27_offsets():
+    """27 entries, lexicographic (dx fastest, dz slowest); the centre is entry 13."""
+    return [(dx, dy, dz) for dz in (-1, 0, 1) for dy in (-1, 0, 1) for dx in (-1, 0, 1)]
+
+
+VARCOEFF27_WEIGHTS = (0.0, 14.0 / 30.0, 3.0 / 30.0, 1.0 / 30.0)  # faces, edges, corners of the compact 27-point Laplacian
+
+
+def varcoeff27_programs(h, kappa):
+    """Postfix programs (examg_field_eval) that assemble BASELINE config 3's operator, the 27-point analogue of
+    InitLaplace in Testing/SISC/3D_VarCoeff.exa4:212-240: entry d != 0 is  ((-1 * w_|d|) * a(x + d*h/2)) / (h*h)
+    with getCoefficient a = exp(kappa * (((x - x*x) * (y - y*y)) * (z - z*z))), the centre is -(sum of the others,
+    in entry order).  Returns [(component, program)] in the order they have to run."""
+    out = []
+
+    def pos(op, d):  # x + (0.5 * d) * h
+        return [(op, 0.0), (rt.OP_CONST, (0.5 * d) * h), (rt.OP_ADD, 0.0)]
+
+    def bump(op, d):  # X - X * X
+        return pos(op, d) + pos(op, d) + pos(op, d) + [(rt.OP_MUL, 0.0), (rt.OP_SUB, 0.0)]
+
+    for e, (dx, dy, dz) in enumerate(varcoeff27_offsets()):
+        if e == 13:
+            continue
+        w = VARCOEFF27_WEIGHTS[(dx != 0) + (dy != 0) + (dz != 0)]
+        prog = [(rt.OP_CONST, -1.0 * w), (rt.OP_CONST, kappa)]
+        prog += bump(rt.OP_X, dx) + bump(rt.OP_Y, dy) + [(rt.OP_MUL, 0.0)] + bump(rt.OP_Z, dz) + [(rt.OP_MUL, 0.0)]
+        prog += [(rt.OP_MUL, 0.0), (rt.OP_EXP, 0.0), (rt.OP_MUL, 0.0), (rt.OP_CONST, h * h), (rt.OP_DIV, 0.0)]
+        out.append((e, prog))
+    others = [e for e in range(27) if e != 13]
+    prog = [(rt.OP_COMP, float(others[0]))]
+    for e in others[1:]:
+        prog += [(rt.OP_COMP, float(e)), (rt.OP_ADD, 0.0)]
+    out.append((13, prog + [(rt.OP_NEG, 0.0)]))
+    return out
+
+
 class MultigridProgram:
     """One generated solver instance (one block on one GPU)."""
 
@@ -71,7 +108,15 @@ class MultigridProgram:
         for lvl in self.levels:
             h = ctx.width(lvl)
             offsets, coeffs = laplace_stencil(dim, h, scaled=(op != "unscaled"), order=order)
-            if op == "varcoeff":
+            if op == "varcoeff27":
+                assert dim == 3 and h[0] == h[1] == h[2], "varcoeff27: cubic cells"
+                offsets = varcoeff27_offsets()
+                cf = ctx.field_create("LaplaceCoeff", lvl, 1, 27)
+                self.coeff_field[lvl] = cf
+                self.stencil[lvl] = ctx.stencil_field(lvl, offsets, cf)
+                for comp, prog in varcoeff27_programs(h[0], kappa):  # InitLaplace@lvl, on the device
+                    ctx.field_eval(cf, prog, comp)
+            elif op == "varcoeff":
                 cf = ctx.field_create("LaplaceCoeff", lvl, 1, len(offsets))
                 self.coeff_field[lvl] = cf
                 self.stencil[lvl] = ctx.stencil_field(lvl, offsets, cf)
@@ -147,7 +192,7 @@ class MultigridProgram:
         return self._staging(("f", lvl), lvl)
 
     def coeff(self, lvl):
-        if self.op != "varcoeff":
+        if self.op not in ("varcoeff", "varcoeff27"):
             return None
         return self._staging(("c", lvl), lvl, lead=len(self._offsets))
 

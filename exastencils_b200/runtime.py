@@ -20,6 +20,7 @@ HEADER_PATH = os.path.join(os.path.dirname(_PKG), "include", "examg.h")
 MAX_STENCIL = 27
 BC_NONE, BC_DIRICHLET_CONST, BC_DIRICHLET_EXPR, BC_DIRICHLET_HOST = 0, 1, 2, 3
 OP_CONST, OP_X, OP_Y, OP_Z, OP_ADD, OP_SUB, OP_MUL, OP_DIV, OP_NEG = range(9)
+OP_EXP, OP_SIN, OP_COS, OP_SINH, OP_SQRT, OP_COMP = range(9, 15)
 SMOOTH_JACOBI, SMOOTH_RBGS = 0, 1
 BC_NEUMANN = 4
 F_SOLUTION, F_RHS, F_RESIDUAL, F_CGTMP0, F_CGTMP1 = range(5)
@@ -86,6 +87,7 @@ SIGNATURES = {
     "examg_field_advance": (C.c_int, [C.c_void_p, C.c_int]),
     "examg_field_set_bc": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_double]),
     "examg_field_set_bc_expr": (C.c_int, [C.c_void_p, C.c_int, C.POINTER(BcOp), C.c_int]),
+    "examg_field_eval": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.POINTER(BcOp), C.c_int]),
     "examg_apply_bc": (C.c_int, [C.c_void_p, C.c_int, C.c_int]),
     "examg_field_upload": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_void_p]),
     "examg_field_download": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_void_p]),
@@ -286,6 +288,13 @@ class Context:
         for i, (op, val) in enumerate(prog):
             arr[i].op, arr[i].value = op, val
         check(self.L.examg_field_set_bc_expr(self.h, f, arr, len(prog)))
+
+    def field_eval(self, f, prog, comp=0, slot=-1):
+        """loop over F { F[comp] = <postfix program over the node position> } (local nodes + one ghost layer)."""
+        arr = (BcOp * len(prog))()
+        for i, (op, val) in enumerate(prog):
+            arr[i].op, arr[i].value = op, val
+        check(self.L.examg_field_eval(self.h, f, slot, comp, arr, len(prog)))
 
     def apply_bc(self, f, slot=-1):
         check(self.L.examg_apply_bc(self.h, f, slot))

@@ -110,11 +110,21 @@ enum {
 enum {
   EXAMG_OP_CONST = 0, /* push value */
   EXAMG_OP_X = 1, EXAMG_OP_Y = 2, EXAMG_OP_Z = 3, /* push node position */
-  EXAMG_OP_ADD = 4, EXAMG_OP_SUB = 5, EXAMG_OP_MUL = 6, EXAMG_OP_DIV = 7, EXAMG_OP_NEG = 8
+  EXAMG_OP_ADD = 4, EXAMG_OP_SUB = 5, EXAMG_OP_MUL = 6, EXAMG_OP_DIV = 7, EXAMG_OP_NEG = 8,
+  /* math functions of the L4 language (C/s/e/base/ir/IR_MathFunctions.scala): the device's libm, which can
+   * differ from the host's in the last bit */
+  EXAMG_OP_EXP = 9, EXAMG_OP_SIN = 10, EXAMG_OP_COS = 11, EXAMG_OP_SINH = 12, EXAMG_OP_SQRT = 13,
+  /* examg_field_eval only: push component `value` of the field being written, at the same node */
+  EXAMG_OP_COMP = 14
 };
 typedef struct { int op; double value; } examg_bc_op;
 int examg_field_set_bc(examg_ctx *ctx, int field, int kind, double value);
 int examg_field_set_bc_expr(examg_ctx *ctx, int field, const examg_bc_op *prog, int n_ops);
+/* loop over F { F[comp] = <expr> } with <expr> a postfix program over vf_nodePosition_{x,y,z}: the initialisation
+ * loops of the L4 programs (InitRHS, InitLaplace of Testing/SISC/3D_VarCoeff.exa4:212-240).  Runs on every local node
+ * and on the first ghost layer (node positions continue beyond the block), so stencil-field coefficients need no
+ * exchange.  EXAMG_OP_COMP reads components written by earlier calls (e.g. centre = -(sum of the others)). */
+int examg_field_eval(examg_ctx *ctx, int field, int slot, int comp, const examg_bc_op *prog, int n_ops);
 /* applyBCs<F>_<lvl>(slot)  (C/s/e/boundary/ir/IR_ApplyBCFunction.scala:53-105); slot < 0 = active */
 int examg_apply_bc(examg_ctx *ctx, int field, int slot);
 

@@ -104,7 +104,9 @@ void og_xpay(const int n[3], const double *x, double beta, double *y);   /* y = 
 enum { OG_SMOOTH_JACOBI = 0, OG_SMOOTH_RBGS = 1 };
 enum { OG_OP_LAPLACE_SCALED = 0,   /* 2/h^2.., -1/h^2 per level (Benchmark, Examples, SISC ConstCoeff) */
        OG_OP_LAPLACE_UNSCALED = 1, /* [2d, -1 ...] on every level (Testing/Smoothers, Testing/Opts)    */
-       OG_OP_VARCOEFF = 2 };       /* 7-pt stencil field (Testing/SISC/3D_VarCoeff.exa4)                */
+       OG_OP_VARCOEFF = 2,         /* 7-pt stencil field (Testing/SISC/3D_VarCoeff.exa4)                */
+       OG_OP_VARCOEFF27 = 3 };     /* 27-pt stencil field of BASELINE config 3 (the reference ships none: SURVEY 8h);
+                                      defined here, see og_init_varcoeff27                                */
 enum { OG_ORDER_BENCH = 0,   /* centre,-x,+x,-y,+y,-z,+z  (Benchmark/Poisson3D, Examples/Poisson) */
        OG_ORDER_TESTING = 1 }; /* centre,+x,-x,+y,-y,+z,-z  (Testing/Smoothers, SISC, Opts)      */
 
@@ -114,7 +116,7 @@ typedef struct {
   int min_level, max_level;
   int op;               /* OG_OP_* */
   int order;            /* OG_ORDER_* */
-  double kappa;         /* OG_OP_VARCOEFF */
+  double kappa;         /* OG_OP_VARCOEFF, OG_OP_VARCOEFF27 */
   int smoother;         /* OG_SMOOTH_* */
   double omega;
   int nu_pre, nu_post;

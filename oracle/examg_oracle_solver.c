@@ -55,6 +55,11 @@ static void og_build_stencil(const og_config *c, og_level *l) {
   const int dim = c->dim;
   og_stencil *st = &l->st;
   memset(st, 0, sizeof(*st));
+  if (c->op == OG_OP_VARCOEFF27) { /* 27 entries, lexicographic (dx fastest, dz slowest): centre is entry 13 */
+    st->nst = 27;
+    for (int e = 0; e < 27; ++e) { st->off[e][0] = e % 3 - 1; st->off[e][1] = (e / 3) % 3 - 1; st->off[e][2] = e / 9 - 1; }
+    return;
+  }
   st->nst = 2 * dim + 1;
   /* entry order as declared in the .exa4 files */
   int e = 1;
@@ -118,6 +123,35 @@ static void og_init_varcoeff(const og_config *c, og_level *l) {
       }
 }
 
+/* BASELINE config 3: "3D 27-point variable-coefficient Poisson".  The reference has no such program (its
+ * variable-coefficient tests are 7-point, Testing/SISC/3D_VarCoeff.exa4); the operator is defined here in the style of
+ * that file's InitLaplace: the compact 27-point Laplacian (faces 14/30, edges 3/30, corners 1/30 over h^2, centre
+ * 128/30) with every off-centre entry weighted by getCoefficient at the midpoint towards that neighbour, and the
+ * centre = -(sum of the others, accumulated in entry order), so rows sum to zero.  Cubic cells (hx = hy = hz). */
+static void og_init_varcoeff27(const og_config *c, og_level *l) {
+  const double kap = c->kappa, h = l->h[0];
+  static const double w[4] = {0.0, 14.0 / 30.0, 3.0 / 30.0, 1.0 / 30.0};
+  l->sf = og_calloc((size_t)27 * l->size);
+#pragma omp parallel for schedule(static) collapse(2)
+  for (int k = 0; k < l->n[2]; ++k)
+    for (int j = 0; j < l->n[1]; ++j)
+      for (int i = 0; i < l->n[0]; ++i) {
+        size_t p = (size_t)i + (size_t)l->n[0] * ((size_t)j + (size_t)l->n[1] * (size_t)k);
+        double x = i * h, y = j * h, z = k * h;
+        double sum = 0.0;
+        for (int e = 0; e < 27; ++e) {
+          if (e == 13) continue;
+          const int dx = e % 3 - 1, dy = (e / 3) % 3 - 1, dz = e / 9 - 1;
+          const int m = (dx != 0) + (dy != 0) + (dz != 0);
+          const double a = og_coeff3(kap, x + (0.5 * dx) * h, y + (0.5 * dy) * h, z + (0.5 * dz) * h);
+          const double v = ((-1.0 * w[m]) * a) / (h * h);
+          l->sf[(size_t)e * l->size + p] = v;
+          sum = sum + v;
+        }
+        l->sf[(size_t)13 * l->size + p] = -sum;
+      }
+}
+
 og_solver *og_solver_create(const og_config *cfg) {
   og_solver *s = (og_solver *)calloc(1, sizeof(*s));
   s->cfg = *cfg;
@@ -135,6 +169,7 @@ og_solver *og_solver_create(const og_config *cfg) {
     l->size = (size_t)l->n[0] * l->n[1] * l->n[2];
     og_build_stencil(cfg, l);
     if (cfg->op == OG_OP_VARCOEFF) og_init_varcoeff(cfg, l);
+    if (cfg->op == OG_OP_VARCOEFF27) og_init_varcoeff27(cfg, l);
     l->u[0] = og_calloc(l->size);
     if (cfg->smoother == OG_SMOOTH_JACOBI) l->u[1] = og_calloc(l->size);
     l->rhs = og_calloc(l->size);

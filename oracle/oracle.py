@@ -16,7 +16,7 @@ _SO = os.path.join(_HERE, "_ref", "libexamg_oracle.so")
 
 OG_MAX_ST = 27
 SMOOTH_JACOBI, SMOOTH_RBGS = 0, 1
-OP_LAPLACE_SCALED, OP_LAPLACE_UNSCALED, OP_VARCOEFF = 0, 1, 2
+OP_LAPLACE_SCALED, OP_LAPLACE_UNSCALED, OP_VARCOEFF, OP_VARCOEFF27 = 0, 1, 2, 3
 ORDER_BENCH, ORDER_TESTING = 0, 1
 
 

@@ -1,7 +1,7 @@
 """Builds an oracle Solver for a tests.programs.Program (test helper)."""
 from oracle import oracle as og
 
-_OP = {"scaled": og.OP_LAPLACE_SCALED, "unscaled": og.OP_LAPLACE_UNSCALED, "varcoeff": og.OP_VARCOEFF}
+_OP = {"scaled": og.OP_LAPLACE_SCALED, "unscaled": og.OP_LAPLACE_UNSCALED, "varcoeff": og.OP_VARCOEFF, "varcoeff27": og.OP_VARCOEFF27}
 _ORDER = {"bench": og.ORDER_BENCH, "testing": og.ORDER_TESTING}
 _SM = {"jacobi": og.SMOOTH_JACOBI, "rbgs": og.SMOOTH_RBGS}
 

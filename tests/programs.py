@@ -163,6 +163,17 @@ BC_3D_POLY = Program("BC_3D_Polynomial", "BC_3D_Polynomial", _BC_CFG3, bc=_quad_
 BC_3D_TRIG = Program("BC_3D_Trigonometric", "BC_3D_Trigonometric", _BC_CFG3, bc=_trig3, exact=_trig3, prints="err")
 BC_PROGRAMS = [BC_2D_POLY, BC_2D_TRIG, BC_3D_POLY, BC_3D_TRIG]
 
+# BASELINE config 3: "3D 27-point variable-coefficient Poisson, damped Jacobi with temporally blocked sweeps".  The
+# reference ships no such program; this is Testing/SISC/3D_VarCoeff (same coefficient, RHS, boundary data,
+# omega) with the 27-point operator of oracle/examg_oracle_solver.c:og_init_varcoeff27 and V(2,2), on one fragment.
+# No golden vector: parity is oracle <-> GPU only ("parity unpinned by the reference").
+CONFIG3_VARCOEFF27 = Program(
+    "Config3_VarCoeff27", None,
+    dict(dim=3, F=(1, 1, 1), min_level=1, max_level=6, op="varcoeff27", order="testing", kappa=KAPPA,
+         smoother="jacobi", omega=0.85, nu_pre=2, nu_post=2, restrict_scale=1.0, cg_max_it=1024, cg_rel_tol=1e-3),
+    rhs=_rhs3, bc=lambda X, Y, Z: 1.0 - np.exp((-1.0 * KAPPA) * _b3(X, Y, Z)),
+    exact=lambda X, Y, Z: 1.0 - np.exp((-1.0 * KAPPA) * _b3(X, Y, Z)), prints="res")
+
 ALL = [POISSON_2D, SMOOTHERS_RBGS, SMOOTHERS_JAC, SISC_3D_CONST, SISC_3D_VAR, SISC_2D_CONST, SISC_2D_VAR]
 
 

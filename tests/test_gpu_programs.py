@@ -32,7 +32,7 @@ def _setup_pair(prog, mode, **override):
     prog.setup(ref)
     ref.sync_slots()
     prog.setup(gpu)
-    if prog.cfg["op"] == "varcoeff":  # identical operator data on both sides
+    if prog.cfg["op"] in ("varcoeff", "varcoeff27"):  # identical operator data on both sides
         for lvl in range(ref.min_level, ref.max_level + 1):
             gpu.coeff(lvl)[...] = ref.coeff(lvl).reshape(gpu.coeff(lvl).shape)
     gpu.sync_slots()
@@ -49,7 +49,7 @@ def test_golden_stdout(prog, mode, oracle):
         pytest.skip("call-by-call mode is covered in 2D and by test_oracle_parity")
     gpu = make_gpu_solver(prog.cfg, mode)
     prog.setup(gpu)
-    if prog.cfg["op"] == "varcoeff":
+    if prog.cfg["op"] in ("varcoeff", "varcoeff27"):
         ref = make_oracle_solver(prog.cfg)
         for lvl in range(ref.min_level, ref.max_level + 1):
             gpu.coeff(lvl)[...] = ref.coeff(lvl).reshape(gpu.coeff(lvl).shape)
@@ -67,7 +67,7 @@ def test_golden_stdout_3d_sisc(prog, oracle):
     (polynomial and sin*sin*sinh Dirichlet data)."""
     gpu = make_gpu_solver(prog.cfg, "library")
     prog.setup(gpu)
-    if prog.cfg["op"] == "varcoeff":
+    if prog.cfg["op"] in ("varcoeff", "varcoeff27"):
         ref = make_oracle_solver(prog.cfg)
         for lvl in range(ref.min_level, ref.max_level + 1):
             gpu.coeff(lvl)[...] = ref.coeff(lvl).reshape(gpu.coeff(lvl).shape)
@@ -91,6 +91,8 @@ SMALL = dict(max_level=4)
     (programs.SISC_3D_VAR, dict(max_level=3)),
     (programs.SMOOTHERS_RBGS, dict(max_level=3, nu_pre=2, nu_post=2, omega=0.8)),   # V(2,2), north-star smoother
     (programs.SMOOTHERS_JAC, dict(max_level=3, nu_pre=2, nu_post=1)),                # odd sweep count: slot parity flips
+    (programs.CONFIG3_VARCOEFF27, dict(max_level=6)),   # 27-point stencil field, V(2,2): pairs of sweeps fused on 33^3, 65^3
+    (programs.CONFIG3_VARCOEFF27, dict(max_level=5, nu_pre=3, nu_post=3)),           # 2 fused + 1 generic sweep
 ], ids=lambda v: v.name if hasattr(v, "name") else "-".join("%s%s" % kv for kv in v.items()))
 def test_oracle_parity(prog, override, mode, oracle):
     ref, gpu = _setup_pair(prog, mode, **override)
@@ -111,6 +113,58 @@ def test_oracle_parity(prog, override, mode, oracle):
         assert np.array_equal(gpu.fetch_solution(l), ref.solution(l).reshape(gpu.ctx.shape(l))), "Solution@%d" % l
     gpu.close()
     ref.close()
+
+
+def test_varcoeff27_device_assembly(oracle):
+    """InitLaplace of BASELINE config 3 on the device (examg_field_eval: postfix programs with exp) against the
+    oracle's host assembly: equal up to the last bits of exp (device libm vs glibc), rows sum to zero."""
+    prog = programs.CONFIG3_VARCOEFF27
+    ref = make_oracle_solver(prog.cfg, max_level=4)
+    gpu = make_gpu_solver(prog.cfg, "library", max_level=4)
+    for lvl in range(ref.min_level, ref.max_level + 1):
+        got = gpu.ctx.download(gpu.coeff_field[lvl], lvl, ncomp=27)
+        want = ref.coeff(lvl).reshape(got.shape)
+        assert np.allclose(got, want, rtol=4e-15, atol=0.0), "level %d" % lvl
+        off = np.delete(got, 13, axis=0)
+        assert np.all(np.abs(off.sum(axis=0) + got[13]) <= 1e-12 * np.abs(got[13]))
+    # the cycle runs on the device-assembled operator: same contraction as with the oracle's coefficients
+    prog.setup(ref)
+    ref.sync_slots()
+    prog.setup(gpu)
+    gpu.sync_slots()
+    r_ref, r_gpu = ref.update_residual_norm(), gpu.update_residual_norm()
+    for _ in range(3):
+        ref.vcycle()
+        gpu.vcycle()
+    a, b = ref.update_residual_norm() / r_ref, gpu.update_residual_norm() / r_gpu
+    assert abs(a - b) <= 1e-9 * a and b < 0.01
+    gpu.close()
+    ref.close()
+
+
+def test_field_eval_ops():
+    """examg_field_eval: every postfix op against numpy on a ragged 2D grid (ghost layer included in the loop)."""
+    from exastencils_b200 import runtime as rt
+    ctx = rt.Context(2, 3, 3, block_cells=(3, 5))
+    f = ctx.field_create("f", 3, 1, 2)
+    n = ctx.dims(3)
+    h = ctx.width(3)
+    x = np.arange(n[0]) * h[0]
+    y = np.arange(n[1]) * h[1]
+    X, Y = x[None, None, :], y[None, :, None]
+    ctx.field_eval(f, [(rt.OP_X, 0), (rt.OP_SIN, 0), (rt.OP_Y, 0), (rt.OP_COS, 0), (rt.OP_MUL, 0), (rt.OP_CONST, 2.0),
+                       (rt.OP_SQRT, 0), (rt.OP_X, 0), (rt.OP_MUL, 0), (rt.OP_SINH, 0), (rt.OP_ADD, 0)], comp=0)
+    ctx.field_eval(f, [(rt.OP_COMP, 0.0), (rt.OP_NEG, 0), (rt.OP_Y, 0), (rt.OP_EXP, 0), (rt.OP_DIV, 0),
+                       (rt.OP_CONST, 1.5), (rt.OP_SUB, 0)], comp=1)
+    got = ctx.download(f, 3, ncomp=2)
+    want0 = np.sin(X) * np.cos(Y) + np.sinh(np.sqrt(2.0) * X)
+    assert np.allclose(got[0], np.broadcast_to(want0, got[0].shape), rtol=1e-14, atol=1e-15)
+    assert np.allclose(got[1], -got[0] / np.exp(np.broadcast_to(Y, got[0].shape)) - 1.5, rtol=1e-14, atol=1e-15)
+    with pytest.raises(rt.ExaMGError):
+        ctx.field_eval(f, [(rt.OP_COMP, 2.0)], comp=0)   # component out of range
+    with pytest.raises(rt.ExaMGError):
+        ctx.field_eval(f, [(rt.OP_X, 0), (rt.OP_ADD, 0)], comp=0)   # stack underflow
+    ctx.close()
 
 
 def test_benchmark_program_properties(oracle):
