@@ -92,6 +92,7 @@ KAPPA = 10.0  # getCoefficient of Testing/SISC/3D_VarCoeff.exa4
 
 # --workload: poisson7 = BASELINE configs[1] (the bench contract), varcoef27 = configs[2] (27-point stencil field,
 # damped Jacobi with pairs of sweeps fused into one pass over the coefficients; 1 GPU)
+VBLOCKS = {1: (1, 1, 1), 8: (2, 2, 2)}  # varcoef27: the unit cube, cubic cells
 WORKLOADS = {
     "poisson7": dict(op="scaled", order="bench", smoother="rbgs", omega=OMEGA, kappa=0.0, bytes_sweep=24.0,
                      bytes_residual=24.0),
@@ -210,8 +211,9 @@ def workload_config(n_gpus, level, workload="poisson7"):
     if workload == "varcoef27":
         return {"workload": "3D 27-point variable-coefficient Poisson (stencil field, coefficient exp(10 (x-x^2)(y-y^2)"
                             "(z-z^2))), V(2,2) damped Jacobi omega=0.85 with pairs of sweeps fused into one pass, CG "
-                            "coarse solve, %d^3 cells, levels %d..%d" % (1 << level, MIN_LEVEL, level),
-                "blocks": [1, 1, 1], "cells_per_gpu": (1 << level) ** 3, "smoother": "jacobi", "nu_pre": NU_PRE,
+                            "coarse solve, %d^3 cells per GPU (%d^3 in all), levels %d..%d" % (
+                                1 << level, VBLOCKS[n_gpus][0] << level, MIN_LEVEL, level),
+                "blocks": list(VBLOCKS[n_gpus]), "cells_per_gpu": (1 << level) ** 3, "smoother": "jacobi", "nu_pre": NU_PRE,
                 "nu_post": NU_POST, "l2_policy": "inputs larger than L2 (27 coefficient components x %.2f GB on the "
                 "finest level)" % (8.0 * ((1 << level) + 1) ** 3 / 1e9)}
     return {"workload": "Benchmark/Poisson3D 7-point constant-coefficient, V(2,2) RBGS omega=0.8, CG coarse solve, "
@@ -263,8 +265,11 @@ def main():
         args.level = 8 if args.workload == "varcoef27" else 9
     if args.cpu_level is None:
         args.cpu_level = min(args.level, 8) if args.workload == "varcoef27" else 9
-    if args.workload == "varcoef27" and args.gpus != 1:
-        raise SystemExit("--workload varcoef27 runs on one GPU (stencil fields are single-block so far)")
+    if args.workload == "varcoef27" and args.gpus not in VBLOCKS:
+        raise SystemExit("--workload varcoef27 runs on 1 GPU or on 8 (2x2x2 blocks of the unit cube: 1024^3 cells at "
+                         "level 9 per GPU)")
+    blocks = VBLOCKS[args.gpus] if args.workload == "varcoef27" else BLOCKS[args.gpus]
+    domain_hi = (1.0, 1.0, 1.0) if args.workload == "varcoef27" else tuple(float(b) for b in blocks)
     if args.impl == "reference":
         return run_reference(args)
 
@@ -286,14 +291,14 @@ def main():
     level = args.level
     prog = MultigridProgram(3, (1, 1, 1), MIN_LEVEL, level, op=wl["op"], order=wl["order"], smoother=wl["smoother"],
                             omega=wl["omega"], kappa=wl["kappa"], nu_pre=NU_PRE, nu_post=NU_POST, cg_max_it=128, cg_rel_tol=1e-3,
-                            num_blocks=BLOCKS[world], rank=rank, device=local_rank, stream=stream.cuda_stream,
-                            domain_hi=tuple(float(b) for b in BLOCKS[world]))
+                            num_blocks=blocks, rank=rank, device=local_rank, stream=stream.cuda_stream,
+                            domain_hi=domain_hi)
     if world > 1:
         from exastencils_b200.distributed import wire_peers
         wire_peers(prog.ctx, dist, device="cuda:%d" % local_rank)
     set_problem(prog, args.workload)
     ctx = prog.ctx
-    nb = BLOCKS[world]
+    nb = blocks
     dof = 1.0
     for d in range(3):
         dof *= (nb[d] << level) - 1

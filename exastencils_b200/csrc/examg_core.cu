@@ -456,7 +456,22 @@ int examg_field_eval(examg_ctx *c, int h, int slot, int comp, const examg_bc_op 
   if (f->loc != 0) return set_error(EXAMG_EUNSUP, "examg_field_eval: node-localised fields only");
   int rc = check_program("examg_field_eval", prog, n, f->ncomp);
   if (rc) return rc;
-  return launch_field_eval(c, *f, slot, comp, prog, n);
+  if ((rc = launch_field_eval(c, *f, slot, comp, prog, n))) return rc;
+  if (slot <= 0 || f->nslots == 1) {
+    f->evals.emplace_back(comp, std::vector<examg_bc_op>(prog, prog + n));
+    f->eval_gen++;
+    // the loop also ran on the first ghost layer (global node positions): once every component was produced this
+    // way the layer holds what the neighbour blocks computed for their own nodes
+    std::vector<char> seen(f->ncomp, 0);
+    for (const auto &e : f->evals) seen[e.first] = 1;
+    bool all = true;
+    for (char v : seen) all = all && v;
+    if (all && f->halo_depth < 1) f->halo_depth = 1;
+  } else {
+    f->evals.clear();
+    f->eval_gen++;
+  }
+  return EXAMG_OK;
 }
 
 int examg_apply_bc(examg_ctx *c, int h, int slot) {
@@ -474,7 +489,7 @@ static int copy_field(examg_ctx *c, int h, int slot, double *host, bool up, bool
   if (!host) return set_error(EXAMG_EINVAL, "null host pointer");
   if (slot >= f->nslots) return set_error(EXAMG_EINVAL, "bad slot %d", slot);
   const LevelGeom &g = *geom(c, f->level);
-  if (up) f->halo_depth = 0;
+  if (up) { f->halo_depth = 0; f->evals.clear(); f->eval_gen++; }
   int e[3];  // dense extents: nodes, or cells of a cell-localised field
   for (int d = 0; d < 3; ++d) e[d] = g.n[d] - (f->loc == 1 && d < c->cfg.dim ? 1 : 0);
   const size_t dense = (size_t)e[0] * e[1] * e[2];
@@ -593,6 +608,8 @@ int examg_field_upload_finish(examg_ctx *c) {
   }
   EXAMG_CUDA(cudaEventRecord(c->up_d2d[b], c->stream));
   f->halo_depth = 0;
+  f->evals.clear();
+  f->eval_gen++;
   c->up_turn ^= 1;
   c->up_pending = false;
   return EXAMG_OK;
@@ -604,6 +621,8 @@ int examg_field_fill(examg_ctx *c, int h, double value) {
   const LevelGeom &g = *geom(c, f->level);
   const size_t count = (size_t)f->ncomp * g.vol;
   f->halo_depth = 0;
+  f->evals.clear();
+  f->eval_gen++;
   std::vector<double> row(g.pitch, value);
   for (int sl = 0; sl < f->nslots; ++sl) {
     double *base = f->slot[sl];

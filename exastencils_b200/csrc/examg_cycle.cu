@@ -30,6 +30,10 @@ struct examg_solver {
   int agg_level = -1;
   examg_ctx *agg_ctx = nullptr;       // rank 0 only
   examg_solver *agg = nullptr;
+  // stencil fields on the agglomerated levels (rank 0): coefficient field of this context -> its twin on the
+  // agglomerated grid, re-created there by replaying the examg_field_eval programs of the source
+  struct AggCoef { int src, dst; long long gen; };
+  std::vector<AggCoef> agg_coef;
   bool use_graph = true;
   struct Graph { cudaGraphExec_t exec; long long launches; std::vector<int> exit_slots; };
   std::map<std::vector<int>, Graph> graphs;  // keyed by the active slots of Solution on entry
@@ -209,9 +213,12 @@ examg_solver *examg_solver_create(examg_ctx *c, const examg_cycle_desc *d) {
       for (int lvl = c->cfg.min_level; lvl <= T; ++lvl) {
         const Stencil &st = *get_stencil(c, s->stencils[lvl - c->cfg.min_level]);
         if (st.coeff_field >= 0) {
-          set_error(EXAMG_EUNSUP, "multi-block solver: stencil fields on agglomerated levels");
-          examg_solver_destroy(s);
-          return nullptr;
+          const Field &cf = c->fields[st.coeff_field];
+          const int dst = examg_field_create(s->agg_ctx, cf.name.c_str(), lvl, 1, cf.ncomp);
+          if (dst < 0) { examg_solver_destroy(s); return nullptr; }
+          s->agg_coef.push_back({st.coeff_field, dst, -1});
+          ast.push_back(examg_stencil_field(s->agg_ctx, lvl, st.nst, st.off, dst));
+          continue;
         }
         ast.push_back(examg_stencil_const(s->agg_ctx, lvl, st.nst, st.off, st.coef));
       }
@@ -287,6 +294,34 @@ int examg_solver_vcycle(examg_solver *s, int level) {
   examg_ctx *c = s->c;
   if (level < 0) level = c->cfg.max_level;
   if (level < c->cfg.min_level || level > c->cfg.max_level) return set_error(EXAMG_EINVAL, "examg_solver_vcycle: level %d", level);
+  // static operands: ghost layers of stencil-field coefficients are exchanged once, outside the captured cycle
+  // (the fused stencil-field Jacobi reads them, examg_jacv.cuh); the twins on the agglomerated grid are brought
+  // up to date
+  if (c->world > 1) {
+    for (int l = lv(s, s->agg_level) + 1; l < (int)s->stencils.size(); ++l) {
+      const Stencil *st = get_stencil(c, s->stencils[l]);
+      if (st && st->coeff_field >= 0 && c->fields[st->coeff_field].halo_depth < 1) {
+        int rc = do_exchange(c, c->fields[st->coeff_field], 0, 1);
+        if (rc) return rc;
+      }
+    }
+    for (auto &ac : s->agg_coef) {
+      const Field &src = c->fields[ac.src];
+      if (ac.gen == src.eval_gen) continue;
+      std::vector<char> seen(src.ncomp, 0);
+      for (const auto &e : src.evals) seen[e.first] = 1;
+      for (char v : seen)
+        if (!v)
+          return set_error(EXAMG_EUNSUP, "multi-block solver: the stencil field %s@%d of an agglomerated level was not "
+                           "produced by examg_field_eval (uploaded coefficients cannot be re-created on rank 0)",
+                           src.name.c_str(), src.level);
+      for (const auto &e : src.evals) {
+        int rc = examg_field_eval(s->agg_ctx, ac.dst, 0, e.first, e.second.data(), (int)e.second.size());
+        if (rc) return rc;
+      }
+      ac.gen = src.eval_gen;
+    }
+  }
   if (!s->use_graph || level != c->cfg.max_level) return vcycle_rec(s, level);
 
   std::vector<int> key;

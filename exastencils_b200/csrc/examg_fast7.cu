@@ -626,7 +626,7 @@ constexpr int JACV_MIN_N = 33;
 
 bool fused_jacv_usable(examg_ctx *c, const Stencil &s, const Field &fu) {
   if (!fused_enabled() || jacv_mode() <= 0 || c->cfg.dim != 3 || s.coeff_field < 0 || fu.ncomp != 1 ||
-      fu.nslots != 2 || c->world != 1)
+      fu.nslots != 2)
     return false;
   const int shape = jacv_shape(s);
   if (shape < 0 || (shape < 2 && jacv_mode() < 2)) return false;
@@ -653,7 +653,8 @@ static int launch_jacv(examg_ctx *c, const Stencil &s, double omega, Field &fu, 
     a.n[d] = g.n[d];
     a.ulo[d] = g.lo[d];
     a.uhi[d] = g.hi[d];
-    a.elo[d] = a.ehi[d] = 0;  // single block (fused_jacv_usable)
+    a.elo[d] = c->nb[d][0] ? 1 : 0;  // sweep 1 also runs on the first layer of the neighbour blocks' nodes
+    a.ehi[d] = c->nb[d][1] ? 1 : 0;
   }
   a.pitch = g.pitch;
   a.plane = g.plane;

@@ -61,6 +61,10 @@ int examg::residual_op(examg_ctx *c, int A, int u, int u_slot, int rhs, int res,
   if (c->world == 1) extend = 0;
   const int us = u_slot < 0 ? fu->cur : u_slot;
   int rc;
+  if (extend > 0 && s->coeff_field >= 0 && c->fields[s->coeff_field].halo_depth < extend) {
+    if (extend > 1) return set_error(EXAMG_EUNSUP, "examg_residual: stencil fields carry one valid ghost layer");
+    if ((rc = do_exchange(c, c->fields[s->coeff_field], 0, 1))) return rc;  // static: once
+  }
   if (extend > 0 && fr->halo_depth < extend) {  // communicate Solution (and RHS where its ghost layers are stale)
     Field *fs[2] = {fu, fr};
     const int slots[2] = {us, fr->cur}, depths[2] = {extend + 1, extend};
@@ -146,7 +150,22 @@ int examg_smooth_jacobi(examg_ctx *c, int A, int u, int rhs, double omega, int n
   int it0 = 0;
   if (fused_jacv_usable(c, *s, *fu)) {  // stencil-field coefficients: pairs of sweeps read them once (examg_jacv.cuh)
     for (; it0 + 2 <= nsweeps; it0 += 2) {
-      int rc = launch_jacv_fused(c, *s, omega, *fu, field_ptr(c, fr, -1));
+      int rc = EXAMG_OK;
+      if (c->world > 1) {
+        // sweep 1 is computed redundantly on the first ghost layer: two layers of Solution, one of RHS and one of
+        // the coefficients (static: exchanged once unless examg_field_eval already filled the layer)
+        Field &cf = c->fields[s->coeff_field];
+        if (cf.halo_depth < 1 && (rc = do_exchange(c, cf, 0, 1))) return rc;
+        if (fr->halo_depth < 1) {
+          Field *fs[2] = {fu, fr};
+          const int slots[2] = {fu->cur, fr->cur}, depths[2] = {2, 1};
+          rc = do_exchange_many(c, fs, slots, depths, 2);
+        } else {
+          rc = do_exchange(c, *fu, fu->cur, 2);
+        }
+        if (rc) return rc;
+      }
+      rc = launch_jacv_fused(c, *s, omega, *fu, field_ptr(c, fr, -1));
       if (rc) return rc;
       fu->halo_depth = 0;
     }

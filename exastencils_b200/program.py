@@ -53,15 +53,17 @@ def varcoeff27_offsets():
 VARCOEFF27_WEIGHTS = (0.0, 14.0 / 30.0, 3.0 / 30.0, 1.0 / 30.0)  # faces, edges, corners of the compact 27-point Laplacian
 
 
-def varcoeff27_programs(h, kappa):
+def varcoeff27_programs(hs, kappa):
     """Postfix programs (examg_field_eval) that assemble BASELINE config 3's operator, the 27-point analogue of
     InitLaplace in Testing/SISC/3D_VarCoeff.exa4:212-240: entry d != 0 is  ((-1 * w_|d|) * a(x + d*h/2)) / (h*h)
     with getCoefficient a = exp(kappa * (((x - x*x) * (y - y*y)) * (z - z*z))), the centre is -(sum of the others,
     in entry order).  Returns [(component, program)] in the order they have to run."""
     out = []
+    h = hs[0]  # scaling 1/hx^2 (cubic cells in all measured configurations); midpoints use each dimension's width
+    width = {rt.OP_X: hs[0], rt.OP_Y: hs[1], rt.OP_Z: hs[2]}
 
     def pos(op, d):  # x + (0.5 * d) * h
-        return [(op, 0.0), (rt.OP_CONST, (0.5 * d) * h), (rt.OP_ADD, 0.0)]
+        return [(op, 0.0), (rt.OP_CONST, (0.5 * d) * width[op]), (rt.OP_ADD, 0.0)]
 
     def bump(op, d):  # X - X * X
         return pos(op, d) + pos(op, d) + pos(op, d) + [(rt.OP_MUL, 0.0), (rt.OP_SUB, 0.0)]
@@ -109,12 +111,12 @@ class MultigridProgram:
             h = ctx.width(lvl)
             offsets, coeffs = laplace_stencil(dim, h, scaled=(op != "unscaled"), order=order)
             if op == "varcoeff27":
-                assert dim == 3 and h[0] == h[1] == h[2], "varcoeff27: cubic cells"
+                assert dim == 3, "varcoeff27: 3D"
                 offsets = varcoeff27_offsets()
                 cf = ctx.field_create("LaplaceCoeff", lvl, 1, 27)
                 self.coeff_field[lvl] = cf
                 self.stencil[lvl] = ctx.stencil_field(lvl, offsets, cf)
-                for comp, prog in varcoeff27_programs(h[0], kappa):  # InitLaplace@lvl, on the device
+                for comp, prog in varcoeff27_programs(h, kappa):  # InitLaplace@lvl, on the device
                     ctx.field_eval(cf, prog, comp)
             elif op == "varcoeff":
                 cf = ctx.field_create("LaplaceCoeff", lvl, 1, len(offsets))

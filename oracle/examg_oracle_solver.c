@@ -127,9 +127,10 @@ static void og_init_varcoeff(const og_config *c, og_level *l) {
  * variable-coefficient tests are 7-point, Testing/SISC/3D_VarCoeff.exa4); the operator is defined here in the style of
  * that file's InitLaplace: the compact 27-point Laplacian (faces 14/30, edges 3/30, corners 1/30 over h^2, centre
  * 128/30) with every off-centre entry weighted by getCoefficient at the midpoint towards that neighbour, and the
- * centre = -(sum of the others, accumulated in entry order), so rows sum to zero.  Cubic cells (hx = hy = hz). */
+ * centre = -(sum of the others, accumulated in entry order), so rows sum to zero.  Meant for cubic cells (all measured
+ * configurations); on other grids the midpoints use each dimension's width and the scaling stays 1/hx^2. */
 static void og_init_varcoeff27(const og_config *c, og_level *l) {
-  const double kap = c->kappa, h = l->h[0];
+  const double kap = c->kappa, h = l->h[0], hy = l->h[1], hz = l->h[2];
   static const double w[4] = {0.0, 14.0 / 30.0, 3.0 / 30.0, 1.0 / 30.0};
   l->sf = og_calloc((size_t)27 * l->size);
 #pragma omp parallel for schedule(static) collapse(2)
@@ -137,13 +138,13 @@ static void og_init_varcoeff27(const og_config *c, og_level *l) {
     for (int j = 0; j < l->n[1]; ++j)
       for (int i = 0; i < l->n[0]; ++i) {
         size_t p = (size_t)i + (size_t)l->n[0] * ((size_t)j + (size_t)l->n[1] * (size_t)k);
-        double x = i * h, y = j * h, z = k * h;
+        double x = i * h, y = j * hy, z = k * hz;
         double sum = 0.0;
         for (int e = 0; e < 27; ++e) {
           if (e == 13) continue;
           const int dx = e % 3 - 1, dy = (e / 3) % 3 - 1, dz = e / 9 - 1;
           const int m = (dx != 0) + (dy != 0) + (dz != 0);
-          const double a = og_coeff3(kap, x + (0.5 * dx) * h, y + (0.5 * dy) * h, z + (0.5 * dz) * h);
+          const double a = og_coeff3(kap, x + (0.5 * dx) * h, y + (0.5 * dy) * hy, z + (0.5 * dz) * hz);
           const double v = ((-1.0 * w[m]) * a) / (h * h);
           l->sf[(size_t)e * l->size + p] = v;
           sum = sum + v;

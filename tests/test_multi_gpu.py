@@ -26,3 +26,17 @@ def test_blocks_match_global_oracle(world, blocks, level):
            "--level", str(level), "--cycles", "3", "--blocks", blocks]
     out = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
     assert out.returncode == 0 and "MGPU PARITY OK" in out.stdout, out.stdout[-3000:] + out.stderr[-3000:]
+
+
+@pytest.mark.parametrize("world,blocks,level", [(2, "1,1,2", 7), (8, "2,2,2", 7)])
+def test_stencil_field_blocks(world, blocks, level):
+    """BASELINE config 3's program (27-point stencil field assembled on the device, V(2,2) damped Jacobi with fused
+    pairs of sweeps, coefficients of the agglomerated levels re-created on rank 0) on several blocks: bit-identical to
+    the same program on one block covering the global grid, and within 1e-9 of the oracle (host exp)."""
+    if _ngpus() < world:
+        pytest.skip("needs %d GPUs" % world)
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", str(world),
+           "--master-addr", "127.0.0.1", "--master-port", str(29720 + world), os.path.join(ROOT, "tests", "mgpu", "worker.py"),
+           "--level", str(level), "--cycles", "3", "--blocks", blocks, "--op", "varcoeff27", "--smoother", "jacobi"]
+    out = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
+    assert out.returncode == 0 and "MGPU PARITY OK" in out.stdout, out.stdout[-3000:] + out.stderr[-3000:]
