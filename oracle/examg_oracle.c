@@ -183,6 +183,11 @@ double og_dot(const int n[3], const double *a, const double *b) {
   return total.hi + total.lo;
 }
 
+void og_glibc_rand_fill(double *out, long long n) {
+  srand(1); /* the state a fresh process starts with */
+  for (long long i = 0; i < n; ++i) out[i] = ((double)rand() / RAND_MAX);
+}
+
 double og_max_abs_diff(const int n[3], const double *a, const double *b) {
   OG_LOOP_BEGIN(n)
   double m = 0.0;

@@ -78,6 +78,8 @@ def lib():
     L.og_dot.restype = C.c_double
     L.og_max_abs_diff.argtypes = [i3, dp, dp]
     L.og_max_abs_diff.restype = C.c_double
+    L.og_glibc_rand_fill.argtypes = [dp, C.c_longlong]
+    L.og_glibc_rand_fill.restype = None
     L.og_restrict.argtypes = [C.c_int, i3, i3, C.c_double, dp, dp]
     L.og_prolong_add.argtypes = [C.c_int, i3, i3, dp, dp]
     L.og_set_interior.argtypes = [i3, dp, C.c_double]
@@ -146,6 +148,13 @@ def smooth_rb(st, omega, u, rhs, color, sf=None):
 
 def dot(a, b):
     return lib().og_dot(_n(a), _dp(a), _dp(b))
+
+
+def glibc_rand(n):
+    """n values of (double)std::rand()/RAND_MAX from a freshly started process (Testing/Opts/base.exa4:167-169)."""
+    out = np.empty(int(n), dtype=np.float64)
+    lib().og_glibc_rand_fill(_dp(out), int(n))
+    return out
 
 
 def max_abs_diff(a, b):

@@ -22,6 +22,7 @@ FILES = {
     "SISC_2D_ConstCoeff": "Testing/SISC/2D_ConstCoeff.results",
     "SISC_2D_VarCoeff": "Testing/SISC/2D_VarCoeff.results",
     "Opts_seq": "Testing/Opts/seq.results",
+    "Opts_par": "Testing/Opts/par.results",
     "Application_OpticalFlow2D": "Testing/Application/OpticalFlow2D.results",
     "BC_2D_Polynomial": "Testing/BC/2D_Polynomial.results",
     "BC_2D_Trigonometric": "Testing/BC/2D_Trigonometric.results",

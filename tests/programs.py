@@ -163,6 +163,39 @@ BC_3D_POLY = Program("BC_3D_Polynomial", "BC_3D_Polynomial", _BC_CFG3, bc=_quad_
 BC_3D_TRIG = Program("BC_3D_Trigonometric", "BC_3D_Trigonometric", _BC_CFG3, bc=_trig3, exact=_trig3, prints="err")
 BC_PROGRAMS = [BC_2D_POLY, BC_2D_TRIG, BC_3D_POLY, BC_3D_TRIG]
 
+# Testing/Opts/{base,tempBlock}.exa4 with the seq_* knowledge files (one fragment, levels 0-6) and
+# {base_par,tempBlock_par}.exa4 with par_* (2x2x2 blocks, levels 0-8 => F=2, 513^3 nodes): the Smoothers/Jac cycle,
+# Dirichlet 0, RHS 0, Solution@finest filled with (double)std::rand()/RAND_MAX by a sequential loop.  ALL knowledge
+# variants (address precalculation, unrolling, vectorisation, polyhedral tiling) and the temporally blocked program
+# must print the same history -- the reference's own statement that these optimisations leave results unchanged.
+def _opts_init_seq(shape):
+    from oracle import oracle as og
+    return og.glibc_rand(int(np.prod(shape))).reshape(shape)
+
+
+def _opts_init_par(shape):
+    """Every MPI rank draws the same rand() sequence for its own loop points (256 per dimension: the interface node is
+    looped over by both neighbours); the first `communicate` then copies the lower block's value onto the shared
+    node (C/s/e/communication/ir/IR_PackInfoDuplicate.scala:15-39) => the lower block wins on every interface."""
+    from oracle import oracle as og
+    nz, ny, nx = shape  # interior of the 513^3 global grid: 511 per dimension
+    m = (nx + 1) // 2   # 256 loop points per block and dimension
+    r = og.glibc_rand(m ** 3).reshape((m, m, m))
+    g = np.zeros((nz + 2, ny + 2, nx + 2))
+    for bz in (1, 0):
+        for by in (1, 0):
+            for bx in (1, 0):
+                # block 0 loops over local nodes 1..m (global 1..m), block 1 over local 0..m-1 (global m..2m-1)
+                z0, y0, x0 = (1 if bz == 0 else m), (1 if by == 0 else m), (1 if bx == 0 else m)
+                g[z0:z0 + m, y0:y0 + m, x0:x0 + m] = r
+    return g[1:-1, 1:-1, 1:-1]
+
+
+_OPTS_CFG = dict(dim=3, F=(1, 1, 1), min_level=0, max_level=6, op="unscaled", order="testing", smoother="jacobi",
+                 omega=0.8, nu_pre=3, nu_post=3, restrict_scale=4.0, cg_max_it=512, cg_rel_tol=1e-3)
+OPTS_SEQ = Program("Opts_seq", "Opts_seq", _OPTS_CFG, init=_opts_init_seq)
+OPTS_PAR = Program("Opts_par", "Opts_par", dict(_OPTS_CFG, F=(2, 2, 2), max_level=8), init=_opts_init_par)
+
 # BASELINE config 3: "3D 27-point variable-coefficient Poisson, damped Jacobi with temporally blocked sweeps".  The
 # reference ships no such program (SURVEY 8h); this is Testing/SISC/3D_VarCoeff (same coefficient, RHS, boundary data,
 # omega) with the 27-point operator of oracle/examg_oracle_solver.c:og_init_varcoeff27 and V(2,2), on one fragment.
