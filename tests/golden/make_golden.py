@@ -23,6 +23,8 @@ FILES = {
     "SISC_2D_VarCoeff": "Testing/SISC/2D_VarCoeff.results",
     "Opts_seq": "Testing/Opts/seq.results",
     "Opts_par": "Testing/Opts/par.results",
+    "CommBasic_2D": "Testing/CommBasic/2D.results",
+    "Large_Hybrid": "Testing/Large/Hybrid.results",
     "Application_OpticalFlow2D": "Testing/Application/OpticalFlow2D.results",
     "BC_2D_Polynomial": "Testing/BC/2D_Polynomial.results",
     "BC_2D_Trigonometric": "Testing/BC/2D_Trigonometric.results",

@@ -161,6 +161,8 @@ BC_2D_POLY = Program("BC_2D_Polynomial", "BC_2D_Polynomial", _BC_CFG2, bc=_poly2
 BC_2D_TRIG = Program("BC_2D_Trigonometric", "BC_2D_Trigonometric", _BC_CFG2, bc=_trig2, exact=_trig2, prints="err")
 BC_3D_POLY = Program("BC_3D_Polynomial", "BC_3D_Polynomial", _BC_CFG3, bc=_quad_bc, exact=_quad_bc, prints="err")
 BC_3D_TRIG = Program("BC_3D_Trigonometric", "BC_3D_Trigonometric", _BC_CFG3, bc=_trig3, exact=_trig3, prints="err")
+# Testing/CommBasic/2D.{exa4,knowledge}: the same 2D cycle on 3x3 blocks x 3x3 fragments (F=9), prints the residual
+COMMBASIC_2D = Program("CommBasic_2D", "CommBasic_2D", dict(_BC_CFG2, F=(9, 9)), bc=_poly2)
 BC_PROGRAMS = [BC_2D_POLY, BC_2D_TRIG, BC_3D_POLY, BC_3D_TRIG]
 
 # Testing/Opts/{base,tempBlock}.exa4 with the seq_* knowledge files (one fragment, levels 0-6) and
@@ -174,19 +176,20 @@ def _opts_init_seq(shape):
 
 
 def _opts_init_par(shape):
-    """Every MPI rank draws the same rand() sequence for its own loop points (256 per dimension: the interface node is
-    looped over by both neighbours); the first `communicate` then copies the lower block's value onto the shared
-    node (C/s/e/communication/ir/IR_PackInfoDuplicate.scala:15-39) => the lower block wins on every interface."""
+    """Every MPI rank draws the same rand() sequence for its own loop points, then `apply bc` resets the physical
+    boundary and the first `communicate` copies the lower block's value onto the shared nodes
+    (C/s/e/communication/ir/IR_PackInfoDuplicate.scala:15-39).  Pinned empirically by par.results: the sequence
+    covers ALL 257 local nodes per dimension (boundary nodes included) -- that reproduces all seven printed values,
+    256 loop points per dimension (interface included, boundary excluded) gives 2.161e+04 / 257.2 / ... instead."""
     from oracle import oracle as og
     nz, ny, nx = shape  # interior of the 513^3 global grid: 511 per dimension
-    m = (nx + 1) // 2   # 256 loop points per block and dimension
+    m = (nx + 1) // 2 + 1   # 257 local nodes per block and dimension
     r = og.glibc_rand(m ** 3).reshape((m, m, m))
     g = np.zeros((nz + 2, ny + 2, nx + 2))
     for bz in (1, 0):
         for by in (1, 0):
             for bx in (1, 0):
-                # block 0 loops over local nodes 1..m (global 1..m), block 1 over local 0..m-1 (global m..2m-1)
-                z0, y0, x0 = (1 if bz == 0 else m), (1 if by == 0 else m), (1 if bx == 0 else m)
+                z0, y0, x0 = bz * (m - 1), by * (m - 1), bx * (m - 1)
                 g[z0:z0 + m, y0:y0 + m, x0:x0 + m] = r
     return g[1:-1, 1:-1, 1:-1]
 

@@ -40,3 +40,14 @@ def test_stencil_field_blocks(world, blocks, level):
            "--level", str(level), "--cycles", "3", "--blocks", blocks, "--op", "varcoeff27", "--smoother", "jacobi"]
     out = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
     assert out.returncode == 0 and "MGPU PARITY OK" in out.stdout, out.stdout[-3000:] + out.stderr[-3000:]
+
+
+def test_large_hybrid_golden():
+    """Testing/Large/Hybrid: 2560 x 1024 x 2048 cells (5.4e9 unknowns) on 4 GPUs must print the reference's golden
+    stdout (the oracle cannot hold this size; the golden vector comes from the reference's 4 x 10-way hybrid run)."""
+    if _ngpus() < 4:
+        pytest.skip("needs 4 GPUs")
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "4",
+           "--master-addr", "127.0.0.1", "--master-port", "29741", os.path.join(ROOT, "tests", "mgpu", "large_worker.py")]
+    out = subprocess.run(cmd, capture_output=True, text=True, timeout=900)
+    assert out.returncode == 0 and "LARGE GOLDEN OK" in out.stdout, out.stdout[-3000:] + out.stderr[-3000:]

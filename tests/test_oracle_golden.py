@@ -21,14 +21,15 @@ def _run(prog, og):
 
 
 @pytest.mark.parametrize("prog", [programs.POISSON_2D, programs.SISC_2D_CONST, programs.SISC_2D_VAR,
-                                  programs.BC_2D_POLY, programs.BC_2D_TRIG], ids=lambda p: p.name)
+                                  programs.BC_2D_POLY, programs.BC_2D_TRIG, programs.COMMBASIC_2D], ids=lambda p: p.name)
 def test_golden_2d(prog, oracle):
     assert _run(prog, oracle) == prog.expected()
 
 
 @pytest.mark.slow
 @pytest.mark.parametrize("prog", [programs.SMOOTHERS_RBGS, programs.SMOOTHERS_JAC, programs.SISC_3D_CONST,
-                                  programs.SISC_3D_VAR, programs.BC_3D_POLY, programs.BC_3D_TRIG], ids=lambda p: p.name)
+                                  programs.SISC_3D_VAR, programs.BC_3D_POLY, programs.BC_3D_TRIG, programs.OPTS_SEQ,
+                                  programs.OPTS_PAR], ids=lambda p: p.name)
 def test_golden_3d(prog, oracle):
     assert _run(prog, oracle) == prog.expected()
 
