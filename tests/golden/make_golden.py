@@ -24,6 +24,10 @@ FILES = {
     "Opts_seq": "Testing/Opts/seq.results",
     "Opts_par": "Testing/Opts/par.results",
     "CommBasic_2D": "Testing/CommBasic/2D.results",
+    "FMG_2D_ConstCoeff": "Testing/FMG/2D_ConstCoeff.results",
+    "FMG_2D_Polynomial": "Testing/FMG/2D_Polynomial.results",
+    "FMG_3D_Trigonometric": "Testing/FMG/3D_Trigonometric.results",
+    "FMG_3D_VarCoeff": "Testing/FMG/3D_VarCoeff.results",
     "Large_Hybrid": "Testing/Large/Hybrid.results",
     "Application_OpticalFlow2D": "Testing/Application/OpticalFlow2D.results",
     "BC_2D_Polynomial": "Testing/BC/2D_Polynomial.results",

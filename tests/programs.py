@@ -48,8 +48,8 @@ class Program:
     """One reference test program."""
 
     def __init__(self, name, golden_name, cfg, rhs=None, bc=None, exact=None, init=None,
-                 tol=1e-5, strict=True, prints="res", print_count=True, max_it=100):
-        self.name, self.golden_name, self.cfg = name, golden_name, cfg
+                 tol=1e-5, strict=True, prints="res", print_count=True, max_it=100, fmg=False):
+        self.name, self.golden_name, self.cfg, self.fmg = name, golden_name, cfg, fmg
         self.rhs, self.bc, self.exact, self.init = rhs, bc, exact, init
         self.tol, self.strict, self.prints, self.print_count, self.max_it = tol, strict, prints, print_count, max_it
 
@@ -210,7 +210,69 @@ CONFIG3_VARCOEFF27 = Program(
     rhs=_rhs3, bc=lambda X, Y, Z: 1.0 - np.exp((-1.0 * KAPPA) * _b3(X, Y, Z)),
     exact=lambda X, Y, Z: 1.0 - np.exp((-1.0 * KAPPA) * _b3(X, Y, Z)), prints="res")
 
+# Testing/FMG/*.{exa4,knowledge}: the SISC / BC programs (scaled stencils, restriction unscaled) started by a full
+# multigrid sweep from the coarsest level
+FMG_2D_CONST = Program("FMG_2D_ConstCoeff", "FMG_2D_ConstCoeff", SISC_2D_CONST.cfg, rhs=_rhs2, bc=SISC_2D_CONST.bc,
+                       exact=SISC_2D_CONST.exact, prints="err", fmg=True)
+FMG_3D_VAR = Program("FMG_3D_VarCoeff", "FMG_3D_VarCoeff", SISC_3D_VAR.cfg, rhs=_rhs3, bc=SISC_3D_VAR.bc,
+                     exact=SISC_3D_VAR.exact, prints="err", fmg=True)
+FMG_2D_POLY = Program("FMG_2D_Polynomial", "FMG_2D_Polynomial", dict(_BC_CFG2, op="scaled", restrict_scale=1.0),
+                      bc=_poly2, exact=_poly2, prints="err", fmg=True)
+FMG_3D_TRIG = Program("FMG_3D_Trigonometric", "FMG_3D_Trigonometric", dict(_BC_CFG3, op="scaled", restrict_scale=1.0),
+                      bc=_trig3, exact=_trig3, prints="err", fmg=True)
+FMG_PROGRAMS = [FMG_2D_CONST, FMG_2D_POLY, FMG_3D_TRIG, FMG_3D_VAR]
+
 ALL = [POISSON_2D, SMOOTHERS_RBGS, SMOOTHERS_JAC, SISC_3D_CONST, SISC_3D_VAR, SISC_2D_CONST, SISC_2D_VAR]
+
+
+# ---- full multigrid start-up (Testing/FMG/*.exa4: Function FMG@(all but finest)) -------------------------------
+def _is_gpu(solver):
+    return hasattr(solver, "ctx")
+
+
+def _put_solution(solver, lvl, arr):
+    """Solution<0>@lvl and Solution<1>@lvl := arr (the interior of the non-active slot is dead data)."""
+    if _is_gpu(solver):
+        from exastencils_b200 import runtime as rt
+        f = solver.f_solution[lvl]
+        for slot in range(rt.check(solver.ctx.L.examg_field_num_slots(solver.ctx.h, f))):
+            solver.ctx.upload(f, arr, slot)
+    else:
+        solver.solution(lvl)[...] = arr
+        solver.sync_slots()
+
+
+def _get_solution(solver, lvl):
+    return solver.fetch_solution(lvl) if _is_gpu(solver) else solver.solution(lvl).copy()
+
+
+def run_fmg(prog, solver):
+    """FMG@coarsest: on every level below the finest, coarsest first: SetFuncDir (analytic Dirichlet data on the
+    boundary nodes of both slots), InitRHS, VCycle@lvl, Correction@finer (Solution@finer += P * Solution@lvl),
+    ResetBC (the level's declared boundary value 0 again)."""
+    dim = prog.dim
+    for lvl in range(solver.min_level, solver.max_level):
+        X, Y, Z = _grid(solver.node_positions(lvl), dim)
+        u = _get_solution(solver, lvl)
+        _set_boundary(u, prog.bc(X, Y, Z), dim)
+        _put_solution(solver, lvl, u)
+        f = np.zeros_like(u)
+        if prog.rhs is not None:
+            inner = _interior(dim)
+            f[inner] = np.broadcast_to(prog.rhs(X, Y, Z), f.shape)[inner]
+        if _is_gpu(solver):
+            solver.ctx.upload(solver.f_rhs[lvl], f)
+        else:
+            solver.rhs(lvl)[...] = f
+        solver.vcycle(lvl)
+        if _is_gpu(solver):
+            solver.ctx.prolong_add(solver.f_solution[lvl], solver.f_solution[lvl + 1])
+        else:
+            from oracle import oracle as og
+            og.prolong_add(dim, solver.solution(lvl), solver.solution(lvl + 1))
+        u = _get_solution(solver, lvl)
+        _set_boundary(u, np.zeros_like(u), dim)
+        _put_solution(solver, lvl, u)
 
 
 def run_solve(prog, solver, printer, max_abs_err=None):
@@ -224,6 +286,8 @@ def run_solve(prog, solver, printer, max_abs_err=None):
     init_res = solver.update_residual_norm()
     out.append(printer(init_res))
     res = init_res
+    if prog.fmg:
+        run_fmg(prog, solver)
     it = 0
     while not (it >= prog.max_it or prog.converged(res, init_res)):
         it += 1

@@ -42,7 +42,8 @@ def _setup_pair(prog, mode, **override):
 @pytest.mark.parametrize("mode", ["library", "calls"])
 @pytest.mark.parametrize("prog", [programs.POISSON_2D, programs.SISC_2D_CONST, programs.SISC_2D_VAR,
                                   programs.SMOOTHERS_RBGS, programs.SMOOTHERS_JAC, programs.BC_2D_POLY,
-                                  programs.BC_2D_TRIG, programs.COMMBASIC_2D], ids=lambda p: p.name)
+                                  programs.BC_2D_TRIG, programs.COMMBASIC_2D, programs.FMG_2D_CONST,
+                                  programs.FMG_2D_POLY], ids=lambda p: p.name)
 def test_golden_stdout(prog, mode, oracle):
     """Same printed history as the reference's .results file."""
     if mode == "calls" and prog.dim == 3:
@@ -61,7 +62,8 @@ def test_golden_stdout(prog, mode, oracle):
 
 
 @pytest.mark.parametrize("prog", [programs.SISC_3D_CONST, programs.SISC_3D_VAR, programs.BC_3D_POLY,
-                                  programs.BC_3D_TRIG, programs.OPTS_SEQ, programs.OPTS_PAR], ids=lambda p: p.name)
+                                  programs.BC_3D_TRIG, programs.OPTS_SEQ, programs.OPTS_PAR, programs.FMG_3D_TRIG,
+                                  programs.FMG_3D_VAR], ids=lambda p: p.name)
 def test_golden_stdout_3d_sisc(prog, oracle):
     """256^3-cell programs: Testing/SISC (the reference's own CUDA target is tested on these) and Testing/BC
     (polynomial and sin*sin*sinh Dirichlet data); Testing/Opts seq (65^3) and par (513^3 nodes: three Jacobi sweeps
