@@ -24,6 +24,14 @@ FILES = {
     "Opts_seq": "Testing/Opts/seq.results",
     "Opts_par": "Testing/Opts/par.results",
     "CommBasic_2D": "Testing/CommBasic/2D.results",
+    "CommBasic_PureMPI": "Testing/CommBasic/PureMPI.results",
+    "CommBasic_PureOMP": "Testing/CommBasic/PureOMP.results",
+    "CommBasic_Hybrid": "Testing/CommBasic/Hybrid.results",
+    "CommBasic_Strategy26": "Testing/CommBasic/Strategy26.results",
+    "CommBasic_Summarize": "Testing/CommBasic/Summarize.results",
+    "Poisson_2D_FD_Poisson_fromL2": "Testing/Poisson/2D_FD_Poisson_fromL2.results",
+    "Poisson_2D_FD_Poisson_fromL3": "Testing/Poisson/2D_FD_Poisson_fromL3.results",
+    "CUDA_2D_VarCoeff": "Testing/CUDA/2D_VarCoeff.results",
     "FMG_2D_ConstCoeff": "Testing/FMG/2D_ConstCoeff.results",
     "FMG_2D_Polynomial": "Testing/FMG/2D_Polynomial.results",
     "FMG_3D_Trigonometric": "Testing/FMG/3D_Trigonometric.results",

@@ -111,6 +111,11 @@ SMOOTHERS_JAC = Program(
          omega=0.8, nu_pre=3, nu_post=3, restrict_scale=4.0, cg_max_it=512, cg_rel_tol=1e-3),
     bc=_quad_bc)
 
+# Testing/CommBasic/{PureMPI,PureOMP}: the Jac program on 3x3x3 blocks (or fragments) of one fragment => F=3.
+# CommBasic/{Hybrid,Strategy26,Summarize}.results are byte-identical to Smoothers/Jac.results (same program, other
+# communication strategies), see tests/test_oracle_golden.py::test_identical_golden_files.
+COMMBASIC_PURE = Program("CommBasic_PureMPI", "CommBasic_PureMPI", dict(SMOOTHERS_JAC.cfg, F=(3, 3, 3)), bc=_quad_bc)
+
 KAPPA = 10.0
 _b3 = lambda X, Y, Z: ((X - X ** 2) * (Y - Y ** 2)) * (Z - Z ** 2)
 _b2 = lambda X, Y, Z: (X - X ** 2) * (Y - Y ** 2)

@@ -41,7 +41,8 @@ def _setup_pair(prog, mode, **override):
 
 @pytest.mark.parametrize("mode", ["library", "calls"])
 @pytest.mark.parametrize("prog", [programs.POISSON_2D, programs.SISC_2D_CONST, programs.SISC_2D_VAR,
-                                  programs.SMOOTHERS_RBGS, programs.SMOOTHERS_JAC, programs.BC_2D_POLY,
+                                  programs.SMOOTHERS_RBGS, programs.SMOOTHERS_JAC, programs.COMMBASIC_PURE,
+                                  programs.BC_2D_POLY,
                                   programs.BC_2D_TRIG, programs.COMMBASIC_2D, programs.FMG_2D_CONST,
                                   programs.FMG_2D_POLY], ids=lambda p: p.name)
 def test_golden_stdout(prog, mode, oracle):
