@@ -256,8 +256,9 @@ class MultigridProgram:
                     ctx.apply_bc(u)
         else:
             for _ in range(n):
-                ctx.smooth_jacobi(A, u, f, self.omega, 1)  # communicate; loop; advance
-                ctx.apply_bc(u)
+                # communicate ghost; loop; advance -- no `apply bc` in the Jacobi programs (Testing/SISC, Testing/Smoothers/Jac,
+                # Testing/FMG: their FMG start-up relies on the boundary nodes keeping what SetFuncDir wrote)
+                ctx.smooth_jacobi(A, u, f, self.omega, 1)
 
     def mgCycle(self, lvl):
         ctx = self.ctx
@@ -274,7 +275,8 @@ class MultigridProgram:
         self.mgCycle(lvl - 1)
         ctx.exchange(self.f_solution[lvl - 1])
         ctx.prolong_add(self.f_solution[lvl - 1], self.f_solution[lvl])
-        ctx.apply_bc(self.f_solution[lvl])
+        if self.smoother == "rbgs":  # Benchmark/Poisson3D/3D_FD_Poisson_fromL4.exa4:233-237
+            ctx.apply_bc(self.f_solution[lvl])
         self.Smoother(lvl, self.nu_post)
 
     def vcycle(self, lvl=None):
