@@ -21,9 +21,30 @@ static inline size_t og_size(const int n[3]) {
   return (size_t)n[0] * (size_t)n[1] * (size_t)n[2];
 }
 
-/* interior range of dimension d: 1..n-2, or the single plane 0 if n == 1 (2D) */
+/* domain_rect_periodic_{x,y,z} (Knowledge; Testing/BC/{2D,3D}_Periodic.knowledge).  In a periodic dimension the
+ * first and the last node are the same point: the boundary fragments are each other's neighbours, so loops cover
+ * both copies (iteration offsets 0, C/s/e/domain/ir/IR_ConnectFragments.scala:60-93), reductions count the point
+ * once (i >= numDupLeft, C/s/e/baseExt/ir/IR_LoopOverPointsInOneFragment.scala:116-125), and a stencil leaving the
+ * array on one side continues one node inside the other (`communicate ghost`).  Process-wide switch of the oracle. */
+static int og_per[3] = {0, 0, 0};
+void og_set_periodic(const int per[3]) { for (int d = 0; d < 3; ++d) og_per[d] = per[d]; }
+static inline int og_per_any(void) { return og_per[0] | og_per[1] | og_per[2]; }
+
+/* loop range of dimension d: 1..n-2 (0..n-1 if periodic), or the single plane 0 if n == 1 (2D) */
 static inline void og_range(const int n[3], int d, int *lo, int *hi) {
-  if (n[d] == 1) { *lo = 0; *hi = 1; } else { *lo = 1; *hi = n[d] - 1; }
+  if (n[d] == 1) { *lo = 0; *hi = 1; }
+  else if (og_per[d]) { *lo = 0; *hi = n[d]; }
+  else { *lo = 1; *hi = n[d] - 1; }
+}
+/* reductions: a periodic dimension counts its duplicated point once */
+static inline void og_range_red(const int n[3], int d, int *lo, int *hi) {
+  og_range(n, d, lo, hi);
+  if (n[d] > 1 && og_per[d]) *lo = 1;
+}
+/* neighbour index in dimension d with the periodic continuation */
+static inline int og_wrap(const int n[3], int d, int i) {
+  if (n[d] > 1 && og_per[d]) { if (i < 0) return n[d] - 2 - (-1 - i); if (i > n[d] - 1) return i - (n[d] - 1); }
+  return i;
 }
 
 /* linear offsets of the stencil entries */
@@ -58,6 +79,27 @@ static inline double og_conv(int nst, const ptrdiff_t *lo, const double *c,
   return acc;
 }
 
+/* the same fold at a node on a periodic boundary: neighbours by wrapped coordinates */
+static double og_conv_wrap(const int n[3], const og_stencil *st, const double *sf, size_t size, const double *u,
+                           int i, int j, int k) {
+  const size_t p = (size_t)i + (size_t)n[0] * ((size_t)j + (size_t)n[1] * (size_t)k);
+  double acc = 0.0;
+  for (int e = 0; e < st->nst; ++e) {
+    const int ii = og_wrap(n, 0, i + st->off[e][0]), jj = og_wrap(n, 1, j + st->off[e][1]),
+              kk = og_wrap(n, 2, k + st->off[e][2]);
+    const double v = u[(size_t)ii + (size_t)n[0] * ((size_t)jj + (size_t)n[1] * (size_t)kk)];
+    const double c = sf ? sf[(size_t)e * size + p] : st->coef[e];
+    acc = e == 0 ? c * v : fma(c, v, acc);
+  }
+  return acc;
+}
+static inline int og_on_per_boundary(const int n[3], int i, int j, int k) {
+  return (og_per[0] && n[0] > 1 && (i == 0 || i == n[0] - 1)) || (og_per[1] && n[1] > 1 && (j == 0 || j == n[1] - 1)) ||
+         (og_per[2] && n[2] > 1 && (k == 0 || k == n[2] - 1));
+}
+#define OG_CONV(i, j, k, p) \
+  (og_on_per_boundary(n, i, j, k) ? og_conv_wrap(n, st, sf, size, u, i, j, k) : og_conv(nst, lo, st->coef, sf, size, u, p))
+
 #define OG_LOOP_BEGIN(n)                                         \
   int xl, xh, yl, yh, zl, zh;                                    \
   og_range(n, 0, &xl, &xh);                                      \
@@ -80,7 +122,7 @@ void og_apply(const int n[3], const og_stencil *st, const double *sf,
     for (int j = yl; j < yh; ++j) {
       size_t row = (size_t)n[0] * ((size_t)j + (size_t)n[1] * (size_t)k);
       for (int i = xl; i < xh; ++i)
-        out[row + i] = og_conv(nst, lo, st->coef, sf, size, u, row + i);
+        out[row + i] = OG_CONV(i, j, k, row + i);
     }
 }
 
@@ -96,7 +138,7 @@ void og_residual(const int n[3], const og_stencil *st, const double *sf,
     for (int j = yl; j < yh; ++j) {
       size_t row = (size_t)n[0] * ((size_t)j + (size_t)n[1] * (size_t)k);
       for (int i = xl; i < xh; ++i)
-        res[row + i] = rhs[row + i] - og_conv(nst, lo, st->coef, sf, size, u, row + i);
+        res[row + i] = rhs[row + i] - OG_CONV(i, j, k, row + i);
     }
 }
 
@@ -117,7 +159,7 @@ void og_smooth_jacobi(const int n[3], const og_stencil *st, const double *sf,
       for (int i = xl; i < xh; ++i) {
         size_t p = row + i;
         double w = sf ? omega / sf[(size_t)c * size + p] : wconst;
-        double r = rhs[p] - og_conv(nst, lo, st->coef, sf, size, u, p);
+        double r = rhs[p] - OG_CONV(i, j, k, p);
         unext[p] = fma(w, r, u[p]);
       }
     }
@@ -141,7 +183,7 @@ void og_smooth_rb(const int n[3], const og_stencil *st, const double *sf,
       for (int i = i0; i < xh; i += 2) {
         size_t p = row + i;
         double w = sf ? omega / sf[(size_t)c * size + p] : wconst;
-        double r = rhs[p] - og_conv(nst, lo, st->coef, sf, size, u, p);
+        double r = rhs[p] - OG_CONV(i, j, k, p);
         u[p] = fma(w, r, u[p]);
       }
     }
@@ -166,7 +208,10 @@ static inline void og_dd_merge(og_dd *a, const og_dd *b) {
 }
 
 double og_dot(const int n[3], const double *a, const double *b) {
-  OG_LOOP_BEGIN(n)
+  int xl, xh, yl, yh, zl, zh;
+  og_range_red(n, 0, &xl, &xh);
+  og_range_red(n, 1, &yl, &yh);
+  og_range_red(n, 2, &zl, &zh);
   og_dd total = {0.0, 0.0};
 #pragma omp parallel
   {
@@ -230,9 +275,9 @@ void og_restrict(int dim, const int nf[3], const int nc[3], double scale,
           for (int dy = -1; dy <= 1; ++dy)
             for (int dx = -1; dx <= 1; ++dx) {
               int m = (dx != 0) + (dy != 0) + (dz != 0);
-              size_t q = (size_t)(2 * i + dx) +
-                         (size_t)nf[0] * ((size_t)(2 * j + dy) +
-                                          (size_t)nf[1] * (size_t)((dim == 3 ? 2 * k : 0) + dz));
+              size_t q = (size_t)og_wrap(nf, 0, 2 * i + dx) +
+                         (size_t)nf[0] * ((size_t)og_wrap(nf, 1, 2 * j + dy) +
+                                          (size_t)nf[1] * (size_t)og_wrap(nf, 2, (dim == 3 ? 2 * k : 0) + dz));
               if (first[m]) { S[m] = rf[q]; first[m] = 0; } else S[m] += rf[q];
             }
         double acc = w[0] * S[0];

@@ -82,6 +82,8 @@ double og_dot(const int n[3], const double *a, const double *b);
 
 /* max |a - b| over interior nodes (PrintError, Examples/Poisson/2D_FD_Poisson_fromL4.exa4) */
 double og_max_abs_diff(const int n[3], const double *a, const double *b);
+/* domain_rect_periodic_{x,y,z}: process-wide switch, see examg_oracle.c */
+void og_set_periodic(const int per[3]);
 /* out[i] = (double)rand()/RAND_MAX, i = 0..n-1, after srand(1): what `native("((double)std::rand()/RAND_MAX)")` in a
  * `loop ... sequentially` yields in a fresh process (Testing/Opts/base.exa4:167-169; glibc's rand) */
 void og_glibc_rand_fill(double *out, long long n);

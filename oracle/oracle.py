@@ -78,6 +78,8 @@ def lib():
     L.og_dot.restype = C.c_double
     L.og_max_abs_diff.argtypes = [i3, dp, dp]
     L.og_max_abs_diff.restype = C.c_double
+    L.og_set_periodic.argtypes = [i3]
+    L.og_set_periodic.restype = None
     L.og_glibc_rand_fill.argtypes = [dp, C.c_longlong]
     L.og_glibc_rand_fill.restype = None
     L.og_restrict.argtypes = [C.c_int, i3, i3, C.c_double, dp, dp]
@@ -148,6 +150,12 @@ def smooth_rb(st, omega, u, rhs, color, sf=None):
 
 def dot(a, b):
     return lib().og_dot(_n(a), _dp(a), _dp(b))
+
+
+def set_periodic(per=(0, 0, 0)):
+    """domain_rect_periodic_{x,y,z}: process-wide switch of the oracle's loops (examg_oracle.c)."""
+    per = list(per) + [0] * (3 - len(per))
+    lib().og_set_periodic((C.c_int * 3)(*[int(bool(v)) for v in per]))
 
 
 def glibc_rand(n):

@@ -41,6 +41,8 @@ FILES = {
     "BC_2D_Polynomial": "Testing/BC/2D_Polynomial.results",
     "BC_2D_Trigonometric": "Testing/BC/2D_Trigonometric.results",
     "BC_3D_Polynomial": "Testing/BC/3D_Polynomial.results",
+    "BC_2D_Periodic": "Testing/BC/2D_Periodic.results",
+    "BC_3D_Periodic": "Testing/BC/3D_Periodic.results",
     "BC_3D_Trigonometric": "Testing/BC/3D_Trigonometric.results",
 }
 

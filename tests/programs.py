@@ -27,21 +27,29 @@ def _grid(pos, dim):
     return X, Y, Z
 
 
-def _set_boundary(u, vals, dim):
+def _set_boundary(u, vals, dim, periodic=(0, 0, 0)):
     """`apply bc`: Dirichlet value on physical-boundary nodes only
-    (C/s/e/boundary/ir/IR_DirichletBC.scala:37-40)."""
+    (C/s/e/boundary/ir/IR_DirichletBC.scala:37-40); a periodic dimension has no physical boundary."""
     vals = np.broadcast_to(vals, u.shape)
-    u[:, :, 0] = vals[:, :, 0]
-    u[:, :, -1] = vals[:, :, -1]
-    u[:, 0, :] = vals[:, 0, :]
-    u[:, -1, :] = vals[:, -1, :]
-    if dim == 3:
+    per = list(periodic) + [0] * (3 - len(periodic))
+    if not per[0]:
+        u[:, :, 0] = vals[:, :, 0]
+        u[:, :, -1] = vals[:, :, -1]
+    if not per[1]:
+        u[:, 0, :] = vals[:, 0, :]
+        u[:, -1, :] = vals[:, -1, :]
+    if dim == 3 and not per[2]:
         u[0, :, :] = vals[0, :, :]
         u[-1, :, :] = vals[-1, :, :]
 
 
-def _interior(dim):
-    return (slice(1, -1),) * 3 if dim == 3 else (slice(None), slice(1, -1), slice(1, -1))
+def _interior(dim, periodic=(0, 0, 0)):
+    """Loop points of `loop over F`: boundary nodes excluded, except in periodic dimensions."""
+    per = list(periodic) + [0] * (3 - len(periodic))
+    sl = [slice(None) if per[d] else slice(1, -1) for d in (2, 1, 0)]  # (z, y, x)
+    if dim == 2:
+        sl[0] = slice(None)
+    return tuple(sl)
 
 
 class Program:
@@ -67,13 +75,14 @@ class Program:
         X, Y, Z = _grid(solver.node_positions(lvl), self.dim)
         u = solver.solution(lvl)
         f = solver.rhs(lvl)
-        inner = _interior(self.dim)
+        per = self.cfg.get("periodic", (0, 0, 0))
+        inner = _interior(self.dim, per)
         if self.rhs is not None:
             f[inner] = np.broadcast_to(self.rhs(X, Y, Z), f.shape)[inner]
         if self.init is not None:
             u[inner] = self.init(u[inner].shape)
         if self.bc is not None:
-            _set_boundary(u, self.bc(X, Y, Z), self.dim)
+            _set_boundary(u, self.bc(X, Y, Z), self.dim, per)
         self._exact = None
         if self.exact is not None:
             self._exact = np.ascontiguousarray(np.broadcast_to(self.exact(X, Y, Z), u.shape))
@@ -168,6 +177,15 @@ BC_3D_POLY = Program("BC_3D_Polynomial", "BC_3D_Polynomial", _BC_CFG3, bc=_quad_
 BC_3D_TRIG = Program("BC_3D_Trigonometric", "BC_3D_Trigonometric", _BC_CFG3, bc=_trig3, exact=_trig3, prints="err")
 # Testing/CommBasic/2D.{exa4,knowledge}: the same 2D cycle on 3x3 blocks x 3x3 fragments (F=9), prints the residual
 COMMBASIC_2D = Program("CommBasic_2D", "CommBasic_2D", dict(_BC_CFG2, F=(9, 9)), bc=_poly2)
+# Testing/BC/{2D,3D}_Periodic: Dirichlet data x^2 in x, periodic in y (domain_rect_periodic_y), RHS = -2, scaled stencil
+BC_2D_PERIODIC = Program("BC_2D_Periodic", "BC_2D_Periodic",
+                         dict(_BC_CFG2, op="scaled", restrict_scale=1.0, periodic=(0, 1, 0)),
+                         rhs=lambda X, Y, Z: -2.0 + 0.0 * (X + Y + Z), bc=lambda X, Y, Z: X * X + 0.0 * (Y + Z),
+                         exact=lambda X, Y, Z: X * X + 0.0 * (Y + Z), prints="err")
+BC_3D_PERIODIC = Program("BC_3D_Periodic", "BC_3D_Periodic",
+                         dict(_BC_CFG3, op="scaled", restrict_scale=1.0, periodic=(0, 1, 1)),
+                         rhs=lambda X, Y, Z: -2.0 + 0.0 * (X + Y + Z), bc=lambda X, Y, Z: X * X + 0.0 * (Y + Z),
+                         exact=lambda X, Y, Z: X * X + 0.0 * (Y + Z), prints="err")
 BC_PROGRAMS = [BC_2D_POLY, BC_2D_TRIG, BC_3D_POLY, BC_3D_TRIG]
 
 # Testing/Opts/{base,tempBlock}.exa4 with the seq_* knowledge files (one fragment, levels 0-6) and

@@ -22,7 +22,8 @@ def _run(prog, og):
 
 @pytest.mark.parametrize("prog", [programs.POISSON_2D, programs.SISC_2D_CONST, programs.SISC_2D_VAR,
                                   programs.BC_2D_POLY, programs.BC_2D_TRIG, programs.COMMBASIC_2D,
-                                  programs.FMG_2D_CONST, programs.FMG_2D_POLY], ids=lambda p: p.name)
+                                  programs.FMG_2D_CONST, programs.FMG_2D_POLY, programs.BC_2D_PERIODIC],
+                         ids=lambda p: p.name)
 def test_golden_2d(prog, oracle):
     assert _run(prog, oracle) == prog.expected()
 
@@ -47,7 +48,8 @@ def test_identical_golden_files():
 @pytest.mark.slow
 @pytest.mark.parametrize("prog", [programs.COMMBASIC_PURE, programs.SMOOTHERS_RBGS, programs.SMOOTHERS_JAC, programs.SISC_3D_CONST,
                                   programs.SISC_3D_VAR, programs.BC_3D_POLY, programs.BC_3D_TRIG, programs.OPTS_SEQ,
-                                  programs.OPTS_PAR, programs.FMG_3D_TRIG, programs.FMG_3D_VAR], ids=lambda p: p.name)
+                                  programs.OPTS_PAR, programs.FMG_3D_TRIG, programs.FMG_3D_VAR,
+                                  programs.BC_3D_PERIODIC], ids=lambda p: p.name)
 def test_golden_3d(prog, oracle):
     assert _run(prog, oracle) == prog.expected()
 
