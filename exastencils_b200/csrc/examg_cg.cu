@@ -34,6 +34,7 @@ int launch_cg(examg_ctx *c, const Stencil &s, double *u, const double *rhs, doub
   a.sfvol = g.vol;
   a.max_it = max_it;
   a.rel_tol = rel_tol;
+  for (int d = 0; d < 3; ++d) a.per[d] = c->per[d] ? 1 : 0;
   if (total <= 0) {
     EXAMG_CUDA(cudaMemsetAsync(c->int_out, 0, sizeof(int), c->stream));
     return EXAMG_OK;

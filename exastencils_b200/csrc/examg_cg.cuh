@@ -12,6 +12,7 @@ struct CgArgs {
   long long sfvol;
   int max_it;
   double rel_tol;
+  int per[3];  // periodic dimensions: the block is its own neighbour (ghost layers refreshed inside the kernel)
 };
 
 template <bool VAR>
@@ -35,6 +36,38 @@ __device__ __forceinline__ long long cg_point(const GridArgs &g, int t, int ex, 
   return i + (long long)g.pitch * j + g.plane * k;
 }
 
+// loop point t counts in reductions (a point shared by the two ends of a periodic dimension counts once)
+__device__ __forceinline__ bool cg_counts(const GridArgs &g, int t, int ex, int ey) {
+  const int i = g.lo[0] + t % ex;
+  const int j = g.lo[1] + (t / ex) % ey;
+  const int k = g.lo[2] + t / (ex * ey);
+  return i >= g.rlo[0] && j >= g.rlo[1] && k >= g.rlo[2];
+}
+
+// `communicate x` of a single periodic block: duplicate + ghost layer on the low side from the high end, ghost layer
+// on the high side from the low end, one dimension after the other over the orthogonal extents incl. ghost layers
+__device__ __forceinline__ void cg_refresh(const CgArgs &a, double *x) {
+  const GridArgs &g = a.g;
+  __syncthreads();
+  for (int d = 0; d < 3; ++d) {
+    if (!a.per[d]) continue;
+    const int da = d == 0 ? 1 : 0, db = d == 2 ? 1 : 2;
+    const int ga = g.n[da] > 1 ? 1 : 0, gb = g.n[db] > 1 ? 1 : 0;
+    const int ea = g.n[da] + 2 * ga, eb = g.n[db] + 2 * gb;
+    const int total = 3 * ea * eb;
+    for (int t = threadIdx.x; t < total; t += blockDim.x) {
+      const int l = t % 3, ia = (t / 3) % ea - ga, ib = t / (3 * ea) - gb;
+      int idx[3], src[3];
+      idx[da] = src[da] = ia;
+      idx[db] = src[db] = ib;
+      idx[d] = l == 0 ? -1 : (l == 1 ? 0 : g.n[d]);
+      src[d] = l == 0 ? g.n[d] - 2 : (l == 1 ? g.n[d] - 1 : 1);
+      x[idx[0] + (long long)g.pitch * idx[1] + g.plane * idx[2]] = x[src[0] + (long long)g.pitch * src[1] + g.plane * src[2]];
+    }
+    __syncthreads();
+  }
+}
+
 // block-wide sum, result broadcast to all threads
 __device__ __forceinline__ double cg_sum(dd part) {
   __shared__ double bc;
@@ -54,16 +87,19 @@ __device__ __forceinline__ int cg_device(const CgArgs &a, const double *__restri
   const int ex = g.hi[0] - g.lo[0], ey = g.hi[1] - g.lo[1], ez = g.hi[2] - g.lo[2];
   const int total = ex * ey * ez;
   const int tid = threadIdx.x, nt = blockDim.x;
+  const bool per = a.per[0] || a.per[1] || a.per[2];
 
   // Residual = RHS - A*Solution; curRes = ||Residual||; cgTmp0 = Residual
+  if (per) cg_refresh(a, u);
   dd part = {0.0, 0.0};
   for (int t = tid; t < total; t += nt) {
     const long long q = cg_point(g, t, ex, ey);
     const double r = rhs[q] - cg_conv<VAR>(a, sf, u, q);
     res[q] = r;
     p[q] = r;
-    dd_add(part, r * r);
+    dd_add(part, !per || cg_counts(g, t, ex, ey) ? r * r : 0.0);
   }
+  if (per) cg_refresh(a, p);
   double curRes = sqrt(cg_sum(part));
   const double initRes = curRes;
   int iters = 0;
@@ -76,8 +112,9 @@ __device__ __forceinline__ int cg_device(const CgArgs &a, const double *__restri
       const double v = cg_conv<VAR>(a, sf, p, q);
       ap[q] = v;
       const double r = res[q];
-      dd_add(pn, r * r);
-      dd_add(pd, p[q] * v);
+      const bool cnt = !per || cg_counts(g, t, ex, ey);
+      dd_add(pn, cnt ? r * r : 0.0);
+      dd_add(pd, cnt ? p[q] * v : 0.0);
     }
     const double alphaNom = cg_sum(pn);
     const double alphaDenom = cg_sum(pd);
@@ -89,7 +126,7 @@ __device__ __forceinline__ int cg_device(const CgArgs &a, const double *__restri
       u[q] = fma(alpha, p[q], u[q]);
       const double r = fma(-alpha, ap[q], res[q]);
       res[q] = r;
-      dd_add(pr, r * r);
+      dd_add(pr, !per || cg_counts(g, t, ex, ey) ? r * r : 0.0);
     }
     const double nextRes = sqrt(cg_sum(pr));
     if (nextRes <= a.rel_tol * initRes) break;
@@ -99,6 +136,7 @@ __device__ __forceinline__ int cg_device(const CgArgs &a, const double *__restri
       p[q] = fma(beta, p[q], res[q]);
     }
     curRes = nextRes;
+    if (per) cg_refresh(a, p);
     __syncthreads();
   }
   return iters;

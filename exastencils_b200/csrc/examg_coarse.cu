@@ -158,6 +158,7 @@ __global__ void __launch_bounds__(1024, 1) k_coarse_cycle(const __grid_constant_
       ca.sfvol = 0;
       ca.max_it = a.cg_max_it;
       ca.rel_tol = a.cg_rel_tol;
+      ca.per[0] = ca.per[1] = ca.per[2] = 0;  // periodic contexts do not use this kernel (coarse_cycle_top)
     }
     __syncthreads();
     const int iters = cg_device<false>(ca, nullptr, sm + L.su[cur[0]], sm + L.sf, sm + L.sr, sm + a.sp, sm + a.sap);
@@ -216,7 +217,7 @@ int coarse_cycle_top(examg_ctx *c, const examg_cycle_desc &d, const int *stencil
   // benchmark against ~55 us for the same levels as nodes of the cycle's CUDA graph (profiles/r01_notes.md).
   static const bool off = !(getenv("EXAMG_COARSE_FUSE") && getenv("EXAMG_COARSE_FUSE")[0] == '1');
   const int lo = c->cfg.min_level;
-  if (off || c->world > 1) return lo - 1;
+  if (off || c->world > 1 || c->periodic_any) return lo - 1;
   int top = lo - 1;
   for (int lvl = lo; lvl <= max_top && lvl - lo < CMAXL; ++lvl) {
     const Stencil &s = c->stencils[stencils[lvl - lo]];

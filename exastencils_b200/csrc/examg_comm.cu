@@ -353,8 +353,71 @@ static double *peer_buffer(examg_ctx *c, int rank, int field, const double *p) {
 
 // One `communicate` of up to two fields (e.g. Solution and RHS in front of a fused sweep): one
 // kernel and one handshake per dimension for all of them.
+// `communicate` across a periodic boundary of a single block: the block is its own neighbour, so the face copies of
+// k_exchange_dim become copies inside one array -- duplicate + ghost layers on the low side from the high end
+// (the + neighbour's layers n-1-G..n-1 -> -G..0), ghost layers on the high side from the low end (1..G -> n..n+G-1),
+// over the orthogonal extents including ghost layers, one dimension after the other.
+struct SelfExchArgs {
+  int n[3];
+  int d, depth, gw[3];
+  int pitch;
+  long long plane;
+};
+
+__global__ void __launch_bounds__(256) k_self_exchange(const SelfExchArgs a, double *f) {
+  const int G = a.depth, d = a.d;
+  const int da = d == 0 ? 1 : 0, db = d == 2 ? 1 : 2;
+  const int ea = a.n[da] + 2 * a.gw[da], eb = a.n[db] + 2 * a.gw[db];
+  const int layers = 2 * G + 1;
+  const long long total = (long long)layers * ea * eb;
+  for (long long t = blockIdx.x * (long long)blockDim.x + threadIdx.x; t < total; t += (long long)gridDim.x * blockDim.x) {
+    // the fastest index runs along x whenever x is not the exchanged dimension
+    int l, ia, ib;
+    if (d == 0) { l = (int)(t % layers); ia = (int)((t / layers) % ea); ib = (int)(t / ((long long)layers * ea)); }
+    else { ia = (int)(t % ea); l = (int)((t / ea) % layers); ib = (int)(t / ((long long)ea * layers)); }
+    int idx[3], src[3];
+    idx[da] = src[da] = ia - a.gw[da];
+    idx[db] = src[db] = ib - a.gw[db];
+    if (l <= G) { idx[d] = l - G; src[d] = a.n[d] - 1 - G + l; }  // -G..0  <-  n-1-G..n-1
+    else { idx[d] = a.n[d] + (l - G - 1); src[d] = 1 + (l - G - 1); }  // n..n+G-1  <-  1..G
+    f[idx[0] + (long long)a.pitch * idx[1] + a.plane * idx[2]] = f[src[0] + (long long)a.pitch * src[1] + a.plane * src[2]];
+  }
+}
+
+static int self_exchange(examg_ctx *c, Field *const *fs, const int *slots, const int *depths, int nfields) {
+  for (int d = 0; d < c->cfg.dim; ++d) {
+    if (!c->per[d]) continue;
+    for (int q = 0; q < nfields; ++q) {
+      Field &f = *fs[q];
+      const LevelGeom &g = *geom(c, f.level);
+      const int G = depths[q];
+      if (G < 1 || G > GHOST) return set_error(EXAMG_EINVAL, "examg_exchange: depth %d", G);
+      if (g.n[d] - 1 <= 2 * G) return set_error(EXAMG_EUNSUP, "examg_exchange: periodic level with %d cells, depth %d", g.n[d] - 1, G);
+      SelfExchArgs a;
+      for (int w = 0; w < 3; ++w) {
+        a.n[w] = g.n[w];
+        a.gw[w] = w < c->cfg.dim ? G : 0;
+      }
+      a.d = d;
+      a.depth = G;
+      a.pitch = g.pitch;
+      a.plane = g.plane;
+      const int da = d == 0 ? 1 : 0, db = d == 2 ? 1 : 2;
+      const long long total = (long long)(2 * G + 1) * (g.n[da] + 2 * a.gw[da]) * (g.n[db] + 2 * a.gw[db]);
+      int grid = (int)((total + 255) / 256);
+      if (grid > 592) grid = 592;
+      for (int comp = 0; comp < f.ncomp; ++comp) {
+        k_self_exchange<<<grid, 256, 0, c->stream>>>(a, f.slot[slots[q]] + (long long)comp * g.vol + g.origin);
+        EXAMG_LAUNCH_CHECK(c);
+      }
+    }
+  }
+  for (int q = 0; q < nfields; ++q) fs[q]->halo_depth = depths[q];
+  return EXAMG_OK;
+}
+
 int do_exchange_many(examg_ctx *c, Field *const *fs, const int *slots, const int *depths, int nfields) {
-  if (c->world == 1) return EXAMG_OK;  // no neighbour blocks: nothing to exchange
+  if (c->world == 1) return c->periodic_any ? self_exchange(c, fs, slots, depths, nfields) : EXAMG_OK;
   examg_comm *cm = c->comm;
   if (!cm || !cm->wired) return set_error(EXAMG_ESTATE, "examg_exchange: peers not wired (examg_comm_import)");
   for (int d = 0; d < c->cfg.dim; ++d) {

@@ -144,6 +144,16 @@ examg_ctx *examg_init(const examg_config *cfg) {
     r /= nbk;
     c->nb[d][0] = c->bidx[d] > 0;
     c->nb[d][1] = c->bidx[d] < nbk - 1;
+    if (d < cfg->dim && cfg->periodic[d]) {
+      if (nbk != 1) {
+        set_error(EXAMG_EUNSUP, "examg_init: a periodic dimension takes one block so far (num_blocks[%d] = %d)", d, nbk);
+        delete c;
+        return nullptr;
+      }
+      c->nb[d][0] = c->nb[d][1] = true;  // iteration offsets 0 on both sides, C/s/e/domain/ir/IR_ConnectFragments.scala:60-93
+      c->per[d] = true;
+      c->periodic_any = true;
+    }
   }
   for (int lvl = cfg->min_level; lvl <= cfg->max_level; ++lvl) {
     LevelGeom g;
@@ -333,7 +343,8 @@ int examg_field_create(examg_ctx *c, const char *name, int level, int num_slots,
 }
 
 int examg_field_create_cell(examg_ctx *c, const char *name, int level, int num_slots, int ncomp) {
-  if (c && c->world > 1) return set_error(EXAMG_EUNSUP, "examg_field_create_cell: cell fields are single-block so far");
+  if (c && (c->world > 1 || c->periodic_any))
+    return set_error(EXAMG_EUNSUP, "examg_field_create_cell: cell fields are single-block and non-periodic so far");
   return field_create(c, name, level, num_slots, ncomp, 1);
 }
 

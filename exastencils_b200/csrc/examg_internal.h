@@ -127,7 +127,9 @@ struct examg_ctx {
   int device = 0;
   int bidx[3] = {0, 0, 0};  // block index of this rank
   int world = 1;
-  bool nb[3][2];  // neighbour present on the -/+ side of dim d
+  bool nb[3][2];  // neighbour present on the -/+ side of dim d (a periodic dimension: the block itself)
+  bool per[3] = {false, false, false};  // periodic dimension (its only block is its own neighbour)
+  bool periodic_any = false;
   std::vector<examg::LevelGeom> levels;  // index level - min_level
   std::vector<examg::Field> fields;
   std::vector<examg::Stencil> stencils;

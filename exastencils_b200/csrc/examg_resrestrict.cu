@@ -171,7 +171,7 @@ static bool rr_enabled() {
 
 bool residual_restrict_usable(examg_ctx *c, const Stencil &s) {
   if (!rr_enabled() || c->cfg.dim != 3 || !s.is7 || s.coeff_field >= 0 || stencil_order(s) < 0) return false;
-  if (s.level <= c->cfg.min_level) return false;
+  if (s.level <= c->cfg.min_level || c->periodic_any) return false;
   const LevelGeom &g = *geom(c, s.level);
   return g.n[0] >= 65 && g.n[1] >= 65 && g.n[2] >= 65;
 }

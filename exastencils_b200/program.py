@@ -90,7 +90,7 @@ class MultigridProgram:
     def __init__(self, dim, block_cells, min_level, max_level, op="scaled", order="bench", kappa=0.0,
                  smoother="rbgs", omega=0.8, nu_pre=3, nu_post=3, restrict_scale=1.0, cg_max_it=128,
                  cg_rel_tol=1e-3, num_blocks=(1, 1, 1), rank=0, device=0, mode="library", stream=None,
-                 domain_lo=(0.0, 0.0, 0.0), domain_hi=(1.0, 1.0, 1.0)):
+                 domain_lo=(0.0, 0.0, 0.0), domain_hi=(1.0, 1.0, 1.0), periodic=(0, 0, 0)):
         assert mode in ("library", "calls")
         self.dim, self.min_level, self.max_level = dim, min_level, max_level
         self.op, self.order, self.kappa = op, order, kappa
@@ -99,7 +99,7 @@ class MultigridProgram:
         self.mode = mode
         # initGlobals / initDomain / setupBuffers
         self.ctx = rt.Context(dim, min_level, max_level, block_cells=block_cells, num_blocks=num_blocks, rank=rank,
-                              device=device, domain_lo=domain_lo, domain_hi=domain_hi)
+                              device=device, domain_lo=domain_lo, domain_hi=domain_hi, periodic=periodic)
         if stream is not None:
             self.ctx.set_stream(stream)
         ctx = self.ctx

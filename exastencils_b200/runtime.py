@@ -33,7 +33,8 @@ class ExaMGError(RuntimeError):
 class Config(C.Structure):
     _fields_ = [("dim", C.c_int), ("min_level", C.c_int), ("max_level", C.c_int),
                 ("block_cells", C.c_int * 3), ("num_blocks", C.c_int * 3), ("rank", C.c_int),
-                ("device", C.c_int), ("domain_lo", C.c_double * 3), ("domain_hi", C.c_double * 3)]
+                ("device", C.c_int), ("domain_lo", C.c_double * 3), ("domain_hi", C.c_double * 3),
+                ("periodic", C.c_int * 3)]
 
 
 class BcOp(C.Structure):
@@ -185,7 +186,7 @@ class Context:
     """One block of the domain on one GPU (initGlobals + initDomain + setupBuffers)."""
 
     def __init__(self, dim, min_level, max_level, block_cells=(1, 1, 1), num_blocks=(1, 1, 1), rank=0, device=0,
-                 domain_lo=(0.0, 0.0, 0.0), domain_hi=(1.0, 1.0, 1.0)):
+                 domain_lo=(0.0, 0.0, 0.0), domain_hi=(1.0, 1.0, 1.0), periodic=(0, 0, 0)):
         cfg = Config()
         cfg.dim, cfg.min_level, cfg.max_level, cfg.rank, cfg.device = dim, min_level, max_level, rank, device
         bc = list(block_cells) + [1] * (3 - len(block_cells))
@@ -193,6 +194,7 @@ class Context:
         for d in range(3):
             cfg.block_cells[d], cfg.num_blocks[d] = bc[d], nb[d]
             cfg.domain_lo[d], cfg.domain_hi[d] = domain_lo[d], domain_hi[d]
+            cfg.periodic[d] = int(bool(periodic[d])) if d < len(periodic) else 0
         self.cfg = cfg
         self.dim, self.min_level, self.max_level = dim, min_level, max_level
         self.L = lib()

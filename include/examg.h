@@ -64,6 +64,9 @@ typedef struct {
   int device;           /* CUDA device ordinal (cuda_deviceId)                     */
   double domain_lo[3];  /* Domain global< lo to hi >                               */
   double domain_hi[3];
+  int periodic[3];      /* domain_rect_periodic_{x,y,z}: the first and the last node of the dimension are the
+                           same point (one block in that dimension so far); loops cover both copies, reductions
+                           count it once, `communicate` continues the field across the boundary             */
 } examg_config;
 
 int examg_abi_version(void);

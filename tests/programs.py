@@ -76,6 +76,8 @@ class Program:
         u = solver.solution(lvl)
         f = solver.rhs(lvl)
         per = self.cfg.get("periodic", (0, 0, 0))
+        from oracle import oracle as og
+        og.set_periodic(per)  # the oracle's loop ranges (also used for NormError on GPU results) are process-wide state
         inner = _interior(self.dim, per)
         if self.rhs is not None:
             f[inner] = np.broadcast_to(self.rhs(X, Y, Z), f.shape)[inner]

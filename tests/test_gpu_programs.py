@@ -23,7 +23,7 @@ def make_gpu_solver(cfg, mode="library", **override):
     return MultigridProgram(c["dim"], tuple(c["F"]), c["min_level"], c["max_level"], op=c["op"], order=c["order"],
                             kappa=c.get("kappa", 0.0), smoother=c["smoother"], omega=c["omega"], nu_pre=c["nu_pre"],
                             nu_post=c["nu_post"], restrict_scale=c["restrict_scale"], cg_max_it=c["cg_max_it"],
-                            cg_rel_tol=c["cg_rel_tol"], mode=mode)
+                            cg_rel_tol=c["cg_rel_tol"], mode=mode, periodic=c.get("periodic", (0, 0, 0)))
 
 
 def _setup_pair(prog, mode, **override):
@@ -44,7 +44,7 @@ def _setup_pair(prog, mode, **override):
                                   programs.SMOOTHERS_RBGS, programs.SMOOTHERS_JAC, programs.COMMBASIC_PURE,
                                   programs.BC_2D_POLY,
                                   programs.BC_2D_TRIG, programs.COMMBASIC_2D, programs.FMG_2D_CONST,
-                                  programs.FMG_2D_POLY], ids=lambda p: p.name)
+                                  programs.FMG_2D_POLY, programs.BC_2D_PERIODIC], ids=lambda p: p.name)
 def test_golden_stdout(prog, mode, oracle):
     """Same printed history as the reference's .results file."""
     if mode == "calls" and prog.dim == 3:
@@ -64,7 +64,7 @@ def test_golden_stdout(prog, mode, oracle):
 
 @pytest.mark.parametrize("prog", [programs.SISC_3D_CONST, programs.SISC_3D_VAR, programs.BC_3D_POLY,
                                   programs.BC_3D_TRIG, programs.OPTS_SEQ, programs.OPTS_PAR, programs.FMG_3D_TRIG,
-                                  programs.FMG_3D_VAR], ids=lambda p: p.name)
+                                  programs.FMG_3D_VAR, programs.BC_3D_PERIODIC], ids=lambda p: p.name)
 def test_golden_stdout_3d_sisc(prog, oracle):
     """256^3-cell programs: Testing/SISC (the reference's own CUDA target is tested on these) and Testing/BC
     (polynomial and sin*sin*sinh Dirichlet data); Testing/Opts seq (65^3) and par (513^3 nodes: three Jacobi sweeps
@@ -96,6 +96,8 @@ SMALL = dict(max_level=4)
     (programs.SISC_3D_VAR, dict(max_level=3)),
     (programs.SMOOTHERS_RBGS, dict(max_level=3, nu_pre=2, nu_post=2, omega=0.8)),   # V(2,2), north-star smoother
     (programs.SMOOTHERS_JAC, dict(max_level=3, nu_pre=2, nu_post=1)),                # odd sweep count: slot parity flips
+    (programs.BC_2D_PERIODIC, dict(max_level=5)),      # domain_rect_periodic_y: self-exchange, wrap inside the device CG
+    (programs.BC_3D_PERIODIC, dict(max_level=3)),      # periodic in y and z
     (programs.CONFIG3_VARCOEFF27, dict(max_level=6)),   # 27-point stencil field, V(2,2): pairs of sweeps fused on 33^3, 65^3
     (programs.CONFIG3_VARCOEFF27, dict(max_level=5, nu_pre=3, nu_post=3)),           # 2 fused + 1 generic sweep
 ], ids=lambda v: v.name if hasattr(v, "name") else "-".join("%s%s" % kv for kv in v.items()))
