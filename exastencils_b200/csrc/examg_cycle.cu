@@ -183,12 +183,19 @@ examg_solver *examg_solver_create(examg_ctx *c, const examg_cycle_desc *d) {
         return nullptr;
       }
   if (c->world > 1) {
-    // agglomeration level: the largest one whose global grid has <= 128 cells per dimension
+    // agglomeration level: the largest one whose global grid has <= 256 cells per dimension and <= 2^21 cells in all
+    // (measured at 8 x 512^3, blocks 1x2x4: gathering level 6 = 64 x 128 x 256 cells onto rank 0 gives 4.66 ms per
+    // step against 4.72 ms with level 5 and 5.41 ms with level 7, profiles/r01_notes.md)
     int T = c->cfg.min_level;
     for (int lvl = c->cfg.min_level; lvl < c->cfg.max_level; ++lvl) {
       bool ok = true;
-      for (int dd = 0; dd < c->cfg.dim; ++dd) ok = ok && ((long long)c->cfg.block_cells[dd] * c->cfg.num_blocks[dd] << lvl) <= 128;
-      if (ok) T = lvl;
+      long long cells = 1;
+      for (int dd = 0; dd < c->cfg.dim; ++dd) {
+        const long long g = (long long)c->cfg.block_cells[dd] * c->cfg.num_blocks[dd] << lvl;
+        ok = ok && g <= 256;
+        cells *= g;
+      }
+      if (ok && cells <= (1LL << 21)) T = lvl;
     }
     if (const char *e = getenv("EXAMG_AGG_LEVEL")) T = atoi(e);
     if (T < c->cfg.min_level || T >= c->cfg.max_level) {
