@@ -358,3 +358,71 @@ void og_xpay(const int n[3], const double *x, double beta, double *y) {
       for (int i = xl; i < xh; ++i) y[row + i] = fma(beta, y[row + i], x[row + i]);
     }
 }
+
+/* ---------- cell-centred fields (the Testing/CellBased programs) ------------------------------------------------
+ * A cell field with one ghost layer is stored as an array of (nc+2)^dim entries -- which is a node array whose
+ * "boundary nodes" are the ghost cells: every loop above (og_apply, og_residual, og_smooth_jacobi, og_dot, og_axpy,
+ * ...) runs over exactly the cells and reads the ghosts through the stencil.  Only the boundary update and the
+ * inter-grid transfer are specific to the localisation.
+ */
+
+/* `apply bc` on a cell field.  kind 1: Dirichlet, ghost = 2 * value - inner cell (order 1,
+ * C/s/e/boundary/ir/IR_DirichletBC.scala:42-50); face values g[f] per ghost cell of face f = 2*d + side in the
+ * face's own lexicographic order, NULL = 0.  kind 2: Neumann(1), ghost = inner cell
+ * (C/s/e/boundary/ir/IR_NeumannBC.scala:70-80).  n = padded extents (cells + 2; 1 for the unused dimension). */
+void og_cell_apply_bc(int dim, const int n[3], double *u, int kind, const double *const g[6]) {
+  for (int d = 0; d < dim; ++d)
+    for (int side = 0; side < 2; ++side) {
+      const int da = d == 0 ? 1 : 0, db = d == 2 ? 1 : 2;
+      const int na = n[da] > 1 ? n[da] - 2 : 1, nb = (db < dim && n[db] > 1) ? n[db] - 2 : 1;
+      const double *gv = g ? g[2 * d + side] : NULL;
+      for (int b = 0; b < nb; ++b)
+        for (int a = 0; a < na; ++a) {
+          int idx[3] = {0, 0, 0}, inner[3];
+          idx[da] = a + 1;
+          if (db < dim) idx[db] = b + 1;
+          idx[d] = side ? n[d] - 1 : 0;
+          inner[0] = idx[0]; inner[1] = idx[1]; inner[2] = idx[2];
+          inner[d] = side ? n[d] - 2 : 1;
+          const size_t pg = (size_t)idx[0] + (size_t)n[0] * ((size_t)idx[1] + (size_t)n[1] * (size_t)idx[2]);
+          const size_t pi = (size_t)inner[0] + (size_t)n[0] * ((size_t)inner[1] + (size_t)n[1] * (size_t)inner[2]);
+          if (kind == 2) u[pg] = u[pi];
+          else u[pg] = (2.0 * (gv ? gv[(size_t)a + (size_t)na * (size_t)b] : 0.0)) - u[pi];
+        }
+    }
+}
+
+/* RHS@coarser = RestrictionCell * Residual: mean of the 2^dim children, summed in lexicographic (z,y,x) order
+ * (C/s/e/operator/l4/L4_DefaultRestriction.scala:40-47); padded extents */
+void og_cell_restrict(int dim, const int nf[3], const int nc[3], const double *rf, double *rc) {
+  const int ncz = dim == 3 ? nc[2] - 2 : 1;
+#pragma omp parallel for schedule(static) collapse(2)
+  for (int k = 0; k < ncz; ++k)
+    for (int j = 0; j < nc[1] - 2; ++j)
+      for (int i = 0; i < nc[0] - 2; ++i) {
+        double s = 0.0;
+        int first = 1;
+        for (int dz = 0; dz <= (dim == 3); ++dz)
+          for (int dy = 0; dy <= 1; ++dy)
+            for (int dx = 0; dx <= 1; ++dx) {
+              const double v = rf[(size_t)(2 * i + dx + 1) +
+                                  (size_t)nf[0] * ((size_t)(2 * j + dy + 1) + (size_t)nf[1] * (size_t)(dim == 3 ? 2 * k + dz + 1 : 0))];
+              if (first) { s = v; first = 0; } else s += v;
+            }
+        rc[(size_t)(i + 1) + (size_t)nc[0] * ((size_t)(j + 1) + (size_t)nc[1] * (size_t)(dim == 3 ? k + 1 : 0))] =
+            ldexp(1.0, -dim) * s;
+      }
+}
+
+/* Solution += CorrectionCell * Solution@coarser: every child takes its parent's value
+ * (transpose of the restriction times 2^dim, C/s/e/operator/l4/L4_DefaultProlongation.scala:30-45) */
+void og_cell_prolong_add(int dim, const int nf[3], const int nc[3], const double *uc, double *uf) {
+  const int nfz = dim == 3 ? nf[2] - 2 : 1;
+#pragma omp parallel for schedule(static) collapse(2)
+  for (int k = 0; k < nfz; ++k)
+    for (int j = 0; j < nf[1] - 2; ++j)
+      for (int i = 0; i < nf[0] - 2; ++i) {
+        const double v = uc[(size_t)(i / 2 + 1) + (size_t)nc[0] * ((size_t)(j / 2 + 1) + (size_t)nc[1] * (size_t)(dim == 3 ? k / 2 + 1 : 0))];
+        uf[(size_t)(i + 1) + (size_t)nf[0] * ((size_t)(j + 1) + (size_t)nf[1] * (size_t)(dim == 3 ? k + 1 : 0))] += v;
+      }
+}

@@ -82,6 +82,10 @@ double og_dot(const int n[3], const double *a, const double *b);
 
 /* max |a - b| over interior nodes (PrintError, Examples/Poisson/2D_FD_Poisson_fromL4.exa4) */
 double og_max_abs_diff(const int n[3], const double *a, const double *b);
+/* cell-centred fields: padded arrays (cells + 2 per dimension), see examg_oracle.c */
+void og_cell_apply_bc(int dim, const int n[3], double *u, int kind, const double *const g[6]);
+void og_cell_restrict(int dim, const int nf[3], const int nc[3], const double *rf, double *rc);
+void og_cell_prolong_add(int dim, const int nf[3], const int nc[3], const double *uc, double *uf);
 /* domain_rect_periodic_{x,y,z}: process-wide switch, see examg_oracle.c */
 void og_set_periodic(const int per[3]);
 /* out[i] = (double)rand()/RAND_MAX, i = 0..n-1, after srand(1): what `native("((double)std::rand()/RAND_MAX)")` in a

@@ -78,6 +78,12 @@ def lib():
     L.og_dot.restype = C.c_double
     L.og_max_abs_diff.argtypes = [i3, dp, dp]
     L.og_max_abs_diff.restype = C.c_double
+    L.og_cell_apply_bc.argtypes = [C.c_int, i3, dp, C.c_int, C.POINTER(dp)]
+    L.og_cell_apply_bc.restype = None
+    L.og_cell_restrict.argtypes = [C.c_int, i3, i3, dp, dp]
+    L.og_cell_restrict.restype = None
+    L.og_cell_prolong_add.argtypes = [C.c_int, i3, i3, dp, dp]
+    L.og_cell_prolong_add.restype = None
     L.og_set_periodic.argtypes = [i3]
     L.og_set_periodic.restype = None
     L.og_glibc_rand_fill.argtypes = [dp, C.c_longlong]
@@ -150,6 +156,37 @@ def smooth_rb(st, omega, u, rhs, color, sf=None):
 
 def dot(a, b):
     return lib().og_dot(_n(a), _dp(a), _dp(b))
+
+
+# ---- cell-centred fields: padded arrays (cells + 2 per dimension); the node loops above run over exactly the cells ----
+BC_CELL_DIRICHLET, BC_CELL_NEUMANN = 1, 2
+
+
+def cell_apply_bc(dim, u, kind, face_values=None):
+    """In place.  face_values: list of 6 arrays (face 2*d + side, the face's cells in lexicographic order) or None = 0."""
+    arr = None
+    keep = []
+    if face_values is not None:
+        arr = (C.POINTER(C.c_double) * 6)()
+        for f in range(6):
+            v = face_values[f] if f < len(face_values) else None
+            if v is not None:
+                v = np.ascontiguousarray(v, dtype=np.float64)
+                keep.append(v)
+                arr[f] = _dp(v)
+    lib().og_cell_apply_bc(dim, _n(u), _dp(u), kind, arr)
+    return u
+
+
+def cell_restrict(dim, rf, coarse_shape):
+    rc = np.zeros(coarse_shape, dtype=np.float64)
+    lib().og_cell_restrict(dim, _n(rf), _n(rc), _dp(rf), _dp(rc))
+    return rc
+
+
+def cell_prolong_add(dim, uc, uf):
+    lib().og_cell_prolong_add(dim, _n(uf), _n(uc), _dp(uc), _dp(uf))
+    return uf
 
 
 def set_periodic(per=(0, 0, 0)):

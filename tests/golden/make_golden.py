@@ -24,6 +24,10 @@ FILES = {
     "Opts_seq": "Testing/Opts/seq.results",
     "Opts_par": "Testing/Opts/par.results",
     "CommBasic_2D": "Testing/CommBasic/2D.results",
+    "CellBased_2D_Basic": "Testing/CellBased/2D_Basic.results",
+    "CellBased_2D_Neumann": "Testing/CellBased/2D_Neumann.results",
+    "CellBased_3D_Basic": "Testing/CellBased/3D_Basic.results",
+    "CellBased_3D_Neumann": "Testing/CellBased/3D_Neumann.results",
     "CommBasic_PureMPI": "Testing/CommBasic/PureMPI.results",
     "CommBasic_PureOMP": "Testing/CommBasic/PureOMP.results",
     "CommBasic_Hybrid": "Testing/CommBasic/Hybrid.results",

@@ -90,3 +90,12 @@ def test_golden_optical_flow_2d(oracle):
     s.close()
     path = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "Application_OpticalFlow2D.results")
     assert got == open(path).read().split()
+
+
+def test_golden_cell_based(oracle):
+    """Testing/CellBased/{2D,3D}_{Basic,Neumann}: cell-centred FV Poisson, Dirichlet ghost cells 2g - u / Neumann ghost
+    cells, cell restriction and correction, CG with `apply bc to VecP`, mean subtraction of the pure Neumann problem."""
+    import cell_programs as cp
+    for prog in cp.PROGRAMS:
+        b = cp.OracleCells(prog)
+        assert cp.solve(b, oracle.print_reduced_prec) == prog.expected(), prog.name
