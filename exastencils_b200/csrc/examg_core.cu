@@ -82,6 +82,16 @@ GridArgs examg::grid_args(const LevelGeom &g) {
   return a;
 }
 
+GridArgs examg::grid_args_loc(examg_ctx *c, const LevelGeom &g) {
+  GridArgs a = grid_args(g);
+  if (c->loop_loc == 1)
+    for (int d = 0; d < c->cfg.dim; ++d) { a.lo[d] = 0; a.hi[d] = g.n[d] - 1; a.rlo[d] = 0; a.rhi[d] = g.n[d] - 1; }
+  return a;
+}
+
+examg::LocGuard::LocGuard(examg_ctx *ctx, int loc) : c(ctx) { c->loop_loc = loc; }
+examg::LocGuard::~LocGuard() { c->loop_loc = 0; }
+
 StencilArgs examg::stencil_args(const LevelGeom &g, const Stencil &s) {
   StencilArgs a;
   a.nst = s.nst;
@@ -412,8 +422,9 @@ int examg_field_set_bc(examg_ctx *c, int h, int kind, double value) {
   if (!f) return set_error(EXAMG_EINVAL, "bad field %d", h);
   if (kind == EXAMG_BC_NEUMANN && f->loc != 1)
     return set_error(EXAMG_EUNSUP, "examg_field_set_bc: Neumann is implemented for cell-localised fields");
-  if (f->loc == 1 && kind != EXAMG_BC_NONE && kind != EXAMG_BC_NEUMANN)
-    return set_error(EXAMG_EUNSUP, "examg_field_set_bc: cell-localised fields take None or Neumann");
+  if (f->loc == 1 && kind == EXAMG_BC_DIRICHLET_HOST)
+    return set_error(EXAMG_EUNSUP, "examg_field_set_bc: cell-localised fields take None, Neumann or a Dirichlet value / program "
+                     "(the ghost cell is 2 * value - inner cell)");
   if (kind != EXAMG_BC_NONE && kind != EXAMG_BC_DIRICHLET_CONST && kind != EXAMG_BC_DIRICHLET_HOST &&
       kind != EXAMG_BC_NEUMANN)
     return set_error(EXAMG_EINVAL, "examg_field_set_bc: kind %d (use examg_field_set_bc_expr for programs)", kind);
@@ -490,7 +501,8 @@ int examg_apply_bc(examg_ctx *c, int h, int slot) {
   if (!f) return set_error(EXAMG_EINVAL, "bad field %d", h);
   if (slot >= f->nslots) return set_error(EXAMG_EINVAL, "bad slot %d", slot);
   if (f->bc_kind == EXAMG_BC_NONE || f->bc_kind == EXAMG_BC_DIRICHLET_HOST) return EXAMG_OK;
-  if (f->loc == 1) return launch_bc_cell(c, *f, slot);
+  if (f->loc == 1)
+    return f->bc_kind == EXAMG_BC_NEUMANN && c->cfg.dim == 2 ? launch_bc_cell(c, *f, slot) : launch_bc_cell_generic(c, *f, slot);
   return launch_bc(c, *f, slot);
 }
 

@@ -410,7 +410,7 @@ constexpr int FUSED_MIN_N = 65;
 
 bool fused_rb_usable(examg_ctx *c, const Stencil &s, const Field &fu) {
   if (!fused_enabled() || !s.is7 || c->cfg.dim != 3 || fu.ncomp != 1 || stencil_order(s) < 0) return false;
-  if (c->periodic_any) return false;  // periodic dimensions run on the generic kernels so far
+  if (c->periodic_any || fu.loc != 0) return false;  // periodic dimensions and cell fields run on the generic kernels
   const LevelGeom &g = *geom(c, s.level);
   return g.n[0] >= FUSED_MIN_N && g.n[1] >= FUSED_MIN_N && g.n[2] >= FUSED_MIN_N;
 }
@@ -627,7 +627,7 @@ constexpr int JACV_MIN_N = 33;
 
 bool fused_jacv_usable(examg_ctx *c, const Stencil &s, const Field &fu) {
   if (!fused_enabled() || jacv_mode() <= 0 || c->cfg.dim != 3 || s.coeff_field < 0 || fu.ncomp != 1 ||
-      fu.nslots != 2 || c->periodic_any)
+      fu.nslots != 2 || c->periodic_any || fu.loc != 0)
     return false;
   const int shape = jacv_shape(s);
   if (shape < 0 || (shape < 2 && jacv_mode() < 2)) return false;

@@ -130,6 +130,7 @@ struct examg_ctx {
   bool nb[3][2];  // neighbour present on the -/+ side of dim d (a periodic dimension: the block itself)
   bool per[3] = {false, false, false};  // periodic dimension (its only block is its own neighbour)
   bool periodic_any = false;
+  int loop_loc = 0;  // localisation of the fields of the entry point being executed (0 node, 1 cell)
   std::vector<examg::LevelGeom> levels;  // index level - min_level
   std::vector<examg::Field> fields;
   std::vector<examg::Stencil> stencils;
@@ -178,6 +179,15 @@ inline double *field_ptr(examg_ctx *c, const Field *f, int slot, int comp = 0) {
   return f->slot[slot] + (long long)comp * g.vol + g.origin;
 }
 GridArgs grid_args(const LevelGeom &g);
+// loop ranges of the localisation the current entry point works on (examg_ctx::loop_loc): node fields as grid_args,
+// cell fields all cells 0 .. n-2 of every dimension (`loop over F` of a cell field, reductions alike)
+GridArgs grid_args_loc(examg_ctx *c, const LevelGeom &g);
+// sets examg_ctx::loop_loc for the duration of one entry point
+struct LocGuard {
+  examg_ctx *c;
+  LocGuard(examg_ctx *ctx, int loc);
+  ~LocGuard();
+};
 StencilArgs stencil_args(const LevelGeom &g, const Stencil &s);
 
 // global (all-rank) sum of a device dd partial written to c->red_out[slot]; returns hi+lo
@@ -220,7 +230,8 @@ enum { STREAM_SET = 0, STREAM_COPY = 1, STREAM_AXPY = 2, STREAM_XPAY = 3 };
 int launch_stream_op(examg_ctx *c, int level, int op, double alpha, const double *x, double *y);
 int launch_bc(examg_ctx *c, const Field &f, int slot);
 int launch_field_eval(examg_ctx *c, const Field &f, int slot, int comp, const examg_bc_op *prog, int n);
-int launch_bc_cell(examg_ctx *c, const Field &f, int slot);  // Neumann ghost cells (examg_optflow.cu)
+int launch_bc_cell(examg_ctx *c, const Field &f, int slot);  // 2D Neumann ghost cells incl. corners (examg_optflow.cu)
+int launch_bc_cell_generic(examg_ctx *c, const Field &f, int slot);  // Dirichlet / Neumann faces, 2D and 3D
 int launch_cg(examg_ctx *c, const Stencil &s, double *u, const double *rhs, double *res, double *p,
               double *ap, int max_it, double rel_tol);
 // communicate: `depth` ghost layers (+ the duplicate layer) per side, 1 <= depth <= GHOST

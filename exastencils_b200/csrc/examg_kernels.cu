@@ -220,6 +220,45 @@ k_dirichlet(const BcArgs a, const __grid_constant__ BcProg pr, int use_prog, dou
   }
 }
 
+// `apply bc` on a cell-localised field: blockIdx.y = face (2*d + side), one thread per ghost cell of the face.
+// Dirichlet (order 1): ghost = 2 * value - adjacent inner cell, value constant or a program over vf_boundaryCoord
+// (the face position in the face's dimension, cell centres = node position + 0.5 * width in the others;
+// C/s/e/boundary/ir/IR_DirichletBC.scala:42-50); Neumann(1): ghost = adjacent inner cell (IR_NeumannBC.scala:70-80).
+__global__ void __launch_bounds__(256)
+k_cell_bc(const BcArgs a, const __grid_constant__ BcProg pr, int kind, double value, double *f) {
+  const int face = blockIdx.y;
+  if (!((a.face_mask >> face) & 1)) return;
+  const int d = face >> 1, side = face & 1;
+  const int da = d == 0 ? 1 : 0, db = d == 2 ? 1 : 2;
+  const int na = a.n[da] - 1, nb = db < a.dim ? a.n[db] - 1 : 1;  // cells
+  const long long total = (long long)na * nb;
+  for (long long t = blockIdx.x * (long long)blockDim.x + threadIdx.x; t < total; t += (long long)gridDim.x * blockDim.x) {
+    int idx[3] = {0, 0, 0}, in[3];
+    idx[da] = (int)(t % na);
+    if (db < a.dim) idx[db] = (int)(t / na);
+    idx[d] = side ? a.n[d] - 1 : -1;
+    in[0] = idx[0]; in[1] = idx[1]; in[2] = idx[2];
+    in[d] = side ? a.n[d] - 2 : 0;
+    const double inner = f[in[0] + (long long)a.pitch * in[1] + a.plane * in[2]];
+    double v;
+    if (kind == EXAMG_BC_NEUMANN) {
+      v = inner;
+    } else {
+      double g = value;
+      if (kind == EXAMG_BC_DIRICHLET_EXPR) {
+        double pos[3] = {0.0, 0.0, 0.0};
+        for (int w = 0; w < a.dim; ++w) {
+          if (w == d) pos[w] = (double)(a.goff[w] + (side ? a.n[w] - 1 : 0)) * a.h[w] + a.x0[w];
+          else pos[w] = ((double)(a.goff[w] + idx[w]) * a.h[w] + a.x0[w]) + 0.5 * a.h[w];
+        }
+        g = bc_eval(pr, pos[0], pos[1], pos[2]);
+      }
+      v = (2.0 * g) - inner;
+    }
+    f[idx[0] + (long long)a.pitch * idx[1] + a.plane * idx[2]] = v;
+  }
+}
+
 // loop over F { F[comp] = <expr>(vf_nodePosition) } on the local nodes and one ghost layer
 __global__ void __launch_bounds__(256)
 k_field_eval(const BcArgs a, const __grid_constant__ BcProg pr, double *f0, long long vol, int comp) {
@@ -241,7 +280,7 @@ template <int MODE>
 static int launch_stencil(examg_ctx *c, const Stencil &s, const double *u, const double *rhs, double *out,
                           double omega, int color, int red_slot, int extend = 0) {
   const LevelGeom &g = *geom(c, s.level);
-  GridArgs ga = grid_args(g);
+  GridArgs ga = grid_args_loc(c, g);
   // `extend` layers of the neighbour blocks' nodes are computed redundantly (saves their exchange)
   for (int d = 0; d < c->cfg.dim && extend > 0; ++d) {
     if (c->nb[d][0]) ga.lo[d] -= extend;
@@ -309,14 +348,14 @@ int launch_rb_generic(examg_ctx *c, const Stencil &s, double omega, double *u, c
 
 static int launch_reduce(examg_ctx *c, int level, const double *a, const double *b, int red_slot, int kind) {
   const LevelGeom &g = *geom(c, level);
-  const GridArgs ga = grid_args(g);
-  int xlo = g.lo[0], ylo = g.lo[1], zlo = g.lo[2];
+  const GridArgs ga = grid_args_loc(c, g);
+  int xlo = ga.lo[0], ylo = ga.lo[1], zlo = ga.lo[2];
   if (kind == R_DOT) {
-    xlo = g.lo[0] > g.rlo[0] ? g.lo[0] : g.rlo[0];
-    ylo = g.lo[1] > g.rlo[1] ? g.lo[1] : g.rlo[1];
-    zlo = g.lo[2] > g.rlo[2] ? g.lo[2] : g.rlo[2];
+    xlo = ga.lo[0] > ga.rlo[0] ? ga.lo[0] : ga.rlo[0];
+    ylo = ga.lo[1] > ga.rlo[1] ? ga.lo[1] : ga.rlo[1];
+    zlo = ga.lo[2] > ga.rlo[2] ? ga.lo[2] : ga.rlo[2];
   }
-  const int ex = g.hi[0] - xlo, ey = g.hi[1] - ylo, ez = g.hi[2] - zlo;
+  const int ex = ga.hi[0] - xlo, ey = ga.hi[1] - ylo, ez = ga.hi[2] - zlo;
   if (ex <= 0 || ey <= 0 || ez <= 0) {
     EXAMG_CUDA(cudaMemsetAsync(c->red_out + red_slot, 0, sizeof(dd), c->stream));
     return EXAMG_OK;
@@ -344,8 +383,8 @@ int launch_maxdiff(examg_ctx *c, int level, const double *a, const double *b, in
 
 int launch_stream_op(examg_ctx *c, int level, int op, double alpha, const double *x, double *y) {
   const LevelGeom &g = *geom(c, level);
-  const GridArgs ga = grid_args(g);
-  const int ex = g.hi[0] - g.lo[0], ey = g.hi[1] - g.lo[1], ez = g.hi[2] - g.lo[2];
+  const GridArgs ga = grid_args_loc(c, g);
+  const int ex = ga.hi[0] - ga.lo[0], ey = ga.hi[1] - ga.lo[1], ez = ga.hi[2] - ga.lo[2];
   if (ex <= 0 || ey <= 0 || ez <= 0) return EXAMG_OK;
   const Shape sh = make_shape(ex, ey, ez);
   switch (op) {
@@ -379,6 +418,47 @@ int launch_field_eval(examg_ctx *c, const Field &f, int slot, int comp, const ex
   if (blocks > 148 * 16) blocks = 148 * 16;
   k_field_eval<<<(int)blocks, 256, 0, c->stream>>>(a, pr, field_ptr(c, &f, slot, 0), g.vol, comp);
   EXAMG_LAUNCH_CHECK(c);
+  return EXAMG_OK;
+}
+
+int launch_bc_cell_generic(examg_ctx *c, const Field &f, int slot) {
+  const LevelGeom &g = *geom(c, f.level);
+  BcArgs a;
+  int mask = 0;
+  for (int d = 0; d < 3; ++d) {
+    a.n[d] = g.n[d];
+    a.goff[d] = g.goff[d];
+    a.h[d] = g.h[d];
+    a.x0[d] = d < c->cfg.dim ? c->cfg.domain_lo[d] : 0.0;
+    if (d < c->cfg.dim) {
+      if (!c->nb[d][0]) mask |= 1 << (2 * d);
+      if (!c->nb[d][1]) mask |= 1 << (2 * d + 1);
+    }
+  }
+  a.pitch = g.pitch;
+  a.plane = g.plane;
+  a.face_mask = mask;
+  a.dim = c->cfg.dim;
+  BcProg pr;
+  pr.n = 0;
+  if (f.bc_kind == EXAMG_BC_DIRICHLET_EXPR) {
+    pr.n = (int)f.bc_prog.size();
+    for (int q = 0; q < pr.n; ++q) { pr.op[q] = f.bc_prog[q].op; pr.val[q] = f.bc_prog[q].value; }
+  }
+  long long maxface = 1;
+  for (int d = 0; d < c->cfg.dim; ++d) {
+    long long fsz = 1;
+    for (int e = 0; e < c->cfg.dim; ++e)
+      if (e != d) fsz *= g.n[e] - 1;
+    if (fsz > maxface) maxface = fsz;
+  }
+  int gx = (int)((maxface + 255) / 256);
+  if (gx > 1024) gx = 1024;
+  dim3 grid(gx, 2 * c->cfg.dim, 1);
+  for (int comp = 0; comp < f.ncomp; ++comp) {
+    k_cell_bc<<<grid, 256, 0, c->stream>>>(a, pr, f.bc_kind, f.bc_value, field_ptr(c, &f, slot, comp));
+    EXAMG_LAUNCH_CHECK(c);
+  }
   return EXAMG_OK;
 }
 

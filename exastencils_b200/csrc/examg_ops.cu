@@ -58,6 +58,8 @@ int examg::residual_op(examg_ctx *c, int A, int u, int u_slot, int rhs, int res,
   GET_STENCIL(s, A); GET_FIELD(fu, u); GET_FIELD(fr, rhs); GET_FIELD(fo, res);
   CHECK_SLOT(fu, u_slot); CHECK_LEVEL(fu, s->level); CHECK_LEVEL(fr, s->level); CHECK_LEVEL(fo, s->level);
   if (fu == fo) return set_error(EXAMG_EINVAL, "examg_residual: Residual aliases Solution");
+  if (fu->loc != fr->loc || fu->loc != fo->loc) return set_error(EXAMG_EINVAL, "examg_residual: fields of different localisation");
+  LocGuard lg(c, fu->loc);
   if (c->world == 1) extend = 0;
   const int us = u_slot < 0 ? fu->cur : u_slot;
   int rc;
@@ -107,6 +109,7 @@ int examg_apply(examg_ctx *c, int A, int u, int u_slot, int out) {
   GET_STENCIL(s, A); GET_FIELD(fu, u); GET_FIELD(fo, out);
   CHECK_SLOT(fu, u_slot); CHECK_LEVEL(fu, s->level); CHECK_LEVEL(fo, s->level);
   if (fu == fo) return set_error(EXAMG_EINVAL, "examg_apply: in-place application");
+  LocGuard lg(c, fu->loc);
   int rc = do_exchange(c, *fu, u_slot < 0 ? fu->cur : u_slot);
   if (rc) return rc;
   fo->halo_depth = 0;
@@ -128,6 +131,8 @@ int examg_smooth_jacobi(examg_ctx *c, int A, int u, int rhs, double omega, int n
   GET_STENCIL(s, A); GET_FIELD(fu, u); GET_FIELD(fr, rhs);
   CHECK_LEVEL(fu, s->level); CHECK_LEVEL(fr, s->level);
   if (fu->nslots < 2) return set_error(EXAMG_EINVAL, "examg_smooth_jacobi: Solution needs 2 slots");
+  if (fu->loc != fr->loc) return set_error(EXAMG_EINVAL, "examg_smooth_jacobi: fields of different localisation");
+  LocGuard lg(c, fu->loc);
   if (fused_jac_usable(c, *s, *fu)) {  // up to three sweeps in one pass over HBM (examg_jac7.cuh)
     for (int it = 0; it < nsweeps;) {
       // `plan` sweeps need that many ghost layers of Solution and one less of RHS (redundant updates there)
@@ -250,6 +255,7 @@ int examg_dot(examg_ctx *c, int a, int a_slot, int b, int b_slot, double *out) {
   GET_FIELD(fa, a); GET_FIELD(fb, b);
   CHECK_SLOT(fa, a_slot); CHECK_SLOT(fb, b_slot); CHECK_LEVEL(fb, fa->level);
   if (!out) return set_error(EXAMG_EINVAL, "examg_dot: null output");
+  LocGuard lg(c, fa->loc);
   int rc = launch_dot(c, fa->level, field_ptr(c, fa, a_slot), field_ptr(c, fb, b_slot), 0);
   if (rc) return rc;
   return finish_sum(c, 0, out);
@@ -259,6 +265,7 @@ int examg_max_abs_diff(examg_ctx *c, int a, int a_slot, int b, int b_slot, doubl
   GET_FIELD(fa, a); GET_FIELD(fb, b);
   CHECK_SLOT(fa, a_slot); CHECK_SLOT(fb, b_slot); CHECK_LEVEL(fb, fa->level);
   if (!out) return set_error(EXAMG_EINVAL, "examg_max_abs_diff: null output");
+  LocGuard lg(c, fa->loc);
   int rc = launch_maxdiff(c, fa->level, field_ptr(c, fa, a_slot), field_ptr(c, fb, b_slot), 1);
   if (rc) return rc;
   EXAMG_CUDA(cudaMemcpyAsync(c->red_host + 1, c->red_out + 1, sizeof(dd), cudaMemcpyDeviceToHost, c->stream));
@@ -270,24 +277,28 @@ int examg_max_abs_diff(examg_ctx *c, int a, int a_slot, int b, int b_slot, doubl
 int examg_set(examg_ctx *c, int f, int slot, double value) {
   GET_FIELD(ff, f); CHECK_SLOT(ff, slot);
   ff->halo_depth = 0;
+  LocGuard lg(c, ff->loc);
   return launch_stream_op(c, ff->level, STREAM_SET, value, nullptr, field_ptr(c, ff, slot));
 }
 int examg_copy(examg_ctx *c, int src, int src_slot, int dst, int dst_slot) {
   GET_FIELD(fs, src); GET_FIELD(fd, dst);
   CHECK_SLOT(fs, src_slot); CHECK_SLOT(fd, dst_slot); CHECK_LEVEL(fd, fs->level);
   fd->halo_depth = 0;
+  LocGuard lg(c, fs->loc);
   return launch_stream_op(c, fs->level, STREAM_COPY, 0.0, field_ptr(c, fs, src_slot), field_ptr(c, fd, dst_slot));
 }
 int examg_axpy(examg_ctx *c, double alpha, int x, int x_slot, int y, int y_slot) {
   GET_FIELD(fx, x); GET_FIELD(fy, y);
   CHECK_SLOT(fx, x_slot); CHECK_SLOT(fy, y_slot); CHECK_LEVEL(fy, fx->level);
   fy->halo_depth = 0;
+  LocGuard lg(c, fx->loc);
   return launch_stream_op(c, fx->level, STREAM_AXPY, alpha, field_ptr(c, fx, x_slot), field_ptr(c, fy, y_slot));
 }
 int examg_xpay(examg_ctx *c, int x, int x_slot, double beta, int y, int y_slot) {
   GET_FIELD(fx, x); GET_FIELD(fy, y);
   CHECK_SLOT(fx, x_slot); CHECK_SLOT(fy, y_slot); CHECK_LEVEL(fy, fx->level);
   fy->halo_depth = 0;
+  LocGuard lg(c, fx->loc);
   return launch_stream_op(c, fx->level, STREAM_XPAY, beta, field_ptr(c, fx, x_slot), field_ptr(c, fy, y_slot));
 }
 

@@ -197,6 +197,45 @@ __global__ void __launch_bounds__(256) k_of_prolong_add(const Pair pr, int nxc, 
   }
 }
 
+// 3D cell transfer (Testing/CellBased/3D_*.exa4): coarse = 0.125 * (sum of the 8 children in lexicographic z,y,x order);
+// fine += parent.  Thread per coarse cell, x fastest; ghost cells are the business of `apply bc`.
+__global__ void __launch_bounds__(256)
+k_cell_restrict3(const Pair pr, int nxc, int nyc, int nzc, int pitch_f, long long plane_f, int pitch_c, long long plane_c) {
+  const double *__restrict__ f = pr.src[blockIdx.z];
+  double *__restrict__ cdst = pr.dst[blockIdx.z];
+  const long long total = (long long)nxc * nyc * nzc;
+  for (long long t = blockIdx.x * (long long)blockDim.x + threadIdx.x; t < total; t += (long long)gridDim.x * blockDim.x) {
+    const int i = (int)(t % nxc), j = (int)((t / nxc) % nyc), k = (int)(t / ((long long)nxc * nyc));
+    const double *q = f + 2 * i + (long long)pitch_f * (2 * j) + plane_f * (2 * k);
+    const double2 a = *reinterpret_cast<const double2 *>(q), b = *reinterpret_cast<const double2 *>(q + pitch_f);
+    const double2 cc = *reinterpret_cast<const double2 *>(q + plane_f), dd2 = *reinterpret_cast<const double2 *>(q + plane_f + pitch_f);
+    cdst[i + (long long)pitch_c * j + plane_c * k] =
+        0.125 * (((((((a.x + a.y) + b.x) + b.y) + cc.x) + cc.y) + dd2.x) + dd2.y);
+  }
+}
+
+__global__ void __launch_bounds__(256)
+k_cell_prolong3(const Pair pr, int nxc, int nyc, int nzc, int pitch_f, long long plane_f, int pitch_c, long long plane_c) {
+  const double *__restrict__ cs = pr.src[blockIdx.z];
+  double *__restrict__ f = pr.dst[blockIdx.z];
+  const long long total = (long long)nxc * nyc * nzc;
+  for (long long t = blockIdx.x * (long long)blockDim.x + threadIdx.x; t < total; t += (long long)gridDim.x * blockDim.x) {
+    const int i = (int)(t % nxc), j = (int)((t / nxc) % nyc), k = (int)(t / ((long long)nxc * nyc));
+    const double cv = cs[i + (long long)pitch_c * j + plane_c * k];
+    double *q = f + 2 * i + (long long)pitch_f * (2 * j) + plane_f * (2 * k);
+#pragma unroll
+    for (int dz = 0; dz < 2; ++dz)
+#pragma unroll
+      for (int dy = 0; dy < 2; ++dy) {
+        double2 *p2 = reinterpret_cast<double2 *>(q + plane_f * dz + (long long)pitch_f * dy);
+        double2 v = *p2;
+        v.x += cv;
+        v.y += cv;
+        *p2 = v;
+      }
+  }
+}
+
 // InitFields: Ix, Iy, It -> IxIx, IxIy, IyIy and rhs (images carry valid Neumann ghosts)
 __global__ void __launch_bounds__(256)
 k_of_init(const double *__restrict__ img0, const double *__restrict__ img1, int nx, int ny, int pitch, double gx1,
@@ -635,8 +674,20 @@ static int cell_transfer(examg_ctx *c, const int *src, const int *dst, int n, bo
     pr.src[k] = field_ptr(c, fs, -1);
     pr.dst[k] = field_ptr(c, fd, -1);
   }
-  if (c->cfg.dim != 2) return set_error(EXAMG_EUNSUP, "%s: 2D only", who);
   const LevelGeom &gf = *geom(c, lf), &gc = *geom(c, lc);
+  if (c->cfg.dim == 3) {
+    const int nxc = gc.n[0] - 1, nyc = gc.n[1] - 1, nzc = gc.n[2] - 1;
+    const long long total = (long long)nxc * nyc * nzc;
+    long long gx = (total + 255) / 256;
+    if (gx > 148 * 8) gx = 148 * 8;
+    const dim3 grid((unsigned)gx, 1, n);
+    if (restrict_op)
+      k_cell_restrict3<<<grid, 256, 0, c->stream>>>(pr, nxc, nyc, nzc, gf.pitch, gf.plane, gc.pitch, gc.plane);
+    else
+      k_cell_prolong3<<<grid, 256, 0, c->stream>>>(pr, nxc, nyc, nzc, gf.pitch, gf.plane, gc.pitch, gc.plane);
+    EXAMG_LAUNCH_CHECK(c);
+    return EXAMG_OK;
+  }
   const int nxc = gc.n[0] - 1, nyc = gc.n[1] - 1;
   const dim3 block(64, 4), grid = rows_grid(nxc, nyc, block, n);
   if (restrict_op)

@@ -88,7 +88,11 @@ int examg_level_width(examg_ctx *ctx, int level, double h[3]);
 int examg_field_create(examg_ctx *ctx, const char *name, int level, int num_slots, int ncomp);
 /* Cell-localised field (Layout< Real, Cell >: duplicateLayers 0, ghostLayers 1): n-1 cells per
  * dimension where the level has n nodes; upload/download move the dense cell array, no ghosts.
- * 2D, single block so far. */
+ * 2D and 3D, single block so far.  The loops of the entry points below (apply, residual, smooth_jacobi, dot,
+ * max_abs_diff, set, copy, axpy, xpay) run over all cells when their fields are cell-localised; boundary
+ * conditions write the ghost cells: Dirichlet value / program g -> 2*g - inner cell
+ * (C/s/e/boundary/ir/IR_DirichletBC.scala:42-50, the program sees vf_boundaryCoord: the face position in the
+ * face's dimension, cell centres in the others), Neumann -> inner cell.  Programs: Testing/CellBased. */
 int examg_field_create_cell(examg_ctx *ctx, const char *name, int level, int num_slots, int ncomp);
 int examg_level_cells(examg_ctx *ctx, int level, int n[3]);
 int examg_field_destroy(examg_ctx *ctx, int field);
@@ -104,7 +108,7 @@ enum {
   EXAMG_BC_DIRICHLET_CONST = 1, /* value                                             */
   EXAMG_BC_DIRICHLET_EXPR = 2,  /* postfix program over vf_boundaryPosition_{x,y,z}  */
   EXAMG_BC_DIRICHLET_HOST = 3,  /* boundary nodes keep what upload() wrote           */
-  EXAMG_BC_NEUMANN = 4          /* cell fields, order 1: ghost cell = adjacent inner cell
+  EXAMG_BC_NEUMANN = 4          /* cell fields, order 1 (Neumann(1)): ghost cell = adjacent inner cell
                                    (C/s/e/boundary/ir/IR_NeumannBC.scala:70-80)       */
 };
 /* postfix (RPN) program for boundary expressions -- what the kernel printer
@@ -259,7 +263,7 @@ int examg_system2_residual(examg_ctx *ctx, int sys, int u, int v, int rhs_u, int
 int examg_system2_smooth_rb(examg_ctx *ctx, int sys, int u, int v, int rhs_u, int rhs_v, double relax, int nsweeps);
 int examg_system2_smooth_rb_color(examg_ctx *ctx, int sys, int u, int v, int rhs_u, int rhs_v, double relax,
                                   int color);
-/* coarse[k] = RestrictionCell * fine[k] (mean of the 2^d children), k < nfields <= 3
+/* 2D and 3D.  coarse[k] = RestrictionCell * fine[k] (mean of the 2^d children), k < nfields <= 3
  * (C/s/e/operator/l4/L4_DefaultRestriction.scala:40-47)                                         */
 int examg_restrict_cell(examg_ctx *ctx, const int *fine, const int *coarse, int nfields);
 /* fine[k] += ProlongationCell * coarse[k] (piecewise constant); apply bc

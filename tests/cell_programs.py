@@ -247,3 +247,101 @@ class OracleCells:
 
     def close(self):
         pass
+
+
+# ---- libexamg backend (through the C ABI) -------------------------------------------------------------------------
+class GpuCells:
+    """Cell-localised fields of libexamg: examg_field_create_cell, Dirichlet / Neumann ghost-cell updates by
+    examg_apply_bc, the generic stencil kernels on the cells, examg_restrict_cell / examg_prolong_add_cell."""
+
+    def __init__(self, prog):
+        from exastencils_b200 import runtime as rt
+        self.rt, self.prog = rt, prog
+        P = prog
+        self.ctx = ctx = rt.Context(P.dim, P.min_level, P.max_level, block_cells=(P.F,) * P.dim)
+        self.f, self.A = {}, {}
+        offs = [(0, 0, 0), (1, 0, 0), (-1, 0, 0), (0, 1, 0), (0, -1, 0)] + ([(0, 0, 1), (0, 0, -1)] if P.dim == 3 else [])
+        kind = rt.BC_NEUMANN if P.neumann else rt.BC_DIRICHLET_CONST
+        for lvl in range(P.min_level, P.max_level + 1):
+            h = P.h(lvl)
+            diag = 2.0 / (h * h) + 2.0 / (h * h)
+            if P.dim == 3:
+                diag = diag + 2.0 / (h * h)
+            self.A[lvl] = ctx.stencil_const(lvl, offs, [diag] + [-1.0 / (h * h)] * (2 * P.dim))
+            self.f[("u", lvl)] = ctx.field_create_cell("Solution", lvl, 2)
+            self.f[("f", lvl)] = ctx.field_create_cell("RHS", lvl)
+            self.f[("r", lvl)] = ctx.field_create_cell("Residual", lvl)
+            ctx.field_set_bc(self.f[("u", lvl)], kind, 0.0)
+            ctx.field_set_bc(self.f[("r", lvl)], kind, 0.0)
+        self.f[("p", P.min_level)] = ctx.field_create_cell("VecP", P.min_level)
+        self.f[("ap", P.min_level)] = ctx.field_create_cell("VecGradP", P.min_level)
+        ctx.field_set_bc(self.f[("p", P.min_level)], kind, 0.0)
+        L = P.max_level
+        if not P.neumann:  # Field Solution< global, ..., sin(PI x) * sinh(PI y) >@finest, x = vf_boundaryCoord_x
+            if P.dim == 2:
+                prog_bc = [(rt.OP_CONST, PI), (rt.OP_X, 0), (rt.OP_MUL, 0), (rt.OP_SIN, 0),
+                           (rt.OP_CONST, PI), (rt.OP_Y, 0), (rt.OP_MUL, 0), (rt.OP_SINH, 0), (rt.OP_MUL, 0)]
+            else:
+                prog_bc = [(rt.OP_CONST, PI), (rt.OP_X, 0), (rt.OP_MUL, 0), (rt.OP_SIN, 0),
+                           (rt.OP_CONST, PI), (rt.OP_Y, 0), (rt.OP_MUL, 0), (rt.OP_SIN, 0), (rt.OP_MUL, 0),
+                           (rt.OP_CONST, math.sqrt(2.0) * PI), (rt.OP_Z, 0), (rt.OP_MUL, 0), (rt.OP_SINH, 0), (rt.OP_MUL, 0)]
+            ctx.field_set_bc_expr(self.f[("u", L)], prog_bc)
+        X, Y, Z = P.grid(L)
+        shape = ctx.cell_shape(L)
+        self.exact = ctx.field_create_cell("Exact", L)
+        self.ones = ctx.field_create_cell("Ones", L)
+        ctx.upload(self.f[("f", L)], np.ascontiguousarray(np.broadcast_to(P.rhs(X, Y, Z), shape)))
+        ctx.upload(self.exact, np.ascontiguousarray(np.broadcast_to(P.exact(X, Y, Z), shape)))
+        ctx.upload(self.ones, np.ones(shape))
+
+    def apply_bc(self, k, lvl):
+        self.ctx.apply_bc(self.f[(k, lvl)])
+
+    def jacobi(self, lvl):
+        self.ctx.smooth_jacobi(self.A[lvl], self.f[("u", lvl)], self.f[("f", lvl)], OMEGA, 1)
+
+    def residual(self, lvl):
+        self.ctx.residual(self.A[lvl], self.f[("u", lvl)], self.f[("f", lvl)], self.f[("r", lvl)])
+
+    def norm(self, lvl):
+        r = self.f[("r", lvl)]
+        return math.sqrt(self.ctx.dot(r, r))
+
+    def dot(self, x, y, lvl):
+        return self.ctx.dot(self.f[(x, lvl)], self.f[(y, lvl)])
+
+    def apply(self, x, y, lvl):
+        self.ctx.apply(self.A[lvl], self.f[(x, lvl)], self.f[(y, lvl)])
+
+    def copy(self, src, dst, lvl):
+        self.ctx.copy(self.f[(src, lvl)], self.f[(dst, lvl)])
+
+    def set(self, k, lvl, v):
+        self.ctx.set(self.f[(k, lvl)], v)
+
+    def axpy(self, alpha, x, y, lvl):
+        self.ctx.axpy(alpha, self.f[(x, lvl)], self.f[(y, lvl)])
+
+    def xpay(self, x, beta, y, lvl):
+        self.ctx.xpay(self.f[(x, lvl)], beta, self.f[(y, lvl)])
+
+    def restrict(self, lvl):
+        self.ctx.restrict_cell([self.f[("r", lvl)]], [self.f[("f", lvl - 1)]])
+
+    def correct(self, lvl):
+        self.ctx.prolong_add_cell([self.f[("u", lvl - 1)]], [self.f[("u", lvl)]])
+
+    def sum(self, k, lvl):
+        return self.ctx.dot(self.f[(k, lvl)], self.ones)
+
+    def shift(self, k, lvl, c):
+        self.ctx.axpy(c, self.ones, self.f[(k, lvl)])
+
+    def max_error(self, lvl):
+        return self.ctx.max_abs_diff(self.f[("u", lvl)], self.exact)
+
+    def interior(self, k, lvl):
+        return self.ctx.download_cells(self.f[(k, lvl)], lvl)
+
+    def close(self):
+        self.ctx.close()

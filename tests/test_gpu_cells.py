@@ -1,0 +1,45 @@
+"""Cell-centred finite-volume Poisson on the GPU (Testing/CellBased/{2D,3D}_{Basic,Neumann}.exa4): the
+programs' text (tests/cell_programs.py) on libexamg's cell-localised fields must print the reference's golden stdout and
+match the CPU oracle -- bit for bit where the boundary data is a constant or Neumann, to 1e-12 where the Dirichlet
+expression goes through the device's sin / sinh."""
+import numpy as np
+import pytest
+
+import cell_programs as cp
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.mark.parametrize("prog", cp.PROGRAMS, ids=lambda p: p.name)
+def test_golden_stdout(prog, oracle):
+    b = cp.GpuCells(prog)
+    out = cp.solve(b, oracle.print_reduced_prec)
+    b.close()
+    assert out == prog.expected()
+
+
+@pytest.mark.parametrize("name,dim,neumann,lvl", [("2D_Basic", 2, False, 5), ("2D_Neumann", 2, True, 5),
+                                                  ("3D_Basic", 3, False, 3), ("3D_Neumann", 3, True, 3)])
+def test_oracle_parity(name, dim, neumann, lvl, oracle):
+    prog = cp.CellProgram(name, dim, neumann, max_level=lvl)
+    ref, gpu = cp.OracleCells(prog), cp.GpuCells(prog)
+    L = prog.max_level
+    for b in (ref, gpu):
+        cp.up_residual(b, L)
+    assert abs(gpu.norm(L) - ref.norm(L)) <= 1e-12 * ref.norm(L)
+    for cyc in range(3):
+        for b in (ref, gpu):
+            cp.vcycle(b, L)
+            if neumann:
+                b.shift("u", L, -(b.sum("u", L) / float(prog.cells(L) ** dim)))
+            cp.up_residual(b, L)
+        ug = gpu.interior("u", L)
+        ur = ref.interior("u", L).reshape(ug.shape)
+        if neumann:
+            assert np.array_equal(ug, ur), "cycle %d" % cyc
+        else:
+            assert np.allclose(ug, ur, rtol=1e-12, atol=1e-12 * np.max(np.abs(ur))), "cycle %d" % cyc
+        assert abs(gpu.norm(L) - ref.norm(L)) <= 1e-10 * ref.norm(L) + 1e-300
+        assert abs(gpu.max_error(L) - ref.max_error(L)) <= 1e-10 * ref.max_error(L)
+    gpu.close()
+    ref.close()
