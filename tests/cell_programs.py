@@ -17,12 +17,31 @@ OMEGA = 0.8
 
 
 class CellProgram:
-    def __init__(self, name, dim, neumann, max_level=6, F=4):
+    """kind "cellbased": Testing/CellBased (scaled stencil, trigonometric data, prints NormError_0);
+    kind "hybridcell": Testing/CommBasic/{HybridCell,Strategy26Cell} (3x3x3 blocks x 3x3x3 fragments => F = 9, unscaled
+    stencil [6, -1 ...], 4.0 * RestrictionStencil, Dirichlet data x^2 - y^2/2 - z^2/2, prints the residual)."""
+
+    def __init__(self, name, dim, neumann, max_level=6, F=4, kind="cellbased", golden=None):
         self.name, self.dim, self.neumann, self.max_level, self.F, self.min_level = name, dim, neumann, max_level, F, 0
+        self.kind = kind
+        self.scaled = kind == "cellbased"
+        self.restrict_scale = 1.0 if kind == "cellbased" else 4.0
+        self.prints = "err" if kind == "cellbased" else "res"
+        self.golden = golden or "CellBased_" + name
 
     def expected(self):
-        with open(os.path.join(GOLDEN_DIR, "CellBased_" + self.name + ".results")) as f:
+        with open(os.path.join(GOLDEN_DIR, self.golden + ".results")) as f:
             return f.read().split()
+
+    def stencil_coeffs(self, lvl):
+        """Stencil Laplace@all in declaration order: centre, +x, -x, +y, -y[, +z, -z]"""
+        if not self.scaled:
+            return [2.0 * self.dim] + [-1.0] * (2 * self.dim)
+        h = self.h(lvl)
+        diag = 2.0 / (h * h) + 2.0 / (h * h)
+        if self.dim == 3:
+            diag = diag + 2.0 / (h * h)
+        return [diag] + [-1.0 / (h * h)] * (2 * self.dim)
 
     def cells(self, lvl):
         return self.F << lvl
@@ -37,6 +56,8 @@ class CellProgram:
 
     # analytic data (Field declarations, InitRHS, NormError_0)
     def exact(self, X, Y, Z):
+        if self.kind == "hybridcell":
+            return ((X * X) - ((0.5 * Y) * Y)) - ((0.5 * Z) * Z)
         if self.neumann:
             e = np.cos((2.0 * PI) * X) * np.cos((2.0 * PI) * Y)
             return e * np.cos((2.0 * PI) * Z) if self.dim == 3 else e
@@ -84,6 +105,8 @@ class CellProgram:
 
 PROGRAMS = [CellProgram("2D_Basic", 2, False), CellProgram("2D_Neumann", 2, True),
             CellProgram("3D_Basic", 3, False), CellProgram("3D_Neumann", 3, True)]
+# 576^3 cells: GPU only (tests/test_gpu_cells.py); the oracle checks the same program at a lower finest level
+HYBRID_CELL = CellProgram("HybridCell", 3, False, F=9, kind="hybridcell", golden="CommBasic_HybridCell")
 
 
 # ---- the programs' functions, on a backend -----------------------------------------------------------------------
@@ -126,7 +149,7 @@ def vcycle(B, lvl):
         smoother(B, lvl)
     up_residual(B, lvl)
     B.apply_bc("r", lvl)          # Restriction: apply bc to Residual; communicate ghost
-    B.restrict(lvl)
+    B.restrict(lvl)               # RHS@coarser = RestrictionStencil * Residual  (HybridCell: 4.0 * RestrictionStencil)
     B.set("u", lvl - 1, 0.0)      # SetSolution@coarser ( 0 )
     vcycle(B, lvl - 1)
     B.apply_bc("u", lvl - 1)      # Correction: apply bc to Solution@coarser; communicate
@@ -152,7 +175,7 @@ def solve(B, printer):
             B.shift("u", L, -integral)
         up_residual(B, L)
         res = B.norm(L)
-        out.append(printer(B.max_error(L)))
+        out.append(printer(B.max_error(L) if P.prints == "err" else res))
     out.append(str(it))
     return out
 
@@ -173,10 +196,7 @@ class OracleCells:
             shape = ((n + 2,) * 3) if P.dim == 3 else (1, n + 2, n + 2)
             for k in ("u", "f", "r"):
                 self.a[(k, lvl)] = np.zeros(shape)
-            diag = 2.0 / (h * h) + 2.0 / (h * h)
-            if P.dim == 3:
-                diag = diag + 2.0 / (h * h)
-            self.st[lvl] = og.Stencil.make(offs, [diag] + [-1.0 / (h * h)] * (2 * P.dim))
+            self.st[lvl] = og.Stencil.make(offs, P.stencil_coeffs(lvl))
         for k in ("p", "ap"):
             self.a[(k, P.min_level)] = np.zeros_like(self.a[("u", P.min_level)])
         L = P.max_level
@@ -225,6 +245,8 @@ class OracleCells:
 
     def restrict(self, lvl):
         self.a[("f", lvl - 1)] = self.og.cell_restrict(self.prog.dim, self.a[("r", lvl)], self.a[("f", lvl - 1)].shape)
+        if self.prog.restrict_scale != 1.0:
+            self.a[("f", lvl - 1)] *= self.prog.restrict_scale  # a power of two: exact
 
     def correct(self, lvl):
         self.og.cell_prolong_add(self.prog.dim, self.a[("u", lvl - 1)], self.a[("u", lvl)])
@@ -263,12 +285,10 @@ class GpuCells:
         offs = [(0, 0, 0), (1, 0, 0), (-1, 0, 0), (0, 1, 0), (0, -1, 0)] + ([(0, 0, 1), (0, 0, -1)] if P.dim == 3 else [])
         kind = rt.BC_NEUMANN if P.neumann else rt.BC_DIRICHLET_CONST
         for lvl in range(P.min_level, P.max_level + 1):
-            h = P.h(lvl)
-            diag = 2.0 / (h * h) + 2.0 / (h * h)
-            if P.dim == 3:
-                diag = diag + 2.0 / (h * h)
-            self.A[lvl] = ctx.stencil_const(lvl, offs, [diag] + [-1.0 / (h * h)] * (2 * P.dim))
+            self.A[lvl] = ctx.stencil_const(lvl, offs, P.stencil_coeffs(lvl))
             self.f[("u", lvl)] = ctx.field_create_cell("Solution", lvl, 2)
+            if P.restrict_scale != 1.0:
+                self.f[("zero", lvl)] = ctx.field_create_cell("Zero", lvl)
             self.f[("f", lvl)] = ctx.field_create_cell("RHS", lvl)
             self.f[("r", lvl)] = ctx.field_create_cell("Residual", lvl)
             ctx.field_set_bc(self.f[("u", lvl)], kind, 0.0)
@@ -278,7 +298,11 @@ class GpuCells:
         ctx.field_set_bc(self.f[("p", P.min_level)], kind, 0.0)
         L = P.max_level
         if not P.neumann:  # Field Solution< global, ..., sin(PI x) * sinh(PI y) >@finest, x = vf_boundaryCoord_x
-            if P.dim == 2:
+            if P.kind == "hybridcell":
+                prog_bc = [(rt.OP_X, 0), (rt.OP_X, 0), (rt.OP_MUL, 0),
+                           (rt.OP_CONST, 0.5), (rt.OP_Y, 0), (rt.OP_MUL, 0), (rt.OP_Y, 0), (rt.OP_MUL, 0), (rt.OP_SUB, 0),
+                           (rt.OP_CONST, 0.5), (rt.OP_Z, 0), (rt.OP_MUL, 0), (rt.OP_Z, 0), (rt.OP_MUL, 0), (rt.OP_SUB, 0)]
+            elif P.dim == 2:
                 prog_bc = [(rt.OP_CONST, PI), (rt.OP_X, 0), (rt.OP_MUL, 0), (rt.OP_SIN, 0),
                            (rt.OP_CONST, PI), (rt.OP_Y, 0), (rt.OP_MUL, 0), (rt.OP_SINH, 0), (rt.OP_MUL, 0)]
             else:
@@ -327,6 +351,8 @@ class GpuCells:
 
     def restrict(self, lvl):
         self.ctx.restrict_cell([self.f[("r", lvl)]], [self.f[("f", lvl - 1)]])
+        if self.prog.restrict_scale != 1.0:  # RHS@coarser = 0 + scale * RHS@coarser (a power of two: exact)
+            self.ctx.xpay(self.f[("zero", lvl - 1)], self.prog.restrict_scale, self.f[("f", lvl - 1)])
 
     def correct(self, lvl):
         self.ctx.prolong_add_cell([self.f[("u", lvl - 1)]], [self.f[("u", lvl)]])

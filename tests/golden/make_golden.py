@@ -24,6 +24,8 @@ FILES = {
     "Opts_seq": "Testing/Opts/seq.results",
     "Opts_par": "Testing/Opts/par.results",
     "CommBasic_2D": "Testing/CommBasic/2D.results",
+    "CommBasic_HybridCell": "Testing/CommBasic/HybridCell.results",
+    "CommBasic_Strategy26Cell": "Testing/CommBasic/Strategy26Cell.results",
     "CellBased_2D_Basic": "Testing/CellBased/2D_Basic.results",
     "CellBased_2D_Neumann": "Testing/CellBased/2D_Neumann.results",
     "CellBased_3D_Basic": "Testing/CellBased/3D_Basic.results",

@@ -18,6 +18,27 @@ def test_golden_stdout(prog, oracle):
     assert out == prog.expected()
 
 
+def test_golden_stdout_hybrid_cell(oracle):
+    """Testing/CommBasic/{HybridCell,Strategy26Cell}: 576^3 cells (1.9e8 unknowns) on one GPU; the oracle pins the same
+    program at a lower finest level (test_oracle_parity_hybrid_cell)."""
+    b = cp.GpuCells(cp.HYBRID_CELL)
+    out = cp.solve(b, oracle.print_reduced_prec)
+    b.close()
+    assert out == cp.HYBRID_CELL.expected()
+    import programs
+    assert programs.golden("CommBasic_Strategy26Cell") == cp.HYBRID_CELL.expected()
+
+
+def test_oracle_parity_hybrid_cell(oracle):
+    prog = cp.CellProgram("HybridCell", 3, False, max_level=2, F=9, kind="hybridcell", golden="CommBasic_HybridCell")
+    ref, gpu = cp.OracleCells(prog), cp.GpuCells(prog)
+    out_ref, out_gpu = cp.solve(ref, float.hex), cp.solve(gpu, float.hex)
+    assert out_gpu == out_ref  # polynomial boundary data: no libm involved, residual history bit-identical
+    assert np.array_equal(gpu.interior("u", 2), ref.interior("u", 2).reshape(gpu.interior("u", 2).shape))
+    gpu.close()
+    ref.close()
+
+
 @pytest.mark.parametrize("name,dim,neumann,lvl", [("2D_Basic", 2, False, 5), ("2D_Neumann", 2, True, 5),
                                                   ("3D_Basic", 3, False, 3), ("3D_Neumann", 3, True, 3)])
 def test_oracle_parity(name, dim, neumann, lvl, oracle):
