@@ -37,6 +37,8 @@ FILES = {
     "CommBasic_Summarize": "Testing/CommBasic/Summarize.results",
     "Poisson_2D_FD_Poisson_fromL2": "Testing/Poisson/2D_FD_Poisson_fromL2.results",
     "Poisson_2D_FD_Poisson_fromL3": "Testing/Poisson/2D_FD_Poisson_fromL3.results",
+    "Poisson_2D_FV_Poisson_fromL4": "Testing/Poisson/2D_FV_Poisson_fromL4.results",
+    "Poisson_2D_FV_Poisson_fromL2": "Testing/Poisson/2D_FV_Poisson_fromL2.results",
     "CUDA_2D_VarCoeff": "Testing/CUDA/2D_VarCoeff.results",
     "FMG_2D_ConstCoeff": "Testing/FMG/2D_ConstCoeff.results",
     "FMG_2D_Polynomial": "Testing/FMG/2D_Polynomial.results",

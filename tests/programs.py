@@ -106,6 +106,20 @@ POISSON_2D = Program(
     exact=lambda X, Y, Z: np.cos(PI * X) - np.sin(2.0 * PI * Y),
     tol=1e-10, strict=False, prints="err+res", print_count=False)
 
+# Examples/Poisson/2D_FV_Poisson_fromL4.exa4 (Testing/Poisson/2D_FV_Poisson_fromL{2,4}): the vertex-centred finite-volume
+# form of the same problem -- stencil entries vf_cellWidth_y / (0.5 * (vf_cellWidth_x + vf_cellWidth_x@[-1,0])) = 1 on the
+# uniform grid (centre 1+1+1+1), RHS scaled by vf_cellVolume, residual restricted with the integral weights
+# (NodeRestrictionForRes = 4 x full weighting).  Errors equal the FD program's, residuals are h^2 times smaller.
+def _fv_rhs(X, Y, Z):
+    vol = (X[0, 0, 1] - X[0, 0, 0]) * (Y[0, 1, 0] - Y[0, 0, 0])
+    return vol * (PI ** 2 * np.cos(PI * X) - 4.0 * PI ** 2 * np.sin(2.0 * PI * Y))
+
+
+POISSON_2D_FV = Program(
+    "Poisson2D_FV_fromL4", "Poisson_2D_FV_Poisson_fromL4",
+    dict(POISSON_2D.cfg, op="unscaled", restrict_scale=4.0),
+    rhs=_fv_rhs, bc=POISSON_2D.bc, exact=POISSON_2D.exact, tol=1e-10, strict=False, prints="err+res", print_count=False)
+
 _quad_bc = lambda X, Y, Z: ((X * X) - ((0.5 * Y) * Y)) - ((0.5 * Z) * Z)
 
 # Testing/Smoothers/RBGS.{exa4,knowledge}: 3x3x3 blocks x 3x3x3 fragments, levels 0-6 => F=9

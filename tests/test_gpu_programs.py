@@ -40,7 +40,7 @@ def _setup_pair(prog, mode, **override):
 
 
 @pytest.mark.parametrize("mode", ["library", "calls"])
-@pytest.mark.parametrize("prog", [programs.POISSON_2D, programs.SISC_2D_CONST, programs.SISC_2D_VAR,
+@pytest.mark.parametrize("prog", [programs.POISSON_2D, programs.POISSON_2D_FV, programs.SISC_2D_CONST, programs.SISC_2D_VAR,
                                   programs.SMOOTHERS_RBGS, programs.SMOOTHERS_JAC, programs.COMMBASIC_PURE,
                                   programs.BC_2D_POLY,
                                   programs.BC_2D_TRIG, programs.COMMBASIC_2D, programs.FMG_2D_CONST,

@@ -20,7 +20,7 @@ def _run(prog, og):
     return out
 
 
-@pytest.mark.parametrize("prog", [programs.POISSON_2D, programs.SISC_2D_CONST, programs.SISC_2D_VAR,
+@pytest.mark.parametrize("prog", [programs.POISSON_2D, programs.POISSON_2D_FV, programs.SISC_2D_CONST, programs.SISC_2D_VAR,
                                   programs.BC_2D_POLY, programs.BC_2D_TRIG, programs.COMMBASIC_2D,
                                   programs.FMG_2D_CONST, programs.FMG_2D_POLY, programs.BC_2D_PERIODIC],
                          ids=lambda p: p.name)
@@ -40,6 +40,7 @@ def test_identical_golden_files():
     assert g("CommBasic_PureOMP") == g("CommBasic_PureMPI")
     for name in ("Poisson_2D_FD_Poisson_fromL2", "Poisson_2D_FD_Poisson_fromL3"):
         assert g(name) == g("Poisson_2D_FD_Poisson_fromL4"), name
+    assert g("Poisson_2D_FV_Poisson_fromL2") == g("Poisson_2D_FV_Poisson_fromL4")
     cuda, cpu = g("CUDA_2D_VarCoeff"), g("SISC_2D_VarCoeff")
     assert cuda != cpu and len(cuda) == len(cpu)
     assert all(abs(float(a) - float(b)) <= 1e-3 * abs(float(b)) for a, b in zip(cuda, cpu))
