@@ -480,6 +480,17 @@ int examg_field_eval(examg_ctx *c, int h, int slot, int comp, const examg_bc_op 
   if (rc) return rc;
   if ((rc = launch_field_eval(c, *f, slot, comp, prog, n))) return rc;
   if (slot <= 0 || f->nslots == 1) {
+    // a later program for the same component supersedes the earlier one unless something in between read it
+    bool read_since = false;
+    for (size_t i = f->evals.size(); i-- > 0;) {
+      if (f->evals[i].first == comp) {
+        if (!read_since) f->evals.erase(f->evals.begin() + i);
+        break;
+      }
+      for (const examg_bc_op &o : f->evals[i].second)
+        read_since = read_since || (o.op == EXAMG_OP_COMP && (int)o.value == comp);
+    }
+    if (f->evals.size() >= 1024) f->evals.clear();  // a log this long is not an assembly recipe any more
     f->evals.emplace_back(comp, std::vector<examg_bc_op>(prog, prog + n));
     f->eval_gen++;
     // the loop also ran on the first ghost layer (global node positions): once every component was produced this
