@@ -222,6 +222,8 @@ int residual_restrict_op(examg_ctx *c, int A, int u, int rhs, int rhs_coarse, do
 int launch_jacobi(examg_ctx *c, const Stencil &s, double omega, const double *u, const double *rhs,
                   double *unext);
 int launch_rb(examg_ctx *c, const Stencil &s, double omega, double *u, const double *rhs, int color);
+int launch_color_generic(examg_ctx *c, const Stencil &s, double omega, double *u, const double *rhs, int ncol, int cx,
+                         int cy, int cz);
 int launch_restrict(examg_ctx *c, int lvl_fine, double scale, const double *rf, double *rhsc);
 int launch_prolong(examg_ctx *c, int lvl_fine, const double *uc, double *uf);
 int launch_dot(examg_ctx *c, int level, const double *a, const double *b, int red_slot);

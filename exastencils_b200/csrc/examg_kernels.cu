@@ -86,6 +86,26 @@ k_stencil(const GridArgs g, const __grid_constant__ StencilArgs st, const double
   }
 }
 
+// One colour of an n^dim-way coloured Gauss-Seidel sweep (solver_smoother_coloring = "4-way" / "8-way" / "9-way" /
+// "27-way", C/s/e/solver/l3/L3_VankaForEquation.scala:154-183): in place on the points with i_d % ncol == c_d.
+// Points of one colour are at least ncol >= 2 apart in every dimension, so a compact stencil never couples them and
+// the result does not depend on the traversal order.
+template <int NST, bool VAR>
+__global__ void __launch_bounds__(256)
+k_stencil_color(const GridArgs g, const __grid_constant__ StencilArgs st, const double *__restrict__ sf, long long sfvol,
+                double *u, const double *__restrict__ rhs, double w, int ncol, int cx, int cy, int cz, int ex, int ey,
+                int ez, int fx, int fy, int fz) {
+  const long long total = (long long)ex * ey * ez;
+  for (long long t = blockIdx.x * (long long)blockDim.x + threadIdx.x; t < total; t += (long long)gridDim.x * blockDim.x) {
+    const int i = fx + ncol * (int)(t % ex), j = fy + ncol * (int)((t / ex) % ey), k = fz + ncol * (int)(t / ((long long)ex * ey));
+    const long long p = i + (long long)g.pitch * j + g.plane * k;
+    const double acc = conv<NST, VAR>(st, sf, sfvol, u, p);
+    const double ww = VAR ? w / sf[st.centre * sfvol + p] : w;
+    u[p] = fma(ww, rhs[p] - acc, u[p]);
+  }
+  (void)cx; (void)cy; (void)cz;
+}
+
 // merges the per-block partials in index order; one block
 __global__ void __launch_bounds__(1024) k_final_sum(const dd *__restrict__ partials, int n, dd *out) {
   dd v = {0.0, 0.0};
@@ -327,6 +347,48 @@ static int launch_stencil(examg_ctx *c, const Stencil &s, const double *u, const
     k_final_sum<<<1, 1024, 0, c->stream>>>(c->partials, sh.nblocks, c->red_out + red_slot);
     EXAMG_LAUNCH_CHECK(c);
   }
+  return EXAMG_OK;
+}
+
+// colour (cx, cy, cz) of an ncol^dim-way colouring; the colour of a point is its block-local index modulo ncol
+int launch_color_generic(examg_ctx *c, const Stencil &s, double omega, double *u, const double *rhs, int ncol, int cx,
+                         int cy, int cz) {
+  const LevelGeom &g = *geom(c, s.level);
+  const GridArgs ga = grid_args_loc(c, g);
+  const StencilArgs sa = stencil_args(g, s);
+  const bool var = s.coeff_field >= 0;
+  const double *sf = var ? field_ptr(c, &c->fields[s.coeff_field], 0, 0) : nullptr;
+  const int col[3] = {cx, cy, cz};
+  int first[3], ext[3];
+  for (int d = 0; d < 3; ++d) {
+    if (d >= c->cfg.dim) { first[d] = 0; ext[d] = 1; continue; }
+    first[d] = ga.lo[d] + ((col[d] - ga.lo[d]) % ncol + ncol) % ncol;
+    ext[d] = first[d] < ga.hi[d] ? (ga.hi[d] - first[d] + ncol - 1) / ncol : 0;
+  }
+  const long long total = (long long)ext[0] * ext[1] * ext[2];
+  if (total <= 0) return EXAMG_OK;
+  long long blocks = (total + 255) / 256;
+  if (blocks > 148 * 16) blocks = 148 * 16;
+  const double w = var ? omega : omega / s.coef[s.centre];
+  const int czz = c->cfg.dim == 3 ? cz : -1;
+#define EXAMG_GOC(NST, VAR)                                                                                         \
+  k_stencil_color<NST, VAR><<<(int)blocks, 256, 0, c->stream>>>(ga, sa, sf, g.vol, u, rhs, w, ncol, cx, cy, czz, ext[0], \
+                                                                 ext[1], ext[2], first[0], first[1], first[2])
+  if (var) {
+    switch (s.nst) {
+      case 9: EXAMG_GOC(9, true); break;
+      case 27: EXAMG_GOC(27, true); break;
+      default: EXAMG_GOC(0, true); break;
+    }
+  } else {
+    switch (s.nst) {
+      case 9: EXAMG_GOC(9, false); break;
+      case 27: EXAMG_GOC(27, false); break;
+      default: EXAMG_GOC(0, false); break;
+    }
+  }
+#undef EXAMG_GOC
+  EXAMG_LAUNCH_CHECK(c);
   return EXAMG_OK;
 }
 

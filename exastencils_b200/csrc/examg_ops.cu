@@ -201,6 +201,30 @@ int examg_smooth_rb_color(examg_ctx *c, int A, int u, int rhs, double omega, int
   return launch_rb(c, *s, omega, field_ptr(c, fu, -1), field_ptr(c, fr, -1), color);
 }
 
+int examg_smooth_colored(examg_ctx *c, int A, int u, int rhs, double omega, int ncol, int nsweeps) {
+  GET_STENCIL(s, A); GET_FIELD(fu, u); GET_FIELD(fr, rhs);
+  CHECK_LEVEL(fu, s->level); CHECK_LEVEL(fr, s->level);
+  if (ncol != 2 && ncol != 3) return set_error(EXAMG_EINVAL, "examg_smooth_colored: %d colours per dimension (2 or 3)", ncol);
+  if (fu->loc != fr->loc) return set_error(EXAMG_EINVAL, "examg_smooth_colored: fields of different localisation");
+  for (int k = 0; k < s->nst; ++k)
+    for (int d = 0; d < 3; ++d)
+      if (s->off[k][d] < -1 || s->off[k][d] > 1)
+        return set_error(EXAMG_EUNSUP, "examg_smooth_colored: compact stencils only (entry [%d,%d,%d])", s->off[k][0], s->off[k][1], s->off[k][2]);
+  LocGuard lg(c, fu->loc);
+  const int nz = c->cfg.dim == 3 ? ncol : 1;
+  for (int it = 0; it < nsweeps; ++it)
+    for (int cz = 0; cz < nz; ++cz)
+      for (int cy = 0; cy < ncol; ++cy)
+        for (int cx = 0; cx < ncol; ++cx) {
+          int rc = do_exchange(c, *fu, fu->cur);
+          if (rc) return rc;
+          fu->halo_depth = 0;
+          if ((rc = launch_color_generic(c, *s, omega, field_ptr(c, fu, -1), field_ptr(c, fr, -1), ncol, cx, cy, cz))) return rc;
+          if (fu->loc == 0 && (rc = examg_apply_bc(c, u, -1))) return rc;
+        }
+  return EXAMG_OK;
+}
+
 int examg_smooth_rbgs(examg_ctx *c, int A, int u, int rhs, double omega, int nsweeps) {
   {
     GET_STENCIL(s, A); GET_FIELD(fu, u); GET_FIELD(fr, rhs);

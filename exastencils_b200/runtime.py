@@ -88,6 +88,7 @@ SIGNATURES = {
     "examg_field_advance": (C.c_int, [C.c_void_p, C.c_int]),
     "examg_field_set_bc": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_double]),
     "examg_field_set_bc_expr": (C.c_int, [C.c_void_p, C.c_int, C.POINTER(BcOp), C.c_int]),
+    "examg_smooth_colored": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_double, C.c_int, C.c_int]),
     "examg_field_eval": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.POINTER(BcOp), C.c_int]),
     "examg_apply_bc": (C.c_int, [C.c_void_p, C.c_int, C.c_int]),
     "examg_field_upload": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_void_p]),
@@ -361,6 +362,9 @@ class Context:
 
     def smooth_rbgs(self, A, u, rhs, omega, nsweeps=1):
         check(self.L.examg_smooth_rbgs(self.h, A, u, rhs, omega, nsweeps))
+
+    def smooth_colored(self, A, u, rhs, omega, colors_per_dim, nsweeps=1):
+        check(self.L.examg_smooth_colored(self.h, A, u, rhs, omega, colors_per_dim, nsweeps))
 
     def smooth_rb_color(self, A, u, rhs, omega, color):
         check(self.L.examg_smooth_rb_color(self.h, A, u, rhs, omega, color))

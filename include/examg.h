@@ -181,6 +181,13 @@ int examg_smooth_jacobi(examg_ctx *ctx, int stencil, int u, int rhs, double omeg
 int examg_smooth_rbgs(examg_ctx *ctx, int stencil, int u, int rhs, double omega, int nsweeps);
 /* a single colour half-sweep (the unfused form) */
 int examg_smooth_rb_color(examg_ctx *ctx, int stencil, int u, int rhs, double omega, int color);
+/* nsweeps x Gauss-Seidel with an n^dim-way colouring, n = colors_per_dim = 2 or 3: solver_smoother_coloring "4-way" /
+ * "9-way" (2D), "8-way" / "27-way" (3D) of the layer-3 solver generator
+ * (C/s/e/solver/l3/L3_VankaForEquation.scala:154-183).  Colours run with the last dimension slowest
+ * (C/s/e/baseExt/l4/L4_ColorLoops.scala:44-70), each { communicate; loop over Solution where i_d % n == c_d
+ * { Solution += omega/diag(A) * (RHS - A*Solution) }; apply bc }.  For compact stencils with diagonal entries
+ * (9- and 27-point), which two colours do not decouple.                                            */
+int examg_smooth_colored(examg_ctx *ctx, int stencil, int u, int rhs, double omega, int colors_per_dim, int nsweeps);
 /* RHS@coarser = scale * NodeRestriction * Residual
  * (C/s/e/operator/l4/L4_DefaultRestriction.scala:29-90)                     */
 int examg_restrict(examg_ctx *ctx, int res_fine, int rhs_coarse, double scale);

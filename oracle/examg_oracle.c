@@ -189,6 +189,33 @@ void og_smooth_rb(const int n[3], const og_stencil *st, const double *sf,
     }
 }
 
+/* One colour (cx, cy, cz) of an ncol^dim-way coloured Gauss-Seidel sweep: in place on the loop points with
+ * i_d % ncol == c_d (solver_smoother_coloring "4-way" ... "27-way", C/s/e/solver/l3/L3_VankaForEquation.scala:154-183) */
+void og_smooth_color(const int n[3], const og_stencil *st, const double *sf, double omega, double *u,
+                     const double *rhs, int ncol, int cx, int cy, int cz) {
+  ptrdiff_t lo[OG_MAX_ST];
+  og_lin_offsets(n, st, lo);
+  const size_t size = og_size(n);
+  const int nst = st->nst;
+  const int c = og_centre(st);
+  const double wconst = omega / st->coef[c];
+  OG_LOOP_BEGIN(n)
+  for (int k = zl; k < zh; ++k) {
+    if (n[2] > 1 && k % ncol != cz) continue;
+    for (int j = yl; j < yh; ++j) {
+      if (j % ncol != cy) continue;
+      size_t row = (size_t)n[0] * ((size_t)j + (size_t)n[1] * (size_t)k);
+      for (int i = xl; i < xh; ++i) {
+        if (i % ncol != cx) continue;
+        size_t p = row + i;
+        double w = sf ? omega / sf[(size_t)c * size + p] : wconst;
+        double r = rhs[p] - OG_CONV(i, j, k, p);
+        u[p] = fma(w, r, u[p]);
+      }
+    }
+  }
+}
+
 /* ---------- reductions ---------------------------------------------------- */
 
 /* double-double accumulator: (hi, lo) += x via Knuth TwoSum */

@@ -78,6 +78,8 @@ def lib():
     L.og_dot.restype = C.c_double
     L.og_max_abs_diff.argtypes = [i3, dp, dp]
     L.og_max_abs_diff.restype = C.c_double
+    L.og_smooth_color.argtypes = [i3, stp, dp, C.c_double, dp, dp, C.c_int, C.c_int, C.c_int, C.c_int]
+    L.og_smooth_color.restype = None
     L.og_cell_apply_bc.argtypes = [C.c_int, i3, dp, C.c_int, C.POINTER(dp)]
     L.og_cell_apply_bc.restype = None
     L.og_cell_restrict.argtypes = [C.c_int, i3, i3, dp, dp]
@@ -151,6 +153,15 @@ def smooth_jacobi(st, omega, u, rhs, sf=None):
 def smooth_rb(st, omega, u, rhs, color, sf=None):
     """In place on u."""
     lib().og_smooth_rb(_n(u), C.byref(st), _sf(sf), omega, _dp(u), _dp(rhs), int(color))
+    return u
+
+
+def smooth_colored(st, omega, u, rhs, ncol, dim, sf=None):
+    """One n^dim-way coloured Gauss-Seidel sweep in place on u: colours with the last dimension slowest."""
+    for cz in range(ncol if dim == 3 else 1):
+        for cy in range(ncol):
+            for cx in range(ncol):
+                lib().og_smooth_color(_n(u), C.byref(st), _sf(sf), omega, _dp(u), _dp(rhs), ncol, cx, cy, cz)
     return u
 
 

@@ -421,3 +421,48 @@ def test_timers():
     with pytest.raises(rt.ExaMGError):
         ctx.timer_total_ms("nope")
     ctx.close()
+
+
+@pytest.mark.parametrize("dim,cells,lvl,npts,ncol", [(2, (3, 5), 3, 9, 2), (2, (4, 4), 4, 9, 3), (3, (1, 1, 1), 4, 27, 2),
+                                                     (3, (5, 3, 2), 2, 27, 3), (3, (1, 1, 1), 5, 7, 2)])
+@pytest.mark.parametrize("var", [False, True], ids=["const", "stencilfield"])
+def test_colored_gauss_seidel(dim, cells, lvl, npts, ncol, var, oracle):
+    """solver_smoother_coloring 4-/9-way (2D) and 8-/27-way (3D): n^dim colours, last dimension slowest, in place
+    (C/s/e/solver/l3/L3_VankaForEquation.scala:154-183) -- against the oracle, bit for bit, and contracting."""
+    og = oracle
+    ctx = _ctx(dim, cells, lvl, lvl)
+    shape = ctx.shape(lvl)
+    offs = _stencil_offsets(dim, npts)
+    centre = offs.index((0, 0, 0))
+    seed = 7000 * lvl + 10 * sum(cells) + npts + ncol
+    coeffs = -np.abs(_rand(npts, seed)) - 0.1
+    coeffs[centre] = -np.sum(coeffs) + coeffs[centre] + 1.0  # diagonally dominant
+    sf = None
+    fu, ff = ctx.field_create("u", lvl), ctx.field_create("rhs", lvl)
+    if var:
+        sf = -np.abs(_rand((npts,) + shape, seed + 5)) - 0.1
+        sf[centre] = -(np.sum(sf, axis=0) - sf[centre]) + 1.0
+        sf = np.ascontiguousarray(sf)
+        cf = ctx.field_create("coef", lvl, 1, npts)
+        ctx.upload(cf, sf)
+        A = ctx.stencil_field(lvl, offs, cf)
+        st = og.Stencil.make(offs, np.zeros(npts))
+    else:
+        A = ctx.stencil_const(lvl, offs, list(coeffs))
+        st = og.Stencil.make(offs, list(coeffs))
+    u, rhs = _rand(shape, seed + 1), _rand(shape, seed + 2)
+    ctx.upload(fu, u)
+    ctx.upload(ff, rhs)
+    ctx.smooth_colored(A, fu, ff, 0.9, ncol, 2)
+    e = u.copy()
+    for _ in range(2):
+        og.smooth_colored(st, 0.9, e, rhs, ncol, dim, sf)
+    got = ctx.download(fu, lvl)
+    assert np.array_equal(got, e)
+    r0 = og.residual(st, u, rhs, sf)
+    r1 = og.residual(st, got, rhs, sf)
+    assert og.dot(r1, r1) < og.dot(r0, r0)
+    from exastencils_b200 import runtime as rt
+    with pytest.raises(rt.ExaMGError):
+        ctx.smooth_colored(A, fu, ff, 0.9, 4, 1)
+    ctx.close()
