@@ -142,5 +142,92 @@ __device__ __forceinline__ int cg_device(const CgArgs &a, const double *__restri
   return iters;
 }
 
+// BiCGStab of the layer-3 generator (solver_cgs = "BiCGStab", C/s/e/solver/l3/L3_BiCGStabForEquation.scala:36-198):
+// resHat = r0; rho = rhoOld = alpha = beta = omega = 1; v = p = 0; per step
+//   rho = <resHat, r>; beta = (rho/rhoOld)*(alpha/omega); p = r + beta*(p - omega*v); v = A p; alpha = rho/<resHat, v>;
+//   s = r - alpha*v; t = A s; omega = <t,s>/<t,t>; u += alpha*p + omega*s; r = s - omega*t;
+//   stop at ||r|| <= rel_tol * ||r0||.
+// Association: p = fma(beta, fma(-omega, v, p), r); s = fma(-alpha, v, r); u = fma(omega, s, fma(alpha, p, u));
+// r = fma(-omega, t, s); sums in double-double.  All threads of the block must call it; returns the step count.
+template <bool VAR>
+__device__ __forceinline__ int bicgstab_device(const CgArgs &a, const double *__restrict__ sf, double *u, const double *rhs,
+                                               double *res, double *v, double *p, double *sv, double *tv, double *rhat) {
+  const GridArgs &g = a.g;
+  const int ex = g.hi[0] - g.lo[0], ey = g.hi[1] - g.lo[1], ez = g.hi[2] - g.lo[2];
+  const int total = ex * ey * ez;
+  const int tid = threadIdx.x, nt = blockDim.x;
+  const bool per = a.per[0] || a.per[1] || a.per[2];
+  if (per) cg_refresh(a, u);
+  dd part = {0.0, 0.0};
+  for (int t = tid; t < total; t += nt) {
+    const long long q = cg_point(g, t, ex, ey);
+    const double r = rhs[q] - cg_conv<VAR>(a, sf, u, q);
+    res[q] = r;
+    rhat[q] = r;
+    v[q] = 0.0;
+    p[q] = 0.0;
+    dd_add(part, !per || cg_counts(g, t, ex, ey) ? r * r : 0.0);
+  }
+  double curRes = sqrt(cg_sum(part));
+  const double initRes = curRes;
+  if (curRes <= 0.0) return 0;  // solver_cgs_absResThreshold = 0
+  double rho = 1.0, rhoOld = 1.0, alpha = 1.0, omega = 1.0;
+  int iters = 0;
+  for (int step = 0; step < a.max_it; ++step) {
+    iters = step + 1;
+    rhoOld = rho;
+    dd pr = {0.0, 0.0};
+    for (int t = tid; t < total; t += nt) {
+      const long long q = cg_point(g, t, ex, ey);
+      dd_add(pr, !per || cg_counts(g, t, ex, ey) ? rhat[q] * res[q] : 0.0);
+    }
+    rho = cg_sum(pr);
+    const double beta = (rho / rhoOld) * (alpha / omega);
+    for (int t = tid; t < total; t += nt) {
+      const long long q = cg_point(g, t, ex, ey);
+      p[q] = fma(beta, fma(-omega, v[q], p[q]), res[q]);
+    }
+    if (per) cg_refresh(a, p);
+    __syncthreads();
+    dd pa = {0.0, 0.0};
+    for (int t = tid; t < total; t += nt) {
+      const long long q = cg_point(g, t, ex, ey);
+      const double w = cg_conv<VAR>(a, sf, p, q);
+      v[q] = w;
+      dd_add(pa, !per || cg_counts(g, t, ex, ey) ? rhat[q] * w : 0.0);
+    }
+    alpha = rho / cg_sum(pa);
+    for (int t = tid; t < total; t += nt) {
+      const long long q = cg_point(g, t, ex, ey);
+      sv[q] = fma(-alpha, v[q], res[q]);
+    }
+    if (per) cg_refresh(a, sv);
+    __syncthreads();
+    dd pn = {0.0, 0.0}, pd = {0.0, 0.0};
+    for (int t = tid; t < total; t += nt) {
+      const long long q = cg_point(g, t, ex, ey);
+      const double w = cg_conv<VAR>(a, sf, sv, q);
+      tv[q] = w;
+      const bool cnt = !per || cg_counts(g, t, ex, ey);
+      dd_add(pn, cnt ? w * sv[q] : 0.0);
+      dd_add(pd, cnt ? w * w : 0.0);
+    }
+    const double omegaNom = cg_sum(pn);
+    const double omegaDenom = cg_sum(pd);
+    omega = omegaNom / omegaDenom;
+    dd pq = {0.0, 0.0};
+    for (int t = tid; t < total; t += nt) {
+      const long long q = cg_point(g, t, ex, ey);
+      u[q] = fma(omega, sv[q], fma(alpha, p[q], u[q]));
+      const double r = fma(-omega, tv[q], sv[q]);
+      res[q] = r;
+      dd_add(pq, !per || cg_counts(g, t, ex, ey) ? r * r : 0.0);
+    }
+    curRes = sqrt(cg_sum(pq));
+    if (curRes <= a.rel_tol * initRes) break;
+    __syncthreads();
+  }
+  return iters;
+}
 
 }  // namespace examg

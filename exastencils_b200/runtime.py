@@ -88,6 +88,8 @@ SIGNATURES = {
     "examg_field_advance": (C.c_int, [C.c_void_p, C.c_int]),
     "examg_field_set_bc": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_double]),
     "examg_field_set_bc_expr": (C.c_int, [C.c_void_p, C.c_int, C.POINTER(BcOp), C.c_int]),
+    "examg_bicgstab_coarse": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_int), C.c_int,
+                                        C.c_double, C.POINTER(C.c_int)]),
     "examg_smooth_colored": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_double, C.c_int, C.c_int]),
     "examg_field_eval": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.POINTER(BcOp), C.c_int]),
     "examg_apply_bc": (C.c_int, [C.c_void_p, C.c_int, C.c_int]),
@@ -410,6 +412,12 @@ class Context:
         return its.value
 
     # -- coupled two-unknown systems on cell fields (optical flow)
+    def bicgstab_coarse(self, A, u, rhs, res, tmp, max_it, rel_tol):
+        """tmp = (v, p, s, t, resHat); returns the number of steps."""
+        it = C.c_int()
+        check(self.L.examg_bicgstab_coarse(self.h, A, u, rhs, res, (C.c_int * 5)(*tmp), max_it, rel_tol, C.byref(it)))
+        return it.value
+
     @staticmethod
     def _ints(v):
         return (C.c_int * len(v))(*[int(x) for x in v])

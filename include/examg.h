@@ -220,6 +220,11 @@ int examg_exchange_depth(examg_ctx *ctx, int field, int slot, int depth);
 int examg_cg_coarse(examg_ctx *ctx, int stencil, int u, int rhs, int res, int p, int ap,
                     int max_it, double rel_tol, int *iters_out);
 
+/* The same with BiCGStab (solver_cgs = "BiCGStab", C/s/e/solver/l3/L3_BiCGStabForEquation.scala:36-198) for operators
+ * that are not symmetric positive definite; tmp = { v, p, s, t, resHat } (fields of the level).               */
+int examg_bicgstab_coarse(examg_ctx *ctx, int stencil, int u, int rhs, int res, const int tmp[5], int max_it,
+                          double rel_tol, int *iters_out);
+
 /* ---- whole cycle: Solve@finest / mgCycle@lvl as one library object -----------
  * (C/s/e/solver/l3/L3_SolverForEquation.scala:259-395).  Creates the field set
  * of the L4 programs on every level (Solution[slots], RHS, Residual and, on the

@@ -453,3 +453,59 @@ void og_cell_prolong_add(int dim, const int nf[3], const int nc[3], const double
         uf[(size_t)(i + 1) + (size_t)nf[0] * ((size_t)(j + 1) + (size_t)nf[1] * (size_t)(dim == 3 ? k + 1 : 0))] += v;
       }
 }
+
+/* ---------- BiCGStab of the layer-3 generator ----------------------------------------------------------------
+ * solver_cgs = "BiCGStab", C/s/e/solver/l3/L3_BiCGStabForEquation.scala:36-198 (statement order and start values as
+ * generated; solver_cgs_absResThreshold = 0).  Elementwise updates in the association the library uses:
+ * p = fma(beta, fma(-omega, v, p), r); s = fma(-alpha, v, r); u = fma(omega, s, fma(alpha, p, u)); r = fma(-omega, t, s).
+ * Returns the number of steps. */
+int og_bicgstab(const int n[3], const og_stencil *st, const double *sf, double *u, const double *rhs, double *res,
+                int max_it, double rel_tol) {
+  const size_t size = og_size(n);
+  double *v = (double *)calloc(size, sizeof(double)), *p = (double *)calloc(size, sizeof(double));
+  double *s = (double *)calloc(size, sizeof(double)), *t = (double *)calloc(size, sizeof(double));
+  double *rhat = (double *)calloc(size, sizeof(double));
+  OG_LOOP_BEGIN(n)
+  og_residual(n, st, sf, u, rhs, res);
+  double curRes = sqrt(og_dot(n, res, res));
+  const double initRes = curRes;
+  int iters = 0;
+  if (curRes > 0.0) {
+    og_copy_interior(n, res, rhat);
+    double rho = 1.0, rhoOld = 1.0, alpha = 1.0, omega = 1.0;
+    for (int step = 0; step < max_it; ++step) {
+      iters = step + 1;
+      rhoOld = rho;
+      rho = og_dot(n, rhat, res);
+      const double beta = (rho / rhoOld) * (alpha / omega);
+      for (int k = zl; k < zh; ++k)
+        for (int j = yl; j < yh; ++j)
+          for (int i = xl; i < xh; ++i) {
+            size_t q = (size_t)i + (size_t)n[0] * ((size_t)j + (size_t)n[1] * (size_t)k);
+            p[q] = fma(beta, fma(-omega, v[q], p[q]), res[q]);
+          }
+      og_apply(n, st, sf, p, v);
+      alpha = rho / og_dot(n, rhat, v);
+      for (int k = zl; k < zh; ++k)
+        for (int j = yl; j < yh; ++j)
+          for (int i = xl; i < xh; ++i) {
+            size_t q = (size_t)i + (size_t)n[0] * ((size_t)j + (size_t)n[1] * (size_t)k);
+            s[q] = fma(-alpha, v[q], res[q]);
+          }
+      og_apply(n, st, sf, s, t);
+      const double omegaNom = og_dot(n, t, s), omegaDenom = og_dot(n, t, t);
+      omega = omegaNom / omegaDenom;
+      for (int k = zl; k < zh; ++k)
+        for (int j = yl; j < yh; ++j)
+          for (int i = xl; i < xh; ++i) {
+            size_t q = (size_t)i + (size_t)n[0] * ((size_t)j + (size_t)n[1] * (size_t)k);
+            u[q] = fma(omega, s[q], fma(alpha, p[q], u[q]));
+            res[q] = fma(-omega, t[q], s[q]);
+          }
+      curRes = sqrt(og_dot(n, res, res));
+      if (curRes <= rel_tol * initRes) break;
+    }
+  }
+  free(v); free(p); free(s); free(t); free(rhat);
+  return iters;
+}

@@ -466,3 +466,45 @@ def test_colored_gauss_seidel(dim, cells, lvl, npts, ncol, var, oracle):
     with pytest.raises(rt.ExaMGError):
         ctx.smooth_colored(A, fu, ff, 0.9, 4, 1)
     ctx.close()
+
+
+@pytest.mark.parametrize("dim,cells,lvl,npts,var", [(2, (4, 4), 2, 9, False), (3, (3, 2, 5), 1, 7, True),
+                                                    (3, (1, 1, 1), 3, 27, True), (2, (1, 1), 4, 5, False)])
+def test_bicgstab_coarse(dim, cells, lvl, npts, var, oracle):
+    """solver_cgs = "BiCGStab" (C/s/e/solver/l3/L3_BiCGStabForEquation.scala:36-198) on a NON-symmetric operator
+    (convection-like perturbation of the stencil entries): step count, Solution and Residual against the oracle."""
+    og = oracle
+    ctx = _ctx(dim, cells, lvl, lvl)
+    shape = ctx.shape(lvl)
+    offs = _stencil_offsets(dim, npts)
+    centre = offs.index((0, 0, 0))
+    seed = 9000 * lvl + 10 * sum(cells) + npts
+    coeffs = -np.abs(_rand(npts, seed)) - 0.1   # unsymmetric: the entry of +d differs from the entry of -d
+    coeffs[centre] = -np.sum(coeffs) + coeffs[centre] + 0.5
+    sf = None
+    if var:
+        sf = -np.abs(_rand((npts,) + shape, seed + 5)) - 0.1
+        sf[centre] = -(np.sum(sf, axis=0) - sf[centre]) + 0.5
+        sf = np.ascontiguousarray(sf)
+        cf = ctx.field_create("coef", lvl, 1, npts)
+        ctx.upload(cf, sf)
+        A = ctx.stencil_field(lvl, offs, cf)
+        st = og.Stencil.make(offs, np.zeros(npts))
+    else:
+        A = ctx.stencil_const(lvl, offs, list(coeffs))
+        st = og.Stencil.make(offs, list(coeffs))
+    fu, ff, fr = ctx.field_create("u", lvl), ctx.field_create("rhs", lvl), ctx.field_create("res", lvl)
+    tmp = [ctx.field_create("t%d" % k, lvl) for k in range(5)]
+    u, rhs = _rand(shape, seed + 1), _rand(shape, seed + 2)
+    ctx.upload(fu, u)
+    ctx.upload(ff, rhs)
+    its = ctx.bicgstab_coarse(A, fu, ff, fr, tmp, 200, 1e-8)
+    e = u.copy()
+    its_ref, res_ref = og.bicgstab(st, e, rhs, 200, 1e-8, sf)
+    assert its == its_ref and 1 <= its < 200
+    assert np.array_equal(ctx.download(fu, lvl), e)
+    inner = (slice(1, -1),) * 3 if dim == 3 else (slice(None), slice(1, -1), slice(1, -1))
+    assert np.array_equal(ctx.download(fr, lvl)[inner], res_ref[inner])
+    r0 = og.residual(st, u, rhs, sf)
+    assert og.dot(res_ref, res_ref) <= 1e-15 * og.dot(r0, r0)
+    ctx.close()
