@@ -230,4 +230,83 @@ __device__ __forceinline__ int bicgstab_device(const CgArgs &a, const double *__
   return iters;
 }
 
+// Conjugate residuals of the layer-3 generator (solver_cgs = "ConjugateResidual",
+// C/s/e/solver/l3/L3_ConjugateResidualForEquation.scala:36-170): p = r; ap = A p; ar = A r; per step
+//   alpha = <r, ar> / <ap, ap>; u += alpha p; r -= alpha ap; stop at ||r|| <= rel_tol ||r0||;
+//   ar = A r; beta = <r, ar> / <r, ar>_old; p = r + beta p; ap = ar + beta ap.
+// Association: u = fma(alpha, p, u); r = fma(-alpha, ap, r); p = fma(beta, p, r); ap = fma(beta, ap, ar).
+template <bool VAR>
+__device__ __forceinline__ int cr_device(const CgArgs &a, const double *__restrict__ sf, double *u, const double *rhs,
+                                         double *res, double *p, double *ap, double *ar) {
+  const GridArgs &g = a.g;
+  const int ex = g.hi[0] - g.lo[0], ey = g.hi[1] - g.lo[1], ez = g.hi[2] - g.lo[2];
+  const int total = ex * ey * ez;
+  const int tid = threadIdx.x, nt = blockDim.x;
+  const bool per = a.per[0] || a.per[1] || a.per[2];
+  if (per) cg_refresh(a, u);
+  dd part = {0.0, 0.0};
+  for (int t = tid; t < total; t += nt) {
+    const long long q = cg_point(g, t, ex, ey);
+    const double r = rhs[q] - cg_conv<VAR>(a, sf, u, q);
+    res[q] = r;
+    p[q] = r;
+    dd_add(part, !per || cg_counts(g, t, ex, ey) ? r * r : 0.0);
+  }
+  double curRes = sqrt(cg_sum(part));
+  const double initRes = curRes;
+  if (curRes <= 0.0) return 0;
+  if (per) cg_refresh(a, p);
+  if (per) cg_refresh(a, res);
+  __syncthreads();
+  for (int t = tid; t < total; t += nt) {
+    const long long q = cg_point(g, t, ex, ey);
+    const double w = cg_conv<VAR>(a, sf, p, q);
+    ap[q] = w;
+    ar[q] = w;  // p == r
+  }
+  __syncthreads();
+  int iters = 0;
+  for (int step = 0; step < a.max_it; ++step) {
+    iters = step + 1;
+    dd pn = {0.0, 0.0}, pd = {0.0, 0.0};
+    for (int t = tid; t < total; t += nt) {
+      const long long q = cg_point(g, t, ex, ey);
+      const bool cnt = !per || cg_counts(g, t, ex, ey);
+      dd_add(pn, cnt ? res[q] * ar[q] : 0.0);
+      dd_add(pd, cnt ? ap[q] * ap[q] : 0.0);
+    }
+    const double alphaNom = cg_sum(pn);
+    const double alphaDenom = cg_sum(pd);
+    const double alpha = alphaNom / alphaDenom;
+    dd pr = {0.0, 0.0};
+    for (int t = tid; t < total; t += nt) {
+      const long long q = cg_point(g, t, ex, ey);
+      u[q] = fma(alpha, p[q], u[q]);
+      const double r = fma(-alpha, ap[q], res[q]);
+      res[q] = r;
+      dd_add(pr, !per || cg_counts(g, t, ex, ey) ? r * r : 0.0);
+    }
+    const double nextRes = sqrt(cg_sum(pr));
+    if (nextRes <= a.rel_tol * initRes) break;
+    if (per) cg_refresh(a, res);
+    __syncthreads();
+    dd pb = {0.0, 0.0};
+    for (int t = tid; t < total; t += nt) {
+      const long long q = cg_point(g, t, ex, ey);
+      const double w = cg_conv<VAR>(a, sf, res, q);
+      ar[q] = w;
+      dd_add(pb, !per || cg_counts(g, t, ex, ey) ? res[q] * w : 0.0);
+    }
+    const double beta = cg_sum(pb) / alphaNom;
+    for (int t = tid; t < total; t += nt) {
+      const long long q = cg_point(g, t, ex, ey);
+      p[q] = fma(beta, p[q], res[q]);
+      ap[q] = fma(beta, ap[q], ar[q]);
+    }
+    curRes = nextRes;
+    __syncthreads();
+  }
+  return iters;
+}
+
 }  // namespace examg

@@ -236,6 +236,8 @@ int launch_bc_cell(examg_ctx *c, const Field &f, int slot);  // 2D Neumann ghost
 int launch_bc_cell_generic(examg_ctx *c, const Field &f, int slot);  // Dirichlet / Neumann faces, 2D and 3D
 int launch_cg(examg_ctx *c, const Stencil &s, double *u, const double *rhs, double *res, double *p,
               double *ap, int max_it, double rel_tol);
+int launch_cr(examg_ctx *c, const Stencil &s, double *u, const double *rhs, double *res, double *const tmp[3], int max_it,
+              double rel_tol);
 int launch_bicgstab(examg_ctx *c, const Stencil &s, double *u, const double *rhs, double *res, double *const tmp[5],
                     int max_it, double rel_tol);
 // communicate: `depth` ghost layers (+ the duplicate layer) per side, 1 <= depth <= GHOST

@@ -336,6 +336,31 @@ int examg_exchange_depth(examg_ctx *c, int field, int slot, int depth) {
   return do_exchange(c, *f, slot < 0 ? f->cur : slot, depth);
 }
 
+int examg_cr_coarse(examg_ctx *c, int A, int u, int rhs, int res, const int tmp[3], int max_it, double rel_tol,
+                    int *iters_out) {
+  GET_STENCIL(s, A); GET_FIELD(fu, u); GET_FIELD(fr, rhs); GET_FIELD(fres, res);
+  CHECK_LEVEL(fu, s->level); CHECK_LEVEL(fr, s->level); CHECK_LEVEL(fres, s->level);
+  if (!tmp) return set_error(EXAMG_EINVAL, "examg_cr_coarse: null tmp");
+  if (fu->loc != 0) return set_error(EXAMG_EUNSUP, "examg_cr_coarse: node-localised fields");
+  double *tp[3];
+  for (int k = 0; k < 3; ++k) {
+    Field *ft = get_field(c, tmp[k]);
+    if (!ft || ft->level != s->level || ft->loc != 0) return set_error(EXAMG_EINVAL, "examg_cr_coarse: tmp[%d]", k);
+    for (int j = 0; j < k; ++j)
+      if (tmp[j] == tmp[k]) return set_error(EXAMG_EINVAL, "examg_cr_coarse: tmp fields must be distinct");
+    tp[k] = field_ptr(c, ft, -1);
+    ft->halo_depth = 0;
+  }
+  fu->halo_depth = 0;
+  fres->halo_depth = 0;
+  int rc = launch_cr(c, *s, field_ptr(c, fu, -1), field_ptr(c, fr, -1), field_ptr(c, fres, -1), tp, max_it, rel_tol);
+  if (rc || !iters_out) return rc;
+  EXAMG_CUDA(cudaMemcpyAsync(c->int_host, c->int_out, sizeof(int), cudaMemcpyDeviceToHost, c->stream));
+  EXAMG_CUDA(cudaStreamSynchronize(c->stream));
+  *iters_out = c->int_host[0];
+  return EXAMG_OK;
+}
+
 int examg_bicgstab_coarse(examg_ctx *c, int A, int u, int rhs, int res, const int tmp[5], int max_it, double rel_tol,
                           int *iters_out) {
   GET_STENCIL(s, A); GET_FIELD(fu, u); GET_FIELD(fr, rhs); GET_FIELD(fres, res);

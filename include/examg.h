@@ -224,6 +224,10 @@ int examg_cg_coarse(examg_ctx *ctx, int stencil, int u, int rhs, int res, int p,
  * that are not symmetric positive definite; tmp = { v, p, s, t, resHat } (fields of the level).               */
 int examg_bicgstab_coarse(examg_ctx *ctx, int stencil, int u, int rhs, int res, const int tmp[5], int max_it,
                           double rel_tol, int *iters_out);
+/* Conjugate residuals (solver_cgs = "ConjugateResidual", C/s/e/solver/l3/L3_ConjugateResidualForEquation.scala:36-170) for
+ * symmetric, possibly indefinite operators; tmp = { p, ap, ar }.                                              */
+int examg_cr_coarse(examg_ctx *ctx, int stencil, int u, int rhs, int res, const int tmp[3], int max_it, double rel_tol,
+                    int *iters_out);
 
 /* ---- whole cycle: Solve@finest / mgCycle@lvl as one library object -----------
  * (C/s/e/solver/l3/L3_SolverForEquation.scala:259-395).  Creates the field set

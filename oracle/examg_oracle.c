@@ -509,3 +509,38 @@ int og_bicgstab(const int n[3], const og_stencil *st, const double *sf, double *
   free(v); free(p); free(s); free(t); free(rhat);
   return iters;
 }
+
+/* ---------- conjugate residuals of the layer-3 generator -----------------------------------------------------
+ * solver_cgs = "ConjugateResidual", C/s/e/solver/l3/L3_ConjugateResidualForEquation.scala:36-170.  Association as in the
+ * library: u = fma(alpha, p, u); r = fma(-alpha, ap, r); p = fma(beta, p, r); ap = fma(beta, ap, ar). */
+int og_cr(const int n[3], const og_stencil *st, const double *sf, double *u, const double *rhs, double *res, int max_it,
+          double rel_tol) {
+  const size_t size = og_size(n);
+  double *p = (double *)calloc(size, sizeof(double)), *ap = (double *)calloc(size, sizeof(double));
+  double *ar = (double *)calloc(size, sizeof(double));
+  og_residual(n, st, sf, u, rhs, res);
+  double curRes = sqrt(og_dot(n, res, res));
+  const double initRes = curRes;
+  int iters = 0;
+  if (curRes > 0.0) {
+    og_copy_interior(n, res, p);
+    og_apply(n, st, sf, p, ap);
+    og_apply(n, st, sf, res, ar);
+    for (int step = 0; step < max_it; ++step) {
+      iters = step + 1;
+      const double alphaNom = og_dot(n, res, ar), alphaDenom = og_dot(n, ap, ap);
+      const double alpha = alphaNom / alphaDenom;
+      og_axpy(n, alpha, p, u);
+      og_axpy(n, -alpha, ap, res);
+      const double nextRes = sqrt(og_dot(n, res, res));
+      if (nextRes <= rel_tol * initRes) break;
+      og_apply(n, st, sf, res, ar);
+      const double beta = og_dot(n, res, ar) / alphaNom;
+      og_xpay(n, res, beta, p);   /* p = r + beta p */
+      og_xpay(n, ar, beta, ap);   /* ap = ar + beta ap */
+      curRes = nextRes;
+    }
+  }
+  free(p); free(ap); free(ar);
+  return iters;
+}

@@ -84,6 +84,8 @@ double og_dot(const int n[3], const double *a, const double *b);
 double og_max_abs_diff(const int n[3], const double *a, const double *b);
 void og_smooth_color(const int n[3], const og_stencil *st, const double *sf, double omega, double *u,
                      const double *rhs, int ncol, int cx, int cy, int cz);
+int og_cr(const int n[3], const og_stencil *st, const double *sf, double *u, const double *rhs, double *res, int max_it,
+          double rel_tol);
 int og_bicgstab(const int n[3], const og_stencil *st, const double *sf, double *u, const double *rhs, double *res,
                 int max_it, double rel_tol);
 /* cell-centred fields: padded arrays (cells + 2 per dimension), see examg_oracle.c */

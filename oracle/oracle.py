@@ -78,6 +78,8 @@ def lib():
     L.og_dot.restype = C.c_double
     L.og_max_abs_diff.argtypes = [i3, dp, dp]
     L.og_max_abs_diff.restype = C.c_double
+    L.og_cr.argtypes = [i3, stp, dp, dp, dp, dp, C.c_int, C.c_double]
+    L.og_cr.restype = C.c_int
     L.og_bicgstab.argtypes = [i3, stp, dp, dp, dp, dp, C.c_int, C.c_double]
     L.og_bicgstab.restype = C.c_int
     L.og_smooth_color.argtypes = [i3, stp, dp, C.c_double, dp, dp, C.c_int, C.c_int, C.c_int, C.c_int]
@@ -165,6 +167,13 @@ def smooth_colored(st, omega, u, rhs, ncol, dim, sf=None):
             for cx in range(ncol):
                 lib().og_smooth_color(_n(u), C.byref(st), _sf(sf), omega, _dp(u), _dp(rhs), ncol, cx, cy, cz)
     return u
+
+
+def conjugate_residual(st, u, rhs, max_it, rel_tol, sf=None):
+    """In place on u; returns (steps, residual field)."""
+    res = np.zeros_like(u)
+    it = lib().og_cr(_n(u), C.byref(st), _sf(sf), _dp(u), _dp(rhs), _dp(res), int(max_it), float(rel_tol))
+    return it, res
 
 
 def bicgstab(st, u, rhs, max_it, rel_tol, sf=None):

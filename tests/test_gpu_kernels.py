@@ -508,3 +508,32 @@ def test_bicgstab_coarse(dim, cells, lvl, npts, var, oracle):
     r0 = og.residual(st, u, rhs, sf)
     assert og.dot(res_ref, res_ref) <= 1e-15 * og.dot(r0, r0)
     ctx.close()
+
+
+@pytest.mark.parametrize("dim,cells,lvl,npts", [(2, (4, 4), 2, 5), (3, (3, 2, 5), 1, 7), (3, (1, 1, 1), 3, 27)])
+def test_conjugate_residual_coarse(dim, cells, lvl, npts, oracle):
+    """solver_cgs = "ConjugateResidual" (C/s/e/solver/l3/L3_ConjugateResidualForEquation.scala:36-170) on a symmetric
+    operator: step count, Solution and Residual against the oracle, bit for bit."""
+    og = oracle
+    ctx = _ctx(dim, cells, lvl, lvl)
+    shape = ctx.shape(lvl)
+    offs = _stencil_offsets(dim, npts)
+    centre = offs.index((0, 0, 0))
+    coeffs = np.array([-1.0 / (1 + sum(abs(v) for v in o)) for o in offs])  # symmetric: depends on |offset| only
+    coeffs[centre] = -(np.sum(coeffs) - coeffs[centre]) + 0.25
+    A = ctx.stencil_const(lvl, offs, list(coeffs))
+    st = og.Stencil.make(offs, list(coeffs))
+    fu, ff, fr = ctx.field_create("u", lvl), ctx.field_create("rhs", lvl), ctx.field_create("res", lvl)
+    tmp = [ctx.field_create("t%d" % k, lvl) for k in range(3)]
+    seed = 9500 * lvl + npts
+    u, rhs = _rand(shape, seed + 1), _rand(shape, seed + 2)
+    ctx.upload(fu, u)
+    ctx.upload(ff, rhs)
+    its = ctx.cr_coarse(A, fu, ff, fr, tmp, 300, 1e-8)
+    e = u.copy()
+    its_ref, res_ref = og.conjugate_residual(st, e, rhs, 300, 1e-8)
+    assert its == its_ref and 1 <= its < 300
+    assert np.array_equal(ctx.download(fu, lvl), e)
+    inner = (slice(1, -1),) * 3 if dim == 3 else (slice(None), slice(1, -1), slice(1, -1))
+    assert np.array_equal(ctx.download(fr, lvl)[inner], res_ref[inner])
+    ctx.close()
