@@ -66,6 +66,44 @@ int launch_cr(examg_ctx *c, const Stencil &s, double *u, const double *rhs, doub
   return EXAMG_OK;
 }
 
+template <bool VAR>
+__global__ void __launch_bounds__(1024)
+k_minres(const __grid_constant__ CgArgs a, const double *__restrict__ sf, double *u, const double *__restrict__ rhs,
+         double *res, double *w0, double *w1, double *w2, double *w3, double *w4, double *w5, double *av, int *iters_out) {
+  const int iters = minres_device<VAR>(a, sf, u, rhs, res, w0, w1, w2, w3, w4, w5, av);
+  if (threadIdx.x == 0) *iters_out = iters;
+}
+
+int launch_minres(examg_ctx *c, const Stencil &s, double *u, const double *rhs, double *res, double *const tmp[7],
+                  int max_it, double rel_tol) {
+  const LevelGeom &g = *geom(c, s.level);
+  if (c->world > 1)
+    return set_error(EXAMG_EUNSUP, "examg_minres_coarse: the coarse solve runs on the agglomerated (single-block) grid");
+  const long long total = (long long)(g.hi[0] - g.lo[0]) * (g.hi[1] - g.lo[1]) * (g.hi[2] - g.lo[2]);
+  if (total > (1LL << 21)) return set_error(EXAMG_EUNSUP, "examg_minres_coarse: coarsest level has %lld unknowns; lower minLevel", total);
+  CgArgs a;
+  a.g = grid_args(g);
+  a.st = stencil_args(g, s);
+  a.sfvol = g.vol;
+  a.max_it = max_it;
+  a.rel_tol = rel_tol;
+  for (int d = 0; d < 3; ++d) a.per[d] = c->per[d] ? 1 : 0;
+  if (total <= 0) {
+    EXAMG_CUDA(cudaMemsetAsync(c->int_out, 0, sizeof(int), c->stream));
+    return EXAMG_OK;
+  }
+  int nt = 32;
+  while (nt < 1024 && nt < total) nt <<= 1;
+  if (s.coeff_field >= 0) {
+    const double *sf = field_ptr(c, &c->fields[s.coeff_field], 0, 0);
+    k_minres<true><<<1, nt, 0, c->stream>>>(a, sf, u, rhs, res, tmp[0], tmp[1], tmp[2], tmp[3], tmp[4], tmp[5], tmp[6], c->int_out);
+  } else {
+    k_minres<false><<<1, nt, 0, c->stream>>>(a, nullptr, u, rhs, res, tmp[0], tmp[1], tmp[2], tmp[3], tmp[4], tmp[5], tmp[6], c->int_out);
+  }
+  EXAMG_LAUNCH_CHECK(c);
+  return EXAMG_OK;
+}
+
 int launch_bicgstab(examg_ctx *c, const Stencil &s, double *u, const double *rhs, double *res, double *const tmp[5],
                     int max_it, double rel_tol) {
   const LevelGeom &g = *geom(c, s.level);

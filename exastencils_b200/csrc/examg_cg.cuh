@@ -309,4 +309,91 @@ __device__ __forceinline__ int cr_device(const CgArgs &a, const double *__restri
   return iters;
 }
 
+// MINRES of the layer-3 generator (solver_cgs = "MinRes", C/s/e/solver/l3/L3_MinResForEquation.scala:36-230): Lanczos
+// vectors vOld, v, vNew, search directions pOld, p, pNew (buffers rotated instead of copied), Givens rotations in scalars,
+// the residual norm from the recurrence curRes = -sNew * curRes.  Association: vNew = fma(-beta, vOld, A v);
+// vNew = fma(-alpha, v, vNew); vNew /= betaNew; pNew = fma(-rho2, p, fma(-rho1, pOld, v)) / rho3;
+// u = fma(cNew * curRes, pNew, u); scalars exactly as written below.  w = { v0, v1, v2, p0, p1, p2, av }.
+template <bool VAR>
+__device__ __forceinline__ int minres_device(const CgArgs &a, const double *__restrict__ sf, double *u, const double *rhs,
+                                             double *res, double *w0, double *w1, double *w2, double *w3, double *w4,
+                                             double *w5, double *av) {
+  const GridArgs &g = a.g;
+  const int ex = g.hi[0] - g.lo[0], ey = g.hi[1] - g.lo[1], ez = g.hi[2] - g.lo[2];
+  const int total = ex * ey * ez;
+  const int tid = threadIdx.x, nt = blockDim.x;
+  const bool per = a.per[0] || a.per[1] || a.per[2];
+  double *vOld = w0, *v = w1, *vNew = w2, *pOld = w3, *pp = w4, *pNew = w5;
+  if (per) cg_refresh(a, u);
+  dd part = {0.0, 0.0};
+  for (int t = tid; t < total; t += nt) {
+    const long long q = cg_point(g, t, ex, ey);
+    const double r = rhs[q] - cg_conv<VAR>(a, sf, u, q);
+    res[q] = r;
+    dd_add(part, !per || cg_counts(g, t, ex, ey) ? r * r : 0.0);
+  }
+  double curRes = sqrt(cg_sum(part));
+  const double initRes = curRes;
+  if (curRes <= 0.0) return 0;
+  for (int t = tid; t < total; t += nt) {
+    const long long q = cg_point(g, t, ex, ey);
+    pp[q] = 0.0;
+    pNew[q] = 0.0;
+    v[q] = 0.0;
+    vNew[q] = res[q] / initRes;
+  }
+  double beta = 0.0, betaNew = 0.0, cOld = 1.0, c = 1.0, cNew = 1.0, sOld = 0.0, sn = 0.0, sNew = 0.0;
+  int iters = 0;
+  for (int step = 0; step < a.max_it; ++step) {
+    iters = step + 1;
+    beta = betaNew;
+    { double *tp = vOld; vOld = v; v = vNew; vNew = tp; }  // vOld = v; v = vNew
+    if (per) cg_refresh(a, v);
+    __syncthreads();
+    dd pa = {0.0, 0.0};
+    for (int t = tid; t < total; t += nt) {
+      const long long q = cg_point(g, t, ex, ey);
+      const double avq = cg_conv<VAR>(a, sf, v, q);
+      av[q] = avq;
+      const double vn = fma(-beta, vOld[q], avq);
+      vNew[q] = vn;
+      dd_add(pa, !per || cg_counts(g, t, ex, ey) ? vn * v[q] : 0.0);
+    }
+    const double alpha = cg_sum(pa);
+    dd pb = {0.0, 0.0};
+    for (int t = tid; t < total; t += nt) {
+      const long long q = cg_point(g, t, ex, ey);
+      const double vn = fma(-alpha, v[q], vNew[q]);
+      vNew[q] = vn;
+      dd_add(pb, !per || cg_counts(g, t, ex, ey) ? vn * vn : 0.0);
+    }
+    betaNew = sqrt(cg_sum(pb));
+    cOld = c;
+    c = cNew;
+    sOld = sn;
+    sn = sNew;
+    const double rho1 = sOld * beta;
+    const double rho2 = c * cOld * beta + sn * alpha;
+    const double rho3Tilde = c * alpha - sn * cOld * beta;
+    const double tau = fabs(rho3Tilde) + fabs(betaNew);
+    const double nu = tau * sqrt((rho3Tilde / tau) * (rho3Tilde / tau) + (betaNew / tau) * (betaNew / tau));
+    cNew = rho3Tilde / nu;
+    sNew = betaNew / nu;
+    const double rho3 = nu;
+    { double *tp = pOld; pOld = pp; pp = pNew; pNew = tp; }  // pOld = p; p = pNew
+    const double scale = cNew * curRes;
+    for (int t = tid; t < total; t += nt) {
+      const long long q = cg_point(g, t, ex, ey);
+      vNew[q] = vNew[q] / betaNew;
+      const double pn = fma(-rho2, pp[q], fma(-rho1, pOld[q], v[q])) / rho3;
+      pNew[q] = pn;
+      u[q] = fma(scale, pn, u[q]);
+    }
+    curRes = -1.0 * sNew * curRes;
+    if (fabs(curRes) <= a.rel_tol * initRes) break;
+    __syncthreads();
+  }
+  return iters;
+}
+
 }  // namespace examg

@@ -238,6 +238,8 @@ int launch_cg(examg_ctx *c, const Stencil &s, double *u, const double *rhs, doub
               double *ap, int max_it, double rel_tol);
 int launch_cr(examg_ctx *c, const Stencil &s, double *u, const double *rhs, double *res, double *const tmp[3], int max_it,
               double rel_tol);
+int launch_minres(examg_ctx *c, const Stencil &s, double *u, const double *rhs, double *res, double *const tmp[7],
+                  int max_it, double rel_tol);
 int launch_bicgstab(examg_ctx *c, const Stencil &s, double *u, const double *rhs, double *res, double *const tmp[5],
                     int max_it, double rel_tol);
 // communicate: `depth` ghost layers (+ the duplicate layer) per side, 1 <= depth <= GHOST

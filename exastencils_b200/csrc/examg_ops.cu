@@ -361,6 +361,31 @@ int examg_cr_coarse(examg_ctx *c, int A, int u, int rhs, int res, const int tmp[
   return EXAMG_OK;
 }
 
+int examg_minres_coarse(examg_ctx *c, int A, int u, int rhs, int res, const int tmp[7], int max_it, double rel_tol,
+                        int *iters_out) {
+  GET_STENCIL(s, A); GET_FIELD(fu, u); GET_FIELD(fr, rhs); GET_FIELD(fres, res);
+  CHECK_LEVEL(fu, s->level); CHECK_LEVEL(fr, s->level); CHECK_LEVEL(fres, s->level);
+  if (!tmp) return set_error(EXAMG_EINVAL, "examg_minres_coarse: null tmp");
+  if (fu->loc != 0) return set_error(EXAMG_EUNSUP, "examg_minres_coarse: node-localised fields");
+  double *tp[7];
+  for (int k = 0; k < 7; ++k) {
+    Field *ft = get_field(c, tmp[k]);
+    if (!ft || ft->level != s->level || ft->loc != 0) return set_error(EXAMG_EINVAL, "examg_minres_coarse: tmp[%d]", k);
+    for (int j = 0; j < k; ++j)
+      if (tmp[j] == tmp[k]) return set_error(EXAMG_EINVAL, "examg_minres_coarse: tmp fields must be distinct");
+    tp[k] = field_ptr(c, ft, -1);
+    ft->halo_depth = 0;
+  }
+  fu->halo_depth = 0;
+  fres->halo_depth = 0;
+  int rc = launch_minres(c, *s, field_ptr(c, fu, -1), field_ptr(c, fr, -1), field_ptr(c, fres, -1), tp, max_it, rel_tol);
+  if (rc || !iters_out) return rc;
+  EXAMG_CUDA(cudaMemcpyAsync(c->int_host, c->int_out, sizeof(int), cudaMemcpyDeviceToHost, c->stream));
+  EXAMG_CUDA(cudaStreamSynchronize(c->stream));
+  *iters_out = c->int_host[0];
+  return EXAMG_OK;
+}
+
 int examg_bicgstab_coarse(examg_ctx *c, int A, int u, int rhs, int res, const int tmp[5], int max_it, double rel_tol,
                           int *iters_out) {
   GET_STENCIL(s, A); GET_FIELD(fu, u); GET_FIELD(fr, rhs); GET_FIELD(fres, res);

@@ -90,6 +90,8 @@ SIGNATURES = {
     "examg_field_set_bc_expr": (C.c_int, [C.c_void_p, C.c_int, C.POINTER(BcOp), C.c_int]),
     "examg_cr_coarse": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_int), C.c_int, C.c_double,
                                   C.POINTER(C.c_int)]),
+    "examg_minres_coarse": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_int), C.c_int,
+                                      C.c_double, C.POINTER(C.c_int)]),
     "examg_bicgstab_coarse": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_int), C.c_int,
                                         C.c_double, C.POINTER(C.c_int)]),
     "examg_smooth_colored": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_double, C.c_int, C.c_int]),
@@ -418,6 +420,12 @@ class Context:
         """tmp = (p, ap, ar); returns the number of steps."""
         it = C.c_int()
         check(self.L.examg_cr_coarse(self.h, A, u, rhs, res, (C.c_int * 3)(*tmp), max_it, rel_tol, C.byref(it)))
+        return it.value
+
+    def minres_coarse(self, A, u, rhs, res, tmp, max_it, rel_tol):
+        """tmp = seven work fields; returns the number of steps."""
+        it = C.c_int()
+        check(self.L.examg_minres_coarse(self.h, A, u, rhs, res, (C.c_int * 7)(*tmp), max_it, rel_tol, C.byref(it)))
         return it.value
 
     def bicgstab_coarse(self, A, u, rhs, res, tmp, max_it, rel_tol):

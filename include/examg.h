@@ -228,6 +228,11 @@ int examg_bicgstab_coarse(examg_ctx *ctx, int stencil, int u, int rhs, int res, 
  * symmetric, possibly indefinite operators; tmp = { p, ap, ar }.                                              */
 int examg_cr_coarse(examg_ctx *ctx, int stencil, int u, int rhs, int res, const int tmp[3], int max_it, double rel_tol,
                     int *iters_out);
+/* MINRES (solver_cgs = "MinRes", C/s/e/solver/l3/L3_MinResForEquation.scala:36-230); tmp = seven work fields (three
+ * Lanczos vectors, three search directions, A v).  Residual is the initial residual; the norm is tracked by the
+ * recurrence, as in the generated code.                                                                      */
+int examg_minres_coarse(examg_ctx *ctx, int stencil, int u, int rhs, int res, const int tmp[7], int max_it,
+                        double rel_tol, int *iters_out);
 
 /* ---- whole cycle: Solve@finest / mgCycle@lvl as one library object -----------
  * (C/s/e/solver/l3/L3_SolverForEquation.scala:259-395).  Creates the field set

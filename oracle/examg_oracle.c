@@ -544,3 +544,67 @@ int og_cr(const int n[3], const og_stencil *st, const double *sf, double *u, con
   free(p); free(ap); free(ar);
   return iters;
 }
+
+/* ---------- MINRES of the layer-3 generator -------------------------------------------------------------------
+ * solver_cgs = "MinRes", C/s/e/solver/l3/L3_MinResForEquation.scala:36-230: statements and start values as generated
+ * (vOld = v; v = vNew and pOld = p; p = pNew done by rotating buffers).  Association as in the library. */
+int og_minres(const int n[3], const og_stencil *st, const double *sf, double *u, const double *rhs, double *res,
+              int max_it, double rel_tol) {
+  const size_t size = og_size(n);
+  double *w[7];
+  for (int k = 0; k < 7; ++k) w[k] = (double *)calloc(size, sizeof(double));
+  double *vOld = w[0], *v = w[1], *vNew = w[2], *pOld = w[3], *p = w[4], *pNew = w[5], *av = w[6];
+  OG_LOOP_BEGIN(n)
+  og_residual(n, st, sf, u, rhs, res);
+  double curRes = sqrt(og_dot(n, res, res));
+  const double initRes = curRes;
+  int iters = 0;
+  if (curRes > 0.0) {
+    for (int k = zl; k < zh; ++k)
+      for (int j = yl; j < yh; ++j)
+        for (int i = xl; i < xh; ++i) {
+          size_t q = (size_t)i + (size_t)n[0] * ((size_t)j + (size_t)n[1] * (size_t)k);
+          vNew[q] = res[q] / initRes;
+        }
+    double beta = 0.0, betaNew = 0.0, cOld = 1.0, c = 1.0, cNew = 1.0, sOld = 0.0, s = 0.0, sNew = 0.0;
+    for (int step = 0; step < max_it; ++step) {
+      iters = step + 1;
+      beta = betaNew;
+      { double *tp = vOld; vOld = v; v = vNew; vNew = tp; }
+      og_apply(n, st, sf, v, av);
+      for (int k = zl; k < zh; ++k)
+        for (int j = yl; j < yh; ++j)
+          for (int i = xl; i < xh; ++i) {
+            size_t q = (size_t)i + (size_t)n[0] * ((size_t)j + (size_t)n[1] * (size_t)k);
+            vNew[q] = fma(-beta, vOld[q], av[q]);
+          }
+      const double alpha = og_dot(n, vNew, v);
+      og_axpy(n, -alpha, v, vNew);
+      betaNew = sqrt(og_dot(n, vNew, vNew));
+      cOld = c; c = cNew; sOld = s; s = sNew;
+      const double rho1 = sOld * beta;
+      const double rho2 = c * cOld * beta + s * alpha;
+      const double rho3Tilde = c * alpha - s * cOld * beta;
+      const double tau = fabs(rho3Tilde) + fabs(betaNew);
+      const double nu = tau * sqrt((rho3Tilde / tau) * (rho3Tilde / tau) + (betaNew / tau) * (betaNew / tau));
+      cNew = rho3Tilde / nu;
+      sNew = betaNew / nu;
+      const double rho3 = nu;
+      { double *tp = pOld; pOld = p; p = pNew; pNew = tp; }
+      const double scale = cNew * curRes;
+      for (int k = zl; k < zh; ++k)
+        for (int j = yl; j < yh; ++j)
+          for (int i = xl; i < xh; ++i) {
+            size_t q = (size_t)i + (size_t)n[0] * ((size_t)j + (size_t)n[1] * (size_t)k);
+            vNew[q] = vNew[q] / betaNew;
+            const double pn = fma(-rho2, p[q], fma(-rho1, pOld[q], v[q])) / rho3;
+            pNew[q] = pn;
+            u[q] = fma(scale, pn, u[q]);
+          }
+      curRes = -1.0 * sNew * curRes;
+      if (fabs(curRes) <= rel_tol * initRes) break;
+    }
+  }
+  for (int k = 0; k < 7; ++k) free(w[k]);
+  return iters;
+}

@@ -86,6 +86,8 @@ void og_smooth_color(const int n[3], const og_stencil *st, const double *sf, dou
                      const double *rhs, int ncol, int cx, int cy, int cz);
 int og_cr(const int n[3], const og_stencil *st, const double *sf, double *u, const double *rhs, double *res, int max_it,
           double rel_tol);
+int og_minres(const int n[3], const og_stencil *st, const double *sf, double *u, const double *rhs, double *res,
+              int max_it, double rel_tol);
 int og_bicgstab(const int n[3], const og_stencil *st, const double *sf, double *u, const double *rhs, double *res,
                 int max_it, double rel_tol);
 /* cell-centred fields: padded arrays (cells + 2 per dimension), see examg_oracle.c */

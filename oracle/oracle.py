@@ -80,6 +80,8 @@ def lib():
     L.og_max_abs_diff.restype = C.c_double
     L.og_cr.argtypes = [i3, stp, dp, dp, dp, dp, C.c_int, C.c_double]
     L.og_cr.restype = C.c_int
+    L.og_minres.argtypes = [i3, stp, dp, dp, dp, dp, C.c_int, C.c_double]
+    L.og_minres.restype = C.c_int
     L.og_bicgstab.argtypes = [i3, stp, dp, dp, dp, dp, C.c_int, C.c_double]
     L.og_bicgstab.restype = C.c_int
     L.og_smooth_color.argtypes = [i3, stp, dp, C.c_double, dp, dp, C.c_int, C.c_int, C.c_int, C.c_int]
@@ -173,6 +175,13 @@ def conjugate_residual(st, u, rhs, max_it, rel_tol, sf=None):
     """In place on u; returns (steps, residual field)."""
     res = np.zeros_like(u)
     it = lib().og_cr(_n(u), C.byref(st), _sf(sf), _dp(u), _dp(rhs), _dp(res), int(max_it), float(rel_tol))
+    return it, res
+
+
+def minres(st, u, rhs, max_it, rel_tol, sf=None):
+    """In place on u; returns (steps, initial residual field)."""
+    res = np.zeros_like(u)
+    it = lib().og_minres(_n(u), C.byref(st), _sf(sf), _dp(u), _dp(rhs), _dp(res), int(max_it), float(rel_tol))
     return it, res
 
 

@@ -537,3 +537,35 @@ def test_conjugate_residual_coarse(dim, cells, lvl, npts, oracle):
     inner = (slice(1, -1),) * 3 if dim == 3 else (slice(None), slice(1, -1), slice(1, -1))
     assert np.array_equal(ctx.download(fr, lvl)[inner], res_ref[inner])
     ctx.close()
+
+
+@pytest.mark.parametrize("dim,cells,lvl,npts,shift", [(2, (4, 4), 2, 5, -0.5), (3, (3, 2, 5), 1, 7, 0.25),
+                                                      (3, (1, 1, 1), 3, 27, -0.3)])
+def test_minres_coarse(dim, cells, lvl, npts, shift, oracle):
+    """solver_cgs = "MinRes" (C/s/e/solver/l3/L3_MinResForEquation.scala:36-230) on symmetric operators, two of them
+    indefinite (negative shift of the diagonal): step count and Solution against the oracle, bit for bit; the true
+    residual has dropped by the requested factor."""
+    og = oracle
+    ctx = _ctx(dim, cells, lvl, lvl)
+    shape = ctx.shape(lvl)
+    offs = _stencil_offsets(dim, npts)
+    centre = offs.index((0, 0, 0))
+    coeffs = np.array([-1.0 / (1 + sum(abs(v) for v in o)) for o in offs])
+    coeffs[centre] = -(np.sum(coeffs) - coeffs[centre]) + shift
+    A = ctx.stencil_const(lvl, offs, list(coeffs))
+    st = og.Stencil.make(offs, list(coeffs))
+    fu, ff, fr = ctx.field_create("u", lvl), ctx.field_create("rhs", lvl), ctx.field_create("res", lvl)
+    tmp = [ctx.field_create("t%d" % k, lvl) for k in range(7)]
+    seed = 9700 * lvl + npts
+    u, rhs = _rand(shape, seed + 1), _rand(shape, seed + 2)
+    ctx.upload(fu, u)
+    ctx.upload(ff, rhs)
+    its = ctx.minres_coarse(A, fu, ff, fr, tmp, 500, 1e-6)
+    e = u.copy()
+    its_ref, _ = og.minres(st, e, rhs, 500, 1e-6)
+    assert its == its_ref and 1 <= its < 500
+    got = ctx.download(fu, lvl)
+    assert np.array_equal(got, e)
+    r0, r1 = og.residual(st, u, rhs), og.residual(st, got, rhs)
+    assert og.dot(r1, r1) <= (1e-5) ** 2 * og.dot(r0, r0)
+    ctx.close()
