@@ -245,13 +245,197 @@ def cpu_baseline(args):
                 reps, 1 << level, ncores, dt)}
 
 
+
+# ---- BASELINE configs[0] and configs[3] (parity-test cases of the bench contract; measured the same way) -----------
+AUX = ("poisson2d", "optflow")
+
+
+def _aux_config(workload, level):
+    if workload == "poisson2d":
+        return {"workload": "Examples/Poisson 2D 5-point FD, V(3,3) RBGS omega=0.8, CG coarse solve, max level 10 "
+                            "(1025^2 nodes = 4x4 fragments of level 8, Testing/Poisson/2D_FD_Poisson_fromL4)",
+                "cells_per_gpu": 1024 ** 2, "smoother": "rbgs", "nu_pre": 3, "nu_post": 3,
+                "l2_policy": "none: 8.4 MB per field, the whole problem lives in L2 (latency-bound cycle)"}
+    n = 1 << level
+    return {"workload": "Examples/OpticalFlow 2D coupled two-component system, V(3,3) red-black 2x2 block smoother, "
+                        "coupled CG, %d^2 cells, levels 2..%d" % (n, level),
+            "cells_per_gpu": n * n, "smoother": "block2x2-rb", "nu_pre": 3, "nu_post": 3,
+            "l2_policy": "inputs larger than L2 (9 fields x %.2f GB on the finest level)" % (8.0 * n * n / 1e9)}
+
+
+def _aux_oracle(workload, level):
+    """(solver, step function, unknowns) of the CPU oracle for the bounded sample."""
+    import numpy as np
+    if workload == "poisson2d":
+        from oracle import oracle as og
+        og.build()
+        s = og.Solver(2, (4, 4), 0, 8, op=og.OP_LAPLACE_SCALED, order=og.ORDER_BENCH, smoother=og.SMOOTH_RBGS, omega=0.8,
+                      nu_pre=3, nu_post=3, cg_max_it=128, cg_rel_tol=1e-3)
+        x, y, _ = s.node_positions(8)
+        X, Y = x[None, None, :], y[None, :, None]
+        u = s.solution(8)
+        u[...] = np.broadcast_to(np.cos(np.pi * X) - np.sin(2.0 * np.pi * Y), u.shape)
+        u[:, 1:-1, 1:-1] = 0.0
+        s.rhs(8)[...] = np.broadcast_to(np.pi ** 2 * np.cos(np.pi * X) - 4.0 * np.pi ** 2 * np.sin(2.0 * np.pi * Y), u.shape)
+        return s, 1023.0 ** 2
+    from oracle import optflow as oof
+    from oracle import oracle as og
+    og.build()
+    s = oof.Solver((1, 1), 2, level)
+    s.init_images()
+    s.init_fields()
+    return s, 2.0 * float(1 << level) ** 2
+
+
+def _aux_cpu(workload, level, reps, warm=1):
+    s, unknowns = _aux_oracle(workload, level)
+    ncores = os.cpu_count() or 1
+    for _ in range(warm):
+        s.vcycle()
+        s.update_residual_norm()
+    t0 = time.perf_counter()
+    for _ in range(reps):
+        s.vcycle()
+        s.update_residual_norm()
+    dt = time.perf_counter() - t0
+    s.close()
+    what = "1025^2 nodes" if workload == "poisson2d" else "%d^2 cells" % (1 << level)
+    return {"value": unknowns * reps / dt, "unit": "DoF-cycles/s", "cores": ncores, "kind": "port",
+            "sample": "%d V(3,3) cycles + residual norm at %s (OpenMP, %d threads, %.1f s)" % (reps, what, ncores, dt)}, dt
+
+
+def run_aux(args):
+    """--workload poisson2d | optflow on one GPU: same JSON line as the main workload."""
+    level = args.level if args.level is not None else (8 if args.workload == "poisson2d" else 13)
+    cpu_level = args.cpu_level if args.cpu_level is not None else (8 if args.workload == "poisson2d" else min(level, 12))
+    if int(os.environ.get("RANK", "0")) != 0:
+        return
+    if args.gpus != 1:
+        raise SystemExit("--workload %s runs on one GPU" % args.workload)
+    if args.impl == "reference":
+        cb, dt = _aux_cpu(args.workload, cpu_level, args.steps, args.warmup)
+        line = {"impl": "reference", "metric": "V-cycle DoF-cycles/s", "value": cb["value"], "unit": "DoF-cycles/s",
+                "n_gpus": 1, "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps,
+                "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+                "config": _aux_config(args.workload, level), "cpu_baseline": cb,
+                "e2e": {"value": cb["value"], "unit": "DoF-cycles/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+                "gpu_launches": 0}
+        print(json.dumps(line))
+        return
+    import numpy as np
+    import torch
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: libexamg has no CPU path")
+    stream = torch.cuda.Stream()
+    peak, peak_kind = peaks()
+    if args.workload == "poisson2d":
+        from exastencils_b200 import MultigridProgram
+        prog = MultigridProgram(2, (4, 4), 0, 8, op="scaled", order="bench", smoother="rbgs", omega=0.8, nu_pre=3,
+                                nu_post=3, restrict_scale=1.0, cg_max_it=128, cg_rel_tol=1e-3, stream=stream.cuda_stream)
+        ctx = prog.ctx
+        x, y, _ = prog.node_positions(8)
+        X, Y = x[None, None, :], y[None, :, None]
+        u = prog.solution(8)
+        u[...] = np.broadcast_to(np.cos(np.pi * X) - np.sin(2.0 * np.pi * Y), u.shape)
+        u[:, 1:-1, 1:-1] = 0.0
+        rhs = np.ascontiguousarray(np.broadcast_to(np.pi ** 2 * np.cos(np.pi * X) - 4.0 * np.pi ** 2 * np.sin(2.0 * np.pi * Y), u.shape))
+        prog.rhs(8)[...] = rhs
+        prog.commit()
+        unknowns = 1023.0 ** 2
+        inputs = [(prog.f_rhs[8], torch.from_numpy(rhs.copy()).pin_memory())]
+        prepare = lambda: None
+        A, fu, ff = prog.stencil[8], prog.f_solution[8], prog.f_rhs[8]
+        kernel = lambda: ctx.smooth_rbgs(A, fu, ff, 0.8, 3)
+        kname, kbytes = "RBGS smoother, 3 sweeps at 1025^2 (generic colour kernels, L2-resident)", 3 * 24.0 * unknowns
+    else:
+        from exastencils_b200 import OpticalFlowProgram
+        from exastencils_b200 import optflow as gof
+        prog = OpticalFlowProgram((1, 1), 2, level, nu_pre=3, nu_post=3, stream=stream.cuda_stream)
+        ctx = prog.ctx
+        nx, ny = prog.cells()
+        img0, img1 = gof.analytic_images(nx, ny)
+        prog.set_images(img0, img1)
+        unknowns = 2.0 * nx * ny
+        inputs = [(prog.field(gof.IMG0), torch.from_numpy(img0).pin_memory()),
+                  (prog.field(gof.IMG1), torch.from_numpy(img1).pin_memory())]
+        from exastencils_b200.runtime import check as rt_check
+        prepare = lambda: rt_check(ctx.L.examg_optflow_init_fields(prog._h))
+        sys_h = level - 2  # systems are created per level in order
+        f = {w: prog.field(w) for w in range(9)}
+        kernel = lambda: ctx.system2_smooth_rb(sys_h, f[gof.U], f[gof.V], f[gof.RHS_U], f[gof.RHS_V], 1.0, 3)
+        kname, kbytes = "red-black 2x2 block smoother, 3 sweeps on the finest level", 3 * 80.0 * nx * ny
+    with torch.cuda.stream(stream):
+        sampler = ClockSampler(0)
+        sampler.start()
+        for _ in range(args.warmup):
+            prog.cycles(1)
+        torch.cuda.synchronize()
+        l0 = ctx.launch_count()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(stream)
+        for _ in range(args.steps):
+            res = prog.cycles(1)
+        e1.record(stream)
+        torch.cuda.synchronize()
+        ms = e0.elapsed_time(e1)
+        launches = ctx.launch_count() - l0
+        # end to end: every step uploads its input from pinned host memory, (re)initialises, cycles, reads the norm back
+        h2d = sum(t.numel() * 8 for _, t in inputs)
+        for _ in range(args.warmup):
+            for fld, t in inputs:
+                ctx.upload_async(fld, t.data_ptr())
+            prepare()
+            prog.cycles(1)
+        torch.cuda.synchronize()
+        e0.record(stream)
+        for _ in range(args.steps):
+            for fld, t in inputs:
+                ctx.upload_async(fld, t.data_ptr())
+            prepare()
+            res_e2e = prog.cycles(1)
+        e1.record(stream)
+        torch.cuda.synchronize()
+        ms_e2e = e0.elapsed_time(e1)
+        clocks = sampler.stop()
+        reps = max(5, args.steps)
+        for _ in range(3):
+            kernel()
+        torch.cuda.synchronize()
+        l1 = ctx.launch_count()
+        e0.record(stream)
+        for _ in range(reps):
+            kernel()
+        e1.record(stream)
+        torch.cuda.synchronize()
+        ms_k = e0.elapsed_time(e1) / reps
+        k_launches = (ctx.launch_count() - l1) // reps
+    achieved = kbytes / (ms_k * 1e-3) / 1e9
+    cb = None
+    if not args.no_cpu_baseline:
+        cb, _ = _aux_cpu(args.workload, cpu_level, args.cpu_cycles)
+    line = {"metric": "V-cycle DoF-cycles/s", "value": unknowns * args.steps / (ms * 1e-3), "unit": "DoF-cycles/s", "n_gpus": 1,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": _aux_config(args.workload, level),
+            "e2e": {"value": unknowns * args.steps / (ms_e2e * 1e-3), "unit": "DoF-cycles/s", "h2d_bytes_per_step": h2d,
+                    "d2h_bytes_per_step": 8, "ms_per_step": ms_e2e / args.steps,
+                    "what": "per step: input H2D from pinned memory, (re)initialisation, one cycle + residual, norm D2H"},
+            "gpu_launches": int(launches), "clocks": clocks,
+            "roofline": {"bound": "hbm", "kernel": "%s (%d launch(es))" % (kname, k_launches), "achieved": achieved,
+                         "peak": peak, "peak_kind": peak_kind + " (MEASURED_PEAKS.json hbm_gbs, burst)", "unit": "GB/s",
+                         "frac": achieved / peak, "traffic": None, "algorithmic_bytes_per_launch_group": kbytes, "ms": ms_k},
+            "cpu_baseline": cb, "final_residual": res, "device_bytes": ctx.device_bytes()}
+    print(json.dumps(line))
+    prog.close()
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=30)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="examg", choices=["examg", "reference"])
-    ap.add_argument("--workload", default="poisson7", choices=sorted(WORKLOADS))
+    ap.add_argument("--workload", default="poisson7", choices=sorted(WORKLOADS) + list(AUX))
     ap.add_argument("--level", type=int, default=None, help="finest level per GPU (9 = 512^3 cells; default 9, "
                     "varcoef27: 8)")
     ap.add_argument("--cpu-level", type=int, default=None)
@@ -260,6 +444,8 @@ def main():
     args = ap.parse_args()
     if args.gpus not in BLOCKS:
         raise SystemExit("--gpus must be 1, 2, 4 or 8")
+    if args.workload in AUX:
+        return run_aux(args)
     wl = WORKLOADS[args.workload]
     if args.level is None:
         args.level = 8 if args.workload == "varcoef27" else 9
