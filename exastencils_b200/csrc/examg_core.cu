@@ -649,6 +649,39 @@ int examg_field_upload_finish(examg_ctx *c) {
   return EXAMG_OK;
 }
 
+int examg_field_print(examg_ctx *c, int h, int slot, const char *filename, const char *separator) {
+  Field *f = get_field(c, h);
+  if (!f) return set_error(EXAMG_EINVAL, "bad field %d", h);
+  if (!filename) return set_error(EXAMG_EINVAL, "examg_field_print: null file name");
+  if (slot >= f->nslots) return set_error(EXAMG_EINVAL, "bad slot %d", slot);
+  const LevelGeom &g = *geom(c, f->level);
+  const char *sep = separator ? separator : " ";
+  int e[3];
+  for (int d = 0; d < 3; ++d) e[d] = g.n[d] - (f->loc == 1 && d < c->cfg.dim ? 1 : 0);
+  const size_t dense = (size_t)e[0] * e[1] * e[2];
+  std::vector<double> host((size_t)f->ncomp * dense);
+  int rc = examg_field_download(c, h, slot, host.data());
+  if (rc) return rc;
+  FILE *fp = fopen(filename, "w");
+  if (!fp) return set_error(EXAMG_EINVAL, "examg_field_print: cannot open %s", filename);
+  const double off = f->loc == 1 ? 0.5 : 0.0;
+  for (int k = 0; k < e[2]; ++k)
+    for (int j = 0; j < e[1]; ++j)
+      for (int i = 0; i < e[0]; ++i) {
+        const int idx[3] = {i, j, k};
+        for (int d = 0; d < c->cfg.dim; ++d) {
+          // vf_nodePosition = i * h + lo; vf_cellCenter = vf_nodePosition + 0.5 * vf_cellWidth
+          const double pos = ((double)(g.goff[d] + idx[d]) * g.h[d] + c->cfg.domain_lo[d]) + off * g.h[d];
+          fprintf(fp, "%g%s", pos, sep);
+        }
+        const size_t p = (size_t)i + (size_t)e[0] * ((size_t)j + (size_t)e[1] * (size_t)k);
+        for (int comp = 0; comp < f->ncomp; ++comp)
+          fprintf(fp, comp + 1 < f->ncomp ? "%g%s" : "%g\n", host[(size_t)comp * dense + p], sep);
+      }
+  fclose(fp);
+  return EXAMG_OK;
+}
+
 int examg_field_fill(examg_ctx *c, int h, double value) {
   Field *f = get_field(c, h);
   if (!f) return set_error(EXAMG_EINVAL, "bad field %d", h);

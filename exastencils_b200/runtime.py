@@ -95,6 +95,7 @@ SIGNATURES = {
     "examg_bicgstab_coarse": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_int), C.c_int,
                                         C.c_double, C.POINTER(C.c_int)]),
     "examg_smooth_colored": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_double, C.c_int, C.c_int]),
+    "examg_field_print": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_char_p, C.c_char_p]),
     "examg_field_eval": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.POINTER(BcOp), C.c_int]),
     "examg_apply_bc": (C.c_int, [C.c_void_p, C.c_int, C.c_int]),
     "examg_field_upload": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_void_p]),
@@ -304,6 +305,10 @@ class Context:
         for i, (op, val) in enumerate(prog):
             arr[i].op, arr[i].value = op, val
         check(self.L.examg_field_eval(self.h, f, slot, comp, arr, len(prog)))
+
+    def field_print(self, f, filename, slot=-1, separator=None):
+        """printField ( "file", F ): ascii, one line per point (position, value[s])."""
+        check(self.L.examg_field_print(self.h, f, slot, filename.encode(), separator.encode() if separator else None))
 
     def apply_bc(self, f, slot=-1):
         check(self.L.examg_apply_bc(self.h, f, slot))

@@ -151,6 +151,12 @@ int examg_field_upload_finish(examg_ctx *ctx);
 /* whole allocation (ghosts, padding, all slots) := value (initFieldsWithZero) */
 int examg_field_fill(examg_ctx *ctx, int field, double value);
 
+/* printField ( "file", F ) of the L4 programs in its ascii form (io interface "lock", C/s/e/field/ir/IR_PrintField.scala:49-100):
+ * one line per point of the block in lexicographic order (x fastest) -- the position (vf_nodePosition of node fields,
+ * vf_cellCenter of cell fields) in every dimension, then the components, all in std::defaultfloat (6 significant
+ * digits), joined by `separator` (" " unless given).  Ghost layers are not written.  Synchronises.            */
+int examg_field_print(examg_ctx *ctx, int field, int slot, const char *filename, const char *separator);
+
 /* ---- stencils ---------------------------------------------------------------
  * Stencil Name@lvl { [dx,dy,dz] => coeff ... }: entries in declaration order.
  * Stencil fields take their coefficients from a field with ncomp = n_entries

@@ -198,3 +198,36 @@ def test_benchmark_program_properties(oracle):
     exact = (x[None, None, :] ** 2 - 0.5 * y[None, :, None] ** 2) - 0.5 * z[:, None, None] ** 2
     assert np.max(np.abs(gpu.fetch_solution() - exact)) < 1e-9
     gpu.close()
+
+
+def test_print_field(tmp_path):
+    """printField ( "file", F ) in ascii (C/s/e/field/ir/IR_PrintField.scala:49-100): position and value per point, x fastest,
+    std::defaultfloat -- node field in 3D, cell field with two components in 2D and a custom separator."""
+    from exastencils_b200 import runtime as rt
+    ctx = rt.Context(3, 2, 2, block_cells=(1, 2, 1))
+    f = ctx.field_create("u", 2)
+    shape = ctx.shape(2)
+    u = np.random.default_rng(3).uniform(-1.0, 1.0, size=shape)
+    ctx.upload(f, u)
+    path = str(tmp_path / "u.txt")
+    ctx.field_print(f, path)
+    h = ctx.width(2)
+    lines = open(path).read().splitlines()
+    assert len(lines) == u.size
+    n = ctx.dims(2)
+    for t in (0, 1, n[0], n[0] * n[1] + 3, u.size - 1):
+        i, j, k = t % n[0], (t // n[0]) % n[1], t // (n[0] * n[1])
+        assert lines[t] == "%g %g %g %g" % (i * h[0], j * h[1], k * h[2], u[k, j, i])
+    ctx.close()
+    ctx = rt.Context(2, 3, 3, block_cells=(1, 1))
+    f = ctx.field_create_cell("c", 3, 1, 2)
+    cs = ctx.cell_shape(3)
+    v = np.random.default_rng(4).uniform(-1.0, 1.0, size=(2,) + cs)
+    ctx.upload(f, np.ascontiguousarray(v))
+    path = str(tmp_path / "c.csv")
+    ctx.field_print(f, path, separator=",")
+    lines = open(path).read().splitlines()
+    hh = ctx.width(3)
+    assert len(lines) == cs[1] * cs[2]
+    assert lines[9] == "%g,%g,%g,%g" % (1 * hh[0] + 0.5 * hh[0], 1 * hh[1] + 0.5 * hh[1], v[0, 0, 1, 1], v[1, 0, 1, 1])
+    ctx.close()
