@@ -25,6 +25,7 @@ struct examg_solver {
   std::vector<int> stencils;          // per level
   std::vector<int> sol, rhs, res;     // field handles per level
   int cg_p = -1, cg_ap = -1;
+  int cgs_tmp[7] = {-1, -1, -1, -1, -1, -1, -1};  // work fields of the other coarse solvers (solver_cgs)
   int coarse_top = -1;                // mgCycle@level for level <= coarse_top is one single-CTA kernel
   // several blocks: mgCycle@agg_level runs on rank 0 on the agglomerated (global, single-block) grid
   int agg_level = -1;
@@ -111,8 +112,20 @@ static int vcycle_rec(examg_solver *s, int level) {
   if (c->world > 1 && level <= s->agg_level)
     return set_error(EXAMG_EUNSUP, "mgCycle@%d of a multi-block run: levels <= %d live on the agglomerated grid", level, s->agg_level);
   if (level == c->cfg.min_level)
-    return examg_cg_coarse(c, s->stencils[l], s->sol[l], s->rhs[l], s->res[l], s->cg_p, s->cg_ap,
-                           s->desc.cg_max_it, s->desc.cg_rel_tol, nullptr);
+    switch (s->desc.coarse_solver) {
+      case EXAMG_CGS_BICGSTAB:
+        return examg_bicgstab_coarse(c, s->stencils[l], s->sol[l], s->rhs[l], s->res[l], s->cgs_tmp, s->desc.cg_max_it,
+                                     s->desc.cg_rel_tol, nullptr);
+      case EXAMG_CGS_CR:
+        return examg_cr_coarse(c, s->stencils[l], s->sol[l], s->rhs[l], s->res[l], s->cgs_tmp, s->desc.cg_max_it,
+                               s->desc.cg_rel_tol, nullptr);
+      case EXAMG_CGS_MINRES:
+        return examg_minres_coarse(c, s->stencils[l], s->sol[l], s->rhs[l], s->res[l], s->cgs_tmp, s->desc.cg_max_it,
+                                   s->desc.cg_rel_tol, nullptr);
+      default:
+        return examg_cg_coarse(c, s->stencils[l], s->sol[l], s->rhs[l], s->res[l], s->cg_p, s->cg_ap,
+                               s->desc.cg_max_it, s->desc.cg_rel_tol, nullptr);
+    }
   if (level <= s->coarse_top)
     return launch_coarse_cycle(c, s->desc, level, s->stencils.data(), s->sol.data(), s->rhs.data(), s->res.data(),
                                s->cg_p, s->cg_ap);
@@ -173,6 +186,19 @@ examg_solver *examg_solver_create(examg_ctx *c, const examg_cycle_desc *d) {
   s->cg_p = examg_field_create(c, "cgTmp0", c->cfg.min_level, 1, 1);
   s->cg_ap = examg_field_create(c, "cgTmp1", c->cfg.min_level, 1, 1);
   if (s->cg_p < 0 || s->cg_ap < 0) { delete s; return nullptr; }
+  if (d->coarse_solver < EXAMG_CGS_CG || d->coarse_solver > EXAMG_CGS_MINRES) {
+    set_error(EXAMG_EINVAL, "examg_solver_create: coarse_solver %d", d->coarse_solver);
+    delete s;
+    return nullptr;
+  }
+  {
+    const int ntmp = d->coarse_solver == EXAMG_CGS_BICGSTAB ? 5 : d->coarse_solver == EXAMG_CGS_CR ? 3
+                     : d->coarse_solver == EXAMG_CGS_MINRES ? 7 : 0;
+    for (int k = 0; k < ntmp; ++k) {
+      s->cgs_tmp[k] = examg_field_create(c, "cgsTmp", c->cfg.min_level, 1, 1);
+      if (s->cgs_tmp[k] < 0) { delete s; return nullptr; }
+    }
+  }
   examg_field_set_bc(c, s->cg_p, EXAMG_BC_DIRICHLET_CONST, 0.0);
   // second buffers of the fused sweeps: now, so that they are part of what examg_comm_export publishes
   if (d->smoother == EXAMG_SMOOTH_RBGS)
@@ -257,6 +283,8 @@ int examg_solver_destroy(examg_solver *s) {
   for (int h : s->res) examg_field_destroy(s->c, h);
   examg_field_destroy(s->c, s->cg_p);
   examg_field_destroy(s->c, s->cg_ap);
+  for (int k = 0; k < 7; ++k)
+    if (s->cgs_tmp[k] >= 0) examg_field_destroy(s->c, s->cgs_tmp[k]);
   delete s;
   return EXAMG_OK;
 }

@@ -22,6 +22,7 @@ BC_NONE, BC_DIRICHLET_CONST, BC_DIRICHLET_EXPR, BC_DIRICHLET_HOST = 0, 1, 2, 3
 OP_CONST, OP_X, OP_Y, OP_Z, OP_ADD, OP_SUB, OP_MUL, OP_DIV, OP_NEG = range(9)
 OP_EXP, OP_SIN, OP_COS, OP_SINH, OP_SQRT, OP_COMP = range(9, 15)
 SMOOTH_JACOBI, SMOOTH_RBGS = 0, 1
+CGS_CG, CGS_BICGSTAB, CGS_CR, CGS_MINRES = range(4)
 BC_NEUMANN = 4
 F_SOLUTION, F_RHS, F_RESIDUAL, F_CGTMP0, F_CGTMP1 = range(5)
 
@@ -44,7 +45,7 @@ class BcOp(C.Structure):
 class CycleDesc(C.Structure):
     _fields_ = [("smoother", C.c_int), ("omega", C.c_double), ("nu_pre", C.c_int), ("nu_post", C.c_int),
                 ("restrict_scale", C.c_double), ("cg_max_it", C.c_int), ("cg_rel_tol", C.c_double),
-                ("stencils", C.POINTER(C.c_int))]
+                ("stencils", C.POINTER(C.c_int)), ("coarse_solver", C.c_int)]
 
 
 class System2Desc(C.Structure):

@@ -254,7 +254,9 @@ typedef struct {
   int cg_max_it;         /* solver_cgs_maxNumIts                                 */
   double cg_rel_tol;     /* solver_cgs_targetResReduction                        */
   const int *stencils;   /* stencil handle per level, index level - min_level   */
+  int coarse_solver;     /* solver_cgs: EXAMG_CGS_CG (0, the default), _BICGSTAB, _CR, _MINRES   */
 } examg_cycle_desc;
+enum { EXAMG_CGS_CG = 0, EXAMG_CGS_BICGSTAB = 1, EXAMG_CGS_CR = 2, EXAMG_CGS_MINRES = 3 };
 typedef struct examg_solver examg_solver;
 examg_solver *examg_solver_create(examg_ctx *ctx, const examg_cycle_desc *desc);
 int examg_solver_destroy(examg_solver *s);

@@ -231,3 +231,30 @@ def test_print_field(tmp_path):
     assert len(lines) == cs[1] * cs[2]
     assert lines[9] == "%g,%g,%g,%g" % (1 * hh[0] + 0.5 * hh[0], 1 * hh[1] + 0.5 * hh[1], v[0, 0, 1, 1], v[1, 0, 1, 1])
     ctx.close()
+
+
+@pytest.mark.parametrize("cgs", ["bicgstab", "cr", "minres"])
+def test_coarse_solver_choice(cgs, oracle):
+    """solver_cgs of the layer-3 generator inside the library cycle (examg_cycle_desc.coarse_solver): on the SPD Poisson
+    operator every coarse solver reaches the same 1e-3 coarse reduction, so the V-cycle history stays that of the CG
+    program to a few per cent and the Solve loop takes the same number of cycles."""
+    prog = programs.SMOOTHERS_JAC
+    hist = {}
+    for name in ("cg", cgs):
+        from exastencils_b200 import MultigridProgram
+        c = dict(prog.cfg, max_level=3)
+        gpu = MultigridProgram(c["dim"], tuple(c["F"]), c["min_level"], c["max_level"], op=c["op"], order=c["order"],
+                               smoother=c["smoother"], omega=c["omega"], nu_pre=c["nu_pre"], nu_post=c["nu_post"],
+                               restrict_scale=c["restrict_scale"], cg_max_it=c["cg_max_it"], cg_rel_tol=c["cg_rel_tol"],
+                               coarse_solver=name)
+        prog.setup(gpu)
+        gpu.sync_slots()
+        h = [gpu.update_residual_norm()]
+        for _ in range(6):
+            gpu.vcycle()
+            h.append(gpu.update_residual_norm())
+        assert gpu.last_cg_iters() >= 1
+        gpu.close()
+        hist[name] = h
+    assert all(abs(a - b) <= 0.05 * b for a, b in zip(hist[cgs], hist["cg"])), (hist[cgs], hist["cg"])
+    assert hist[cgs][-1] < 1e-3 * hist[cgs][0]
