@@ -79,3 +79,50 @@ def test_laplace_stencil_matches_oracle(oracle):
         assert offs == st.offsets()
         assert coefs == st.coeffs()
         s.close()
+
+
+def _rpn(prog, X, Y, Z, comps):
+    """Reference interpreter of the postfix programs of examg_field_eval / examg_field_set_bc_expr (numpy, host libm)."""
+    import math
+    import numpy as np
+    from exastencils_b200 import runtime as rt
+    st = []
+    for op, val in prog:
+        if op == rt.OP_CONST: st.append(np.float64(val))
+        elif op == rt.OP_X: st.append(X)
+        elif op == rt.OP_Y: st.append(Y)
+        elif op == rt.OP_Z: st.append(Z)
+        elif op == rt.OP_COMP: st.append(comps[int(val)])
+        elif op == rt.OP_NEG: st.append(-st.pop())
+        elif op == rt.OP_EXP: st.append(np.vectorize(math.exp)(st.pop()))  # the host libm, not numpy's SIMD exp
+        elif op == rt.OP_SIN: st.append(np.sin(st.pop()))
+        elif op == rt.OP_COS: st.append(np.cos(st.pop()))
+        elif op == rt.OP_SINH: st.append(np.sinh(st.pop()))
+        elif op == rt.OP_SQRT: st.append(np.sqrt(st.pop()))
+        else:
+            b, a = st.pop(), st.pop()
+            st.append(a + b if op == rt.OP_ADD else a - b if op == rt.OP_SUB else a * b if op == rt.OP_MUL else a / b)
+    assert len(st) == 1
+    return st[0]
+
+
+def test_varcoeff27_programs_match_oracle(oracle):
+    """The postfix programs the host side hands to examg_field_eval for BASELINE config 3's operator
+    (exastencils_b200.program.varcoeff27_programs), interpreted with numpy, give the oracle's coefficients bit for bit
+    (same association; numpy and the oracle share the host libm) -- the device differs only by its exp."""
+    import numpy as np
+    from exastencils_b200.program import varcoeff27_programs
+    lvl, kappa = 3, 10.0
+    s = oracle.Solver(3, (1, 1, 1), lvl, lvl, op=oracle.OP_VARCOEFF27, order=oracle.ORDER_TESTING, kappa=kappa,
+                      smoother=oracle.SMOOTH_JACOBI)
+    want = s.coeff(lvl)
+    x, y, z = s.node_positions(lvl)
+    X, Y, Z = np.broadcast_arrays(x[None, None, :], y[None, :, None], z[:, None, None])
+    h = 1.0 / (1 << lvl)
+    comps = {}
+    for comp, prog in varcoeff27_programs((h, h, h), kappa):
+        assert len(prog) <= 64
+        comps[comp] = np.broadcast_to(_rpn(prog, X, Y, Z, comps), X.shape)
+    for comp in range(27):
+        assert np.array_equal(comps[comp], want[comp]), comp
+    s.close()
