@@ -87,7 +87,7 @@ int examg::residual_op(examg_ctx *c, int A, int u, int u_slot, int rhs, int res,
 int examg::residual_restrict_op(examg_ctx *c, int A, int u, int rhs, int rhs_coarse, double scale) {
   GET_STENCIL(s, A); GET_FIELD(fu, u); GET_FIELD(fr, rhs); GET_FIELD(fc, rhs_coarse);
   CHECK_LEVEL(fu, s->level); CHECK_LEVEL(fr, s->level); CHECK_LEVEL(fc, s->level - 1);
-  if (!residual_restrict_usable(c, *s) || fu->ncomp != 1) return 1;
+  if (!residual_restrict_usable(c, *s) || fu->ncomp != 1 || fu->loc != 0 || fr->loc != 0 || fc->loc != 0) return 1;
   int rc;
   if (c->world > 1) {  // the residual is needed one layer beyond the block: Solution 2 layers, RHS 1
     if (fr->halo_depth < 1) {
@@ -191,6 +191,8 @@ int examg_smooth_rb_color(examg_ctx *c, int A, int u, int rhs, double omega, int
   GET_STENCIL(s, A); GET_FIELD(fu, u); GET_FIELD(fr, rhs);
   CHECK_LEVEL(fu, s->level); CHECK_LEVEL(fr, s->level);
   if (color != 0 && color != 1) return set_error(EXAMG_EINVAL, "examg_smooth_rb_color: colour %d", color);
+  if (fu->loc != fr->loc) return set_error(EXAMG_EINVAL, "examg_smooth_rb_color: fields of different localisation");
+  LocGuard lg(c, fu->loc);
   for (int k = 0; k < s->nst; ++k)
     if (k != s->centre && ((s->off[k][0] + s->off[k][1] + s->off[k][2]) & 1) == 0)
       return set_error(EXAMG_EUNSUP, "examg_smooth_rb: two colours do not decouple this stencil (entry [%d,%d,%d] "
@@ -261,6 +263,7 @@ int examg_smooth_rbgs(examg_ctx *c, int A, int u, int rhs, double omega, int nsw
 int examg_restrict(examg_ctx *c, int res_fine, int rhs_coarse, double scale) {
   GET_FIELD(ff, res_fine); GET_FIELD(fc, rhs_coarse);
   if (fc->level != ff->level - 1) return set_error(EXAMG_EINVAL, "examg_restrict: levels %d -> %d", ff->level, fc->level);
+  if (ff->loc != 0 || fc->loc != 0) return set_error(EXAMG_EUNSUP, "examg_restrict: node-localised fields (cell fields: examg_restrict_cell)");
   int rc = ff->halo_depth >= 1 ? EXAMG_OK : do_exchange(c, *ff, ff->cur);  // communicate Residual
   if (rc) return rc;
   fc->halo_depth = 0;
@@ -271,6 +274,7 @@ int examg_prolong_add(examg_ctx *c, int u_coarse, int uc_slot, int u_fine, int u
   GET_FIELD(fc, u_coarse); GET_FIELD(ff, u_fine);
   CHECK_SLOT(fc, uc_slot); CHECK_SLOT(ff, uf_slot);
   if (fc->level != ff->level - 1) return set_error(EXAMG_EINVAL, "examg_prolong_add: levels %d -> %d", fc->level, ff->level);
+  if (ff->loc != 0 || fc->loc != 0) return set_error(EXAMG_EUNSUP, "examg_prolong_add: node-localised fields (cell fields: examg_prolong_add_cell)");
   ff->halo_depth = 0;
   return launch_prolong(c, ff->level, field_ptr(c, fc, uc_slot), field_ptr(c, ff, uf_slot));
 }
@@ -416,6 +420,7 @@ int examg_cg_coarse(examg_ctx *c, int A, int u, int rhs, int res, int p, int ap,
   GET_STENCIL(s, A); GET_FIELD(fu, u); GET_FIELD(fr, rhs); GET_FIELD(fres, res); GET_FIELD(fp, p); GET_FIELD(fap, ap);
   CHECK_LEVEL(fu, s->level); CHECK_LEVEL(fr, s->level); CHECK_LEVEL(fres, s->level);
   CHECK_LEVEL(fp, s->level); CHECK_LEVEL(fap, s->level);
+  if (fu->loc != 0) return set_error(EXAMG_EUNSUP, "examg_cg_coarse: node-localised fields");
   int rc = launch_cg(c, *s, field_ptr(c, fu, -1), field_ptr(c, fr, -1), field_ptr(c, fres, -1), field_ptr(c, fp, -1),
                      field_ptr(c, fap, -1), max_it, rel_tol);
   if (rc || !iters_out) return rc;

@@ -64,3 +64,24 @@ def test_oracle_parity(name, dim, neumann, lvl, oracle):
         assert abs(gpu.max_error(L) - ref.max_error(L)) <= 1e-10 * ref.max_error(L)
     gpu.close()
     ref.close()
+
+
+def test_node_only_entry_points_reject_cell_fields():
+    """Entry points whose loops exist for node fields only fail loudly on cell-localised handles instead of running
+    with the wrong iteration space."""
+    from exastencils_b200 import runtime as rt
+    ctx = rt.Context(3, 1, 2, block_cells=(2, 2, 2))
+    cf, cc = ctx.field_create_cell("f", 2), ctx.field_create_cell("c", 1)
+    offs = [(0, 0, 0), (1, 0, 0), (-1, 0, 0), (0, 1, 0), (0, -1, 0), (0, 0, 1), (0, 0, -1)]
+    A = ctx.stencil_const(1, offs, [6.0] + [-1.0] * 6)
+    tmp = [ctx.field_create_cell("t%d" % k, 1) for k in range(4)]
+    with pytest.raises(rt.ExaMGError):
+        ctx.restrict(cf, cc)
+    with pytest.raises(rt.ExaMGError):
+        ctx.prolong_add(cc, cf)
+    with pytest.raises(rt.ExaMGError):
+        ctx.cg_coarse(A, cc, tmp[0], tmp[1], tmp[2], tmp[3], 10, 1e-3)
+    nf = ctx.field_create("node", 1)
+    with pytest.raises(rt.ExaMGError):
+        ctx.residual(A, cc, nf, tmp[0])  # mixed localisations
+    ctx.close()
