@@ -507,13 +507,36 @@ int examg_field_eval(examg_ctx *c, int h, int slot, int comp, const examg_bc_op 
   return EXAMG_OK;
 }
 
+int examg_field_set_bc_face(examg_ctx *c, int h, int face, int kind, double value, const examg_bc_op *prog, int n) {
+  Field *f = get_field(c, h);
+  if (!f) return set_error(EXAMG_EINVAL, "bad field %d", h);
+  if (f->loc != 1) return set_error(EXAMG_EUNSUP, "examg_field_set_bc_face: cell-localised fields");
+  if (face < 0 || face >= 2 * c->cfg.dim) return set_error(EXAMG_EINVAL, "examg_field_set_bc_face: face %d", face);
+  if (kind != EXAMG_BC_NONE && kind != EXAMG_BC_DIRICHLET_CONST && kind != EXAMG_BC_DIRICHLET_EXPR && kind != EXAMG_BC_NEUMANN)
+    return set_error(EXAMG_EINVAL, "examg_field_set_bc_face: kind %d", kind);
+  f->bc_face_prog[face].clear();
+  if (kind == EXAMG_BC_DIRICHLET_EXPR) {
+    int rc = check_program("bc program", prog, n, 0);
+    if (rc) return rc;
+    f->bc_face_prog[face].assign(prog, prog + n);
+  }
+  f->bc_face_kind[face] = kind;
+  f->bc_face_value[face] = value;
+  if (f->bc_kind == EXAMG_BC_NONE) f->bc_kind = EXAMG_BC_DIRICHLET_CONST;  // so that apply bc reaches the faces
+  return EXAMG_OK;
+}
+
 int examg_apply_bc(examg_ctx *c, int h, int slot) {
   Field *f = get_field(c, h);
   if (!f) return set_error(EXAMG_EINVAL, "bad field %d", h);
   if (slot >= f->nslots) return set_error(EXAMG_EINVAL, "bad slot %d", slot);
   if (f->bc_kind == EXAMG_BC_NONE || f->bc_kind == EXAMG_BC_DIRICHLET_HOST) return EXAMG_OK;
-  if (f->loc == 1)
-    return f->bc_kind == EXAMG_BC_NEUMANN && c->cfg.dim == 2 ? launch_bc_cell(c, *f, slot) : launch_bc_cell_generic(c, *f, slot);
+  if (f->loc == 1) {
+    bool face_own = false;
+    for (int k = 0; k < 6; ++k) face_own = face_own || f->bc_face_kind[k] >= 0;
+    return f->bc_kind == EXAMG_BC_NEUMANN && c->cfg.dim == 2 && !face_own ? launch_bc_cell(c, *f, slot)
+                                                                          : launch_bc_cell_generic(c, *f, slot);
+  }
   return launch_bc(c, *f, slot);
 }
 

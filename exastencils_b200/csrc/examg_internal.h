@@ -78,6 +78,10 @@ struct Field {
   int bc_kind = EXAMG_BC_NONE;
   double bc_value = 0.0;
   std::vector<examg_bc_op> bc_prog;
+  // per-face overrides (cell fields): kind < 0 = the field's condition
+  int bc_face_kind[6] = {-1, -1, -1, -1, -1, -1};
+  double bc_face_value[6] = {0, 0, 0, 0, 0, 0};
+  std::vector<examg_bc_op> bc_face_prog[6];
   // examg_field_eval programs applied to slot 0 since the last upload / fill, in order: a field whose every component
   // was produced this way can be re-created on another grid (the agglomerated coarse levels of a multi-block run)
   std::vector<std::pair<int, std::vector<examg_bc_op>>> evals;

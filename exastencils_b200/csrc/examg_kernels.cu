@@ -501,12 +501,6 @@ int launch_bc_cell_generic(examg_ctx *c, const Field &f, int slot) {
   a.plane = g.plane;
   a.face_mask = mask;
   a.dim = c->cfg.dim;
-  BcProg pr;
-  pr.n = 0;
-  if (f.bc_kind == EXAMG_BC_DIRICHLET_EXPR) {
-    pr.n = (int)f.bc_prog.size();
-    for (int q = 0; q < pr.n; ++q) { pr.op[q] = f.bc_prog[q].op; pr.val[q] = f.bc_prog[q].value; }
-  }
   long long maxface = 1;
   for (int d = 0; d < c->cfg.dim; ++d) {
     long long fsz = 1;
@@ -517,9 +511,33 @@ int launch_bc_cell_generic(examg_ctx *c, const Field &f, int slot) {
   int gx = (int)((maxface + 255) / 256);
   if (gx > 1024) gx = 1024;
   dim3 grid(gx, 2 * c->cfg.dim, 1);
-  for (int comp = 0; comp < f.ncomp; ++comp) {
-    k_cell_bc<<<grid, 256, 0, c->stream>>>(a, pr, f.bc_kind, f.bc_value, field_ptr(c, &f, slot, comp));
-    EXAMG_LAUNCH_CHECK(c);
+  // faces with the field's own condition in one launch, faces with a condition of their own one launch each
+  int own = 0;
+  for (int k = 0; k < 2 * c->cfg.dim; ++k)
+    if (f.bc_face_kind[k] >= 0) own |= 1 << k;
+  for (int pass = -1; pass < 2 * c->cfg.dim; ++pass) {
+    int kind = f.bc_kind, m = mask & ~own;
+    double value = f.bc_value;
+    const std::vector<examg_bc_op> *prog = &f.bc_prog;
+    if (pass >= 0) {
+      if (!((own >> pass) & 1)) continue;
+      kind = f.bc_face_kind[pass];
+      value = f.bc_face_value[pass];
+      prog = &f.bc_face_prog[pass];
+      m = mask & (1 << pass);
+    }
+    if (!m || kind == EXAMG_BC_NONE || kind == EXAMG_BC_DIRICHLET_HOST) continue;
+    BcProg pr;
+    pr.n = 0;
+    if (kind == EXAMG_BC_DIRICHLET_EXPR) {
+      pr.n = (int)prog->size();
+      for (int q = 0; q < pr.n; ++q) { pr.op[q] = (*prog)[q].op; pr.val[q] = (*prog)[q].value; }
+    }
+    a.face_mask = m;
+    for (int comp = 0; comp < f.ncomp; ++comp) {
+      k_cell_bc<<<grid, 256, 0, c->stream>>>(a, pr, kind, value, field_ptr(c, &f, slot, comp));
+      EXAMG_LAUNCH_CHECK(c);
+    }
   }
   return EXAMG_OK;
 }

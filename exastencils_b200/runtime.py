@@ -97,6 +97,7 @@ SIGNATURES = {
                                         C.c_double, C.POINTER(C.c_int)]),
     "examg_smooth_colored": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_double, C.c_int, C.c_int]),
     "examg_field_print": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_char_p, C.c_char_p]),
+    "examg_field_set_bc_face": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_double, C.POINTER(BcOp), C.c_int]),
     "examg_field_eval": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.POINTER(BcOp), C.c_int]),
     "examg_apply_bc": (C.c_int, [C.c_void_p, C.c_int, C.c_int]),
     "examg_field_upload": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_void_p]),
@@ -299,6 +300,14 @@ class Context:
         for i, (op, val) in enumerate(prog):
             arr[i].op, arr[i].value = op, val
         check(self.L.examg_field_set_bc_expr(self.h, f, arr, len(prog)))
+
+    def field_set_bc_face(self, f, face, kind, value=0.0, prog=None):
+        """A condition of its own for face 2*d + side of a cell field."""
+        n = len(prog) if prog else 0
+        arr = (BcOp * max(n, 1))()
+        for i, (op, val) in enumerate(prog or []):
+            arr[i].op, arr[i].value = op, val
+        check(self.L.examg_field_set_bc_face(self.h, f, face, kind, value, arr, n))
 
     def field_eval(self, f, prog, comp=0, slot=-1):
         """loop over F { F[comp] = <postfix program over the node position> } (local nodes + one ghost layer)."""

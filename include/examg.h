@@ -127,6 +127,12 @@ enum {
 typedef struct { int op; double value; } examg_bc_op;
 int examg_field_set_bc(examg_ctx *ctx, int field, int kind, double value);
 int examg_field_set_bc_expr(examg_ctx *ctx, int field, const examg_bc_op *prog, int n_ops);
+/* A boundary condition of its own for ONE face (face = 2*d + side) of a cell-localised field: what a user-written
+ * boundary function with `loop over F only ghost [..] on boundary` per face does
+ * (Benchmark/FivePointStencil/5pt_Jac_Cell.exa4 `applyBC_solution`).  kind: EXAMG_BC_NONE (leave the face alone),
+ * _DIRICHLET_CONST (value), _DIRICHLET_EXPR (prog), _NEUMANN; the other faces keep the field's condition.      */
+int examg_field_set_bc_face(examg_ctx *ctx, int field, int face, int kind, double value, const examg_bc_op *prog,
+                            int n_ops);
 /* loop over F { F[comp] = <expr> } with <expr> a postfix program over vf_nodePosition_{x,y,z}: the initialisation
  * loops of the L4 programs (InitRHS, InitLaplace of Testing/SISC/3D_VarCoeff.exa4:212-240).  Runs on every local node
  * and on the first ghost layer (node positions continue beyond the block), so stencil-field coefficients need no

@@ -85,3 +85,36 @@ def test_node_only_entry_points_reject_cell_fields():
     with pytest.raises(rt.ExaMGError):
         ctx.residual(A, cc, nf, tmp[0])  # mixed localisations
     ctx.close()
+
+
+def test_five_point_benchmark_app(oracle):
+    """Benchmark/FivePointStencil/5pt_Jac_Cell.exa4 (tools/fivepoint_bench.py) at level 5: anisotropic cell widths, the
+    user-written ghost-cell function (a condition of its own on the top face, examg_field_set_bc_face) -- 20 iterations of
+    Smoother + UpResidual against the oracle's cell loops."""
+    import math
+    import sys, os
+    sys.path.insert(0, os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tools"))
+    import fivepoint_bench as fb
+    og = oracle
+    og.set_periodic((0, 0, 0))
+    lvl = 5
+    ctx, A, u, f, r, (nx, ny, hx, hy) = fb.setup(lvl)
+    offs = [(0, 0, 0), (1, 0, 0), (-1, 0, 0), (0, 1, 0), (0, -1, 0)]
+    st = og.Stencil.make(offs, [(2.0 / (hx * hx)) + (2.0 / (hy * hy)), -1.0 / (hx * hx), -1.0 / (hx * hx),
+                                -1.0 / (hy * hy), -1.0 / (hy * hy)])
+    U = np.zeros((1, ny + 2, nx + 2))
+    F = np.zeros_like(U)
+    F[:, 1:-1, 1:-1] = ctx.download_cells(f, lvl)
+    top = 0.5 * (np.sin((2.0 * math.pi) * (np.arange(nx) * hx)) * math.sinh(2.0 * math.pi))
+    faces = [None, None, None, np.ascontiguousarray(top.reshape(1, nx)), None, None]
+    for it in range(20):
+        got = fb.iteration(ctx, A, u, f, r)
+        og.cell_apply_bc(2, U, og.BC_CELL_DIRICHLET, faces)
+        U = og.smooth_jacobi(st, 0.8, U, F)
+        og.cell_apply_bc(2, U, og.BC_CELL_DIRICHLET, faces)
+        R = og.residual(st, U, F)
+        want = math.sqrt(og.dot(R, R))
+        assert abs(got - want) <= 1e-11 * want, it
+    ug = ctx.download_cells(u, lvl)
+    assert np.allclose(ug, U[:, 1:-1, 1:-1], rtol=1e-11, atol=1e-11 * np.max(np.abs(U)))
+    ctx.close()
