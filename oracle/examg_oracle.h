@@ -140,7 +140,17 @@ typedef struct {
   double restrict_scale; /* 1 or 4 (Testing/Smoothers: 4.0 * RestrictionStencil) */
   int cg_max_it;
   double cg_rel_tol;     /* 1e-3 */
+  double domain_hi[3];   /* Domain global< [0,0,0] to hi >; 0 = 1.0 (the unit cube of every shipped program).  bench.py's
+                            weak-scaling runs grow the domain with the block grid so that the mesh width stays put */
 } og_config;
+
+/* OpenMP team size of the `parallel for` loops (omp_numThreads of the Knowledge file,
+ * C/s/e/parallelization/api/omp/OMP_Loop.scala:101-110).  A launcher such as torchrun exports OMP_NUM_THREADS=1;
+ * the timed CPU baseline sets the count explicitly and reports what OpenMP really uses. */
+void og_set_num_threads(int n);
+int og_get_max_threads(void);
+/* threads of an actual parallel region (what a loop gets, after OMP_DYNAMIC / cgroup limits) */
+int og_count_threads(void);
 
 typedef struct og_solver og_solver;
 

@@ -9,6 +9,8 @@
  * generator: C/s/e/solver/l3/L3_SolverForEquation.scala:341-395,
  * C/s/e/solver/l3/L3_ConjugateGradientForEquation.scala:37-151).
  */
+#include <omp.h>
+
 #include "examg_oracle.h"
 
 #include <math.h>
@@ -153,6 +155,18 @@ static void og_init_varcoeff27(const og_config *c, og_level *l) {
       }
 }
 
+void og_set_num_threads(int n) { if (n > 0) omp_set_num_threads(n); }
+int og_get_max_threads(void) { return omp_get_max_threads(); }
+int og_count_threads(void) {
+  int n = 1;
+#pragma omp parallel
+  {
+#pragma omp master
+    n = omp_get_num_threads();
+  }
+  return n;
+}
+
 og_solver *og_solver_create(const og_config *cfg) {
   og_solver *s = (og_solver *)calloc(1, sizeof(*s));
   s->cfg = *cfg;
@@ -164,7 +178,8 @@ og_solver *og_solver_create(const og_config *cfg) {
       if (d < cfg->dim) {
         int cells = cfg->F[d] << lvl;
         l->n[d] = cells + 1;
-        l->h[d] = 1.0 / (double)cells; /* IR_DomainFromAABB.scala:31-40, domain [0,1]^d */
+        const double hi = cfg->domain_hi[d] > 0.0 ? cfg->domain_hi[d] : 1.0;
+        l->h[d] = hi / (double)cells; /* IR_DomainFromAABB.scala:31-40, domain [0,hi]^d */
       } else { l->n[d] = 1; l->h[d] = 1.0; }
     }
     l->size = (size_t)l->n[0] * l->n[1] * l->n[2];

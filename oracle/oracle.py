@@ -45,7 +45,8 @@ class Config(C.Structure):
     _fields_ = [("dim", C.c_int), ("F", C.c_int * 3), ("min_level", C.c_int), ("max_level", C.c_int),
                 ("op", C.c_int), ("order", C.c_int), ("kappa", C.c_double), ("smoother", C.c_int),
                 ("omega", C.c_double), ("nu_pre", C.c_int), ("nu_post", C.c_int),
-                ("restrict_scale", C.c_double), ("cg_max_it", C.c_int), ("cg_rel_tol", C.c_double)]
+                ("restrict_scale", C.c_double), ("cg_max_it", C.c_int), ("cg_rel_tol", C.c_double),
+                ("domain_hi", C.c_double * 3)]
 
 
 def build(force=False):
@@ -117,8 +118,18 @@ def lib():
     L.og_solver_last_cg_iters.argtypes = [C.c_void_p]
     L.og_solver_last_cg_iters.restype = C.c_int
     L.og_print_reduced_prec.argtypes = [C.c_double, C.c_char_p, C.c_size_t]
+    L.og_set_num_threads.argtypes = [C.c_int]
+    L.og_set_num_threads.restype = None
+    L.og_get_max_threads.restype = C.c_int
+    L.og_count_threads.restype = C.c_int
     _lib = L
     return L
+
+
+def set_num_threads(n):
+    """omp_numThreads of the timed CPU baseline; returns the team size an OpenMP loop really gets."""
+    lib().og_set_num_threads(int(n))
+    return lib().og_count_threads()
 
 
 def _dp(a):
@@ -277,8 +288,10 @@ class Solver:
 
     def __init__(self, dim, F, min_level, max_level, op=OP_LAPLACE_SCALED, order=ORDER_BENCH, kappa=0.0,
                  smoother=SMOOTH_RBGS, omega=0.8, nu_pre=3, nu_post=3, restrict_scale=1.0,
-                 cg_max_it=128, cg_rel_tol=1e-3):
+                 cg_max_it=128, cg_rel_tol=1e-3, domain_hi=(1.0, 1.0, 1.0)):
         cfg = Config()
+        for d in range(3):
+            cfg.domain_hi[d] = domain_hi[d] if d < len(domain_hi) else 1.0
         cfg.dim = dim
         F = list(F) + [1] * (3 - len(F))
         for d in range(3):
@@ -335,7 +348,8 @@ class Solver:
         F = self.cfg.F
         out = []
         for d, n in enumerate((nx, ny, nz)):
-            out.append(np.arange(n, dtype=np.float64) * (1.0 / float(n - 1)) if n > 1 else np.zeros(1))
+            hi = self.cfg.domain_hi[d] if self.cfg.domain_hi[d] > 0.0 else 1.0
+            out.append(np.arange(n, dtype=np.float64) * (hi / float(n - 1)) if n > 1 else np.zeros(1))
         return out
 
     def sync_slots(self):
