@@ -118,6 +118,7 @@ SIGNATURES = {
     "examg_residual_restrict": (C.c_int, [C.c_void_p] + [C.c_int] * 5 + [C.c_double]),
     "examg_prolong_add": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int]),
     "examg_dot": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, _dp]),
+    "examg_dot_dense_noalloc": (C.c_int, [C.c_void_p, C.c_void_p, C.c_longlong, C.c_void_p, C.c_void_p]),
     "examg_max_abs_diff": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, _dp]),
     "examg_set": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_double]),
     "examg_copy": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int]),

@@ -213,6 +213,16 @@ int examg_residual_restrict(examg_ctx *ctx, int stencil, int u, int rhs, int res
 int examg_prolong_add(examg_ctx *ctx, int u_coarse, int u_coarse_slot, int u_fine, int u_fine_slot);
 /* loop over F with reduction(+: x) { x += a * b }; global over all blocks */
 int examg_dot(examg_ctx *ctx, int a, int a_slot, int b, int b_slot, double *out);
+/* No counterpart in the reference.  The dot-product reduction of
+ * examg_dot for callers that may not allocate (CUDA graph capture, tight serving loops, harnesses that forbid
+ * cudaMalloc): *out_dev = sum a_dev[i] * b_dev[i], i < n, double-double accumulation as examg_dot.  All four
+ * pointers are plain device addresses of the caller (dense arrays, no context, no handles); the per-block partial
+ * sums live in a 65 792-byte file-scope device array that every GPU loading the library holds until exit.  n is
+ * limited to EXAMG_NOALLOC_MAX_N elements (larger: EXAMG_EINVAL with a message).  Calls no cudaMalloc / cudaFree or
+ * allocating routine; asynchronous on cuda_stream (a cudaStream_t, NULL = default stream).  All calls share the
+ * array: calls that overlap on the GPU (unordered streams, several host threads) race -- serialise them.        */
+#define EXAMG_NOALLOC_MAX_N (1LL << 28)
+int examg_dot_dense_noalloc(const double *a_dev, const double *b_dev, long long n, double *out_dev, void *cuda_stream);
 /* max |a - b| over the loop points (PrintError / NormError) */
 int examg_max_abs_diff(examg_ctx *ctx, int a, int a_slot, int b, int b_slot, double *out);
 /* streaming loops on the loop points */
