@@ -11,17 +11,22 @@
 //     plus (field, buffer, block, offset) entries and its flag page; the host process group
 //     all-gathers the blobs (examg_comm_export / examg_comm_import); a rank maps the blocks of its
 //     face neighbours and of rank 0, and the flag pages of everybody.
-//   * exchange of dimension d = ONE kernel: tell the neighbours "ready to receive" (flag in their
-//     memory), wait for theirs, store the boundary layers straight into their ghost layers
-//     (remote stores over NVLink, no pack buffer, no host), fence, tell them "done", wait for theirs.
-//     Dimensions run one after the other and faces carry the orthogonal ghost layers already
-//     received, so edges and corners become valid as in the reference.  `depth` ghost layers + the
-//     duplicate layer travel (+dir block's node 0 := -dir block's node n-1, as IR_PackInfoDuplicate).
+//   * one `communicate` = ONE kernel and ONE handshake (k_exchange_all): tell the neighbours "ready to
+//     receive" (flag in their memory), wait for theirs, store the boundary layers straight into the ghost
+//     layers of the face, edge and corner neighbours (remote stores over NVLink, no pack buffer, no host),
+//     fence, tell them "done", wait for theirs.  The reference runs the dimensions one after the other and
+//     forwards received ghosts so that edges and corners become valid (three dependent message rounds);
+//     behind an NVSwitch every peer is one hop away, so the diagonal neighbours are written directly.
+//     `depth` ghost layers + the duplicate layer travel (+dir block's node 0 := -dir block's node n-1, as
+//     IR_PackInfoDuplicate).
 //   * epochs are counted on the device, so the same kernels replay inside a CUDA graph.
 //   * sums: every rank stores its double-double partial into a mailbox of every rank and adds the
 //     mailboxes in rank order -- deterministic and identical on all ranks.
-//   * every spin is bounded (~2 s): a lost peer turns into EXAMG_ESTATE on the next host
-//     synchronisation instead of a hung GPU.
+//   * every wait for a peer is bounded (EXAMG_PEER_TIMEOUT_S, default 60 s, 0 = for ever as MPI would):
+//     on a timeout the operation is ABANDONED -- no remote store, no signal, no epoch bump, partial sums
+//     untouched -- the failure is sticky (later communication kernels return at once) and every host
+//     synchronisation of the context reports EXAMG_ESTATE (comm_poll_error through a mapped pinned word).
+//     Ranks must therefore reach matching calls within that time of one another.
 // Kernels of different ranks wait for one another: ranks must sit on different GPUs
 // (examg_comm_import refuses two ranks on one device).
 #include <array>
@@ -36,15 +41,15 @@ namespace {
 constexpr int MAXW = 64;                 // ranks
 constexpr int FLAG_WORDS = 1024;         // 8 KiB flag page
 // word indices in the flag page
-constexpr int F_READY = 0;               // [2*d + side]   written by the neighbour on that side
-constexpr int F_DONE = 8;                // [2*d + side]
-constexpr int F_ERROR = 15;              // set locally when a wait timed out
-constexpr int F_EPOCH = 16;              // local: [d] exchange, [3] reduction, [4] gather, [5] scatter
-constexpr int F_TICKET = 24;             // local: [d] block counter of the exchange kernel
+constexpr int F_ERROR = 15;              // set locally when a wait timed out (sticky: every later kernel returns at once)
+constexpr int F_EPOCH = 16;              // local: [0] exchange, [3] reduction, [4] gather, [5] scatter
+constexpr int F_TICKET = 24;             // local: [0] block counter of the exchange kernel, [4] gather, [5] scatter
 constexpr int F_AGG_IN = 32;             // on rank 0: [rank] gather epoch
 constexpr int F_AGG_OUT = 96;            // on every rank: scatter epoch, written by rank 0
 constexpr int F_MAIL = 128;              // [parity][rank]{hi, lo, epoch}
-constexpr long long SPIN_LIMIT = 4000000000LL;  // clock64 ticks
+constexpr int F_READY = 512;             // [direction code]  written by the neighbour in that direction
+constexpr int F_DONE = 544;              // [direction code]
+constexpr int NPEER = 26;                // face, edge and corner neighbours
 
 constexpr unsigned BLOB_MAGIC = 0x45584d47u;  // "EXMG"
 constexpr int BLOB_MAX_BLOCKS = 96, BLOB_MAX_ENTRIES = 512;
@@ -68,90 +73,153 @@ __device__ __forceinline__ unsigned long long ld_acquire_sys(const unsigned long
 __device__ __forceinline__ void st_release_sys(unsigned long long *p, unsigned long long v) {
   asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
 }
+__device__ __forceinline__ unsigned long long global_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
+// What every kernel of this file gets about waiting: the local flag page, the host-visible error word and the
+// longest time a wait for a peer may take (0 = wait for ever, as MPI would).
+struct WaitCtl {
+  unsigned long long *flags;
+  int *err_host;                  // mapped pinned memory: the host sees a failure without a copy
+  unsigned long long timeout_ns;
+};
 // wait until *p >= want; false on timeout
-__device__ __forceinline__ bool spin_ge(const unsigned long long *p, unsigned long long want, unsigned long long *flags) {
-  const long long t0 = clock64();
+__device__ __forceinline__ bool spin_ge(const unsigned long long *p, unsigned long long want, const WaitCtl &w) {
+  if (ld_acquire_sys(p) >= want) return true;
+  const unsigned long long t0 = global_ns();
   while (ld_acquire_sys(p) < want) {
-    if (clock64() - t0 > SPIN_LIMIT) {
-      flags[F_ERROR] = 1;
-      return false;
-    }
+    if (w.timeout_ns && global_ns() - t0 > w.timeout_ns) return false;
     __nanosleep(100);
   }
   return true;
 }
+// A wait timed out: the operation is abandoned (no remote stores, no signals, no epoch bump) and the failure is
+// sticky -- every later communication kernel of this context returns at once, the host reports EXAMG_ESTATE at its
+// next synchronisation (comm_poll_error).
+__device__ __forceinline__ void comm_fail(const WaitCtl &w) {
+  *reinterpret_cast<volatile unsigned long long *>(w.flags + F_ERROR) = 1ULL;
+  *reinterpret_cast<volatile int *>(w.err_host) = 1;
+  __threadfence_system();
+}
+__device__ __forceinline__ bool comm_dead(const WaitCtl &w) {
+  return *reinterpret_cast<volatile unsigned long long *>(w.flags + F_ERROR) != 0ULL;
+}
 
-struct Box { int lo[3], ext[3]; };
+constexpr int EXF = 4;  // field components per exchange kernel
 
-constexpr int EXF = 4;  // face copies (field components) per exchange kernel
-
-struct FaceCopy {
-  const double *src;        // node (0,0,0) of the local buffer
-  double *dst[2];           // node (0,0,0) of the neighbour's buffer on side 0 (-) / 1 (+)
-  Box sbox[2];              // d == 0: what is sent to side s (local coordinates) ...
-  int dlo[2][3];            //         ... and where it lands (neighbour coordinates)
-  // d >= 1: whole rows travel (x pad included), so a face is `nchunks` runs of `len2` double2
-  long long soff[2], doff[2];  // first element of the runs, relative to src / dst[s]
-  long long len2[2];
-  int nchunks;
-  long long cstride;        // elements between runs
+// `communicate` of up to EXF field components with ONE handshake: every block stores its boundary layers straight
+// into the ghost layers of its face, edge AND corner neighbours (the reference reaches edges and corners by running
+// the dimensions one after the other and forwarding ghosts, IR_CommunicateFunction.scala:412-470: three dependent
+// message rounds; over NVSwitch every peer is one hop away, so the diagonal neighbours are written directly).
+// Direction v of a peer, per dimension: -1: my layers 1..G -> its n..n+G-1;  +1: my layers n-1-G..n-1 -> its -G..0
+// (ghosts + the duplicate layer, IR_PackInfoDuplicate.scala:15-39);  0: my nodes 0..n-1 -> the same nodes.
+// Nodes shared by several blocks are written more than once with bit-identical values (arithmetic contract).
+struct ExchField {
+  const double *src;  // node (0,0,0) of the local buffer
+  int n[3];
   int pitch;
   long long plane;
+  int depth;
 };
-
+struct ExchPeer {
+  int v[3];
+  int code;                    // (vx+1) + 3 (vy+1) + 9 (vz+1): index of the flag this peer writes here
+  unsigned long long *pflags;  // its flag page
+  double *dst[EXF];            // node (0,0,0) of its buffer per field
+};
 struct ExchArgs {
-  int d;
-  int has[2];               // neighbour on side 0 (-) / 1 (+)
-  int nf;
-  FaceCopy f[EXF];
-  unsigned long long *flags;      // local flag page
-  unsigned long long *pflags[2];  // neighbours' flag pages
+  int nf, np;
+  ExchField f[EXF];
+  ExchPeer p[NPEER];
+  WaitCtl w;
 };
 
-__global__ void __launch_bounds__(256) k_exchange_dim(const __grid_constant__ ExchArgs a) {
-  unsigned long long *fl = a.flags;
-  const unsigned long long e = *reinterpret_cast<volatile unsigned long long *>(fl + F_EPOCH + a.d) + 1;
-  // ready-to-receive: this rank no longer reads the ghost layers of the previous epoch
-  if (blockIdx.x == 0 && threadIdx.x < 2 && a.has[threadIdx.x])
-    st_release_sys(a.pflags[threadIdx.x] + F_READY + 2 * a.d + (1 - threadIdx.x), e);
-  if (threadIdx.x < 2 && a.has[threadIdx.x]) spin_ge(fl + F_READY + 2 * a.d + threadIdx.x, e, fl);
+__global__ void __launch_bounds__(256) k_exchange_all(const __grid_constant__ ExchArgs a) {
+  unsigned long long *fl = a.w.flags;
+  if (comm_dead(a.w)) return;
+  const unsigned long long e = *reinterpret_cast<volatile unsigned long long *>(fl + F_EPOCH) + 1;
+  __shared__ int ok;
+  if (threadIdx.x == 0) ok = 1;
   __syncthreads();
-  for (int fi = 0; fi < a.nf; ++fi) {
-    const FaceCopy &fc = a.f[fi];
-    for (int s = 0; s < 2; ++s) {
-      if (!a.has[s]) continue;
-      double *dst = fc.dst[s];
-      if (a.d == 0) {
-        // x faces: rows are a few elements long; consecutive threads take consecutive rows
-        const Box &b = fc.sbox[s];
-        const long long rows = (long long)b.ext[1] * b.ext[2];
-        for (long long t = blockIdx.x * (long long)blockDim.x + threadIdx.x; t < rows; t += (long long)gridDim.x * blockDim.x) {
-          const int j = (int)(t % b.ext[1]), k = (int)(t / b.ext[1]);
-          const long long so = b.lo[0] + (long long)fc.pitch * (b.lo[1] + j) + fc.plane * (b.lo[2] + k);
-          const long long dof = fc.dlo[s][0] + (long long)fc.pitch * (fc.dlo[s][1] + j) + fc.plane * (fc.dlo[s][2] + k);
-          for (int i = 0; i < b.ext[0]; ++i) dst[dof + i] = fc.src[so + i];
-        }
-      } else {
-        // y / z faces: runs of whole rows, 128-bit accesses, four independent loads per thread in flight
-        const long long n2 = fc.len2[s] * fc.nchunks;
-        const long long stride = (long long)gridDim.x * blockDim.x;
-        const double *sb = fc.src + fc.soff[s];
-        double *db = dst + fc.doff[s];
-        for (long long t0 = blockIdx.x * (long long)blockDim.x + threadIdx.x; t0 < n2; t0 += 4 * stride) {
-          double2 v[4];
-          long long off[4];
+  // ready-to-receive: this rank no longer reads the ghost layers of the previous epoch
+  if ((int)threadIdx.x < a.np) {
+    const ExchPeer &p = a.p[threadIdx.x];
+    if (blockIdx.x == 0) st_release_sys(p.pflags + F_READY + (26 - p.code), e);
+    if (!spin_ge(fl + F_READY + p.code, e, a.w)) ok = 0;
+  }
+  __syncthreads();
+  if (!ok) {
+    if (threadIdx.x == 0) comm_fail(a.w);
+    return;
+  }
+  const long long tid = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  for (int pi = 0; pi < a.np; ++pi) {
+    const ExchPeer &p = a.p[pi];
+    for (int q = 0; q < a.nf; ++q) {
+      const ExchField &f = a.f[q];
+      const int G = f.depth;
+      int slo[3], dlo[3], ext[3];
 #pragma unroll
-          for (int q = 0; q < 4; ++q) {
-            const long long t = t0 + q * stride;
-            if (t < n2) {
-              const long long ch = fc.nchunks == 1 ? 0 : t / fc.len2[s];
-              off[q] = ch * fc.cstride + 2 * (t - ch * fc.len2[s]);
-              v[q] = *reinterpret_cast<const double2 *>(sb + off[q]);
+      for (int w = 0; w < 3; ++w) {
+        if (p.v[w] == 0) { slo[w] = 0; dlo[w] = 0; ext[w] = f.n[w]; }
+        else if (p.v[w] < 0) { slo[w] = 1; dlo[w] = f.n[w]; ext[w] = G; }
+        else { slo[w] = f.n[w] - 1 - G; dlo[w] = -G; ext[w] = G + 1; }
+      }
+      const double *sb = f.src + slo[0] + (long long)f.pitch * slo[1] + f.plane * slo[2];
+      double *db = p.dst[q] + dlo[0] + (long long)f.pitch * dlo[1] + f.plane * dlo[2];
+      if (p.v[0] == 0) {
+        // whole rows of the block's own nodes: node 0 of a row is 128-byte aligned on both sides -> 128-bit accesses
+        // (the odd last node of a row travels alone), four independent loads per thread in flight
+        const int h = (ext[0] + 1) >> 1;
+        const long long total = (long long)h * ext[1] * ext[2];
+        for (long long t0 = tid; t0 < total; t0 += 4 * stride) {
+          double2 val[4];
+          long long off[4];
+          bool pair[4];
+#pragma unroll
+          for (int u = 0; u < 4; ++u) {
+            const long long t = t0 + u * stride;
+            if (t < total) {
+              const int i2 = (int)(t % h);
+              const long long r = t / h;
+              const int j = (int)(r % ext[1]), k = (int)(r / ext[1]);
+              off[u] = 2 * i2 + (long long)f.pitch * j + f.plane * k;
+              pair[u] = 2 * i2 + 1 < ext[0];
+              if (pair[u]) val[u] = *reinterpret_cast<const double2 *>(sb + off[u]);
+              else val[u].x = sb[off[u]];
             }
           }
 #pragma unroll
-          for (int q = 0; q < 4; ++q)
-            if (t0 + q * stride < n2) *reinterpret_cast<double2 *>(db + off[q]) = v[q];
+          for (int u = 0; u < 4; ++u)
+            if (t0 + u * stride < total) {
+              if (pair[u]) *reinterpret_cast<double2 *>(db + off[u]) = val[u];
+              else db[off[u]] = val[u].x;
+            }
+        }
+      } else {
+        // x faces, and edges / corners with an x component: G (G+1) nodes per row; consecutive threads take
+        // consecutive nodes, so a warp moves whole 32-byte sectors of 32/G rows
+        const long long total = (long long)ext[0] * ext[1] * ext[2];
+        for (long long t0 = tid; t0 < total; t0 += 4 * stride) {
+          double val[4];
+          long long off[4];
+#pragma unroll
+          for (int u = 0; u < 4; ++u) {
+            const long long t = t0 + u * stride;
+            if (t < total) {
+              const int i = (int)(t % ext[0]);
+              const long long r = t / ext[0];
+              const int j = (int)(r % ext[1]), k = (int)(r / ext[1]);
+              off[u] = i + (long long)f.pitch * j + f.plane * k;
+              val[u] = sb[off[u]];
+            }
+          }
+#pragma unroll
+          for (int u = 0; u < 4; ++u)
+            if (t0 + u * stride < total) db[off[u]] = val[u];
         }
       }
     }
@@ -159,36 +227,40 @@ __global__ void __launch_bounds__(256) k_exchange_dim(const __grid_constant__ Ex
   __threadfence_system();
   __syncthreads();
   __shared__ int last;
-  if (threadIdx.x == 0) {
-    const unsigned long long ticket = atomicAdd(fl + F_TICKET + a.d, 1ULL);
-    last = ticket == gridDim.x - 1;
-  }
+  if (threadIdx.x == 0) last = atomicAdd(fl + F_TICKET, 1ULL) == gridDim.x - 1;
   __syncthreads();
   if (!last) return;
   __threadfence_system();
-  if (threadIdx.x < 2 && a.has[threadIdx.x]) {
-    st_release_sys(a.pflags[threadIdx.x] + F_DONE + 2 * a.d + (1 - threadIdx.x), e);
-    spin_ge(fl + F_DONE + 2 * a.d + threadIdx.x, e, fl);
+  if ((int)threadIdx.x < a.np) {
+    const ExchPeer &p = a.p[threadIdx.x];
+    st_release_sys(p.pflags + F_DONE + (26 - p.code), e);
+    if (!spin_ge(fl + F_DONE + p.code, e, a.w)) ok = 0;
   }
   __syncthreads();
   if (threadIdx.x == 0) {
-    fl[F_TICKET + a.d] = 0;
-    *reinterpret_cast<volatile unsigned long long *>(fl + F_EPOCH + a.d) = e;
+    if (!ok) { comm_fail(a.w); return; }
+    fl[F_TICKET] = 0;
+    *reinterpret_cast<volatile unsigned long long *>(fl + F_EPOCH) = e;
   }
 }
 
 struct RedArgs {
   int world, rank;
-  unsigned long long *flags;
+  int op;  // 0: double-double sum, 1: maximum of .hi
+  WaitCtl w;
   unsigned long long *pflags[MAXW];
-  dd *value;  // in: this rank's partial, out: the global sum
+  dd *value;  // in: this rank's partial, out: the global result
 };
 
 __global__ void __launch_bounds__(MAXW) k_allreduce_dd(const __grid_constant__ RedArgs a) {
-  unsigned long long *fl = a.flags;
+  unsigned long long *fl = a.w.flags;
+  if (comm_dead(a.w)) return;
   const unsigned long long e = *reinterpret_cast<volatile unsigned long long *>(fl + F_EPOCH + 3) + 1;
   const int par = (int)(e & 1);
   const int r = threadIdx.x;
+  __shared__ int ok;
+  if (r == 0) ok = 1;
+  __syncthreads();
   if (r < a.world) {
     unsigned long long *m = a.pflags[r] + F_MAIL + 3 * (par * MAXW + a.rank);
     const dd v = *a.value;
@@ -196,17 +268,19 @@ __global__ void __launch_bounds__(MAXW) k_allreduce_dd(const __grid_constant__ R
     m[1] = (unsigned long long)__double_as_longlong(v.lo);
     __threadfence_system();
     st_release_sys(m + 2, e);
-    spin_ge(fl + F_MAIL + 3 * (par * MAXW + r) + 2, e, fl);
+    if (!spin_ge(fl + F_MAIL + 3 * (par * MAXW + r) + 2, e, a.w)) ok = 0;
   }
   __syncthreads();
   if (r == 0) {
+    if (!ok) { comm_fail(a.w); return; }  // the partial stays: no stale mailbox is added
     dd s = {0.0, 0.0};
     for (int q = 0; q < a.world; ++q) {
       const unsigned long long *m = fl + F_MAIL + 3 * (par * MAXW + q);
       dd v;
       v.hi = __longlong_as_double((long long)ld_acquire_sys(m));
       v.lo = __longlong_as_double((long long)ld_acquire_sys(m + 1));
-      dd_merge(s, v);
+      if (a.op == 0) dd_merge(s, v);
+      else s.hi = q == 0 ? v.hi : fmax(s.hi, v.hi);
     }
     *a.value = s;
     *reinterpret_cast<volatile unsigned long long *>(fl + F_EPOCH + 3) = e;
@@ -224,13 +298,15 @@ struct AggArgs {
   double *fdst;        // scatter: local field
   double *dense;       // staging array on rank 0 (peer pointer on the other ranks)
   int rank, world;
-  unsigned long long *flags, *flags0;  // local page / rank 0's page
+  WaitCtl w;                           // local flag page
+  unsigned long long *flags0;          // rank 0's page
   unsigned long long *pflags[MAXW];    // scatter signal: rank 0 -> everybody
 };
 
 // every rank: field -> rank 0's dense array, then signal; rank 0 additionally waits for everybody
 __global__ void __launch_bounds__(256) k_agg_gather(const __grid_constant__ AggArgs a) {
-  unsigned long long *fl = a.flags;
+  unsigned long long *fl = a.w.flags;
+  if (comm_dead(a.w)) return;
   const unsigned long long e = *reinterpret_cast<volatile unsigned long long *>(fl + F_EPOCH + 4) + 1;
   const long long total = (long long)a.n[0] * a.n[1] * a.n[2];
   for (long long t = blockIdx.x * (long long)blockDim.x + threadIdx.x; t < total; t += (long long)gridDim.x * blockDim.x) {
@@ -247,10 +323,16 @@ __global__ void __launch_bounds__(256) k_agg_gather(const __grid_constant__ AggA
   __syncthreads();
   if (!last) return;
   __threadfence_system();
-  if (threadIdx.x == 0) st_release_sys(a.flags0 + F_AGG_IN + a.rank, e);
-  if (a.rank == 0 && threadIdx.x < a.world) spin_ge(fl + F_AGG_IN + threadIdx.x, e, fl);
+  __shared__ int ok;
+  if (threadIdx.x == 0) {
+    ok = 1;
+    st_release_sys(a.flags0 + F_AGG_IN + a.rank, e);
+  }
+  __syncthreads();
+  if (a.rank == 0 && (int)threadIdx.x < a.world && !spin_ge(fl + F_AGG_IN + threadIdx.x, e, a.w)) ok = 0;
   __syncthreads();
   if (threadIdx.x == 0) {
+    if (!ok) { comm_fail(a.w); return; }
     fl[F_TICKET + 4] = 0;
     *reinterpret_cast<volatile unsigned long long *>(fl + F_EPOCH + 4) = e;
   }
@@ -258,7 +340,8 @@ __global__ void __launch_bounds__(256) k_agg_gather(const __grid_constant__ AggA
 
 // rank 0: signal "dense solution ready" to everybody (one block)
 __global__ void __launch_bounds__(MAXW) k_agg_signal(const __grid_constant__ AggArgs a) {
-  unsigned long long *fl = a.flags;
+  unsigned long long *fl = a.w.flags;
+  if (comm_dead(a.w)) return;
   const unsigned long long e = *reinterpret_cast<volatile unsigned long long *>(fl + F_EPOCH + 5) + 1;
   __threadfence_system();
   if ((int)threadIdx.x < a.world) st_release_sys(a.pflags[threadIdx.x] + F_AGG_OUT, e);
@@ -266,10 +349,16 @@ __global__ void __launch_bounds__(MAXW) k_agg_signal(const __grid_constant__ Agg
 
 // every rank: wait for the signal, pull the block out of rank 0's dense array
 __global__ void __launch_bounds__(256) k_agg_scatter(const __grid_constant__ AggArgs a) {
-  unsigned long long *fl = a.flags;
+  unsigned long long *fl = a.w.flags;
+  if (comm_dead(a.w)) return;
   const unsigned long long e = *reinterpret_cast<volatile unsigned long long *>(fl + F_EPOCH + 5) + 1;
-  if (threadIdx.x == 0) spin_ge(fl + F_AGG_OUT, e, fl);
+  __shared__ int ok;
+  if (threadIdx.x == 0) {
+    ok = spin_ge(fl + F_AGG_OUT, e, a.w) ? 1 : 0;
+    if (!ok) comm_fail(a.w);
+  }
   __syncthreads();
+  if (!ok) return;
   const long long total = (long long)a.n[0] * a.n[1] * a.n[2];
   for (long long t = blockIdx.x * (long long)blockDim.x + threadIdx.x; t < total; t += (long long)gridDim.x * blockDim.x) {
     const int i = (int)(t % a.n[0]);
@@ -298,7 +387,12 @@ struct examg_comm {
   std::vector<std::vector<char *>> pblock;          // [rank][block] mapped base (nullptr: not mapped)
   std::vector<Blob> blobs;                          // [rank]
   std::vector<void *> opened;
-  int nbr[3][2];                                    // neighbour rank per dim/side, -1: none
+  int nbr[3][2];                                    // face neighbour rank per dim/side, -1: none
+  // face, edge and corner neighbours (`communicate` writes all of them directly)
+  struct Peer { int v[3], code, rank; };
+  std::vector<Peer> peers;
+  int *err_host = nullptr, *err_dev = nullptr;      // mapped pinned word set by a kernel whose wait for a peer timed out
+  unsigned long long timeout_ns = 60ULL * 1000000000ULL;  // EXAMG_PEER_TIMEOUT_S (0: wait for ever)
   // agglomeration staging (dense global arrays of one level), allocated by examg_comm_agg_setup
   double *agg_in = nullptr, *agg_out = nullptr;     // local pointers on rank 0
   double *agg_in0 = nullptr, *agg_out0 = nullptr;   // rank 0's arrays as seen from this rank
@@ -311,6 +405,7 @@ namespace examg {
 void comm_destroy(examg_ctx *c) {
   if (!c->comm) return;
   for (void *p : c->comm->opened) cudaIpcCloseMemHandle(p);
+  if (c->comm->err_host) cudaFreeHost(c->comm->err_host);
   delete c->comm;
   c->comm = nullptr;
 }
@@ -320,8 +415,27 @@ static examg_comm *comm_get(examg_ctx *c) {
     c->comm = new examg_comm();
     c->comm->world = c->world;
     c->comm->rank = c->cfg.rank;
+    if (const char *e = getenv("EXAMG_PEER_TIMEOUT_S")) {
+      const double sec = atof(e);
+      c->comm->timeout_ns = sec > 0.0 ? (unsigned long long)(sec * 1e9) : 0ULL;
+    }
   }
   return c->comm;
+}
+
+static WaitCtl wait_ctl(const examg_comm *cm) {
+  WaitCtl w;
+  w.flags = cm->flags;
+  w.err_host = cm->err_dev;
+  w.timeout_ns = cm->timeout_ns;
+  return w;
+}
+
+int comm_poll_error(examg_ctx *c) {
+  if (!c->comm || !c->comm->err_host || !*reinterpret_cast<volatile int *>(c->comm->err_host)) return EXAMG_OK;
+  return set_error(EXAMG_ESTATE, "a wait for a peer rank timed out after %.0f s (lost rank, mismatched call sequence, or ranks "
+                   "further apart than EXAMG_PEER_TIMEOUT_S); the operation was abandoned and the multi-GPU state of this "
+                   "context is no longer usable", (double)c->comm->timeout_ns * 1e-9);
 }
 
 static int find_block(examg_ctx *c, const void *p, long long *off) {
@@ -420,97 +534,66 @@ int do_exchange_many(examg_ctx *c, Field *const *fs, const int *slots, const int
   if (c->world == 1) return c->periodic_any ? self_exchange(c, fs, slots, depths, nfields) : EXAMG_OK;
   examg_comm *cm = c->comm;
   if (!cm || !cm->wired) return set_error(EXAMG_ESTATE, "examg_exchange: peers not wired (examg_comm_import)");
-  for (int d = 0; d < c->cfg.dim; ++d) {
-    if (cm->nbr[d][0] < 0 && cm->nbr[d][1] < 0) continue;
-    ExchArgs a;
-    a.d = d;
-    a.flags = cm->flags;
-    a.nf = 0;
-    long long work = 0;  // threads' worth of work
-    for (int s = 0; s < 2; ++s) {
-      a.has[s] = cm->nbr[d][s] >= 0;
-      a.pflags[s] = a.has[s] ? cm->pflags[cm->nbr[d][s]] : nullptr;
-    }
-    auto flush = [&]() -> int {
-      if (a.nf == 0) return EXAMG_OK;
-      int grid = (int)((work + 255) / 256);
-      if (grid > 592) grid = 592;
-      if (grid < 1) grid = 1;
-      k_exchange_dim<<<grid, 256, 0, c->stream>>>(a);
-      EXAMG_LAUNCH_CHECK(c);
-      a.nf = 0;
-      work = 0;
-      return EXAMG_OK;
-    };
-    for (int q = 0; q < nfields; ++q) {
-      Field &f = *fs[q];
-      const int field = (int)(&f - c->fields.data());
-      const LevelGeom &g = *geom(c, f.level);
-      const int G = depths[q];
-      if (G < 1 || G > GHOST) return set_error(EXAMG_EINVAL, "examg_exchange: depth %d", G);
-      double *buf = f.slot[slots[q]];
-      for (int comp = 0; comp < f.ncomp; ++comp) {
-        if (a.nf == EXF) {
-          int rc = flush();
-          if (rc) return rc;
-        }
-        FaceCopy &fc = a.f[a.nf++];
-        fc.src = buf + (long long)comp * g.vol + g.origin;
-        fc.pitch = g.pitch;
-        fc.plane = g.plane;
-        fc.nchunks = 1;
-        fc.cstride = 0;
-        for (int s = 0; s < 2; ++s) {
-          fc.dst[s] = nullptr;
-          fc.soff[s] = fc.doff[s] = fc.len2[s] = 0;
-          if (!a.has[s]) continue;
-          double *pb = peer_buffer(c, cm->nbr[d][s], field, buf);
-          if (!pb) return set_error(EXAMG_ESTATE, "examg_exchange: field %s@%d is not mapped on rank %d (created after "
-                                    "examg_comm_export?)", f.name.c_str(), f.level, cm->nbr[d][s]);
-          fc.dst[s] = pb + (long long)comp * g.vol + g.origin;
-          for (int w = 0; w < 3; ++w) {  // orthogonal extents: everything incl. ghost layers
-            const int gw = w < c->cfg.dim ? G : 0;
-            fc.sbox[s].lo[w] = -gw;
-            fc.sbox[s].ext[w] = g.n[w] + 2 * gw;
-            fc.dlo[s][w] = -gw;
-          }
-          if (s == 0) {  // to the - neighbour: my layers 1..G -> its n..n+G-1
-            fc.sbox[s].lo[d] = 1;
-            fc.sbox[s].ext[d] = G;
-            fc.dlo[s][d] = g.n[d];
-          } else {       // to the + neighbour: my layers n-1-G..n-1 -> its -G..0 (ghosts + duplicate)
-            fc.sbox[s].lo[d] = g.n[d] - 1 - G;
-            fc.sbox[s].ext[d] = G + 1;
-            fc.dlo[s][d] = -G;
-          }
-          if (d == 0) {
-            work += (long long)fc.sbox[s].ext[1] * fc.sbox[s].ext[2];
-            continue;
-          }
-          // whole rows: from the first row of the allocation's y range (last dim) resp. of the sent layers
-          const int gy = GHOST, gz = c->cfg.dim == 3 ? GHOST : 0;
-          const int lo = fc.sbox[s].lo[d], ext = fc.sbox[s].ext[d], dlo = fc.dlo[s][d];
-          if (d == 2 || c->cfg.dim == 2) {  // last dimension: one run of `ext` planes (rows in 2D)
-            const long long unit = d == 2 ? g.plane : g.pitch;
-            const long long first = d == 2 ? -(long long)XPAD - (long long)g.pitch * gy : -(long long)XPAD;
-            fc.soff[s] = first + unit * lo;
-            fc.doff[s] = first + unit * dlo;
-            fc.len2[s] = unit * ext / 2;
-            fc.nchunks = 1;
-          } else {  // d == 1 in 3D: `ext` rows in every plane (ghost planes included)
-            fc.soff[s] = -(long long)XPAD + (long long)g.pitch * lo - g.plane * gz;
-            fc.doff[s] = -(long long)XPAD + (long long)g.pitch * dlo - g.plane * gz;
-            fc.len2[s] = (long long)g.pitch * ext / 2;
-            fc.nchunks = g.n[2] + 2 * gz;
-            fc.cstride = g.plane;
-          }
-          work += fc.len2[s] * fc.nchunks / 4;
-        }
-      }
-    }
-    int rc = flush();
-    if (rc) return rc;
+  if (cm->peers.empty()) return EXAMG_OK;
+  ExchArgs a;
+  a.w = wait_ctl(cm);
+  a.np = (int)cm->peers.size();
+  for (int pi = 0; pi < a.np; ++pi) {
+    const examg_comm::Peer &pr = cm->peers[pi];
+    for (int w = 0; w < 3; ++w) a.p[pi].v[w] = pr.v[w];
+    a.p[pi].code = pr.code;
+    a.p[pi].pflags = cm->pflags[pr.rank];
   }
+  a.nf = 0;
+  long long work = 0;  // threads' worth of work (four accesses per thread)
+  auto flush = [&]() -> int {
+    if (a.nf == 0) return EXAMG_OK;
+    int grid = (int)((work + 255) / 256);
+    if (grid > 592) grid = 592;
+    if (grid < 1) grid = 1;
+    k_exchange_all<<<grid, 256, 0, c->stream>>>(a);
+    EXAMG_LAUNCH_CHECK(c);
+    a.nf = 0;
+    work = 0;
+    return EXAMG_OK;
+  };
+  for (int q = 0; q < nfields; ++q) {
+    Field &f = *fs[q];
+    const int field = (int)(&f - c->fields.data());
+    const LevelGeom &g = *geom(c, f.level);
+    const int G = depths[q];
+    if (G < 1 || G > GHOST) return set_error(EXAMG_EINVAL, "examg_exchange: depth %d", G);
+    if (f.loc != 0) return set_error(EXAMG_EUNSUP, "examg_exchange: cell-localised fields live on one block so far");
+    for (int w = 0; w < c->cfg.dim; ++w)
+      if (g.n[w] - 1 < G)
+        return set_error(EXAMG_EUNSUP, "examg_exchange: %d ghost layers of a level with %d cells per block", G, g.n[w] - 1);
+    double *buf = f.slot[slots[q]];
+    for (int comp = 0; comp < f.ncomp; ++comp) {
+      if (a.nf == EXF) {
+        int rc = flush();
+        if (rc) return rc;
+      }
+      ExchField &ef = a.f[a.nf];
+      ef.src = buf + (long long)comp * g.vol + g.origin;
+      for (int w = 0; w < 3; ++w) ef.n[w] = g.n[w];
+      ef.pitch = g.pitch;
+      ef.plane = g.plane;
+      ef.depth = G;
+      for (int pi = 0; pi < a.np; ++pi) {
+        const examg_comm::Peer &pr = cm->peers[pi];
+        double *pb = peer_buffer(c, pr.rank, field, buf);
+        if (!pb) return set_error(EXAMG_ESTATE, "examg_exchange: field %s@%d is not mapped on rank %d (created after "
+                                  "examg_comm_export?)", f.name.c_str(), f.level, pr.rank);
+        a.p[pi].dst[a.nf] = pb + (long long)comp * g.vol + g.origin;
+        long long cnt = 1;
+        for (int w = 0; w < 3; ++w) cnt *= pr.v[w] == 0 ? g.n[w] : (pr.v[w] < 0 ? G : G + 1);
+        work += (pr.v[0] == 0 ? cnt / 2 : cnt) / 4 + 1;
+      }
+      ++a.nf;
+    }
+  }
+  int rc = flush();
+  if (rc) return rc;
   for (int q = 0; q < nfields; ++q) fs[q]->halo_depth = depths[q];
   return EXAMG_OK;
 }
@@ -520,29 +603,28 @@ int do_exchange(examg_ctx *c, Field &f, int slot, int depth) {
   return do_exchange_many(c, &fp, &slot, &depth, 1);
 }
 
-int finish_sum(examg_ctx *c, int slot, double *out) {
+static int finish_reduce(examg_ctx *c, int slot, int op, double *out) {
   if (c->world > 1) {
     examg_comm *cm = c->comm;
     if (!cm || !cm->wired) return set_error(EXAMG_ESTATE, "global reduction: peers not wired (examg_comm_import)");
     RedArgs a;
     a.world = c->world;
     a.rank = c->cfg.rank;
-    a.flags = cm->flags;
+    a.op = op;
+    a.w = wait_ctl(cm);
     for (int r = 0; r < c->world; ++r) a.pflags[r] = cm->pflags[r];
     a.value = c->red_out + slot;
     k_allreduce_dd<<<1, MAXW, 0, c->stream>>>(a);
     EXAMG_LAUNCH_CHECK(c);
   }
   EXAMG_CUDA(cudaMemcpyAsync(c->red_host + slot, c->red_out + slot, sizeof(dd), cudaMemcpyDeviceToHost, c->stream));
-  EXAMG_CUDA(cudaStreamSynchronize(c->stream));
-  if (c->world > 1) {
-    unsigned long long err = 0;
-    EXAMG_CUDA(cudaMemcpy(&err, c->comm->flags + F_ERROR, sizeof(err), cudaMemcpyDeviceToHost));
-    if (err) return set_error(EXAMG_ESTATE, "a wait for a peer rank timed out (lost rank or mismatched call sequence)");
-  }
-  *out = c->red_host[slot].hi + c->red_host[slot].lo;
+  EXAMG_SYNC(c);
+  *out = op == 0 ? c->red_host[slot].hi + c->red_host[slot].lo : c->red_host[slot].hi;
   return EXAMG_OK;
 }
+
+int finish_sum(examg_ctx *c, int slot, double *out) { return finish_reduce(c, slot, 0, out); }
+int finish_max(examg_ctx *c, int slot, double *out) { return finish_reduce(c, slot, 1, out); }
 
 // ---- agglomeration staging -------------------------------------------------------------------
 
@@ -582,7 +664,7 @@ static int agg_args(examg_ctx *c, const Field &f, AggArgs *a) {
   a->plane = g.plane;
   a->rank = c->cfg.rank;
   a->world = c->world;
-  a->flags = cm->flags;
+  a->w = wait_ctl(cm);
   a->flags0 = cm->pflags[0];
   for (int r = 0; r < c->world; ++r) a->pflags[r] = cm->pflags[r];
   a->fsrc = nullptr;
@@ -642,7 +724,12 @@ int examg_comm_export(examg_ctx *c, void *blob) {
     cm->flags = reinterpret_cast<unsigned long long *>(dev_alloc(c, FLAG_WORDS * sizeof(unsigned long long)));
     if (!cm->flags) return set_error(EXAMG_ENOMEM, "examg_comm_export: flag page");
   }
-  EXAMG_CUDA(cudaStreamSynchronize(c->stream));
+  if (!cm->err_host) {
+    EXAMG_CUDA(cudaHostAlloc(reinterpret_cast<void **>(&cm->err_host), sizeof(int), cudaHostAllocMapped));
+    *cm->err_host = 0;
+    EXAMG_CUDA(cudaHostGetDevicePointer(reinterpret_cast<void **>(&cm->err_dev), cm->err_host, 0));
+  }
+  EXAMG_SYNC(c);
   Blob *b = static_cast<Blob *>(blob);
   memset(b, 0, sizeof(Blob));
   b->magic = BLOB_MAGIC;
@@ -700,13 +787,31 @@ int examg_comm_import(examg_ctx *c, const void *all_blobs, int world) {
       idx[d] += s ? 1 : -1;
       cm->nbr[d][s] = idx[0] + nb[0] * (idx[1] + (c->cfg.dim > 1 ? nb[1] : 1) * idx[2]);
     }
+  cm->peers.clear();
+  for (int vz = -1; vz <= 1; ++vz)
+    for (int vy = -1; vy <= 1; ++vy)
+      for (int vx = -1; vx <= 1; ++vx) {
+        const int v[3] = {vx, vy, vz};
+        if (!vx && !vy && !vz) continue;
+        bool ok = true;
+        int idx[3];
+        for (int d = 0; d < 3; ++d) {
+          idx[d] = c->bidx[d] + v[d];
+          if (v[d] && (d >= c->cfg.dim || idx[d] < 0 || idx[d] >= nb[d])) ok = false;
+        }
+        if (!ok) continue;
+        examg_comm::Peer pr;
+        for (int d = 0; d < 3; ++d) pr.v[d] = v[d];
+        pr.code = (vx + 1) + 3 * (vy + 1) + 9 * (vz + 1);
+        pr.rank = idx[0] + nb[0] * (idx[1] + (c->cfg.dim > 1 ? nb[1] : 1) * idx[2]);
+        cm->peers.push_back(pr);
+      }
   cm->pblock.assign(world, std::vector<char *>());
   cm->pflags.assign(world, nullptr);
   auto need_all = [&](int r) {
     if (r == 0) return true;  // agglomeration staging lives on rank 0
-    for (int d = 0; d < 3; ++d)
-      for (int s = 0; s < 2; ++s)
-        if (cm->nbr[d][s] == r) return true;
+    for (const auto &pr : cm->peers)
+      if (pr.rank == r) return true;
     return false;
   };
   for (int r = 0; r < world; ++r) {

@@ -241,7 +241,7 @@ int examg_finalize(examg_ctx *c) {
 
 int examg_set_stream(examg_ctx *c, void *s) {
   if (!c) return set_error(EXAMG_EINVAL, "null context");
-  EXAMG_CUDA(cudaStreamSynchronize(c->stream));
+  EXAMG_SYNC(c);
   if (s) {
     if (c->own_stream) cudaStreamDestroy(c->stream);
     c->stream = (cudaStream_t)s;
@@ -255,7 +255,7 @@ int examg_set_stream(examg_ctx *c, void *s) {
 
 int examg_sync(examg_ctx *c) {
   if (!c) return set_error(EXAMG_EINVAL, "null context");
-  EXAMG_CUDA(cudaStreamSynchronize(c->stream));
+  EXAMG_SYNC(c);
   return EXAMG_OK;
 }
 
@@ -393,7 +393,7 @@ static int field_create(examg_ctx *c, const char *name, int level, int num_slots
 int examg_field_destroy(examg_ctx *c, int h) {
   Field *f = get_field(c, h);
   if (!f) return set_error(EXAMG_EINVAL, "examg_field_destroy: handle %d", h);
-  EXAMG_CUDA(cudaStreamSynchronize(c->stream));
+  EXAMG_SYNC(c);
   for (int i = 0; i < 5; ++i)
     if (f->orig[i]) dev_free(c, f->orig[i]);
   for (int sl = 0; sl < 4; ++sl) f->slot[sl] = nullptr;
@@ -556,7 +556,7 @@ static int copy_field(examg_ctx *c, int h, int slot, double *host, bool up, bool
   double *stage = nullptr;
   if (!device_side && dense * sizeof(double) >= (1u << 20)) {
     if (c->stage_doubles < dense) {
-      EXAMG_CUDA(cudaStreamSynchronize(c->stream));
+      EXAMG_SYNC(c);
       if (c->stage) dev_free(c, c->stage);
       c->stage = dev_alloc(c, dense * sizeof(double));
       c->stage_doubles = c->stage ? dense : 0;
@@ -580,7 +580,7 @@ static int copy_field(examg_ctx *c, int h, int slot, double *host, bool up, bool
     EXAMG_CUDA(cudaMemcpy3DAsync(&p, c->stream));
     if (stage && !up) EXAMG_CUDA(cudaMemcpyAsync(hp, stage, dense * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
   }
-  if (!async) EXAMG_CUDA(cudaStreamSynchronize(c->stream));
+  if (!async) EXAMG_SYNC(c);
   return EXAMG_OK;
 }
 
@@ -627,7 +627,7 @@ int examg_field_upload_begin(examg_ctx *c, int h, int slot, const double *host) 
   }
   const int b = c->up_turn;
   if (c->up_doubles[b] < need) {
-    EXAMG_CUDA(cudaStreamSynchronize(c->stream));
+    EXAMG_SYNC(c);
     EXAMG_CUDA(cudaStreamSynchronize(c->copy_stream));
     if (c->up_stage[b]) dev_free(c, c->up_stage[b]);
     c->up_stage[b] = dev_alloc(c, need * sizeof(double));
@@ -722,7 +722,7 @@ int examg_field_fill(examg_ctx *c, int h, double value) {
     }
     // no 64-bit memset in the runtime API: stage one row, then doubling device copies
     EXAMG_CUDA(cudaMemcpyAsync(base, row.data(), sizeof(double) * g.pitch, cudaMemcpyHostToDevice, c->stream));
-    EXAMG_CUDA(cudaStreamSynchronize(c->stream));
+    EXAMG_SYNC(c);
     for (size_t done = g.pitch; done < count;) {
       size_t chunk = done < count - done ? done : count - done;
       EXAMG_CUDA(cudaMemcpyAsync(base + done, base, sizeof(double) * chunk, cudaMemcpyDeviceToDevice, c->stream));

@@ -370,12 +370,19 @@ int examg_solver_vcycle(examg_solver *s, int level) {
     EXAMG_CUDA(cudaStreamBeginCapture(c->stream, cudaStreamCaptureModeThreadLocal));
     int rc = vcycle_rec(s, level);
     cudaError_t e = cudaStreamEndCapture(c->stream, &graph);
-    if (rc) { if (graph) cudaGraphDestroy(graph); return rc; }
-    if (e != cudaSuccess) return set_error(EXAMG_ECUDA, "graph capture of mgCycle failed: %s", cudaGetErrorString(e));
+    // nothing ran: on any failure the host bookkeeping (active slots, buffer permutation, valid ghost layers, launch
+    // count) goes back to the entry state
+    auto undo = [&]() {
+      size_t pos0 = 0;
+      restore_cycle_state(s, key, pos0);
+      c->launches = l0;
+    };
+    if (rc) { if (graph) cudaGraphDestroy(graph); undo(); return rc; }
+    if (e != cudaSuccess) { undo(); return set_error(EXAMG_ECUDA, "graph capture of mgCycle failed: %s", cudaGetErrorString(e)); }
     examg_solver::Graph g;
     e = cudaGraphInstantiate(&g.exec, graph, 0);
     cudaGraphDestroy(graph);
-    if (e != cudaSuccess) return set_error(EXAMG_ECUDA, "cudaGraphInstantiate: %s", cudaGetErrorString(e));
+    if (e != cudaSuccess) { undo(); return set_error(EXAMG_ECUDA, "cudaGraphInstantiate: %s", cudaGetErrorString(e)); }
     g.launches = c->launches - l0;
     c->launches = l0;  // nothing ran yet
     cycle_state(s, g.exit_slots);
@@ -418,7 +425,7 @@ int examg_solver_last_cg_iters(examg_solver *s, int *iters_out) {
     return examg_solver_last_cg_iters(s->agg, iters_out);
   }
   EXAMG_CUDA(cudaMemcpyAsync(c->int_host, c->int_out, sizeof(int), cudaMemcpyDeviceToHost, c->stream));
-  EXAMG_CUDA(cudaStreamSynchronize(c->stream));
+  EXAMG_SYNC(c);
   *iters_out = c->int_host[0];
   return EXAMG_OK;
 }

@@ -417,20 +417,18 @@ bool fused_rb_usable(examg_ctx *c, const Stencil &s, const Field &fu) {
 
 // Allocates the second buffer of a field (not capturable: call before graph capture).
 int ensure_shadow(examg_ctx *c, Field &fu) {
-  static bool attr_set = false;
-  if (!attr_set) {
+  EXAMG_ONCE_PER_DEVICE(c, {
     EXAMG_CUDA(cudaFuncSetAttribute(k_rbw<2, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)rbw_smem<2>()));
     EXAMG_CUDA(cudaFuncSetAttribute(k_rbw<2, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)rbw_smem<2>()));
     EXAMG_CUDA(cudaFuncSetAttribute(k_rbw<4, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)rbw_smem<4>()));
     EXAMG_CUDA(cudaFuncSetAttribute(k_rbw<4, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)rbw_smem<4>()));
-    attr_set = true;
-  }
+  });
   if (fu.shadow) return EXAMG_OK;
   const LevelGeom &g = *geom(c, fu.level);
   const size_t bytes = sizeof(double) * (size_t)g.vol;
   fu.shadow = fu.orig[4] = dev_alloc(c, bytes);
   if (!fu.shadow) return set_error(EXAMG_ENOMEM, "shadow buffer of %s@%d: cudaMalloc of %zu bytes failed", fu.name.c_str(), fu.level, bytes);
-  EXAMG_CUDA(cudaStreamSynchronize(c->stream));
+  EXAMG_SYNC(c);
   return EXAMG_OK;
 }
 
@@ -522,12 +520,10 @@ int jac_fused_plan(int nsweeps) {
 
 template <int S>
 static int launch_jacw(examg_ctx *c, const Stencil &s, double omega, Field &fu, const double *rhs) {
-  static bool attr_set = false;
-  if (!attr_set) {
+  EXAMG_ONCE_PER_DEVICE(c, {
     EXAMG_CUDA(cudaFuncSetAttribute(k_jacw<S, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)jacw_smem<S>()));
     EXAMG_CUDA(cudaFuncSetAttribute(k_jacw<S, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)jacw_smem<S>()));
-    attr_set = true;
-  }
+  });
   const LevelGeom &g = *geom(c, s.level);
   const int nxt = (fu.cur + 1) % 2;
   CUtensorMap tm_u, tm_f;
@@ -637,11 +633,9 @@ bool fused_jacv_usable(examg_ctx *c, const Stencil &s, const Field &fu) {
 
 template <int NST, int ORD>
 static int launch_jacv(examg_ctx *c, const Stencil &s, double omega, Field &fu, const double *rhs) {
-  static bool attr_set = false;
-  if (!attr_set) {
+  EXAMG_ONCE_PER_DEVICE(c, {
     EXAMG_CUDA(cudaFuncSetAttribute(k_jacv2<NST, ORD>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)jacv_smem<NST>()));
-    attr_set = true;
-  }
+  });
   const LevelGeom &g = *geom(c, s.level);
   const Field &cf = c->fields[s.coeff_field];
   const int nxt = (fu.cur + 1) % 2;

@@ -196,6 +196,10 @@ StencilArgs stencil_args(const LevelGeom &g, const Stencil &s);
 
 // global (all-rank) sum of a device dd partial written to c->red_out[slot]; returns hi+lo
 int finish_sum(examg_ctx *c, int slot, double *out);
+// the same for a maximum (red_out[slot].hi)
+int finish_max(examg_ctx *c, int slot, double *out);
+// EXAMG_ESTATE if a device-side wait for a peer rank timed out since the peers were wired (sticky), else 0
+int comm_poll_error(examg_ctx *c);
 
 #define EXAMG_CUDA(expr)                                                              \
   do {                                                                                \
@@ -203,6 +207,24 @@ int finish_sum(examg_ctx *c, int slot, double *out);
     if (e__ != cudaSuccess)                                                           \
       return examg::set_error(EXAMG_ECUDA, "%s:%d %s: %s", __FILE__, __LINE__, #expr, \
                               cudaGetErrorString(e__));                               \
+  } while (0)
+
+// cudaFuncSetAttribute is per device: `static unsigned long long done` bit = device ordinal (< 64)
+#define EXAMG_ONCE_PER_DEVICE(c, body)                                 \
+  do {                                                                 \
+    static unsigned long long done__ = 0ULL;                           \
+    const unsigned long long bit__ = 1ULL << ((c)->device & 63);       \
+    if (!(done__ & bit__)) {                                           \
+      body;                                                            \
+      done__ |= bit__;                                                 \
+    }                                                                  \
+  } while (0)
+
+// host synchronisation of the context stream; reports a peer wait that timed out (examg_comm.cu) as EXAMG_ESTATE
+#define EXAMG_SYNC(c)                                                  \
+  do {                                                                 \
+    EXAMG_CUDA(cudaStreamSynchronize((c)->stream));                    \
+    if (int rc__ = examg::comm_poll_error(c)) return rc__;             \
   } while (0)
 
 #define EXAMG_LAUNCH_CHECK(c)                                                        \

@@ -183,6 +183,10 @@ int examg_smooth_jacobi(examg_ctx *c, int A, int u, int rhs, double omega, int n
     if (rc) return rc;
     fu->cur = nxt;  // advance Solution
     fu->halo_depth = 0;
+    // cell-localised fields: the ghost cells are functions of the inner cells (Dirichlet 2g - u, Neumann u), so the
+    // next sweep needs `apply bc` (the loop bodies of Testing/CellBased/*.exa4 Smoother); node fields keep their
+    // Dirichlet nodes (never written by the loop)
+    if (fu->loc == 1 && (rc = examg_apply_bc(c, u, -1))) return rc;
   }
   return EXAMG_OK;
 }
@@ -200,7 +204,9 @@ int examg_smooth_rb_color(examg_ctx *c, int A, int u, int rhs, double omega, int
   int rc = do_exchange(c, *fu, fu->cur);
   if (rc) return rc;
   fu->halo_depth = 0;
-  return launch_rb(c, *s, omega, field_ptr(c, fu, -1), field_ptr(c, fr, -1), color);
+  if ((rc = launch_rb(c, *s, omega, field_ptr(c, fu, -1), field_ptr(c, fr, -1), color))) return rc;
+  // { communicate; update; apply bc } per colour: ghost cells of a cell-localised field follow the inner cells
+  return fu->loc == 1 ? examg_apply_bc(c, u, -1) : EXAMG_OK;
 }
 
 int examg_smooth_colored(examg_ctx *c, int A, int u, int rhs, double omega, int ncol, int nsweeps) {
@@ -222,7 +228,7 @@ int examg_smooth_colored(examg_ctx *c, int A, int u, int rhs, double omega, int 
           if (rc) return rc;
           fu->halo_depth = 0;
           if ((rc = launch_color_generic(c, *s, omega, field_ptr(c, fu, -1), field_ptr(c, fr, -1), ncol, cx, cy, cz))) return rc;
-          if (fu->loc == 0 && (rc = examg_apply_bc(c, u, -1))) return rc;
+          if ((rc = examg_apply_bc(c, u, -1))) return rc;
         }
   return EXAMG_OK;
 }
@@ -283,6 +289,7 @@ int examg_dot(examg_ctx *c, int a, int a_slot, int b, int b_slot, double *out) {
   GET_FIELD(fa, a); GET_FIELD(fb, b);
   CHECK_SLOT(fa, a_slot); CHECK_SLOT(fb, b_slot); CHECK_LEVEL(fb, fa->level);
   if (!out) return set_error(EXAMG_EINVAL, "examg_dot: null output");
+  if (fa->loc != fb->loc) return set_error(EXAMG_EINVAL, "examg_dot: fields of different localisation");
   LocGuard lg(c, fa->loc);
   int rc = launch_dot(c, fa->level, field_ptr(c, fa, a_slot), field_ptr(c, fb, b_slot), 0);
   if (rc) return rc;
@@ -293,13 +300,11 @@ int examg_max_abs_diff(examg_ctx *c, int a, int a_slot, int b, int b_slot, doubl
   GET_FIELD(fa, a); GET_FIELD(fb, b);
   CHECK_SLOT(fa, a_slot); CHECK_SLOT(fb, b_slot); CHECK_LEVEL(fb, fa->level);
   if (!out) return set_error(EXAMG_EINVAL, "examg_max_abs_diff: null output");
+  if (fa->loc != fb->loc) return set_error(EXAMG_EINVAL, "examg_max_abs_diff: fields of different localisation");
   LocGuard lg(c, fa->loc);
   int rc = launch_maxdiff(c, fa->level, field_ptr(c, fa, a_slot), field_ptr(c, fb, b_slot), 1);
   if (rc) return rc;
-  EXAMG_CUDA(cudaMemcpyAsync(c->red_host + 1, c->red_out + 1, sizeof(dd), cudaMemcpyDeviceToHost, c->stream));
-  EXAMG_CUDA(cudaStreamSynchronize(c->stream));
-  *out = c->red_host[1].hi;  // per-block maximum; the host process group takes the max over blocks
-  return EXAMG_OK;
+  return finish_max(c, 1, out);  // global over all blocks, as examg_dot
 }
 
 int examg_set(examg_ctx *c, int f, int slot, double value) {
@@ -311,6 +316,7 @@ int examg_set(examg_ctx *c, int f, int slot, double value) {
 int examg_copy(examg_ctx *c, int src, int src_slot, int dst, int dst_slot) {
   GET_FIELD(fs, src); GET_FIELD(fd, dst);
   CHECK_SLOT(fs, src_slot); CHECK_SLOT(fd, dst_slot); CHECK_LEVEL(fd, fs->level);
+  if (fs->loc != fd->loc) return set_error(EXAMG_EINVAL, "examg_copy: fields of different localisation");
   fd->halo_depth = 0;
   LocGuard lg(c, fs->loc);
   return launch_stream_op(c, fs->level, STREAM_COPY, 0.0, field_ptr(c, fs, src_slot), field_ptr(c, fd, dst_slot));
@@ -318,6 +324,8 @@ int examg_copy(examg_ctx *c, int src, int src_slot, int dst, int dst_slot) {
 int examg_axpy(examg_ctx *c, double alpha, int x, int x_slot, int y, int y_slot) {
   GET_FIELD(fx, x); GET_FIELD(fy, y);
   CHECK_SLOT(fx, x_slot); CHECK_SLOT(fy, y_slot); CHECK_LEVEL(fy, fx->level);
+  if (fx->loc != fy->loc) return set_error(EXAMG_EINVAL, "examg_axpy: fields of different localisation");
+  if (fx->loc != fy->loc) return set_error(EXAMG_EINVAL, "examg_xpay: fields of different localisation");
   fy->halo_depth = 0;
   LocGuard lg(c, fx->loc);
   return launch_stream_op(c, fx->level, STREAM_AXPY, alpha, field_ptr(c, fx, x_slot), field_ptr(c, fy, y_slot));
@@ -360,7 +368,7 @@ int examg_cr_coarse(examg_ctx *c, int A, int u, int rhs, int res, const int tmp[
   int rc = launch_cr(c, *s, field_ptr(c, fu, -1), field_ptr(c, fr, -1), field_ptr(c, fres, -1), tp, max_it, rel_tol);
   if (rc || !iters_out) return rc;
   EXAMG_CUDA(cudaMemcpyAsync(c->int_host, c->int_out, sizeof(int), cudaMemcpyDeviceToHost, c->stream));
-  EXAMG_CUDA(cudaStreamSynchronize(c->stream));
+  EXAMG_SYNC(c);
   *iters_out = c->int_host[0];
   return EXAMG_OK;
 }
@@ -385,7 +393,7 @@ int examg_minres_coarse(examg_ctx *c, int A, int u, int rhs, int res, const int 
   int rc = launch_minres(c, *s, field_ptr(c, fu, -1), field_ptr(c, fr, -1), field_ptr(c, fres, -1), tp, max_it, rel_tol);
   if (rc || !iters_out) return rc;
   EXAMG_CUDA(cudaMemcpyAsync(c->int_host, c->int_out, sizeof(int), cudaMemcpyDeviceToHost, c->stream));
-  EXAMG_CUDA(cudaStreamSynchronize(c->stream));
+  EXAMG_SYNC(c);
   *iters_out = c->int_host[0];
   return EXAMG_OK;
 }
@@ -410,7 +418,7 @@ int examg_bicgstab_coarse(examg_ctx *c, int A, int u, int rhs, int res, const in
   int rc = launch_bicgstab(c, *s, field_ptr(c, fu, -1), field_ptr(c, fr, -1), field_ptr(c, fres, -1), tp, max_it, rel_tol);
   if (rc || !iters_out) return rc;
   EXAMG_CUDA(cudaMemcpyAsync(c->int_host, c->int_out, sizeof(int), cudaMemcpyDeviceToHost, c->stream));
-  EXAMG_CUDA(cudaStreamSynchronize(c->stream));
+  EXAMG_SYNC(c);
   *iters_out = c->int_host[0];
   return EXAMG_OK;
 }
@@ -421,11 +429,18 @@ int examg_cg_coarse(examg_ctx *c, int A, int u, int rhs, int res, int p, int ap,
   CHECK_LEVEL(fu, s->level); CHECK_LEVEL(fr, s->level); CHECK_LEVEL(fres, s->level);
   CHECK_LEVEL(fp, s->level); CHECK_LEVEL(fap, s->level);
   if (fu->loc != 0) return set_error(EXAMG_EUNSUP, "examg_cg_coarse: node-localised fields");
+  {
+    const int hs[5] = {u, rhs, res, p, ap};
+    for (int k = 0; k < 5; ++k)
+      for (int j = 0; j < k; ++j)
+        if (hs[j] == hs[k]) return set_error(EXAMG_EINVAL, "examg_cg_coarse: u, rhs, res, p and ap must be distinct fields");
+  }
+  fu->halo_depth = fres->halo_depth = fp->halo_depth = fap->halo_depth = 0;
   int rc = launch_cg(c, *s, field_ptr(c, fu, -1), field_ptr(c, fr, -1), field_ptr(c, fres, -1), field_ptr(c, fp, -1),
                      field_ptr(c, fap, -1), max_it, rel_tol);
   if (rc || !iters_out) return rc;
   EXAMG_CUDA(cudaMemcpyAsync(c->int_host, c->int_out, sizeof(int), cudaMemcpyDeviceToHost, c->stream));
-  EXAMG_CUDA(cudaStreamSynchronize(c->stream));
+  EXAMG_SYNC(c);
   *iters_out = c->int_host[0];
   return EXAMG_OK;
 }

@@ -722,7 +722,7 @@ int examg_system2_cg_coarse(examg_ctx *c, int sys, const int *fields, int max_it
   EXAMG_LAUNCH_CHECK(c);
   if (iters_out) {
     EXAMG_CUDA(cudaMemcpyAsync(c->int_host, c->int_out, sizeof(int), cudaMemcpyDeviceToHost, c->stream));
-    EXAMG_CUDA(cudaStreamSynchronize(c->stream));
+    EXAMG_SYNC(c);
     *iters_out = c->int_host[0];
   }
   return EXAMG_OK;
@@ -963,7 +963,7 @@ int examg_optflow_last_cg_iters(examg_optflow *o, int *iters_out) {
   if (!o || !iters_out) return set_error(EXAMG_EINVAL, "examg_optflow_last_cg_iters: null argument");
   examg_ctx *c = o->c;
   EXAMG_CUDA(cudaMemcpyAsync(c->int_host, c->int_out, sizeof(int), cudaMemcpyDeviceToHost, c->stream));
-  EXAMG_CUDA(cudaStreamSynchronize(c->stream));
+  EXAMG_SYNC(c);
   *iters_out = c->int_host[0];
   return EXAMG_OK;
 }

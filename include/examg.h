@@ -223,7 +223,7 @@ int examg_dot(examg_ctx *ctx, int a, int a_slot, int b, int b_slot, double *out)
  * array: calls that overlap on the GPU (unordered streams, several host threads) race -- serialise them.        */
 #define EXAMG_NOALLOC_MAX_N (1LL << 28)
 int examg_dot_dense_noalloc(const double *a_dev, const double *b_dev, long long n, double *out_dev, void *cuda_stream);
-/* max |a - b| over the loop points (PrintError / NormError) */
+/* max |a - b| over the loop points (PrintError / NormError); global over all blocks, as examg_dot */
 int examg_max_abs_diff(examg_ctx *ctx, int a, int a_slot, int b, int b_slot, double *out);
 /* streaming loops on the loop points */
 int examg_set(examg_ctx *ctx, int f, int slot, double value);
@@ -343,7 +343,11 @@ int examg_optflow_last_cg_iters(examg_optflow *o, int *iters_out);
  * Peers are wired by exchanging opaque blobs through the host's process group
  * (torch.distributed / MPI): every rank exports a blob, all blobs are gathered
  * and imported.  After that `communicate` writes faces directly into the
- * neighbours' ghost layers over NVLink.                                       */
+ * neighbours' ghost layers over NVLink (face, edge and corner neighbours, one handshake per call).
+ * Ranks wait for each other inside kernels: they must reach matching calls within EXAMG_PEER_TIMEOUT_S
+ * seconds (environment, default 60; 0 = wait for ever) of one another.  A wait that times out abandons
+ * the operation (nothing is stored or summed), and every later synchronising call on the context
+ * (examg_sync, downloads, reductions, solver cycles) returns EXAMG_ESTATE.                            */
 int examg_comm_blob_size(examg_ctx *ctx);
 int examg_comm_export(examg_ctx *ctx, void *blob);
 int examg_comm_import(examg_ctx *ctx, const void *all_blobs, int world);

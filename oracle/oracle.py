@@ -182,6 +182,12 @@ def smooth_colored(st, omega, u, rhs, ncol, dim, sf=None):
     return u
 
 
+def smooth_color(st, omega, u, rhs, ncol, cx, cy, cz, sf=None):
+    """One colour (i % ncol == cx, j % ncol == cy, k % ncol == cz by array index) of the n^dim-way colouring, in place."""
+    lib().og_smooth_color(_n(u), C.byref(st), _sf(sf), omega, _dp(u), _dp(rhs), ncol, cx, cy, cz)
+    return u
+
+
 def conjugate_residual(st, u, rhs, max_it, rel_tol, sf=None):
     """In place on u; returns (steps, residual field)."""
     res = np.zeros_like(u)

@@ -118,3 +118,80 @@ def test_five_point_benchmark_app(oracle):
     ug = ctx.download_cells(u, lvl)
     assert np.allclose(ug, U[:, 1:-1, 1:-1], rtol=1e-11, atol=1e-11 * np.max(np.abs(U)))
     ctx.close()
+
+
+@pytest.mark.parametrize("dim,neumann", [(2, False), (2, True), (3, False), (3, True)])
+def test_cell_smoothers_refresh_ghost_cells(dim, neumann, oracle):
+    """Round-1 advisor finding: on cell-localised fields every colour of examg_smooth_rbgs / examg_smooth_rb_color /
+    examg_smooth_colored and every sweep of a multi-sweep examg_smooth_jacobi is { update; apply bc } -- the ghost cells
+    (Dirichlet 2g - u, Neumann u) follow the inner cells -- as the smoother bodies of Testing/CellBased/*.exa4 spell it
+    out.  Against the oracle's loops with og_cell_apply_bc after every colour / sweep: bit-identical."""
+    from exastencils_b200 import runtime as rt
+    og = oracle
+    og.set_periodic((0, 0, 0))
+    lvl = 4 if dim == 2 else 3
+    cells = (3, 5) if dim == 2 else (2, 3, 1)
+    ctx = rt.Context(dim, lvl, lvl, block_cells=cells)
+    n = ctx.cell_shape(lvl)  # (nz, ny, nx) of the cells
+    rng = np.random.default_rng(11 + dim + 2 * int(neumann))
+    offs = [(0, 0, 0), (1, 0, 0), (-1, 0, 0), (0, 1, 0), (0, -1, 0)] + ([(0, 0, 1), (0, 0, -1)] if dim == 3 else [])
+    coef = [2.0 * dim + 0.5] + [-1.0] * (2 * dim)
+    A = ctx.stencil_const(lvl, offs, coef)
+    st = og.Stencil.make(offs, coef)
+    u0, f0 = rng.uniform(-1.0, 1.0, size=n), rng.uniform(-1.0, 1.0, size=n)
+    kind_gpu, kind_og = (rt.BC_NEUMANN, og.BC_CELL_NEUMANN) if neumann else (rt.BC_DIRICHLET_CONST, og.BC_CELL_DIRICHLET)
+    g = 0.0 if neumann else 0.75
+    pad = [(1, 1)] * 3 if dim == 3 else [(0, 0), (1, 1), (1, 1)]
+    faces = None
+    if not neumann:
+        faces = []
+        for fc in range(6):
+            d = fc // 2
+            if d >= dim:
+                faces.append(None)
+                continue
+            shp = [n[2 - w] for w in range(3) if w != d and w < dim]  # the face's cells, x fastest
+            faces.append(np.full(int(np.prod(shp)), g))
+
+    def bc(U):
+        og.cell_apply_bc(dim, U, kind_og, faces)
+
+    def fresh():
+        fu, ff = ctx.field_create_cell("u", lvl, 2), ctx.field_create_cell("f", lvl, 1)
+        ctx.field_set_bc(fu, kind_gpu, g)
+        for s in (0, 1):
+            ctx.upload(fu, u0, s)
+            ctx.apply_bc(fu, s)
+        ctx.upload(ff, f0)
+        U = np.pad(u0, pad)
+        F = np.pad(f0, pad)
+        bc(U)
+        return fu, ff, U, F
+
+    # red-black: colour c of the cells = colour (c + dim) % 2 of the padded array the oracle loops over
+    fu, ff, U, F = fresh()
+    ctx.smooth_rbgs(A, fu, ff, 0.8, 2)
+    for _ in range(2):
+        for colour in (0, 1):
+            og.smooth_rb(st, 0.8, U, F, (colour + dim) % 2)
+            bc(U)
+    sl = (slice(1, -1),) * 3 if dim == 3 else (slice(None), slice(1, -1), slice(1, -1))
+    assert np.array_equal(ctx.download_cells(fu, lvl), U[sl])
+    # three Jacobi sweeps in one call
+    fu, ff, U, F = fresh()
+    ctx.smooth_jacobi(A, fu, ff, 0.8, 3)
+    for _ in range(3):
+        U = og.smooth_jacobi(st, 0.8, U, F)
+        bc(U)
+    assert np.array_equal(ctx.download_cells(fu, lvl), U[sl])
+    # 2^dim-way coloured Gauss-Seidel
+    fu, ff, U, F = fresh()
+    ctx.smooth_colored(A, fu, ff, 0.8, 2, 1)
+    for cz in range(2 if dim == 3 else 1):
+        for cy in range(2):
+            for cx in range(2):
+                # cell colour c_d <-> padded-array index colour (c_d + 1) % 2 in the padded dimensions
+                og.smooth_color(st, 0.8, U, F, 2, (cx + 1) % 2, (cy + 1) % 2, (cz + 1) % 2 if dim == 3 else 0)
+                bc(U)
+    assert np.array_equal(ctx.download_cells(fu, lvl), U[sl])
+    ctx.close()
