@@ -61,6 +61,10 @@ struct Blob {
   long long flag_offset;
   long long agg_in_off, agg_out_off;  // staging buffers of the agglomeration (rank 0), -1: none
   int agg_in_block, agg_out_block;
+  // receive staging of the x faces (side 0: from the - neighbour, 1: from the + neighbour), -1: none
+  int xst_block[2];
+  long long xst_off[2];
+  long long xst_cap;                  // doubles per field component
   cudaIpcMemHandle_t handles[BLOB_MAX_BLOCKS];
   BlobEntry entries[BLOB_MAX_ENTRIES];
 };
@@ -128,9 +132,11 @@ struct ExchPeer {
   int code;                    // (vx+1) + 3 (vy+1) + 9 (vz+1): index of the flag this peer writes here
   unsigned long long *pflags;  // its flag page
   double *dst[EXF];            // node (0,0,0) of its buffer per field
+  double *stage;               // pure x faces: its receive staging for this block (nullptr: store in place)
 };
 struct ExchArgs {
   int nf, np;
+  long long stage_cap;         // doubles per field component in a staging array
   ExchField f[EXF];
   ExchPeer p[NPEER];
   WaitCtl w;
@@ -201,8 +207,32 @@ __global__ void __launch_bounds__(256) k_exchange_all(const __grid_constant__ Ex
         }
       } else {
         // x faces, and edges / corners with an x component: G (G+1) nodes per row; consecutive threads take
-        // consecutive nodes, so a warp moves whole 32-byte sectors of 32/G rows
+        // consecutive nodes, so a warp moves whole 32-byte sectors of 32/G rows.  A pure x face has one such
+        // 32-byte piece per row of the block -- a million NVLink packets at 1024^3, measured 2.7 ms against 0.09 ms
+        // for a z face of the same size -- so it travels PACKED: the same threads store their values contiguously
+        // (256 bytes per warp) into a staging array on the receiver, which scatters them into its ghost columns
+        // itself (k_unpack_x, a local kernel behind this one on the receiver's stream).
         const long long total = (long long)ext[0] * ext[1] * ext[2];
+        if (p.stage && p.v[1] == 0 && p.v[2] == 0) {
+          double *stg = p.stage + q * a.stage_cap;
+          for (long long t0 = tid; t0 < total; t0 += 4 * stride) {
+            double val[4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+              const long long t = t0 + u * stride;
+              if (t < total) {
+                const int i = (int)(t % ext[0]);
+                const long long r = t / ext[0];
+                const int j = (int)(r % ext[1]), k = (int)(r / ext[1]);
+                val[u] = sb[i + (long long)f.pitch * j + f.plane * k];
+              }
+            }
+#pragma unroll
+            for (int u = 0; u < 4; ++u)
+              if (t0 + u * stride < total) stg[t0 + u * stride] = val[u];
+          }
+          continue;
+        }
         for (long long t0 = tid; t0 < total; t0 += 4 * stride) {
           double val[4];
           long long off[4];
@@ -241,6 +271,54 @@ __global__ void __launch_bounds__(256) k_exchange_all(const __grid_constant__ Ex
     if (!ok) { comm_fail(a.w); return; }
     fl[F_TICKET] = 0;
     *reinterpret_cast<volatile unsigned long long *>(fl + F_EPOCH) = e;
+  }
+}
+
+// Receiver side of the packed x faces: staging (written by the x neighbours during k_exchange_all, complete once
+// that kernel has seen their DONE) -> ghost columns.  From the - neighbour: its layers n-1-G..n-1 -> my -G..0; from
+// the + neighbour: its layers 1..G -> my n..n+G-1; rows y in [0,n1), planes z in [0,n2) (edges and corners arrive in
+// place).
+struct UnpackArgs {
+  int nf;
+  int has[2];
+  const double *stage[2];
+  long long stage_cap;
+  double *dst[EXF];  // node (0,0,0) of the local buffers
+  int n0[EXF];
+  int pitch[EXF];
+  long long plane[EXF];
+  int depth[EXF];
+  int n1[EXF], n2[EXF];
+};
+
+__global__ void __launch_bounds__(256) k_unpack_x(const __grid_constant__ UnpackArgs a) {
+  const long long tid = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  for (int s = 0; s < 2; ++s) {
+    if (!a.has[s]) continue;
+    for (int q = 0; q < a.nf; ++q) {
+      const int G = a.depth[q];
+      const int ext0 = s == 0 ? G + 1 : G, dlo0 = s == 0 ? -G : a.n0[q];
+      const long long total = (long long)ext0 * a.n1[q] * a.n2[q];
+      const double *stg = a.stage[s] + q * a.stage_cap;
+      double *db = a.dst[q] + dlo0;
+      for (long long t0 = tid; t0 < total; t0 += 4 * stride) {
+        double val[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u)
+          if (t0 + u * stride < total) val[u] = stg[t0 + u * stride];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+          const long long t = t0 + u * stride;
+          if (t < total) {
+            const int i = (int)(t % ext0);
+            const long long r = t / ext0;
+            const int j = (int)(r % a.n1[q]), k = (int)(r / a.n1[q]);
+            db[i + (long long)a.pitch[q] * j + a.plane[q] * k] = val[u];
+          }
+        }
+      }
+    }
   }
 }
 
@@ -391,6 +469,9 @@ struct examg_comm {
   // face, edge and corner neighbours (`communicate` writes all of them directly)
   struct Peer { int v[3], code, rank; };
   std::vector<Peer> peers;
+  double *xstage[2] = {nullptr, nullptr};           // local receive staging of packed x faces (side 0: from -x, 1: from +x)
+  long long xstage_cap = 0;                         // doubles per field component
+  double *pxstage[2] = {nullptr, nullptr};          // the x neighbours' staging for this block (side of the neighbour)
   int *err_host = nullptr, *err_dev = nullptr;      // mapped pinned word set by a kernel whose wait for a peer timed out
   unsigned long long timeout_ns = 60ULL * 1000000000ULL;  // EXAMG_PEER_TIMEOUT_S (0: wait for ever)
   // agglomeration staging (dense global arrays of one level), allocated by examg_comm_agg_setup
@@ -543,7 +624,16 @@ int do_exchange_many(examg_ctx *c, Field *const *fs, const int *slots, const int
     for (int w = 0; w < 3; ++w) a.p[pi].v[w] = pr.v[w];
     a.p[pi].code = pr.code;
     a.p[pi].pflags = cm->pflags[pr.rank];
+    a.p[pi].stage = nullptr;
+    if (pr.v[0] != 0 && pr.v[1] == 0 && pr.v[2] == 0) a.p[pi].stage = cm->pxstage[pr.v[0] < 0 ? 0 : 1];
   }
+  a.stage_cap = cm->xstage_cap;
+  UnpackArgs ua;
+  ua.has[0] = cm->nbr[0][0] >= 0 && cm->xstage[0];
+  ua.has[1] = cm->nbr[0][1] >= 0 && cm->xstage[1];
+  ua.stage[0] = cm->xstage[0];
+  ua.stage[1] = cm->xstage[1];
+  ua.stage_cap = cm->xstage_cap;
   a.nf = 0;
   long long work = 0;  // threads' worth of work (four accesses per thread)
   auto flush = [&]() -> int {
@@ -553,6 +643,15 @@ int do_exchange_many(examg_ctx *c, Field *const *fs, const int *slots, const int
     if (grid < 1) grid = 1;
     k_exchange_all<<<grid, 256, 0, c->stream>>>(a);
     EXAMG_LAUNCH_CHECK(c);
+    if (ua.has[0] || ua.has[1]) {  // packed x faces: scatter what the x neighbours left in the staging arrays
+      ua.nf = a.nf;
+      long long uw = 0;
+      for (int q = 0; q < a.nf; ++q) uw += (long long)(2 * ua.depth[q] + 1) * ua.n1[q] * ua.n2[q] / 4 + 1;
+      int ug = (int)((uw + 255) / 256);
+      if (ug > 1184) ug = 1184;
+      k_unpack_x<<<ug, 256, 0, c->stream>>>(ua);
+      EXAMG_LAUNCH_CHECK(c);
+    }
     a.nf = 0;
     work = 0;
     return EXAMG_OK;
@@ -579,6 +678,15 @@ int do_exchange_many(examg_ctx *c, Field *const *fs, const int *slots, const int
       ef.pitch = g.pitch;
       ef.plane = g.plane;
       ef.depth = G;
+      ua.dst[a.nf] = buf + (long long)comp * g.vol + g.origin;
+      ua.n0[a.nf] = g.n[0];
+      ua.pitch[a.nf] = g.pitch;
+      ua.plane[a.nf] = g.plane;
+      ua.depth[a.nf] = G;
+      ua.n1[a.nf] = g.n[1];
+      ua.n2[a.nf] = g.n[2];
+      if ((ua.has[0] || ua.has[1]) && (long long)(G + 1) * g.n[1] * g.n[2] > cm->xstage_cap)
+        return set_error(EXAMG_ESTATE, "examg_exchange: x face of %s@%d exceeds the staging arrays", f.name.c_str(), f.level);
       for (int pi = 0; pi < a.np; ++pi) {
         const examg_comm::Peer &pr = cm->peers[pi];
         double *pb = peer_buffer(c, pr.rank, field, buf);
@@ -735,15 +843,33 @@ int examg_comm_export(examg_ctx *c, void *blob) {
   b->magic = BLOB_MAGIC;
   b->rank = c->cfg.rank;
   b->device = c->device;
-  if ((int)c->blocks.size() > BLOB_MAX_BLOCKS) return set_error(EXAMG_EUNSUP, "examg_comm_export: %zu device blocks", c->blocks.size());
-  b->nblocks = (int)c->blocks.size();
-  for (int i = 0; i < b->nblocks; ++i) EXAMG_CUDA(cudaIpcGetMemHandle(&b->handles[i], c->blocks[i].base));
+  // packed x faces: receive staging for the finest level, one array per x neighbour (EXF components each)
+  if (c->cfg.num_blocks[0] > 1 && !cm->xstage_cap) {
+    const LevelGeom &gf = *geom(c, c->cfg.max_level);
+    cm->xstage_cap = (long long)(GHOST + 1) * gf.n[1] * gf.n[2];
+    for (int sd = 0; sd < 2; ++sd) {
+      if (!c->nb[0][sd]) continue;
+      cm->xstage[sd] = dev_alloc(c, sizeof(double) * (size_t)cm->xstage_cap * EXF);
+      if (!cm->xstage[sd]) return set_error(EXAMG_ENOMEM, "examg_comm_export: staging of the x faces");
+    }
+  }
   b->flag_block = find_block(c, cm->flags, &b->flag_offset);
   b->agg_in_block = b->agg_out_block = -1;
+  b->xst_cap = cm->xstage_cap;
+  for (int sd = 0; sd < 2; ++sd) {
+    b->xst_block[sd] = -1;
+    b->xst_off[sd] = 0;
+  }
   if (cm->agg_in) {
     b->agg_in_block = find_block(c, cm->agg_in, &b->agg_in_off);
     b->agg_out_block = find_block(c, cm->agg_out, &b->agg_out_off);
   }
+  // (after the allocations above: the block list is final now)
+  b->nblocks = (int)c->blocks.size();
+  if (b->nblocks > BLOB_MAX_BLOCKS) return set_error(EXAMG_EUNSUP, "examg_comm_export: %d device blocks", b->nblocks);
+  for (int i = 0; i < b->nblocks; ++i) EXAMG_CUDA(cudaIpcGetMemHandle(&b->handles[i], c->blocks[i].base));
+  for (int sd = 0; sd < 2; ++sd)
+    if (cm->xstage[sd]) b->xst_block[sd] = find_block(c, cm->xstage[sd], &b->xst_off[sd]);
   int ne = 0;
   for (size_t fi = 0; fi < c->fields.size(); ++fi) {
     const Field &f = c->fields[fi];
@@ -834,6 +960,15 @@ int examg_comm_import(examg_ctx *c, const void *all_blobs, int world) {
       cm->pblock[r][b] = static_cast<char *>(p);
     }
     cm->pflags[r] = reinterpret_cast<unsigned long long *>(cm->pblock[r][bl[r].flag_block] + bl[r].flag_offset);
+  }
+  for (int sd = 0; sd < 2; ++sd) {
+    cm->pxstage[sd] = nullptr;
+    const int r = cm->nbr[0][sd];
+    if (r < 0) continue;
+    // this block sits on side 1-sd of its neighbour on side sd
+    if (bl[r].xst_block[1 - sd] < 0 || bl[r].xst_cap != cm->xstage_cap)
+      return set_error(EXAMG_ESTATE, "examg_comm_import: rank %d exported no staging for its x face", r);
+    cm->pxstage[sd] = reinterpret_cast<double *>(cm->pblock[r][bl[r].xst_block[1 - sd]] + bl[r].xst_off[1 - sd]);
   }
   if (bl[0].agg_in_block >= 0) {
     cm->agg_in0 = reinterpret_cast<double *>(cm->pblock[0][bl[0].agg_in_block] + bl[0].agg_in_off);

@@ -16,7 +16,7 @@ def _ngpus():
     return torch.cuda.device_count() if torch.cuda.is_available() else 0
 
 
-@pytest.mark.parametrize("world,blocks,level", [(2, "2,1,1", 7), (2, "1,1,2", 7), (4, "1,2,2", 7), (8, "2,2,2", 6),
+@pytest.mark.parametrize("world,blocks,level", [(2, "2,1,1", 7), (2, "1,1,2", 7), (4, "1,2,2", 7), (4, "2,2,1", 7), (8, "2,2,2", 6),
                                                 (8, "1,2,4", 6)])
 def test_blocks_match_global_oracle(world, blocks, level):
     if _ngpus() < world:
