@@ -64,12 +64,11 @@ USED = {
     "IR_LoopOverPoints": 10, "IR_Communicate": 6, "IR_ApplyBC": 2, "IR_AdvanceSlot": 2, "IR_SlotAccess": 2,
     "IR_IV_ActiveSlot": 2, "IR_Assignment": 3, "IR_Multiplication": 1, "IR_Addition": 1, "IR_Subtraction": 2,
     "IR_Division": 2, "IR_Modulo": 2, "IR_EqEq": 2, "IR_AndAnd": 2, "IR_Negative": 1, "IR_Power": 2, "IR_FunctionCall": 2,
-    "IR_StencilAccess": 2, "IR_StencilFieldAccess": 5, "IR_Stencil": 5, "IR_StencilField": 4, "IR_StencilOffsetEntry": 2,
-    "IR_Field": 9, "IR_LocalSolve": 4, "IR_Equation": 2, "IR_DirichletBC": 2, "IR_NeumannBC": 1, "IR_PrintField": 8,
+    "IR_StencilAccess": 2, "IR_StencilFieldAccess": 5, "IR_Stencil": 5, "IR_StencilField": 4,     "IR_Field": 9, "IR_LocalSolve": 4, "IR_DirichletBC": 2, "IR_NeumannBC": 1, "IR_PrintField": 8,
     "IR_CopyFromExternalField": 2, "IR_CopyToExternalField": 2, "IR_VariableDeclaration": 3, "IR_IfCondition": 3,
-    "IR_WhileLoop": 2, "IR_Scope": 1, "IR_Reduction": 3, "IR_ParallelizationInfo": 8, "IR_AllocateDataFunction": 2,
+    "IR_WhileLoop": 2, "IR_Scope": 1, "IR_AllocateDataFunction": 2,
     "IR_GlobalCollection": 1, "IR_RealConstant": 1, "IR_IntegerConstant": 1, "IR_StringConstant": 1,
-    "IR_PointerDatatype": 1, "IR_SpecialDatatype": 1, "IR_AABB": 2, "IR_DomainFromAABB": 2,
+    "IR_PointerDatatype": 1, "IR_SpecialDatatype": 1, "IR_DomainFromAABB": 2,
     "ConditionedSingleStrategyWrapper": 2,
 }
 OBJECTS = ["IR_ResolveLoopOverPoints", "IR_SetupAllocateDataFunctionWrapper", "IR_ResolveBenchmarkFunctions",
