@@ -50,6 +50,7 @@ object ExaMG_Symbols {
   val smoothColored = "examg_smooth_colored"
   val restrict = "examg_restrict"
   val prolongAdd = "examg_prolong_add"
+  val prolongAddSmoothRBGS = "examg_prolong_add_smooth_rbgs"
   val restrictCell = "examg_restrict_cell"
   val prolongAddCell = "examg_prolong_add_cell"
   val dot = "examg_dot"

@@ -15,6 +15,7 @@ import exastencils.datastructures._
 //   colour 0, colour 1                         -> examg_smooth_rbgs(A, u, f, omega, 1)
 //   k x examg_smooth_rbgs(.., 1)               -> examg_smooth_rbgs(.., k)          (same for Jacobi sweeps)
 //   all n^d colours in canonical order         -> examg_smooth_colored(A, u, f, omega, n, 1)
+//   prolongation, (apply bc), red-black sweeps -> examg_prolong_add_smooth_rbgs     (the interpolation rides on the first pass)
 //   residual, (apply bc), restriction          -> examg_residual_restrict           (Residual has no other reader)
 //   residual, (apply bc), norm reduction       -> examg_residual(..., &norm)        (fused sum of squares)
 //   one transfer loop per unknown (u, v)       -> one examg_restrict_cell / examg_prolong_add_cell with nfields = 2
@@ -107,6 +108,25 @@ object ExaMG_MergeCalls extends DefaultStrategy("Merge libexamg calls") {
             stmts.remove(i, j - i)
             stmts.insert(i, ExaMG_Call(smoothColored, first.op, first.u, first.rhs, first.omega, IR_IntegerConstant(first.n), IR_IntegerConstant(1)))
             return true
+          }
+        // correction followed by the post-smoothing of the same field (after the sweeps were merged into one call)
+        case ExaMG_Call(`prolongAdd`, pa, _) if pa(1) == IR_IntegerConstant(-1) && pa(3) == IR_IntegerConstant(-1) =>
+          val j = next(i + 1, pa(2))
+          if (j < stmts.length) stmts(j) match {
+            case ExaMG_Call(`smoothRBGS`, sm, _) if sm(1) == pa(2) =>
+              // wait until the sweeps behind it are merged: the merged call takes the sweep count
+              val jj = next(j + 1, pa(2))
+              val more = jj < stmts.length && (stmts(jj) match {
+                case ExaMG_Call(`smoothRBGS`, b, _)    => sameSmoother(sm, b)
+                case ExaMG_Call(`smoothRBColor`, b, _) => sameSmoother(sm, b)
+                case _                                 => false
+              })
+              if (!more) {
+                stmts.remove(i, j - i + 1)
+                stmts.insert(i, ExaMG_Call(prolongAddSmoothRBGS, sm(0), pa(0), pa(2), sm(2), sm(3), sm(4)))
+                return true
+              }
+            case _                                                 =>
           }
         // residual (+ apply bc) followed by the restriction of the same field: one pass
         case ExaMG_Call(`residual`, r, _) if r.last.isInstanceOf[IR_VariableAccess] /* NULL norm */ =>

@@ -145,6 +145,9 @@ static int vcycle_rec(examg_solver *s, int level) {
     if ((rc = examg_set(c, s->sol[l - 1], -1, 0.0))) return rc;
     if ((rc = vcycle_rec(s, level - 1))) return rc;
   }
+  // Correction + post-smoothing: with red-black sweeps the interpolation rides on the first smoothing pass
+  if (s->desc.smoother == EXAMG_SMOOTH_RBGS && s->desc.nu_post >= 1)
+    return examg_prolong_add_smooth_rbgs(c, s->stencils[l], s->sol[l - 1], s->sol[l], s->rhs[l], s->desc.omega, s->desc.nu_post);
   if ((rc = examg_prolong_add(c, s->sol[l - 1], -1, s->sol[l], -1))) return rc;
   return smooth(s, level, s->desc.nu_post);
 }

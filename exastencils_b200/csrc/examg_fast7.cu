@@ -47,8 +47,17 @@ constexpr int RPLANE = RW * RH;        // doubles per staged plane
 constexpr int RXB = (RH + 2) * 32 + 32;  // doubles per exchange buffer: rows -1..RH of 32, 16 pad each end
 constexpr int ROFF_RING = 1024;        // bytes in front of the ring: mbarriers + landing zone of row -1 reads
 
-template <int S>
-constexpr size_t rbw_smem() { return ROFF_RING + sizeof(double) * (2 * RD * RPLANE + (S - 1) * 2 * RXB); }
+// PRO adds a pair of exchange buffers: the corrected plane is published for half-sweep 1 (the staged plane in the ring
+// holds the uncorrected values)
+// PRO also stages the coarse planes under the tile (33 x 17 nodes, box 34 x 17) in a 4-deep TMA ring of its own
+constexpr int CBW = RW / 2 + 4, CBH = RH / 2 + 1;  // coarse box: 33 x 17 nodes, one more on the left when the corner is odd
+constexpr int CPLS = 640;                          // doubles per coarse ring slot (128-byte multiple >= CBW * CBH)
+constexpr int CRD = 4;                             // coarse ring depth
+static_assert(CBW * CBH <= CPLS && (CPLS * 8) % 128 == 0, "coarse ring slot");
+template <int S, bool PRO = false>
+constexpr size_t rbw_smem() {
+  return ROFF_RING + sizeof(double) * (2 * RD * RPLANE + (S - 1 + (PRO ? 1 : 0)) * 2 * RXB + (PRO ? CRD * CPLS : 0));
+}
 
 struct RbwArgs {
   int n[3];
@@ -62,6 +71,10 @@ struct RbwArgs {
   int pf;              // planes ahead of the TMA loads that are prefetched into L2 (0: none)
   double coef[7];
   double w;            // omega / diag
+  // PRO: `Solution += Prolongation@coarser * Solution@coarser` applied to every plane as it enters the register window
+  int plo[3], phi[3];  // fine nodes that take the correction (the loop range, S layers wider where a neighbour block is)
+  int cpitch;
+  long long cplane;
 };
 
 __device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -122,10 +135,15 @@ __device__ __forceinline__ double rb_update(double c, double xm, double xp, doub
   return fma(w, r, c);
 }
 
-template <int S, int ORD>
+// PRO = true: the correction step of mgCycle (`Solution += NodeProlongation@coarser * Solution@coarser`,
+// Benchmark/Poisson3D/3D_FD_Poisson_fromL4.exa4:233-236) is folded into the load stage of the post-smoothing pass: a
+// plane that enters the register window first takes its interpolated coarse values -- the sums and weights of
+// prolong_point (examg_point_ops.cuh), so the result is bit-identical to the separate loop -- and is smoothed from
+// there.  Saves one read and one write of the fine Solution per cycle.  uc = node (0,0,0) of Solution@coarser.
+template <int S, int ORD, bool PRO>
 __global__ void __launch_bounds__(RNT, 1)
 k_rbw(const __grid_constant__ CUtensorMap tm_u, const __grid_constant__ CUtensorMap tm_f,
-      const __grid_constant__ RbwArgs a, double *__restrict__ uout) {
+      const __grid_constant__ RbwArgs a, double *__restrict__ uout, const __grid_constant__ CUtensorMap tm_c) {
   constexpr int NW = S + 2;  // planes in the register window: t-S-1 .. t
   static_assert(S == 2 || S == 4, "S half-sweeps");
   extern __shared__ __align__(1024) unsigned char smem[];
@@ -133,11 +151,15 @@ k_rbw(const __grid_constant__ CUtensorMap tm_u, const __grid_constant__ CUtensor
   double *ring_u = reinterpret_cast<double *>(smem + ROFF_RING);
   double *ring_f = ring_u + RD * RPLANE;
   double *xbuf = ring_f + RD * RPLANE;  // [(s-1)*2 + plane parity][RXB], s = 1..S-1
+  uint64_t *cfull = full + 8;           // PRO: mbarriers of the coarse ring
+  double *cring = xbuf + S * 2 * RXB;   // PRO: [CRD][CPLS] coarse planes (behind S pairs of exchange buffers)
 
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int x0 = 2 * lane, y0 = 2 * warp;  // the thread's 2x2 block inside the tile
   if (tid == 0) {
     for (int i = 0; i < RD; ++i) mbar_init(&full[i], 1);
+    if (PRO)
+      for (int i = 0; i < CRD; ++i) mbar_init(&cfull[i], 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   __syncthreads();
@@ -161,6 +183,7 @@ k_rbw(const __grid_constant__ CUtensorMap tm_u, const __grid_constant__ CUtensor
   const long long u1 = rem_units * (bid + 1) / G;
   long long ub = rem_units * bid / G;
   uint32_t kt = 0;  // planes loaded so far, modulo 2*RD: ring slot kt & 3, mbarrier phase kt >> 2
+  uint32_t kcn0 = 0;  // PRO: the same count for the coarse ring, at the first coarse plane of the tile
   for (int seg = 0;; ++seg) {
     int tile, za, zb;
     if (seg < nfull) {
@@ -201,6 +224,28 @@ k_rbw(const __grid_constant__ CUtensorMap tm_u, const __grid_constant__ CUtensor
         mk |= (ok ? 1u : 0u) << (4 * (s - 1) + j);
       }
     }
+    // PRO: which of the block's four points take the correction (x, y), and the coarse cell under the block
+    uint32_t pm = 0;
+    if (PRO) {
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const int xx = gx + (j & 1), yy = gy + (j >> 1);
+        pm |= (xx >= a.plo[0] && xx < a.phi[0] && yy >= a.plo[1] && yy < a.phi[1] ? 1u : 0u) << j;
+      }
+    }
+    // PRO: coarse planes kc0 .. kce lie under the fine planes t0 .. tl of this segment; plane kc is the
+    // (kcn0 + kc - kc0)-th load of the coarse ring
+    const int kc0 = t0 >> 1, kce = (tl >> 1) + (tl & 1);
+    // ox - S, oy - S are even.  A TMA box has to start on a 16-byte boundary in global memory (an odd x of doubles is
+    // an "illegal instruction" on B200, tools/tma_probe.cu): an odd corner (S = 2) is loaded from one node further left
+    const int cxo = ((ox - S) >> 1) & 1;
+    const int ccx = ((ox - S) >> 1) - cxo + XPAD, ccy = ((oy - S) >> 1) + GHOST;
+    auto cissue = [&](int kc) {
+      const uint32_t n = (kcn0 + (uint32_t)(kc - kc0)) & (2 * CRD - 1);
+      const int sl = n & (CRD - 1);
+      mbar_expect_tx(&cfull[sl], CBW * CBH * 8);
+      tma_load_plane(cring + sl * CPLS, &tm_c, ccx, ccy, kc + GHOST, &cfull[sl]);
+    };
     const bool xst = x0 >= S && x0 < RW - S && gx < a.n[0];
     const bool st0 = xst && y0 >= S && y0 < RH - S && gy < a.n[1];
     const bool st1 = xst && y0 >= S && y0 < RH - S && gy + 1 < a.n[1];
@@ -216,6 +261,9 @@ k_rbw(const __grid_constant__ CUtensorMap tm_u, const __grid_constant__ CUtensor
       asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
       for (int i = 0; i < RD - 1; ++i)
         if (t0 + i <= tl) issue(t0 + i, kt + i);
+      if (PRO)
+        for (int i = 0; i < CRD; ++i)
+          if (kc0 + i <= kce) cissue(kc0 + i);
       for (int i = RD - 1; i < RD - 1 + a.pf; ++i)
         if (t0 + i <= tl) {
           tma_prefetch_plane(&tm_u, cx, cy, t0 + i + GHOST);
@@ -243,6 +291,39 @@ k_rbw(const __grid_constant__ CUtensorMap tm_u, const __grid_constant__ CUtensor
         u[K][0] = a0.x; u[K][1] = a0.y; u[K][2] = a1.x; u[K][3] = a1.y;
         f[K][0] = b0.x; f[K][1] = b0.y; f[K][2] = b1.x; f[K][3] = b1.y;
       }
+      if (PRO) {
+        // every thread waits (the barriers' phases have to be observed in order), few threads use the values
+        const uint32_t nq = (kcn0 + (uint32_t)((t >> 1) - kc0)) & (2 * CRD - 1);
+        mbar_wait(&cfull[nq & (CRD - 1)], nq >> 2);
+        if (t & 1) mbar_wait(&cfull[(nq + 1) & (CRD - 1)], ((nq + 1) & (2 * CRD - 1)) >> 2);
+        if (pm != 0u && t >= a.plo[2] && t < a.phi[2]) {
+          // c<dy><dx>: coarse plane t>>1; d<dy><dx>: the plane above it (odd fine planes)
+          const double *q = cring + (nq & (CRD - 1)) * CPLS + warp * CBW + lane + cxo;
+          const double c00 = q[0], c01 = q[1], c10 = q[CBW], c11 = q[CBW + 1];
+          double v0, v1, v2, v3;
+          if ((t & 1) == 0) {
+            v0 = fma(1.0, c00, u[K][0]);
+            v1 = fma(0.5, c00 + c01, u[K][1]);
+            v2 = fma(0.5, c00 + c10, u[K][2]);
+            v3 = fma(0.25, ((c00 + c01) + c10) + c11, u[K][3]);
+          } else {
+            const double *qd = cring + ((nq + 1) & (CRD - 1)) * CPLS + warp * CBW + lane + cxo;
+            const double d00 = qd[0], d01 = qd[1], d10 = qd[CBW], d11 = qd[CBW + 1];
+            v0 = fma(0.5, c00 + d00, u[K][0]);
+            v1 = fma(0.25, ((c00 + c01) + d00) + d01, u[K][1]);
+            v2 = fma(0.25, ((c00 + c10) + d00) + d10, u[K][2]);
+            v3 = fma(0.125, ((((((c00 + c01) + c10) + c11) + d00) + d01) + d10) + d11, u[K][3]);
+          }
+          if (pm & 1u) u[K][0] = v0;
+          if (pm & 2u) u[K][1] = v1;
+          if (pm & 4u) u[K][2] = v2;
+          if (pm & 8u) u[K][3] = v3;
+        }
+        // the colour half-sweep 1 will read next step (it then updates the other one): this step's P0 / P1
+        double *xw = xbuf + ((S - 1) * 2 + (K & 1)) * RXB + x_off;
+        xw[0] = u[K][P0];
+        xw[32] = u[K][P1];
+      }
 #pragma unroll
       for (int s = 1; s <= S; ++s) {
         const int c = (K + NW - s) % NW, cm = (K + NW - s - 1) % NW, cp = (K + NW - s + 1) % NW;
@@ -252,7 +333,13 @@ k_rbw(const __grid_constant__ CUtensorMap tm_u, const __grid_constant__ CUtensor
         if (zok) {
           // neighbours owned by other threads: row y0 -> (ex0 in x, ey0 at y0-1), row y0+1 -> (ex1, ey1 at y0+2)
           double ex0, ey0, ex1, ey1;
-          if (s == 1) {  // original values: the staged plane t-1
+          if (s == 1 && PRO) {  // the corrected plane t-1, published one step ago (buffer pair S-1)
+            const double *xb = xbuf + ((S - 1) * 2 + pp) * RXB + x_off;
+            ex0 = xb[DIAG ? -1 : 1];
+            ey0 = xb[-32];
+            ex1 = xb[32 + (DIAG ? 1 : -1)];
+            ey1 = xb[64];
+          } else if (s == 1) {  // original values: the staged plane t-1
             const double *pl = ring_u + ((slot_t + RD - 1) & (RD - 1)) * RPLANE + ld_off;
             ex0 = pl[DIAG ? -1 : 2];
             ey0 = pl[-RW + (DIAG ? 0 : 1)];
@@ -291,6 +378,8 @@ k_rbw(const __grid_constant__ CUtensorMap tm_u, const __grid_constant__ CUtensor
       // the slot has returned its data before its thread arrived at the barrier above (the values
       // were consumed by this step's arithmetic), so no proxy fence is needed -- a fence here would
       // also make the TMA issue wait for this thread's outstanding global accesses.
+      // PRO: after an odd fine plane the coarse plane under it is done with; its slot takes the plane CRD further up
+      if (PRO && tid == 0 && (t & 1) && (t >> 1) + CRD <= kce) cissue((t >> 1) + CRD);
       if (tid == 0 && t + RD - 1 <= tl) {
         issue(t + RD - 1, kt + RD - 1);
         if (a.pf > 0 && t + RD - 1 + a.pf <= tl) {
@@ -316,6 +405,7 @@ k_rbw(const __grid_constant__ CUtensorMap tm_u, const __grid_constant__ CUtensor
         step(std::integral_constant<int, 5 % NW>{}, t + 5);
       }
     }
+    if (PRO) kcn0 = (kcn0 + (uint32_t)(kce - kc0 + 1)) & (2 * CRD - 1);
   }
 }
 
@@ -418,10 +508,14 @@ bool fused_rb_usable(examg_ctx *c, const Stencil &s, const Field &fu) {
 // Allocates the second buffer of a field (not capturable: call before graph capture).
 int ensure_shadow(examg_ctx *c, Field &fu) {
   EXAMG_ONCE_PER_DEVICE(c, {
-    EXAMG_CUDA(cudaFuncSetAttribute(k_rbw<2, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)rbw_smem<2>()));
-    EXAMG_CUDA(cudaFuncSetAttribute(k_rbw<2, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)rbw_smem<2>()));
-    EXAMG_CUDA(cudaFuncSetAttribute(k_rbw<4, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)rbw_smem<4>()));
-    EXAMG_CUDA(cudaFuncSetAttribute(k_rbw<4, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)rbw_smem<4>()));
+    EXAMG_CUDA(cudaFuncSetAttribute(k_rbw<2, 0, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)rbw_smem<2>()));
+    EXAMG_CUDA(cudaFuncSetAttribute(k_rbw<2, 1, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)rbw_smem<2>()));
+    EXAMG_CUDA(cudaFuncSetAttribute(k_rbw<4, 0, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)rbw_smem<4>()));
+    EXAMG_CUDA(cudaFuncSetAttribute(k_rbw<4, 1, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)rbw_smem<4>()));
+    EXAMG_CUDA(cudaFuncSetAttribute(k_rbw<2, 0, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)rbw_smem<2, true>()));
+    EXAMG_CUDA(cudaFuncSetAttribute(k_rbw<2, 1, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)rbw_smem<2, true>()));
+    EXAMG_CUDA(cudaFuncSetAttribute(k_rbw<4, 0, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)rbw_smem<4, true>()));
+    EXAMG_CUDA(cudaFuncSetAttribute(k_rbw<4, 1, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)rbw_smem<4, true>()));
   });
   if (fu.shadow) return EXAMG_OK;
   const LevelGeom &g = *geom(c, fu.level);
@@ -433,8 +527,12 @@ int ensure_shadow(examg_ctx *c, Field &fu) {
 }
 
 // nhalf/2 full sweeps (colour 0, colour 1, ...) in one pass.  Swaps fu.slot[cur] with the shadow buffer.
+static int make_box_map(const LevelGeom &g, const double *base, int ncomp, int bw, int bh, CUtensorMap *tm);
+
+// uc != nullptr: node (0,0,0) of Solution@coarser, whose interpolation is added to Solution on the way in (PRO)
 template <int S>
-static int launch_rbw(examg_ctx *c, const Stencil &s, double omega, Field &fu, const double *rhs) {
+static int launch_rbw(examg_ctx *c, const Stencil &s, double omega, Field &fu, const double *rhs,
+                      const double *uc = nullptr) {
   const LevelGeom &g = *geom(c, s.level);
   CUtensorMap tm_u, tm_f;
   int rc = make_plane_map(g, fu.slot[fu.cur], &tm_u);
@@ -447,6 +545,17 @@ static int launch_rbw(examg_ctx *c, const Stencil &s, double omega, Field &fu, c
     a.uhi[d] = g.hi[d];
     a.elo[d] = c->nb[d][0] ? 1 : 0;
     a.ehi[d] = c->nb[d][1] ? 1 : 0;
+    a.plo[d] = g.lo[d] - S * a.elo[d];
+    a.phi[d] = g.hi[d] + S * a.ehi[d];
+  }
+  a.cpitch = 0;
+  a.cplane = 0;
+  CUtensorMap tm_c = tm_u;
+  if (uc) {
+    const LevelGeom &gc = *geom(c, s.level - 1);
+    a.cpitch = gc.pitch;
+    a.cplane = gc.plane;
+    if ((rc = make_box_map(gc, uc - gc.origin, 1, CBW, CBH, &tm_c))) return rc;
   }
   a.pitch = g.pitch;
   a.plane = g.plane;
@@ -467,10 +576,16 @@ static int launch_rbw(examg_ctx *c, const Stencil &s, double omega, Field &fu, c
   const long long min_units = 6 * S;  // at least this many planes per CTA (2S are restart overhead)
   if (grid > units / min_units) grid = units / min_units;
   if (grid < 1) grid = 1;
-  if (ord == 0)
-    k_rbw<S, 0><<<(int)grid, RNT, rbw_smem<S>(), c->stream>>>(tm_u, tm_f, a, fu.shadow + g.origin);
-  else
-    k_rbw<S, 1><<<(int)grid, RNT, rbw_smem<S>(), c->stream>>>(tm_u, tm_f, a, fu.shadow + g.origin);
+  if (uc) {
+    if (ord == 0)
+      k_rbw<S, 0, true><<<(int)grid, RNT, rbw_smem<S, true>(), c->stream>>>(tm_u, tm_f, a, fu.shadow + g.origin, tm_c);
+    else
+      k_rbw<S, 1, true><<<(int)grid, RNT, rbw_smem<S, true>(), c->stream>>>(tm_u, tm_f, a, fu.shadow + g.origin, tm_c);
+  } else if (ord == 0) {
+    k_rbw<S, 0, false><<<(int)grid, RNT, rbw_smem<S>(), c->stream>>>(tm_u, tm_f, a, fu.shadow + g.origin, tm_c);
+  } else {
+    k_rbw<S, 1, false><<<(int)grid, RNT, rbw_smem<S>(), c->stream>>>(tm_u, tm_f, a, fu.shadow + g.origin, tm_c);
+  }
   EXAMG_LAUNCH_CHECK(c);
   double *t = fu.slot[fu.cur];
   fu.slot[fu.cur] = fu.shadow;
@@ -482,17 +597,24 @@ static int launch_rbw(examg_ctx *c, const Stencil &s, double omega, Field &fu, c
 // sweeps the next launch will fuse (1 or 2)
 int rb_fused_plan(int nsweeps) { return nsweeps >= 2 && max_half_sweeps() >= 4 ? 2 : 1; }
 
-// nsweeps full sweeps; returns the number of sweeps done by one launch through *done
+// nsweeps full sweeps; returns the number of sweeps done by one launch through *done.  uc: see launch_rbw
 int launch_rb_fused(examg_ctx *c, const Stencil &s, double omega, Field &fu, const double *rhs, int nsweeps,
-                    int *done) {
+                    int *done, const double *uc) {
   int rc = ensure_shadow(c, fu);
   if (rc) return rc;
   if (rb_fused_plan(nsweeps) == 2) {
     *done = 2;
-    return launch_rbw<4>(c, s, omega, fu, rhs);
+    return launch_rbw<4>(c, s, omega, fu, rhs, uc);
   }
   *done = 1;
-  return launch_rbw<2>(c, s, omega, fu, rhs);
+  return launch_rbw<2>(c, s, omega, fu, rhs, uc);
+}
+
+// the correction can ride on the first post-smoothing pass (EXAMG_NO_FUSED_PROLONG=1: separate loop)
+bool fused_prolong_enabled() {
+  static int v = -1;
+  if (v < 0) v = env_flag("EXAMG_NO_FUSED_PROLONG", 0) ? 0 : 1;
+  return v == 1;
 }
 
 // ---- Jacobi: S sweeps per pass (examg_jac7.cuh) ------------------------------------

@@ -15,7 +15,9 @@ int launch_rb_generic(examg_ctx *c, const Stencil &s, double omega, double *u, c
 int launch_restrict_generic(examg_ctx *c, int lvl_fine, double scale, const double *rf, double *rhsc);
 int launch_prolong_generic(examg_ctx *c, int lvl_fine, const double *uc, double *uf);
 bool fused_rb_usable(examg_ctx *c, const Stencil &s, const Field &fu);
-int launch_rb_fused(examg_ctx *c, const Stencil &s, double omega, Field &fu, const double *rhs, int nsweeps, int *done);
+int launch_rb_fused(examg_ctx *c, const Stencil &s, double omega, Field &fu, const double *rhs, int nsweeps, int *done,
+                    const double *uc = nullptr);
+bool fused_prolong_enabled();
 int rb_fused_plan(int nsweeps);
 bool fused_jac_usable(examg_ctx *c, const Stencil &s, const Field &fu);
 int launch_jac_fused(examg_ctx *c, const Stencil &s, double omega, Field &fu, const double *rhs, int nsweeps, int *done);
@@ -233,30 +235,50 @@ int examg_smooth_colored(examg_ctx *c, int A, int u, int rhs, double omega, int 
   return EXAMG_OK;
 }
 
+// nsweeps red-black sweeps through the fused kernel; fc != nullptr: Solution += Prolongation * fc rides on the first pass
+static int rbgs_fused(examg_ctx *c, Stencil *s, Field *fu, Field *fr, double omega, int nsweeps, Field *fc) {
+  for (int it = 0; it < nsweeps;) {
+    // one launch does `plan` sweeps = 2*plan half-sweeps: that many ghost layers of Solution and one
+    // less of RHS (the redundant updates in the ghost layers read RHS there); the correction of the ghost layers
+    // needs plan + 1 layers of Solution@coarser (fine layer -2 plan sits on coarse layer -plan, odd layers between two)
+    const int plan = rb_fused_plan(nsweeps - it);
+    int rc, done = 0;
+    Field *fs[3];
+    int slots[3], depths[3], nf = 0;
+    fs[nf] = fu; slots[nf] = fu->cur; depths[nf++] = 2 * plan;
+    if (c->world > 1 && fr->halo_depth < 2 * plan - 1) {  // Solution and RHS in one handshake
+      fs[nf] = fr; slots[nf] = fr->cur; depths[nf++] = 2 * plan - 1;
+    }
+    if (c->world > 1 && fc && it == 0 && fc->halo_depth < plan + 1) {
+      fs[nf] = fc; slots[nf] = fc->cur; depths[nf++] = plan + 1;
+    }
+    if ((rc = do_exchange_many(c, fs, slots, depths, nf))) return rc;
+    const double *uc = fc && it == 0 ? field_ptr(c, fc, -1) : nullptr;
+    if ((rc = launch_rb_fused(c, *s, omega, *fu, field_ptr(c, fr, -1), nsweeps - it, &done, uc))) return rc;
+    it += done;
+    fu->halo_depth = 0;
+  }
+  return EXAMG_OK;
+}
+
+int examg_prolong_add_smooth_rbgs(examg_ctx *c, int A, int u_coarse, int u, int rhs, double omega, int nsweeps) {
+  {
+    GET_STENCIL(s, A); GET_FIELD(fu, u); GET_FIELD(fr, rhs); GET_FIELD(fc, u_coarse);
+    CHECK_LEVEL(fu, s->level); CHECK_LEVEL(fr, s->level); CHECK_LEVEL(fc, s->level - 1);
+    if (nsweeps >= 1 && fused_prolong_enabled() && fused_rb_usable(c, *s, *fu) && fc->loc == 0 && fc->ncomp == 1)
+      return rbgs_fused(c, s, fu, fr, omega, nsweeps, fc);
+  }
+  int rc = examg_prolong_add(c, u_coarse, -1, u, -1);
+  if (rc) return rc;
+  return examg_smooth_rbgs(c, A, u, rhs, omega, nsweeps);
+}
+
 int examg_smooth_rbgs(examg_ctx *c, int A, int u, int rhs, double omega, int nsweeps) {
   {
     GET_STENCIL(s, A); GET_FIELD(fu, u); GET_FIELD(fr, rhs);
     CHECK_LEVEL(fu, s->level); CHECK_LEVEL(fr, s->level);
-    if (fused_rb_usable(c, *s, *fu)) {  // both colours of one or two sweeps in one pass over HBM
-      for (int it = 0; it < nsweeps;) {
-        // one launch does `plan` sweeps = 2*plan half-sweeps: that many ghost layers of Solution and one
-        // less of RHS (the redundant updates in the ghost layers read RHS there)
-        const int plan = rb_fused_plan(nsweeps - it);
-        int rc, done = 0;
-        if (c->world > 1 && fr->halo_depth < 2 * plan - 1) {  // Solution and RHS in one handshake
-          Field *fs[2] = {fu, fr};
-          const int slots[2] = {fu->cur, fr->cur}, depths[2] = {2 * plan, 2 * plan - 1};
-          rc = do_exchange_many(c, fs, slots, depths, 2);
-        } else {
-          rc = do_exchange(c, *fu, fu->cur, 2 * plan);
-        }
-        if (rc) return rc;
-        if ((rc = launch_rb_fused(c, *s, omega, *fu, field_ptr(c, fr, -1), nsweeps - it, &done))) return rc;
-        it += done;
-        fu->halo_depth = 0;
-      }
-      return EXAMG_OK;
-    }
+    // both colours of one or two sweeps in one pass over HBM
+    if (fused_rb_usable(c, *s, *fu)) return rbgs_fused(c, s, fu, fr, omega, nsweeps, nullptr);
   }
   for (int it = 0; it < nsweeps; ++it)
     for (int color = 0; color < 2; ++color) {

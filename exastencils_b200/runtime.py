@@ -117,6 +117,7 @@ SIGNATURES = {
     "examg_restrict": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_double]),
     "examg_residual_restrict": (C.c_int, [C.c_void_p] + [C.c_int] * 5 + [C.c_double]),
     "examg_prolong_add": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int]),
+    "examg_prolong_add_smooth_rbgs": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_double, C.c_int]),
     "examg_dot": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, _dp]),
     "examg_dot_dense_noalloc": (C.c_int, [C.c_void_p, C.c_void_p, C.c_longlong, C.c_void_p, C.c_void_p]),
     "examg_max_abs_diff": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, _dp]),
@@ -399,6 +400,9 @@ class Context:
 
     def prolong_add(self, u_coarse, u_fine, uc_slot=-1, uf_slot=-1):
         check(self.L.examg_prolong_add(self.h, u_coarse, uc_slot, u_fine, uf_slot))
+
+    def prolong_add_smooth_rbgs(self, A, u_coarse, u, rhs, omega, nsweeps=1):
+        check(self.L.examg_prolong_add_smooth_rbgs(self.h, A, u_coarse, u, rhs, omega, nsweeps))
 
     def dot(self, a, b, a_slot=-1, b_slot=-1):
         out = C.c_double()

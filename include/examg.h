@@ -211,6 +211,12 @@ int examg_residual_restrict(examg_ctx *ctx, int stencil, int u, int rhs, int res
 /* Solution += NodeProlongation@coarser * Solution@coarser
  * (C/s/e/operator/l4/L4_DefaultProlongation.scala:30-45)                    */
 int examg_prolong_add(examg_ctx *ctx, int u_coarse, int u_coarse_slot, int u_fine, int u_fine_slot);
+/* Correction + post-smoothing of mgCycle in one call (Benchmark/Poisson3D/3D_FD_Poisson_fromL4.exa4:232-248):
+ *   Solution += NodeProlongation@coarser * Solution@coarser; apply bc; nsweeps x { red-black sweep }.
+ * On large 3D constant-coefficient levels the interpolation is folded into the load stage of the first smoothing pass
+ * (one read and one write of Solution less per cycle); otherwise the two loops run one after the other.  The result
+ * is bit-identical to examg_prolong_add followed by examg_smooth_rbgs.                                          */
+int examg_prolong_add_smooth_rbgs(examg_ctx *ctx, int stencil, int u_coarse, int u, int rhs, double omega, int nsweeps);
 /* loop over F with reduction(+: x) { x += a * b }; global over all blocks */
 int examg_dot(examg_ctx *ctx, int a, int a_slot, int b, int b_slot, double *out);
 /* No counterpart in the reference.  The dot-product reduction of

@@ -344,6 +344,41 @@ def test_residual_restrict_fused(cells, lvl, order, oracle):
     ctx.close()
 
 
+@pytest.mark.parametrize("cells,lvl", [((1, 1, 1), 6), ((5, 3, 2), 5), ((1, 1, 1), 7), ((3, 1, 2), 6), ((1, 1, 1), 4)])
+@pytest.mark.parametrize("order", ["bench", "testing"])
+@pytest.mark.parametrize("nsweeps", [1, 2, 3])
+def test_prolong_add_smooth_fused(cells, lvl, order, nsweeps, oracle):
+    """Correction + post-smoothing of mgCycle as one call: the interpolation of Solution@coarser is folded into the load
+    stage of the first red-black pass (k_rbw<S, ORD, true>).  Solution must be bit-identical to the oracle's
+    prolongation followed by nsweeps x (colour 0, colour 1), on ragged grids too; the last case (17^3) takes the
+    unfused route of the same entry point."""
+    og = oracle
+    ctx = _ctx(3, cells, lvl - 1, lvl)
+    fs, cs = ctx.shape(lvl), ctx.shape(lvl - 1)
+    offs = _ORDERS[order]
+    seed = 3000 * lvl + 10 * sum(cells) + (order == "testing") + 100 * nsweeps
+    coef = _rand(7, seed)
+    coef[0] = 4.0 + abs(coef[0])
+    A = ctx.stencil_const(lvl, offs, coef)
+    st = og.Stencil.make(offs, coef)
+    fu, ff, fc = ctx.field_create("u", lvl), ctx.field_create("rhs", lvl), ctx.field_create("uc", lvl - 1)
+    u, rhs, uc = _rand(fs, seed + 1), _rand(fs, seed + 2), _rand(cs, seed + 3)
+    ctx.upload(fu, u)
+    ctx.upload(ff, rhs)
+    ctx.upload(fc, uc)
+    l0 = ctx.launch_count()
+    ctx.prolong_add_smooth_rbgs(A, fc, fu, ff, 0.8, nsweeps)
+    launches = ctx.launch_count() - l0
+    exp = og.prolong_add(3, uc, u.copy())
+    for _ in range(nsweeps):
+        for colour in (0, 1):
+            og.smooth_rb(st, 0.8, exp, rhs, colour)
+    assert np.array_equal(ctx.download(fu, lvl), exp)
+    if min(fs) >= 65:
+        assert launches == (nsweeps + 1) // 2, "the fused path did not run (%d launches)" % launches
+    ctx.close()
+
+
 def test_pipelined_upload():
     """examg_field_upload_begin/_finish: the copy-stream transfer lands in the field exactly like examg_field_upload,
     for node and cell fields, alternating between the two staging arrays."""
