@@ -573,7 +573,9 @@ static int launch_rbw(examg_ctx *c, const Stencil &s, double omega, Field &fu, c
   cudaGetDevice(&dev);
   cudaDeviceGetAttribute(&nsm, cudaDevAttrMultiProcessorCount, dev);
   long long grid = nsm;
-  const long long min_units = 6 * S;  // at least this many planes per CTA (2S are restart overhead)
+  // at least this many planes per CTA (a segment start costs 2S planes of warm-up): small levels are latency-bound, so
+  // rather more CTAs with short segments than few with long ones (level 6: 30 -> 15 us per launch)
+  const long long min_units = 2 * S;
   if (grid > units / min_units) grid = units / min_units;
   if (grid < 1) grid = 1;
   if (uc) {

@@ -46,7 +46,7 @@ k_stencil(const GridArgs g, const __grid_constant__ StencilArgs st, const double
           for (int k = kb; k < ke; ++k) {
             const long long p = i + (long long)g.pitch * j + g.plane * k;
             const double r = rhs[p] - conv<NST, VAR>(st, sf, sfvol, u, p);
-            out[p] = r;
+            if (out) out[p] = r;  // out == nullptr: only the norm is wanted (examg_solver_cycles)
             sq += (k >= cz0 && k < cz1) ? r * r : 0.0;
           }
           dd_add(part, sq);

@@ -84,6 +84,18 @@ int examg::residual_op(examg_ctx *c, int A, int u, int u_slot, int rhs, int res,
   return finish_sum(c, 0, norm2_out);
 }
 
+int examg::residual_norm2_op(examg_ctx *c, int A, int u, int rhs, double *norm2_out) {
+  GET_STENCIL(s, A); GET_FIELD(fu, u); GET_FIELD(fr, rhs);
+  CHECK_LEVEL(fu, s->level); CHECK_LEVEL(fr, s->level);
+  if (!norm2_out) return set_error(EXAMG_EINVAL, "residual norm: null output");
+  if (fu->loc != fr->loc) return set_error(EXAMG_EINVAL, "residual norm: fields of different localisation");
+  LocGuard lg(c, fu->loc);
+  int rc = do_exchange(c, *fu, fu->cur, 1);
+  if (rc) return rc;
+  if ((rc = launch_residual(c, *s, field_ptr(c, fu, -1), field_ptr(c, fr, -1), nullptr, 0, 0))) return rc;
+  return finish_sum(c, 0, norm2_out);
+}
+
 // RHS@coarser = scale * Restriction * (RHS - A*Solution) without materialising Residual (examg_resrestrict.cu);
 // returns 1 if the combination is not covered (the caller then runs the two separate loops)
 int examg::residual_restrict_op(examg_ctx *c, int A, int u, int rhs, int rhs_coarse, double scale) {

@@ -287,7 +287,9 @@ enum { EXAMG_F_SOLUTION = 0, EXAMG_F_RHS = 1, EXAMG_F_RESIDUAL = 2, EXAMG_F_CGTM
 int examg_solver_field(examg_solver *s, int level, int which);
 /* mgCycle@level (level < 0: finest); asynchronous */
 int examg_solver_vcycle(examg_solver *s, int level);
-/* n x mgCycle@finest followed by one residual+norm; *norm_out = ||Residual||_2 */
+/* n x mgCycle@finest followed by the residual norm of the loop body of Solve@finest:
+ * *norm_out = ||RHS - A*Solution||_2 (nullable).  The field Residual@finest is NOT written by this call -- nothing reads
+ * it before the next cycle -- which makes the pass 16 instead of 24 bytes per point; examg_solver_residual_norm writes it. */
 int examg_solver_cycles(examg_solver *s, int n, double *norm_out);
 /* Residual@finest = RHS - A*Solution; *norm_out = sqrt(global sum r^2) */
 int examg_solver_residual_norm(examg_solver *s, double *norm_out);

@@ -122,6 +122,32 @@ def test_oracle_parity(prog, override, mode, oracle):
     ref.close()
 
 
+@pytest.mark.parametrize("prog,override", [(programs.SMOOTHERS_RBGS, dict(max_level=3, nu_pre=2, nu_post=2, omega=0.8)),
+                                           (programs.SMOOTHERS_JAC, dict(max_level=3))],
+                         ids=["rbgs", "jacobi"])
+def test_solver_cycles_norm_only(prog, override, oracle):
+    """examg_solver_cycles(n, &norm): n cycles and the residual norm of Solve@finest's loop body.  The norm equals the
+    oracle's (the same loop and sums as examg_solver_residual_norm), and Residual@finest is left alone -- the pass that
+    computes the norm does not write it (16 instead of 24 bytes per point; include/examg.h)."""
+    ref, gpu = _setup_pair(prog, "library", **override)
+    lvl = ref.max_level
+    r0 = gpu.update_residual_norm()           # writes Residual@finest
+    before = gpu.fetch_residual().copy()
+    assert abs(r0 - ref.update_residual_norm()) <= RTOL_NORM * r0
+    for n in (1, 2):
+        for _ in range(n):
+            ref.vcycle()
+        r_ref = ref.update_residual_norm()
+        r_gpu = gpu.cycles(n)
+        assert abs(r_gpu - r_ref) <= RTOL_NORM * r_ref
+        assert np.array_equal(gpu.fetch_solution(), ref.solution(lvl).reshape(gpu.ctx.shape(lvl)))
+    assert np.array_equal(gpu.fetch_residual(), before), "examg_solver_cycles wrote Residual@finest"
+    assert gpu.update_residual_norm() == r_gpu  # the explicit statement pair gives the same number, and writes the field
+    assert np.array_equal(gpu.fetch_residual(), ref.residual(lvl).reshape(gpu.ctx.shape(lvl)))
+    gpu.close()
+    ref.close()
+
+
 def test_varcoeff27_device_assembly(oracle):
     """InitLaplace of BASELINE config 3 on the device (examg_field_eval: postfix programs with exp) against the
     oracle's host assembly: equal up to the last bits of exp (device libm vs glibc), rows sum to zero."""
