@@ -38,6 +38,8 @@ object ExaMG_Symbols {
   val fieldDownload = "examg_field_download"
   val fieldAdvance = "examg_field_advance"
   val fieldPrint = "examg_field_print"
+  val fieldWrite = "examg_field_write"
+  val fieldRead = "examg_field_read"
   val stencilConst = "examg_stencil_const"
   val stencilField = "examg_stencil_field"
   // loops
@@ -87,6 +89,8 @@ object ExaMG_Symbols {
   val timerStop = "examg_timer_stop"
   val timerTotalMs = "examg_timer_total_ms"
   val timerPrintAll = "examg_timer_print_all"
+  val benchmarkStart = "examg_benchmark_start"
+  val benchmarkStop = "examg_benchmark_stop"
 }
 
 /// ExaMG_Context

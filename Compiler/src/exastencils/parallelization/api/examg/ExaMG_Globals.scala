@@ -140,6 +140,19 @@ case class ExaMG_StencilCreate(var stencil : IR_Stencil, var stencilField : Opti
   }
 }
 
+/** number of values one block holds of a field (all components, ghost layers excluded) */
+object ExaMG_BlockValues {
+  def apply(field : IR_Field) : IR_Expression = {
+    val layout = field.layout
+    var n : Long = field.layout.datatype.resolveFlattendSize
+    for (d <- 0 until layout.numDimsGrid) n *= (layout.idxById("DRE", d) - layout.idxById("DLB", d)) match {
+      case IR_IntegerConstant(v) => v
+      case _                     => Logger.error("examg back-end: field extents are not compile-time constants"); 1L
+    }
+    IR_IntegerConstant(n)
+  }
+}
+
 /// ExaMG_AddGlobals
 
 /** Handles, the context, the check macro and the (de)initialisation calls in Global/Global.h (+ initGlobals / destroyGlobals). */
@@ -184,11 +197,30 @@ object ExaMG_ResolveHostFunctions extends DefaultStrategy("Forward timers, field
       ExaMG_Call(timerStop, name)
     case IR_ExpressionStatement(IR_FunctionCall(fct, args)) if fct.name == "printAllTimers" && args.isEmpty            =>
       ExaMG_Call(timerPrintAll)
+    // benchmarkStart / benchmarkStop: LIKWID / TALP markers in the reference (util/ir/IR_ResolveBenchmarkFunctions.scala:107-116),
+    // NVTX ranges here; must run before IR_ResolveBenchmarkFunctions turns them into IR_NullStatement
+    case IR_ExpressionStatement(IR_FunctionCall(fct, ListBuffer(name : IR_StringConstant))) if fct.name == "benchmarkStart" =>
+      ExaMG_Call(benchmarkStart, name)
+    case IR_ExpressionStatement(IR_FunctionCall(fct, ListBuffer(name : IR_StringConstant))) if fct.name == "benchmarkStop"  =>
+      ExaMG_Call(benchmarkStop, name)
   })
 
-  this += new Transformation("printField", {
+  this += new Transformation("printField / writeField / readField", {
     case pf : IR_PrintField if !pf.useBinary =>
       ExaMG_Call(fieldPrint, ExaMG_FieldHandle(pf.field), IR_IntegerConstant(-1), pf.filename, pf.separator)
+    // binary dumps through the "lock" interface: block after block in rank order (MPI_Sequential in the reference)
+    case wf : IR_WriteField if wf.useBinary && !wf.includeGhostLayers =>
+      if (Knowledge.mpi_enabled)
+        ExaMG_NativeBlock(
+          s"""for (int r_ = 0; r_ < mpiSize; ++r_) {
+             |  if (r_ == mpiRank) EXAMG_CHECK($fieldWrite(${ ExaMG_Context.name }, ${ ExaMG_FieldHandle(wf.field).handleName }, -1, ${ wf.filename.prettyprint() }, r_ > 0));
+             |  MPI_Barrier(mpiCommunicator);
+             |}""".stripMargin)
+      else
+        ExaMG_Call(fieldWrite, ExaMG_FieldHandle(wf.field), IR_IntegerConstant(-1), wf.filename, IR_IntegerConstant(0))
+    case rf : IR_ReadField if rf.useBinary && !rf.includeGhostLayers  =>
+      ExaMG_Call(fieldRead, ExaMG_FieldHandle(rf.field), IR_IntegerConstant(-1), rf.filename,
+        if (Knowledge.mpi_enabled) IR_VariableAccess("mpiRank", IR_IntegerDatatype) * ExaMG_BlockValues(rf.field) else IR_IntegerConstant(0))
   })
 
   this += new Transformation("external fields", {

@@ -8,6 +8,8 @@
 //   C/s/e/field/ir/IR_FieldLayout.scala:30-129             (layout; redesigned, see examg_internal.h)
 #include <cstring>
 
+#include <nvtx3/nvToolsExt.h>
+
 #include "examg_internal.h"
 
 using namespace examg;
@@ -293,6 +295,25 @@ static int fold_timer(Timer &t, bool wait) {
   }
   t.done.resize(keep);
   return EXAMG_OK;
+}
+
+// benchmarkStart("name") / benchmarkStop("name") of the L4 programs: the reference lowers them to LIKWID / TALP region
+// markers (C/s/e/util/ir/IR_ResolveBenchmarkFunctions.scala:63-120).  The B200 analogue is an NVTX range (nsys / ncu
+// --nvtx pick it up; without a tool attached the calls cost nothing), plus a device timer of the same name.
+int examg_benchmark_start(examg_ctx *c, const char *name) {
+  if (!c || !name) return set_error(EXAMG_EINVAL, "examg_benchmark_start: null argument");
+  nvtxRangePushA(name);
+  c->nvtx_depth++;
+  return examg_timer_start(c, name);
+}
+
+int examg_benchmark_stop(examg_ctx *c, const char *name) {
+  if (!c || !name) return set_error(EXAMG_EINVAL, "examg_benchmark_stop: null argument");
+  if (c->nvtx_depth <= 0) return set_error(EXAMG_ESTATE, "benchmarkStop(\"%s\") without benchmarkStart", name);
+  int rc = examg_timer_stop(c, name);
+  nvtxRangePop();
+  c->nvtx_depth--;
+  return rc;
 }
 
 int examg_timer_start(examg_ctx *c, const char *name) {
@@ -703,6 +724,54 @@ int examg_field_print(examg_ctx *c, int h, int slot, const char *filename, const
       }
   fclose(fp);
   return EXAMG_OK;
+}
+
+// writeField / readField with the "lock" interface in binary mode (C/s/e/field/ir/IR_WriteField.scala:26-45,
+// IR_ReadField.scala:27-46, io/ir/IR_FileAccess_Locking.scala:87-200): the values only, raw doubles in the layout of the
+// get<name>/set<name> arrays -- [comp][z][y][x], x fastest, ghost layers excluded (includeGhostLayers = false).  With
+// several blocks the reference appends block after block in rank order (MPI_Sequential): `append` != 0 does that for
+// this block; the caller sequences the ranks.
+int examg_field_write(examg_ctx *c, int h, int slot, const char *filename, int append) {
+  Field *f = get_field(c, h);
+  if (!f) return set_error(EXAMG_EINVAL, "bad field %d", h);
+  if (!filename) return set_error(EXAMG_EINVAL, "examg_field_write: null file name");
+  if (slot >= f->nslots) return set_error(EXAMG_EINVAL, "bad slot %d", slot);
+  const LevelGeom &g = *geom(c, f->level);
+  size_t dense = 1;
+  for (int d = 0; d < 3; ++d) dense *= (size_t)(g.n[d] - (f->loc == 1 && d < c->cfg.dim ? 1 : 0));
+  std::vector<double> host((size_t)f->ncomp * dense);
+  int rc = examg_field_download(c, h, slot, host.data());
+  if (rc) return rc;
+  FILE *fp = fopen(filename, append ? "ab" : "wb");
+  if (!fp) return set_error(EXAMG_EINVAL, "examg_field_write: cannot open %s", filename);
+  const size_t nw = fwrite(host.data(), sizeof(double), host.size(), fp);
+  fclose(fp);
+  if (nw != host.size()) return set_error(EXAMG_EINVAL, "examg_field_write: short write to %s", filename);
+  return EXAMG_OK;
+}
+
+// offset_doubles: where this block's values start in the file (0 for one block; rank * values per block for the
+// rank-ordered file examg_field_write produces)
+int examg_field_read(examg_ctx *c, int h, int slot, const char *filename, long long offset_doubles) {
+  Field *f = get_field(c, h);
+  if (!f) return set_error(EXAMG_EINVAL, "bad field %d", h);
+  if (!filename) return set_error(EXAMG_EINVAL, "examg_field_read: null file name");
+  if (slot >= f->nslots) return set_error(EXAMG_EINVAL, "bad slot %d", slot);
+  if (offset_doubles < 0) return set_error(EXAMG_EINVAL, "examg_field_read: negative offset");
+  const LevelGeom &g = *geom(c, f->level);
+  size_t dense = 1;
+  for (int d = 0; d < 3; ++d) dense *= (size_t)(g.n[d] - (f->loc == 1 && d < c->cfg.dim ? 1 : 0));
+  std::vector<double> host((size_t)f->ncomp * dense);
+  FILE *fp = fopen(filename, "rb");
+  if (!fp) return set_error(EXAMG_EINVAL, "examg_field_read: cannot open %s", filename);
+  size_t nr = 0;
+  if (fseek(fp, (long)(offset_doubles * (long long)sizeof(double)), SEEK_SET) == 0)
+    nr = fread(host.data(), sizeof(double), host.size(), fp);
+  fclose(fp);
+  if (nr != host.size())
+    return set_error(EXAMG_EINVAL, "examg_field_read: %s holds %zu of the %zu values of %s@%d", filename, nr, host.size(),
+                     f->name.c_str(), f->level);
+  return examg_field_upload(c, h, slot, host.data());
 }
 
 int examg_field_fill(examg_ctx *c, int h, double value) {

@@ -54,9 +54,11 @@ constexpr int CBW = RW / 2 + 4, CBH = RH / 2 + 1;  // coarse box: 33 x 17 nodes,
 constexpr int CPLS = 640;                          // doubles per coarse ring slot (128-byte multiple >= CBW * CBH)
 constexpr int CRD = 4;                             // coarse ring depth
 static_assert(CBW * CBH <= CPLS && (CPLS * 8) % 128 == 0, "coarse ring slot");
-template <int S, bool PRO = false>
+// X0 (without PRO): half-sweep 1 also reads its neighbours from an exchange buffer that the load stage fills, instead
+// of from the staged plane in the ring, whose x neighbours sit two doubles apart per lane (2-way bank conflicts)
+template <int S, bool PRO = false, bool X0 = false>
 constexpr size_t rbw_smem() {
-  return ROFF_RING + sizeof(double) * (2 * RD * RPLANE + (S - 1 + (PRO ? 1 : 0)) * 2 * RXB + (PRO ? CRD * CPLS : 0));
+  return ROFF_RING + sizeof(double) * (2 * RD * RPLANE + (S - 1 + (PRO || X0 ? 1 : 0)) * 2 * RXB + (PRO ? CRD * CPLS : 0));
 }
 
 struct RbwArgs {
@@ -140,7 +142,7 @@ __device__ __forceinline__ double rb_update(double c, double xm, double xp, doub
 // plane that enters the register window first takes its interpolated coarse values -- the sums and weights of
 // prolong_point (examg_point_ops.cuh), so the result is bit-identical to the separate loop -- and is smoothed from
 // there.  Saves one read and one write of the fine Solution per cycle.  uc = node (0,0,0) of Solution@coarser.
-template <int S, int ORD, bool PRO>
+template <int S, int ORD, bool PRO, bool X0 = false>
 __global__ void __launch_bounds__(RNT, 1)
 k_rbw(const __grid_constant__ CUtensorMap tm_u, const __grid_constant__ CUtensorMap tm_f,
       const __grid_constant__ RbwArgs a, double *__restrict__ uout, const __grid_constant__ CUtensorMap tm_c) {
@@ -319,6 +321,8 @@ k_rbw(const __grid_constant__ CUtensorMap tm_u, const __grid_constant__ CUtensor
           if (pm & 4u) u[K][2] = v2;
           if (pm & 8u) u[K][3] = v3;
         }
+      }
+      if (PRO || X0) {
         // the colour half-sweep 1 will read next step (it then updates the other one): this step's P0 / P1
         double *xw = xbuf + ((S - 1) * 2 + (K & 1)) * RXB + x_off;
         xw[0] = u[K][P0];
@@ -333,7 +337,7 @@ k_rbw(const __grid_constant__ CUtensorMap tm_u, const __grid_constant__ CUtensor
         if (zok) {
           // neighbours owned by other threads: row y0 -> (ex0 in x, ey0 at y0-1), row y0+1 -> (ex1, ey1 at y0+2)
           double ex0, ey0, ex1, ey1;
-          if (s == 1 && PRO) {  // the corrected plane t-1, published one step ago (buffer pair S-1)
+          if (s == 1 && (PRO || X0)) {  // the (corrected) plane t-1, published one step ago (buffer pair S-1)
             const double *xb = xbuf + ((S - 1) * 2 + pp) * RXB + x_off;
             ex0 = xb[DIAG ? -1 : 1];
             ey0 = xb[-32];
@@ -512,6 +516,10 @@ int ensure_shadow(examg_ctx *c, Field &fu) {
     EXAMG_CUDA(cudaFuncSetAttribute(k_rbw<2, 1, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)rbw_smem<2>()));
     EXAMG_CUDA(cudaFuncSetAttribute(k_rbw<4, 0, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)rbw_smem<4>()));
     EXAMG_CUDA(cudaFuncSetAttribute(k_rbw<4, 1, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)rbw_smem<4>()));
+    EXAMG_CUDA(cudaFuncSetAttribute(k_rbw<2, 0, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)rbw_smem<2, false, true>()));
+    EXAMG_CUDA(cudaFuncSetAttribute(k_rbw<2, 1, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)rbw_smem<2, false, true>()));
+    EXAMG_CUDA(cudaFuncSetAttribute(k_rbw<4, 0, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)rbw_smem<4, false, true>()));
+    EXAMG_CUDA(cudaFuncSetAttribute(k_rbw<4, 1, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)rbw_smem<4, false, true>()));
     EXAMG_CUDA(cudaFuncSetAttribute(k_rbw<2, 0, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)rbw_smem<2, true>()));
     EXAMG_CUDA(cudaFuncSetAttribute(k_rbw<2, 1, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)rbw_smem<2, true>()));
     EXAMG_CUDA(cudaFuncSetAttribute(k_rbw<4, 0, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)rbw_smem<4, true>()));
@@ -528,6 +536,13 @@ int ensure_shadow(examg_ctx *c, Field &fu) {
 
 // nhalf/2 full sweeps (colour 0, colour 1, ...) in one pass.  Swaps fu.slot[cur] with the shadow buffer.
 static int make_box_map(const LevelGeom &g, const double *base, int ncomp, int bw, int bh, CUtensorMap *tm);
+
+// half-sweep 1 reads its neighbours from an exchange buffer (EXAMG_RBW_X0, default on: measured)
+static bool rbw_x0() {
+  static int v = -1;
+  if (v < 0) v = env_flag("EXAMG_RBW_X0", 1) ? 1 : 0;
+  return v == 1;
+}
 
 // uc != nullptr: node (0,0,0) of Solution@coarser, whose interpolation is added to Solution on the way in (PRO)
 template <int S>
@@ -583,6 +598,11 @@ static int launch_rbw(examg_ctx *c, const Stencil &s, double omega, Field &fu, c
       k_rbw<S, 0, true><<<(int)grid, RNT, rbw_smem<S, true>(), c->stream>>>(tm_u, tm_f, a, fu.shadow + g.origin, tm_c);
     else
       k_rbw<S, 1, true><<<(int)grid, RNT, rbw_smem<S, true>(), c->stream>>>(tm_u, tm_f, a, fu.shadow + g.origin, tm_c);
+  } else if (rbw_x0()) {
+    if (ord == 0)
+      k_rbw<S, 0, false, true><<<(int)grid, RNT, rbw_smem<S, false, true>(), c->stream>>>(tm_u, tm_f, a, fu.shadow + g.origin, tm_c);
+    else
+      k_rbw<S, 1, false, true><<<(int)grid, RNT, rbw_smem<S, false, true>(), c->stream>>>(tm_u, tm_f, a, fu.shadow + g.origin, tm_c);
   } else if (ord == 0) {
     k_rbw<S, 0, false><<<(int)grid, RNT, rbw_smem<S>(), c->stream>>>(tm_u, tm_f, a, fu.shadow + g.origin, tm_c);
   } else {

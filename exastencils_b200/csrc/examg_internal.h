@@ -143,6 +143,7 @@ struct examg_ctx {
   bool own_stream = false;
   long long launches = 0;
   long long dev_bytes = 0;
+  int nvtx_depth = 0;  // open benchmarkStart ranges
   // reduction scratch: per-block partials + final result
   examg::dd *partials = nullptr;  // PARTIAL_CAP
   examg::dd *red_out = nullptr;   // RED_SLOTS results on device

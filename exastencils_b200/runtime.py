@@ -155,6 +155,10 @@ SIGNATURES = {
     "examg_comm_blob_size": (C.c_int, [C.c_void_p]),
     "examg_comm_export": (C.c_int, [C.c_void_p, C.c_void_p]),
     "examg_comm_import": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int]),
+    "examg_benchmark_start": (C.c_int, [C.c_void_p, C.c_char_p]),
+    "examg_benchmark_stop": (C.c_int, [C.c_void_p, C.c_char_p]),
+    "examg_field_write": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_char_p, C.c_int]),
+    "examg_field_read": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_char_p, C.c_longlong]),
     "examg_timer_start": (C.c_int, [C.c_void_p, C.c_char_p]),
     "examg_timer_stop": (C.c_int, [C.c_void_p, C.c_char_p]),
     "examg_timer_total_ms": (C.c_int, [C.c_void_p, C.c_char_p, _dp, C.POINTER(C.c_longlong)]),
@@ -321,6 +325,18 @@ class Context:
     def field_print(self, f, filename, slot=-1, separator=None):
         """printField ( "file", F ): ascii, one line per point (position, value[s])."""
         check(self.L.examg_field_print(self.h, f, slot, filename.encode(), separator.encode() if separator else None))
+
+    def field_write(self, f, filename, slot=-1, append=False):
+        check(self.L.examg_field_write(self.h, f, slot, str(filename).encode(), 1 if append else 0))
+
+    def field_read(self, f, filename, slot=-1, offset_doubles=0):
+        check(self.L.examg_field_read(self.h, f, slot, str(filename).encode(), offset_doubles))
+
+    def benchmark_start(self, name):
+        check(self.L.examg_benchmark_start(self.h, name.encode()))
+
+    def benchmark_stop(self, name):
+        check(self.L.examg_benchmark_stop(self.h, name.encode()))
 
     def apply_bc(self, f, slot=-1):
         check(self.L.examg_apply_bc(self.h, f, slot))

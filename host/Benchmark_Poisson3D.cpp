@@ -183,7 +183,9 @@ int main(int argc, char **argv) {
   EXAMG_CHECK(examg_timer_stop(ctx, "setup"));
   // solve
   EXAMG_CHECK(examg_timer_start(ctx, "solve"));
+  EXAMG_CHECK(examg_benchmark_start(ctx, "solvePhase"));  // benchmarkStart ( "solvePhase" ): an NVTX range on B200
   const int its = Solve();
+  EXAMG_CHECK(examg_benchmark_stop(ctx, "solvePhase"));
   EXAMG_CHECK(examg_timer_stop(ctx, "solve"));
   // de-init
   EXAMG_CHECK(examg_timer_print_all(ctx));

@@ -141,6 +141,14 @@ int examg_field_eval(examg_ctx *ctx, int field, int slot, int comp, const examg_
 /* applyBCs<F>_<lvl>(slot)  (C/s/e/boundary/ir/IR_ApplyBCFunction.scala:53-105); slot < 0 = active */
 int examg_apply_bc(examg_ctx *ctx, int field, int slot);
 
+/* writeField ( "file", F ) / readField ( "file", F ) with the "lock" interface in binary mode
+ * (C/s/e/field/ir/IR_WriteField.scala:26-45, IR_ReadField.scala:27-46, io/ir/IR_FileAccess_Locking.scala:87-200): the
+ * values only, raw doubles [comp][z][y][x] (x fastest), ghost layers excluded.  append != 0 appends (several blocks: the
+ * ranks write one after the other, as MPI_Sequential does); offset_doubles = where this block starts in the file.
+ * Synchronise.                                                                                                */
+int examg_field_write(examg_ctx *ctx, int field, int slot, const char *filename, int append);
+int examg_field_read(examg_ctx *ctx, int field, int slot, const char *filename, long long offset_doubles);
+
 /* set<name>/get<name>: dense caller array [comp][nz][ny][nx], x fastest, local
  * nodes incl. duplicate/boundary nodes, no ghosts.  Synchronous. */
 int examg_field_upload(examg_ctx *ctx, int field, int slot, const double *host);
@@ -365,6 +373,11 @@ int examg_comm_import(examg_ctx *ctx, const void *all_blobs, int world);
  * (C/s/e/timing/ir/IR_GetTime.scala:33-63, IR_PrintAllTimers.scala:38-70).  Measured with CUDA events on the
  * context stream: asynchronous; examg_timer_total_ms waits for the measurements it reports.  Do not start or
  * stop a timer inside a region that the library captures into a CUDA graph (examg_solver_vcycle).        */
+/* benchmarkStart ( "name" ) / benchmarkStop ( "name" ): the reference lowers them to LIKWID / TALP region markers
+ * (C/s/e/util/ir/IR_ResolveBenchmarkFunctions.scala:63-120); here an NVTX range (visible to nsys / ncu --nvtx) plus a
+ * device timer of the same name (examg_timer_total_ms).  Ranges nest.                                          */
+int examg_benchmark_start(examg_ctx *ctx, const char *name);
+int examg_benchmark_stop(examg_ctx *ctx, const char *name);
 int examg_timer_start(examg_ctx *ctx, const char *name);
 int examg_timer_stop(examg_ctx *ctx, const char *name);
 int examg_timer_total_ms(examg_ctx *ctx, const char *name, double *total_ms, long long *count);

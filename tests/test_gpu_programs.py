@@ -122,6 +122,39 @@ def test_oracle_parity(prog, override, mode, oracle):
     ref.close()
 
 
+def test_binary_field_io_and_benchmark_markers(tmp_path):
+    """writeField / readField in binary mode (raw doubles, [comp][z][y][x], no ghost layers; rank-ordered append for
+    several blocks) and benchmarkStart / benchmarkStop (NVTX range + device timer of the same name)."""
+    from exastencils_b200 import runtime as rt
+    ctx = rt.Context(3, 3, 3, block_cells=(2, 1, 3))
+    shape = ctx.shape(3)
+    rng = np.random.default_rng(5)
+    a = rng.uniform(-1.0, 1.0, size=(3,) + shape)
+    f, g = ctx.field_create("f", 3, 1, 3), ctx.field_create("g", 3, 2, 3)
+    ctx.upload(f, a)
+    path = tmp_path / "f.bin"
+    ctx.benchmark_start("io")
+    ctx.field_write(f, path)
+    ctx.field_write(f, path, append=True)   # what a second rank would do
+    ctx.benchmark_stop("io")
+    raw = np.fromfile(path, dtype=np.float64)
+    assert raw.size == 2 * a.size and np.array_equal(raw[:a.size].reshape(a.shape), a) and np.array_equal(raw[a.size:], raw[:a.size])
+    ctx.field_read(g, path, slot=1, offset_doubles=a.size)
+    assert np.array_equal(ctx.download(g, 3, slot=1, ncomp=3), a)
+    with pytest.raises(rt.ExaMGError, match="holds"):
+        ctx.field_read(g, path, offset_doubles=a.size + 1)   # short file
+    with pytest.raises(rt.ExaMGError, match="without benchmarkStart"):
+        ctx.benchmark_stop("io")
+    total, count = ctx.timer_total_ms("io")
+    assert count == 1 and total > 0.0
+    cf = ctx.field_create_cell("c", 3)
+    c = rng.uniform(-1.0, 1.0, size=ctx.cell_shape(3))
+    ctx.upload(cf, c)
+    ctx.field_write(cf, tmp_path / "c.bin")
+    assert np.array_equal(np.fromfile(tmp_path / "c.bin").reshape(c.shape), c)
+    ctx.close()
+
+
 @pytest.mark.parametrize("prog,override", [(programs.SMOOTHERS_RBGS, dict(max_level=3, nu_pre=2, nu_post=2, omega=0.8)),
                                            (programs.SMOOTHERS_JAC, dict(max_level=3))],
                          ids=["rbgs", "jacobi"])
