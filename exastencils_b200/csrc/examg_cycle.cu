@@ -42,6 +42,7 @@ struct examg_solver {
 
 namespace examg {
 bool fused_rb_usable(examg_ctx *c, const Stencil &s, const Field &fu);
+bool fused_rb2d_usable(examg_ctx *c, const Stencil &s, const Field &fu);
 int ensure_shadow(examg_ctx *c, Field &fu);
 // single-CTA coarse sub-cycle (examg_coarse.cu)
 int coarse_cycle_top(examg_ctx *c, const examg_cycle_desc &d, const int *stencils, const int *sol, int max_top);
@@ -206,7 +207,8 @@ examg_solver *examg_solver_create(examg_ctx *c, const examg_cycle_desc *d) {
   // second buffers of the fused sweeps: now, so that they are part of what examg_comm_export publishes
   if (d->smoother == EXAMG_SMOOTH_RBGS)
     for (int l = 0; l < nl; ++l)
-      if (fused_rb_usable(c, *get_stencil(c, s->stencils[l]), c->fields[s->sol[l]]) &&
+      if ((fused_rb_usable(c, *get_stencil(c, s->stencils[l]), c->fields[s->sol[l]]) ||
+           fused_rb2d_usable(c, *get_stencil(c, s->stencils[l]), c->fields[s->sol[l]])) &&
           ensure_shadow(c, c->fields[s->sol[l]])) {
         examg_solver_destroy(s);
         return nullptr;

@@ -273,6 +273,7 @@ k_rbw(const __grid_constant__ CUtensorMap tm_u, const __grid_constant__ CUtensor
         }
     }
 
+    if (PRO) mbar_wait(&cfull[kcn0 & (CRD - 1)], (kcn0 & (2 * CRD - 1)) >> 2);  // coarse plane kc0
     double u[NW][4], f[NW][4];  // [plane slot][jx + 2*jy]
 #pragma unroll
     for (int q = 0; q < NW; ++q)
@@ -294,9 +295,9 @@ k_rbw(const __grid_constant__ CUtensorMap tm_u, const __grid_constant__ CUtensor
         f[K][0] = b0.x; f[K][1] = b0.y; f[K][2] = b1.x; f[K][3] = b1.y;
       }
       if (PRO) {
-        // every thread waits (the barriers' phases have to be observed in order), few threads use the values
+        // Every coarse plane is waited for exactly once by every thread: plane kc0 at the start of the segment (below),
+        // plane (t>>1)+1 at the odd fine plane t that first reads it.
         const uint32_t nq = (kcn0 + (uint32_t)((t >> 1) - kc0)) & (2 * CRD - 1);
-        mbar_wait(&cfull[nq & (CRD - 1)], nq >> 2);
         if (t & 1) mbar_wait(&cfull[(nq + 1) & (CRD - 1)], ((nq + 1) & (2 * CRD - 1)) >> 2);
         if (pm != 0u && t >= a.plo[2] && t < a.phi[2]) {
           // c<dy><dx>: coarse plane t>>1; d<dy><dx>: the plane above it (odd fine planes)
@@ -316,10 +317,14 @@ k_rbw(const __grid_constant__ CUtensorMap tm_u, const __grid_constant__ CUtensor
             v2 = fma(0.25, ((c00 + c10) + d00) + d10, u[K][2]);
             v3 = fma(0.125, ((((((c00 + c01) + c10) + c11) + d00) + d01) + d10) + d11, u[K][3]);
           }
-          if (pm & 1u) u[K][0] = v0;
-          if (pm & 2u) u[K][1] = v1;
-          if (pm & 4u) u[K][2] = v2;
-          if (pm & 8u) u[K][3] = v3;
+          if (pm == 15u) {  // interior of the block: all four points
+            u[K][0] = v0; u[K][1] = v1; u[K][2] = v2; u[K][3] = v3;
+          } else {
+            if (pm & 1u) u[K][0] = v0;
+            if (pm & 2u) u[K][1] = v1;
+            if (pm & 4u) u[K][2] = v2;
+            if (pm & 8u) u[K][3] = v3;
+          }
         }
       }
       if (PRO || X0) {

@@ -18,6 +18,8 @@ bool fused_rb_usable(examg_ctx *c, const Stencil &s, const Field &fu);
 int launch_rb_fused(examg_ctx *c, const Stencil &s, double omega, Field &fu, const double *rhs, int nsweeps, int *done,
                     const double *uc = nullptr);
 bool fused_prolong_enabled();
+bool fused_rb2d_usable(examg_ctx *c, const Stencil &s, const Field &fu);
+int launch_rb2d_fused(examg_ctx *c, const Stencil &s, double omega, Field &fu, const double *rhs, int nsweeps, int *done);
 int rb_fused_plan(int nsweeps);
 bool fused_jac_usable(examg_ctx *c, const Stencil &s, const Field &fu);
 int launch_jac_fused(examg_ctx *c, const Stencil &s, double omega, Field &fu, const double *rhs, int nsweeps, int *done);
@@ -291,6 +293,16 @@ int examg_smooth_rbgs(examg_ctx *c, int A, int u, int rhs, double omega, int nsw
     CHECK_LEVEL(fu, s->level); CHECK_LEVEL(fr, s->level);
     // both colours of one or two sweeps in one pass over HBM
     if (fused_rb_usable(c, *s, *fu)) return rbgs_fused(c, s, fu, fr, omega, nsweeps, nullptr);
+    if (fused_rb2d_usable(c, *s, *fu) && fr->loc == 0) {  // 2D 5-point: up to three sweeps per launch (examg_fast5.cu)
+      for (int it = 0; it < nsweeps;) {
+        int done = 0;
+        int rc = launch_rb2d_fused(c, *s, omega, *fu, field_ptr(c, fr, -1), nsweeps - it, &done);
+        if (rc) return rc;
+        it += done;
+        fu->halo_depth = 0;
+      }
+      return EXAMG_OK;
+    }
   }
   for (int it = 0; it < nsweeps; ++it)
     for (int color = 0; color < 2; ++color) {

@@ -379,6 +379,51 @@ def test_prolong_add_smooth_fused(cells, lvl, order, nsweeps, oracle):
     ctx.close()
 
 
+_RB2D_CASES = [((1, 1), 3), ((3, 5), 4), ((1, 1), 6), ((5, 3), 5), ((1, 1), 9), ((4, 4), 8)]
+
+
+@pytest.mark.parametrize("cells,lvl", _RB2D_CASES)
+@pytest.mark.parametrize("order", ["bench", "testing"])
+def test_rbgs_2d_fused_sweeps(cells, lvl, order, oracle, monkeypatch):
+    """2D 5-point constant coefficients (BASELINE config 1): up to three red-black sweeps per launch (k_rb2d<S>,
+    examg_fast5.cu).  Solution bit-identical to nu x (colour 0, colour 1) of the oracle for nu = 1..7, on ragged grids,
+    9 x 9 (one strip, one segment) up to 1025^2; launches = ceil(nu / 3).  The path is opt-in (EXAMG_FUSED_2D=1: it is
+    not faster than the generic colour kernels on an L2-resident hierarchy) and read once per process, so the
+    test runs in a process of its own."""
+    import os, subprocess, sys
+    if os.environ.get("EXAMG_FUSED_2D") != "1":
+        env = dict(os.environ, EXAMG_FUSED_2D="1")
+        node = "%s::test_rbgs_2d_fused_sweeps[%s-%s-%d]" % (__file__, order, "cells%d" % [c for c, _ in _RB2D_CASES].index(cells), lvl)
+        out = subprocess.run([sys.executable, "-m", "pytest", "-x", "-q", "-m", "gpu", node], env=env, capture_output=True,
+                             text=True, timeout=600)
+        assert out.returncode == 0, out.stdout[-3000:] + out.stderr[-2000:]
+        return
+    og = oracle
+    ctx = _ctx(2, cells, lvl, lvl)
+    shape = ctx.shape(lvl)
+    offs = ([(0, 0, 0), (-1, 0, 0), (1, 0, 0), (0, -1, 0), (0, 1, 0)] if order == "bench" else
+            [(0, 0, 0), (1, 0, 0), (-1, 0, 0), (0, 1, 0), (0, -1, 0)])
+    seed = 4000 * lvl + 10 * sum(cells) + (order == "testing")
+    coef = _rand(5, seed)
+    coef[0] = 3.0 + abs(coef[0])
+    A = ctx.stencil_const(lvl, offs, coef)
+    st = og.Stencil.make(offs, coef)
+    fu, ff = ctx.field_create("u", lvl), ctx.field_create("rhs", lvl)
+    u, rhs = _rand(shape, seed + 1), _rand(shape, seed + 2)
+    ctx.upload(ff, rhs)
+    for nu in (1, 2, 3, 4, 7):
+        ctx.upload(fu, u)
+        l0 = ctx.launch_count()
+        ctx.smooth_rbgs(A, fu, ff, 0.8, nu)
+        assert ctx.launch_count() - l0 == (nu + 2) // 3, "the fused 2D path did not run"
+        e = u.copy()
+        for _ in range(nu):
+            og.smooth_rb(st, 0.8, e, rhs, 0)
+            og.smooth_rb(st, 0.8, e, rhs, 1)
+        assert np.array_equal(ctx.download(fu, lvl), e), "nu = %d" % nu
+    ctx.close()
+
+
 def test_pipelined_upload():
     """examg_field_upload_begin/_finish: the copy-stream transfer lands in the field exactly like examg_field_upload,
     for node and cell fields, alternating between the two staging arrays."""
