@@ -68,6 +68,7 @@ object ExaMG_Symbols {
   val bicgstabCoarse = "examg_bicgstab_coarse"
   val crCoarse = "examg_cr_coarse"
   val minresCoarse = "examg_minres_coarse"
+  val smootherCoarse = "examg_smoother_coarse"
   // coupled two-unknown systems (solve locally)
   val system2Create = "examg_system2_create"
   val system2Residual = "examg_system2_residual"
@@ -75,6 +76,7 @@ object ExaMG_Symbols {
   val system2SmoothRBColor = "examg_system2_smooth_rb_color"
   val system2CGCoarse = "examg_system2_cg_coarse"
   // whole cycle
+  val cycleDescFromOptions = "examg_cycle_desc_from_options"
   val solverCreate = "examg_solver_create"
   val solverCycles = "examg_solver_cycles"
   val solverVCycle = "examg_solver_vcycle"

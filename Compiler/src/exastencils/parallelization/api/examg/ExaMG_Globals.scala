@@ -183,6 +183,35 @@ object ExaMG_AddGlobals extends NoStrategyWrapper {
   }
 }
 
+/// ExaMG_LibraryCycle
+
+/** Knowledge.experimental_examg_libraryCycle: the L3-generated `gen_mgCycle@finest` (solver/l3/L3_SolverForEquation.scala:341-395)
+  * becomes ONE library object -- the solver_* Knowledge values travel as text through examg_cycle_desc_from_options
+  * (smoother, colouring, damping, sweep counts, solver_cgs incl. "Smoother" = examg_smoother_coarse at the bottom), the
+  * cycle runs as a CUDA graph (examg_solver_vcycle).  The statement-by-statement lowering stays the default. */
+object ExaMG_LibraryCycle extends DefaultStrategy("Replace the generated multigrid cycle by the library's solver object") {
+  def options : String = Seq(
+    s"solver_smoother_numPre = ${ Knowledge.solver_smoother_numPre }", s"solver_smoother_numPost = ${ Knowledge.solver_smoother_numPost }",
+    s"solver_smoother_damping = ${ Knowledge.solver_smoother_damping }", s"solver_smoother_jacobiType = ${ Knowledge.solver_smoother_jacobiType }",
+    s"solver_smoother_coloring = ${ Knowledge.solver_smoother_coloring }", s"solver_cgs = ${ Knowledge.solver_cgs }",
+    s"solver_cgs_maxNumIts = ${ Knowledge.solver_cgs_maxNumIts }", s"solver_cgs_targetResReduction = ${ Knowledge.solver_cgs_targetResReduction }",
+    s"solver_useFAS = ${ Knowledge.solver_useFAS }").mkString("; ")
+
+  /** printed once into setupBuffers, after the operators exist; `stencilNames` = handle names per level, coarsest first */
+  def setup(stencilNames : Seq[String]) : IR_Statement = ExaMG_NativeBlock(
+    s"""{ static const int st_[] = { ${ stencilNames.mkString(", ") } };
+       |  examg_cycle_desc d_; d_.restrict_scale = 1.0; d_.stencils = st_;
+       |  EXAMG_CHECK(${ ExaMG_Symbols.cycleDescFromOptions }("$options", ${ Knowledge.dimensionality }, &d_, NULL));
+       |  examgSolver = ${ ExaMG_Symbols.solverCreate }(${ ExaMG_Context.name }, &d_); if (!examgSolver) examgFail(); }""".stripMargin)
+
+  this += new Transformation("gen_mgCycle@finest", {
+    case fct : IR_LeveledFunction if fct.baseName == "gen_mgCycle" && fct.level == Knowledge.maxLevel =>
+      fct.body = ListBuffer[IR_Statement](ExaMG_NativeBlock(
+        s"EXAMG_CHECK(${ ExaMG_Symbols.solverVCycle }(examgSolver, ${ Knowledge.maxLevel }));"))
+      fct
+  })
+}
+
 /// ExaMG_ResolveHostFunctions
 
 /** timers, printField, external fields: the observable host-side functions keep their names and forward */

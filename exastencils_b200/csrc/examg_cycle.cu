@@ -13,7 +13,9 @@
 // stay valid; examg_apply_bc remains available as its own entry point.
 #include <cmath>
 #include <cstdlib>
+#include <cctype>
 #include <map>
+#include <string>
 
 #include "examg_internal.h"
 
@@ -80,6 +82,8 @@ static int smooth(examg_solver *s, int level, int n) {
   examg_ctx *c = s->c;
   const int A = s->stencils[lv(s, level)], u = s->sol[lv(s, level)], f = s->rhs[lv(s, level)];
   if (s->desc.smoother == EXAMG_SMOOTH_RBGS) return examg_smooth_rbgs(c, A, u, f, s->desc.omega, n);
+  if (s->desc.smoother == EXAMG_SMOOTH_COLORED_2) return examg_smooth_colored(c, A, u, f, s->desc.omega, 2, n);
+  if (s->desc.smoother == EXAMG_SMOOTH_COLORED_3) return examg_smooth_colored(c, A, u, f, s->desc.omega, 3, n);
   return examg_smooth_jacobi(c, A, u, f, s->desc.omega, n);
 }
 
@@ -120,6 +124,9 @@ static int vcycle_rec(examg_solver *s, int level) {
       case EXAMG_CGS_CR:
         return examg_cr_coarse(c, s->stencils[l], s->sol[l], s->rhs[l], s->res[l], s->cgs_tmp, s->desc.cg_max_it,
                                s->desc.cg_rel_tol, nullptr);
+      case EXAMG_CGS_SMOOTHER:  // Jacobi on a two-slot Solution uses Solution<next> as its second buffer
+        return examg_smoother_coarse(c, s->stencils[l], s->sol[l], s->rhs[l], s->res[l], s->desc.smoother, s->desc.omega,
+                                     s->cg_p, s->desc.cg_max_it, s->desc.cg_rel_tol, nullptr);
       case EXAMG_CGS_MINRES:
         return examg_minres_coarse(c, s->stencils[l], s->sol[l], s->rhs[l], s->res[l], s->cgs_tmp, s->desc.cg_max_it,
                                    s->desc.cg_rel_tol, nullptr);
@@ -153,11 +160,114 @@ static int vcycle_rec(examg_solver *s, int level) {
   return smooth(s, level, s->desc.nu_post);
 }
 
+// ---- `generate solver for ... with { ... }` options / solver_* Knowledge keys -> cycle descriptor -------------------
+
+static std::string trim_token(const std::string &t) {
+  size_t a = 0, b = t.size();
+  while (a < b && (isspace((unsigned char)t[a]) || t[a] == '"' || t[a] == '\'')) ++a;
+  while (b > a && (isspace((unsigned char)t[b - 1]) || t[b - 1] == '"' || t[b - 1] == '\'')) --b;
+  return t.substr(a, b - a);
+}
+
+static std::string lower(std::string v) {
+  for (char &ch : v) ch = (char)tolower((unsigned char)ch);
+  return v;
+}
+
 extern "C" {
+
+int examg_cycle_desc_from_options(const char *options, int dim, examg_cycle_desc *d, int *colors_per_dim) {
+  if (!d) return set_error(EXAMG_EINVAL, "examg_cycle_desc_from_options: null descriptor");
+  if (dim != 2 && dim != 3) return set_error(EXAMG_EINVAL, "examg_cycle_desc_from_options: dim %d", dim);
+  // defaults: C/s/e/config/Knowledge.scala:203-262
+  int num_pre = 3, num_post = 3, cgs_max = 512;
+  double damping = 1.0, cgs_tol = 0.001;
+  bool jacobi = false;
+  std::string coloring = "none", cgs = "cg";
+  const std::string text = options ? options : "";
+  size_t pos = 0;
+  while (pos <= text.size()) {
+    size_t end = text.find_first_of("\n;,", pos);
+    if (end == std::string::npos) end = text.size();
+    const std::string item = text.substr(pos, end - pos);
+    pos = end + 1;
+    const size_t eq = item.find('=');
+    if (eq == std::string::npos) {
+      if (!trim_token(item).empty()) return set_error(EXAMG_EINVAL, "examg_cycle_desc_from_options: '%s' is not key = value", trim_token(item).c_str());
+      continue;
+    }
+    const std::string key = trim_token(item.substr(0, eq)), val = trim_token(item.substr(eq + 1)), lval = lower(val);
+    auto as_bool = [&](bool *out) {
+      if (lval == "true") { *out = true; return true; }
+      if (lval == "false") { *out = false; return true; }
+      return false;
+    };
+    char *rest = nullptr;
+    if (key == "solver_smoother_numPre") { num_pre = (int)strtol(val.c_str(), &rest, 10); }
+    else if (key == "solver_smoother_numPost") { num_post = (int)strtol(val.c_str(), &rest, 10); }
+    else if (key == "solver_smoother_damping") { damping = strtod(val.c_str(), &rest); }
+    else if (key == "solver_cgs_maxNumIts") { cgs_max = (int)strtol(val.c_str(), &rest, 10); }
+    else if (key == "solver_cgs_targetResReduction") { cgs_tol = strtod(val.c_str(), &rest); }
+    else if (key == "solver_smoother_jacobiType") { if (!as_bool(&jacobi)) return set_error(EXAMG_EINVAL, "%s = %s: true or false", key.c_str(), val.c_str()); }
+    else if (key == "solver_smoother_coloring") { coloring = lval; }
+    else if (key == "solver_cgs") { cgs = lval; }
+    else if (key == "solver_useFAS") {
+      bool fas = false;
+      if (!as_bool(&fas)) return set_error(EXAMG_EINVAL, "%s = %s: true or false", key.c_str(), val.c_str());
+      if (fas) return set_error(EXAMG_EUNSUP, "solver_useFAS = true: full approximation scheme cycles are not offered (linear problems only)");
+    } else if (key == "solver_cgs_restart") {
+      bool r = false;
+      if (!as_bool(&r) || r) return set_error(EXAMG_EUNSUP, "solver_cgs_restart = %s: restarts of the coarse solver are not offered", val.c_str());
+    } else if (key == "solver_cgs_absResThreshold") {
+      if (strtod(val.c_str(), &rest) != 0.0) return set_error(EXAMG_EUNSUP, "solver_cgs_absResThreshold = %s: only the relative criterion", val.c_str());
+    } else if (key == "solver_targetResReduction" || key == "solver_maxNumIts" || key == "solver_absResThreshold" ||
+               key == "solver_silent" || key == "solver_generateDbgOutputs" || key == "solver_cgs_restartAfter" ||
+               key == "solver_eliminateRHS" || key == "solver_overwriteSolutionFields" || key == "solver_splitLocalSolveLoops") {
+      // outer Solve loop / code-generation details: host side
+    } else {
+      return set_error(EXAMG_EUNSUP, "examg_cycle_desc_from_options: unknown option %s", key.c_str());
+    }
+    if (rest && *rest != '\0') return set_error(EXAMG_EINVAL, "%s = %s: not a number", key.c_str(), val.c_str());
+  }
+  if (num_pre < 0 || num_post < 0 || cgs_max < 1) return set_error(EXAMG_EINVAL, "examg_cycle_desc_from_options: negative sweep or iteration count");
+  int ncol = 0;
+  if (jacobi) {
+    if (coloring != "none") return set_error(EXAMG_EUNSUP, "solver_smoother_jacobiType = true with solver_smoother_coloring = %s", coloring.c_str());
+    d->smoother = EXAMG_SMOOTH_JACOBI;
+  } else if (coloring == "red-black" || coloring == "rb" || coloring == "2-way") {
+    d->smoother = EXAMG_SMOOTH_RBGS;
+  } else if ((coloring == "4-way" && dim == 2) || (coloring == "8-way" && dim == 3)) {
+    d->smoother = EXAMG_SMOOTH_COLORED_2;
+    ncol = 2;
+  } else if ((coloring == "9-way" && dim == 2) || (coloring == "27-way" && dim == 3)) {
+    d->smoother = EXAMG_SMOOTH_COLORED_3;
+    ncol = 3;
+  } else if (coloring == "none") {
+    return set_error(EXAMG_EUNSUP, "solver_smoother_coloring = \"None\" with Gauss-Seidel: a lexicographic sweep depends on the "
+                     "traversal order and the decomposition; choose a colouring or solver_smoother_jacobiType = true");
+  } else {
+    return set_error(EXAMG_EUNSUP, "solver_smoother_coloring = %s in %dD", coloring.c_str(), dim);
+  }
+  if (cgs == "cg") d->coarse_solver = EXAMG_CGS_CG;
+  else if (cgs == "bicgstab") d->coarse_solver = EXAMG_CGS_BICGSTAB;
+  else if (cgs == "conjugateresidual" || cgs == "cr") d->coarse_solver = EXAMG_CGS_CR;
+  else if (cgs == "minres") d->coarse_solver = EXAMG_CGS_MINRES;
+  else if (cgs == "smoother") d->coarse_solver = EXAMG_CGS_SMOOTHER;
+  else return set_error(EXAMG_EUNSUP, "solver_cgs = %s", cgs.c_str());
+  if (d->coarse_solver == EXAMG_CGS_SMOOTHER && ncol != 0)
+    return set_error(EXAMG_EUNSUP, "solver_cgs = \"Smoother\" with an n^d-way colouring");
+  d->omega = damping;
+  d->nu_pre = num_pre;
+  d->nu_post = num_post;
+  d->cg_max_it = cgs_max;
+  d->cg_rel_tol = cgs_tol;
+  if (colors_per_dim) *colors_per_dim = ncol;
+  return EXAMG_OK;
+}
 
 examg_solver *examg_solver_create(examg_ctx *c, const examg_cycle_desc *d) {
   if (!c || !d || !d->stencils) { set_error(EXAMG_EINVAL, "examg_solver_create: null argument"); return nullptr; }
-  if (d->smoother != EXAMG_SMOOTH_JACOBI && d->smoother != EXAMG_SMOOTH_RBGS) {
+  if (d->smoother < EXAMG_SMOOTH_JACOBI || d->smoother > EXAMG_SMOOTH_COLORED_3) {
     set_error(EXAMG_EINVAL, "examg_solver_create: smoother %d", d->smoother);
     return nullptr;
   }
@@ -190,7 +300,7 @@ examg_solver *examg_solver_create(examg_ctx *c, const examg_cycle_desc *d) {
   s->cg_p = examg_field_create(c, "cgTmp0", c->cfg.min_level, 1, 1);
   s->cg_ap = examg_field_create(c, "cgTmp1", c->cfg.min_level, 1, 1);
   if (s->cg_p < 0 || s->cg_ap < 0) { delete s; return nullptr; }
-  if (d->coarse_solver < EXAMG_CGS_CG || d->coarse_solver > EXAMG_CGS_MINRES) {
+  if (d->coarse_solver < EXAMG_CGS_CG || d->coarse_solver > EXAMG_CGS_SMOOTHER) {
     set_error(EXAMG_EINVAL, "examg_solver_create: coarse_solver %d", d->coarse_solver);
     delete s;
     return nullptr;

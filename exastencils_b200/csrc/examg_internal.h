@@ -269,6 +269,8 @@ int launch_cr(examg_ctx *c, const Stencil &s, double *u, const double *rhs, doub
               double rel_tol);
 int launch_minres(examg_ctx *c, const Stencil &s, double *u, const double *rhs, double *res, double *const tmp[7],
                   int max_it, double rel_tol);
+int launch_smoother_solve(examg_ctx *c, const Stencil &s, double *u, const double *rhs, double *res, double *other, int kind,
+                          double omega, int max_it, double rel_tol);
 int launch_bicgstab(examg_ctx *c, const Stencil &s, double *u, const double *rhs, double *res, double *const tmp[5],
                     int max_it, double rel_tol);
 // communicate: `depth` ghost layers (+ the duplicate layer) per side, 1 <= depth <= GHOST

@@ -469,6 +469,40 @@ int examg_bicgstab_coarse(examg_ctx *c, int A, int u, int rhs, int res, const in
   return EXAMG_OK;
 }
 
+int examg_smoother_coarse(examg_ctx *c, int A, int u, int rhs, int res, int smoother, double omega, int tmp, int max_it,
+                          double rel_tol, int *iters_out) {
+  GET_STENCIL(s, A); GET_FIELD(fu, u); GET_FIELD(fr, rhs); GET_FIELD(fres, res);
+  CHECK_LEVEL(fu, s->level); CHECK_LEVEL(fr, s->level); CHECK_LEVEL(fres, s->level);
+  if (fu->loc != 0 || fr->loc != 0 || fres->loc != 0) return set_error(EXAMG_EUNSUP, "examg_smoother_coarse: node-localised fields");
+  if (u == rhs || u == res || rhs == res) return set_error(EXAMG_EINVAL, "examg_smoother_coarse: u, rhs and res must be distinct fields");
+  if (smoother != EXAMG_SMOOTH_JACOBI && smoother != EXAMG_SMOOTH_RBGS) return set_error(EXAMG_EINVAL, "examg_smoother_coarse: smoother %d", smoother);
+  double *other = nullptr;
+  if (smoother == EXAMG_SMOOTH_JACOBI) {
+    // the second buffer: Solution<next> of a two-slot field, else the work field `tmp`
+    if (fu->nslots >= 2) {
+      other = field_ptr(c, fu, (fu->cur + 1) % fu->nslots);
+    } else {
+      Field *ft = get_field(c, tmp);
+      if (!ft || ft->level != s->level || ft->loc != 0 || tmp == u || tmp == rhs || tmp == res)
+        return set_error(EXAMG_EINVAL, "examg_smoother_coarse: Jacobi on a one-slot Solution needs a work field (tmp)");
+      other = field_ptr(c, ft, -1);
+      ft->halo_depth = 0;
+    }
+  } else {
+    for (int k = 0; k < s->nst; ++k)
+      if (k != s->centre && ((s->off[k][0] + s->off[k][1] + s->off[k][2]) & 1) == 0)
+        return set_error(EXAMG_EUNSUP, "examg_smoother_coarse: two colours do not decouple this stencil; use Jacobi");
+  }
+  fu->halo_depth = fres->halo_depth = 0;
+  int rc = launch_smoother_solve(c, *s, field_ptr(c, fu, -1), field_ptr(c, fr, -1), field_ptr(c, fres, -1), other, smoother,
+                                 omega, max_it, rel_tol);
+  if (rc || !iters_out) return rc;
+  EXAMG_CUDA(cudaMemcpyAsync(c->int_host, c->int_out, sizeof(int), cudaMemcpyDeviceToHost, c->stream));
+  EXAMG_SYNC(c);
+  *iters_out = c->int_host[0];
+  return EXAMG_OK;
+}
+
 int examg_cg_coarse(examg_ctx *c, int A, int u, int rhs, int res, int p, int ap, int max_it, double rel_tol,
                     int *iters_out) {
   GET_STENCIL(s, A); GET_FIELD(fu, u); GET_FIELD(fr, rhs); GET_FIELD(fres, res); GET_FIELD(fp, p); GET_FIELD(fap, ap);

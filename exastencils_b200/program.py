@@ -93,7 +93,8 @@ class MultigridProgram:
                  domain_lo=(0.0, 0.0, 0.0), domain_hi=(1.0, 1.0, 1.0), periodic=(0, 0, 0), coarse_solver="cg"):
         assert mode in ("library", "calls")
         assert coarse_solver == "cg" or mode == "library", "the call-by-call mirror spells out the CG of the program text"
-        self.coarse_solver = {"cg": rt.CGS_CG, "bicgstab": rt.CGS_BICGSTAB, "cr": rt.CGS_CR, "minres": rt.CGS_MINRES}[coarse_solver]
+        self.coarse_solver = {"cg": rt.CGS_CG, "bicgstab": rt.CGS_BICGSTAB, "cr": rt.CGS_CR, "minres": rt.CGS_MINRES,
+                              "smoother": rt.CGS_SMOOTHER}[coarse_solver]
         self.dim, self.min_level, self.max_level = dim, min_level, max_level
         self.op, self.order, self.kappa = op, order, kappa
         self.smoother, self.omega, self.nu_pre, self.nu_post = smoother, omega, nu_pre, nu_post
@@ -128,7 +129,8 @@ class MultigridProgram:
                 self.stencil[lvl] = ctx.stencil_const(lvl, offsets, coeffs)
             self._offsets = offsets
         desc = rt.CycleDesc()
-        desc.smoother = rt.SMOOTH_RBGS if smoother == "rbgs" else rt.SMOOTH_JACOBI
+        desc.smoother = {"rbgs": rt.SMOOTH_RBGS, "jacobi": rt.SMOOTH_JACOBI, "colored2": rt.SMOOTH_COLORED_2,
+                         "colored3": rt.SMOOTH_COLORED_3}[smoother]
         desc.omega, desc.nu_pre, desc.nu_post = omega, nu_pre, nu_post
         desc.restrict_scale, desc.cg_max_it, desc.cg_rel_tol = restrict_scale, cg_max_it, cg_rel_tol
         desc.coarse_solver = self.coarse_solver

@@ -21,8 +21,8 @@ MAX_STENCIL = 27
 BC_NONE, BC_DIRICHLET_CONST, BC_DIRICHLET_EXPR, BC_DIRICHLET_HOST = 0, 1, 2, 3
 OP_CONST, OP_X, OP_Y, OP_Z, OP_ADD, OP_SUB, OP_MUL, OP_DIV, OP_NEG = range(9)
 OP_EXP, OP_SIN, OP_COS, OP_SINH, OP_SQRT, OP_COMP = range(9, 15)
-SMOOTH_JACOBI, SMOOTH_RBGS = 0, 1
-CGS_CG, CGS_BICGSTAB, CGS_CR, CGS_MINRES = range(4)
+SMOOTH_JACOBI, SMOOTH_RBGS, SMOOTH_COLORED_2, SMOOTH_COLORED_3 = 0, 1, 2, 3
+CGS_CG, CGS_BICGSTAB, CGS_CR, CGS_MINRES, CGS_SMOOTHER = range(5)
 BC_NEUMANN = 4
 F_SOLUTION, F_RHS, F_RESIDUAL, F_CGTMP0, F_CGTMP1 = range(5)
 
@@ -127,6 +127,8 @@ SIGNATURES = {
     "examg_xpay": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_double, C.c_int, C.c_int]),
     "examg_exchange": (C.c_int, [C.c_void_p, C.c_int, C.c_int]),
     "examg_exchange_depth": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int]),
+    "examg_smoother_coarse": (C.c_int, [C.c_void_p] + [C.c_int] * 5 + [C.c_double, C.c_int, C.c_int, C.c_double, _ip]),
+    "examg_cycle_desc_from_options": (C.c_int, [C.c_char_p, C.c_int, C.c_void_p, _ip]),
     "examg_cg_coarse": (C.c_int, [C.c_void_p] + [C.c_int] * 7 + [C.c_double, _ip]),
     "examg_solver_create": (C.c_void_p, [C.c_void_p, C.POINTER(CycleDesc)]),
     "examg_solver_destroy": (C.c_int, [C.c_void_p]),
@@ -185,6 +187,14 @@ def lib():
         raise ExaMGError("libexamg ABI version mismatch")
     _lib = L
     return L
+
+
+def cycle_desc_from_options(options, dim):
+    """`generate solver ... with { ... }` options / solver_* Knowledge keys -> (CycleDesc, colours per dimension)."""
+    desc, ncol = CycleDesc(), C.c_int()
+    desc.restrict_scale = 1.0
+    check(lib().examg_cycle_desc_from_options(options.encode(), dim, C.byref(desc), C.byref(ncol)))
+    return desc, ncol.value
 
 
 def check(rc):
@@ -452,6 +462,11 @@ class Context:
         return its.value
 
     # -- coupled two-unknown systems on cell fields (optical flow)
+    def smoother_coarse(self, A, u, rhs, res, smoother, omega, max_it, rel_tol, tmp=-1):
+        it = C.c_int()
+        check(self.L.examg_smoother_coarse(self.h, A, u, rhs, res, smoother, omega, tmp, max_it, rel_tol, C.byref(it)))
+        return it.value
+
     def cr_coarse(self, A, u, rhs, res, tmp, max_it, rel_tol):
         """tmp = (p, ap, ar); returns the number of steps."""
         it = C.c_int()

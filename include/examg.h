@@ -270,12 +270,22 @@ int examg_cr_coarse(examg_ctx *ctx, int stencil, int u, int rhs, int res, const 
 int examg_minres_coarse(examg_ctx *ctx, int stencil, int u, int rhs, int res, const int tmp[7], int max_it,
                         double rel_tol, int *iters_out);
 
+/* The smoother as coarse-grid solver (solver_cgs = "Smoother", C/s/e/solver/l3/L3_VankaAsSolverForEquation.scala:31-94):
+ * residual and norm, then up to max_it times { ten smoother steps; residual; norm; stop at rel_tol * initial norm }.
+ * smoother = EXAMG_SMOOTH_JACOBI (second buffer: Solution<next> of a two-slot field, else the work field tmp) or
+ * EXAMG_SMOOTH_RBGS (tmp ignored).  One block, no periodic dimensions.  *iters_out = outer steps (nullable).   */
+int examg_smoother_coarse(examg_ctx *ctx, int stencil, int u, int rhs, int res, int smoother, double omega, int tmp,
+                          int max_it, double rel_tol, int *iters_out);
+
 /* ---- whole cycle: Solve@finest / mgCycle@lvl as one library object -----------
  * (C/s/e/solver/l3/L3_SolverForEquation.scala:259-395).  Creates the field set
  * of the L4 programs on every level (Solution[slots], RHS, Residual and, on the
  * coarsest level, cgTmp0/cgTmp1) and runs the level loop without host
  * round-trips (captured into a CUDA graph).                                  */
-enum { EXAMG_SMOOTH_JACOBI = 0, EXAMG_SMOOTH_RBGS = 1 };
+enum { EXAMG_SMOOTH_JACOBI = 0, EXAMG_SMOOTH_RBGS = 1,
+       /* Gauss-Seidel with an n^dim-way colouring, n = 2 / 3 (examg_smooth_colored): solver_smoother_coloring
+        * "4-way" / "8-way" and "9-way" / "27-way"                                                          */
+       EXAMG_SMOOTH_COLORED_2 = 2, EXAMG_SMOOTH_COLORED_3 = 3 };
 typedef struct {
   int smoother;          /* EXAMG_SMOOTH_*                                       */
   double omega;          /* solver_smoother_damping                              */
@@ -284,9 +294,19 @@ typedef struct {
   int cg_max_it;         /* solver_cgs_maxNumIts                                 */
   double cg_rel_tol;     /* solver_cgs_targetResReduction                        */
   const int *stencils;   /* stencil handle per level, index level - min_level   */
-  int coarse_solver;     /* solver_cgs: EXAMG_CGS_CG (0, the default), _BICGSTAB, _CR, _MINRES   */
+  int coarse_solver;     /* solver_cgs: EXAMG_CGS_CG (0, the default), _BICGSTAB, _CR, _MINRES, _SMOOTHER   */
 } examg_cycle_desc;
-enum { EXAMG_CGS_CG = 0, EXAMG_CGS_BICGSTAB = 1, EXAMG_CGS_CR = 2, EXAMG_CGS_MINRES = 3 };
+enum { EXAMG_CGS_CG = 0, EXAMG_CGS_BICGSTAB = 1, EXAMG_CGS_CR = 2, EXAMG_CGS_MINRES = 3, EXAMG_CGS_SMOOTHER = 4 };
+/* `generate solver for ... with { key = value ... }` / the solver_* keys of a Knowledge file -> cycle descriptor
+ * (C/s/e/solver/l3/L3_SolverForEquation.scala:84-94 sets Knowledge fields from the option list; defaults
+ * C/s/e/config/Knowledge.scala:203-262).  options: "key = value" pairs separated by newlines, ';' or ','; values may be
+ * quoted.  Understood: solver_smoother_numPre / numPost / damping / jacobiType / coloring, solver_cgs,
+ * solver_cgs_maxNumIts, solver_cgs_targetResReduction.  desc->stencils and restrict_scale are left alone.
+ * *colors_per_dim (nullable) = 0 for Jacobi or red-black, 2 / 3 for the n^d-way colourings (desc->smoother is then
+ * EXAMG_SMOOTH_COLORED_2 / _3).  Keys of the outer Solve loop (solver_targetResReduction, solver_maxNumIts, ...) are
+ * accepted and ignored: that loop is host code.  Unknown solver_* keys, solver_useFAS = true, coloring "None" with Gauss-Seidel and
+ * unsupported values are errors (EXAMG_EUNSUP / EXAMG_EINVAL with the offending key in the message).            */
+int examg_cycle_desc_from_options(const char *options, int dim, examg_cycle_desc *desc, int *colors_per_dim);
 typedef struct examg_solver examg_solver;
 examg_solver *examg_solver_create(examg_ctx *ctx, const examg_cycle_desc *desc);
 int examg_solver_destroy(examg_solver *s);

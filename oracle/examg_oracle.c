@@ -545,6 +545,40 @@ int og_cr(const int n[3], const og_stencil *st, const double *sf, double *u, con
   return iters;
 }
 
+/* ---------- the smoother as coarse-grid solver -----------------------------------------------------------------
+ * solver_cgs = "Smoother", C/s/e/solver/l3/L3_VankaAsSolverForEquation.scala:31-94: residual and norm; then up to max_it
+ * times { 10 smoother steps (its numInnerSteps); residual; nextRes = norm; return if nextRes <= rel_tol * initRes }.
+ * kind 0: damped Jacobi (two buffers, `advance` after every step; ten steps leave the active buffer where it was),
+ * kind 1: red-black Gauss-Seidel (colour 0, colour 1).  Returns the number of outer steps done (0: zero residual). */
+int og_smoother_solve(const int n[3], const og_stencil *st, const double *sf, double *u, const double *rhs, double *res,
+                      int kind, double omega, int max_it, double rel_tol) {
+  const size_t size = og_size(n);
+  double *other = NULL;
+  if (kind == 0) { other = (double *)malloc(size * sizeof(double)); memcpy(other, u, size * sizeof(double)); }
+  og_residual(n, st, sf, u, rhs, res);
+  const double initRes = sqrt(og_dot(n, res, res));
+  int iters = 0;
+  if (initRes != 0.0) {
+    for (int step = 0; step < max_it; ++step) {
+      iters = step + 1;
+      for (int in = 0; in < 10; ++in) {
+        if (kind == 0) {
+          if (in % 2 == 0) og_smooth_jacobi(n, st, sf, omega, u, rhs, other);
+          else og_smooth_jacobi(n, st, sf, omega, other, rhs, u);
+        } else {
+          og_smooth_rb(n, st, sf, omega, u, rhs, 0);
+          og_smooth_rb(n, st, sf, omega, u, rhs, 1);
+        }
+      }
+      og_residual(n, st, sf, u, rhs, res);
+      const double nextRes = sqrt(og_dot(n, res, res));
+      if (nextRes <= rel_tol * initRes) break;
+    }
+  }
+  free(other);
+  return iters;
+}
+
 /* ---------- MINRES of the layer-3 generator -------------------------------------------------------------------
  * solver_cgs = "MinRes", C/s/e/solver/l3/L3_MinResForEquation.scala:36-230: statements and start values as generated
  * (vOld = v; v = vNew and pOld = p; p = pNew done by rotating buffers).  Association as in the library. */

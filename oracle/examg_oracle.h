@@ -127,6 +127,11 @@ enum { OG_OP_LAPLACE_SCALED = 0,   /* 2/h^2.., -1/h^2 per level (Benchmark, Exam
 enum { OG_ORDER_BENCH = 0,   /* centre,-x,+x,-y,+y,-z,+z  (Benchmark/Poisson3D, Examples/Poisson) */
        OG_ORDER_TESTING = 1 }; /* centre,+x,-x,+y,-y,+z,-z  (Testing/Smoothers, SISC, Opts)      */
 
+/* solver_cgs = "Smoother" (C/s/e/solver/l3/L3_VankaAsSolverForEquation.scala:31-94): kind 0 Jacobi, 1 red-black GS; ten
+ * smoother steps per residual check; returns the number of outer steps */
+int og_smoother_solve(const int n[3], const og_stencil *st, const double *sf, double *u, const double *rhs, double *res,
+                      int kind, double omega, int max_it, double rel_tol);
+
 typedef struct {
   int dim;              /* 2 or 3 */
   int F[3];             /* global cells per dim at level 0 = blocks*frags*fragLen */

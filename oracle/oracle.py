@@ -85,6 +85,8 @@ def lib():
     L.og_minres.restype = C.c_int
     L.og_bicgstab.argtypes = [i3, stp, dp, dp, dp, dp, C.c_int, C.c_double]
     L.og_bicgstab.restype = C.c_int
+    L.og_smoother_solve.argtypes = [i3, stp, dp, dp, dp, dp, C.c_int, C.c_double, C.c_int, C.c_double]
+    L.og_smoother_solve.restype = C.c_int
     L.og_smooth_color.argtypes = [i3, stp, dp, C.c_double, dp, dp, C.c_int, C.c_int, C.c_int, C.c_int]
     L.og_smooth_color.restype = None
     L.og_cell_apply_bc.argtypes = [C.c_int, i3, dp, C.c_int, C.POINTER(dp)]
@@ -186,6 +188,14 @@ def smooth_color(st, omega, u, rhs, ncol, cx, cy, cz, sf=None):
     """One colour (i % ncol == cx, j % ncol == cy, k % ncol == cz by array index) of the n^dim-way colouring, in place."""
     lib().og_smooth_color(_n(u), C.byref(st), _sf(sf), omega, _dp(u), _dp(rhs), ncol, cx, cy, cz)
     return u
+
+
+def smoother_solve(st, u, rhs, kind, omega, max_it, rel_tol, sf=None):
+    """solver_cgs = "Smoother": in place on u; kind 0 Jacobi, 1 red-black GS; returns (outer steps, residual field)."""
+    res = np.zeros_like(u)
+    it = lib().og_smoother_solve(_n(u), C.byref(st), _sf(sf), _dp(u), _dp(rhs), _dp(res), int(kind), float(omega),
+                                 int(max_it), float(rel_tol))
+    return it, res
 
 
 def conjugate_residual(st, u, rhs, max_it, rel_tol, sf=None):

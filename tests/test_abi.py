@@ -126,3 +126,42 @@ def test_varcoeff27_programs_match_oracle(oracle):
     for comp in range(27):
         assert np.array_equal(comps[comp], want[comp]), comp
     s.close()
+
+
+def test_cycle_desc_from_options(built):
+    """`generate solver for ... with { ... }` options / the solver_* Knowledge keys -> examg_cycle_desc (SURVEY 8f-2;
+    C/s/e/solver/l3/L3_SolverForEquation.scala:84-94, defaults C/s/e/config/Knowledge.scala:203-262).  Pure host code:
+    runs without a GPU."""
+    from exastencils_b200 import runtime as rt
+    d, ncol = rt.cycle_desc_from_options("solver_smoother_coloring = \"red-black\"", 3)   # everything else: defaults
+    assert (d.smoother, d.nu_pre, d.nu_post, d.omega, d.coarse_solver, d.cg_max_it, d.cg_rel_tol, ncol) == \
+           (rt.SMOOTH_RBGS, 3, 3, 1.0, rt.CGS_CG, 512, 0.001, 0)
+    # Examples/lib/solver_singleScalarEquation.exa3-style option block
+    d, ncol = rt.cycle_desc_from_options("""
+        solver_smoother_jacobiType = true
+        solver_smoother_numPre = 2
+        solver_smoother_numPost = 1
+        solver_smoother_damping = 0.8
+        solver_cgs = "BiCGStab"
+        solver_cgs_maxNumIts = 128
+        solver_cgs_targetResReduction = 1e-3
+        solver_targetResReduction = 1e-10
+        solver_maxNumIts = 20
+        solver_silent = true""", 2)
+    assert (d.smoother, d.nu_pre, d.nu_post, d.omega, d.coarse_solver, d.cg_max_it, d.cg_rel_tol) == \
+           (rt.SMOOTH_JACOBI, 2, 1, 0.8, rt.CGS_BICGSTAB, 128, 1e-3)
+    for text, dim, want in [("solver_smoother_coloring = 4-way", 2, (rt.SMOOTH_COLORED_2, 2)),
+                            ("solver_smoother_coloring = '8-way'", 3, (rt.SMOOTH_COLORED_2, 2)),
+                            ("solver_smoother_coloring = 9-way; solver_cgs = MinRes", 2, (rt.SMOOTH_COLORED_3, 3)),
+                            ("solver_smoother_coloring = 27-way, solver_cgs = ConjugateResidual", 3, (rt.SMOOTH_COLORED_3, 3))]:
+        d, ncol = rt.cycle_desc_from_options(text, dim)
+        assert (d.smoother, ncol) == want
+    d, _ = rt.cycle_desc_from_options("solver_smoother_coloring = rb; solver_cgs = Smoother", 3)
+    assert d.coarse_solver == rt.CGS_SMOOTHER
+    for bad, match in [("solver_useFAS = true", "solver_useFAS"), ("solver_smoother_coloring = None", "lexicographic"),
+                       ("solver_smoother_coloring = 4-way", "4-way in 3D"), ("solver_smoother_coloring = rb; solver_cgs = GMRES", "solver_cgs = gmres"),
+                       ("solver_smoother_coloring = rb; solver_bogus = 1", "unknown option solver_bogus"),
+                       ("solver_smoother_coloring = rb; solver_smoother_numPre = two", "not a number"),
+                       ("", "lexicographic")]:
+        with pytest.raises(rt.ExaMGError, match=match):
+            rt.cycle_desc_from_options(bad, 3)

@@ -384,7 +384,7 @@ _RB2D_CASES = [((1, 1), 3), ((3, 5), 4), ((1, 1), 6), ((5, 3), 5), ((1, 1), 9), 
 
 @pytest.mark.parametrize("cells,lvl", _RB2D_CASES)
 @pytest.mark.parametrize("order", ["bench", "testing"])
-def test_rbgs_2d_fused_sweeps(cells, lvl, order, oracle, monkeypatch):
+def test_rbgs_2d_fused_sweeps(cells, lvl, order, oracle, request):
     """2D 5-point constant coefficients (BASELINE config 1): up to three red-black sweeps per launch (k_rb2d<S>,
     examg_fast5.cu).  Solution bit-identical to nu x (colour 0, colour 1) of the oracle for nu = 1..7, on ragged grids,
     9 x 9 (one strip, one segment) up to 1025^2; launches = ceil(nu / 3).  The path is opt-in (EXAMG_FUSED_2D=1: it is
@@ -393,7 +393,7 @@ def test_rbgs_2d_fused_sweeps(cells, lvl, order, oracle, monkeypatch):
     import os, subprocess, sys
     if os.environ.get("EXAMG_FUSED_2D") != "1":
         env = dict(os.environ, EXAMG_FUSED_2D="1")
-        node = "%s::test_rbgs_2d_fused_sweeps[%s-%s-%d]" % (__file__, order, "cells%d" % [c for c, _ in _RB2D_CASES].index(cells), lvl)
+        node = "%s::%s" % (__file__, request.node.name)
         out = subprocess.run([sys.executable, "-m", "pytest", "-x", "-q", "-m", "gpu", node], env=env, capture_output=True,
                              text=True, timeout=600)
         assert out.returncode == 0, out.stdout[-3000:] + out.stderr[-2000:]
@@ -616,6 +616,66 @@ def test_conjugate_residual_coarse(dim, cells, lvl, npts, oracle):
     assert np.array_equal(ctx.download(fu, lvl), e)
     inner = (slice(1, -1),) * 3 if dim == 3 else (slice(None), slice(1, -1), slice(1, -1))
     assert np.array_equal(ctx.download(fr, lvl)[inner], res_ref[inner])
+    ctx.close()
+
+
+@pytest.mark.parametrize("dim,cells,lvl,npts,var", [(2, (4, 4), 2, 5, False), (3, (3, 2, 5), 1, 7, False),
+                                                    (3, (1, 1, 1), 3, 7, True), (3, (1, 1, 1), 2, 27, False)])
+@pytest.mark.parametrize("kind", ["rbgs", "jacobi", "jacobi-tmp"])
+def test_smoother_as_coarse_solver(dim, cells, lvl, npts, var, kind, oracle):
+    """solver_cgs = "Smoother" (C/s/e/solver/l3/L3_VankaAsSolverForEquation.scala:31-94): ten smoother steps per residual
+    check, stop at rel_tol * initRes -- outer step count, Solution and Residual against the oracle, bit for bit; Jacobi
+    with Solution<next> or with a work field as second buffer; red-black refuses stencils it does not decouple."""
+    from exastencils_b200 import runtime as rt
+    og = oracle
+    ctx = _ctx(dim, cells, lvl, lvl)
+    shape = ctx.shape(lvl)
+    offs = _stencil_offsets(dim, npts)
+    centre = offs.index((0, 0, 0))
+    coeffs = np.array([-1.0 / (1 + sum(abs(v) for v in o)) for o in offs])
+    coeffs[centre] = -(np.sum(coeffs) - coeffs[centre]) + 0.5
+    seed = 9900 * lvl + npts + (7 if var else 0)
+    sf = None
+    if var:
+        sf = np.ascontiguousarray(np.broadcast_to(coeffs.reshape((-1,) + (1,) * len(shape)), (len(offs),) + shape) *
+                                  (1.0 + 0.1 * _rand((len(offs),) + shape, seed + 5)))
+        cf = ctx.field_create("coef", lvl, 1, len(offs))
+        ctx.upload(cf, sf)
+        A = ctx.stencil_field(lvl, offs, cf)
+    else:
+        A = ctx.stencil_const(lvl, offs, list(coeffs))
+    st = og.Stencil.make(offs, list(coeffs))
+    two_slots = kind == "jacobi"
+    fu = ctx.field_create("u", lvl, 2 if two_slots else 1)
+    ff, fr, ft = ctx.field_create("rhs", lvl), ctx.field_create("res", lvl), ctx.field_create("tmp", lvl)
+    u, rhs = _rand(shape, seed + 1), _rand(shape, seed + 2)
+    ctx.upload(fu, u, 0)
+    if two_slots:
+        ctx.upload(fu, u, 1)
+    ctx.upload(ft, u)   # the work field carries the boundary values as well
+    ctx.upload(ff, rhs)
+    smoother = rt.SMOOTH_RBGS if kind == "rbgs" else rt.SMOOTH_JACOBI
+    if kind == "rbgs" and npts == 27:
+        with pytest.raises(rt.ExaMGError, match="two colours"):
+            ctx.smoother_coarse(A, fu, ff, fr, smoother, 0.8, 50, 1e-4, tmp=ft)
+        ctx.close()
+        return
+    its = ctx.smoother_coarse(A, fu, ff, fr, smoother, 0.8, 50, 1e-4, tmp=ft)
+    e = u.copy()
+    its_ref, res_ref = og.smoother_solve(st, e, rhs, 1 if kind == "rbgs" else 0, 0.8, 50, 1e-4, sf)
+    assert its == its_ref and 1 <= its < 50
+    assert ctx.field_active_slot(fu) == 0
+    assert np.array_equal(ctx.download(fu, lvl), e)
+    inner = (slice(1, -1),) * 3 if dim == 3 else (slice(None), slice(1, -1), slice(1, -1))
+    assert np.array_equal(ctx.download(fr, lvl)[inner], res_ref[inner])
+    # a zero residual is left alone (gen_curRes == 0 -> return)
+    ctx.upload(ff, np.zeros(shape))
+    z = np.zeros(shape)
+    ctx.upload(fu, z, 0)
+    if two_slots:
+        ctx.upload(fu, z, 1)
+    ctx.upload(ft, z)
+    assert ctx.smoother_coarse(A, fu, ff, fr, smoother, 0.8, 50, 1e-4, tmp=ft) == 0
     ctx.close()
 
 

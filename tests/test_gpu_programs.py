@@ -122,6 +122,55 @@ def test_oracle_parity(prog, override, mode, oracle):
     ref.close()
 
 
+@pytest.mark.parametrize("dim,ncol", [(2, 2), (2, 3), (3, 2), (3, 3)])
+def test_coloured_smoother_in_the_library_cycle(dim, ncol, oracle):
+    """solver_smoother_coloring "4-way" / "9-way" / "8-way" / "27-way" inside the library cycle (EXAMG_SMOOTH_COLORED_n,
+    reached through examg_cycle_desc_from_options): the CUDA-graph cycle equals the same statements issued one by one
+    (examg_smooth_colored, residual, restrict, set, recursion, prolong_add; CG at the bottom) bit for bit, and the
+    pieces are pinned against the oracle by tests/test_gpu_kernels.py."""
+    from exastencils_b200 import MultigridProgram
+    from exastencils_b200 import runtime as rt
+    text = "solver_smoother_coloring = %s; solver_smoother_numPre = 2; solver_smoother_numPost = 1; solver_smoother_damping = 0.9; " \
+           "solver_cgs_maxNumIts = 128" % {(2, 2): "4-way", (2, 3): "9-way", (3, 2): "8-way", (3, 3): "27-way"}[(dim, ncol)]
+    d, nc = rt.cycle_desc_from_options(text, dim)
+    assert nc == ncol and d.smoother == (rt.SMOOTH_COLORED_2 if ncol == 2 else rt.SMOOTH_COLORED_3)
+    lo, hi = 1, 5 if dim == 2 else 4
+    kw = dict(op="scaled", order="bench", smoother="colored%d" % ncol, omega=d.omega, nu_pre=d.nu_pre, nu_post=d.nu_post,
+              cg_max_it=d.cg_max_it, cg_rel_tol=d.cg_rel_tol)
+    progs = [MultigridProgram(dim, (1,) * dim, lo, hi, **kw) for _ in range(2)]
+    rng = np.random.default_rng(31 * dim + ncol)
+    u0, f0 = rng.uniform(-1.0, 1.0, size=progs[0].ctx.shape(hi)), rng.uniform(-1.0, 1.0, size=progs[0].ctx.shape(hi))
+    for p in progs:
+        p.solution(hi)[...] = u0
+        p.rhs(hi)[...] = f0
+        p.commit()
+    lib, man = progs
+    ctx = man.ctx
+
+    def cycle(lvl):
+        A, u, f, r = man.stencil[lvl], man.f_solution[lvl], man.f_rhs[lvl], man.f_residual[lvl]
+        if lvl == lo:
+            ctx.cg_coarse(A, u, f, r, man.f_cgtmp0, man.f_cgtmp1, d.cg_max_it, d.cg_rel_tol, want_iters=False)
+            return
+        ctx.smooth_colored(A, u, f, d.omega, ncol, d.nu_pre)
+        ctx.residual(A, u, f, r)
+        ctx.restrict(r, man.f_rhs[lvl - 1], 1.0)
+        ctx.set(man.f_solution[lvl - 1], 0.0)
+        cycle(lvl - 1)
+        ctx.prolong_add(man.f_solution[lvl - 1], u)
+        ctx.smooth_colored(A, u, f, d.omega, ncol, d.nu_post)
+
+    h = [lib.update_residual_norm()]
+    for _ in range(3):
+        lib.vcycle()
+        cycle(hi)
+        h.append(lib.update_residual_norm())
+        assert np.array_equal(lib.fetch_solution(), man.fetch_solution())
+    assert h[-1] < 0.05 * h[0]
+    for p in progs:
+        p.close()
+
+
 def test_binary_field_io_and_benchmark_markers(tmp_path):
     """writeField / readField in binary mode (raw doubles, [comp][z][y][x], no ghost layers; rank-ordered append for
     several blocks) and benchmarkStart / benchmarkStop (NVTX range + device timer of the same name)."""
@@ -292,7 +341,7 @@ def test_print_field(tmp_path):
     ctx.close()
 
 
-@pytest.mark.parametrize("cgs", ["bicgstab", "cr", "minres"])
+@pytest.mark.parametrize("cgs", ["bicgstab", "cr", "minres", "smoother"])
 def test_coarse_solver_choice(cgs, oracle):
     """solver_cgs of the layer-3 generator inside the library cycle (examg_cycle_desc.coarse_solver): on the SPD Poisson
     operator every coarse solver reaches the same 1e-3 coarse reduction, so the V-cycle history stays that of the CG

@@ -45,7 +45,7 @@ def test_symbol_table_matches_header():
     # every loop-shaped / per-statement entry point of the header has to be reachable from the generator
     hot = {s for s in header if re.match(
         r"examg_(apply|residual|residual_restrict|smooth_\w+|restrict\w*|prolong_add\w*|dot|max_abs_diff|set|copy|axpy|xpay|"
-        r"exchange|apply_bc|cg_coarse|bicgstab_coarse|cr_coarse|minres_coarse|system2_\w+|field_(create\w*|set_bc\w*|eval|"
+        r"exchange|apply_bc|cg_coarse|bicgstab_coarse|cr_coarse|minres_coarse|smoother_coarse|cycle_desc_from_options|system2_\w+|field_(create\w*|set_bc\w*|eval|"
         r"advance|upload|download|print|write|read|fill)|stencil_\w+|init|finalize|comm_(export|import|blob_size)|timer_(start|stop|print_all)|benchmark_(start|stop))$", s)}
     assert not (hot - table), "hot-path entry points the back-end never prints: %s" % sorted(hot - table)
 
