@@ -33,6 +33,7 @@ object ExaMG_Symbols {
   val fieldSetBCExpr = "examg_field_set_bc_expr"
   val fieldSetBCFace = "examg_field_set_bc_face"
   val fieldEval = "examg_field_eval"
+  val loopEval = "examg_loop_eval"
   val fieldFill = "examg_field_fill"
   val fieldUpload = "examg_field_upload"
   val fieldDownload = "examg_field_download"

@@ -140,9 +140,14 @@ object ExaMG_Patterns {
 
   /** Lowers an expression over vf_nodePosition / vf_boundaryPosition, constants and the L4 math functions to the
     * postfix program of examg_field_set_bc_expr / examg_field_eval; None if something else occurs in it. */
-  def toPostfix(e : IR_Expression) : Option[ListBuffer[(String, Double)]] = {
+  def toPostfix(e : IR_Expression, fields : Option[ListBuffer[IR_FieldLikeAccess]] = None) : Option[ListBuffer[(String, Double)]] = {
     val prog = ListBuffer[(String, Double)]()
     def emit(x : IR_Expression) : Boolean = x match {
+      // examg_loop_eval: a field read at the loop's own point becomes EXAMG_OP_FIELD <index into the source list>
+      case fa : IR_FieldLikeAccess if fields.isDefined && isCentered(fa) =>
+        val known = fields.get.indexWhere(o => o.field == fa.field && o.slot == fa.slot)
+        val idx = if (known >= 0) known else { fields.get += fa; fields.get.length - 1 }
+        prog += (("EXAMG_OP_FIELD", idx.toDouble)); idx < 8
       case IR_RealConstant(v)                                            => prog += (("EXAMG_OP_CONST", v)); true
       case IR_IntegerConstant(v)                                         => prog += (("EXAMG_OP_CONST", v.toDouble)); true
       case va : exastencils.grid.ir.IR_VirtualFieldAccess

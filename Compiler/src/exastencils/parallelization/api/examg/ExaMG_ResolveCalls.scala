@@ -133,7 +133,13 @@ object ExaMG_ResolveCalls extends DefaultStrategy("Lower loops of the multigrid 
       Some(ExaMG_Call(restrict, handle(c.u), handle(dst), scale)) // `4.0 * ( Restriction * Residual )`
     case _                                                                                                                       =>
       // initialisation loops F = <expr>(vf_nodePosition): lowered to the postfix program of examg_field_eval
-      toPostfix(src).map(prog => ExaMG_FieldEval(handle(dst), slotOf(dst), 0, prog))
+      toPostfix(src).map(prog => ExaMG_FieldEval(handle(dst), slotOf(dst), 0, prog) : IR_Statement).orElse {
+        // any other pointwise expression over fields of the level read at the loop's own point (the nonlinear terms of
+        // Testing/NonLinear/FAS_2D_Basic.exa4 once `Laplace * Solution` sits in a work field): examg_loop_eval
+        val srcs = ListBuffer[IR_FieldLikeAccess]()
+        toPostfix(src, Some(srcs)).filter(_ => srcs.forall(_.field.level == dst.field.level))
+          .map(prog => ExaMG_LoopEval(handle(dst), slotOf(dst), srcs.map(handle), srcs.map(slotOf), prog))
+      }
   }
 
   this += new Transformation("Loops over points", {
@@ -202,6 +208,19 @@ case class ExaMG_FieldEval(var field : IR_Expression, var slot : IR_Expression, 
     out << prog.map(p => s"{ ${ p._1 }, ${ java.lang.Double.toString(p._2) } }").mkString(", ")
     out << " }; "
     out << ExaMG_Call(ExaMG_Symbols.fieldEval, field, slot, IR_IntegerConstant(comp), IR_VariableAccess("prog_", IR_IntegerDatatype), IR_IntegerConstant(prog.length)) << " }"
+  }
+}
+
+/** examg_loop_eval: destination, source handles / slots and the program as static arrays */
+case class ExaMG_LoopEval(var field : IR_Expression, var slot : IR_Expression, var srcs : ListBuffer[IR_Expression],
+    var srcSlots : ListBuffer[IR_Expression], var prog : ListBuffer[(String, Double)]) extends IR_Statement {
+  override def prettyprint(out : exastencils.prettyprinting.PpStream) : Unit = {
+    out << "{ static const examg_bc_op prog_[] = { "
+    out << prog.map(p => s"{ ${ p._1 }, ${ java.lang.Double.toString(p._2) } }").mkString(", ")
+    out << " }; const int src_[] = { " <<< (srcs, ", ") << " }, slot_[] = { " <<< (srcSlots, ", ") << " }; "
+    out << ExaMG_Call(ExaMG_Symbols.loopEval, field, slot, IR_VariableAccess("src_", IR_IntegerDatatype),
+      IR_VariableAccess("slot_", IR_IntegerDatatype), IR_IntegerConstant(srcs.length), IR_VariableAccess("prog_", IR_IntegerDatatype),
+      IR_IntegerConstant(prog.length)) << " }"
   }
 }
 

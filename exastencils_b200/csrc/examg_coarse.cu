@@ -218,7 +218,7 @@ int coarse_cycle_top(examg_ctx *c, const examg_cycle_desc &d, const int *stencil
   static const bool off = !(getenv("EXAMG_COARSE_FUSE") && getenv("EXAMG_COARSE_FUSE")[0] == '1');
   const int lo = c->cfg.min_level;
   if (off || c->world > 1 || c->periodic_any) return lo - 1;
-  if (d.coarse_solver != EXAMG_CGS_CG || d.smoother > EXAMG_SMOOTH_RBGS) return lo - 1;  // k_coarse_cycle ends in CG; BiCGStab / CR / MinRes run as graph nodes
+  if (d.coarse_solver != EXAMG_CGS_CG || d.smoother > EXAMG_SMOOTH_RBGS || d.use_fas) return lo - 1;  // k_coarse_cycle ends in CG; BiCGStab / CR / MinRes run as graph nodes
   int top = lo - 1;
   for (int lvl = lo; lvl <= max_top && lvl - lo < CMAXL; ++lvl) {
     const Stencil &s = c->stencils[stencils[lvl - lo]];

@@ -456,7 +456,7 @@ int examg_field_set_bc(examg_ctx *c, int h, int kind, double value) {
 }
 
 // validates a postfix program on the host so the device never has to; ncomp > 0 allows EXAMG_OP_COMP
-static int check_program(const char *who, const examg_bc_op *prog, int n, int ncomp) {
+static int check_program(const char *who, const examg_bc_op *prog, int n, int ncomp, int nsrc = 0) {
   if (!prog || n < 1 || n > 64) return set_error(EXAMG_EINVAL, "%s: 1..64 ops", who);
   int depth = 0;
   for (int i = 0; i < n; ++i) {
@@ -464,6 +464,10 @@ static int check_program(const char *who, const examg_bc_op *prog, int n, int nc
       case EXAMG_OP_COMP:
         if (ncomp <= 0 || prog[i].value < 0 || prog[i].value >= ncomp || prog[i].value != (int)prog[i].value)
           return set_error(EXAMG_EINVAL, "%s: op %d reads component %g of %d", who, i, prog[i].value, ncomp);
+        ++depth; break;
+      case EXAMG_OP_FIELD:
+        if (prog[i].value < 0 || prog[i].value >= nsrc || prog[i].value != (int)prog[i].value)
+          return set_error(EXAMG_EINVAL, "%s: op %d reads source field %g of %d", who, i, prog[i].value, nsrc);
         ++depth; break;
       case EXAMG_OP_CONST: case EXAMG_OP_X: case EXAMG_OP_Y: case EXAMG_OP_Z: ++depth; break;
       case EXAMG_OP_ADD: case EXAMG_OP_SUB: case EXAMG_OP_MUL: case EXAMG_OP_DIV:
@@ -526,6 +530,30 @@ int examg_field_eval(examg_ctx *c, int h, int slot, int comp, const examg_bc_op 
     f->eval_gen++;
   }
   return EXAMG_OK;
+}
+
+int examg_loop_eval(examg_ctx *c, int dst, int dst_slot, const int *src, const int *src_slot, int nsrc,
+                    const examg_bc_op *prog, int n) {
+  Field *fd = get_field(c, dst);
+  if (!fd) return set_error(EXAMG_EINVAL, "bad field %d", dst);
+  if (dst_slot >= fd->nslots) return set_error(EXAMG_EINVAL, "examg_loop_eval: slot %d of %d", dst_slot, fd->nslots);
+  if (fd->loc != 0 || fd->ncomp != 1) return set_error(EXAMG_EUNSUP, "examg_loop_eval: node-localised scalar fields");
+  if (nsrc < 0 || nsrc > 8 || (nsrc > 0 && !src)) return set_error(EXAMG_EINVAL, "examg_loop_eval: 0..8 source fields");
+  const double *ptr[8] = {nullptr};
+  for (int k = 0; k < nsrc; ++k) {
+    Field *fs = get_field(c, src[k]);
+    if (!fs) return set_error(EXAMG_EINVAL, "bad field %d", src[k]);
+    const int sl = src_slot ? src_slot[k] : -1;
+    if (sl >= fs->nslots) return set_error(EXAMG_EINVAL, "examg_loop_eval: source %d: slot %d of %d", k, sl, fs->nslots);
+    if (fs->level != fd->level || fs->loc != 0 || fs->ncomp != 1)
+      return set_error(EXAMG_EINVAL, "examg_loop_eval: source %d is not a node-localised scalar field of level %d", k, fd->level);
+    ptr[k] = field_ptr(c, fs, sl);
+  }
+  int rc = check_program("examg_loop_eval", prog, n, 0, nsrc);
+  if (rc) return rc;
+  fd->halo_depth = 0;
+  if (dst_slot <= 0 || fd->nslots == 1) { fd->evals.clear(); fd->eval_gen++; }
+  return launch_loop_eval(c, fd->level, ptr, nsrc, field_ptr(c, fd, dst_slot), prog, n);
 }
 
 int examg_field_set_bc_face(examg_ctx *c, int h, int face, int kind, double value, const examg_bc_op *prog, int n) {

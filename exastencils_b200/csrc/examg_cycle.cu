@@ -26,6 +26,7 @@ struct examg_solver {
   examg_cycle_desc desc;
   std::vector<int> stencils;          // per level
   std::vector<int> sol, rhs, res;     // field handles per level
+  std::vector<int> approx;            // gen_approx_* per level (solver_useFAS; -1 on the finest)
   int cg_p = -1, cg_ap = -1;
   int cgs_tmp[7] = {-1, -1, -1, -1, -1, -1, -1};  // work fields of the other coarse solvers (solver_cgs)
   int coarse_top = -1;                // mgCycle@level for level <= coarse_top is one single-CTA kernel
@@ -139,6 +140,22 @@ static int vcycle_rec(examg_solver *s, int level) {
                                s->cg_p, s->cg_ap);
   int rc;
   if ((rc = smooth(s, level, s->desc.nu_pre))) return rc;
+  if (s->desc.use_fas) {
+    // Full approximation scheme (C/s/e/solver/l3/L3_SolverForEquation.scala:401-452): the coarse level carries the
+    // restricted approximation instead of starting from zero, its right-hand side gains A@coarser * approximation and
+    // only the difference is interpolated back.  Residual@coarser is the scratch of A * approximation.
+    if ((rc = residual_op(c, s->stencils[l], s->sol[l], -1, s->rhs[l], s->res[l], nullptr, 1))) return rc;
+    if ((rc = examg_restrict(c, s->res[l], s->rhs[l - 1], s->desc.restrict_scale))) return rc;
+    if ((rc = examg_exchange(c, s->sol[l], -1))) return rc;
+    if ((rc = examg_restrict(c, s->sol[l], s->approx[l - 1], 1.0))) return rc;
+    if ((rc = examg_copy(c, s->approx[l - 1], -1, s->sol[l - 1], -1))) return rc;
+    if ((rc = examg_apply(c, s->stencils[l - 1], s->sol[l - 1], -1, s->res[l - 1]))) return rc;
+    if ((rc = examg_axpy(c, 1.0, s->res[l - 1], -1, s->rhs[l - 1], -1))) return rc;
+    if ((rc = vcycle_rec(s, level - 1))) return rc;
+    if ((rc = examg_axpy(c, -1.0, s->approx[l - 1], -1, s->sol[l - 1], -1))) return rc;
+    if ((rc = examg_prolong_add(c, s->sol[l - 1], -1, s->sol[l], -1))) return rc;
+    return smooth(s, level, s->desc.nu_post);
+  }
   // several blocks: the residual of the first ghost layer is computed here too, so the restriction needs no exchange
   // (on large 3D constant-coefficient levels residual and restriction are one pass and Residual is not materialised)
   rc = residual_restrict_op(c, s->stencils[l], s->sol[l], s->rhs[l], s->rhs[l - 1], s->desc.restrict_scale);
@@ -182,7 +199,7 @@ int examg_cycle_desc_from_options(const char *options, int dim, examg_cycle_desc
   // defaults: C/s/e/config/Knowledge.scala:203-262
   int num_pre = 3, num_post = 3, cgs_max = 512;
   double damping = 1.0, cgs_tol = 0.001;
-  bool jacobi = false;
+  bool jacobi = false, use_fas = false;
   std::string coloring = "none", cgs = "cg";
   const std::string text = options ? options : "";
   size_t pos = 0;
@@ -214,7 +231,7 @@ int examg_cycle_desc_from_options(const char *options, int dim, examg_cycle_desc
     else if (key == "solver_useFAS") {
       bool fas = false;
       if (!as_bool(&fas)) return set_error(EXAMG_EINVAL, "%s = %s: true or false", key.c_str(), val.c_str());
-      if (fas) return set_error(EXAMG_EUNSUP, "solver_useFAS = true: full approximation scheme cycles are not offered (linear problems only)");
+      use_fas = fas;
     } else if (key == "solver_cgs_restart") {
       bool r = false;
       if (!as_bool(&r) || r) return set_error(EXAMG_EUNSUP, "solver_cgs_restart = %s: restarts of the coarse solver are not offered", val.c_str());
@@ -261,6 +278,7 @@ int examg_cycle_desc_from_options(const char *options, int dim, examg_cycle_desc
   d->nu_post = num_post;
   d->cg_max_it = cgs_max;
   d->cg_rel_tol = cgs_tol;
+  d->use_fas = use_fas ? 1 : 0;
   if (colors_per_dim) *colors_per_dim = ncol;
   return EXAMG_OK;
 }
@@ -296,6 +314,17 @@ examg_solver *examg_solver_create(examg_ctx *c, const examg_cycle_desc *d) {
     examg_field_set_bc(c, u, EXAMG_BC_DIRICHLET_CONST, 0.0);
     examg_field_set_bc(c, r, EXAMG_BC_DIRICHLET_CONST, 0.0);
     s->sol.push_back(u); s->rhs.push_back(f); s->res.push_back(r);
+    int a = -1;
+    if (d->use_fas && level != c->cfg.max_level) {
+      if ((a = examg_field_create(c, "Approximation", level, 1, 1)) < 0) { delete s; return nullptr; }
+      examg_field_set_bc(c, a, EXAMG_BC_DIRICHLET_CONST, 0.0);
+    }
+    s->approx.push_back(a);
+  }
+  if (d->use_fas && c->world > 1) {
+    set_error(EXAMG_EUNSUP, "examg_solver_create: solver_useFAS on several blocks (the agglomerated levels start from zero)");
+    delete s;
+    return nullptr;
   }
   s->cg_p = examg_field_create(c, "cgTmp0", c->cfg.min_level, 1, 1);
   s->cg_ap = examg_field_create(c, "cgTmp1", c->cfg.min_level, 1, 1);
@@ -414,6 +443,7 @@ int examg_solver_field(examg_solver *s, int level, int which) {
     case EXAMG_F_RESIDUAL: return s->res[lv(s, level)];
     case EXAMG_F_CGTMP0: if (level == c->cfg.min_level) return s->cg_p; break;
     case EXAMG_F_CGTMP1: if (level == c->cfg.min_level) return s->cg_ap; break;
+    case EXAMG_F_APPROX: if (s->desc.use_fas && level != c->cfg.max_level) return s->approx[lv(s, level)]; break;
   }
   return set_error(EXAMG_EINVAL, "examg_solver_field: no field %d on level %d", which, level);
 }

@@ -165,21 +165,30 @@ static int stencil_order5(const Stencil &s) {
 constexpr int FUSED2D_MIN_N = 9;
 
 bool fused_rb2d_usable(examg_ctx *c, const Stencil &s, const Field &fu) {
-  // Opt-in (EXAMG_FUSED_2D=1).  Measured on B200 (profiles/r02_notes.md): at 1025^2 the whole hierarchy lives in L2 and
-  // a V(3,3) cycle is launch-latency bound; the fused kernel turns 12 smoother launches per level into 2, but a launch
-  // then is one warp's march through ~18-40 fully unrolled steps (straight-line code of ~2700 instructions that every
-  // warp fetches once: instruction-fetch and FP64-latency bound, 11-32 us per launch), so the cycle takes 0.294 ms
-  // against 0.285 ms with the generic colour kernels (2.2 us per graph node).  Bit-identical either way.
-  static const bool off = env_flag5("EXAMG_NO_FUSED", 0) != 0 || env_flag5("EXAMG_FUSED_2D", 0) == 0;
+  // Used where a level exceeds L2 (>= 2^22 nodes: 32 MB per field), i.e. where the sweep is HBM-bound: there three sweeps
+  // per pass are worth 2-3x (tools/matrix_bench.py at 8193^2: 0.49 of the one-pass-per-sweep roofline with one launch per
+  // colour).  On L2-resident levels a V(3,3) cycle is launch-latency bound and the fused kernel -- one warp's march
+  // through ~18-40 fully unrolled steps per launch, 11-32 us -- is not faster than the generic colour kernels (0.294
+  // against 0.285 ms per cycle at 1025^2, profiles/r02_notes.md): there it is opt-in (EXAMG_FUSED_2D=1; =0 switches
+  // it off everywhere).  Bit-identical either way.
+  static const int mode = env_flag5("EXAMG_NO_FUSED", 0) != 0 ? 0 : env_flag5("EXAMG_FUSED_2D", -1);
+  const bool off = mode == 0;
   if (off || c->cfg.dim != 2 || fu.ncomp != 1 || fu.loc != 0 || stencil_order5(s) < 0) return false;
   if (c->world > 1 || c->periodic_any) return false;  // several blocks / periodic dimensions: generic kernels
   const LevelGeom &g = *geom(c, s.level);
+  if (mode < 0 && (long long)g.n[0] * g.n[1] < (1LL << 22)) return false;
   return g.n[0] >= FUSED2D_MIN_N && g.n[1] >= FUSED2D_MIN_N;
 }
 
-// sweeps the next launch will fuse (1..3)
+// sweeps the next launch will fuse (1..3).  On HBM-sized levels two per launch are best (8193^2: 0.283 / 0.268 / 0.307 ms
+// per sweep for one / two / three per launch -- the kernel's time grows with the sweeps it fuses, it is bound by its
+// dependent FP64 chains, not by HBM any more); on L2-resident levels (opt-in) launches count: three.
 int rb2d_fused_plan(int nsweeps) {
-  static const int m = [] { int v = env_flag5("EXAMG_FUSE_SWEEPS_2D", 3); return v < 1 ? 1 : v > 3 ? 3 : v; }();
+  static const int m = [] {
+    const int dflt = env_flag5("EXAMG_FUSED_2D", -1) > 0 ? 3 : 2;
+    int v = env_flag5("EXAMG_FUSE_SWEEPS_2D", dflt);
+    return v < 1 ? 1 : v > 3 ? 3 : v;
+  }();
   return nsweeps < m ? nsweeps : m;
 }
 

@@ -261,6 +261,8 @@ enum { STREAM_SET = 0, STREAM_COPY = 1, STREAM_AXPY = 2, STREAM_XPAY = 3 };
 int launch_stream_op(examg_ctx *c, int level, int op, double alpha, const double *x, double *y);
 int launch_bc(examg_ctx *c, const Field &f, int slot);
 int launch_field_eval(examg_ctx *c, const Field &f, int slot, int comp, const examg_bc_op *prog, int n);
+int launch_loop_eval(examg_ctx *c, int level, const double *const *src, int nsrc, double *dst, const examg_bc_op *prog,
+                     int n);
 int launch_bc_cell(examg_ctx *c, const Field &f, int slot);  // 2D Neumann ghost cells incl. corners (examg_optflow.cu)
 int launch_bc_cell_generic(examg_ctx *c, const Field &f, int slot);  // Dirichlet / Neumann faces, 2D and 3D
 int launch_cg(examg_ctx *c, const Stencil &s, double *u, const double *rhs, double *res, double *p,

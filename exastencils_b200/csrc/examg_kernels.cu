@@ -175,14 +175,17 @@ struct BcProg {
 };
 
 // comp0 / vol: component 0 of the field being written at this node and the component stride (EXAMG_OP_COMP)
+// fsrc / p: the source fields of examg_loop_eval at this node (EXAMG_OP_FIELD)
 __device__ __forceinline__ double bc_eval(const BcProg &pr, double x, double y, double z,
-                                          const double *comp0 = nullptr, long long vol = 0) {
+                                          const double *comp0 = nullptr, long long vol = 0,
+                                          const double *const *fsrc = nullptr, long long p = 0) {
   double stk[16];
   int sp = 0;
   for (int q = 0; q < pr.n; ++q) {
     switch (pr.op[q]) {
       case EXAMG_OP_CONST: stk[sp++] = pr.val[q]; break;
       case EXAMG_OP_COMP: stk[sp++] = comp0[(long long)pr.val[q] * vol]; break;
+      case EXAMG_OP_FIELD: stk[sp++] = fsrc[(int)pr.val[q]][p]; break;
       case EXAMG_OP_EXP: stk[sp - 1] = exp(stk[sp - 1]); break;
       case EXAMG_OP_SIN: stk[sp - 1] = sin(stk[sp - 1]); break;
       case EXAMG_OP_COS: stk[sp - 1] = cos(stk[sp - 1]); break;
@@ -291,6 +294,28 @@ k_field_eval(const BcArgs a, const __grid_constant__ BcProg pr, double *f0, long
     const double z = a.dim == 3 ? (double)(a.goff[2] + k) * a.h[2] + a.x0[2] : 0.0;
     const long long p = i + (long long)a.pitch * j + a.plane * k;
     f0[(long long)comp * vol + p] = bc_eval(pr, x, y, z, f0 + p, vol);
+  }
+}
+
+// loop over F { F = <expr>(vf_nodePosition, G_0 .. G_7 at the same node) } on F's loop points (examg_loop_eval)
+struct EvalSrc {
+  const double *p[8];
+};
+
+__global__ void __launch_bounds__(256)
+k_loop_eval(const GridArgs g, const BcArgs a, const __grid_constant__ BcProg pr, const EvalSrc src, double *dst, int kz) {
+  const int i = g.lo[0] + blockIdx.x * blockDim.x + threadIdx.x;
+  const int z0 = g.lo[2] + blockIdx.z * kz;
+  const int z1 = min(z0 + kz, g.hi[2]);
+  if (i >= g.hi[0]) return;
+  const double x = (double)(a.goff[0] + i) * a.h[0] + a.x0[0];
+  for (int j = g.lo[1] + blockIdx.y * blockDim.y + threadIdx.y; j < g.hi[1]; j += gridDim.y * blockDim.y) {
+    const double y = (double)(a.goff[1] + j) * a.h[1] + a.x0[1];
+    for (int k = z0; k < z1; ++k) {
+      const double z = a.dim == 3 ? (double)(a.goff[2] + k) * a.h[2] + a.x0[2] : 0.0;
+      const long long p = i + (long long)g.pitch * j + g.plane * k;
+      dst[p] = bc_eval(pr, x, y, z, nullptr, 0, src.p, p);
+    }
   }
 }
 
@@ -479,6 +504,34 @@ int launch_field_eval(examg_ctx *c, const Field &f, int slot, int comp, const ex
   long long blocks = (total + 255) / 256;
   if (blocks > 148 * 16) blocks = 148 * 16;
   k_field_eval<<<(int)blocks, 256, 0, c->stream>>>(a, pr, field_ptr(c, &f, slot, 0), g.vol, comp);
+  EXAMG_LAUNCH_CHECK(c);
+  return EXAMG_OK;
+}
+
+int launch_loop_eval(examg_ctx *c, int level, const double *const *src, int nsrc, double *dst, const examg_bc_op *prog,
+                     int n) {
+  const LevelGeom &g = *geom(c, level);
+  const GridArgs ga = grid_args_loc(c, g);
+  const int ex = ga.hi[0] - ga.lo[0], ey = ga.hi[1] - ga.lo[1], ez = ga.hi[2] - ga.lo[2];
+  if (ex <= 0 || ey <= 0 || ez <= 0) return EXAMG_OK;
+  BcArgs a;
+  for (int d = 0; d < 3; ++d) {
+    a.n[d] = g.n[d];
+    a.goff[d] = g.goff[d];
+    a.h[d] = g.h[d];
+    a.x0[d] = d < c->cfg.dim ? c->cfg.domain_lo[d] : 0.0;
+  }
+  a.pitch = g.pitch;
+  a.plane = g.plane;
+  a.face_mask = 0;
+  a.dim = c->cfg.dim;
+  BcProg pr;
+  pr.n = n;
+  for (int q = 0; q < n; ++q) { pr.op[q] = prog[q].op; pr.val[q] = prog[q].value; }
+  EvalSrc es;
+  for (int k = 0; k < 8; ++k) es.p[k] = k < nsrc ? src[k] : nullptr;
+  const Shape sh = make_shape(ex, ey, ez);
+  k_loop_eval<<<sh.grid, sh.block, 0, c->stream>>>(ga, a, pr, es, dst, sh.kz);
   EXAMG_LAUNCH_CHECK(c);
   return EXAMG_OK;
 }

@@ -90,8 +90,9 @@ class MultigridProgram:
     def __init__(self, dim, block_cells, min_level, max_level, op="scaled", order="bench", kappa=0.0,
                  smoother="rbgs", omega=0.8, nu_pre=3, nu_post=3, restrict_scale=1.0, cg_max_it=128,
                  cg_rel_tol=1e-3, num_blocks=(1, 1, 1), rank=0, device=0, mode="library", stream=None,
-                 domain_lo=(0.0, 0.0, 0.0), domain_hi=(1.0, 1.0, 1.0), periodic=(0, 0, 0), coarse_solver="cg"):
+                 domain_lo=(0.0, 0.0, 0.0), domain_hi=(1.0, 1.0, 1.0), periodic=(0, 0, 0), coarse_solver="cg", use_fas=False):
         assert mode in ("library", "calls")
+        assert not use_fas or mode == "library", "solver_useFAS: the library cycle"
         assert coarse_solver == "cg" or mode == "library", "the call-by-call mirror spells out the CG of the program text"
         self.coarse_solver = {"cg": rt.CGS_CG, "bicgstab": rt.CGS_BICGSTAB, "cr": rt.CGS_CR, "minres": rt.CGS_MINRES,
                               "smoother": rt.CGS_SMOOTHER}[coarse_solver]
@@ -134,6 +135,7 @@ class MultigridProgram:
         desc.omega, desc.nu_pre, desc.nu_post = omega, nu_pre, nu_post
         desc.restrict_scale, desc.cg_max_it, desc.cg_rel_tol = restrict_scale, cg_max_it, cg_rel_tol
         desc.coarse_solver = self.coarse_solver
+        desc.use_fas = 1 if use_fas else 0
         arr = (C.c_int * len(self.levels))(*[self.stencil[l] for l in self.levels])
         desc.stencils = C.cast(arr, C.POINTER(C.c_int))
         self._solver = ctx.L.examg_solver_create(ctx.h, C.byref(desc))

@@ -20,11 +20,11 @@ HEADER_PATH = os.path.join(os.path.dirname(_PKG), "include", "examg.h")
 MAX_STENCIL = 27
 BC_NONE, BC_DIRICHLET_CONST, BC_DIRICHLET_EXPR, BC_DIRICHLET_HOST = 0, 1, 2, 3
 OP_CONST, OP_X, OP_Y, OP_Z, OP_ADD, OP_SUB, OP_MUL, OP_DIV, OP_NEG = range(9)
-OP_EXP, OP_SIN, OP_COS, OP_SINH, OP_SQRT, OP_COMP = range(9, 15)
+OP_EXP, OP_SIN, OP_COS, OP_SINH, OP_SQRT, OP_COMP, OP_FIELD = range(9, 16)
 SMOOTH_JACOBI, SMOOTH_RBGS, SMOOTH_COLORED_2, SMOOTH_COLORED_3 = 0, 1, 2, 3
 CGS_CG, CGS_BICGSTAB, CGS_CR, CGS_MINRES, CGS_SMOOTHER = range(5)
 BC_NEUMANN = 4
-F_SOLUTION, F_RHS, F_RESIDUAL, F_CGTMP0, F_CGTMP1 = range(5)
+F_SOLUTION, F_RHS, F_RESIDUAL, F_CGTMP0, F_CGTMP1, F_APPROX = range(6)
 
 
 class ExaMGError(RuntimeError):
@@ -45,7 +45,7 @@ class BcOp(C.Structure):
 class CycleDesc(C.Structure):
     _fields_ = [("smoother", C.c_int), ("omega", C.c_double), ("nu_pre", C.c_int), ("nu_post", C.c_int),
                 ("restrict_scale", C.c_double), ("cg_max_it", C.c_int), ("cg_rel_tol", C.c_double),
-                ("stencils", C.POINTER(C.c_int)), ("coarse_solver", C.c_int)]
+                ("stencils", C.POINTER(C.c_int)), ("coarse_solver", C.c_int), ("use_fas", C.c_int)]
 
 
 class System2Desc(C.Structure):
@@ -99,6 +99,7 @@ SIGNATURES = {
     "examg_field_print": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_char_p, C.c_char_p]),
     "examg_field_set_bc_face": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_double, C.POINTER(BcOp), C.c_int]),
     "examg_field_eval": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.POINTER(BcOp), C.c_int]),
+    "examg_loop_eval": (C.c_int, [C.c_void_p, C.c_int, C.c_int, _ip, _ip, C.c_int, C.POINTER(BcOp), C.c_int]),
     "examg_apply_bc": (C.c_int, [C.c_void_p, C.c_int, C.c_int]),
     "examg_field_upload": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_void_p]),
     "examg_field_download": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_void_p]),
@@ -331,6 +332,17 @@ class Context:
         for i, (op, val) in enumerate(prog):
             arr[i].op, arr[i].value = op, val
         check(self.L.examg_field_eval(self.h, f, slot, comp, arr, len(prog)))
+
+    def loop_eval(self, dst, srcs, prog, dst_slot=-1, src_slots=None):
+        """loop over dst { dst<dst_slot> = <postfix program over the node position and srcs at the same node> }
+        (OP_FIELD k pushes srcs[k]); slots default to the active ones."""
+        arr = (BcOp * len(prog))()
+        for i, (op, val) in enumerate(prog):
+            arr[i].op, arr[i].value = int(op), float(val)
+        n = len(srcs)
+        hs = (C.c_int * max(1, n))(*srcs)
+        sl = (C.c_int * max(1, n))(*(src_slots if src_slots is not None else [-1] * n))
+        check(self.L.examg_loop_eval(self.h, dst, dst_slot, hs, sl, n, arr, len(prog)))
 
     def field_print(self, f, filename, slot=-1, separator=None):
         """printField ( "file", F ): ascii, one line per point (position, value[s])."""

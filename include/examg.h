@@ -122,7 +122,9 @@ enum {
    * differ from the host's in the last bit */
   EXAMG_OP_EXP = 9, EXAMG_OP_SIN = 10, EXAMG_OP_COS = 11, EXAMG_OP_SINH = 12, EXAMG_OP_SQRT = 13,
   /* examg_field_eval only: push component `value` of the field being written, at the same node */
-  EXAMG_OP_COMP = 14
+  EXAMG_OP_COMP = 14,
+  /* examg_loop_eval only: push source field `value` (index into its src list) at the same node */
+  EXAMG_OP_FIELD = 15
 };
 typedef struct { int op; double value; } examg_bc_op;
 int examg_field_set_bc(examg_ctx *ctx, int field, int kind, double value);
@@ -138,6 +140,13 @@ int examg_field_set_bc_face(examg_ctx *ctx, int field, int face, int kind, doubl
  * and on the first ghost layer (node positions continue beyond the block), so stencil-field coefficients need no
  * exchange.  EXAMG_OP_COMP reads components written by earlier calls (e.g. centre = -(sum of the others)). */
 int examg_field_eval(examg_ctx *ctx, int field, int slot, int comp, const examg_bc_op *prog, int n_ops);
+/* The pointwise loop no pattern covers -- `loop over dst { dst<dst_slot> = expr }` with expr a program over the node
+ * position and up to eight node fields of the same level read at the same node (EXAMG_OP_FIELD; slot -1 = active;
+ * a source may be dst itself).  Runs on dst's loop points (Dirichlet boundary nodes excluded, duplicates included).
+ * This is what the nonlinear terms of Testing/NonLinear/FAS_2D_Basic.exa4 go through (Smoother, UpResidual,
+ * Restriction: gam * exp(Solution) * Solution next to a stencil convolution done by examg_apply).               */
+int examg_loop_eval(examg_ctx *ctx, int dst, int dst_slot, const int *src, const int *src_slot, int nsrc,
+                    const examg_bc_op *prog, int n_ops);
 /* applyBCs<F>_<lvl>(slot)  (C/s/e/boundary/ir/IR_ApplyBCFunction.scala:53-105); slot < 0 = active */
 int examg_apply_bc(examg_ctx *ctx, int field, int slot);
 
@@ -295,6 +304,12 @@ typedef struct {
   double cg_rel_tol;     /* solver_cgs_targetResReduction                        */
   const int *stencils;   /* stencil handle per level, index level - min_level   */
   int coarse_solver;     /* solver_cgs: EXAMG_CGS_CG (0, the default), _BICGSTAB, _CR, _MINRES, _SMOOTHER   */
+  int use_fas;           /* solver_useFAS: full approximation scheme -- per level Approx@coarser = Restriction * Solution;
+                          * Solution@coarser = Approx@coarser; RHS@coarser = Restriction * Residual + A@coarser *
+                          * Solution@coarser; mgCycle@coarser; Solution@coarser -= Approx@coarser; correction
+                          * (C/s/e/solver/l3/L3_SolverForEquation.scala:401-452).  One block.  For the linear operators
+                          * a stencil handle describes this equals the correction scheme up to rounding; nonlinear
+                          * terms are host-driven: examg_loop_eval, tests/fas_program.py                              */
 } examg_cycle_desc;
 enum { EXAMG_CGS_CG = 0, EXAMG_CGS_BICGSTAB = 1, EXAMG_CGS_CR = 2, EXAMG_CGS_MINRES = 3, EXAMG_CGS_SMOOTHER = 4 };
 /* `generate solver for ... with { key = value ... }` / the solver_* keys of a Knowledge file -> cycle descriptor
@@ -304,14 +319,16 @@ enum { EXAMG_CGS_CG = 0, EXAMG_CGS_BICGSTAB = 1, EXAMG_CGS_CR = 2, EXAMG_CGS_MIN
  * solver_cgs_maxNumIts, solver_cgs_targetResReduction.  desc->stencils and restrict_scale are left alone.
  * *colors_per_dim (nullable) = 0 for Jacobi or red-black, 2 / 3 for the n^d-way colourings (desc->smoother is then
  * EXAMG_SMOOTH_COLORED_2 / _3).  Keys of the outer Solve loop (solver_targetResReduction, solver_maxNumIts, ...) are
- * accepted and ignored: that loop is host code.  Unknown solver_* keys, solver_useFAS = true, coloring "None" with Gauss-Seidel and
+ * solver_useFAS.  Keys of the outer loop are
+ * accepted and ignored: that loop is host code.  Unknown solver_* keys, coloring "None" with Gauss-Seidel and
  * unsupported values are errors (EXAMG_EUNSUP / EXAMG_EINVAL with the offending key in the message).            */
 int examg_cycle_desc_from_options(const char *options, int dim, examg_cycle_desc *desc, int *colors_per_dim);
 typedef struct examg_solver examg_solver;
 examg_solver *examg_solver_create(examg_ctx *ctx, const examg_cycle_desc *desc);
 int examg_solver_destroy(examg_solver *s);
-/* field handles of a level: which = 0 Solution, 1 RHS, 2 Residual, 3 cgTmp0, 4 cgTmp1 */
-enum { EXAMG_F_SOLUTION = 0, EXAMG_F_RHS = 1, EXAMG_F_RESIDUAL = 2, EXAMG_F_CGTMP0 = 3, EXAMG_F_CGTMP1 = 4 };
+/* field handles of a level: which = 0 Solution, 1 RHS, 2 Residual, 3 cgTmp0, 4 cgTmp1, 5 Approximation */
+enum { EXAMG_F_SOLUTION = 0, EXAMG_F_RHS = 1, EXAMG_F_RESIDUAL = 2, EXAMG_F_CGTMP0 = 3, EXAMG_F_CGTMP1 = 4,
+       EXAMG_F_APPROX = 5 /* gen_approx (use_fas, all levels but the finest) */ };
 int examg_solver_field(examg_solver *s, int level, int which);
 /* mgCycle@level (level < 0: finest); asynchronous */
 int examg_solver_vcycle(examg_solver *s, int level);

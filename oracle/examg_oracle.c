@@ -356,6 +356,43 @@ void og_set_interior(const int n[3], double *a, double v) {
     }
 }
 
+void og_loop_eval(const int n[3], const double h[3], const double x0[3], int nsrc, const double *const *src,
+                  double *dst, const int *ops, const double *vals, int nops) {
+  (void)nsrc;
+  OG_LOOP_BEGIN(n)
+#pragma omp parallel for schedule(static) collapse(2)
+  for (int k = zl; k < zh; ++k)
+    for (int j = yl; j < yh; ++j) {
+      size_t row = (size_t)n[0] * ((size_t)j + (size_t)n[1] * (size_t)k);
+      const double y = (double)j * h[1] + x0[1], z = n[2] > 1 ? (double)k * h[2] + x0[2] : 0.0;
+      for (int i = xl; i < xh; ++i) {
+        const double x = (double)i * h[0] + x0[0];
+        double stk[16];
+        int sp = 0;
+        for (int q = 0; q < nops; ++q)
+          switch (ops[q]) {
+            case 0: stk[sp++] = vals[q]; break;
+            case 1: stk[sp++] = x; break;
+            case 2: stk[sp++] = y; break;
+            case 3: stk[sp++] = z; break;
+            case 4: --sp; stk[sp - 1] = stk[sp - 1] + stk[sp]; break;
+            case 5: --sp; stk[sp - 1] = stk[sp - 1] - stk[sp]; break;
+            case 6: --sp; stk[sp - 1] = stk[sp - 1] * stk[sp]; break;
+            case 7: --sp; stk[sp - 1] = stk[sp - 1] / stk[sp]; break;
+            case 8: stk[sp - 1] = -stk[sp - 1]; break;
+            case 9: stk[sp - 1] = exp(stk[sp - 1]); break;
+            case 10: stk[sp - 1] = sin(stk[sp - 1]); break;
+            case 11: stk[sp - 1] = cos(stk[sp - 1]); break;
+            case 12: stk[sp - 1] = sinh(stk[sp - 1]); break;
+            case 13: stk[sp - 1] = sqrt(stk[sp - 1]); break;
+            case 15: stk[sp++] = src[(int)vals[q]][row + i]; break;
+            default: break;
+          }
+        dst[row + i] = stk[0];
+      }
+    }
+}
+
 void og_copy_interior(const int n[3], const double *src, double *dst) {
   OG_LOOP_BEGIN(n)
 #pragma omp parallel for schedule(static) collapse(2)

@@ -111,6 +111,12 @@ void og_prolong_add(int dim, const int nf[3], const int nc[3], const double *uc,
                     double *uf);
 
 /* interior-only streaming loops (…exa4:160-162,181-198,226-228) */
+/* `loop over dst { dst = expr }`: a postfix program (the EXAMG_OP_* codes of include/examg.h: 0 const, 1-3 x/y/z, 4-7
+ * + - * /, 8 neg, 9 exp, 10 sin, 11 cos, 12 sinh, 13 sqrt, 15 source field vals[q] at the same node) evaluated on the
+ * loop points; node position = i * h + x0 (C/s/e/grid/ir/IR_VF_NodePosition.scala:109-111).  The pointwise loops of
+ * Testing/NonLinear/FAS_2D_Basic.exa4 (Smoother, UpResidual, Restriction). */
+void og_loop_eval(const int n[3], const double h[3], const double x0[3], int nsrc, const double *const *src,
+                  double *dst, const int *ops, const double *vals, int nops);
 void og_set_interior(const int n[3], double *a, double v);
 void og_copy_interior(const int n[3], const double *src, double *dst);
 void og_axpy(const int n[3], double alpha, const double *x, double *y);  /* y = fma(alpha,x,y) */
@@ -147,6 +153,7 @@ typedef struct {
   double cg_rel_tol;     /* 1e-3 */
   double domain_hi[3];   /* Domain global< [0,0,0] to hi >; 0 = 1.0 (the unit cube of every shipped program).  bench.py's
                             weak-scaling runs grow the domain with the block grid so that the mesh width stays put */
+  int use_fas;           /* solver_useFAS: full approximation scheme (C/s/e/solver/l3/L3_SolverForEquation.scala:401-452) */
 } og_config;
 
 /* OpenMP team size of the `parallel for` loops (omp_numThreads of the Knowledge file,

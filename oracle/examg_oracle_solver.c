@@ -28,6 +28,7 @@ typedef struct {
   int cur;      /* currentSlot (C/s/e/field/ir/IR_Slot.scala:33-62) */
   double *rhs, *res;
   double *p, *ap; /* cgTmp0 / cgTmp1 (coarsest only) */
+  double *approx; /* gen_approx (solver_useFAS, all levels but the finest) */
 } og_level;
 
 struct og_solver {
@@ -191,6 +192,7 @@ og_solver *og_solver_create(const og_config *cfg) {
     l->rhs = og_calloc(l->size);
     l->res = og_calloc(l->size);
     if (lvl == cfg->min_level) { l->p = og_calloc(l->size); l->ap = og_calloc(l->size); }
+    if (cfg->use_fas && lvl != cfg->max_level) l->approx = og_calloc(l->size);
   }
   return s;
 }
@@ -200,7 +202,7 @@ void og_solver_destroy(og_solver *s) {
   int nl = s->cfg.max_level - s->cfg.min_level + 1;
   for (int i = 0; i < nl; ++i) {
     og_level *l = &s->lv[i];
-    free(l->sf); free(l->u[0]); free(l->u[1]); free(l->rhs); free(l->res); free(l->p); free(l->ap);
+    free(l->sf); free(l->u[0]); free(l->u[1]); free(l->rhs); free(l->res); free(l->p); free(l->ap); free(l->approx);
   }
   free(s->lv);
   free(s);
@@ -277,8 +279,19 @@ void og_solver_vcycle(og_solver *s, int lvl) {
   og_smooth(s, l, s->cfg.nu_pre);
   og_residual(l->n, &l->st, l->sf, l->u[l->cur], l->rhs, l->res);
   og_restrict(s->cfg.dim, l->n, c->n, s->cfg.restrict_scale, l->res, c->rhs);
-  og_set_interior(c->n, c->u[c->cur], 0.0);
-  og_solver_vcycle(s, lvl - 1);
+  if (s->cfg.use_fas) {
+    /* L3_SolverForEquation.scala:401-452: Approx@coarser = Restriction * Solution; Solution@coarser = Approx@coarser;
+     * RHS@coarser = Restriction * Residual + A@coarser * Solution@coarser; ...; Solution@coarser -= Approx@coarser */
+    og_restrict(s->cfg.dim, l->n, c->n, 1.0, l->u[l->cur], c->approx);
+    og_copy_interior(c->n, c->approx, c->u[c->cur]);
+    og_apply(c->n, &c->st, c->sf, c->u[c->cur], c->res);
+    og_axpy(c->n, 1.0, c->res, c->rhs);
+    og_solver_vcycle(s, lvl - 1);
+    og_axpy(c->n, -1.0, c->approx, c->u[c->cur]);
+  } else {
+    og_set_interior(c->n, c->u[c->cur], 0.0);
+    og_solver_vcycle(s, lvl - 1);
+  }
   og_prolong_add(s->cfg.dim, l->n, c->n, c->u[c->cur], l->u[l->cur]);
   og_smooth(s, l, s->cfg.nu_post);
 }

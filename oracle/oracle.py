@@ -46,7 +46,7 @@ class Config(C.Structure):
                 ("op", C.c_int), ("order", C.c_int), ("kappa", C.c_double), ("smoother", C.c_int),
                 ("omega", C.c_double), ("nu_pre", C.c_int), ("nu_post", C.c_int),
                 ("restrict_scale", C.c_double), ("cg_max_it", C.c_int), ("cg_rel_tol", C.c_double),
-                ("domain_hi", C.c_double * 3)]
+                ("domain_hi", C.c_double * 3), ("use_fas", C.c_int)]
 
 
 def build(force=False):
@@ -101,6 +101,8 @@ def lib():
     L.og_glibc_rand_fill.restype = None
     L.og_restrict.argtypes = [C.c_int, i3, i3, C.c_double, dp, dp]
     L.og_prolong_add.argtypes = [C.c_int, i3, i3, dp, dp]
+    L.og_loop_eval.argtypes = [i3, dp, dp, C.c_int, C.POINTER(dp), dp, i3, dp, C.c_int]
+    L.og_loop_eval.restype = None
     L.og_set_interior.argtypes = [i3, dp, C.c_double]
     L.og_copy_interior.argtypes = [i3, dp, dp]
     L.og_axpy.argtypes = [i3, C.c_double, dp, dp]
@@ -283,6 +285,24 @@ def prolong_add(dim, uc, uf):
     return uf
 
 
+def copy_interior(src, dst):
+    lib().og_copy_interior(_n(src), _dp(src), _dp(dst))
+    return dst
+
+
+def loop_eval(dst, srcs, prog, h, x0=(0.0, 0.0, 0.0)):
+    """dst = program(node position, srcs at the same node) on the loop points; prog = [(op, value), ...] with the
+    EXAMG_OP_* codes of include/examg.h (15 = source field index)."""
+    n = len(prog)
+    ops = (C.c_int * n)(*[int(o) for o, _ in prog])
+    vals = (C.c_double * n)(*[float(v) for _, v in prog])
+    hh = (C.c_double * 3)(*(list(h) + [1.0] * (3 - len(h))))
+    xx = (C.c_double * 3)(*(list(x0) + [0.0] * (3 - len(x0))))
+    ptrs = (C.POINTER(C.c_double) * max(1, len(srcs)))(*[_dp(a) for a in srcs])
+    lib().og_loop_eval(_n(dst), hh, xx, len(srcs), ptrs, _dp(dst), ops, vals, n)
+    return dst
+
+
 def axpy(alpha, x, y):
     lib().og_axpy(_n(x), alpha, _dp(x), _dp(y))
     return y
@@ -304,8 +324,9 @@ class Solver:
 
     def __init__(self, dim, F, min_level, max_level, op=OP_LAPLACE_SCALED, order=ORDER_BENCH, kappa=0.0,
                  smoother=SMOOTH_RBGS, omega=0.8, nu_pre=3, nu_post=3, restrict_scale=1.0,
-                 cg_max_it=128, cg_rel_tol=1e-3, domain_hi=(1.0, 1.0, 1.0)):
+                 cg_max_it=128, cg_rel_tol=1e-3, domain_hi=(1.0, 1.0, 1.0), use_fas=False):
         cfg = Config()
+        cfg.use_fas = 1 if use_fas else 0
         for d in range(3):
             cfg.domain_hi[d] = domain_hi[d] if d < len(domain_hi) else 1.0
         cfg.dim = dim

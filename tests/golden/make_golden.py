@@ -52,6 +52,7 @@ FILES = {
     "BC_2D_Periodic": "Testing/BC/2D_Periodic.results",
     "BC_3D_Periodic": "Testing/BC/3D_Periodic.results",
     "BC_3D_Trigonometric": "Testing/BC/3D_Trigonometric.results",
+    "NonLinear_FAS_2D_Basic": "Testing/NonLinear/FAS_2D_Basic.results",
 }
 
 if __name__ == "__main__":

@@ -157,8 +157,10 @@ def test_cycle_desc_from_options(built):
         d, ncol = rt.cycle_desc_from_options(text, dim)
         assert (d.smoother, ncol) == want
     d, _ = rt.cycle_desc_from_options("solver_smoother_coloring = rb; solver_cgs = Smoother", 3)
-    assert d.coarse_solver == rt.CGS_SMOOTHER
-    for bad, match in [("solver_useFAS = true", "solver_useFAS"), ("solver_smoother_coloring = None", "lexicographic"),
+    assert d.coarse_solver == rt.CGS_SMOOTHER and d.use_fas == 0
+    d, _ = rt.cycle_desc_from_options("solver_smoother_coloring = rb; solver_useFAS = true", 3)
+    assert d.use_fas == 1
+    for bad, match in [("solver_useFAS = maybe", "solver_useFAS"), ("solver_smoother_coloring = None", "lexicographic"),
                        ("solver_smoother_coloring = 4-way", "4-way in 3D"), ("solver_smoother_coloring = rb; solver_cgs = GMRES", "solver_cgs = gmres"),
                        ("solver_smoother_coloring = rb; solver_bogus = 1", "unknown option solver_bogus"),
                        ("solver_smoother_coloring = rb; solver_smoother_numPre = two", "not a number"),

@@ -366,3 +366,102 @@ def test_coarse_solver_choice(cgs, oracle):
         hist[name] = h
     assert all(abs(a - b) <= 0.05 * b for a, b in zip(hist[cgs], hist["cg"])), (hist[cgs], hist["cg"])
     assert hist[cgs][-1] < 1e-3 * hist[cgs][0]
+
+
+def test_fas_2d_basic_golden_and_oracle(oracle):
+    """Testing/NonLinear/FAS_2D_Basic: the nonlinear full approximation scheme program through libexamg --
+    stencil convolutions by examg_apply, the pointwise nonlinear parts by examg_loop_eval, transfers by examg_restrict /
+    examg_prolong_add -- prints the reference's golden stdout, and follows the CPU oracle to 1e-9 (exp() is the
+    device's libm on one side and the host's on the other)."""
+    import fas_program as fp
+    g = fp.GpuFas(fp.FasProgram())
+    assert fp.solve(g, oracle.print_reduced_prec) == fp.expected()
+    g.close()
+    prog = fp.FasProgram(max_level=5)
+    ref, gpu = fp.OracleFas(prog, oracle), fp.GpuFas(prog)
+    for b in (ref, gpu):
+        b.init_finest()
+        fp.up_residual(b, 5)
+    assert abs(gpu.norm(5) - ref.norm(5)) <= 1e-12 * ref.norm(5)
+    for cyc in range(3):
+        for b in (ref, gpu):
+            fp.vcycle(b, 5)
+            fp.up_residual(b, 5)
+        ug, ur = gpu.solution(5), ref.solution(5)
+        assert np.max(np.abs(ug.reshape(ur.shape) - ur)) <= 1e-9 * np.max(np.abs(ur)), cyc
+        assert abs(gpu.norm(5) - ref.norm(5)) <= 1e-8 * ref.norm(5)
+        assert abs(gpu.max_error(5) - ref.max_error(5)) <= 1e-9 * ref.max_error(5)
+    gpu.close()
+    ref.close()
+
+
+def test_loop_eval_is_bit_exact_without_libm(oracle):
+    """examg_loop_eval against og_loop_eval on a program without transcendental functions (+ - * / neg sqrt, node
+    positions, three source fields, one of them the destination): bit-identical; and its argument checks."""
+    import fas_program as fp
+    from exastencils_b200 import runtime as rt
+    ctx = rt.Context(3, 2, 2, block_cells=(3, 2, 1))
+    shape = ctx.shape(2)
+    rng = np.random.default_rng(8)
+    a, b, d = (rng.uniform(0.5, 2.0, size=shape) for _ in range(3))
+    fa, fb, fd = ctx.field_create("a", 2), ctx.field_create("b", 2), ctx.field_create("d", 2, 2)
+    ctx.upload(fa, a)
+    ctx.upload(fb, b)
+    ctx.upload(fd, d)
+    F, K, O = fp.fld, fp.c, fp.op
+    prog = F(2) + F(0) + O(fp.X) + O(fp.MUL) + F(1) + O(fp.Y) + K(0.25) + O(fp.ADD) + O(fp.DIV) + O(fp.SUB) + O(fp.ADD) \
+        + F(0) + O(fp.SQRT) + O(fp.NEG) + O(fp.Z) + O(fp.MUL) + O(fp.SUB)
+    ctx.loop_eval(fd, [fa, fb, fd], prog)
+    want = d.copy()
+    h = [1.0 / (c << 2) for c in (3, 2, 1)]
+    oracle.set_periodic((0, 0, 0))
+    oracle.loop_eval(want, [a, b, d.copy()], prog, h)
+    assert np.array_equal(ctx.download(fd, 2), want)
+    assert not np.array_equal(want, d)
+    with pytest.raises(rt.ExaMGError, match="source field"):
+        ctx.loop_eval(fd, [fa], F(1))
+    ctx.close()
+    two = rt.Context(3, 1, 2, block_cells=(3, 2, 1))
+    with pytest.raises(rt.ExaMGError, match="level"):
+        two.loop_eval(two.field_create("x", 2), [two.field_create("y", 1)], F(0))
+    two.close()
+
+
+@pytest.mark.parametrize("dim,smoother", [(2, "jacobi"), (3, "rbgs")])
+def test_fas_in_the_library_cycle(dim, smoother, oracle):
+    """solver_useFAS = true inside the library cycle (examg_cycle_desc.use_fas, reached through
+    examg_cycle_desc_from_options): bit-identical to the oracle's FAS cycle (og_config.use_fas) from a random first
+    guess, and the same iterates as the correction scheme up to rounding."""
+    from exastencils_b200 import MultigridProgram
+    from exastencils_b200 import runtime as rt
+    d, _ = rt.cycle_desc_from_options("solver_useFAS = true; solver_smoother_coloring = rb", dim)
+    assert d.use_fas == 1
+    lo, hi = 1, 5 if dim == 2 else 4
+    cells = (3, 2) if dim == 2 else (1, 2, 1)
+    kw = dict(op="scaled", order="bench", smoother=smoother, omega=0.8, nu_pre=2, nu_post=2, cg_max_it=128, cg_rel_tol=1e-3)
+    fas, cs = MultigridProgram(dim, cells, lo, hi, use_fas=True, **kw), MultigridProgram(dim, cells, lo, hi, **kw)
+    ref = oracle.Solver(dim, cells, lo, hi, smoother=oracle.SMOOTH_JACOBI if smoother == "jacobi" else oracle.SMOOTH_RBGS,
+                        omega=0.8, nu_pre=2, nu_post=2, cg_max_it=128, cg_rel_tol=1e-3, use_fas=True)
+    rng = np.random.default_rng(17 + dim)
+    u0, f0 = rng.uniform(-1.0, 1.0, size=fas.ctx.shape(hi)), rng.uniform(-1.0, 1.0, size=fas.ctx.shape(hi))
+    for p in (fas, cs):
+        p.solution(hi)[...] = u0
+        p.rhs(hi)[...] = f0
+        p.commit()
+    ref.solution(hi)[...] = u0.reshape(ref.solution(hi).shape)
+    ref.rhs(hi)[...] = f0.reshape(ref.rhs(hi).shape)
+    ref.sync_slots()
+    h = [fas.update_residual_norm()]
+    assert h[0] == ref.update_residual_norm()
+    for _ in range(3):
+        fas.vcycle()
+        cs.vcycle()
+        ref.vcycle()
+        h.append(fas.update_residual_norm())
+        assert h[-1] == ref.update_residual_norm()
+        assert fas.last_cg_iters() == ref.last_cg_iters()
+        assert np.array_equal(fas.fetch_solution(), ref.solution(hi).reshape(fas.fetch_solution().shape))
+        assert np.max(np.abs(fas.fetch_solution() - cs.fetch_solution())) <= 1e-10 * np.max(np.abs(u0))
+    assert h[-1] < 0.02 * h[0]
+    for p in (fas, cs, ref):
+        p.close()

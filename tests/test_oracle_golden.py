@@ -5,6 +5,7 @@ The reference's comparator (Testing/run_test.py:12-43) accepts a line if the
 strings are equal or the numbers differ by <= 1e-6 absolute; we require string
 equality of every printed token (4 significant digits), which is stricter.
 """
+import numpy as np
 import pytest
 
 import programs
@@ -100,3 +101,35 @@ def test_golden_cell_based(oracle):
     for prog in cp.PROGRAMS:
         b = cp.OracleCells(prog)
         assert cp.solve(b, oracle.print_reduced_prec) == prog.expected(), prog.name
+
+
+def test_golden_fas_2d_basic(oracle):
+    """Testing/NonLinear/FAS_2D_Basic.{exa4,knowledge,results}: the nonlinear full approximation scheme program (SURVEY
+    8f-2) on 1152^2 cells, levels 0..7 -- pins og_loop_eval and the FAS transfer statements (tests/fas_program.py)."""
+    import fas_program as fp
+    b = fp.OracleFas(fp.FasProgram(), oracle)
+    assert fp.solve(b, oracle.print_reduced_prec) == fp.expected()
+
+
+def test_fas_cycle_of_a_linear_operator(oracle):
+    """solver_useFAS of the layer-3 generator (og_config.use_fas): for a linear operator the full approximation scheme
+    is the correction scheme in other words -- same iterates up to rounding, from a non-zero first guess."""
+    rng = np.random.default_rng(3)
+    sols = []
+    for fas in (False, True):
+        s = oracle.Solver(2, (3, 2), 1, 5, smoother=oracle.SMOOTH_JACOBI, omega=0.8, nu_pre=2, nu_post=2, use_fas=fas)
+        if not sols:
+            u0, f0 = rng.uniform(-1, 1, s.solution(5).shape), rng.uniform(-1, 1, s.rhs(5).shape)
+        s.solution(5)[...] = u0
+        s.rhs(5)[...] = f0
+        s.sync_slots()
+        hist = [s.update_residual_norm()]
+        for _ in range(4):
+            s.vcycle()
+            hist.append(s.update_residual_norm())
+        sols.append((hist, s.solution(5).copy()))
+        s.close()
+    (h0, u_cs), (h1, u_fas) = sols
+    assert h0[-1] < 1e-3 * h0[0]
+    assert np.allclose(h0, h1, rtol=1e-9)
+    assert np.max(np.abs(u_cs - u_fas)) <= 1e-11 * np.max(np.abs(u_cs))
