@@ -417,7 +417,7 @@ int launch_color_generic(examg_ctx *c, const Stencil &s, double omega, double *u
   return EXAMG_OK;
 }
 
-int launch_apply(examg_ctx *c, const Stencil &s, const double *u, double *out) {
+int launch_apply_generic(examg_ctx *c, const Stencil &s, const double *u, double *out) {
   return launch_stencil<M_APPLY>(c, s, u, nullptr, out, 0.0, 0, -1);
 }
 int launch_residual_generic(examg_ctx *c, const Stencil &s, const double *u, const double *rhs, double *res,

@@ -29,11 +29,23 @@ int launch_jacv_fused(examg_ctx *c, const Stencil &s, double omega, Field &fu, c
 bool residual_restrict_usable(examg_ctx *c, const Stencil &s);
 int launch_residual_restrict(examg_ctx *c, const Stencil &s, const double *u, const double *rhs, double *rhsc, double scale);
 
+int launch_apply_generic(examg_ctx *c, const Stencil &s, const double *u, double *out);
+// full compact constant-coefficient stencils in lexicographic order: register-window kernels (examg_fast27.cu)
+bool lex_usable(examg_ctx *c, const Stencil &s);
+int launch_lex(examg_ctx *c, const Stencil &s, int mode, const double *u, const double *rhs, double *out, double omega,
+               int extend);
+
+int launch_apply(examg_ctx *c, const Stencil &s, const double *u, double *out) {
+  if (lex_usable(c, s)) return launch_lex(c, s, 0, u, nullptr, out, 0.0, 0);
+  return launch_apply_generic(c, s, u, out);
+}
 int launch_residual(examg_ctx *c, const Stencil &s, const double *u, const double *rhs, double *res, int red_slot,
                     int extend) {
+  if (red_slot < 0 && res && lex_usable(c, s)) return launch_lex(c, s, 1, u, rhs, res, 0.0, extend);
   return launch_residual_generic(c, s, u, rhs, res, red_slot, extend);
 }
 int launch_jacobi(examg_ctx *c, const Stencil &s, double omega, const double *u, const double *rhs, double *unext) {
+  if (lex_usable(c, s)) return launch_lex(c, s, 2, u, rhs, unext, omega, 0);
   return launch_jacobi_generic(c, s, omega, u, rhs, unext);
 }
 int launch_rb(examg_ctx *c, const Stencil &s, double omega, double *u, const double *rhs, int color) {

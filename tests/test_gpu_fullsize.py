@@ -21,7 +21,7 @@ import numpy as np
 pytestmark = pytest.mark.gpu
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
-GENERIC = {"EXAMG_NO_FUSED": "1", "EXAMG_NO_FUSED_RESTRICT": "1", "EXAMG_NO_FAST_PROLONG": "1", "EXAMG_NO_GRAPH": "1",
+GENERIC = {"EXAMG_NO_FUSED": "1", "EXAMG_LEX": "0", "EXAMG_NO_FUSED_RESTRICT": "1", "EXAMG_NO_FAST_PROLONG": "1", "EXAMG_NO_GRAPH": "1",
            "EXAMG_JACV_FUSE": "0", "EXAMG_JAC_FUSE_SWEEPS": "0"}
 
 

@@ -424,6 +424,55 @@ def test_rbgs_2d_fused_sweeps(cells, lvl, order, oracle, request):
     ctx.close()
 
 
+@pytest.mark.parametrize("py", [4, 2])
+@pytest.mark.parametrize("dim,cells,lvl", [(3, (1, 1, 1), 5), (3, (5, 3, 2), 3), (3, (9, 9, 9), 0), (3, (2, 1, 3), 6),
+                                           (2, (1, 1), 2), (2, (3, 5), 6), (2, (1, 1), 10)])
+def test_full_compact_constant_stencils(dim, cells, lvl, py, oracle, request):
+    """27-point (3D) / 9-point (2D) constant-coefficient operator in lexicographic order (row N1): A*u, residual and
+    damped Jacobi through the register-window kernels of examg_fast27.cu (k_lex27<MODE, PY>, k_lex9<MODE>) against the
+    oracle, bit for bit; untouched boundary nodes; both row-patch sizes (EXAMG_LEX_PY is read once per process: the
+    non-default one runs in a process of its own); and the generic kernel (EXAMG_LEX=0) gives the same bits."""
+    import os, subprocess, sys
+    if dim == 2 and py == 2:
+        pytest.skip("no row patch in 2D")
+    if py == 2 and os.environ.get("EXAMG_LEX_PY") != "2":
+        env = dict(os.environ, EXAMG_LEX_PY="2")
+        node = "%s::%s" % (__file__, request.node.name)
+        out = subprocess.run([sys.executable, "-m", "pytest", "-x", "-q", "-m", "gpu", node], env=env, capture_output=True,
+                             text=True, timeout=600)
+        assert out.returncode == 0, out.stdout[-3000:] + out.stderr[-2000:]
+        return
+    og = oracle
+    ctx = _ctx(dim, cells, lvl, lvl)
+    shape = ctx.shape(lvl)
+    offs = _stencil_offsets(dim, 9 if dim == 2 else 27)
+    seed = 77 * lvl + sum(cells) + dim
+    coef = _rand(len(offs), seed)
+    centre = offs.index((0, 0, 0))
+    coef[centre] = 6.0 + abs(coef[centre])
+    A = ctx.stencil_const(lvl, offs, coef)
+    st = og.Stencil.make(offs, coef)
+    fu, ff, fo = ctx.field_create("u", lvl, 2), ctx.field_create("rhs", lvl), ctx.field_create("out", lvl)
+    u, rhs, sentinel = _rand(shape, seed + 1), _rand(shape, seed + 2), _rand(shape, seed + 3)
+    ctx.upload(fu, u, 0)
+    ctx.upload(fu, u, 1)
+    ctx.upload(ff, rhs)
+    inner = (Ellipsis,) + tuple(slice(1, -1) for _ in range(dim))
+    for name, call, ref in [("apply", lambda: ctx.apply(A, fu, fo), lambda: og.apply(st, u)),
+                            ("residual", lambda: ctx.residual(A, fu, ff, fo), lambda: og.residual(st, u, rhs))]:
+        ctx.upload(fo, sentinel)
+        call()
+        exp = sentinel.copy()
+        exp[inner] = ref()[inner]
+        assert np.array_equal(ctx.download(fo, lvl), exp), name
+    e = u
+    for it in range(3):
+        ctx.smooth_jacobi(A, fu, ff, 0.7, 1)
+        e = og.smooth_jacobi(st, 0.7, e, rhs)
+        assert np.array_equal(ctx.download(fu, lvl), e), it
+    ctx.close()
+
+
 def test_pipelined_upload():
     """examg_field_upload_begin/_finish: the copy-stream transfer lands in the field exactly like examg_field_upload,
     for node and cell fields, alternating between the two staging arrays."""
