@@ -169,6 +169,125 @@ k_lex9(const GridArgs g, const __grid_constant__ LexArgs a, const double *__rest
   }
 }
 
+// ---- 3D 7-point constant coefficients: the residual loop ----------------------------------------------------------------
+// The generic kernel issues 8 loads per point (7 entries + RHS), five of which hit L1/L2: per thread only two requests
+// that go to DRAM are in flight, and at full occupancy the loop reads at 4.1 TB/s + writes (0.54 ms at 512^3, ncu:
+// long_scoreboard 85 %, DRAM 73 %).  Here a thread owns an x column and two rows and marches in z: the z neighbours stay in
+// registers, the y neighbours of the two rows cost two extra loads, x-1 / x+1 come from the neighbour lanes (warp = 32
+// columns, 30 outputs), everything is requested one plane ahead: 3 loads per point, all of them new data.  0.50 ms,
+// DRAM 81 % (ncu).  Same fold as the generic kernel (declaration order ORD 0 / 1) => bit-identical.
+// The variants that also sum the squares of the residual were tried and dropped (+16..32 registers for the double-double
+// sum: 36 % warps active uncapped, spills when capped; 0.57-0.60 ms for the norm-only pass against 0.50 ms of the generic
+// kernel, 0.70 = 0.70 ms with the store): those loops stay on k_stencil.
+template <int ORD>
+__device__ __forceinline__ double star_resid(double c, double xm, double xp, double ym, double yp, double zm, double zp,
+                                             double f, const double *coef) {
+  double acc = coef[0] * c;
+  if (ORD == 0) {
+    acc = fma(coef[1], xm, acc);
+    acc = fma(coef[2], xp, acc);
+    acc = fma(coef[3], ym, acc);
+    acc = fma(coef[4], yp, acc);
+    acc = fma(coef[5], zm, acc);
+    acc = fma(coef[6], zp, acc);
+  } else {
+    acc = fma(coef[1], xp, acc);
+    acc = fma(coef[2], xm, acc);
+    acc = fma(coef[3], yp, acc);
+    acc = fma(coef[4], ym, acc);
+    acc = fma(coef[5], zp, acc);
+    acc = fma(coef[6], zm, acc);
+  }
+  return f - acc;
+}
+
+template <int ORD>
+__global__ void __launch_bounds__(128, 8)
+k_star7(const GridArgs g, const __grid_constant__ LexArgs a, const double *__restrict__ u, const double *__restrict__ rhs,
+        double *__restrict__ out, int kz) {
+  constexpr int PY = 2;
+  const int tx = threadIdx.x;
+  const int i = g.lo[0] + blockIdx.x * 30 + tx - 1;
+  const int j0 = g.lo[1] + (blockIdx.y * blockDim.y + threadIdx.y) * PY;
+  const int z0 = g.lo[2] + blockIdx.z * kz, z1 = min(z0 + kz, g.hi[2]);
+  if (j0 >= g.hi[1]) return;  // warp-uniform
+  const bool act = tx >= 1 && tx <= 30 && i < g.hi[0];
+  const int ic = min(i, g.hi[0]);
+  long long row[PY + 2];
+#pragma unroll
+  for (int r = 0; r < PY + 2; ++r) row[r] = ic + (long long)g.pitch * min(j0 - 1 + r, g.hi[1]);
+  double zm[PY], zc[PY + 2], vn[PY + 2], fn[PY];
+#pragma unroll
+  for (int r = 0; r < PY; ++r) zm[r] = __ldg(u + g.plane * (z0 - 1) + row[r + 1]);
+#pragma unroll
+  for (int r = 0; r < PY + 2; ++r) zc[r] = __ldg(u + g.plane * z0 + row[r]);
+#pragma unroll
+  for (int r = 0; r < PY + 2; ++r) vn[r] = __ldg(u + g.plane * (z0 + 1) + row[r]);
+#pragma unroll
+  for (int r = 0; r < PY; ++r) fn[r] = __ldg(rhs + g.plane * z0 + row[r + 1]);
+#pragma unroll 2
+  for (int k = z0; k < z1; ++k) {
+    double zp[PY + 2], f[PY];
+#pragma unroll
+    for (int r = 0; r < PY + 2; ++r) zp[r] = vn[r];
+#pragma unroll
+    for (int r = 0; r < PY; ++r) f[r] = fn[r];
+    {  // requests of the next plane (clamped at the end of the segment)
+      const double *p = u + g.plane * min(k + 2, z1);
+#pragma unroll
+      for (int r = 0; r < PY + 2; ++r) vn[r] = __ldg(p + row[r]);
+      const double *q = rhs + g.plane * min(k + 1, z1 - 1);
+#pragma unroll
+      for (int r = 0; r < PY; ++r) fn[r] = __ldg(q + row[r + 1]);
+    }
+#pragma unroll
+    for (int r = 0; r < PY; ++r) {
+      const double c = zc[r + 1];
+      const double xm = __shfl_up_sync(0xffffffffu, c, 1), xp = __shfl_down_sync(0xffffffffu, c, 1);
+      const double res = star_resid<ORD>(c, xm, xp, zc[r], zc[r + 2], zm[r], zp[r + 1], f[r], a.c);
+      if (act && j0 + r < g.hi[1]) out[row[r + 1] + g.plane * k] = res;
+    }
+#pragma unroll
+    for (int r = 0; r < PY; ++r) zm[r] = zc[r + 1];
+#pragma unroll
+    for (int r = 0; r < PY + 2; ++r) zc[r] = zp[r];
+  }
+}
+
+int stencil_order(const Stencil &s);  // examg_fast7.cu
+
+static int env_flag27(const char *name, int dflt);
+
+bool star7_usable(examg_ctx *c, const Stencil &s) {
+  static const bool on = env_flag27("EXAMG_NO_FUSED", 0) == 0 && env_flag27("EXAMG_STAR7", 1) != 0;
+  if (!on || c->cfg.dim != 3 || !s.is7 || s.coeff_field >= 0 || stencil_order(s) < 0) return false;
+  const LevelGeom &g = *geom(c, s.level);
+  return g.n[0] >= 33 && g.n[1] >= 33 && g.n[2] >= 33;  // small levels: launch-latency bound either way
+}
+
+// Residual = RHS - A * Solution; extend: layers of the neighbour blocks' nodes computed redundantly (as launch_stencil)
+int launch_star7(examg_ctx *c, const Stencil &s, const double *u, const double *rhs, double *res, int extend) {
+  const LevelGeom &g = *geom(c, s.level);
+  GridArgs ga = grid_args_loc(c, g);
+  for (int d = 0; d < c->cfg.dim && extend > 0; ++d) {
+    if (c->nb[d][0]) ga.lo[d] -= extend;
+    if (c->nb[d][1]) ga.hi[d] += extend;
+  }
+  const int ex = ga.hi[0] - ga.lo[0], ey = ga.hi[1] - ga.lo[1], ez = ga.hi[2] - ga.lo[2];
+  if (ex <= 0 || ey <= 0 || ez <= 0) return EXAMG_OK;
+  LexArgs a;
+  for (int k = 0; k < 27; ++k) a.c[k] = k < 7 ? s.coef[k] : 0.0;
+  a.w = 0.0;
+  const int gx = (ex + 29) / 30, gy = (ey + 7) / 8;
+  int kz = 64;
+  while (kz > 8 && (long long)gx * gy * ((ez + kz - 1) / kz) < 148 * 16) kz >>= 1;
+  const dim3 grid(gx, gy, (ez + kz - 1) / kz), block(32, 4, 1);
+  if (stencil_order(s) == 0) k_star7<0><<<grid, block, 0, c->stream>>>(ga, a, u, rhs, res, kz);
+  else k_star7<1><<<grid, block, 0, c->stream>>>(ga, a, u, rhs, res, kz);
+  EXAMG_LAUNCH_CHECK(c);
+  return EXAMG_OK;
+}
+
 static int env_flag27(const char *name, int dflt) {
   const char *e = getenv(name);
   return e && e[0] ? atoi(e) : dflt;

@@ -35,6 +35,11 @@ bool lex_usable(examg_ctx *c, const Stencil &s);
 int launch_lex(examg_ctx *c, const Stencil &s, int mode, const double *u, const double *rhs, double *out, double omega,
                int extend);
 
+// 3D 7-point constant coefficients: the residual loop with the z and x neighbours out of registers
+bool star7_usable(examg_ctx *c, const Stencil &s);
+int launch_star7(examg_ctx *c, const Stencil &s, const double *u, const double *rhs, double *res, int extend);
+
+
 int launch_apply(examg_ctx *c, const Stencil &s, const double *u, double *out) {
   if (lex_usable(c, s)) return launch_lex(c, s, 0, u, nullptr, out, 0.0, 0);
   return launch_apply_generic(c, s, u, out);
@@ -42,6 +47,7 @@ int launch_apply(examg_ctx *c, const Stencil &s, const double *u, double *out) {
 int launch_residual(examg_ctx *c, const Stencil &s, const double *u, const double *rhs, double *res, int red_slot,
                     int extend) {
   if (red_slot < 0 && res && lex_usable(c, s)) return launch_lex(c, s, 1, u, rhs, res, 0.0, extend);
+  if (red_slot < 0 && res && star7_usable(c, s)) return launch_star7(c, s, u, rhs, res, extend);
   return launch_residual_generic(c, s, u, rhs, res, red_slot, extend);
 }
 int launch_jacobi(examg_ctx *c, const Stencil &s, double omega, const double *u, const double *rhs, double *unext) {

@@ -108,6 +108,10 @@ def test_stencil_loops(dim, cells, lvl, npts, var, oracle):
     assert np.array_equal(ctx.download(fo, lvl), exp)
     n2_ref = og.dot(e, e)
     assert abs(n2 - n2_ref) <= RTOL_SUM * abs(n2_ref)
+    # the residual loop on its own (3D 7-point constant coefficients from 33^3: k_star7, examg_fast27.cu)
+    ctx.upload(fo, sentinel)
+    ctx.residual(A, fu, ff, fo)
+    assert np.array_equal(ctx.download(fo, lvl), exp)
     # Jacobi (slot 0 -> slot 1, advance)
     omega = 0.8
     ctx.smooth_jacobi(A, fu, ff, omega, 1)
