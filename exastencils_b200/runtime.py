@@ -52,6 +52,10 @@ class System2Desc(C.Structure):
     _fields_ = [("laplace", C.c_int), ("scale", C.c_double), ("c_uu", C.c_int), ("c_uv", C.c_int), ("c_vv", C.c_int)]
 
 
+class StokesDesc(C.Structure):
+    _fields_ = [("nu_pre", C.c_int), ("nu_post", C.c_int), ("nu_coarse", C.c_int), ("top_vel", C.c_double)]
+
+
 class OptFlowDesc(C.Structure):
     _fields_ = [("alpha", C.c_double), ("relax", C.c_double), ("nu_pre", C.c_int), ("nu_post", C.c_int),
                 ("cg_max_it", C.c_int), ("cg_rel_tol", C.c_double)]
@@ -155,6 +159,19 @@ SIGNATURES = {
     "examg_optflow_cycles": (C.c_int, [C.c_void_p, C.c_int, _dp]),
     "examg_optflow_residual_norm": (C.c_int, [C.c_void_p, _dp]),
     "examg_optflow_last_cg_iters": (C.c_int, [C.c_void_p, _ip]),
+    "examg_stokes_create": (C.c_void_p, [C.c_void_p, C.POINTER(StokesDesc)]),
+    "examg_stokes_destroy": (C.c_int, [C.c_void_p]),
+    "examg_stokes_cells": (C.c_int, [C.c_void_p, C.c_int]),
+    "examg_stokes_upload": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_void_p]),
+    "examg_stokes_download": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_void_p]),
+    "examg_stokes_apply_bc": (C.c_int, [C.c_void_p, C.c_int]),
+    "examg_stokes_smooth_color": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int]),
+    "examg_stokes_smooth": (C.c_int, [C.c_void_p, C.c_int, C.c_int]),
+    "examg_stokes_residual": (C.c_int, [C.c_void_p, C.c_int, _dp]),
+    "examg_stokes_restrict": (C.c_int, [C.c_void_p, C.c_int]),
+    "examg_stokes_set_solution": (C.c_int, [C.c_void_p, C.c_int, C.c_double]),
+    "examg_stokes_correct": (C.c_int, [C.c_void_p, C.c_int]),
+    "examg_stokes_vcycle": (C.c_int, [C.c_void_p, C.c_int]),
     "examg_comm_blob_size": (C.c_int, [C.c_void_p]),
     "examg_comm_export": (C.c_int, [C.c_void_p, C.c_void_p]),
     "examg_comm_import": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int]),

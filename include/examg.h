@@ -392,6 +392,41 @@ int examg_optflow_cycles(examg_optflow *o, int n, double *norm_out); /* n cycles
 int examg_optflow_residual_norm(examg_optflow *o, double *norm_out);
 int examg_optflow_last_cg_iters(examg_optflow *o, int *iters_out);
 
+/* ---- staggered grids: face-centred velocities, cell-centred pressure (2D Stokes) ------------------
+ * (Testing/Application/ExaStokes_2D.exa4, Examples/Stokes/2D_FD_Stokes_fromL4.exa4)
+ *   Field u < Face_x >, v < Face_y >, p < Cell >; rhs_* and residual_* alike.
+ *   Smoother: color with { i0 % 3, i1 % 3 } loop over p { solve locally { u@[0,0], u@[1,0], v@[0,0], v@[0,1], p@[0,0] } }
+ *   -- a 5 x 5 local system per cell over three localisations (C/s/e/solver/ir/IR_LocalSolve.scala:88-236,
+ *   IR_LocalDirectInvert.scala:44-150; wall faces are identity rows, IR_IsOnBoundary.scala:53-97) -- then apply bc.
+ * One block, square grid of block_cells << level cells, levels of the context.  Every field of a level is an
+ * (n+3) x (n+3) array, entry (i, j) at (i+1) + (n+3)(j+1), one ghost layer around: u on faces i = 0..n, cells
+ * j = 0..n-1; v on i = 0..n-1, j = 0..n; p on the n x n cells.                                              */
+typedef struct {
+  int nu_pre, nu_post;   /* repeat 3 times { Smoother }                                   */
+  int nu_coarse;         /* VCycle@coarsest: repeat 10 times { Smoother }                 */
+  double top_vel;        /* ApplyBC_u@finest: lid velocity (0.02)                         */
+} examg_stokes_desc;
+typedef struct examg_stokes examg_stokes;
+enum { EXAMG_ST_U = 0, EXAMG_ST_V = 1, EXAMG_ST_P = 2, EXAMG_ST_RHS_U = 3, EXAMG_ST_RHS_V = 4, EXAMG_ST_RHS_P = 5,
+       EXAMG_ST_RES_U = 6, EXAMG_ST_RES_V = 7, EXAMG_ST_RES_P = 8, EXAMG_ST_NFIELDS = 9 };
+examg_stokes *examg_stokes_create(examg_ctx *ctx, const examg_stokes_desc *desc);
+int examg_stokes_destroy(examg_stokes *s);
+int examg_stokes_cells(examg_stokes *s, int level);                     /* n (level < 0: finest)          */
+int examg_stokes_upload(examg_stokes *s, int level, int which, const double *host);   /* (n+3)^2 doubles */
+int examg_stokes_download(examg_stokes *s, int level, int which, double *host);
+/* apply bc to u, v, p: u = ApplyBC_u on the finest level (lid at the top, no-slip elsewhere), Dirichlet 0.0 below;
+ * v = Dirichlet 0.0; p = None (C/s/e/boundary/ir/IR_BoundaryCondition.scala:38-45: the value on the wall faces of a
+ * face field's own dimension, ghost = 2 g - inner in the other)                                         */
+int examg_stokes_apply_bc(examg_stokes *s, int level);
+int examg_stokes_smooth_color(examg_stokes *s, int level, int c0, int c1);   /* one of the nine colours  */
+int examg_stokes_smooth(examg_stokes *s, int level, int nsweeps);  /* nsweeps x { nine colours; apply bc } */
+/* UpdateResidual_{u,v,p}; norms_out (nullable) = NormResidual_{u,v,p}: sqrt of the sums of squares (synchronises) */
+int examg_stokes_residual(examg_stokes *s, int level, double *norms_out);
+int examg_stokes_restrict(examg_stokes *s, int level);      /* rhs_*@coarser = Restriction{FaceX,FaceY,Cell} * residual_* */
+int examg_stokes_set_solution(examg_stokes *s, int level, double value);  /* loop points and one layer around */
+int examg_stokes_correct(examg_stokes *s, int level);       /* u, v, p += Correction * (u, v, p)@coarser; apply bc */
+int examg_stokes_vcycle(examg_stokes *s, int level);        /* VCycle@level (< 0: finest)                 */
+
 /* ---- multi-GPU plumbing (one process per GPU) ---------------------------------
  * Peers are wired by exchanging opaque blobs through the host's process group
  * (torch.distributed / MPI): every rank exports a blob, all blobs are gathered
