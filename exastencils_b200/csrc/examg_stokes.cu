@@ -1,25 +1,26 @@
-// examg_stokes.cu -- staggered-grid Stokes: face-centred velocities, cell-centred pressure, and the mixed-localisation
-// 5 x 5 "Vanka" smoother of the reference's Stokes programs.
+// examg_stokes.cu -- staggered-grid Stokes in 2D and 3D: face-centred velocities, cell-centred pressure, and the
+// mixed-localisation (2 dim + 1) x (2 dim + 1) "Vanka" smoother of the reference's Stokes programs.
 //
-// Reference program: Testing/Application/ExaStokes_2D.exa4 (lid-driven cavity; Examples/Stokes/2D_FD_Stokes_fromL4.exa4 has
-// the same loops):
-//   Field u < Face_x >, v < Face_y >, p < Cell >, rhs_*, residual_*                          ...exa4:3-45
-//   Smoother    color with { i0 % 3, i1 % 3 } loop over p { solve locally { u@[0,0], u@[1,0], v@[0,0], v@[0,1], p@[0,0] } }
-//               communicate; apply bc                                                         ...exa4:228-303
+// Reference programs: Testing/Application/ExaStokes_2D.exa4 and ExaStokes_3D.exa4 (lid-driven cavity;
+// Examples/Stokes/{2D,3D}_FD_Stokes_fromL4.exa4 have the same loops):
+//   Field u < Face_x >, v < Face_y > [, w < Face_z >], p < Cell >, rhs_*, residual_*            2D:3-45, 3D:3-52
+//   Smoother    color with { i0 % 3, i1 % 3 [, i2 % 3] } loop over p { solve locally { the two faces of the cell in
+//               every dimension, p@[0,0] } }; communicate; apply bc                               2D:228-303, 3D:272-381
 //               -> C/s/e/solver/ir/IR_LocalSolve.scala:88-236, IR_LocalDirectInvert.scala:44-150 (identity rows for
 //               unknowns that are no valid computation points: IR_IsOnBoundary.scala:53-97)
-//   UpdateResidual_{u,v,p}, Restriction / Correction with the default 'linear' operators of each localisation
+//   UpdateResidual_*, Restriction / Correction with the default 'linear' operators of each localisation
 //               (C/s/e/operator/l4/L4_DefaultRestriction.scala:29-47,79-100, L4_DefaultProlongation.scala:30-45),
 //               SetSolution, apply bc on face fields (C/s/e/boundary/ir/IR_BoundaryCondition.scala:38-45,
-//               IR_ApplyBCFunction.scala:55-88), V(3,3) cycle with 10 smoother steps at the bottom   ...exa4:206-226
+//               IR_ApplyBCFunction.scala:55-88), V(3,3) cycle with 10 smoother steps at the bottom
 // Loop ranges per localisation: C/s/e/baseExt/ir/IR_LoopOverPointsInOneFragment.scala:76-112 (node-like dimensions skip the
 // physical boundary node, cell-like ones cover all cells).
 //
-// Layout: every field of a level is an (n+3) x (n+3) array of doubles, entry (i, j) at (i+1) + (n+3)(j+1): u uses
-// i = -1..n+1 (faces 0..n, walls at 0 and n), j = -1..n; v the transpose; p -1..n in both -- one ghost layer each.
+// Layout: every field of a level is an (n+3)^dim array of doubles, entry (i, j, k) at (i+1) + (n+3)(j+1) + (n+3)^2 (k+1):
+// velocity component d uses the faces 0..n in dimension d (walls at 0 and n) and the cells 0..n-1 in the others, p the
+// cells; one ghost layer around each.
 // Arithmetic contract = oracle/examg_oracle_stokes.c, bit for bit: fma chains in declaration order, the local system by
 // Gaussian elimination without pivoting in row order and back substitution (built with --fmad=false).
-// One block (one GPU); the grids of the reference test (256^2 cells on the finest level) live in L2.
+// One block (one GPU).
 #include <cmath>
 #include <cstdlib>
 #include <vector>
@@ -31,7 +32,9 @@ using namespace examg;
 namespace {
 
 struct StLevel {
-  int n, pitch;
+  int n;
+  long long s[3];  // strides (s[2] = 0 in 2D)
+  size_t size;
   double h;
   double *f[EXAMG_ST_NFIELDS];
 };
@@ -41,9 +44,10 @@ struct StLevel {
 struct examg_stokes {
   examg_ctx *c = nullptr;
   examg_stokes_desc desc;
+  int dim = 2;
   std::vector<StLevel> lev;
-  dd *partials = nullptr;  // [3][ST_RED_BLOCKS]
-  dd *sums = nullptr;      // [3]
+  dd *partials = nullptr;  // [4][ST_RED_BLOCKS]
+  dd *sums = nullptr;      // [4]
   // VCycle@finest as one CUDA graph (542 kernels of a few microseconds each at 256^2 cells: launch-bound otherwise);
   // EXAMG_NO_GRAPH=1 launches them one by one
   cudaGraphExec_t graph = nullptr;
@@ -55,238 +59,290 @@ namespace {
 constexpr int ST_RED_BLOCKS = 256;
 
 struct StArgs {
-  int n, pitch;
+  int n;
+  long long s[3];
   double c0, cx, ih;
-  double *u, *v, *p;
-  const double *fu, *fv, *fp;
-  double *ru, *rv, *rp;
+  double *vel[3], *p;
+  double *fvel[3], *fp;  // right-hand sides
+  double *rvel[3], *rp;  // residuals
 };
 
-__device__ __forceinline__ double st_lap(const double *w, long long q, int sy, double c0, double cx) {
-  double acc = c0 * w[q];
-  acc = fma(cx, w[q - 1], acc);
-  acc = fma(cx, w[q + 1], acc);
-  acc = fma(cx, w[q - sy], acc);
-  acc = fma(cx, w[q + sy], acc);
+template <int D>
+__device__ __forceinline__ long long st_at(const StArgs &a, int i, int j, int k) {
+  return (i + 1) + a.s[1] * (j + 1) + (D == 3 ? a.s[2] * (k + 1) : 0);
+}
+
+// Laplace * w at q: acc = c0*w; fma in declaration order -x, +x, -y, +y[, -z, +z]
+template <int D>
+__device__ __forceinline__ double st_lap(const StArgs &a, const double *w, long long q) {
+  double acc = a.c0 * w[q];
+#pragma unroll
+  for (int e = 0; e < D; ++e) {
+    acc = fma(a.cx, w[q - a.s[e]], acc);
+    acc = fma(a.cx, w[q + a.s[e]], acc);
+  }
   return acc;
 }
 
-// one colour: cells i = col0 + 3 a, j = col1 + 3 b
-__global__ void __launch_bounds__(128) k_st_smooth_color(const StArgs a, int col0, int col1, int na, int nb) {
-  const int ta = blockIdx.x * blockDim.x + threadIdx.x, tb = blockIdx.y * blockDim.y + threadIdx.y;
-  if (ta >= na || tb >= nb) return;
-  const int i = col0 + 3 * ta, j = col1 + 3 * tb, n = a.n, sy = a.pitch;
-  const long long q = (i + 1) + (long long)sy * (j + 1);
+// one colour: cells col[d] + 3 t_d.  Unknowns 2d, 2d+1 = the faces of the cell in dimension d, last = p.
+// The oracle eliminates the dense (2D+1)^2 matrix; here only the entries that can be non-zero are kept -- per dimension
+// the 2 x 2 block of the two faces, their column of p and their entries of the last row (aa ab ap / ba bb bp / la lb),
+// plus the diagonal of p.  Eliminating with a multiplier 0 leaves a row bit for bit as it was (fma(-0, x, y) = y), and no
+// fill leaves this pattern, so the result equals the dense elimination in row order exactly; the identity rows of wall
+// faces only add zeros.  (The dense form put the 7 x 7 matrix of the 3D program into local memory: 464 B of stack.)
+template <int D>
+__global__ void __launch_bounds__(128)
+k_st_smooth_color(const StArgs a, int col0, int col1, int col2, int na, int nb, int nc) {
+  const int ta = blockIdx.x * blockDim.x + threadIdx.x, tb = blockIdx.y * blockDim.y + threadIdx.y, tc = blockIdx.z;
+  if (ta >= na || tb >= nb || tc >= nc) return;
+  const int idx[3] = {col0 + 3 * ta, col1 + 3 * tb, D == 3 ? col2 + 3 * tc : 0};
+  const int n = a.n;
+  const long long q = st_at<D>(a, idx[0], idx[1], idx[2]);
   const double c0 = a.c0, cx = a.cx, ih = a.ih;
-  double *u = a.u, *v = a.v, *p = a.p;
-  const bool ok[5] = {i >= 1, i + 1 <= n - 1, j >= 1, j + 1 <= n - 1, true};
-  double A[5][5] = {{c0, cx, 0, 0, -ih}, {cx, c0, 0, 0, ih}, {0, 0, c0, cx, -ih}, {0, 0, cx, c0, ih}, {-ih, ih, -ih, ih, 0}};
-  double f[5];
-  f[0] = a.fu[q];
-  f[0] = fma(-cx, u[q - 1], f[0]);
-  f[0] = fma(-cx, u[q - sy], f[0]);
-  f[0] = fma(-cx, u[q + sy], f[0]);
-  f[0] = fma(-ih, p[q - 1], f[0]);
-  f[1] = a.fu[q + 1];
-  f[1] = fma(-cx, u[q + 2], f[1]);
-  f[1] = fma(-cx, u[q + 1 - sy], f[1]);
-  f[1] = fma(-cx, u[q + 1 + sy], f[1]);
-  f[1] = fma(ih, p[q + 1], f[1]);
-  f[2] = a.fv[q];
-  f[2] = fma(-cx, v[q - 1], f[2]);
-  f[2] = fma(-cx, v[q + 1], f[2]);
-  f[2] = fma(-cx, v[q - sy], f[2]);
-  f[2] = fma(-ih, p[q - sy], f[2]);
-  f[3] = a.fv[q + sy];
-  f[3] = fma(-cx, v[q + sy - 1], f[3]);
-  f[3] = fma(-cx, v[q + sy + 1], f[3]);
-  f[3] = fma(-cx, v[q + 2 * sy], f[3]);
-  f[3] = fma(ih, p[q + sy], f[3]);
-  f[4] = a.fp[q];
-  const double cur[5] = {u[q], u[q + 1], v[q], v[q + sy], p[q]};
+  double aa[D], ab[D], ap[D], ba[D], bb[D], bp[D], la[D], lb[D], fa[D], fb[D];
+  bool oka[D], okb[D];
 #pragma unroll
-  for (int k = 0; k < 5; ++k)
-    if (!ok[k]) {
+  for (int d = 0; d < D; ++d) {
+    const double *w = a.vel[d];
+    const double *fw = a.fvel[d];
+    const long long sd = a.s[d];
+    oka[d] = idx[d] >= 1;
+    okb[d] = idx[d] + 1 <= n - 1;
+    double ta_ = fw[q], tb_ = fw[q + sd];
 #pragma unroll
-      for (int cc = 0; cc < 5; ++cc) A[k][cc] = cc == k ? 1.0 : 0.0;
-      f[k] = cur[k];
+    for (int e = 0; e < D; ++e) {
+      const long long se = a.s[e];
+      ta_ = fma(-cx, w[q - se], ta_);
+      if (e != d) ta_ = fma(-cx, w[q + se], ta_);
+      if (e != d) tb_ = fma(-cx, w[q + sd - se], tb_);
+      tb_ = fma(-cx, w[q + sd + se], tb_);
     }
-#pragma unroll
-  for (int k = 0; k < 5; ++k)
-#pragma unroll
-    for (int r = k + 1; r < 5; ++r) {
-      const double m = A[r][k] / A[k][k];
-#pragma unroll
-      for (int cc = k + 1; cc < 5; ++cc) A[r][cc] = fma(-m, A[k][cc], A[r][cc]);
-      f[r] = fma(-m, f[k], f[r]);
-    }
-  double x[5];
-#pragma unroll
-  for (int r = 4; r >= 0; --r) {
-    double t = f[r];
-#pragma unroll
-    for (int cc = r + 1; cc < 5; ++cc) t = fma(-A[r][cc], x[cc], t);
-    x[r] = t / A[r][r];
+    ta_ = fma(-ih, a.p[q - sd], ta_);
+    tb_ = fma(ih, a.p[q + sd], tb_);
+    // rows of wall faces: identity, right-hand side = the current value
+    aa[d] = oka[d] ? c0 : 1.0; ab[d] = oka[d] ? cx : 0.0; ap[d] = oka[d] ? -ih : 0.0; fa[d] = oka[d] ? ta_ : w[q];
+    ba[d] = okb[d] ? cx : 0.0; bb[d] = okb[d] ? c0 : 1.0; bp[d] = okb[d] ? ih : 0.0; fb[d] = okb[d] ? tb_ : w[q + sd];
+    la[d] = -ih;
+    lb[d] = ih;
   }
-  if (ok[0]) u[q] = x[0];
-  if (ok[1]) u[q + 1] = x[1];
-  if (ok[2]) v[q] = x[2];
-  if (ok[3]) v[q + sy] = x[3];
-  p[q] = x[4];
+  double pp = 0.0, fp = a.fp[q];
+#pragma unroll
+  for (int d = 0; d < D; ++d) {
+    {  // pivot row 2d: rows 2d+1 and last
+      const double m = ba[d] / aa[d];
+      bb[d] = fma(-m, ab[d], bb[d]);
+      bp[d] = fma(-m, ap[d], bp[d]);
+      fb[d] = fma(-m, fa[d], fb[d]);
+      const double ml = la[d] / aa[d];
+      lb[d] = fma(-ml, ab[d], lb[d]);
+      pp = fma(-ml, ap[d], pp);
+      fp = fma(-ml, fa[d], fp);
+    }
+    {  // pivot row 2d+1: last row
+      const double ml = lb[d] / bb[d];
+      pp = fma(-ml, bp[d], pp);
+      fp = fma(-ml, fb[d], fp);
+    }
+  }
+  const double xp = fp / pp;
+#pragma unroll
+  for (int d = D - 1; d >= 0; --d) {
+    const double xb = fma(-bp[d], xp, fb[d]) / bb[d];
+    double t = fma(-ab[d], xb, fa[d]);
+    t = fma(-ap[d], xp, t);
+    const double xa = t / aa[d];
+    if (oka[d]) a.vel[d][q] = xa;
+    if (okb[d]) a.vel[d][q + a.s[d]] = xb;
+  }
+  a.p[q] = xp;
 }
 
-// apply bc in the order of the program text, two phases (the corners of the ghost layer are written by both):
-//   u below the finest level (Dirichlet 0.0): phase 0 the wall faces i = 0, n (rows -1..n), phase 1 the ghost rows;
-//   u on the finest level (ApplyBC_u): phase 0 the ghost rows (lid: 2 * top - inner; bottom: - inner), phase 1 the wall
-//   faces (rows 0..n-1);   v (Dirichlet 0.0): phase 0 the ghost columns (2 * 0 - inner), phase 1 the wall faces j = 0, n
-__global__ void __launch_bounds__(256) k_st_bc(const StArgs a, int phase, int lid, double top) {
-  const int t = blockIdx.x * blockDim.x + threadIdx.x - 1;  // -1 .. n+1
-  const int n = a.n, sy = a.pitch;
-  if (t > n + 1) return;
-#define ST_AT(i, j) ((i) + 1 + (long long)sy * ((j) + 1))
-  if ((phase == 0) != (lid != 0)) {  // wall faces of u
-    const bool urow = lid ? (t >= 0 && t <= n - 1) : (t <= n);
-    if (urow) {
-      a.u[ST_AT(0, t)] = 0.0;
-      a.u[ST_AT(n, t)] = 0.0;
-    }
-  } else {  // ghost rows of u
-    if (lid) {
-      a.u[ST_AT(t, n)] = 2.0 * top - a.u[ST_AT(t, n - 1)];
-      a.u[ST_AT(t, -1)] = -a.u[ST_AT(t, 0)];
+// One phase of `apply bc`: for every velocity component one pair of opposite faces (dimension e[d]; -1: nothing).
+// kind 0: wall faces idx[e] = 0, n take 0; kind 1: ghost = g2 - inner; kind 2: ghost = -inner (per side).
+// blockIdx.y = component.  lo / hi: the tangential box (the entry of dimension e is ignored).
+struct StBcPhase {
+  int e[3], kind_lo[3], kind_hi[3];
+  int lo[3][3], hi[3][3];
+  double g2_lo[3], g2_hi[3];
+};
+
+template <int D>
+__global__ void __launch_bounds__(256) k_st_bc(const StArgs a, const __grid_constant__ StBcPhase ph) {
+  const int d = blockIdx.y;
+  const int e = ph.e[d];
+  if (e < 0) return;
+  int ext[3], total = 1;
+#pragma unroll
+  for (int t = 0; t < 3; ++t) {
+    ext[t] = (t < D && t != e) ? ph.hi[d][t] - ph.lo[d][t] + 1 : 1;
+    total *= ext[t];
+  }
+  const int n = a.n;
+  double *w = a.vel[d];
+  for (int t = blockIdx.x * blockDim.x + threadIdx.x; t < 2 * total; t += gridDim.x * blockDim.x) {
+    const int side = t >= total ? 1 : 0;
+    int r = t - side * total, idx[3];
+    idx[0] = ph.lo[d][0] + r % ext[0]; r /= ext[0];
+    idx[1] = ph.lo[d][1] + r % ext[1]; r /= ext[1];
+    idx[2] = D == 3 ? ph.lo[d][2] + r : 0;
+    const int kind = side ? ph.kind_hi[d] : ph.kind_lo[d];
+    idx[e] = kind == 0 ? (side ? n : 0) : (side ? n : -1);
+    const long long q = st_at<D>(a, idx[0], idx[1], idx[2]);
+    if (kind == 0) {
+      w[q] = 0.0;
     } else {
-      a.u[ST_AT(t, -1)] = (2.0 * 0.0) - a.u[ST_AT(t, 0)];
-      a.u[ST_AT(t, n)] = (2.0 * 0.0) - a.u[ST_AT(t, n - 1)];
+      const double inner = side ? w[q - a.s[e]] : w[q + a.s[e]];
+      w[q] = kind == 2 ? -inner : (side ? ph.g2_hi[d] : ph.g2_lo[d]) - inner;
     }
   }
-  if (phase == 0) {
-    a.v[ST_AT(-1, t)] = (2.0 * 0.0) - a.v[ST_AT(0, t)];
-    a.v[ST_AT(n, t)] = (2.0 * 0.0) - a.v[ST_AT(n - 1, t)];
-  } else if (t <= n) {
-    a.v[ST_AT(t, 0)] = 0.0;
-    a.v[ST_AT(t, n)] = 0.0;
-  }
 }
 
+// cell (i, j, k) of thread t in an n^D box
+template <int D>
+__device__ __forceinline__ bool st_cell(int n, int idx[3]) {
+  idx[0] = blockIdx.x * blockDim.x + threadIdx.x;
+  idx[1] = blockIdx.y * blockDim.y + threadIdx.y;
+  idx[2] = D == 3 ? (int)blockIdx.z : 0;
+  return idx[0] < n && idx[1] < n && idx[2] < n;
+}
+
+// UpdateResidual_*: residual_d = rhs_d - ( Laplace * vel_d - d?Left * p ) on the inner faces;
+// residual_p = rhs_p - ( dxRight * u + dyRight * v [+ dzRight * w] )
+template <int D>
 __global__ void __launch_bounds__(256) k_st_residual(const StArgs a) {
-  const int i = blockIdx.x * blockDim.x + threadIdx.x, j = blockIdx.y * blockDim.y + threadIdx.y;
-  const int n = a.n, sy = a.pitch;
-  if (i >= n || j >= n) return;
-  const long long q = ST_AT(i, j);
-  const double c0 = a.c0, cx = a.cx, ih = a.ih;
-  if (i >= 1) {
-    const double dx = fma(ih, a.p[q], (-ih) * a.p[q - 1]);
-    a.ru[q] = a.fu[q] - (st_lap(a.u, q, sy, c0, cx) - dx);
+  int idx[3];
+  if (!st_cell<D>(a.n, idx)) return;
+  const long long q = st_at<D>(a, idx[0], idx[1], idx[2]);
+  const double ih = a.ih;
+  double div = 0.0;
+#pragma unroll
+  for (int d = 0; d < D; ++d) {
+    const double *w = a.vel[d];
+    const long long sd = a.s[d];
+    if (idx[d] >= 1) {
+      const double dl = fma(ih, a.p[q], (-ih) * a.p[q - sd]);
+      a.rvel[d][q] = a.fvel[d][q] - (st_lap<D>(a, w, q) - dl);
+    }
+    const double dr = fma(ih, w[q + sd], (-ih) * w[q]);
+    div = d == 0 ? dr : div + dr;
   }
-  if (j >= 1) {
-    const double dy = fma(ih, a.p[q], (-ih) * a.p[q - sy]);
-    a.rv[q] = a.fv[q] - (st_lap(a.v, q, sy, c0, cx) - dy);
-  }
-  {
-    const double dx = fma(ih, a.u[q + 1], (-ih) * a.u[q]);
-    const double dy = fma(ih, a.v[q + sy], (-ih) * a.v[q]);
-    a.rp[q] = a.fp[q] - (dx + dy);
-  }
+  a.rp[q] = a.fp[q] - div;
 }
 
-// sums of squares of the three residual fields over their loop points
+// sums of squares of the residual fields over their loop points: slots 0..D-1 velocities, D pressure
+template <int D>
 __global__ void __launch_bounds__(256) k_st_norms(const StArgs a, dd *__restrict__ partials) {
-  const int n = a.n, sy = a.pitch;
-  dd su = {0.0, 0.0}, sv = {0.0, 0.0}, sp = {0.0, 0.0};
-  for (long long t = blockIdx.x * (long long)blockDim.x + threadIdx.x; t < (long long)n * n; t += (long long)gridDim.x * blockDim.x) {
-    const int i = (int)(t % n), j = (int)(t / n);
-    const long long q = ST_AT(i, j);
-    if (i >= 1) { const double r = a.ru[q]; dd_add(su, r * r); }
-    if (j >= 1) { const double r = a.rv[q]; dd_add(sv, r * r); }
-    { const double r = a.rp[q]; dd_add(sp, r * r); }
+  const int n = a.n;
+  const long long cells = D == 3 ? (long long)n * n * n : (long long)n * n;
+  dd acc[D + 1];
+#pragma unroll
+  for (int k = 0; k <= D; ++k) acc[k] = dd{0.0, 0.0};
+  for (long long t = blockIdx.x * (long long)blockDim.x + threadIdx.x; t < cells; t += (long long)gridDim.x * blockDim.x) {
+    const int idx[3] = {(int)(t % n), (int)((t / n) % n), (int)(t / ((long long)n * n))};
+    const long long q = st_at<D>(a, idx[0], idx[1], idx[2]);
+#pragma unroll
+    for (int d = 0; d < D; ++d)
+      if (idx[d] >= 1) { const double r = a.rvel[d][q]; dd_add(acc[d], r * r); }
+    const double r = a.rp[q];
+    dd_add(acc[D], r * r);
   }
-  su = dd_block_reduce(su);
-  sv = dd_block_reduce(sv);
-  sp = dd_block_reduce(sp);
-  if (threadIdx.x == 0) {
-    partials[blockIdx.x] = su;
-    partials[ST_RED_BLOCKS + blockIdx.x] = sv;
-    partials[2 * ST_RED_BLOCKS + blockIdx.x] = sp;
+#pragma unroll
+  for (int k = 0; k <= D; ++k) {
+    const dd v = dd_block_reduce(acc[k]);
+    if (threadIdx.x == 0) partials[k * ST_RED_BLOCKS + blockIdx.x] = v;
   }
 }
 
-__global__ void __launch_bounds__(32) k_st_norms_final(const dd *__restrict__ partials, int nblocks, dd *__restrict__ out) {
+__global__ void __launch_bounds__(32) k_st_norms_final(const dd *__restrict__ partials, int nblocks, int nsums, dd *__restrict__ out) {
   const int k = threadIdx.x;
-  if (k >= 3) return;
+  if (k >= nsums) return;
   dd s = {0.0, 0.0};
   for (int b = 0; b < nblocks; ++b) dd_merge(s, partials[k * ST_RED_BLOCKS + b]);
   out[k] = s;
 }
 
-// rhs@coarser = Restriction * residual, one thread per coarse cell (I, J)
-__global__ void __launch_bounds__(256) k_st_restrict(const StArgs f, const StArgs c) {
-  const int I = blockIdx.x * blockDim.x + threadIdx.x, J = blockIdx.y * blockDim.y + threadIdx.y;
-  const int nc = c.n, fy = f.pitch;
-  if (I >= nc || J >= nc) return;
-  const long long q = (2 * I + 1) + (long long)fy * (2 * J + 1);
-  const long long qc = (I + 1) + (long long)c.pitch * (J + 1);
-  if (I >= 1) {
-    double acc = 0.125 * f.ru[q - 1];
-    acc = fma(0.25, f.ru[q], acc);
-    acc = fma(0.125, f.ru[q + 1], acc);
-    acc = fma(0.125, f.ru[q + fy - 1], acc);
-    acc = fma(0.25, f.ru[q + fy], acc);
-    acc = fma(0.125, f.ru[q + fy + 1], acc);
-    const_cast<double *>(c.fu)[qc] = acc;
-  }
-  if (J >= 1) {
-    double acc = 0.125 * f.rv[q - fy];
-    acc = fma(0.125, f.rv[q - fy + 1], acc);
-    acc = fma(0.25, f.rv[q], acc);
-    acc = fma(0.25, f.rv[q + 1], acc);
-    acc = fma(0.125, f.rv[q + fy], acc);
-    acc = fma(0.125, f.rv[q + fy + 1], acc);
-    const_cast<double *>(c.fv)[qc] = acc;
-  }
-  {
-    double acc = 0.25 * f.rp[q];
-    acc = fma(0.25, f.rp[q + 1], acc);
-    acc = fma(0.25, f.rp[q + fy], acc);
-    acc = fma(0.25, f.rp[q + fy + 1], acc);
-    const_cast<double *>(c.fp)[qc] = acc;
-  }
+// Restriction_<loc> * src at the coarse index I: kron of [1/4 1/2 1/4] (fine 2I-1..2I+1) in dimension OWN (OWN < 0:
+// none) and [1/2 1/2] (fine 2I, 2I+1) in the others; entries in lexicographic order (x fastest), fma chain
+template <int D, int OWN>
+__device__ __forceinline__ double st_restrict_point(const StArgs &f, const double *src, const int I[3]) {
+  constexpr int c0 = OWN == 0 ? 3 : 2, c1 = OWN == 1 ? 3 : 2, c2 = D == 3 ? (OWN == 2 ? 3 : 2) : 1;
+  double acc = 0.0;
+#pragma unroll
+  for (int c = 0; c < c2; ++c)
+#pragma unroll
+    for (int b = 0; b < c1; ++b)
+#pragma unroll
+      for (int a = 0; a < c0; ++a) {
+        const int ox = (OWN == 0 ? -1 : 0) + a, oy = (OWN == 1 ? -1 : 0) + b, oz = (OWN == 2 ? -1 : 0) + c;
+        double wgt = OWN == 0 ? (ox == 0 ? 0.5 : 0.25) : 0.5;
+        wgt *= OWN == 1 ? (oy == 0 ? 0.5 : 0.25) : 0.5;
+        if (D == 3) wgt *= OWN == 2 ? (oz == 0 ? 0.5 : 0.25) : 0.5;
+        const double v = src[st_at<D>(f, 2 * I[0] + ox, 2 * I[1] + oy, D == 3 ? 2 * I[2] + oz : 0)];
+        acc = (a == 0 && b == 0 && c == 0) ? wgt * v : fma(wgt, v, acc);
+      }
+  return acc;
 }
 
-// SetSolution ( value ): the loop points of u, v, p and one layer around
+// rhs@coarser = Restriction * residual, one thread per coarse cell
+template <int D>
+__global__ void __launch_bounds__(256) k_st_restrict(const StArgs f, const StArgs c) {
+  int I[3];
+  if (!st_cell<D>(c.n, I)) return;
+  const long long qc = st_at<D>(c, I[0], I[1], I[2]);
+  if (I[0] >= 1) c.fvel[0][qc] = st_restrict_point<D, 0>(f, f.rvel[0], I);
+  if (I[1] >= 1) c.fvel[1][qc] = st_restrict_point<D, 1>(f, f.rvel[1], I);
+  if (D == 3 && I[2] >= 1) c.fvel[2][qc] = st_restrict_point<D, 2>(f, f.rvel[2], I);
+  c.fp[qc] = st_restrict_point<D, -1>(f, f.rp, I);
+}
+
+// SetSolution ( value ): the loop points of the unknowns and one layer around
+template <int D>
 __global__ void __launch_bounds__(256) k_st_set(const StArgs a, double value) {
-  const int i = (int)(blockIdx.x * blockDim.x + threadIdx.x) - 1, j = (int)(blockIdx.y * blockDim.y + threadIdx.y) - 1;
-  const int n = a.n, sy = a.pitch;
-  if (i > n || j > n) return;
-  const long long q = ST_AT(i, j);
-  if (i >= 0) a.u[q] = value;
-  if (j >= 0) a.v[q] = value;
+  int idx[3];
+  if (!st_cell<D>(a.n + 2, idx)) return;
+#pragma unroll
+  for (int t = 0; t < D; ++t) idx[t] -= 1;
+  const long long q = st_at<D>(a, idx[0], idx[1], idx[2]);
+#pragma unroll
+  for (int d = 0; d < D; ++d)
+    if (idx[d] >= 0) a.vel[d][q] = value;
   a.p[q] = value;
 }
 
-// dest += Correction * source@coarser, one thread per fine cell (i, j)
+// dest += Correction * source@coarser, one thread per fine cell: linear in the component's own dimension, constant in
+// the others; p takes the parent's value
+template <int D>
 __global__ void __launch_bounds__(256) k_st_correct(const StArgs f, const StArgs c) {
-  const int i = blockIdx.x * blockDim.x + threadIdx.x, j = blockIdx.y * blockDim.y + threadIdx.y;
-  const int n = f.n, sy = f.pitch, cy = c.pitch;
-  if (i >= n || j >= n) return;
-  const long long q = ST_AT(i, j);
-  const long long qc = ((i >> 1) + 1) + (long long)cy * ((j >> 1) + 1);
-  if (i >= 1) f.u[q] = (i & 1) ? fma(0.5, c.u[qc] + c.u[qc + 1], f.u[q]) : fma(1.0, c.u[qc], f.u[q]);
-  if (j >= 1) f.v[q] = (j & 1) ? fma(0.5, c.v[qc] + c.v[qc + cy], f.v[q]) : fma(1.0, c.v[qc], f.v[q]);
+  int idx[3];
+  if (!st_cell<D>(f.n, idx)) return;
+  const long long q = st_at<D>(f, idx[0], idx[1], idx[2]);
+  const long long qc = st_at<D>(c, idx[0] >> 1, idx[1] >> 1, idx[2] >> 1);
+#pragma unroll
+  for (int d = 0; d < D; ++d)
+    if (idx[d] >= 1) {
+      const double *wc = c.vel[d];
+      f.vel[d][q] = (idx[d] & 1) ? fma(0.5, wc[qc] + wc[qc + c.s[d]], f.vel[d][q]) : fma(1.0, wc[qc], f.vel[d][q]);
+    }
   f.p[q] = fma(1.0, c.p[qc], f.p[q]);
 }
-#undef ST_AT
 
-StArgs st_args(const StLevel &L) {
+StArgs st_args(const examg_stokes *s, const StLevel &L) {
   StArgs a;
   a.n = L.n;
-  a.pitch = L.pitch;
   const double h = L.h;
   a.c0 = 2.0 / (h * h) + 2.0 / (h * h);
+  if (s->dim == 3) a.c0 = a.c0 + 2.0 / (h * h);
   a.cx = -1.0 / (h * h);
   a.ih = 1.0 / h;
-  a.u = L.f[EXAMG_ST_U]; a.v = L.f[EXAMG_ST_V]; a.p = L.f[EXAMG_ST_P];
-  a.fu = L.f[EXAMG_ST_RHS_U]; a.fv = L.f[EXAMG_ST_RHS_V]; a.fp = L.f[EXAMG_ST_RHS_P];
-  a.ru = L.f[EXAMG_ST_RES_U]; a.rv = L.f[EXAMG_ST_RES_V]; a.rp = L.f[EXAMG_ST_RES_P];
+  for (int d = 0; d < 3; ++d) {
+    a.s[d] = L.s[d];
+    a.vel[d] = L.f[EXAMG_ST_VEL + d];
+    a.fvel[d] = L.f[EXAMG_ST_RHS + d];
+    a.rvel[d] = L.f[EXAMG_ST_RES + d];
+  }
+  a.p = L.f[EXAMG_ST_P];
+  a.fp = L.f[EXAMG_ST_RHS_P];
+  a.rp = L.f[EXAMG_ST_RES_P];
   return a;
 }
 
@@ -298,7 +354,21 @@ StLevel *st_level(examg_stokes *s, int level) {
   return &s->lev[level - lo];
 }
 
-dim3 grid2(int nx, int ny, dim3 block) { return dim3((nx + block.x - 1) / block.x, (ny + block.y - 1) / block.y, 1); }
+bool st_field_ok(const examg_stokes *s, int which) {
+  if (which < 0 || which >= EXAMG_ST_NFIELDS) return false;
+  return which >= EXAMG_ST_P || which % 3 < s->dim;
+}
+
+// one thread per cell of an m^dim box: blocks of 32 x 8, z in the grid
+dim3 st_grid(int dim, int m) { return dim3((m + 31) / 32, (m + 7) / 8, dim == 3 ? m : 1); }
+const dim3 ST_BLOCK(32, 8, 1);
+
+#define ST_DISPATCH(s, KERNEL, GRID, BLOCK, ...)                                            \
+  do {                                                                                      \
+    if ((s)->dim == 3) KERNEL<3><<<GRID, BLOCK, 0, (s)->c->stream>>>(__VA_ARGS__);           \
+    else KERNEL<2><<<GRID, BLOCK, 0, (s)->c->stream>>>(__VA_ARGS__);                         \
+    EXAMG_LAUNCH_CHECK((s)->c);                                                             \
+  } while (0)
 
 }  // namespace
 
@@ -306,32 +376,44 @@ extern "C" {
 
 examg_stokes *examg_stokes_create(examg_ctx *c, const examg_stokes_desc *d) {
   if (!c || !d) { set_error(EXAMG_EINVAL, "examg_stokes_create: null argument"); return nullptr; }
-  if (c->cfg.dim != 2 || c->world != 1 || c->periodic_any) {
-    set_error(EXAMG_EUNSUP, "examg_stokes_create: 2D, one block, no periodic dimension");
+  if (c->world != 1 || c->periodic_any) {
+    set_error(EXAMG_EUNSUP, "examg_stokes_create: one block, no periodic dimension");
     return nullptr;
   }
-  if (c->cfg.block_cells[0] != c->cfg.block_cells[1] || c->cfg.min_level + (c->cfg.block_cells[0] > 1 ? 1 : 0) < 1) {
-    set_error(EXAMG_EUNSUP, "examg_stokes_create: square grids with at least 2 cells per dimension on the coarsest level");
+  const int dim = c->cfg.dim;
+  for (int t = 1; t < dim; ++t)
+    if (c->cfg.block_cells[t] != c->cfg.block_cells[0]) {
+      set_error(EXAMG_EUNSUP, "examg_stokes_create: the same number of cells in every dimension");
+      return nullptr;
+    }
+  if ((c->cfg.block_cells[0] << c->cfg.min_level) < 2) {
+    set_error(EXAMG_EUNSUP, "examg_stokes_create: at least 2 cells per dimension on the coarsest level");
     return nullptr;
   }
   if (d->nu_pre < 0 || d->nu_post < 0 || d->nu_coarse < 0) { set_error(EXAMG_EINVAL, "examg_stokes_create: negative sweep count"); return nullptr; }
   examg_stokes *s = new examg_stokes;
   s->c = c;
   s->desc = *d;
+  s->dim = dim;
   bool ok = true;
   for (int level = c->cfg.min_level; level <= c->cfg.max_level && ok; ++level) {
     StLevel L;
     L.n = c->cfg.block_cells[0] << level;
-    L.pitch = L.n + 3;
+    const long long m = L.n + 3;
+    L.s[0] = 1;
+    L.s[1] = m;
+    L.s[2] = dim == 3 ? m * m : 0;
+    L.size = (size_t)(dim == 3 ? m * m * m : m * m);
     L.h = (c->cfg.domain_hi[0] - c->cfg.domain_lo[0]) / (double)L.n;
-    const size_t bytes = sizeof(double) * (size_t)L.pitch * (size_t)L.pitch;
     for (int k = 0; k < EXAMG_ST_NFIELDS; ++k) {
       L.f[k] = nullptr;
-      ok = ok && cudaMalloc(&L.f[k], bytes) == cudaSuccess && cudaMemsetAsync(L.f[k], 0, bytes, c->stream) == cudaSuccess;
+      if (!st_field_ok(s, k)) continue;
+      ok = ok && cudaMalloc(&L.f[k], sizeof(double) * L.size) == cudaSuccess &&
+           cudaMemsetAsync(L.f[k], 0, sizeof(double) * L.size, c->stream) == cudaSuccess;
     }
     s->lev.push_back(L);
   }
-  ok = ok && cudaMalloc(&s->partials, sizeof(dd) * 3 * ST_RED_BLOCKS) == cudaSuccess && cudaMalloc(&s->sums, sizeof(dd) * 3) == cudaSuccess;
+  ok = ok && cudaMalloc(&s->partials, sizeof(dd) * 4 * ST_RED_BLOCKS) == cudaSuccess && cudaMalloc(&s->sums, sizeof(dd) * 4) == cudaSuccess;
   if (!ok) {
     set_error(EXAMG_ECUDA, "examg_stokes_create: device allocation failed");
     examg_stokes_destroy(s);
@@ -360,8 +442,8 @@ int examg_stokes_cells(examg_stokes *s, int level) {
 int examg_stokes_upload(examg_stokes *s, int level, int which, const double *host) {
   StLevel *L = st_level(s, level);
   if (!L) return EXAMG_EINVAL;
-  if (which < 0 || which >= EXAMG_ST_NFIELDS || !host) return set_error(EXAMG_EINVAL, "examg_stokes_upload: field %d", which);
-  EXAMG_CUDA(cudaMemcpyAsync(L->f[which], host, sizeof(double) * (size_t)L->pitch * L->pitch, cudaMemcpyHostToDevice, s->c->stream));
+  if (!st_field_ok(s, which) || !host) return set_error(EXAMG_EINVAL, "examg_stokes_upload: field %d", which);
+  EXAMG_CUDA(cudaMemcpyAsync(L->f[which], host, sizeof(double) * L->size, cudaMemcpyHostToDevice, s->c->stream));
   EXAMG_CUDA(cudaStreamSynchronize(s->c->stream));
   return EXAMG_OK;
 }
@@ -369,8 +451,8 @@ int examg_stokes_upload(examg_stokes *s, int level, int which, const double *hos
 int examg_stokes_download(examg_stokes *s, int level, int which, double *host) {
   StLevel *L = st_level(s, level);
   if (!L) return EXAMG_EINVAL;
-  if (which < 0 || which >= EXAMG_ST_NFIELDS || !host) return set_error(EXAMG_EINVAL, "examg_stokes_download: field %d", which);
-  EXAMG_CUDA(cudaMemcpyAsync(host, L->f[which], sizeof(double) * (size_t)L->pitch * L->pitch, cudaMemcpyDeviceToHost, s->c->stream));
+  if (!st_field_ok(s, which) || !host) return set_error(EXAMG_EINVAL, "examg_stokes_download: field %d", which);
+  EXAMG_CUDA(cudaMemcpyAsync(host, L->f[which], sizeof(double) * L->size, cudaMemcpyDeviceToHost, s->c->stream));
   EXAMG_CUDA(cudaStreamSynchronize(s->c->stream));
   return EXAMG_OK;
 }
@@ -379,36 +461,63 @@ int examg_stokes_apply_bc(examg_stokes *s, int level) {
   StLevel *L = st_level(s, level);
   if (!L) return EXAMG_EINVAL;
   examg_ctx *c = s->c;
-  const StArgs a = st_args(*L);
-  const int lid = (level < 0 || level == c->cfg.max_level) ? 1 : 0;
-  const int blocks = (L->n + 3 + 255) / 256;
-  for (int phase = 0; phase < 2; ++phase) {
-    k_st_bc<<<blocks, 256, 0, c->stream>>>(a, phase, lid, s->desc.top_vel);
-    EXAMG_LAUNCH_CHECK(c);
+  const StArgs a = st_args(s, *L);
+  const int n = L->n, dim = s->dim;
+  const bool lid = level < 0 || level == c->cfg.max_level;
+  // phase ph: component d handles the faces of dimension ph (Dirichlet 0.0, faces in the order -x,+x,-y,+y,-z,+z); u on
+  // the finest level follows ApplyBC_u instead: phase 0 the ghost rows in y (lid on top), phase 1 the wall faces in x
+  for (int ph = 0; ph < dim; ++ph) {
+    StBcPhase p;
+    for (int d = 0; d < 3; ++d) {
+      p.e[d] = d < dim ? ph : -1;
+      p.kind_lo[d] = p.kind_hi[d] = ph == d ? 0 : 1;
+      p.g2_lo[d] = p.g2_hi[d] = 2.0 * 0.0;
+      for (int t = 0; t < 3; ++t) { p.lo[d][t] = -1; p.hi[d][t] = t == d ? n + 1 : n; }
+    }
+    if (lid) {
+      if (ph == 0) {
+        p.e[0] = 1; p.kind_lo[0] = 2; p.kind_hi[0] = 1; p.g2_hi[0] = 2.0 * s->desc.top_vel;
+        p.lo[0][0] = -1; p.hi[0][0] = n + 1; p.lo[0][2] = -1; p.hi[0][2] = n;
+      } else if (ph == 1) {
+        p.e[0] = 0; p.kind_lo[0] = p.kind_hi[0] = 0;
+        for (int t = 0; t < 3; ++t) { p.lo[0][t] = 0; p.hi[0][t] = n - 1; }
+      } else {
+        p.e[0] = -1;
+      }
+    }
+    long long pts = 2;
+    for (int t = 0; t < dim - 1; ++t) pts *= n + 3;
+    int bx = (int)((pts + 255) / 256);
+    if (bx > 1024) bx = 1024;
+    ST_DISPATCH(s, k_st_bc, dim3(bx, dim, 1), 256, a, p);
   }
   return EXAMG_OK;
 }
 
-int examg_stokes_smooth_color(examg_stokes *s, int level, int c0, int c1) {
+int examg_stokes_smooth_color(examg_stokes *s, int level, int c0, int c1, int c2) {
   StLevel *L = st_level(s, level);
   if (!L) return EXAMG_EINVAL;
-  if (c0 < 0 || c0 > 2 || c1 < 0 || c1 > 2) return set_error(EXAMG_EINVAL, "examg_stokes_smooth_color: colour (%d, %d)", c0, c1);
-  examg_ctx *c = s->c;
-  const int na = L->n > c0 ? (L->n - c0 + 2) / 3 : 0, nb = L->n > c1 ? (L->n - c1 + 2) / 3 : 0;
-  if (na <= 0 || nb <= 0) return EXAMG_OK;
-  const dim3 block(32, 4, 1);
-  k_st_smooth_color<<<grid2(na, nb, block), block, 0, c->stream>>>(st_args(*L), c0, c1, na, nb);
-  EXAMG_LAUNCH_CHECK(c);
+  if (c0 < 0 || c0 > 2 || c1 < 0 || c1 > 2 || c2 < 0 || c2 > (s->dim == 3 ? 2 : 0))
+    return set_error(EXAMG_EINVAL, "examg_stokes_smooth_color: colour (%d, %d, %d)", c0, c1, c2);
+  const int n = L->n;
+  const int na = n > c0 ? (n - c0 + 2) / 3 : 0, nb = n > c1 ? (n - c1 + 2) / 3 : 0;
+  const int nc = s->dim == 3 ? (n > c2 ? (n - c2 + 2) / 3 : 0) : 1;
+  if (na <= 0 || nb <= 0 || nc <= 0) return EXAMG_OK;
+  const dim3 block(32, 4, 1), grid((na + 31) / 32, (nb + 3) / 4, nc);
+  ST_DISPATCH(s, k_st_smooth_color, grid, block, st_args(s, *L), c0, c1, c2, na, nb, nc);
   return EXAMG_OK;
 }
 
 int examg_stokes_smooth(examg_stokes *s, int level, int nsweeps) {
+  if (!s) return set_error(EXAMG_EINVAL, "null Stokes solver");
+  const int nz = s->dim == 3 ? 3 : 1;
   for (int it = 0; it < nsweeps; ++it) {
-    for (int c1 = 0; c1 < 3; ++c1)
-      for (int c0 = 0; c0 < 3; ++c0) {
-        const int rc = examg_stokes_smooth_color(s, level, c0, c1);
-        if (rc) return rc;
-      }
+    for (int c2 = 0; c2 < nz; ++c2)
+      for (int c1 = 0; c1 < 3; ++c1)
+        for (int c0 = 0; c0 < 3; ++c0) {
+          const int rc = examg_stokes_smooth_color(s, level, c0, c1, c2);
+          if (rc) return rc;
+        }
     const int rc = examg_stokes_apply_bc(s, level);
     if (rc) return rc;
   }
@@ -419,21 +528,19 @@ int examg_stokes_residual(examg_stokes *s, int level, double *norms_out) {
   StLevel *L = st_level(s, level);
   if (!L) return EXAMG_EINVAL;
   examg_ctx *c = s->c;
-  const StArgs a = st_args(*L);
-  const dim3 block(32, 8, 1);
-  k_st_residual<<<grid2(L->n, L->n, block), block, 0, c->stream>>>(a);
-  EXAMG_LAUNCH_CHECK(c);
+  const StArgs a = st_args(s, *L);
+  ST_DISPATCH(s, k_st_residual, st_grid(s->dim, L->n), ST_BLOCK, a);
   if (!norms_out) return EXAMG_OK;
-  long long nb = ((long long)L->n * L->n + 255) / 256;
+  long long cells = (long long)L->n * L->n * (s->dim == 3 ? L->n : 1);
+  long long nb = (cells + 255) / 256;
   if (nb > ST_RED_BLOCKS) nb = ST_RED_BLOCKS;
-  k_st_norms<<<(int)nb, 256, 0, c->stream>>>(a, s->partials);
+  ST_DISPATCH(s, k_st_norms, (int)nb, 256, a, s->partials);
+  k_st_norms_final<<<1, 32, 0, c->stream>>>(s->partials, (int)nb, s->dim + 1, s->sums);
   EXAMG_LAUNCH_CHECK(c);
-  k_st_norms_final<<<1, 32, 0, c->stream>>>(s->partials, (int)nb, s->sums);
-  EXAMG_LAUNCH_CHECK(c);
-  dd host[3];
-  EXAMG_CUDA(cudaMemcpyAsync(host, s->sums, sizeof(host), cudaMemcpyDeviceToHost, c->stream));
+  dd host[4];
+  EXAMG_CUDA(cudaMemcpyAsync(host, s->sums, sizeof(dd) * (s->dim + 1), cudaMemcpyDeviceToHost, c->stream));
   EXAMG_CUDA(cudaStreamSynchronize(c->stream));
-  for (int k = 0; k < 3; ++k) norms_out[k] = sqrt(host[k].hi + host[k].lo);
+  for (int k = 0; k <= s->dim; ++k) norms_out[k] = sqrt(host[k].hi + host[k].lo);
   return EXAMG_OK;
 }
 
@@ -442,18 +549,14 @@ int examg_stokes_restrict(examg_stokes *s, int level) {
   if (!F) return EXAMG_EINVAL;
   if (F == &s->lev[0]) return set_error(EXAMG_EINVAL, "examg_stokes_restrict: no level below the coarsest");
   StLevel *C = F - 1;
-  const dim3 block(32, 8, 1);
-  k_st_restrict<<<grid2(C->n, C->n, block), block, 0, s->c->stream>>>(st_args(*F), st_args(*C));
-  EXAMG_LAUNCH_CHECK(s->c);
+  ST_DISPATCH(s, k_st_restrict, st_grid(s->dim, C->n), ST_BLOCK, st_args(s, *F), st_args(s, *C));
   return EXAMG_OK;
 }
 
 int examg_stokes_set_solution(examg_stokes *s, int level, double value) {
   StLevel *L = st_level(s, level);
   if (!L) return EXAMG_EINVAL;
-  const dim3 block(32, 8, 1);
-  k_st_set<<<grid2(L->n + 2, L->n + 2, block), block, 0, s->c->stream>>>(st_args(*L), value);
-  EXAMG_LAUNCH_CHECK(s->c);
+  ST_DISPATCH(s, k_st_set, st_grid(s->dim, L->n + 2), ST_BLOCK, st_args(s, *L), value);
   return EXAMG_OK;
 }
 
@@ -462,9 +565,7 @@ int examg_stokes_correct(examg_stokes *s, int level) {
   if (!F) return EXAMG_EINVAL;
   if (F == &s->lev[0]) return set_error(EXAMG_EINVAL, "examg_stokes_correct: no level below the coarsest");
   StLevel *C = F - 1;
-  const dim3 block(32, 8, 1);
-  k_st_correct<<<grid2(F->n, F->n, block), block, 0, s->c->stream>>>(st_args(*F), st_args(*C));
-  EXAMG_LAUNCH_CHECK(s->c);
+  ST_DISPATCH(s, k_st_correct, st_grid(s->dim, F->n), ST_BLOCK, st_args(s, *F), st_args(s, *C));
   return examg_stokes_apply_bc(s, level);
 }
 

@@ -165,7 +165,7 @@ SIGNATURES = {
     "examg_stokes_upload": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_void_p]),
     "examg_stokes_download": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_void_p]),
     "examg_stokes_apply_bc": (C.c_int, [C.c_void_p, C.c_int]),
-    "examg_stokes_smooth_color": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int]),
+    "examg_stokes_smooth_color": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int]),
     "examg_stokes_smooth": (C.c_int, [C.c_void_p, C.c_int, C.c_int]),
     "examg_stokes_residual": (C.c_int, [C.c_void_p, C.c_int, _dp]),
     "examg_stokes_restrict": (C.c_int, [C.c_void_p, C.c_int]),

@@ -392,40 +392,44 @@ int examg_optflow_cycles(examg_optflow *o, int n, double *norm_out); /* n cycles
 int examg_optflow_residual_norm(examg_optflow *o, double *norm_out);
 int examg_optflow_last_cg_iters(examg_optflow *o, int *iters_out);
 
-/* ---- staggered grids: face-centred velocities, cell-centred pressure (2D Stokes) ------------------
- * (Testing/Application/ExaStokes_2D.exa4, Examples/Stokes/2D_FD_Stokes_fromL4.exa4)
- *   Field u < Face_x >, v < Face_y >, p < Cell >; rhs_* and residual_* alike.
- *   Smoother: color with { i0 % 3, i1 % 3 } loop over p { solve locally { u@[0,0], u@[1,0], v@[0,0], v@[0,1], p@[0,0] } }
- *   -- a 5 x 5 local system per cell over three localisations (C/s/e/solver/ir/IR_LocalSolve.scala:88-236,
- *   IR_LocalDirectInvert.scala:44-150; wall faces are identity rows, IR_IsOnBoundary.scala:53-97) -- then apply bc.
- * One block, square grid of block_cells << level cells, levels of the context.  Every field of a level is an
- * (n+3) x (n+3) array, entry (i, j) at (i+1) + (n+3)(j+1), one ghost layer around: u on faces i = 0..n, cells
- * j = 0..n-1; v on i = 0..n-1, j = 0..n; p on the n x n cells.                                              */
+/* ---- staggered grids: face-centred velocities, cell-centred pressure (Stokes, 2D and 3D) -----------
+ * (Testing/Application/ExaStokes_2D.exa4 / ExaStokes_3D.exa4, Examples/Stokes/{2D,3D}_FD_Stokes_fromL4.exa4)
+ *   Field u < Face_x >, v < Face_y > [, w < Face_z >], p < Cell >; rhs_* and residual_* alike.
+ *   Smoother: color with { i0 % 3, i1 % 3 [, i2 % 3] } loop over p { solve locally { the two faces of the cell in every
+ *   dimension, p@[0,0] } } -- a 5 x 5 (7 x 7) local system per cell over three (four) localisations
+ *   (C/s/e/solver/ir/IR_LocalSolve.scala:88-236, IR_LocalDirectInvert.scala:44-150; wall faces are identity rows,
+ *   IR_IsOnBoundary.scala:53-97) -- then apply bc.
+ * One block; dimensionality, level range and block_cells (the same in every dimension) of the context.  Every field of a
+ * level is an (n+3)^dim array, entry (i, j, k) at (i+1) + (n+3)(j+1) + (n+3)^2 (k+1), one ghost layer around: velocity
+ * component d on the faces 0..n in dimension d and the cells 0..n-1 in the others, p on the cells.              */
 typedef struct {
   int nu_pre, nu_post;   /* repeat 3 times { Smoother }                                   */
   int nu_coarse;         /* VCycle@coarsest: repeat 10 times { Smoother }                 */
-  double top_vel;        /* ApplyBC_u@finest: lid velocity (0.02)                         */
+  double top_vel;        /* ApplyBC_u@finest: lid velocity (0.02 in 2D, 0.2 in 3D)        */
 } examg_stokes_desc;
 typedef struct examg_stokes examg_stokes;
-enum { EXAMG_ST_U = 0, EXAMG_ST_V = 1, EXAMG_ST_P = 2, EXAMG_ST_RHS_U = 3, EXAMG_ST_RHS_V = 4, EXAMG_ST_RHS_P = 5,
-       EXAMG_ST_RES_U = 6, EXAMG_ST_RES_V = 7, EXAMG_ST_RES_P = 8, EXAMG_ST_NFIELDS = 9 };
+/* field ids: EXAMG_ST_VEL + d, EXAMG_ST_RHS + d, EXAMG_ST_RES + d (d = 0 u, 1 v, 2 w), then p, rhs_p, residual_p */
+enum { EXAMG_ST_VEL = 0, EXAMG_ST_RHS = 3, EXAMG_ST_RES = 6, EXAMG_ST_P = 9, EXAMG_ST_RHS_P = 10, EXAMG_ST_RES_P = 11,
+       EXAMG_ST_NFIELDS = 12 };
 examg_stokes *examg_stokes_create(examg_ctx *ctx, const examg_stokes_desc *desc);
 int examg_stokes_destroy(examg_stokes *s);
 int examg_stokes_cells(examg_stokes *s, int level);                     /* n (level < 0: finest)          */
-int examg_stokes_upload(examg_stokes *s, int level, int which, const double *host);   /* (n+3)^2 doubles */
+int examg_stokes_upload(examg_stokes *s, int level, int which, const double *host);   /* (n+3)^dim doubles */
 int examg_stokes_download(examg_stokes *s, int level, int which, double *host);
-/* apply bc to u, v, p: u = ApplyBC_u on the finest level (lid at the top, no-slip elsewhere), Dirichlet 0.0 below;
- * v = Dirichlet 0.0; p = None (C/s/e/boundary/ir/IR_BoundaryCondition.scala:38-45: the value on the wall faces of a
- * face field's own dimension, ghost = 2 g - inner in the other)                                         */
+/* apply bc to the velocities (p: None): u = ApplyBC_u on the finest level (lid: ghost rows in y = 2 top - inner above,
+ * - inner below, then 0 on the wall faces in x), Dirichlet 0.0 otherwise -- the value on the wall faces of a face field's
+ * own dimension, ghost = 2 g - inner in the others, faces in the order -x,+x,-y,+y,-z,+z
+ * (C/s/e/boundary/ir/IR_BoundaryCondition.scala:38-45, IR_ApplyBCFunction.scala:55-88)                         */
 int examg_stokes_apply_bc(examg_stokes *s, int level);
-int examg_stokes_smooth_color(examg_stokes *s, int level, int c0, int c1);   /* one of the nine colours  */
-int examg_stokes_smooth(examg_stokes *s, int level, int nsweeps);  /* nsweeps x { nine colours; apply bc } */
-/* UpdateResidual_{u,v,p}; norms_out (nullable) = NormResidual_{u,v,p}: sqrt of the sums of squares (synchronises) */
+int examg_stokes_smooth_color(examg_stokes *s, int level, int c0, int c1, int c2);  /* one of the 3^dim colours (2D: c2 = 0) */
+int examg_stokes_smooth(examg_stokes *s, int level, int nsweeps);  /* nsweeps x { all colours, i0 fastest; apply bc } */
+/* UpdateResidual_*; norms_out (nullable, dim + 1 doubles) = NormResidual_{u,v[,w],p}: sqrt of the sums of squares
+ * over the loop points (synchronises) */
 int examg_stokes_residual(examg_stokes *s, int level, double *norms_out);
-int examg_stokes_restrict(examg_stokes *s, int level);      /* rhs_*@coarser = Restriction{FaceX,FaceY,Cell} * residual_* */
+int examg_stokes_restrict(examg_stokes *s, int level);      /* rhs_*@coarser = Restriction<loc> * residual_*           */
 int examg_stokes_set_solution(examg_stokes *s, int level, double value);  /* loop points and one layer around */
-int examg_stokes_correct(examg_stokes *s, int level);       /* u, v, p += Correction * (u, v, p)@coarser; apply bc */
-int examg_stokes_vcycle(examg_stokes *s, int level);        /* VCycle@level (< 0: finest)                 */
+int examg_stokes_correct(examg_stokes *s, int level);       /* unknowns += Correction<loc> * unknowns@coarser; apply bc */
+int examg_stokes_vcycle(examg_stokes *s, int level);        /* VCycle@level (< 0: finest; the finest as one CUDA graph) */
 
 /* ---- multi-GPU plumbing (one process per GPU) ---------------------------------
  * Peers are wired by exchanging opaque blobs through the host's process group

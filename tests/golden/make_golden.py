@@ -54,6 +54,7 @@ FILES = {
     "BC_3D_Trigonometric": "Testing/BC/3D_Trigonometric.results",
     "NonLinear_FAS_2D_Basic": "Testing/NonLinear/FAS_2D_Basic.results",
     "Application_ExaStokes_2D": "Testing/Application/ExaStokes_2D.results",
+    "Application_ExaStokes_3D": "Testing/Application/ExaStokes_3D.results",
 }
 
 if __name__ == "__main__":

@@ -135,14 +135,16 @@ def test_fas_cycle_of_a_linear_operator(oracle):
     assert np.max(np.abs(u_cs - u_fas)) <= 1e-11 * np.max(np.abs(u_cs))
 
 
-def test_golden_stokes_2d(oracle):
-    """Testing/Application/ExaStokes_2D.{exa4,knowledge,results}: staggered grid (u at Face_x, v at Face_y, p at cell
-    centres), nine-colour 5 x 5 local solves, default 'linear' transfer operators per localisation, levels 2..8 -- pins
-    examg_oracle_stokes.c: all 34 printed residual norms."""
+@pytest.mark.parametrize("dim", [2, 3])
+def test_golden_stokes(dim, oracle):
+    """Testing/Application/ExaStokes_{2D,3D}.{exa4,knowledge,results}: staggered grid (velocity component d at Face_d, p
+    at cell centres), 3^dim-colour (2 dim + 1)^2 local solves, default 'linear' transfer operators per localisation,
+    levels 2..8 / 1..6 -- pins examg_oracle_stokes.c: all 34 / 45 printed residual norms."""
     import os
     from oracle import stokes
-    s = stokes.Solver()
+    s = stokes.Solver(dim=dim)
     got = stokes.solve(s, oracle.print_reduced_prec)
     s.close()
-    path = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "Application_ExaStokes_2D.results")
-    assert got == open(path).read().split("\n")[:len(got)] and len(got) == 34
+    path = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "Application_ExaStokes_%dD.results" % dim)
+    want = [w for w in open(path).read().split("\n") if w]
+    assert got == want and len(got) == (34 if dim == 2 else 45)

@@ -1,5 +1,5 @@
 #!/usr/bin/env python
-"""Testing/Application/ExaStokes_2D through libexamg: time per V(3,3) cycle (CUDA events) on the reference's grid
+"""Testing/Application/ExaStokes_{2D,3D} through libexamg: time per V(3,3) cycle (CUDA events) on the reference's grid
 (levels 2..8, 256^2 cells) and on larger ones, next to the CPU oracle on the host cores.  Development tool."""
 import os
 import sys
@@ -13,8 +13,8 @@ def main():
     import torch
     from exastencils_b200 import StokesProgram
     from oracle import stokes
-    for hi in (8, 10, 12):
-        g = StokesProgram(2, hi)
+    for dim, lo, hi in ((2, 2, 8), (2, 2, 10), (2, 2, 12), (3, 1, 6), (3, 1, 8)):
+        g = StokesProgram(lo, hi, dim=dim)
         g.apply_bc(hi)
         for _ in range(2):
             g.vcycle()
@@ -29,16 +29,16 @@ def main():
         launches = (g.ctx.launch_count() - l0) // reps
         n = g.cells(hi)
         cpu = float("nan")
-        if hi <= 10:
-            r = stokes.Solver(2, hi)
+        if hi <= (10 if dim == 2 else 6):
+            r = stokes.Solver(lo, hi, dim=dim)
             r.apply_bc(hi)
             r.vcycle()
             t0 = time.perf_counter()
             r.vcycle()
             cpu = (time.perf_counter() - t0) * 1e3
             r.close()
-        print("levels 2..%d (%d^2 cells, %.1f M unknowns): %.3f ms per V(3,3) cycle, %d launches; CPU oracle %.1f ms" %
-              (hi, n, 3.0 * n * n / 1e6, ms, launches, cpu), flush=True)
+        print("%dD levels %d..%d (%d^%d cells, %.1f M unknowns): %.3f ms per V(3,3) cycle, %d launches; CPU oracle %.1f ms" %
+              (dim, lo, hi, n, dim, (dim + 1.0) * n ** dim / 1e6, ms, launches, cpu), flush=True)
         g.close()
 
 
