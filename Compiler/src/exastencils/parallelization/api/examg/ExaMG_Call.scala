@@ -76,6 +76,16 @@ object ExaMG_Symbols {
   val system2SmoothRB = "examg_system2_smooth_rb"
   val system2SmoothRBColor = "examg_system2_smooth_rb_color"
   val system2CGCoarse = "examg_system2_cg_coarse"
+  // staggered-grid Stokes (ExaMG_Stokes)
+  val stokesCreate = "examg_stokes_create"
+  val stokesSmoothColor = "examg_stokes_smooth_color"
+  val stokesSmooth = "examg_stokes_smooth"
+  val stokesResidual = "examg_stokes_residual"
+  val stokesRestrict = "examg_stokes_restrict"
+  val stokesSetSolution = "examg_stokes_set_solution"
+  val stokesCorrect = "examg_stokes_correct"
+  val stokesApplyBC = "examg_stokes_apply_bc"
+  val stokesVCycle = "examg_stokes_vcycle"
   // whole cycle
   val cycleDescFromOptions = "examg_cycle_desc_from_options"
   val solverCreate = "examg_solver_create"

@@ -115,6 +115,9 @@ object ExaMG_ResolveCalls extends DefaultStrategy("Lower loops of the multigrid 
           case _                              => None
         }
 
+      // ---- (2 dim + 1)^2 block smoother of the staggered-grid Stokes programs ---------------------------------------
+      case Some(ls : IR_LocalSolve) if ls.unknowns.length == 2 * numDims + 1 => ExaMG_Stokes.lower(ls, colouring)
+
       case _ => None
     }
   }

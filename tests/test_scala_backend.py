@@ -69,7 +69,7 @@ USED = {
     "IR_WhileLoop": 2, "IR_Scope": 1, "IR_AllocateDataFunction": 2,
     "IR_GlobalCollection": 1, "IR_RealConstant": 1, "IR_IntegerConstant": 1, "IR_StringConstant": 1,
     "IR_PointerDatatype": 1, "IR_SpecialDatatype": 1, "IR_DomainFromAABB": 2,
-    "ConditionedSingleStrategyWrapper": 2,
+    "ConditionedSingleStrategyWrapper": 2, "IR_AtFaceCenter": 1,
 }
 OBJECTS = ["IR_ResolveLoopOverPoints", "IR_SetupAllocateDataFunctionWrapper", "IR_ResolveBenchmarkFunctions",
            "IR_DefaultLayerHandler", "IR_FieldCollection", "IR_StencilCollection", "IR_StencilFieldCollection",
