@@ -122,10 +122,12 @@ constexpr int EXF = 4;  // field components per exchange kernel
 // Nodes shared by several blocks are written more than once with bit-identical values (arithmetic contract).
 struct ExchField {
   const double *src;  // node (0,0,0) of the local buffer
-  int n[3];
+  int n[3];           // own points per dimension: nodes (duplicate layer included) or cells
   int pitch;
   long long plane;
   int depth;
+  int dup;            // 1: node-localised (the blocks share their boundary nodes), 0: cell-localised -- nothing is shared:
+                      // my cells 0..G-1 -> its n..n+G-1 and my cells n-G..n-1 -> its -G..-1 (IR_PackInfoGhost.scala:13-60)
 };
 struct ExchPeer {
   int v[3];
@@ -171,8 +173,8 @@ __global__ void __launch_bounds__(256) k_exchange_all(const __grid_constant__ Ex
 #pragma unroll
       for (int w = 0; w < 3; ++w) {
         if (p.v[w] == 0) { slo[w] = 0; dlo[w] = 0; ext[w] = f.n[w]; }
-        else if (p.v[w] < 0) { slo[w] = 1; dlo[w] = f.n[w]; ext[w] = G; }
-        else { slo[w] = f.n[w] - 1 - G; dlo[w] = -G; ext[w] = G + 1; }
+        else if (p.v[w] < 0) { slo[w] = f.dup; dlo[w] = f.n[w]; ext[w] = G; }
+        else { slo[w] = f.n[w] - f.dup - G; dlo[w] = -G; ext[w] = G + f.dup; }
       }
       const double *sb = f.src + slo[0] + (long long)f.pitch * slo[1] + f.plane * slo[2];
       double *db = p.dst[q] + dlo[0] + (long long)f.pitch * dlo[1] + f.plane * dlo[2];
@@ -289,6 +291,7 @@ struct UnpackArgs {
   long long plane[EXF];
   int depth[EXF];
   int n1[EXF], n2[EXF];
+  int dup[EXF];
 };
 
 __global__ void __launch_bounds__(256) k_unpack_x(const __grid_constant__ UnpackArgs a) {
@@ -298,7 +301,7 @@ __global__ void __launch_bounds__(256) k_unpack_x(const __grid_constant__ Unpack
     if (!a.has[s]) continue;
     for (int q = 0; q < a.nf; ++q) {
       const int G = a.depth[q];
-      const int ext0 = s == 0 ? G + 1 : G, dlo0 = s == 0 ? -G : a.n0[q];
+      const int ext0 = s == 0 ? G + a.dup[q] : G, dlo0 = s == 0 ? -G : a.n0[q];
       const long long total = (long long)ext0 * a.n1[q] * a.n2[q];
       const double *stg = a.stage[s] + q * a.stage_cap;
       double *db = a.dst[q] + dlo0;
@@ -662,7 +665,9 @@ int do_exchange_many(examg_ctx *c, Field *const *fs, const int *slots, const int
     const LevelGeom &g = *geom(c, f.level);
     const int G = depths[q];
     if (G < 1 || G > GHOST) return set_error(EXAMG_EINVAL, "examg_exchange: depth %d", G);
-    if (f.loc != 0) return set_error(EXAMG_EUNSUP, "examg_exchange: cell-localised fields live on one block so far");
+    const int dup = f.loc == 0 ? 1 : 0;
+    int np[3];  // own points: nodes, or the n - 1 cells between them
+    for (int w = 0; w < 3; ++w) np[w] = (w < c->cfg.dim && !dup) ? g.n[w] - 1 : g.n[w];
     for (int w = 0; w < c->cfg.dim; ++w)
       if (g.n[w] - 1 < G)
         return set_error(EXAMG_EUNSUP, "examg_exchange: %d ghost layers of a level with %d cells per block", G, g.n[w] - 1);
@@ -674,17 +679,19 @@ int do_exchange_many(examg_ctx *c, Field *const *fs, const int *slots, const int
       }
       ExchField &ef = a.f[a.nf];
       ef.src = buf + (long long)comp * g.vol + g.origin;
-      for (int w = 0; w < 3; ++w) ef.n[w] = g.n[w];
+      for (int w = 0; w < 3; ++w) ef.n[w] = np[w];
       ef.pitch = g.pitch;
       ef.plane = g.plane;
       ef.depth = G;
+      ef.dup = dup;
       ua.dst[a.nf] = buf + (long long)comp * g.vol + g.origin;
-      ua.n0[a.nf] = g.n[0];
+      ua.n0[a.nf] = np[0];
       ua.pitch[a.nf] = g.pitch;
       ua.plane[a.nf] = g.plane;
       ua.depth[a.nf] = G;
-      ua.n1[a.nf] = g.n[1];
-      ua.n2[a.nf] = g.n[2];
+      ua.n1[a.nf] = np[1];
+      ua.n2[a.nf] = np[2];
+      ua.dup[a.nf] = dup;
       if ((ua.has[0] || ua.has[1]) && (long long)(G + 1) * g.n[1] * g.n[2] > cm->xstage_cap)
         return set_error(EXAMG_ESTATE, "examg_exchange: x face of %s@%d exceeds the staging arrays", f.name.c_str(), f.level);
       for (int pi = 0; pi < a.np; ++pi) {
@@ -694,7 +701,7 @@ int do_exchange_many(examg_ctx *c, Field *const *fs, const int *slots, const int
                                   "examg_comm_export?)", f.name.c_str(), f.level, pr.rank);
         a.p[pi].dst[a.nf] = pb + (long long)comp * g.vol + g.origin;
         long long cnt = 1;
-        for (int w = 0; w < 3; ++w) cnt *= pr.v[w] == 0 ? g.n[w] : (pr.v[w] < 0 ? G : G + 1);
+        for (int w = 0; w < 3; ++w) cnt *= pr.v[w] == 0 ? np[w] : (pr.v[w] < 0 ? G : G + dup);
         work += (pr.v[0] == 0 ? cnt / 2 : cnt) / 4 + 1;
       }
       ++a.nf;

@@ -374,8 +374,8 @@ int examg_field_create(examg_ctx *c, const char *name, int level, int num_slots,
 }
 
 int examg_field_create_cell(examg_ctx *c, const char *name, int level, int num_slots, int ncomp) {
-  if (c && (c->world > 1 || c->periodic_any))
-    return set_error(EXAMG_EUNSUP, "examg_field_create_cell: cell fields are single-block and non-periodic so far");
+  if (c && c->periodic_any)
+    return set_error(EXAMG_EUNSUP, "examg_field_create_cell: cell fields are non-periodic so far");
   return field_create(c, name, level, num_slots, ncomp, 1);
 }
 

@@ -88,7 +88,9 @@ int examg_level_width(examg_ctx *ctx, int level, double h[3]);
 int examg_field_create(examg_ctx *ctx, const char *name, int level, int num_slots, int ncomp);
 /* Cell-localised field (Layout< Real, Cell >: duplicateLayers 0, ghostLayers 1): n-1 cells per
  * dimension where the level has n nodes; upload/download move the dense cell array, no ghosts.
- * 2D and 3D, single block so far.  The loops of the entry points below (apply, residual, smooth_jacobi, dot,
+ * 2D and 3D; several blocks: `communicate` fills the ghost cells at block faces with the neighbour's cells (nothing is
+ * shared between blocks, C/s/e/communication/ir/IR_PackInfoGhost.scala:13-60), `apply bc` the ones at the physical
+ * boundary; no periodic dimensions.  The loops of the entry points below (apply, residual, smooth_jacobi, dot,
  * max_abs_diff, set, copy, axpy, xpay) run over all cells when their fields are cell-localised; boundary
  * conditions write the ghost cells: Dirichlet value / program g -> 2*g - inner cell
  * (C/s/e/boundary/ir/IR_DirichletBC.scala:42-50, the program sees vf_boundaryCoord: the face position in the

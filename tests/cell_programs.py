@@ -276,11 +276,17 @@ class GpuCells:
     """Cell-localised fields of libexamg: examg_field_create_cell, Dirichlet / Neumann ghost-cell updates by
     examg_apply_bc, the generic stencil kernels on the cells, examg_restrict_cell / examg_prolong_add_cell."""
 
-    def __init__(self, prog):
+    def __init__(self, prog, num_blocks=None, rank=0, device=0, dist=None):
+        """num_blocks / rank / dist: this process owns block `rank` of a num_blocks grid (x fastest) and wires the peers
+        through the process group `dist` once every field exists (tests/mgpu/cell_worker.py)."""
         from exastencils_b200 import runtime as rt
         self.rt, self.prog = rt, prog
         P = prog
-        self.ctx = ctx = rt.Context(P.dim, P.min_level, P.max_level, block_cells=(P.F,) * P.dim)
+        nb = tuple(num_blocks) if num_blocks else (1,) * P.dim
+        assert all(P.F % v == 0 for v in nb)
+        self.nb, self.rank = nb + (1,) * (3 - len(nb)), rank
+        self.ctx = ctx = rt.Context(P.dim, P.min_level, P.max_level, block_cells=tuple(P.F // v for v in nb),
+                                    num_blocks=self.nb, rank=rank, device=device)
         self.f, self.A = {}, {}
         offs = [(0, 0, 0), (1, 0, 0), (-1, 0, 0), (0, 1, 0), (0, -1, 0)] + ([(0, 0, 1), (0, 0, -1)] if P.dim == 3 else [])
         kind = rt.BC_NEUMANN if P.neumann else rt.BC_DIRICHLET_CONST
@@ -312,11 +318,21 @@ class GpuCells:
             ctx.field_set_bc_expr(self.f[("u", L)], prog_bc)
         X, Y, Z = P.grid(L)
         shape = ctx.cell_shape(L)
+        gshape = (shape[0] * self.nb[2], shape[1] * self.nb[1], shape[2] * self.nb[0])  # (z, y, x)
         self.exact = ctx.field_create_cell("Exact", L)
         self.ones = ctx.field_create_cell("Ones", L)
-        ctx.upload(self.f[("f", L)], np.ascontiguousarray(np.broadcast_to(P.rhs(X, Y, Z), shape)))
-        ctx.upload(self.exact, np.ascontiguousarray(np.broadcast_to(P.exact(X, Y, Z), shape)))
+        if dist is not None:
+            from exastencils_b200.distributed import wire_peers
+            wire_peers(ctx, dist, device="cuda:%d" % device)
+        sl = self.block_slice(shape)
+        ctx.upload(self.f[("f", L)], np.ascontiguousarray(np.broadcast_to(P.rhs(X, Y, Z), gshape)[sl]))
+        ctx.upload(self.exact, np.ascontiguousarray(np.broadcast_to(P.exact(X, Y, Z), gshape)[sl]))
         ctx.upload(self.ones, np.ones(shape))
+
+    def block_slice(self, shape):
+        """this block's part of a global cell array shaped (z, y, x); blocks are numbered x fastest"""
+        b = [self.rank % self.nb[0], (self.rank // self.nb[0]) % self.nb[1], self.rank // (self.nb[0] * self.nb[1])]
+        return tuple(slice(b[2 - k] * shape[k], (b[2 - k] + 1) * shape[k]) for k in range(3))
 
     def apply_bc(self, k, lvl):
         self.ctx.apply_bc(self.f[(k, lvl)])

@@ -42,6 +42,20 @@ def test_stencil_field_blocks(world, blocks, level):
     assert out.returncode == 0 and "MGPU PARITY OK" in out.stdout, out.stdout[-3000:] + out.stderr[-3000:]
 
 
+@pytest.mark.parametrize("world,name,blocks", [(2, "2D_Basic", "2,1"), (2, "2D_Neumann", "1,2"), (2, "3D_Neumann", "1,1,2"),
+                                               (2, "3D_Basic", "2,1,1"), (4, "3D_Neumann", "2,2,1"), (8, "3D_Basic", "2,2,2")])
+def test_cell_fields_on_several_blocks(world, name, blocks):
+    """Cell-localised fields on several blocks: the Testing/CellBased programs split over 2 / 4 / 8 GPUs
+    print the reference's golden stdout and give the oracle's global Solution (tests/mgpu/cell_worker.py)."""
+    if _ngpus() < world:
+        pytest.skip("needs %d GPUs" % world)
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", str(world),
+           "--master-addr", "127.0.0.1", "--master-port", str(29760 + world), os.path.join(ROOT, "tests", "mgpu", "cell_worker.py"),
+           "--name", name, "--blocks", blocks]
+    out = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
+    assert out.returncode == 0 and "CELL MGPU OK" in out.stdout, out.stdout[-3000:] + out.stderr[-3000:]
+
+
 def test_large_hybrid_golden():
     """Testing/Large/Hybrid: 2560 x 1024 x 2048 cells (5.4e9 unknowns) on 4 GPUs must print the reference's golden
     stdout (the oracle cannot hold this size; the golden vector comes from the reference's 4 x 10-way hybrid run)."""
