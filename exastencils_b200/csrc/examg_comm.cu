@@ -739,6 +739,30 @@ static int finish_reduce(examg_ctx *c, int slot, int op, double *out) {
 }
 
 int finish_sum(examg_ctx *c, int slot, double *out) { return finish_reduce(c, slot, 0, out); }
+
+// n global sums at once (red_out[first .. first+n-1]): one all-reduce launch per slot, ONE host synchronisation
+int finish_sums(examg_ctx *c, int first, int n, double *out) {
+  if (first < 0 || n < 1 || first + n > RED_SLOTS) return set_error(EXAMG_EINVAL, "finish_sums: slots %d..%d", first, first + n - 1);
+  if (c->world > 1) {
+    examg_comm *cm = c->comm;
+    if (!cm || !cm->wired) return set_error(EXAMG_ESTATE, "global reduction: peers not wired (examg_comm_import)");
+    for (int k = 0; k < n; ++k) {
+      RedArgs a;
+      a.world = c->world;
+      a.rank = c->cfg.rank;
+      a.op = 0;
+      a.w = wait_ctl(cm);
+      for (int r = 0; r < c->world; ++r) a.pflags[r] = cm->pflags[r];
+      a.value = c->red_out + first + k;
+      k_allreduce_dd<<<1, MAXW, 0, c->stream>>>(a);
+      EXAMG_LAUNCH_CHECK(c);
+    }
+  }
+  EXAMG_CUDA(cudaMemcpyAsync(c->red_host + first, c->red_out + first, sizeof(dd) * n, cudaMemcpyDeviceToHost, c->stream));
+  EXAMG_SYNC(c);
+  for (int k = 0; k < n; ++k) out[k] = c->red_host[first + k].hi + c->red_host[first + k].lo;
+  return EXAMG_OK;
+}
 int finish_max(examg_ctx *c, int slot, double *out) { return finish_reduce(c, slot, 1, out); }
 
 // ---- agglomeration staging -------------------------------------------------------------------

@@ -583,7 +583,7 @@ int examg_apply_bc(examg_ctx *c, int h, int slot) {
   if (f->loc == 1) {
     bool face_own = false;
     for (int k = 0; k < 6; ++k) face_own = face_own || f->bc_face_kind[k] >= 0;
-    return f->bc_kind == EXAMG_BC_NEUMANN && c->cfg.dim == 2 && !face_own ? launch_bc_cell(c, *f, slot)
+    return f->bc_kind == EXAMG_BC_NEUMANN && c->cfg.dim == 2 && !face_own && c->world == 1 ? launch_bc_cell(c, *f, slot)
                                                                           : launch_bc_cell_generic(c, *f, slot);
   }
   return launch_bc(c, *f, slot);

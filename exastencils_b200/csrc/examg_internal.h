@@ -197,6 +197,7 @@ StencilArgs stencil_args(const LevelGeom &g, const Stencil &s);
 
 // global (all-rank) sum of a device dd partial written to c->red_out[slot]; returns hi+lo
 int finish_sum(examg_ctx *c, int slot, double *out);
+int finish_sums(examg_ctx *c, int first, int n, double *out);  // n sums, one host synchronisation
 // the same for a maximum (red_out[slot].hi)
 int finish_max(examg_ctx *c, int slot, double *out);
 // EXAMG_ESTATE if a device-side wait for a peer rank timed out since the peers were wired (sticky), else 0

@@ -42,6 +42,7 @@ __device__ __forceinline__ bool of_steps(std::integer_sequence<int, Ks...>, F &&
 
 struct OfArgs {
   int nx, ny, pitch;
+  int par;  // parity of the block's first cell in the global grid: the colour of cell (i, j) is (i + j + par) & 1
   double L[5];
   double a2;
   const double *cuu, *cuv, *cvv;
@@ -111,7 +112,7 @@ k_of_smooth_color(const OfArgs a, double *__restrict__ u, double *__restrict__ v
                   const double *__restrict__ fv, double relax, int color) {
   const int j = blockIdx.y * blockDim.y + threadIdx.y;
   if (j >= a.ny) return;
-  const int i = 2 * (blockIdx.x * blockDim.x + threadIdx.x) + ((j + color) & 1);
+  const int i = 2 * (blockIdx.x * blockDim.x + threadIdx.x) + ((j + color + a.par) & 1);
   if (i >= a.nx) return;
   const long long p = i + (long long)a.pitch * j;
   double nu, nv;
@@ -459,6 +460,74 @@ k_of_cg(const OfArgs a, double *u, double *v, const double *fu, const double *fv
   if (tid == 0 && iters_out) *iters_out = iters;
 }
 
+// ---- the same CG on several blocks: one kernel per loop of k_of_cg, global sums in between ---------------------------
+// (the scalars are formed from the same sums -- sum r_u^2 and sum r_v^2 rounded separately, then added, etc. -- in
+// double-double, so they do not depend on how the cells are spread over blocks)
+
+// cgTmp1 = A * cgTmp0; partial sums of r_u^2, r_v^2, p_u (A p)_u, p_v (A p)_v -> partials[k * nblocks + block]
+__global__ void __launch_bounds__(256)
+k_of_cg_apply(const OfArgs a, const double *__restrict__ ru, const double *__restrict__ rv, const double *__restrict__ pu,
+              const double *__restrict__ pv, double *__restrict__ apu, double *__restrict__ apv, dd *partials) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  dd n0 = {0.0, 0.0}, n1 = {0.0, 0.0}, d0 = {0.0, 0.0}, d1 = {0.0, 0.0};
+  for (int j = blockIdx.y * blockDim.y + threadIdx.y; j < a.ny; j += gridDim.y * blockDim.y) {
+    if (i >= a.nx) break;
+    const long long p = i + (long long)a.pitch * j;
+    const double au = fma(a.a2, of_lap(a.L, pu, p, a.pitch), fma(a.cuv[p], pv[p], a.cuu[p] * pu[p]));
+    const double av = fma(a.a2, of_lap(a.L, pv, p, a.pitch), fma(a.cvv[p], pv[p], a.cuv[p] * pu[p]));
+    apu[p] = au;
+    apv[p] = av;
+    dd_add(n0, ru[p] * ru[p]);
+    dd_add(n1, rv[p] * rv[p]);
+    dd_add(d0, pu[p] * au);
+    dd_add(d1, pv[p] * av);
+  }
+  const int nb = gridDim.x * gridDim.y, b = blockIdx.x + gridDim.x * blockIdx.y;
+  dd v = dd_block_reduce(n0);
+  if (threadIdx.x == 0 && threadIdx.y == 0) partials[b] = v;
+  v = dd_block_reduce(n1);
+  if (threadIdx.x == 0 && threadIdx.y == 0) partials[nb + b] = v;
+  v = dd_block_reduce(d0);
+  if (threadIdx.x == 0 && threadIdx.y == 0) partials[2 * nb + b] = v;
+  v = dd_block_reduce(d1);
+  if (threadIdx.x == 0 && threadIdx.y == 0) partials[3 * nb + b] = v;
+}
+
+// Solution += alpha * cgTmp0; Residual -= alpha * cgTmp1 (ghost cells with them); partial sums of r_u^2 + r_v^2
+__global__ void __launch_bounds__(256)
+k_of_cg_update(const OfArgs a, double alpha, double *__restrict__ u, double *__restrict__ v, double *__restrict__ ru,
+               double *__restrict__ rv, const double *__restrict__ pu, const double *__restrict__ pv,
+               const double *__restrict__ apu, const double *__restrict__ apv, dd *partials) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  dd pr = {0.0, 0.0};
+  for (int j = blockIdx.y * blockDim.y + threadIdx.y; j < a.ny; j += gridDim.y * blockDim.y) {
+    if (i >= a.nx) break;
+    const long long p = i + (long long)a.pitch * j;
+    store_neumann(u, i, j, a.nx, a.ny, a.pitch, fma(alpha, pu[p], u[p]));
+    store_neumann(v, i, j, a.nx, a.ny, a.pitch, fma(alpha, pv[p], v[p]));
+    const double r0 = fma(-alpha, apu[p], ru[p]), r1 = fma(-alpha, apv[p], rv[p]);
+    store_neumann(ru, i, j, a.nx, a.ny, a.pitch, r0);
+    store_neumann(rv, i, j, a.nx, a.ny, a.pitch, r1);
+    dd_add(pr, r0 * r0);
+    dd_add(pr, r1 * r1);
+  }
+  pr = dd_block_reduce(pr);
+  if (threadIdx.x == 0 && threadIdx.y == 0) partials[blockIdx.x + gridDim.x * blockIdx.y] = pr;
+}
+
+// cgTmp0 = Residual + beta * cgTmp0 (ghost cells with it); beta = 0 with copy: cgTmp0 = Residual
+__global__ void __launch_bounds__(256)
+k_of_cg_dir(const OfArgs a, double beta, int copy, const double *__restrict__ ru, const double *__restrict__ rv,
+            double *__restrict__ pu, double *__restrict__ pv) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  for (int j = blockIdx.y * blockDim.y + threadIdx.y; j < a.ny; j += gridDim.y * blockDim.y) {
+    if (i >= a.nx) break;
+    const long long p = i + (long long)a.pitch * j;
+    store_neumann(pu, i, j, a.nx, a.ny, a.pitch, copy ? ru[p] : fma(beta, pu[p], ru[p]));
+    store_neumann(pv, i, j, a.nx, a.ny, a.pitch, copy ? rv[p] : fma(beta, pv[p], rv[p]));
+  }
+}
+
 // ---- host side ---------------------------------------------------------------------
 
 static System2 *get_system(examg_ctx *c, int h) {
@@ -478,6 +547,7 @@ static OfArgs of_args(examg_ctx *c, const System2 &s) {
   a.nx = g.n[0] - 1;
   a.ny = g.n[1] - 1;
   a.pitch = g.pitch;
+  a.par = (g.goff[0] + g.goff[1]) & 1;
   for (int k = 0; k < 5; ++k) a.L[k] = s.L[k];
   a.a2 = s.a2;
   a.cuu = field_ptr(c, &c->fields[s.cuu], -1);
@@ -520,7 +590,17 @@ static int of_max_sweeps() {
 static bool of_fused_usable(examg_ctx *c, const System2 &s) {
   const LevelGeom &g = *geom(c, s.level);
   const int nx = g.n[0] - 1, ny = g.n[1] - 1;
-  return of_max_sweeps() > 0 && nx % 2 == 0 && nx >= 128 && ny >= 16;
+  // several blocks: the colour kernels with `communicate` in between (the wavefront kernel clamps at all four edges)
+  return c->world == 1 && of_max_sweeps() > 0 && nx % 2 == 0 && nx >= 128 && ny >= 16;
+}
+
+// several blocks: `communicate` of both unknowns in one handshake; the ghost cells at block faces take the neighbour's
+// cells (the Neumann copies the kernels left there are overwritten), the ones at the physical boundary stay
+static int of_exchange2(examg_ctx *c, Field *fa, Field *fb) {
+  if (c->world == 1) return EXAMG_OK;
+  Field *fs[2] = {fa, fb};
+  const int slots[2] = {fa->cur, fb->cur}, depths[2] = {1, 1};
+  return do_exchange_many(c, fs, slots, depths, fa == fb ? 1 : 2);
 }
 
 template <int S>
@@ -606,6 +686,10 @@ int examg_system2_residual(examg_ctx *c, int sys, int u, int v, int rhs_u, int r
   OF_SYS(s, sys);
   OF_FIELD(fu, u, s->level); OF_FIELD(fv, v, s->level); OF_FIELD(bu, rhs_u, s->level); OF_FIELD(bv, rhs_v, s->level);
   OF_FIELD(ru, res_u, s->level); OF_FIELD(rv, res_v, s->level);
+  {
+    const int rc = of_exchange2(c, fu, fv);
+    if (rc) return rc;
+  }
   const OfArgs a = of_args(c, *s);
   const dim3 block(64, 4), grid = rows_grid(a.nx, a.ny, block);
   if (norm2_out) {
@@ -628,6 +712,10 @@ int examg_system2_smooth_rb_color(examg_ctx *c, int sys, int u, int v, int rhs_u
   OF_SYS(s, sys);
   OF_FIELD(fu, u, s->level); OF_FIELD(fv, v, s->level); OF_FIELD(bu, rhs_u, s->level); OF_FIELD(bv, rhs_v, s->level);
   if (color != 0 && color != 1) return set_error(EXAMG_EINVAL, "examg_system2_smooth_rb_color: colour %d", color);
+  {
+    const int rc = of_exchange2(c, fu, fv);
+    if (rc) return rc;
+  }
   const OfArgs a = of_args(c, *s);
   const dim3 block(64, 4), grid((a.nx / 2 + 1 + block.x - 1) / block.x, (a.ny + block.y - 1) / block.y);
   k_of_smooth_color<<<grid, block, 0, c->stream>>>(a, field_ptr(c, fu, -1), field_ptr(c, fv, -1), field_ptr(c, bu, -1),
@@ -706,6 +794,66 @@ int examg_prolong_add_cell(examg_ctx *c, const int *coarse, const int *fine, int
   return cell_transfer(c, coarse, fine, nfields, false, "examg_prolong_add_cell");
 }
 
+}  // extern "C"
+
+// mgCycle@coarsest on several blocks: the loops of k_of_cg as kernels over this block's cells, `communicate` of cgTmp0
+// before A * cgTmp0, global sums (all-reduce + one host synchronisation) where the program has its reductions.
+// fields = { u, v, rhs_u, rhs_v, residual_u, residual_v, cgTmp0_u, cgTmp0_v, cgTmp1_u, cgTmp1_v }
+static int of_cg_blocks(examg_ctx *c, const System2 &s, const int *fields, int max_it, double rel_tol, int *iters_out) {
+  Field *f[10];
+  double *p[10];
+  for (int k = 0; k < 10; ++k) {
+    f[k] = cell_field(c, fields[k], s.level);
+    p[k] = field_ptr(c, f[k], -1);
+  }
+  int rc;
+  double n2 = 0.0;
+  // Residual = RHS - A * Solution (+ its sum of squares); cgTmp0 = Residual
+  const int sys = (int)(&s - c->systems.data());
+  if ((rc = examg_system2_residual(c, sys, fields[0], fields[1], fields[2], fields[3], fields[4], fields[5], &n2))) return rc;
+  const OfArgs a = of_args(c, s);
+  const dim3 block(64, 4), grid = rows_grid(a.nx, a.ny, block);
+  const int nb = (int)(grid.x * grid.y);
+  k_of_cg_dir<<<grid, block, 0, c->stream>>>(a, 0.0, 1, p[4], p[5], p[6], p[7]);
+  EXAMG_LAUNCH_CHECK(c);
+  double curRes = std::sqrt(n2);
+  const double initRes = curRes;
+  int iters = 0;
+  for (int step = 0; step < max_it; ++step) {
+    iters = step + 1;
+    if ((rc = of_exchange2(c, f[6], f[7]))) return rc;
+    k_of_cg_apply<<<grid, block, 0, c->stream>>>(a, p[4], p[5], p[6], p[7], p[8], p[9], c->partials);
+    EXAMG_LAUNCH_CHECK(c);
+    for (int k = 0; k < 4; ++k) {
+      k_of_final_sum<<<1, 1024, 0, c->stream>>>(c->partials + k * nb, nb, c->red_out + 4 + k);
+      EXAMG_LAUNCH_CHECK(c);
+    }
+    double sums[4];
+    if ((rc = finish_sums(c, 4, 4, sums))) return rc;
+    const double alpha = (sums[0] + sums[1]) / (sums[2] + sums[3]);
+    k_of_cg_update<<<grid, block, 0, c->stream>>>(a, alpha, p[0], p[1], p[4], p[5], p[6], p[7], p[8], p[9], c->partials);
+    EXAMG_LAUNCH_CHECK(c);
+    k_of_final_sum<<<1, 1024, 0, c->stream>>>(c->partials, nb, c->red_out + 4);
+    EXAMG_LAUNCH_CHECK(c);
+    double pr = 0.0;
+    if ((rc = finish_sums(c, 4, 1, &pr))) return rc;
+    const double nextRes = std::sqrt(pr);
+    if (nextRes <= rel_tol * initRes) break;
+    const double beta = (nextRes * nextRes) / (curRes * curRes);
+    k_of_cg_dir<<<grid, block, 0, c->stream>>>(a, beta, 0, p[4], p[5], p[6], p[7]);
+    EXAMG_LAUNCH_CHECK(c);
+    curRes = nextRes;
+  }
+  for (int k : {0, 1, 4, 5, 6, 7}) f[k]->halo_depth = 0;
+  c->int_host[0] = iters;
+  EXAMG_CUDA(cudaMemcpyAsync(c->int_out, c->int_host, sizeof(int), cudaMemcpyHostToDevice, c->stream));
+  EXAMG_SYNC(c);
+  if (iters_out) *iters_out = iters;
+  return EXAMG_OK;
+}
+
+extern "C" {
+
 int examg_system2_cg_coarse(examg_ctx *c, int sys, const int *fields, int max_it, double rel_tol, int *iters_out) {
   OF_SYS(s, sys);
   if (!fields) return set_error(EXAMG_EINVAL, "examg_system2_cg_coarse: null field list");
@@ -715,6 +863,7 @@ int examg_system2_cg_coarse(examg_ctx *c, int sys, const int *fields, int max_it
     if (!f) return set_error(EXAMG_EINVAL, "examg_system2_cg_coarse: field %d (#%d) is not a cell field of level %d", fields[k], k, s->level);
     p[k] = field_ptr(c, f, -1);
   }
+  if (c->world > 1) return of_cg_blocks(c, *s, fields, max_it, rel_tol, iters_out);
   const OfArgs a = of_args(c, *s);
   int nt = 32;
   while (nt < 1024 && nt < a.nx * a.ny) nt <<= 1;
@@ -806,8 +955,8 @@ extern "C" {
 
 examg_optflow *examg_optflow_create(examg_ctx *c, const examg_optflow_desc *d) {
   if (!c || !d) { set_error(EXAMG_EINVAL, "examg_optflow_create: null argument"); return nullptr; }
-  if (c->cfg.dim != 2 || c->world != 1) {
-    set_error(EXAMG_EUNSUP, "examg_optflow_create: 2D single-block programs only");
+  if (c->cfg.dim != 2) {
+    set_error(EXAMG_EUNSUP, "examg_optflow_create: 2D programs only");
     return nullptr;
   }
   examg_optflow *o = new examg_optflow;
@@ -890,6 +1039,7 @@ int examg_optflow_init_fields(examg_optflow *o) {
   examg_ctx *c = o->c;
   int rc;
   if ((rc = examg_apply_bc(c, o->img0, -1)) || (rc = examg_apply_bc(c, o->img1, -1))) return rc;
+  if ((rc = of_exchange2(c, &c->fields[o->img0], &c->fields[o->img1]))) return rc;  // the gradients read [1,0], [0,1]
   const int L = c->cfg.max_level, l = of_lv(o, L);
   const LevelGeom &g = *geom(c, L);
   const int nx = g.n[0] - 1, ny = g.n[1] - 1;
@@ -912,7 +1062,8 @@ int examg_optflow_vcycle(examg_optflow *o, int level) {
   examg_ctx *c = o->c;
   if (level < 0) level = c->cfg.max_level;
   if (level < c->cfg.min_level || level > c->cfg.max_level) return set_error(EXAMG_EINVAL, "examg_optflow_vcycle: level %d", level);
-  if (level != c->cfg.max_level) return of_vcycle_rec(o, level);
+  // several blocks: the coarse solve synchronises with the host for its global sums -- no graph
+  if (level != c->cfg.max_level || c->world > 1) return of_vcycle_rec(o, level);
   // one graph per buffer state (the fused sweeps exchange u, v with their second buffers)
   const std::vector<int> key = of_state(o);
   auto it = o->graphs.find(key);

@@ -25,8 +25,12 @@ def analytic_images(nx, ny):
 
 class OpticalFlowProgram:
     def __init__(self, block_cells, min_level, max_level, alpha=1.0, relax=1.0, nu_pre=3, nu_post=3, cg_max_it=128,
-                 cg_rel_tol=1e-3, device=0, stream=None):
-        self.ctx = rt.Context(2, min_level, max_level, block_cells=tuple(block_cells) + (1,), device=device)
+                 cg_rel_tol=1e-3, device=0, stream=None, num_blocks=(1, 1), rank=0, dist=None):
+        """num_blocks / rank / dist: this process owns block `rank` (x fastest) of a num_blocks grid of blocks with
+        block_cells cells each on level 0; the peers are wired through the process group `dist` (one process per GPU)."""
+        self.num_blocks, self.rank = tuple(num_blocks), rank
+        self.ctx = rt.Context(2, min_level, max_level, block_cells=tuple(block_cells) + (1,), device=device,
+                              num_blocks=tuple(num_blocks) + (1,), rank=rank)
         if stream is not None:
             self.ctx.set_stream(stream)
         self.min_level, self.max_level = min_level, max_level
@@ -34,6 +38,15 @@ class OpticalFlowProgram:
         self._h = self.ctx.L.examg_optflow_create(self.ctx.h, C.byref(d))
         if not self._h:
             raise rt.ExaMGError("examg_optflow_create: " + self.ctx.L.examg_last_error().decode())
+        if dist is not None:
+            from .distributed import wire_peers
+            wire_peers(self.ctx, dist, device="cuda:%d" % device)
+
+    def block_slice(self, level=None):
+        """this block's part of a global (ny, nx) cell array of the level"""
+        nx, ny = self.cells(level)
+        bx, by = self.rank % self.num_blocks[0], self.rank // self.num_blocks[0]
+        return (slice(by * ny, (by + 1) * ny), slice(bx * nx, (bx + 1) * nx))
 
     def close(self):
         if getattr(self, "_h", None):
@@ -50,7 +63,7 @@ class OpticalFlowProgram:
         return nx, ny
 
     def set_images(self, img0, img1):
-        """upload the two frames (dense (ny, nx) arrays) and run InitFields"""
+        """upload the two frames (dense (ny, nx) arrays of this block's cells) and run InitFields"""
         self.ctx.upload(self.field(IMG0), np.ascontiguousarray(img0, dtype=np.float64))
         self.ctx.upload(self.field(IMG1), np.ascontiguousarray(img1, dtype=np.float64))
         rt.check(self.ctx.L.examg_optflow_init_fields(self._h))
