@@ -426,10 +426,15 @@ def run_aux(args):
     """--workload poisson2d | optflow on one GPU: same JSON line as the main workload."""
     level = args.level if args.level is not None else (8 if args.workload == "poisson2d" else 13)
     cpu_level = args.cpu_level if args.cpu_level is not None else (8 if args.workload == "poisson2d" else min(level, 12))
-    if int(os.environ.get("RANK", "0")) != 0:
+    rank, world = int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", rank))
+    multi = args.workload == "optflow" and args.gpus > 1 and args.impl != "reference"
+    if rank != 0 and not multi:
         return
-    if args.gpus != 1:
+    if args.gpus != 1 and not multi and args.impl != "reference":
         raise SystemExit("--workload %s runs on one GPU" % args.workload)
+    if multi and world != args.gpus:
+        raise SystemExit("--gpus %d needs torch.distributed.run with %d ranks" % (args.gpus, args.gpus))
     if args.impl == "reference":
         cb, dt = _aux_cpu(args.workload, cpu_level, args.steps, args.warmup)
         line = {"impl": "reference", "metric": "V-cycle DoF-cycles/s", "value": cb["value"], "unit": "DoF-cycles/s",
@@ -444,6 +449,12 @@ def run_aux(args):
     import torch
     if not torch.cuda.is_available():
         raise SystemExit("bench.py needs a CUDA device: libexamg has no CPU path")
+    torch.cuda.set_device(local_rank)
+    dist = None
+    if multi:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    of_blocks = {1: (1, 1), 2: (2, 1), 4: (2, 2), 8: (4, 2)}.get(args.gpus, (args.gpus, 1))
     stream = torch.cuda.Stream()
     peak, peak_kind = peaks()
     if args.workload == "poisson2d":
@@ -468,12 +479,17 @@ def run_aux(args):
     else:
         from exastencils_b200 import OpticalFlowProgram
         from exastencils_b200 import optflow as gof
-        prog = OpticalFlowProgram((1, 1), 2, level, nu_pre=3, nu_post=3, stream=stream.cuda_stream)
+        # several GPUs: one block of 2^level x 2^level cells per GPU (weak scaling), blocks 2x1 / 2x2 / 4x2
+        prog = OpticalFlowProgram((1, 1), 2, level, nu_pre=3, nu_post=3, stream=stream.cuda_stream, num_blocks=of_blocks,
+                                  rank=rank, device=local_rank, dist=dist)
         ctx = prog.ctx
         nx, ny = prog.cells()
-        img0, img1 = gof.analytic_images(nx, ny)
+        x = (np.arange(nx, dtype=np.float64) + (rank % of_blocks[0]) * nx + 0.5) * (1.0 / (nx * of_blocks[0]))
+        y = (np.arange(ny, dtype=np.float64) + (rank // of_blocks[0]) * ny + 0.5) * (1.0 / (ny * of_blocks[1]))
+        img0 = np.ascontiguousarray(np.sin(x)[None, :] + np.cos(y)[:, None])      # initImgs@finest, this block's part
+        img1 = np.ascontiguousarray(np.sin(x - 0.01)[None, :] + np.cos(y + 0.01)[:, None])
         prog.set_images(img0, img1)
-        unknowns = 2.0 * nx * ny
+        unknowns = 2.0 * nx * ny * args.gpus
         inputs = [(prog.field(gof.IMG0), torch.from_numpy(img0).pin_memory()),
                   (prog.field(gof.IMG1), torch.from_numpy(img1).pin_memory())]
         from exastencils_b200.runtime import check as rt_check
@@ -482,20 +498,33 @@ def run_aux(args):
         f = {w: prog.field(w) for w in range(9)}
         kernel = lambda: ctx.system2_smooth_rb(sys_h, f[gof.U], f[gof.V], f[gof.RHS_U], f[gof.RHS_V], 1.0, 3)
         kname, kbytes = "red-black 2x2 block smoother, 3 sweeps on the finest level", 3 * 80.0 * nx * ny
+
+    def sync_all():
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_ms(v):
+        if dist is None:
+            return v
+        t = torch.tensor([v], device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
     with torch.cuda.stream(stream):
         sampler = ClockSampler(0)
         sampler.start()
         for _ in range(args.warmup):
             prog.cycles(1)
-        torch.cuda.synchronize()
+        sync_all()
         l0 = ctx.launch_count()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record(stream)
         for _ in range(args.steps):
             res = prog.cycles(1)
         e1.record(stream)
-        torch.cuda.synchronize()
-        ms = e0.elapsed_time(e1)
+        sync_all()
+        ms = max_ms(e0.elapsed_time(e1))
         launches = ctx.launch_count() - l0
         # end to end: every step uploads its input from pinned host memory, (re)initialises, cycles, reads the norm back
         h2d = sum(t.numel() * 8 for _, t in inputs)
@@ -504,7 +533,7 @@ def run_aux(args):
                 ctx.upload_async(fld, t.data_ptr())
             prepare()
             prog.cycles(1)
-        torch.cuda.synchronize()
+        sync_all()
         e0.record(stream)
         for _ in range(args.steps):
             for fld, t in inputs:
@@ -512,8 +541,8 @@ def run_aux(args):
             prepare()
             res_e2e = prog.cycles(1)
         e1.record(stream)
-        torch.cuda.synchronize()
-        ms_e2e = e0.elapsed_time(e1)
+        sync_all()
+        ms_e2e = max_ms(e0.elapsed_time(e1))
         clocks = sampler.stop()
         reps = max(5, args.steps)
         for _ in range(3):
@@ -528,10 +557,14 @@ def run_aux(args):
         ms_k = e0.elapsed_time(e1) / reps
         k_launches = (ctx.launch_count() - l1) // reps
     achieved = kbytes / (ms_k * 1e-3) / 1e9
+    if rank != 0:
+        prog.close()
+        dist.destroy_process_group()
+        return
     cb = None
-    if not args.no_cpu_baseline:
+    if not args.no_cpu_baseline and not multi:
         cb, _ = _aux_cpu(args.workload, cpu_level, args.cpu_cycles)
-    line = {"metric": "V-cycle DoF-cycles/s", "value": unknowns * args.steps / (ms * 1e-3), "unit": "DoF-cycles/s", "n_gpus": 1,
+    line = {"metric": "V-cycle DoF-cycles/s", "value": unknowns * args.steps / (ms * 1e-3), "unit": "DoF-cycles/s", "n_gpus": args.gpus,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
             "config": _aux_config(args.workload, level),
@@ -543,8 +576,14 @@ def run_aux(args):
                          "peak": peak, "peak_kind": peak_kind + " (MEASURED_PEAKS.json hbm_gbs, burst)", "unit": "GB/s",
                          "frac": achieved / peak, "traffic": None, "algorithmic_bytes_per_launch_group": kbytes, "ms": ms_k},
             "cpu_baseline": cb, "final_residual": res, "device_bytes": ctx.device_bytes()}
+    if multi:
+        line["config"]["blocks"] = list(of_blocks)
+        line["config"]["workload"] += "; one such block per GPU, blocks %d x %d" % of_blocks
+        line["e2e"]["h2d_bytes_per_step"] = h2d * args.gpus
     print(json.dumps(line))
     prog.close()
+    if dist is not None:
+        dist.destroy_process_group()
 
 
 def parity_vs_one_block(args, decomp, wl, dist, rank, local_rank, world, stream):

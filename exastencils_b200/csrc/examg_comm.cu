@@ -482,6 +482,10 @@ struct examg_comm {
   double *agg_in0 = nullptr, *agg_out0 = nullptr;   // rank 0's arrays as seen from this rank
   int agg_level = -1;
   int agg_gn[3] = {0, 0, 0};
+  // cell-localised staging (comm_agg_setup_cells): agg_in / agg_out hold several dense arrays of agg_tot cells each
+  bool agg_cells = false;
+  long long agg_tot = 0;
+  int agg_nin = 0, agg_nout = 0;
 };
 
 namespace examg {
@@ -786,6 +790,42 @@ int comm_agg_setup(examg_ctx *c, int level) {
   return EXAMG_OK;
 }
 
+// The same for cell-localised fields (nothing shared between blocks): `nin` dense arrays in, `nout` out and `extra`
+// more doubles behind them, on rank 0.  Before examg_comm_export, on every rank.
+int comm_agg_setup_cells(examg_ctx *c, int level, int nin, int nout, int extra) {
+  examg_comm *cm = comm_get(c);
+  if (cm->agg_level >= 0) return set_error(EXAMG_ESTATE, "agglomeration staging is already set up (level %d)", cm->agg_level);
+  const LevelGeom &g = *geom(c, level);
+  cm->agg_level = level;
+  cm->agg_cells = true;
+  cm->agg_nin = nin;
+  cm->agg_nout = nout;
+  long long tot = 1;
+  for (int d = 0; d < 3; ++d) {
+    cm->agg_gn[d] = d < c->cfg.dim ? (g.n[d] - 1) * c->cfg.num_blocks[d] : 1;
+    tot *= cm->agg_gn[d];
+  }
+  cm->agg_tot = tot;
+  if (c->cfg.rank == 0) {
+    cm->agg_in = dev_alloc(c, (size_t)nin * tot * sizeof(double));
+    cm->agg_out = dev_alloc(c, ((size_t)nout * tot + extra) * sizeof(double));
+    if (!cm->agg_in || !cm->agg_out) return set_error(EXAMG_ENOMEM, "agglomeration staging of level %d", level);
+  }
+  return EXAMG_OK;
+}
+
+// level of the cell staging (-1: none), global cell counts, cells per dense array
+int comm_agg_cells(examg_ctx *c, int gn[3], long long *tot) {
+  examg_comm *cm = c->comm;
+  if (!cm || !cm->agg_cells) return -1;
+  for (int d = 0; d < 3; ++d) gn[d] = cm->agg_gn[d];
+  *tot = cm->agg_tot;
+  return cm->agg_level;
+}
+
+// rank 0's dense "out" arrays as mapped into this rank
+const double *comm_agg_out_peer(examg_ctx *c) { return c->comm ? c->comm->agg_out0 : nullptr; }
+
 double *comm_agg_in(examg_ctx *c) { return c->comm ? c->comm->agg_in : nullptr; }
 double *comm_agg_out(examg_ctx *c) { return c->comm ? c->comm->agg_out : nullptr; }
 
@@ -793,9 +833,11 @@ static int agg_args(examg_ctx *c, const Field &f, AggArgs *a) {
   examg_comm *cm = c->comm;
   if (!cm || !cm->wired) return set_error(EXAMG_ESTATE, "agglomeration: peers not wired (examg_comm_import)");
   if (f.level != cm->agg_level) return set_error(EXAMG_EINVAL, "agglomeration: field level %d, staging level %d", f.level, cm->agg_level);
+  if (cm->agg_cells != (f.loc == 1))
+    return set_error(EXAMG_EINVAL, "agglomeration: the staging of level %d is for %s fields", f.level, cm->agg_cells ? "cell" : "node");
   const LevelGeom &g = *geom(c, f.level);
   for (int d = 0; d < 3; ++d) {
-    a->n[d] = g.n[d];
+    a->n[d] = cm->agg_cells && d < c->cfg.dim ? g.n[d] - 1 : g.n[d];
     a->goff[d] = g.goff[d];
     a->gn[d] = cm->agg_gn[d];
   }
@@ -818,25 +860,27 @@ static int agg_grid(const AggArgs &a) {
   return (int)(grid > 128 ? 128 : (grid < 1 ? 1 : grid));
 }
 
-// all ranks: field (active slot) -> rank 0's dense "in" array; rank 0 returns when all blocks arrived
-int comm_agg_gather(examg_ctx *c, Field &f) {
+// all ranks: field (active slot) -> rank 0's dense "in" array number `comp`; rank 0 returns when all blocks arrived
+int comm_agg_gather(examg_ctx *c, Field &f, int comp) {
   AggArgs a;
   int rc = agg_args(c, f, &a);
   if (rc) return rc;
+  if (comp < 0 || comp >= (c->comm->agg_cells ? c->comm->agg_nin : 1)) return set_error(EXAMG_EINVAL, "agglomeration: in array %d", comp);
   a.fsrc = field_ptr(c, &f, -1);
-  a.dense = c->comm->agg_in0;
+  a.dense = c->comm->agg_in0 + comp * c->comm->agg_tot;
   k_agg_gather<<<agg_grid(a), 256, 0, c->stream>>>(a);
   EXAMG_LAUNCH_CHECK(c);
   return EXAMG_OK;
 }
 
 // rank 0 (after filling the dense "out" array): signal; all ranks: dense "out" -> field (active slot)
-int comm_agg_scatter(examg_ctx *c, Field &f) {
+int comm_agg_scatter(examg_ctx *c, Field &f, int comp) {
   AggArgs a;
   int rc = agg_args(c, f, &a);
   if (rc) return rc;
+  if (comp < 0 || comp >= (c->comm->agg_cells ? c->comm->agg_nout : 1)) return set_error(EXAMG_EINVAL, "agglomeration: out array %d", comp);
   a.fdst = field_ptr(c, &f, -1);
-  a.dense = c->comm->agg_out0;
+  a.dense = c->comm->agg_out0 + comp * c->comm->agg_tot;
   if (c->cfg.rank == 0) {
     k_agg_signal<<<1, MAXW, 0, c->stream>>>(a);
     EXAMG_LAUNCH_CHECK(c);

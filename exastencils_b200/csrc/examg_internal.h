@@ -102,6 +102,8 @@ struct System2 {
   double a2 = 1.0;
   int cuu = -1, cuv = -1, cvv = -1;
   double L[5];
+  // several blocks, level agglomerated for the coarse solve: 13 padded global arrays on rank 0 (examg_optflow.cu, of_cg_agg)
+  double *agg_pad = nullptr;
 };
 
 // startTimer / stopTimer of the L4 programs, measured on the device (CUDA events on the context stream)
@@ -285,7 +287,11 @@ int copy_field_device(examg_ctx *c, int field, int slot, double *dense, bool to_
 int comm_agg_setup(examg_ctx *c, int level);
 double *comm_agg_in(examg_ctx *c);
 double *comm_agg_out(examg_ctx *c);
-int comm_agg_gather(examg_ctx *c, Field &f);
-int comm_agg_scatter(examg_ctx *c, Field &f);
+int comm_agg_gather(examg_ctx *c, Field &f, int comp = 0);
+int comm_agg_scatter(examg_ctx *c, Field &f, int comp = 0);
+// the same staging for cell-localised fields, several dense arrays in and out (coarse solve of a coupled system)
+int comm_agg_setup_cells(examg_ctx *c, int level, int nin, int nout, int extra);
+int comm_agg_cells(examg_ctx *c, int gn[3], long long *tot);
+const double *comm_agg_out_peer(examg_ctx *c);
 
 }  // namespace examg

@@ -43,6 +43,11 @@ __device__ __forceinline__ bool of_steps(std::integer_sequence<int, Ks...>, F &&
 struct OfArgs {
   int nx, ny, pitch;
   int par;  // parity of the block's first cell in the global grid: the colour of cell (i, j) is (i + j + par) & 1
+  // k_of_rbw on several blocks: the cells [xlo, xhi) x [ylo, yhi) it works on -- the block's own cells plus S layers of
+  // the neighbour blocks' cells where there is a neighbour (exchanged beforehand; updated redundantly, one layer less per
+  // half-sweep) -- and which sides are physical (Neumann: clamped neighbour access, ghost cells mirror the result)
+  int xlo, xhi, ylo, yhi;
+  int phys;  // bit 0 west, 1 east, 2 south, 3 north
   double L[5];
   double a2;
   const double *cuu, *cuv, *cvv;
@@ -269,7 +274,7 @@ k_of_init(const double *__restrict__ img0, const double *__restrict__ img1, int 
 // neighbour access; the ghost cells of the result are written with the cells they mirror.
 // HBM traffic per cell: 7 reads + 2 writes = 72 B per pass for S/2 sweeps of 80 B algorithmic each
 // (halo columns come from L2: adjacent strips run in the same CTA).
-template <int S>
+template <int S, bool MB>
 __global__ void __launch_bounds__(128)
 k_of_rbw(const OfArgs a, const double *__restrict__ u, const double *__restrict__ v, const double *__restrict__ fu,
          const double *__restrict__ fv, double *__restrict__ uo, double *__restrict__ vo, double relax, int seg_rows,
@@ -284,9 +289,13 @@ k_of_rbw(const OfArgs a, const double *__restrict__ u, const double *__restrict_
   int t0 = za - S;
   t0 -= t0 & 1;  // even: at odd steps every half-sweep updates cell A of its row, at even steps cell B
   const int tl = zb - 1 + S;
-  const bool inx = x0 >= 0 && x0 < nx;
-  const bool west_edge = x0 == 0, east_edge = x0 + 1 == nx - 1;
-  const bool st = inx && x0 >= ox && x0 < ox + IW;
+  // MB = false (one block): the block's own cells, all four sides physical -- compile-time constants
+  const int xlo = MB ? a.xlo : 0, xhi = MB ? a.xhi : nx, ylo = MB ? a.ylo : 0, yhi = MB ? a.yhi : ny;
+  const int phys = MB ? a.phys : 15;
+  const bool inx = x0 >= xlo && x0 < xhi;
+  const bool west_edge = x0 == 0 && (phys & 1), east_edge = x0 + 1 == nx - 1 && (phys & 2);
+  const bool phys_s = (phys & 4) != 0, phys_n = (phys & 8) != 0;
+  const bool st = inx && x0 >= ox && x0 < ox + IW && x0 < nx;
   const double keep = 1.0 - relax, a2 = a.a2;
   const double L0 = a.L[0], L1 = a.L[1], L2 = a.L[2], L3 = a.L[3], L4 = a.L[4];
 
@@ -299,7 +308,7 @@ k_of_rbw(const OfArgs a, const double *__restrict__ u, const double *__restrict_
   }
   double2 nx_u, nx_v, nx_c[5];  // row t+1, in flight
   auto fetch = [&](int r) {
-    if (inx && r >= 0 && r < ny && r <= tl) {
+    if (inx && r >= ylo && r < yhi && r <= tl) {
       const long long p = x0 + (long long)pitch * r;
       nx_u = *reinterpret_cast<const double2 *>(u + p);
       nx_v = *reinterpret_cast<const double2 *>(v + p);
@@ -336,7 +345,7 @@ k_of_rbw(const OfArgs a, const double *__restrict__ u, const double *__restrict_
       // x neighbour owned by the adjacent lane: A's west = B of lane-1, B's east = A of lane+1
       const double su = X == 0 ? __shfl_up_sync(0xffffffffu, uw[c][1], 1) : __shfl_down_sync(0xffffffffu, uw[c][0], 1);
       const double sv = X == 0 ? __shfl_up_sync(0xffffffffu, vw[c][1], 1) : __shfl_down_sync(0xffffffffu, vw[c][0], 1);
-      if (inx && r >= 0 && r < ny) {
+      if (inx && r >= ylo && r < yhi) {
         const double cu = uw[c][X], cv = vw[c][X];
         double uwst, uest, vwst, vest;
         if (X == 0) {
@@ -346,8 +355,9 @@ k_of_rbw(const OfArgs a, const double *__restrict__ u, const double *__restrict_
           uwst = uw[c][0]; vwst = vw[c][0];
           uest = east_edge ? cu : su; vest = east_edge ? cv : sv;
         }
-        const double usth = r == 0 ? cu : uw[cm][X], vsth = r == 0 ? cv : vw[cm][X];
-        const double unth = r == ny - 1 ? cu : uw[cp][X], vnth = r == ny - 1 ? cv : vw[cp][X];
+        const bool cs = r == 0 && phys_s, cn = r == ny - 1 && phys_n;
+        const double usth = cs ? cu : uw[cm][X], vsth = cs ? cv : vw[cm][X];
+        const double unth = cn ? cu : uw[cp][X], vnth = cn ? cv : vw[cp][X];
         double o0 = L1 * uwst;
         o0 = fma(L2, uest, o0);
         o0 = fma(L3, usth, o0);
@@ -373,7 +383,7 @@ k_of_rbw(const OfArgs a, const double *__restrict__ u, const double *__restrict_
       // Neumann ghost cells mirror the cells just written
       if (west_edge) { uo[p - 1] = ru.x; vo[p - 1] = rv.x; }
       if (east_edge) { uo[p + 2] = ru.y; vo[p + 2] = rv.y; }
-      if (zf == 0 || zf == ny - 1) {
+      if ((zf == 0 && phys_s) || (zf == ny - 1 && phys_n)) {
         const long long g = p + (zf == 0 ? -(long long)pitch : (long long)pitch);
         *reinterpret_cast<double2 *>(uo + g) = ru;
         *reinterpret_cast<double2 *>(vo + g) = rv;
@@ -528,6 +538,38 @@ k_of_cg_dir(const OfArgs a, double beta, int copy, const double *__restrict__ ru
   }
 }
 
+// ---- the same CG on several blocks, coarsest level agglomerated: rank 0 runs k_of_cg on the global grid ---------------
+// dense global arrays [gny][gnx] <-> rank 0's padded arrays (pitch gnx + 2, one ghost cell all round)
+
+// in: 7 dense arrays u, v, rhs_u, rhs_v, cuu, cuv, cvv -> pad[0..3], pad[10..12] (u, v with their Neumann ghost cells)
+__global__ void __launch_bounds__(256) k_of_agg_in(const double *__restrict__ dense, long long tot, int gnx, int gny,
+                                                   double *pad, long long padsz) {
+  static constexpr int which[7] = {0, 1, 2, 3, 10, 11, 12};
+  const int pitch = gnx + 2;
+  for (long long t = blockIdx.x * (long long)blockDim.x + threadIdx.x; t < 7 * tot; t += (long long)gridDim.x * blockDim.x) {
+    const int k = (int)(t / tot);
+    const long long q = t - k * tot;
+    const int i = (int)(q % gnx), j = (int)(q / gnx);
+    double *dst = pad + which[k] * padsz + pitch + 1;
+    if (k < 2) store_neumann(dst, i, j, gnx, gny, pitch, dense[t]);
+    else dst[i + (long long)pitch * j] = dense[t];
+  }
+}
+
+// out: u, v -> 2 dense arrays, the iteration count behind them
+__global__ void __launch_bounds__(256) k_of_agg_out(const double *__restrict__ pad, long long padsz, int gnx, double *dense,
+                                                    long long tot, const int *iters) {
+  const int pitch = gnx + 2;
+  for (long long t = blockIdx.x * (long long)blockDim.x + threadIdx.x; t < 2 * tot; t += (long long)gridDim.x * blockDim.x) {
+    const int k = (int)(t / tot);
+    const long long q = t - k * tot;
+    dense[t] = pad[k * padsz + pitch + 1 + (q % gnx) + (long long)pitch * (q / gnx)];
+  }
+  if (blockIdx.x == 0 && threadIdx.x == 0) dense[2 * tot] = (double)*iters;
+}
+
+__global__ void k_of_agg_iters(const double *src, int *iters) { *iters = (int)*src; }
+
 // ---- host side ---------------------------------------------------------------------
 
 static System2 *get_system(examg_ctx *c, int h) {
@@ -548,6 +590,10 @@ static OfArgs of_args(examg_ctx *c, const System2 &s) {
   a.ny = g.n[1] - 1;
   a.pitch = g.pitch;
   a.par = (g.goff[0] + g.goff[1]) & 1;
+  a.xlo = a.ylo = 0;
+  a.xhi = a.nx;
+  a.yhi = a.ny;
+  a.phys = (c->nb[0][0] ? 0 : 1) | (c->nb[0][1] ? 0 : 2) | (c->nb[1][0] ? 0 : 4) | (c->nb[1][1] ? 0 : 8);
   for (int k = 0; k < 5; ++k) a.L[k] = s.L[k];
   a.a2 = s.a2;
   a.cuu = field_ptr(c, &c->fields[s.cuu], -1);
@@ -590,8 +636,9 @@ static int of_max_sweeps() {
 static bool of_fused_usable(examg_ctx *c, const System2 &s) {
   const LevelGeom &g = *geom(c, s.level);
   const int nx = g.n[0] - 1, ny = g.n[1] - 1;
-  // several blocks: the colour kernels with `communicate` in between (the wavefront kernel clamps at all four edges)
-  return c->world == 1 && of_max_sweeps() > 0 && nx % 2 == 0 && nx >= 128 && ny >= 16;
+  // several blocks: blocks start on even cells (the colour pattern of the lanes), up to two sweeps per pass (S = 4 layers)
+  if (c->world > 1 && (((g.goff[0] | g.goff[1]) & 1) || getenv("EXAMG_OF_NO_FUSED_BLOCKS"))) return false;
+  return of_max_sweeps() > 0 && nx % 2 == 0 && nx >= 128 && ny >= 16;
 }
 
 // several blocks: `communicate` of both unknowns in one handshake; the ghost cells at block faces take the neighbour's
@@ -615,7 +662,8 @@ static int launch_of_rbw_s(examg_ctx *c, const OfArgs &a, const double *u, const
   if (nseg > max_seg) nseg = max_seg;
   const int seg_rows = (a.ny + nseg - 1) / nseg;
   nseg = (a.ny + seg_rows - 1) / seg_rows;
-  k_of_rbw<S><<<dim3(gx, nseg), 128, 0, c->stream>>>(a, u, v, bu, bv, uo, vo, relax, seg_rows, nstrips);
+  if (c->world > 1) k_of_rbw<S, true><<<dim3(gx, nseg), 128, 0, c->stream>>>(a, u, v, bu, bv, uo, vo, relax, seg_rows, nstrips);
+  else k_of_rbw<S, false><<<dim3(gx, nseg), 128, 0, c->stream>>>(a, u, v, bu, bv, uo, vo, relax, seg_rows, nstrips);
   EXAMG_LAUNCH_CHECK(c);
   return EXAMG_OK;
 }
@@ -624,7 +672,12 @@ static int launch_of_rbw_s(examg_ctx *c, const OfArgs &a, const double *u, const
 static int launch_of_rbw(examg_ctx *c, const System2 &s, Field &fu, Field &fv, const double *bu, const double *bv,
                          double relax, int sweeps) {
   const LevelGeom &g = *geom(c, s.level);
-  const OfArgs a = of_args(c, s);
+  OfArgs a = of_args(c, s);
+  const int S = 2 * sweeps;
+  if (!(a.phys & 1)) a.xlo = -S;
+  if (!(a.phys & 2)) a.xhi = a.nx + S;
+  if (!(a.phys & 4)) a.ylo = -S;
+  if (!(a.phys & 8)) a.yhi = a.ny + S;
   const double *u = field_ptr(c, &fu, -1), *v = field_ptr(c, &fv, -1);
   double *uo = fu.shadow + g.origin, *vo = fv.shadow + g.origin;
   int rc;
@@ -733,8 +786,25 @@ int examg_system2_smooth_rb(examg_ctx *c, int sys, int u, int v, int rhs_u, int 
       if ((rc = ensure_shadow(c, *fu)) || (rc = ensure_shadow(c, *fv))) return rc;
       for (int it = 0; it < nsweeps;) {
         int plan = of_max_sweeps();
+        if (c->world > 1 && plan > 2) plan = 2;  // four ghost layers per side
         if (plan > nsweeps - it) plan = nsweeps - it;
+        if (c->world > 1) {
+          // `plan` sweeps = 2 plan half-sweeps: that many layers of u, v and one less of the right-hand sides and the
+          // coefficients (the redundant updates in the neighbours' layers read them), in one handshake; the static
+          // fields only when their layers are stale
+          const int S = 2 * plan;
+          Field *fs[7] = {fu, fv, bu, bv, &c->fields[s->cuu], &c->fields[s->cuv], &c->fields[s->cvv]};
+          Field *todo[7];
+          int slots[7], depths[7], n = 0;
+          for (int k = 0; k < 7; ++k) {
+            const int d = k < 2 ? S : S - 1;
+            if (k >= 2 && fs[k]->halo_depth >= d) continue;
+            todo[n] = fs[k]; slots[n] = fs[k]->cur; depths[n++] = d;
+          }
+          if ((rc = do_exchange_many(c, todo, slots, depths, n))) return rc;
+        }
         if ((rc = launch_of_rbw(c, *s, *fu, *fv, field_ptr(c, bu, -1), field_ptr(c, bv, -1), relax, plan))) return rc;
+        fu->halo_depth = fv->halo_depth = 0;
         it += plan;
       }
       return EXAMG_OK;
@@ -761,6 +831,7 @@ static int cell_transfer(examg_ctx *c, const int *src, const int *dst, int n, bo
     lc = coarse;
     pr.src[k] = field_ptr(c, fs, -1);
     pr.dst[k] = field_ptr(c, fd, -1);
+    fd->halo_depth = 0;
   }
   const LevelGeom &gf = *geom(c, lf), &gc = *geom(c, lc);
   if (c->cfg.dim == 3) {
@@ -852,6 +923,77 @@ static int of_cg_blocks(examg_ctx *c, const System2 &s, const int *fields, int m
   return EXAMG_OK;
 }
 
+// The level is agglomerated (comm_agg_setup_cells, examg_optflow_create): every block stores its cells of u, v, the
+// right-hand sides and the coefficients into dense global arrays on rank 0, rank 0 runs the one-block kernel on the
+// global grid, every block takes its cells of the result.  No host synchronisation: the cycle stays one CUDA graph.
+static bool of_cg_agg_usable(examg_ctx *c, const System2 &s) {
+  int gn[3];
+  long long tot;
+  return comm_agg_cells(c, gn, &tot) == s.level && !getenv("EXAMG_OF_NO_AGG");
+}
+
+static int of_cg_agg(examg_ctx *c, System2 &s, const int *fields, int max_it, double rel_tol, int *iters_out) {
+  int gn[3], rc;
+  long long tot;
+  comm_agg_cells(c, gn, &tot);
+  Field *in[7] = {cell_field(c, fields[0], s.level), cell_field(c, fields[1], s.level), cell_field(c, fields[2], s.level),
+                  cell_field(c, fields[3], s.level), &c->fields[s.cuu], &c->fields[s.cuv], &c->fields[s.cvv]};
+  for (int k = 0; k < 7; ++k)
+    if ((rc = comm_agg_gather(c, *in[k], k))) return rc;
+  if (c->cfg.rank == 0) {
+    if (!s.agg_pad) return set_error(EXAMG_ESTATE, "examg_system2_cg_coarse: no global arrays for the agglomerated level");
+    const int pitch = gn[0] + 2;
+    const long long padsz = (long long)pitch * (gn[1] + 2);
+    const int grid = (int)((7 * tot + 255) / 256 > 148 ? 148 : (7 * tot + 255) / 256);
+    k_of_agg_in<<<grid, 256, 0, c->stream>>>(comm_agg_in(c), tot, gn[0], gn[1], s.agg_pad, padsz);
+    EXAMG_LAUNCH_CHECK(c);
+    double *p[13];
+    for (int k = 0; k < 13; ++k) p[k] = s.agg_pad + k * padsz + pitch + 1;
+    OfArgs a = of_args(c, s);
+    a.nx = gn[0];
+    a.ny = gn[1];
+    a.pitch = pitch;
+    a.par = 0;
+    a.xlo = a.ylo = 0;
+    a.xhi = a.nx;
+    a.yhi = a.ny;
+    a.phys = 15;
+    a.cuu = p[10];
+    a.cuv = p[11];
+    a.cvv = p[12];
+    int nt = 32;
+    while (nt < 1024 && nt < a.nx * a.ny) nt <<= 1;
+    k_of_cg<<<1, nt, 0, c->stream>>>(a, p[0], p[1], p[2], p[3], p[4], p[5], p[6], p[7], p[8], p[9], max_it, rel_tol, c->int_out);
+    EXAMG_LAUNCH_CHECK(c);
+    k_of_agg_out<<<grid, 256, 0, c->stream>>>(s.agg_pad, padsz, gn[0], comm_agg_out(c), tot, c->int_out);
+    EXAMG_LAUNCH_CHECK(c);
+  }
+  if ((rc = comm_agg_scatter(c, *in[0], 0)) || (rc = comm_agg_scatter(c, *in[1], 1))) return rc;
+  if (c->cfg.rank != 0) {
+    k_of_agg_iters<<<1, 1, 0, c->stream>>>(comm_agg_out_peer(c) + 2 * tot, c->int_out);
+    EXAMG_LAUNCH_CHECK(c);
+  }
+  if ((rc = examg_apply_bc(c, fields[0], -1)) || (rc = examg_apply_bc(c, fields[1], -1))) return rc;
+  if (iters_out) {
+    EXAMG_CUDA(cudaMemcpyAsync(c->int_host, c->int_out, sizeof(int), cudaMemcpyDeviceToHost, c->stream));
+    EXAMG_SYNC(c);
+    *iters_out = c->int_host[0];
+  }
+  return EXAMG_OK;
+}
+
+// global arrays of the agglomerated level on rank 0 (allocation: not inside a captured cycle)
+static int of_agg_prepare(examg_ctx *c, System2 &s) {
+  int gn[3];
+  long long tot;
+  if (comm_agg_cells(c, gn, &tot) != s.level || c->cfg.rank != 0 || s.agg_pad) return EXAMG_OK;
+  const size_t padsz = (size_t)(gn[0] + 2) * (gn[1] + 2);
+  s.agg_pad = dev_alloc(c, 13 * padsz * sizeof(double));
+  if (!s.agg_pad) return set_error(EXAMG_ENOMEM, "global arrays of the agglomerated level %d", s.level);
+  EXAMG_CUDA(cudaMemsetAsync(s.agg_pad, 0, 13 * padsz * sizeof(double), c->stream));
+  return EXAMG_OK;
+}
+
 extern "C" {
 
 int examg_system2_cg_coarse(examg_ctx *c, int sys, const int *fields, int max_it, double rel_tol, int *iters_out) {
@@ -863,7 +1005,9 @@ int examg_system2_cg_coarse(examg_ctx *c, int sys, const int *fields, int max_it
     if (!f) return set_error(EXAMG_EINVAL, "examg_system2_cg_coarse: field %d (#%d) is not a cell field of level %d", fields[k], k, s->level);
     p[k] = field_ptr(c, f, -1);
   }
-  if (c->world > 1) return of_cg_blocks(c, *s, fields, max_it, rel_tol, iters_out);
+  if (c->world > 1)
+    return of_cg_agg_usable(c, *s) ? of_cg_agg(c, *s, fields, max_it, rel_tol, iters_out)
+                                   : of_cg_blocks(c, *s, fields, max_it, rel_tol, iters_out);
   const OfArgs a = of_args(c, *s);
   int nt = 32;
   while (nt < 1024 && nt < a.nx * a.ny) nt <<= 1;
@@ -891,6 +1035,8 @@ struct examg_optflow {
   int cg[4] = {-1, -1, -1, -1};  // cgTmp0_u, cgTmp0_v, cgTmp1_u, cgTmp1_v @coarsest
   struct Graph { cudaGraphExec_t exec = nullptr; long long launches = 0; std::vector<int> exit_state; };
   std::map<std::vector<int>, Graph> graphs;  // keyed by which buffer of u, v is active on every level
+  // several blocks: the legs before and after the coarse solve (which synchronises with the host for its global sums)
+  std::map<std::vector<int>, Graph> graphs_down, graphs_up;
 };
 
 namespace {
@@ -905,10 +1051,15 @@ int of_zero(examg_ctx *c, int h) {  // u@coarser = 0; apply bc: the whole alloca
   return EXAMG_OK;
 }
 
+// which buffer of u, v is active, and how many ghost layers of every field hold the neighbour blocks' values (the
+// host-side decisions of a captured leg depend on both, and a replay has to leave both as the capture did)
 std::vector<int> of_state(examg_optflow *o) {
   std::vector<int> key;
   for (int k = 0; k < 2; ++k)
     for (int h : o->f[k]) key.push_back(o->c->fields[h].swapped ? 1 : 0);
+  if (o->c->world > 1)
+    for (int k = 0; k < 9; ++k)
+      for (int h : o->f[k]) key.push_back(o->c->fields[h].halo_depth);
   return key;
 }
 
@@ -924,6 +1075,9 @@ void of_restore(examg_optflow *o, const std::vector<int> &key) {
         f.swapped = !f.swapped;
       }
     }
+  if (o->c->world > 1)
+    for (int k = 0; k < 9; ++k)
+      for (int h : o->f[k]) o->c->fields[h].halo_depth = key[pos++];
 }
 
 int of_vcycle_rec(examg_optflow *o, int level) {
@@ -947,6 +1101,66 @@ int of_vcycle_rec(examg_optflow *o, int level) {
   if ((rc = examg_prolong_add_cell(c, uc, uf, 2))) return rc;
   return examg_system2_smooth_rb(c, o->sys[l], o->f[0][l], o->f[1][l], o->f[2][l], o->f[3][l], o->desc.relax,
                                  o->desc.nu_post);
+}
+
+// the same cycle as two loops around the coarse solve
+int of_down(examg_optflow *o, int level) {
+  examg_ctx *c = o->c;
+  int rc;
+  for (; level > c->cfg.min_level; --level) {
+    const int l = of_lv(o, level);
+    if ((rc = examg_system2_smooth_rb(c, o->sys[l], o->f[0][l], o->f[1][l], o->f[2][l], o->f[3][l], o->desc.relax,
+                                      o->desc.nu_pre))) return rc;
+    if ((rc = examg_system2_residual(c, o->sys[l], o->f[0][l], o->f[1][l], o->f[2][l], o->f[3][l], o->f[4][l],
+                                     o->f[5][l], nullptr))) return rc;
+    const int res[2] = {o->f[4][l], o->f[5][l]}, rhsc[2] = {o->f[2][l - 1], o->f[3][l - 1]};
+    if ((rc = examg_restrict_cell(c, res, rhsc, 2))) return rc;
+    if ((rc = of_zero(c, o->f[0][l - 1])) || (rc = of_zero(c, o->f[1][l - 1]))) return rc;
+  }
+  return EXAMG_OK;
+}
+
+int of_up(examg_optflow *o, int level) {
+  examg_ctx *c = o->c;
+  int rc;
+  for (int lv = c->cfg.min_level + 1; lv <= level; ++lv) {
+    const int l = of_lv(o, lv);
+    const int uc[2] = {o->f[0][l - 1], o->f[1][l - 1]}, uf[2] = {o->f[0][l], o->f[1][l]};
+    if ((rc = examg_prolong_add_cell(c, uc, uf, 2))) return rc;
+    if ((rc = examg_system2_smooth_rb(c, o->sys[l], o->f[0][l], o->f[1][l], o->f[2][l], o->f[3][l], o->desc.relax,
+                                      o->desc.nu_post))) return rc;
+  }
+  return EXAMG_OK;
+}
+
+// capture `leg` once per state, replay it afterwards
+int of_replay(examg_optflow *o, std::map<std::vector<int>, examg_optflow::Graph> &graphs, int (*leg)(examg_optflow *, int),
+              int level) {
+  examg_ctx *c = o->c;
+  const std::vector<int> key = of_state(o);
+  auto it = graphs.find(key);
+  if (it == graphs.end()) {
+    const long long l0 = c->launches;
+    cudaGraph_t graph = nullptr;
+    EXAMG_CUDA(cudaStreamBeginCapture(c->stream, cudaStreamCaptureModeThreadLocal));
+    const int rc = leg(o, level);
+    const cudaError_t e = cudaStreamEndCapture(c->stream, &graph);
+    if (rc) { if (graph) cudaGraphDestroy(graph); return rc; }
+    if (e != cudaSuccess) return set_error(EXAMG_ECUDA, "graph capture of mgCycle failed: %s", cudaGetErrorString(e));
+    examg_optflow::Graph g;
+    const cudaError_t e2 = cudaGraphInstantiate(&g.exec, graph, 0);
+    cudaGraphDestroy(graph);
+    if (e2 != cudaSuccess) return set_error(EXAMG_ECUDA, "cudaGraphInstantiate: %s", cudaGetErrorString(e2));
+    g.launches = c->launches - l0;
+    c->launches = l0;  // nothing ran yet
+    g.exit_state = of_state(o);
+    of_restore(o, key);
+    it = graphs.emplace(key, g).first;
+  }
+  EXAMG_CUDA(cudaGraphLaunch(it->second.exec, c->stream));
+  c->launches += it->second.launches;
+  of_restore(o, it->second.exit_state);
+  return EXAMG_OK;
 }
 
 }  // namespace
@@ -993,6 +1207,10 @@ examg_optflow *examg_optflow_create(examg_ctx *c, const examg_optflow_desc *d) {
     if (ok && of_fused_usable(c, c->systems[sh]))
       ok = ensure_shadow(c, c->fields[o->f[0].back()]) == EXAMG_OK && ensure_shadow(c, c->fields[o->f[1].back()]) == EXAMG_OK;
   }
+  // several blocks: the coarsest level as one grid on rank 0 for the coarse solve (7 arrays in, 2 out + the iteration
+  // count; a few dozen cells)
+  if (ok && c->world > 1 && !getenv("EXAMG_OF_NO_AGG"))
+    ok = comm_agg_setup_cells(c, c->cfg.min_level, 7, 2, 1) == EXAMG_OK && of_agg_prepare(c, c->systems[o->sys[0]]) == EXAMG_OK;
   if (ok) {
     o->img0 = examg_field_create_cell(c, "img0", c->cfg.max_level, 1, 1);
     o->img1 = examg_field_create_cell(c, "img1", c->cfg.max_level, 1, 1);
@@ -1018,8 +1236,9 @@ examg_optflow *examg_optflow_create(examg_ctx *c, const examg_optflow_desc *d) {
 
 int examg_optflow_destroy(examg_optflow *o) {
   if (!o) return EXAMG_OK;
-  for (auto &kv : o->graphs)
-    if (kv.second.exec) cudaGraphExecDestroy(kv.second.exec);
+  for (auto *m : {&o->graphs, &o->graphs_down, &o->graphs_up})
+    for (auto &kv : *m)
+      if (kv.second.exec) cudaGraphExecDestroy(kv.second.exec);
   delete o;
   return EXAMG_OK;
 }
@@ -1049,6 +1268,7 @@ int examg_optflow_init_fields(examg_optflow *o) {
                                            1.0 / g.h[1], -1.0 / g.h[1], ptr(o->f[6][l]), ptr(o->f[7][l]),
                                            ptr(o->f[8][l]), ptr(o->f[2][l]), ptr(o->f[3][l]));
   EXAMG_LAUNCH_CHECK(c);
+  for (int k : {2, 3, 6, 7, 8}) c->fields[o->f[k][l]].halo_depth = 0;
   for (int level = L - 1; level >= c->cfg.min_level; --level) {  // initGradients@(all but finest)
     const int k = of_lv(o, level);
     const int fine[3] = {o->f[6][k + 1], o->f[7][k + 1], o->f[8][k + 1]}, coarse[3] = {o->f[6][k], o->f[7][k], o->f[8][k]};
@@ -1062,33 +1282,20 @@ int examg_optflow_vcycle(examg_optflow *o, int level) {
   examg_ctx *c = o->c;
   if (level < 0) level = c->cfg.max_level;
   if (level < c->cfg.min_level || level > c->cfg.max_level) return set_error(EXAMG_EINVAL, "examg_optflow_vcycle: level %d", level);
-  // several blocks: the coarse solve synchronises with the host for its global sums -- no graph
-  if (level != c->cfg.max_level || c->world > 1) return of_vcycle_rec(o, level);
-  // one graph per buffer state (the fused sweeps exchange u, v with their second buffers)
-  const std::vector<int> key = of_state(o);
-  auto it = o->graphs.find(key);
-  if (it == o->graphs.end()) {
-    const long long l0 = c->launches;
-    cudaGraph_t graph = nullptr;
-    EXAMG_CUDA(cudaStreamBeginCapture(c->stream, cudaStreamCaptureModeThreadLocal));
-    const int rc = of_vcycle_rec(o, level);
-    const cudaError_t e = cudaStreamEndCapture(c->stream, &graph);
-    if (rc) { if (graph) cudaGraphDestroy(graph); return rc; }
-    if (e != cudaSuccess) return set_error(EXAMG_ECUDA, "graph capture of mgCycle failed: %s", cudaGetErrorString(e));
-    examg_optflow::Graph g;
-    const cudaError_t e2 = cudaGraphInstantiate(&g.exec, graph, 0);
-    cudaGraphDestroy(graph);
-    if (e2 != cudaSuccess) return set_error(EXAMG_ECUDA, "cudaGraphInstantiate: %s", cudaGetErrorString(e2));
-    g.launches = c->launches - l0;
-    c->launches = l0;  // nothing ran yet
-    g.exit_state = of_state(o);
-    of_restore(o, key);
-    it = o->graphs.emplace(key, g).first;
+  if (level != c->cfg.max_level || getenv("EXAMG_NO_GRAPH")) return of_vcycle_rec(o, level);
+  if (c->world > 1 && !of_cg_agg_usable(c, c->systems[o->sys[0]])) {
+    // several blocks, coarse solve on the blocks: it synchronises with the host for its global sums; one graph for
+    // the legs on either side of it
+    int rc;
+    if ((rc = of_replay(o, o->graphs_down, of_down, level))) return rc;
+    const int l = 0;
+    const int fl[10] = {o->f[0][l], o->f[1][l], o->f[2][l], o->f[3][l], o->f[4][l], o->f[5][l],
+                        o->cg[0], o->cg[1], o->cg[2], o->cg[3]};
+    if ((rc = examg_system2_cg_coarse(c, o->sys[l], fl, o->desc.cg_max_it, o->desc.cg_rel_tol, nullptr))) return rc;
+    return of_replay(o, o->graphs_up, of_up, level);
   }
-  EXAMG_CUDA(cudaGraphLaunch(it->second.exec, c->stream));
-  c->launches += it->second.launches;
-  of_restore(o, it->second.exit_state);
-  return EXAMG_OK;
+  // one graph per buffer state (the fused sweeps exchange u, v with their second buffers)
+  return of_replay(o, o->graphs, of_vcycle_rec, level);
 }
 
 int examg_optflow_residual_norm(examg_optflow *o, double *norm_out) {

@@ -56,17 +56,23 @@ def test_cell_fields_on_several_blocks(world, name, blocks):
     assert out.returncode == 0 and "CELL MGPU OK" in out.stdout, out.stdout[-3000:] + out.stderr[-3000:]
 
 
+@pytest.mark.parametrize("variant", ["default", "on-blocks"])
 @pytest.mark.parametrize("world,blocks,level", [(2, "2,1", 8), (2, "1,2", 7), (4, "2,2", 8), (8, "4,2", 8)])
-def test_optical_flow_on_several_blocks(world, blocks, level):
-    """Benchmark/OptFlow2D on several blocks: colour kernels with `communicate` in between, the
-    coarse CG with global sums; flow field bit-identical to the same program on one block and to the oracle, norms
-    within 1e-12, CG iteration counts equal (tests/mgpu/optflow_worker.py)."""
+def test_optical_flow_on_several_blocks(world, blocks, level, variant):
+    """Benchmark/OptFlow2D on several blocks.  default: fused wavefront sweeps over the block
+    plus the neighbours' layers, coarsest level agglomerated onto rank 0 for the coupled CG, the cycle one CUDA graph;
+    on-blocks: colour kernels with `communicate` in between and the CG on the blocks with global sums.  Flow field
+    bit-identical to the same program on one block and to the oracle, norms within 1e-12, CG iteration counts equal
+    (tests/mgpu/optflow_worker.py)."""
     if _ngpus() < world:
         pytest.skip("needs %d GPUs" % world)
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", str(world),
            "--master-addr", "127.0.0.1", "--master-port", str(29780 + world), os.path.join(ROOT, "tests", "mgpu", "optflow_worker.py"),
            "--level", str(level), "--blocks", blocks]
-    out = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
+    env = dict(os.environ)
+    if variant == "on-blocks":
+        env.update(EXAMG_OF_NO_AGG="1", EXAMG_OF_NO_FUSED_BLOCKS="1")
+    out = subprocess.run(cmd, capture_output=True, text=True, timeout=600, env=env)
     assert out.returncode == 0 and "OPTFLOW MGPU OK" in out.stdout, out.stdout[-3000:] + out.stderr[-3000:]
 
 
