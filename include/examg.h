@@ -348,7 +348,10 @@ int examg_solver_last_cg_iters(examg_solver *s, int *iters_out);
  *   A = [ c_uu + scale*L   c_uv          ]   L = constant 5-point stencil (declared centre,-x,+x,-y,+y),
  *       [ c_uv             c_vv + scale*L ]   c_* = cell fields (uuSten, uvSten = vuSten, vvSten)
  * All loops run over all cells; Neumann ghost cells of the written fields are refreshed by the same
- * kernel (`apply bc` costs no launch).                                                          */
+ * kernel (`apply bc` costs no launch).
+ * Several blocks (contexts wired with examg_comm_export / _import): the entry points below `communicate`
+ * what they read (the smoother: u, v, the right-hand sides and the coefficients, as many layers as the sweeps
+ * of one pass need, in one handshake); results do not depend on the block grid.                  */
 typedef struct {
   int laplace;          /* stencil handle; fixes the level */
   double scale;         /* alpha ** 2 */
@@ -370,10 +373,15 @@ int examg_restrict_cell(examg_ctx *ctx, const int *fine, const int *coarse, int 
  * (C/s/e/operator/l4/L4_DefaultProlongation.scala:30-45)                                        */
 int examg_prolong_add_cell(examg_ctx *ctx, const int *coarse, const int *fine, int nfields);
 /* mgCycle@coarsest of the optical-flow programs: CG on both unknowns.  fields = { u, v, rhs_u, rhs_v,
- * residual_u, residual_v, cgTmp0_u, cgTmp0_v, cgTmp1_u, cgTmp1_v }; runs on the device.        */
+ * residual_u, residual_v, cgTmp0_u, cgTmp0_v, cgTmp1_u, cgTmp1_v }; runs on the device.  Several blocks: on the
+ * level examg_optflow_create set up for it, rank 0 solves on the global grid (u, v come back to every block, the
+ * other fields stay as they are); on any other level the loops run on the blocks with global sums, which
+ * synchronises with the host at every reduction point.                                            */
 int examg_system2_cg_coarse(examg_ctx *ctx, int sys, const int *fields, int max_it, double rel_tol, int *iters_out);
 
-/* whole program: InitFields / mgCycle@all / doSolve@finest as one library object */
+/* whole program: InitFields / mgCycle@all / doSolve@finest as one library object.  Several blocks: create it on
+ * every rank BEFORE examg_comm_export (it allocates the staging of the coarsest level on rank 0); blocks must
+ * start on even cells for the fused sweeps (otherwise the per-colour kernels run).                 */
 typedef struct {
   double alpha;          /* Globals { Val alpha }              */
   double relax;          /* solve locally relax ...            */
