@@ -94,6 +94,10 @@ struct Stencil {
   double coef[EXAMG_MAX_STENCIL];
   int coeff_field = -1;  // -1: constant coefficients
   bool is7 = false;      // 3D 7-point constant stencil (fast path)
+  // red-black sweeps over stencil-field coefficients: a copy of the coefficient field with every row split into its
+  // even and its odd elements (examg_kernels.cu, k_rbv), valid for coefficient generation rbc_gen
+  double *rbc = nullptr;
+  long long rbc_gen = -1;
 };
 
 // [c_uu + a2*L, c_uv; c_uv, c_vv + a2*L] on two cell fields (the optical-flow operator, examg_optflow.cu)
@@ -254,6 +258,9 @@ int residual_restrict_op(examg_ctx *c, int A, int u, int rhs, int rhs_coarse, do
 int launch_jacobi(examg_ctx *c, const Stencil &s, double omega, const double *u, const double *rhs,
                   double *unext);
 int launch_rb(examg_ctx *c, const Stencil &s, double omega, double *u, const double *rhs, int color);
+// brings the split-row coefficient copy of a stencil-field operator up to date (allocates on first use: call it
+// outside graph capture; launch_rb falls back to the strided reads while there is no valid copy)
+int rb_compact_prepare(examg_ctx *c, Stencil &s);
 int launch_color_generic(examg_ctx *c, const Stencil &s, double omega, double *u, const double *rhs, int ncol, int cx,
                          int cy, int cz);
 int launch_restrict(examg_ctx *c, int lvl_fine, double scale, const double *rf, double *rhsc);

@@ -110,6 +110,49 @@ k_stencil_color(const GridArgs g, const __grid_constant__ StencilArgs st, const 
   (void)cx; (void)cy; (void)cz;
 }
 
+// ---- red-black Gauss-Seidel over stencil-field coefficients ------------------------------------------------------------
+// One colour of a sweep touches every other node of a row: the NST coefficient loads of a warp use half of every
+// 32-byte sector they fetch, and both colour passes fetch all of them -- 2 x 8 NST bytes per node and sweep where
+// 8 NST are needed (measured 0.52 of the roofline, 7-point operator at 256^3).  The coefficients are static, so the
+// operator keeps a second copy with every row split into its even and its odd elements
+//   split(row, i') = row + (i' & 1) * pitch / 2 + (i' >> 1),      i' = index inside the allocated row
+// and a colour pass reads consecutive doubles: each coefficient is fetched once per sweep.  Same values, same fold
+// order as k_stencil<M_RB> => bit-identical.  Cost: the coefficient memory twice (EXAMG_RB_COMPACT=0 turns it off).
+__global__ void __launch_bounds__(256) k_split_rows(const double *__restrict__ src, double *__restrict__ dst, int pitch,
+                                                    long long total) {
+  for (long long t = blockIdx.x * (long long)blockDim.x + threadIdx.x; t < total; t += (long long)gridDim.x * blockDim.x) {
+    const int ip = (int)(t % pitch);
+    dst[t - ip + (ip & 1) * (pitch >> 1) + (ip >> 1)] = src[t];
+  }
+}
+
+template <int NST>
+__global__ void __launch_bounds__(256)
+k_rbv(const GridArgs g, const __grid_constant__ StencilArgs st, const double *__restrict__ cs, long long sfvol,
+      long long origin, double *u, const double *__restrict__ rhs, double w, int color, int kz) {
+  const int nst = NST > 0 ? NST : st.nst;
+  const int tx = blockIdx.x * blockDim.x + threadIdx.x;
+  const int z0 = g.lo[2] + blockIdx.z * kz;
+  const int z1 = min(z0 + kz, g.hi[2]);
+  const int xoff = (int)(origin % g.pitch), half = g.pitch >> 1;
+  for (int j = g.lo[1] + blockIdx.y * blockDim.y + threadIdx.y; j < g.hi[1]; j += gridDim.y * blockDim.y) {
+    for (int k = z0; k < z1; ++k) {
+      const int i = g.lo[0] + ((g.lo[0] + j + k + g.par + color) & 1) + 2 * tx;
+      if (i < g.hi[0]) {
+        const long long row = (long long)g.pitch * j + g.plane * k;
+        const long long p = i + row;
+        const int ip = i + xoff;
+        const double *cp = cs + (origin - xoff + row) + (ip & 1) * half + (ip >> 1);
+        double acc = cp[0] * u[p + st.lin[0]];
+#pragma unroll
+        for (int q = 1; q < nst; ++q) acc = fma(cp[q * sfvol], u[p + st.lin[q]], acc);
+        const double ww = w / cp[st.centre * sfvol];
+        u[p] = fma(ww, rhs[p] - acc, u[p]);
+      }
+    }
+  }
+}
+
 // merges the per-block partials in index order; one block
 __global__ void __launch_bounds__(1024) k_final_sum(const dd *__restrict__ partials, int n, dd *out) {
   dd v = {0.0, 0.0};
@@ -434,7 +477,60 @@ int launch_jacobi_generic(examg_ctx *c, const Stencil &s, double omega, const do
                           double *unext) {
   return launch_stencil<M_JACOBI>(c, s, u, rhs, unext, omega, 0, -1);
 }
+static bool rb_compact_wanted(examg_ctx *c, const Stencil &s) {
+  static int mode = -1;
+  if (mode < 0) {
+    const char *e = getenv("EXAMG_RB_COMPACT");
+    mode = e ? atoi(e) : 1;
+  }
+  if (mode <= 0 || s.coeff_field < 0) return false;
+  const LevelGeom &g = *geom(c, s.level);
+  return (long long)g.n[0] * g.n[1] * g.n[2] >= (1 << 15) && g.pitch % 2 == 0;
+}
+
+int rb_compact_prepare(examg_ctx *c, Stencil &s) {
+  if (!rb_compact_wanted(c, s)) return EXAMG_OK;
+  const Field &cf = c->fields[s.coeff_field];
+  if (s.rbc && s.rbc_gen == cf.eval_gen) return EXAMG_OK;
+  cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;
+  cudaStreamIsCapturing(c->stream, &cap);
+  if (cap != cudaStreamCaptureStatusNone) return EXAMG_OK;  // not now: the strided reads serve until the next chance
+  const LevelGeom &g = *geom(c, s.level);
+  const long long total = (long long)cf.ncomp * g.vol;
+  if (!s.rbc) {
+    s.rbc = dev_alloc(c, (size_t)total * sizeof(double));
+    if (!s.rbc) {  // no room for the copy: keep the strided reads
+      s.rbc_gen = -1;
+      return EXAMG_OK;
+    }
+  }
+  k_split_rows<<<148 * 8, 256, 0, c->stream>>>(cf.slot[0], s.rbc, g.pitch, total);
+  EXAMG_LAUNCH_CHECK(c);
+  s.rbc_gen = cf.eval_gen;
+  return EXAMG_OK;
+}
+
 int launch_rb_generic(examg_ctx *c, const Stencil &s, double omega, double *u, const double *rhs, int color) {
+  if (s.coeff_field >= 0 && rb_compact_wanted(c, s)) {
+    Stencil &ms = const_cast<Stencil &>(s);  // the copy is a cache
+    int rc = rb_compact_prepare(c, ms);
+    if (rc) return rc;
+    if (s.rbc && s.rbc_gen == c->fields[s.coeff_field].eval_gen) {
+      const LevelGeom &g = *geom(c, s.level);
+      const GridArgs ga = grid_args_loc(c, g);
+      int ex = ga.hi[0] - ga.lo[0], ey = ga.hi[1] - ga.lo[1], ez = ga.hi[2] - ga.lo[2];
+      if (ex <= 0 || ey <= 0 || ez <= 0) return EXAMG_OK;
+      const Shape sh = make_shape((ex + 1) / 2, ey, ez);
+      const StencilArgs sa = stencil_args(g, s);
+      switch (s.nst) {
+        case 5: k_rbv<5><<<sh.grid, sh.block, 0, c->stream>>>(ga, sa, s.rbc, g.vol, g.origin, u, rhs, omega, color, sh.kz); break;
+        case 7: k_rbv<7><<<sh.grid, sh.block, 0, c->stream>>>(ga, sa, s.rbc, g.vol, g.origin, u, rhs, omega, color, sh.kz); break;
+        default: k_rbv<0><<<sh.grid, sh.block, 0, c->stream>>>(ga, sa, s.rbc, g.vol, g.origin, u, rhs, omega, color, sh.kz); break;
+      }
+      EXAMG_LAUNCH_CHECK(c);
+      return EXAMG_OK;
+    }
+  }
   return launch_stencil<M_RB>(c, s, u, rhs, u, omega, color, -1);
 }
 

@@ -142,6 +142,41 @@ def test_stencil_loops(dim, cells, lvl, npts, var, oracle):
     ctx.close()
 
 
+@pytest.mark.parametrize("dim,cells,lvl", [(3, (1, 1, 1), 6), (2, (3, 5), 7)])
+def test_rb_stencil_field_split_rows(dim, cells, lvl, oracle):
+    """Red-black sweeps over a stencil field read a copy of the coefficients with every row split into its even and odd
+    elements (k_rbv, examg_kernels.cu): bit-identical to the oracle, the copy follows new coefficients (upload and
+    examg_field_eval), and EXAMG_RB_COMPACT=0 (checked by the caller's environment in test_stencil_loops) is the same."""
+    from exastencils_b200 import runtime as rt
+    og = oracle
+    ctx = _ctx(dim, cells, lvl, lvl)
+    shape = ctx.shape(lvl)
+    offs = _stencil_offsets(dim, 2 * dim + 1)
+    st = og.Stencil.make(offs, [1.0] * len(offs))
+    u, rhs = _rand(shape, 11), _rand(shape, 12)
+    fu, ff = ctx.field_create("u", lvl, 2, 1), ctx.field_create("rhs", lvl, 1, 1)
+    cf = ctx.field_create("coef", lvl, 1, len(offs))
+    A = ctx.stencil_field(lvl, offs, cf)
+    ctx.upload(fu, u, 0)
+    ctx.upload(ff, rhs)
+    e = u.copy()
+    for gen in range(3):
+        sf = _rand((len(offs),) + shape, 20 + gen)
+        sf[0] = 4.0 + np.abs(sf[0])
+        if gen == 2:  # one component replaced on the device
+            sf[1] = -0.75
+        sf = np.ascontiguousarray(sf)
+        ctx.upload(cf, sf)
+        if gen == 2:
+            ctx.field_eval(cf, [(rt.OP_CONST, -0.75)], comp=1)
+        ctx.smooth_rbgs(A, fu, ff, 0.9, 2)
+        for _ in range(2):
+            og.smooth_rb(st, 0.9, e, rhs, 0, sf)
+            og.smooth_rb(st, 0.9, e, rhs, 1, sf)
+        assert np.array_equal(ctx.download(fu, lvl), e), "coefficient generation %d" % gen
+    ctx.close()
+
+
 @pytest.mark.parametrize("dim,cells,lvl", [(2, (1, 1), 5), (2, (3, 5), 3), (3, (1, 1, 1), 4), (3, (3, 2, 5), 2),
                                            (3, (9, 9, 9), 1), (3, (1, 1, 1), 1), (2, (1, 1), 1), (3, (1, 1, 1), 6),
                                            (2, (1, 1), 9)])
