@@ -477,7 +477,7 @@ int examg_solver_vcycle(examg_solver *s, int level) {
   // static operands: ghost layers of stencil-field coefficients are exchanged once, outside the captured cycle
   // (the fused stencil-field Jacobi reads them, examg_jacv.cuh); the twins on the agglomerated grid are brought
   // up to date
-  if (s->desc.smoother == EXAMG_SMOOTH_RBGS)  // split-row copies of stencil-field coefficients (k_rbv): allocate / refresh now
+  if (s->desc.smoother == EXAMG_SMOOTH_RBGS || s->desc.smoother == EXAMG_SMOOTH_COLORED_2)  // split-row copies of stencil-field coefficients (k_rbv): allocate / refresh now
     for (int h : s->stencils) {
       Stencil *st = get_stencil(c, h);
       int rc = st ? rb_compact_prepare(c, *st) : EXAMG_OK;

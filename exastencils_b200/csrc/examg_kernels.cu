@@ -94,17 +94,26 @@ k_stencil(const GridArgs g, const __grid_constant__ StencilArgs st, const double
 // "27-way", C/s/e/solver/l3/L3_VankaForEquation.scala:154-183): in place on the points with i_d % ncol == c_d.
 // Points of one colour are at least ncol >= 2 apart in every dimension, so a compact stencil never couples them and
 // the result does not depend on the traversal order.
-template <int NST, bool VAR>
+// SPLIT (two colours per dimension, stencil field): the coefficients come from the split-row copy of the operator
+// (see k_rbv below) -- `sf` is that copy and `origin` the offset of node (0,0,0) in it
+template <int NST, bool VAR, bool SPLIT = false>
 __global__ void __launch_bounds__(256)
 k_stencil_color(const GridArgs g, const __grid_constant__ StencilArgs st, const double *__restrict__ sf, long long sfvol,
                 double *u, const double *__restrict__ rhs, double w, int ncol, int cx, int cy, int cz, int ex, int ey,
-                int ez, int fx, int fy, int fz) {
+                int ez, int fx, int fy, int fz, long long origin = 0) {
   const long long total = (long long)ex * ey * ez;
+  const int xoff = SPLIT ? (int)(origin % g.pitch) : 0, half = g.pitch >> 1;
   for (long long t = blockIdx.x * (long long)blockDim.x + threadIdx.x; t < total; t += (long long)gridDim.x * blockDim.x) {
     const int i = fx + ncol * (int)(t % ex), j = fy + ncol * (int)((t / ex) % ey), k = fz + ncol * (int)(t / ((long long)ex * ey));
     const long long p = i + (long long)g.pitch * j + g.plane * k;
-    const double acc = conv<NST, VAR>(st, sf, sfvol, u, p);
-    const double ww = VAR ? w / sf[st.centre * sfvol + p] : w;
+    // conv() indexes its coefficient pointer with p: shift the pointer so that [p] is the node's place in the copy
+    const double *cf = sf;
+    if (SPLIT) {
+      const int ip = i + xoff;
+      cf = sf + (origin - xoff - i) + (ip & 1) * half + (ip >> 1);
+    }
+    const double acc = conv<NST, VAR>(st, cf, sfvol, u, p);
+    const double ww = VAR ? w / cf[st.centre * sfvol + p] : w;
     u[p] = fma(ww, rhs[p] - acc, u[p]);
   }
   (void)cx; (void)cy; (void)cz;
@@ -422,6 +431,8 @@ static int launch_stencil(examg_ctx *c, const Stencil &s, const double *u, const
   return EXAMG_OK;
 }
 
+static bool rb_compact_wanted(examg_ctx *c, const Stencil &s);
+
 // colour (cx, cy, cz) of an ncol^dim-way colouring; the colour of a point is its block-local index modulo ncol
 int launch_color_generic(examg_ctx *c, const Stencil &s, double omega, double *u, const double *rhs, int ncol, int cx,
                          int cy, int cz) {
@@ -443,6 +454,25 @@ int launch_color_generic(examg_ctx *c, const Stencil &s, double omega, double *u
   if (blocks > 148 * 16) blocks = 148 * 16;
   const double w = var ? omega : omega / s.coef[s.centre];
   const int czz = c->cfg.dim == 3 ? cz : -1;
+  // two colours per dimension on a stencil field: every other node of a row -> the split-row copy of the coefficients
+  if (var && ncol == 2 && rb_compact_wanted(c, s)) {
+    int rc = rb_compact_prepare(c, const_cast<Stencil &>(s));
+    if (rc) return rc;
+    if (s.rbc && s.rbc_gen == c->fields[s.coeff_field].eval_gen) {
+#define EXAMG_GOS(NST)                                                                                                  \
+  k_stencil_color<NST, true, true><<<(int)blocks, 256, 0, c->stream>>>(ga, sa, s.rbc, g.vol, u, rhs, w, ncol, cx, cy, czz, \
+                                                                        ext[0], ext[1], ext[2], first[0], first[1],      \
+                                                                        first[2], g.origin)
+      switch (s.nst) {
+        case 9: EXAMG_GOS(9); break;
+        case 27: EXAMG_GOS(27); break;
+        default: EXAMG_GOS(0); break;
+      }
+#undef EXAMG_GOS
+      EXAMG_LAUNCH_CHECK(c);
+      return EXAMG_OK;
+    }
+  }
 #define EXAMG_GOC(NST, VAR)                                                                                         \
   k_stencil_color<NST, VAR><<<(int)blocks, 256, 0, c->stream>>>(ga, sa, sf, g.vol, u, rhs, w, ncol, cx, cy, czz, ext[0], \
                                                                  ext[1], ext[2], first[0], first[1], first[2])

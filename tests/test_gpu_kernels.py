@@ -592,7 +592,9 @@ def test_timers():
 
 
 @pytest.mark.parametrize("dim,cells,lvl,npts,ncol", [(2, (3, 5), 3, 9, 2), (2, (4, 4), 4, 9, 3), (3, (1, 1, 1), 4, 27, 2),
-                                                     (3, (5, 3, 2), 2, 27, 3), (3, (1, 1, 1), 5, 7, 2)])
+                                                     (3, (5, 3, 2), 2, 27, 3), (3, (1, 1, 1), 5, 7, 2),
+                                                     # from 2^15 nodes: split-row coefficient copy of stencil fields
+                                                     (3, (1, 1, 1), 5, 27, 2), (2, (3, 5), 6, 9, 2)])
 @pytest.mark.parametrize("var", [False, True], ids=["const", "stencilfield"])
 def test_colored_gauss_seidel(dim, cells, lvl, npts, ncol, var, oracle):
     """solver_smoother_coloring 4-/9-way (2D) and 8-/27-way (3D): n^dim colours, last dimension slowest, in place
