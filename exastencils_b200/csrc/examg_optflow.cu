@@ -126,6 +126,42 @@ k_of_smooth_color(const OfArgs a, double *__restrict__ u, double *__restrict__ v
   store_neumann(v, i, j, a.nx, a.ny, a.pitch, nv);
 }
 
+// the same on the cells [xlo, xhi) x [ylo, yhi) of a block among several: its own cells plus layers of the neighbours'
+// cells (exchanged beforehand, updated redundantly); Neumann ghost cells on physical sides only
+__global__ void __launch_bounds__(256)
+k_of_smooth_color_mb(const OfArgs a, double *__restrict__ u, double *__restrict__ v, const double *__restrict__ fu,
+                     const double *__restrict__ fv, double relax, int color) {
+  const int j = a.ylo + blockIdx.y * blockDim.y + threadIdx.y;
+  if (j >= a.yhi) return;
+  const int i = a.xlo + ((a.xlo + j + color + a.par) & 1) + 2 * (blockIdx.x * blockDim.x + threadIdx.x);
+  if (i >= a.xhi) return;
+  const long long p = i + (long long)a.pitch * j;
+  // neighbours across a physical side: the cell itself (what its Neumann ghost cell holds; the ghost cells next to the
+  // neighbours' layers are not part of the exchange)
+  const bool cw = i == 0 && (a.phys & 1), ce = i == a.nx - 1 && (a.phys & 2);
+  const bool cs = j == 0 && (a.phys & 4), cn = j == a.ny - 1 && (a.phys & 8);
+  const long long pw = cw ? p : p - 1, pe = ce ? p : p + 1, ps = cs ? p : p - a.pitch, pn = cn ? p : p + a.pitch;
+  double ou = a.L[1] * u[pw], ov = a.L[1] * v[pw];
+  ou = fma(a.L[2], u[pe], ou); ov = fma(a.L[2], v[pe], ov);
+  ou = fma(a.L[3], u[ps], ou); ov = fma(a.L[3], v[ps], ov);
+  ou = fma(a.L[4], u[pn], ou); ov = fma(a.L[4], v[pn], ov);
+  const double f0 = fu[p] - a.a2 * ou, f1 = fv[p] - a.a2 * ov;
+  const double a01 = a.cuv[p];
+  const double a00 = fma(a.a2, a.L[0], a.cuu[p]), a11 = fma(a.a2, a.L[0], a.cvv[p]);
+  const double rdet = 1.0 / (a00 * a11 - a01 * a01);
+  const double i00 = rdet * a11, i01 = -(rdet * a01), i11 = rdet * a00;
+  const double su = i00 * f0 + i01 * f1, sv = i01 * f0 + i11 * f1;
+  const double keep = 1.0 - relax;
+  const double nu = u[p] * keep + relax * su, nv = v[p] * keep + relax * sv;
+  u[p] = nu;
+  v[p] = nv;
+  const int gi = (i == 0 && (a.phys & 1)) ? -1 : ((i == a.nx - 1 && (a.phys & 2)) ? a.nx : i);
+  const int gj = (j == 0 && (a.phys & 4)) ? -1 : ((j == a.ny - 1 && (a.phys & 8)) ? a.ny : j);
+  if (gi != i) { u[gi + (long long)a.pitch * j] = nu; v[gi + (long long)a.pitch * j] = nv; }
+  if (gj != j) { u[i + (long long)a.pitch * gj] = nu; v[i + (long long)a.pitch * gj] = nv; }
+  if (gi != i && gj != j) { u[gi + (long long)a.pitch * gj] = nu; v[gi + (long long)a.pitch * gj] = nv; }
+}
+
 // residual of both unknowns (+ sum of squares); thread per cell, rows by grid stride
 template <bool NORM>
 __global__ void __launch_bounds__(256)
@@ -777,6 +813,21 @@ int examg_system2_smooth_rb_color(examg_ctx *c, int sys, int u, int v, int rhs_u
   return EXAMG_OK;
 }
 
+// several blocks, S half-sweeps in a row: S layers of u, v and one less of the right-hand sides and the coefficients
+// (the redundant updates in the neighbours' layers read them), in one handshake; the static fields only when their
+// layers are stale
+static int of_exchange_deep(examg_ctx *c, const System2 &s, Field *fu, Field *fv, Field *bu, Field *bv, int S) {
+  Field *fs[7] = {fu, fv, bu, bv, &c->fields[s.cuu], &c->fields[s.cuv], &c->fields[s.cvv]};
+  Field *todo[7];
+  int slots[7], depths[7], n = 0;
+  for (int k = 0; k < 7; ++k) {
+    const int d = k < 2 ? S : S - 1;
+    if (k >= 2 && fs[k]->halo_depth >= d) continue;
+    todo[n] = fs[k]; slots[n] = fs[k]->cur; depths[n++] = d;
+  }
+  return do_exchange_many(c, todo, slots, depths, n);
+}
+
 int examg_system2_smooth_rb(examg_ctx *c, int sys, int u, int v, int rhs_u, int rhs_v, double relax, int nsweeps) {
   {
     OF_SYS(s, sys);
@@ -788,22 +839,38 @@ int examg_system2_smooth_rb(examg_ctx *c, int sys, int u, int v, int rhs_u, int 
         int plan = of_max_sweeps();
         if (c->world > 1 && plan > 2) plan = 2;  // four ghost layers per side
         if (plan > nsweeps - it) plan = nsweeps - it;
-        if (c->world > 1) {
-          // `plan` sweeps = 2 plan half-sweeps: that many layers of u, v and one less of the right-hand sides and the
-          // coefficients (the redundant updates in the neighbours' layers read them), in one handshake; the static
-          // fields only when their layers are stale
-          const int S = 2 * plan;
-          Field *fs[7] = {fu, fv, bu, bv, &c->fields[s->cuu], &c->fields[s->cuv], &c->fields[s->cvv]};
-          Field *todo[7];
-          int slots[7], depths[7], n = 0;
-          for (int k = 0; k < 7; ++k) {
-            const int d = k < 2 ? S : S - 1;
-            if (k >= 2 && fs[k]->halo_depth >= d) continue;
-            todo[n] = fs[k]; slots[n] = fs[k]->cur; depths[n++] = d;
-          }
-          if ((rc = do_exchange_many(c, todo, slots, depths, n))) return rc;
-        }
+        if (c->world > 1 && (rc = of_exchange_deep(c, *s, fu, fv, bu, bv, 2 * plan))) return rc;
         if ((rc = launch_of_rbw(c, *s, *fu, *fv, field_ptr(c, bu, -1), field_ptr(c, bv, -1), relax, plan))) return rc;
+        fu->halo_depth = fv->halo_depth = 0;
+        it += plan;
+      }
+      return EXAMG_OK;
+    }
+  }
+  {
+    // several blocks, levels too small for the wavefront kernel: the same redundancy with the colour kernel -- one
+    // handshake per two sweeps instead of one per colour; half-sweep h of S works on S - 1 - h layers of the
+    // neighbours' cells
+    OF_SYS(s, sys);
+    OF_FIELD(fu, u, s->level); OF_FIELD(fv, v, s->level); OF_FIELD(bu, rhs_u, s->level); OF_FIELD(bv, rhs_v, s->level);
+    const OfArgs a0 = of_args(c, *s);
+    if (c->world > 1 && fu != fv && a0.nx >= GHOST && a0.ny >= GHOST && !getenv("EXAMG_OF_NO_FUSED_BLOCKS")) {
+      for (int it = 0; it < nsweeps;) {
+        const int plan = nsweeps - it >= 2 ? 2 : 1, S = 2 * plan;
+        int rc = of_exchange_deep(c, *s, fu, fv, bu, bv, S);
+        if (rc) return rc;
+        for (int h = 0; h < S; ++h) {
+          OfArgs a = a0;
+          const int ext = S - 1 - h;
+          if (!(a.phys & 1)) a.xlo = -ext;
+          if (!(a.phys & 2)) a.xhi = a.nx + ext;
+          if (!(a.phys & 4)) a.ylo = -ext;
+          if (!(a.phys & 8)) a.yhi = a.ny + ext;
+          const dim3 block(64, 4), grid(((a.xhi - a.xlo) / 2 + 1 + block.x - 1) / block.x, (a.yhi - a.ylo + block.y - 1) / block.y);
+          k_of_smooth_color_mb<<<grid, block, 0, c->stream>>>(a, field_ptr(c, fu, -1), field_ptr(c, fv, -1),
+                                                              field_ptr(c, bu, -1), field_ptr(c, bv, -1), relax, h & 1);
+          EXAMG_LAUNCH_CHECK(c);
+        }
         fu->halo_depth = fv->halo_depth = 0;
         it += plan;
       }
