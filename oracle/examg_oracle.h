@@ -223,6 +223,33 @@ double ogf_solver_update_residual_norm(ogf_solver *s, int lvl);
 void ogf_solver_vcycle(ogf_solver *s, int lvl);
 int ogf_solver_last_cg_iters(const ogf_solver *s);
 
+/* ---- 3D optical flow: Vec3 unknown, 3x3 block inverse per cell (examg_oracle_optflow3.c;
+ *      Testing/Application/OpticalFlow3D.exa4) ------------------------------------------------ */
+typedef struct {
+  int F[3];               /* cells per dimension at level 0 */
+  int min_level, max_level;
+  double alpha;
+  int nu_pre, nu_post;
+  int cg_max_it;
+  double cg_rel_tol;
+} og3_config;
+/* fields of a level: flow 0..2, rhs 3..5, residual 6..8, gradContribution xx,xy,xz,yy,yz,zz 9..14 */
+enum { OG3_FLOW = 0, OG3_RHS = 3, OG3_RES = 6, OG3_G = 9, OG3_IMG0 = 15, OG3_IMG1 = 16 };
+typedef struct og3_solver og3_solver;
+og3_solver *og3_solver_create(const og3_config *cfg);
+void og3_solver_destroy(og3_solver *s);
+void og3_solver_dims(const og3_solver *s, int lvl, int n[3]);
+double *og3_solver_field(og3_solver *s, int lvl, int which);
+void og3_solver_init_images(og3_solver *s);
+void og3_solver_init_fields(og3_solver *s);
+double og3_solver_update_residual_norm(og3_solver *s, int lvl);
+void og3_solver_smooth_color(og3_solver *s, int lvl, int color);
+void og3_solver_smooth(og3_solver *s, int lvl, int n);
+void og3_solver_restrict(og3_solver *s, int lvl);
+void og3_solver_correct(og3_solver *s, int lvl);
+void og3_solver_vcycle(og3_solver *s, int lvl);
+int og3_solver_last_cg_iters(const og3_solver *s);
+
 /* printWithReducedPrec (C/s/e/util/ir/IR_ResolvePrintWithReducedPrec.scala:33-78):
  * formats like std::cout with precision p (default float notation). */
 void og_print_reduced_prec(double v, char *buf, size_t buflen);

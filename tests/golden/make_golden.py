@@ -46,6 +46,7 @@ FILES = {
     "FMG_3D_VarCoeff": "Testing/FMG/3D_VarCoeff.results",
     "Large_Hybrid": "Testing/Large/Hybrid.results",
     "Application_OpticalFlow2D": "Testing/Application/OpticalFlow2D.results",
+    "Application_OpticalFlow3D": "Testing/Application/OpticalFlow3D.results",
     "BC_2D_Polynomial": "Testing/BC/2D_Polynomial.results",
     "BC_2D_Trigonometric": "Testing/BC/2D_Trigonometric.results",
     "BC_3D_Polynomial": "Testing/BC/3D_Polynomial.results",

@@ -94,6 +94,20 @@ def test_golden_optical_flow_2d(oracle):
     assert got == open(path).read().split()
 
 
+def test_golden_optical_flow_3d(oracle):
+    """Testing/Application/OpticalFlow3D.{exa4,knowledge,results}: Vec3 flow on 64^3 cells, levels 2..6, V(3,3) red-black
+    sweeps with the 3x3 diagonal block inverted per cell, CG on 4^3 cells; pins examg_oracle_optflow3.c."""
+    import os
+    from oracle import optflow3
+    s = optflow3.Solver((1, 1, 1), 2, 6)
+    s.init_images()
+    s.init_fields()
+    got = optflow_history(s, oracle.print_reduced_prec)
+    s.close()
+    path = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "Application_OpticalFlow3D.results")
+    assert got == open(path).read().split()
+
+
 def test_golden_cell_based(oracle):
     """Testing/CellBased/{2D,3D}_{Basic,Neumann}: cell-centred FV Poisson, Dirichlet ghost cells 2g - u / Neumann ghost
     cells, cell restriction and correction, CG with `apply bc to VecP`, mean subtraction of the pure Neumann problem."""
