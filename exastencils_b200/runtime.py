@@ -52,6 +52,11 @@ class System2Desc(C.Structure):
     _fields_ = [("laplace", C.c_int), ("scale", C.c_double), ("c_uu", C.c_int), ("c_uv", C.c_int), ("c_vv", C.c_int)]
 
 
+class OptFlow3Desc(C.Structure):
+    _fields_ = [("alpha", C.c_double), ("nu_pre", C.c_int), ("nu_post", C.c_int), ("cg_max_it", C.c_int),
+                ("cg_rel_tol", C.c_double)]
+
+
 class StokesDesc(C.Structure):
     _fields_ = [("nu_pre", C.c_int), ("nu_post", C.c_int), ("nu_coarse", C.c_int), ("top_vel", C.c_double)]
 
@@ -172,6 +177,21 @@ SIGNATURES = {
     "examg_stokes_set_solution": (C.c_int, [C.c_void_p, C.c_int, C.c_double]),
     "examg_stokes_correct": (C.c_int, [C.c_void_p, C.c_int]),
     "examg_stokes_vcycle": (C.c_int, [C.c_void_p, C.c_int]),
+    "examg_optflow3_create": (C.c_void_p, [C.c_void_p, C.POINTER(OptFlow3Desc)]),
+    "examg_optflow3_destroy": (C.c_int, [C.c_void_p]),
+    "examg_optflow3_cells": (C.c_int, [C.c_void_p, C.c_int, C.POINTER(C.c_int)]),
+    "examg_optflow3_upload": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_void_p]),
+    "examg_optflow3_download": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_void_p]),
+    "examg_optflow3_init_fields": (C.c_int, [C.c_void_p]),
+    "examg_optflow3_smooth_color": (C.c_int, [C.c_void_p, C.c_int, C.c_int]),
+    "examg_optflow3_smooth": (C.c_int, [C.c_void_p, C.c_int, C.c_int]),
+    "examg_optflow3_residual": (C.c_int, [C.c_void_p, C.c_int, _dp]),
+    "examg_optflow3_restrict": (C.c_int, [C.c_void_p, C.c_int]),
+    "examg_optflow3_correct": (C.c_int, [C.c_void_p, C.c_int]),
+    "examg_optflow3_cg": (C.c_int, [C.c_void_p, C.POINTER(C.c_int)]),
+    "examg_optflow3_last_cg_iters": (C.c_int, [C.c_void_p, C.POINTER(C.c_int)]),
+    "examg_optflow3_vcycle": (C.c_int, [C.c_void_p, C.c_int]),
+    "examg_optflow3_cycles": (C.c_int, [C.c_void_p, C.c_int, _dp]),
     "examg_comm_blob_size": (C.c_int, [C.c_void_p]),
     "examg_comm_export": (C.c_int, [C.c_void_p, C.c_void_p]),
     "examg_comm_import": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int]),

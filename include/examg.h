@@ -441,6 +441,44 @@ int examg_stokes_set_solution(examg_stokes *s, int level, double value);  /* loo
 int examg_stokes_correct(examg_stokes *s, int level);       /* unknowns += Correction<loc> * unknowns@coarser; apply bc */
 int examg_stokes_vcycle(examg_stokes *s, int level);        /* VCycle@level (< 0: finest; the finest as one CUDA graph) */
 
+/* ---- the 3D optical-flow program: a Vec3 unknown on cell centres, 3 x 3 block inverse per cell ------------
+ * (Testing/Application/OpticalFlow3D.exa4; golden OpticalFlow3D.results)
+ *   combinedOp = alpha**2 * Laplace (x) I_3 + gradContribution,  gradContribution = the symmetric block of the
+ *   cell fields IxIx, IxIy, IxIz, IyIy, IyIz, IzIz at the centre entry;
+ *   smoother: repeat with { colour 0, colour 1 } { flow += inverse ( diag ( combinedOp ) ) * ( rhs - combinedOp * flow );
+ *   apply bc } -- diag() = the centre block, inverted per cell with the cofactor formulas of the generator's
+ *   compile-time branch (C/s/e/baseExt/ir/IR_MatOperations/IR_CompiletimeMatOps.scala:804-826).
+ * One block, 3D; level range and block_cells of the context.  Every array of a level is dense (nz+2) x (ny+2) x (nx+2)
+ * doubles, x fastest, one ghost cell per side (Neumann ghost cells are kept up to date by every kernel that writes).
+ * The components of the Vec3 fields are separate arrays.                                                       */
+typedef struct {
+  double alpha;          /* Globals { Val alpha }                                          */
+  int nu_pre, nu_post;   /* repeat 3 times                                                 */
+  int cg_max_it;         /* 128                                                            */
+  double cg_rel_tol;     /* 0.001                                                          */
+} examg_optflow3_desc;
+typedef struct examg_optflow3 examg_optflow3;
+/* array ids of a level: EXAMG_OF3_FLOW + c, EXAMG_OF3_RHS + c, EXAMG_OF3_RES + c (c = 0..2), EXAMG_OF3_G + 0..5 =
+ * xx, xy, xz, yy, yz, zz; the images live on the finest level */
+enum { EXAMG_OF3_FLOW = 0, EXAMG_OF3_RHS = 3, EXAMG_OF3_RES = 6, EXAMG_OF3_G = 9, EXAMG_OF3_IMG0 = 15, EXAMG_OF3_IMG1 = 16 };
+examg_optflow3 *examg_optflow3_create(examg_ctx *ctx, const examg_optflow3_desc *desc);
+int examg_optflow3_destroy(examg_optflow3 *o);
+int examg_optflow3_cells(examg_optflow3 *o, int level, int n[3]);       /* level < 0: finest */
+int examg_optflow3_upload(examg_optflow3 *o, int level, int which, const double *host);
+int examg_optflow3_download(examg_optflow3 *o, int level, int which, double *host);
+/* apply bc to the images; initGradients@all; rhs@finest (`InitFields` after the images are uploaded) */
+int examg_optflow3_init_fields(examg_optflow3 *o);
+int examg_optflow3_smooth_color(examg_optflow3 *o, int level, int color);
+int examg_optflow3_smooth(examg_optflow3 *o, int level, int nsweeps);    /* nsweeps x { colour 0, colour 1 } */
+/* residual = rhs - combinedOp * flow; apply bc; *norm_out (nullable) = resNorm: sqrt of the sum of dot ( residual, residual ) */
+int examg_optflow3_residual(examg_optflow3 *o, int level, double *norm_out);
+int examg_optflow3_restrict(examg_optflow3 *o, int level);   /* rhs@coarser = RestrictionCell * residual; flow@coarser = 0 */
+int examg_optflow3_correct(examg_optflow3 *o, int level);    /* flow += ProlongationCell@coarser * flow@coarser; apply bc */
+int examg_optflow3_cg(examg_optflow3 *o, int *iters_out);    /* mgCycle@coarsest: CG on the Vec3 unknown, one kernel */
+int examg_optflow3_last_cg_iters(examg_optflow3 *o, int *iters_out);
+int examg_optflow3_vcycle(examg_optflow3 *o, int level);     /* mgCycle@level (< 0: finest; the finest as one CUDA graph) */
+int examg_optflow3_cycles(examg_optflow3 *o, int n, double *norm_out);  /* n cycles, then the residual norm (nullable) */
+
 /* ---- multi-GPU plumbing (one process per GPU) ---------------------------------
  * Peers are wired by exchanging opaque blobs through the host's process group
  * (torch.distributed / MPI): every rank exports a blob, all blobs are gathered
