@@ -178,9 +178,9 @@ __global__ void __launch_bounds__(256) k3_restrict(const O3Pairs pr, int nxc, in
 // flow += ProlongationCell * flow@coarser (piecewise constant); apply bc
 __global__ void __launch_bounds__(256) k3_correct(const O3Args a, const double *__restrict__ c0, const double *__restrict__ c1,
                                                   const double *__restrict__ c2, long long syc, long long szc) {
-  const long long total = (long long)a.nx * a.ny * a.nz;
-  for (long long t = blockIdx.x * (long long)blockDim.x + threadIdx.x; t < total; t += (long long)gridDim.x * blockDim.x) {
-    const int i = (int)(t % a.nx), j = (int)((t / a.nx) % a.ny), k = (int)(t / ((long long)a.nx * a.ny));
+  const int i = blockIdx.x * blockDim.x + threadIdx.x, j = blockIdx.y * blockDim.y + threadIdx.y;
+  if (i >= a.nx || j >= a.ny) return;
+  for (int k = blockIdx.z; k < a.nz; k += gridDim.z) {
     const long long p = o3_idx(a, i, j, k), q = ((i >> 1) + 1) + syc * ((j >> 1) + 1) + szc * ((k >> 1) + 1);
     o3_store(a, a.f[0], i, j, k, a.f[0][p] + c0[q]);
     o3_store(a, a.f[1], i, j, k, a.f[1][p] + c1[q]);
@@ -189,23 +189,24 @@ __global__ void __launch_bounds__(256) k3_correct(const O3Args a, const double *
 }
 
 // residual = rhs - combinedOp * flow; apply bc; NORM: partial sums of dot ( residual, residual )
+// thread blocks of 64 x 4 cells in x, y; planes by grid stride (no integer division per cell)
 template <bool NORM>
 __global__ void __launch_bounds__(256) k3_residual(const O3Args a, dd *__restrict__ partials) {
-  const long long total = (long long)a.nx * a.ny * a.nz;
+  const int i = blockIdx.x * blockDim.x + threadIdx.x, j = blockIdx.y * blockDim.y + threadIdx.y;
   dd part = {0.0, 0.0};
-  for (long long t = blockIdx.x * (long long)blockDim.x + threadIdx.x; t < total; t += (long long)gridDim.x * blockDim.x) {
-    const int i = (int)(t % a.nx), j = (int)((t / a.nx) % a.ny), k = (int)(t / ((long long)a.nx * a.ny));
-    const long long p = o3_idx(a, i, j, k);
-    double r[3];
-    o3_residual_at(a, a.f[0], a.f[1], a.f[2], p, r);
-    o3_store(a, a.f[6], i, j, k, r[0]);
-    o3_store(a, a.f[7], i, j, k, r[1]);
-    o3_store(a, a.f[8], i, j, k, r[2]);
-    if (NORM) dd_add(part, r[0] * r[0] + r[1] * r[1] + r[2] * r[2]);
-  }
+  if (i < a.nx && j < a.ny)
+    for (int k = blockIdx.z; k < a.nz; k += gridDim.z) {
+      const long long p = o3_idx(a, i, j, k);
+      double r[3];
+      o3_residual_at(a, a.f[0], a.f[1], a.f[2], p, r);
+      o3_store(a, a.f[6], i, j, k, r[0]);
+      o3_store(a, a.f[7], i, j, k, r[1]);
+      o3_store(a, a.f[8], i, j, k, r[2]);
+      if (NORM) dd_add(part, r[0] * r[0] + r[1] * r[1] + r[2] * r[2]);
+    }
   if (NORM) {
     part = dd_block_reduce(part);
-    if (threadIdx.x == 0) partials[blockIdx.x] = part;
+    if (threadIdx.x == 0 && threadIdx.y == 0) partials[blockIdx.x + gridDim.x * (blockIdx.y + gridDim.y * blockIdx.z)] = part;
   }
 }
 
@@ -226,19 +227,21 @@ __device__ __forceinline__ void o3_block_solve(const O3Args &a, long long p, con
   const double D = -(b * i_ - c * h), E = a_ * i_ - c * g, F = -(a_ * h - b * g);
   const double G = b * f - c * e, H = -(a_ * f - c * d), I = a_ * e - b * d;
   const double det = a_ * A + b * B + c * C;
-  x[0] = (A / det) * r[0] + (D / det) * r[1] + (G / det) * r[2];
-  x[1] = (B / det) * r[0] + (E / det) * r[1] + (H / det) * r[2];
-  x[2] = (C / det) * r[0] + (F / det) * r[1] + (I / det) * r[2];
+  // d = b, g = c, h = f: D = B, G = C, H = F bit for bit (the products commute) -- six divisions
+  (void)D; (void)G; (void)H;
+  const double i00 = A / det, i01 = B / det, i02 = C / det, i11 = E / det, i12 = F / det, i22 = I / det;
+  x[0] = i00 * r[0] + i01 * r[1] + i02 * r[2];
+  x[1] = i01 * r[0] + i11 * r[1] + i12 * r[2];
+  x[2] = i02 * r[0] + i12 * r[1] + i22 * r[2];
 }
 
 // one colour: flow += inverse ( diag ( combinedOp ) ) * ( rhs - combinedOp * flow ) on the cells with
 // (i + j + k) % 2 == color; apply bc
 __global__ void __launch_bounds__(256) k3_smooth_color(const O3Args a, int color) {
-  const int hx = (a.nx + 1) >> 1;
-  const long long total = (long long)hx * a.ny * a.nz;
-  for (long long t = blockIdx.x * (long long)blockDim.x + threadIdx.x; t < total; t += (long long)gridDim.x * blockDim.x) {
-    const int j = (int)((t / hx) % a.ny), k = (int)(t / ((long long)hx * a.ny));
-    const int i = 2 * (int)(t % hx) + ((j + k + color) & 1);
+  const int tx = blockIdx.x * blockDim.x + threadIdx.x, j = blockIdx.y * blockDim.y + threadIdx.y;
+  if (j >= a.ny) return;
+  for (int k = blockIdx.z; k < a.nz; k += gridDim.z) {
+    const int i = 2 * tx + ((j + k + color) & 1);
     if (i >= a.nx) continue;
     const long long p = o3_idx(a, i, j, k);
     double r[3], d[3];
@@ -361,6 +364,14 @@ O3Args o3_args(const examg_optflow3 *o, const O3Level &L) {
   return a;
 }
 
+// 64 x 4 cells (x, y) per thread block, planes by grid stride: about 2048 blocks
+dim3 o3_shape(int ex, int ny, int nz) {
+  const int gx = (ex + 63) / 64, gy = (ny + 3) / 4;
+  int gz = 2048 / (gx * gy);
+  gz = gz < 1 ? 1 : (gz > nz ? nz : gz);
+  return dim3(gx, gy, gz);
+}
+
 int o3_grid(long long total) {
   long long g = (total + 255) / 256;
   return (int)(g < 1 ? 1 : (g > O3_RED_BLOCKS ? O3_RED_BLOCKS : g));
@@ -380,22 +391,21 @@ double *o3_array(examg_optflow3 *o, int level, int which, size_t *count) {
 
 int o3_smooth_color(examg_optflow3 *o, O3Level &L, int color) {
   examg_ctx *c = o->c;
-  const long long total = (long long)((L.n[0] + 1) / 2) * L.n[1] * L.n[2];
-  k3_smooth_color<<<o3_grid(total), 256, 0, c->stream>>>(o3_args(o, L), color);
+  k3_smooth_color<<<o3_shape((L.n[0] + 1) / 2, L.n[1], L.n[2]), dim3(64, 4), 0, c->stream>>>(o3_args(o, L), color);
   EXAMG_LAUNCH_CHECK(c);
   return EXAMG_OK;
 }
 
 int o3_residual(examg_optflow3 *o, O3Level &L, bool norm) {
   examg_ctx *c = o->c;
-  const int grid = o3_grid((long long)L.n[0] * L.n[1] * L.n[2]);
+  const dim3 grid = o3_shape(L.n[0], L.n[1], L.n[2]);
   if (norm) {
-    k3_residual<true><<<grid, 256, 0, c->stream>>>(o3_args(o, L), o->partials);
+    k3_residual<true><<<grid, dim3(64, 4), 0, c->stream>>>(o3_args(o, L), o->partials);
     EXAMG_LAUNCH_CHECK(c);
-    k3_final_sum<<<1, 1024, 0, c->stream>>>(o->partials, grid, o->sum);
+    k3_final_sum<<<1, 1024, 0, c->stream>>>(o->partials, (int)(grid.x * grid.y * grid.z), o->sum);
     EXAMG_LAUNCH_CHECK(c);
   } else {
-    k3_residual<false><<<grid, 256, 0, c->stream>>>(o3_args(o, L), nullptr);
+    k3_residual<false><<<grid, dim3(64, 4), 0, c->stream>>>(o3_args(o, L), nullptr);
     EXAMG_LAUNCH_CHECK(c);
   }
   return EXAMG_OK;
@@ -446,7 +456,7 @@ int o3_restrict_residual(examg_optflow3 *o, int level) {
 int o3_correct(examg_optflow3 *o, int level) {
   examg_ctx *c = o->c;
   O3Level &L = o->lev[level - c->cfg.min_level], &C = o->lev[level - 1 - c->cfg.min_level];
-  k3_correct<<<o3_grid((long long)L.n[0] * L.n[1] * L.n[2]), 256, 0, c->stream>>>(o3_args(o, L), C.f[0], C.f[1], C.f[2], C.sy, C.sz);
+  k3_correct<<<o3_shape(L.n[0], L.n[1], L.n[2]), dim3(64, 4), 0, c->stream>>>(o3_args(o, L), C.f[0], C.f[1], C.f[2], C.sy, C.sz);
   EXAMG_LAUNCH_CHECK(c);
   return EXAMG_OK;
 }
@@ -514,7 +524,10 @@ examg_optflow3 *examg_optflow3_create(examg_ctx *c, const examg_optflow3_desc *d
       ok = cudaMalloc(&o->img[k], sizeof(double) * vf) == cudaSuccess && cudaMemsetAsync(o->img[k], 0, sizeof(double) * vf, c->stream) == cudaSuccess;
     for (int k = 0; k < 6 && ok; ++k)
       ok = cudaMalloc(&o->cg[k], sizeof(double) * vc) == cudaSuccess && cudaMemsetAsync(o->cg[k], 0, sizeof(double) * vc, c->stream) == cudaSuccess;
-    ok = ok && cudaMalloc(&o->partials, sizeof(dd) * O3_RED_BLOCKS) == cudaSuccess && cudaMalloc(&o->sum, sizeof(dd)) == cudaSuccess &&
+    const dim3 gs = o3_shape(o->lev.back().n[0], o->lev.back().n[1], o->lev.back().n[2]);
+    size_t nblocks = (size_t)gs.x * gs.y * gs.z;
+    if (nblocks < O3_RED_BLOCKS) nblocks = O3_RED_BLOCKS;
+    ok = ok && cudaMalloc(&o->partials, sizeof(dd) * nblocks) == cudaSuccess && cudaMalloc(&o->sum, sizeof(dd)) == cudaSuccess &&
          cudaMalloc(&o->iters, sizeof(int)) == cudaSuccess && cudaMallocHost(&o->sum_host, sizeof(dd)) == cudaSuccess &&
          cudaMallocHost(&o->iters_host, sizeof(int)) == cudaSuccess;
     if (ok) ok = cudaMemsetAsync(o->iters, 0, sizeof(int), c->stream) == cudaSuccess;
