@@ -18,6 +18,7 @@
 // sums in double-double.  One block (one GPU).
 #include <cmath>
 #include <cstdlib>
+#include <map>
 #include <vector>
 
 #include "examg_cg.cuh"
@@ -36,6 +37,8 @@ struct O3Level {
   size_t vol;
   double h[3], L[7];
   double *f[O3_NF];
+  double *alt[3];  // second buffers of flow for the one-pass sweeps (levels of >= 32 cells in x; else nullptr)
+  bool flipped;    // f[0..2] and alt[] have been exchanged an odd number of times
 };
 
 // by value to the kernels
@@ -218,11 +221,12 @@ __global__ void __launch_bounds__(1024) k3_final_sum(const dd *__restrict__ part
 }
 
 // the inverse of the 3 x 3 centre block by cofactors, applied to r
-__device__ __forceinline__ void o3_block_solve(const O3Args &a, long long p, const double (&r)[3], double (&x)[3]) {
+// G = xx, xy, xz, yy, yz, zz at the cell
+__device__ __forceinline__ void o3_block_solve(const O3Args &a, const double (&G6)[6], const double (&r)[3], double (&x)[3]) {
   // rows (a b c), (d e f), (g h i) with d = b, g = c, h = f
-  const double a_ = fma(a.a2, a.L[0], a.f[9][p]), b = a.f[10][p], c = a.f[11][p];
-  const double d = b, e = fma(a.a2, a.L[0], a.f[12][p]), f = a.f[13][p];
-  const double g = c, h = f, i_ = fma(a.a2, a.L[0], a.f[14][p]);
+  const double a_ = fma(a.a2, a.L[0], G6[0]), b = G6[1], c = G6[2];
+  const double d = b, e = fma(a.a2, a.L[0], G6[3]), f = G6[4];
+  const double g = c, h = f, i_ = fma(a.a2, a.L[0], G6[5]);
   const double A = e * i_ - f * h, B = -(d * i_ - f * g), C = d * h - e * g;
   const double D = -(b * i_ - c * h), E = a_ * i_ - c * g, F = -(a_ * h - b * g);
   const double G = b * f - c * e, H = -(a_ * f - c * d), I = a_ * e - b * d;
@@ -246,10 +250,169 @@ __global__ void __launch_bounds__(256) k3_smooth_color(const O3Args a, int color
     const long long p = o3_idx(a, i, j, k);
     double r[3], d[3];
     o3_residual_at(a, a.f[0], a.f[1], a.f[2], p, r);
-    o3_block_solve(a, p, r, d);
+    const double g6[6] = {a.f[9][p], a.f[10][p], a.f[11][p], a.f[12][p], a.f[13][p], a.f[14][p]};
+    o3_block_solve(a, g6, r, d);
     o3_store(a, a.f[0], i, j, k, a.f[0][p] + d[0]);
     o3_store(a, a.f[1], i, j, k, a.f[1][p] + d[1]);
     o3_store(a, a.f[2], i, j, k, a.f[2][p] + d[2]);
+  }
+}
+
+// ---- one whole sweep (colour 0, then colour 1) in one pass over HBM ---------------------------------------------------
+// The per-colour kernel fetches every sector of the 15 arrays twice per sweep and uses half of it each time.  Here a CTA of
+// 32 x 16 threads owns a tile (thread = cell column) and marches in z with a ring of five planes of the three flow
+// components in shared memory (34 x 18 with the halo).  Colour 0 ("red") of plane t is updated at step t from the old
+// values of planes t-1, t, t+1 -- in the ring, in place; colour 1 ("black") of plane t-2 at the same step from the
+// updated red cells of planes t-3, t-2, t-1 (see the schedule below); plane t-2 is final then and goes to the second
+// buffers of flow (out of place: neighbouring tiles recompute the red cells of their one-cell ring from old values).
+// A cell's coefficients and right-hand side are read once, one plane ahead, into registers.  Neumann ghost cells in the
+// ring never need a refresh: a ghost cell mirrors the very cell that reads it.  Same per-cell arithmetic as
+// k3_smooth_color => bit-identical.
+constexpr int F3W = 32, F3H = 16, F3NT = F3W * F3H;  // threads = red region of a tile
+constexpr int F3IW = F3W - 2, F3IH = F3H - 2;        // output region
+constexpr int F3SW = F3W + 2, F3SH = F3H + 2, F3PL = F3SW * F3SH;  // staged plane with halo
+constexpr int F3SL = 5;  // ring slots: planes t-3 .. t+1
+constexpr size_t F3_SMEM = sizeof(double) * 3 * F3SL * F3PL;
+
+struct O3Fused {
+  double *dst[3];
+  int tiles_x, tiles_y, nseg, seg_planes;
+};
+
+__global__ void __launch_bounds__(F3NT, F3NT <= 256 ? 2 : 1) k3_sweep(const O3Args a, const O3Fused fz) {
+  extern __shared__ double ring[];  // [comp][slot][F3PL]
+  const int tid = threadIdx.x, tx = tid % F3W, ty = tid / F3W;
+  const int tile = blockIdx.x % (fz.tiles_x * fz.tiles_y), seg = blockIdx.x / (fz.tiles_x * fz.tiles_y);
+  const int ox = F3IW * (tile % fz.tiles_x), oy = F3IH * (tile / fz.tiles_x);
+  const int za = seg * fz.seg_planes, zb = min(za + fz.seg_planes, a.nz);
+  const int i = ox - 1 + tx, j = oy - 1 + ty;
+  const bool indom = i >= 0 && i < a.nx && j >= 0 && j < a.ny;
+  const bool interior = indom && tx >= 1 && tx <= F3IW && ty >= 1 && ty <= F3IH;
+  const int lo = (ty + 1) * F3SW + tx + 1;  // own cell inside a staged plane
+  const long long col = (i + 1) + a.sy * (j + 1);  // own column, plane k at col + sz (k + 1)
+  // halo elements staged by this thread: e = tid and tid + F3NT
+  const int e0 = tid, e1 = tid + F3NT;
+  const int gx0 = ox - 2 + e0 % F3SW, gy0 = oy - 2 + e0 / F3SW, gx1 = ox - 2 + e1 % F3SW, gy1 = oy - 2 + e1 / F3SW;
+  const bool v0 = gx0 >= -1 && gx0 <= a.nx && gy0 >= -1 && gy0 <= a.ny;
+  const bool v1 = e1 < F3PL && gx1 >= -1 && gx1 <= a.nx && gy1 >= -1 && gy1 <= a.ny;
+  const long long c0 = (gx0 + 1) + a.sy * (gy0 + 1), c1 = (gx1 + 1) + a.sy * (gy1 + 1);
+
+  auto slot = [](int plane) { return (plane + 2 * F3SL) % F3SL; };
+  auto stage = [&](int plane) {  // flow planes -> ring
+    const bool pv = plane >= -1 && plane <= a.nz;
+    const long long zo = a.sz * (plane + 1);
+#pragma unroll
+    for (int c = 0; c < 3; ++c) {
+      double *dstp = ring + (c * F3SL + slot(plane)) * F3PL;
+      dstp[e0] = (pv && v0) ? a.f[c][c0 + zo] : 0.0;
+      if (e1 < F3PL) dstp[e1] = (pv && v1) ? a.f[c][c1 + zo] : 0.0;
+    }
+  };
+  // coefficients and right-hand side of the own cell: G xx,xy,xz,yy,yz,zz, rhs 0..2
+  auto fetch = [&](int plane, double (&cf)[9]) {
+    if (indom && plane >= 0 && plane < a.nz) {
+      const long long p = col + a.sz * (plane + 1);
+#pragma unroll
+      for (int q = 0; q < 6; ++q) cf[q] = a.f[9 + q][p];
+#pragma unroll
+      for (int q = 0; q < 3; ++q) cf[6 + q] = a.f[3 + q][p];
+    }
+  };
+  // the update of the own cell on `plane`, in the ring
+  auto update = [&](int plane, const double (&cf)[9]) {
+    const double *m[3], *c[3], *pp[3];
+#pragma unroll
+    for (int q = 0; q < 3; ++q) {
+      m[q] = ring + (q * F3SL + slot(plane - 1)) * F3PL + lo;
+      c[q] = ring + (q * F3SL + slot(plane)) * F3PL + lo;
+      pp[q] = ring + (q * F3SL + slot(plane + 1)) * F3PL + lo;
+    }
+    auto lap = [&](int q) {
+      double acc = a.L[0] * c[q][0];
+      acc = fma(a.L[1], c[q][-1], acc);
+      acc = fma(a.L[2], c[q][1], acc);
+      acc = fma(a.L[3], c[q][-F3SW], acc);
+      acc = fma(a.L[4], c[q][F3SW], acc);
+      acc = fma(a.L[5], m[q][0], acc);
+      acc = fma(a.L[6], pp[q][0], acc);
+      return acc;
+    };
+    const double u = c[0][0], v = c[1][0], w = c[2][0];
+    double r[3], x[3];
+    double t = cf[0] * u;
+    t = fma(cf[1], v, t);
+    t = fma(cf[2], w, t);
+    r[0] = cf[6] - fma(a.a2, lap(0), t);
+    t = cf[1] * u;
+    t = fma(cf[3], v, t);
+    t = fma(cf[4], w, t);
+    r[1] = cf[7] - fma(a.a2, lap(1), t);
+    t = cf[2] * u;
+    t = fma(cf[4], v, t);
+    t = fma(cf[5], w, t);
+    r[2] = cf[8] - fma(a.a2, lap(2), t);
+    const double g6[6] = {cf[0], cf[1], cf[2], cf[3], cf[4], cf[5]};
+    o3_block_solve(a, g6, r, x);
+    const_cast<double *>(c[0])[0] = u + x[0];
+    const_cast<double *>(c[1])[0] = v + x[1];
+    const_cast<double *>(c[2])[0] = w + x[2];
+  };
+
+  // Schedule without divergence: at step t the lanes with (i + j + t) even update colour 0 on plane t, the others colour 1
+  // on plane t - 2 (whose red neighbours on planes t-3, t-2, t-1 are done) -- every lane runs the same update on its own
+  // (plane, coefficients).  A lane holds the coefficients it uses now, the set it uses next and the set in flight:
+  //   even at t: now = plane t,   next = plane t-1 (it is odd at t+1: colour 1 on plane t-1)
+  //   odd  at t: now = plane t-2, next = plane t+1 (in flight; it is even at t+1)
+  const int t0 = max(za - 1, 0), t1 = zb + 1;  // colour 0 on planes t0 .. min(zb, nz - 1), colour 1 on za .. zb - 1
+  double use[9], saved[9], nxt[9];
+#pragma unroll
+  for (int q = 0; q < 9; ++q) use[q] = saved[q] = nxt[q] = 0.0;
+  for (int pl = t0 - 3; pl <= t0 + 1; ++pl) stage(pl);
+  const bool even0 = ((i + j + t0) & 1) == 0;
+  // even at t0: now = plane t0, saved = plane t0 - 1; odd at t0: now = plane t0 - 2, saved = plane t0
+  fetch(even0 ? t0 : t0 - 2, use);
+  fetch(even0 ? t0 - 1 : t0, saved);
+  __syncthreads();
+  for (int t = t0; t <= t1; ++t) {
+    const bool even = ((i + j + t) & 1) == 0;
+    // requests of the next step first: plane t+2 of flow, plane t+1 of the coefficients
+    double h0[3], h1[3];
+    {
+      const int plane = t + 2;
+      const bool pv = plane <= a.nz && t < t1;
+      const long long zo = a.sz * (plane + 1);
+#pragma unroll
+      for (int c = 0; c < 3; ++c) {
+        h0[c] = (pv && v0) ? a.f[c][c0 + zo] : 0.0;
+        h1[c] = (pv && v1) ? a.f[c][c1 + zo] : 0.0;
+      }
+    }
+    if (t < t1) fetch(t + 1, nxt);
+    const int plane = even ? t : t - 2;
+    const bool act = even ? (indom && t < a.nz && t <= zb) : (interior && plane >= za && plane < zb);
+    if (act) update(plane, use);
+    // plane t - 2 is final
+    const int pz = t - 2;
+    if (interior && pz >= za && pz < zb) {
+#pragma unroll
+      for (int c = 0; c < 3; ++c) o3_store(a, fz.dst[c], i, j, pz, ring[(c * F3SL + slot(pz)) * F3PL + lo]);
+    }
+    __syncthreads();
+    if (t < t1) {
+#pragma unroll
+      for (int c = 0; c < 3; ++c) {
+        double *dstp = ring + (c * F3SL + slot(t + 2)) * F3PL;
+        dstp[e0] = h0[c];
+        if (e1 < F3PL) dstp[e1] = h1[c];
+      }
+#pragma unroll
+      for (int q = 0; q < 9; ++q) {
+        const double sv = saved[q], nx = nxt[q];
+        use[q] = even ? sv : nx;
+        saved[q] = even ? nx : sv;
+      }
+    }
+    __syncthreads();
   }
 }
 
@@ -335,8 +498,9 @@ struct examg_optflow3 {
   dd *partials = nullptr, *sum = nullptr;
   dd *sum_host = nullptr;
   int *iters = nullptr, *iters_host = nullptr;
-  cudaGraphExec_t graph = nullptr;  // mgCycle@finest (the buffers never move: one capture serves every later cycle)
-  long long graph_launches = 0;
+  // mgCycle@finest as a CUDA graph per buffer state (the one-pass sweeps exchange flow with its second buffers)
+  struct Graph { cudaGraphExec_t exec = nullptr; long long launches = 0; std::vector<char> exit_state; };
+  std::map<std::vector<char>, Graph> graphs;
 };
 
 namespace {
@@ -394,6 +558,67 @@ int o3_smooth_color(examg_optflow3 *o, O3Level &L, int color) {
   k3_smooth_color<<<o3_shape((L.n[0] + 1) / 2, L.n[1], L.n[2]), dim3(64, 4), 0, c->stream>>>(o3_args(o, L), color);
   EXAMG_LAUNCH_CHECK(c);
   return EXAMG_OK;
+}
+
+// Opt-in (EXAMG_OF3_FUSED=1): measured on B200 at 256^3 the one-pass sweep takes 0.98 ms against 0.84 ms for the two
+// colour launches -- 27 doubles of per-thread state force one 512-thread CTA per SM (128 registers), and with 25 % of
+// the warp slots the dependent FP64 chains of the block inverse, the two barriers per plane and the global loads are
+// not hidden (ncu: stalls barrier 2.3, wait 2.3, long scoreboard 2.0 warps per issue, FP64 pipe 16 %, DRAM 5 % on a
+// 128^3 level); profiles/r02_notes.md.
+bool o3_fused_on() {
+  static const bool on = getenv("EXAMG_OF3_FUSED") && getenv("EXAMG_OF3_FUSED")[0] == '1';
+  return on;
+}
+
+// one sweep: colour 0, colour 1 -- in one pass where the level has second buffers
+int o3_sweep(examg_optflow3 *o, O3Level &L) {
+  examg_ctx *c = o->c;
+  if (!L.alt[0] || !o3_fused_on()) {
+    int rc;
+    if ((rc = o3_smooth_color(o, L, 0)) || (rc = o3_smooth_color(o, L, 1))) return rc;
+    return EXAMG_OK;
+  }
+  EXAMG_ONCE_PER_DEVICE(c, {
+    EXAMG_CUDA(cudaFuncSetAttribute(k3_sweep, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)F3_SMEM));
+  });
+  O3Fused fz;
+  for (int k = 0; k < 3; ++k) fz.dst[k] = L.alt[k];
+  fz.tiles_x = (L.n[0] + F3IW - 1) / F3IW;
+  fz.tiles_y = (L.n[1] + F3IH - 1) / F3IH;
+  const int tiles = fz.tiles_x * fz.tiles_y;
+  int nseg = (4 * 148 + tiles - 1) / tiles;  // about four CTAs per SM over the launch, segments of >= 16 planes
+  if (nseg > L.n[2] / 16) nseg = L.n[2] / 16;
+  if (nseg < 1) nseg = 1;
+  fz.seg_planes = (L.n[2] + nseg - 1) / nseg;
+  fz.nseg = (L.n[2] + fz.seg_planes - 1) / fz.seg_planes;
+  k3_sweep<<<tiles * fz.nseg, F3NT, F3_SMEM, c->stream>>>(o3_args(o, L), fz);
+  EXAMG_LAUNCH_CHECK(c);
+  for (int k = 0; k < 3; ++k) {
+    double *t = L.f[k];
+    L.f[k] = L.alt[k];
+    L.alt[k] = t;
+  }
+  L.flipped = !L.flipped;
+  return EXAMG_OK;
+}
+
+std::vector<char> o3_state(const examg_optflow3 *o) {
+  std::vector<char> key;
+  for (const O3Level &L : o->lev) key.push_back(L.flipped ? 1 : 0);
+  return key;
+}
+
+void o3_restore(examg_optflow3 *o, const std::vector<char> &key) {
+  for (size_t l = 0; l < o->lev.size(); ++l) {
+    O3Level &L = o->lev[l];
+    if ((L.flipped ? 1 : 0) == key[l]) continue;
+    for (int k = 0; k < 3; ++k) {
+      double *t = L.f[k];
+      L.f[k] = L.alt[k];
+      L.alt[k] = t;
+    }
+    L.flipped = !L.flipped;
+  }
 }
 
 int o3_residual(examg_optflow3 *o, O3Level &L, bool norm) {
@@ -467,13 +692,11 @@ int o3_vcycle_rec(examg_optflow3 *o, int level) {
   O3Level &L = o->lev[level - c->cfg.min_level];
   int rc;
   for (int it = 0; it < o->desc.nu_pre; ++it)
-    for (int color = 0; color < 2; ++color)
-      if ((rc = o3_smooth_color(o, L, color))) return rc;
+    if ((rc = o3_sweep(o, L))) return rc;
   if ((rc = o3_residual(o, L, false)) || (rc = o3_restrict_residual(o, level))) return rc;
   if ((rc = o3_vcycle_rec(o, level - 1)) || (rc = o3_correct(o, level))) return rc;
   for (int it = 0; it < o->desc.nu_post; ++it)
-    for (int color = 0; color < 2; ++color)
-      if ((rc = o3_smooth_color(o, L, color))) return rc;
+    if ((rc = o3_sweep(o, L))) return rc;
   return EXAMG_OK;
 }
 
@@ -516,6 +739,13 @@ examg_optflow3 *examg_optflow3_create(examg_ctx *c, const examg_optflow3_desc *d
       ok = ok && cudaMalloc(&L.f[k], sizeof(double) * L.vol) == cudaSuccess &&
            cudaMemsetAsync(L.f[k], 0, sizeof(double) * L.vol, c->stream) == cudaSuccess;
     }
+    L.flipped = false;
+    for (int k = 0; k < 3; ++k) {
+      L.alt[k] = nullptr;
+      if (L.n[0] >= F3W && L.n[1] >= F3H && L.n[2] >= 4 && o3_fused_on())
+        ok = ok && cudaMalloc(&L.alt[k], sizeof(double) * L.vol) == cudaSuccess &&
+             cudaMemsetAsync(L.alt[k], 0, sizeof(double) * L.vol, c->stream) == cudaSuccess;
+    }
     o->lev.push_back(L);
   }
   if (ok) {
@@ -544,9 +774,12 @@ examg_optflow3 *examg_optflow3_create(examg_ctx *c, const examg_optflow3_desc *d
 int examg_optflow3_destroy(examg_optflow3 *o) {
   if (!o) return EXAMG_OK;
   if (o->c) cudaStreamSynchronize(o->c->stream);
-  for (O3Level &L : o->lev)
+  for (O3Level &L : o->lev) {
     for (int k = 0; k < O3_NF; ++k)
       if (L.f[k]) cudaFree(L.f[k]);
+    for (int k = 0; k < 3; ++k)
+      if (L.alt[k]) cudaFree(L.alt[k]);
+  }
   for (double *p : o->img)
     if (p) cudaFree(p);
   for (double *p : o->cg)
@@ -556,7 +789,8 @@ int examg_optflow3_destroy(examg_optflow3 *o) {
   if (o->iters) cudaFree(o->iters);
   if (o->sum_host) cudaFreeHost(o->sum_host);
   if (o->iters_host) cudaFreeHost(o->iters_host);
-  if (o->graph) cudaGraphExecDestroy(o->graph);
+  for (auto &kv : o->graphs)
+    if (kv.second.exec) cudaGraphExecDestroy(kv.second.exec);
   delete o;
   return EXAMG_OK;
 }
@@ -620,11 +854,10 @@ int examg_optflow3_smooth(examg_optflow3 *o, int level, int nsweeps) {
   O3Level *L = o3_level(o, level);
   if (!L) return EXAMG_EINVAL;
   if (nsweeps < 0) return set_error(EXAMG_EINVAL, "examg_optflow3_smooth: %d sweeps", nsweeps);
-  for (int it = 0; it < nsweeps; ++it)
-    for (int color = 0; color < 2; ++color) {
-      const int rc = o3_smooth_color(o, *L, color);
-      if (rc) return rc;
-    }
+  for (int it = 0; it < nsweeps; ++it) {
+    const int rc = o3_sweep(o, *L);
+    if (rc) return rc;
+  }
   return EXAMG_OK;
 }
 
@@ -679,22 +912,29 @@ int examg_optflow3_vcycle(examg_optflow3 *o, int level) {
   if (level < 0) level = c->cfg.max_level;
   static const bool use_graph = !(getenv("EXAMG_NO_GRAPH") && getenv("EXAMG_NO_GRAPH")[0] == '1');
   if (!use_graph || level != c->cfg.max_level || level == c->cfg.min_level) return o3_vcycle_rec(o, level);
-  if (!o->graph) {
+  const std::vector<char> key = o3_state(o);
+  auto it = o->graphs.find(key);
+  if (it == o->graphs.end()) {
     const long long l0 = c->launches;
     cudaGraph_t graph = nullptr;
     EXAMG_CUDA(cudaStreamBeginCapture(c->stream, cudaStreamCaptureModeThreadLocal));
     const int rc = o3_vcycle_rec(o, level);
     const cudaError_t e = cudaStreamEndCapture(c->stream, &graph);
-    o->graph_launches = c->launches - l0;
+    examg_optflow3::Graph g;
+    g.launches = c->launches - l0;
     c->launches = l0;  // nothing ran yet
+    g.exit_state = o3_state(o);
+    o3_restore(o, key);
     if (rc) { if (graph) cudaGraphDestroy(graph); return rc; }
     if (e != cudaSuccess) return set_error(EXAMG_ECUDA, "graph capture of mgCycle failed: %s", cudaGetErrorString(e));
-    const cudaError_t e2 = cudaGraphInstantiate(&o->graph, graph, 0);
+    const cudaError_t e2 = cudaGraphInstantiate(&g.exec, graph, 0);
     cudaGraphDestroy(graph);
-    if (e2 != cudaSuccess) { o->graph = nullptr; return set_error(EXAMG_ECUDA, "cudaGraphInstantiate: %s", cudaGetErrorString(e2)); }
+    if (e2 != cudaSuccess) return set_error(EXAMG_ECUDA, "cudaGraphInstantiate: %s", cudaGetErrorString(e2));
+    it = o->graphs.emplace(key, g).first;
   }
-  EXAMG_CUDA(cudaGraphLaunch(o->graph, c->stream));
-  c->launches += o->graph_launches;
+  EXAMG_CUDA(cudaGraphLaunch(it->second.exec, c->stream));
+  c->launches += it->second.launches;
+  o3_restore(o, it->second.exit_state);
   return EXAMG_OK;
 }
 

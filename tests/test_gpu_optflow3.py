@@ -42,9 +42,21 @@ def test_golden_stdout(oracle):
     assert its == 4 and out == open(GOLDEN).read().split()
 
 
-@pytest.mark.parametrize("F,lo,hi", [((1, 1, 1), 2, 5), ((3, 2, 1), 1, 3)])
-def test_loops_against_the_oracle(F, lo, hi, oracle):
-    """InitFields, each colour, residual + norm, restriction, correction: bit-identical arrays (ghost cells included)"""
+@pytest.mark.parametrize("fused", [0, 1])
+@pytest.mark.parametrize("F,lo,hi", [((1, 1, 1), 2, 5), ((3, 2, 1), 1, 3), ((5, 3, 2), 1, 4), ((1, 1, 1), 2, 6)])
+def test_loops_against_the_oracle(F, lo, hi, fused, oracle, request):
+    """InitFields, each colour, whole sweeps, residual + norm, restriction, correction: bit-identical arrays (ghost cells
+    included).  fused = 1: the opt-in one-pass sweep k3_sweep (EXAMG_OF3_FUSED is read once per process: it runs in a
+    process of its own; ragged tiles and several z segments at 80 x 48 x 32)."""
+    import subprocess
+    import sys
+    if fused and os.environ.get("EXAMG_OF3_FUSED") != "1":
+        env = dict(os.environ, EXAMG_OF3_FUSED="1")
+        node = "%s::%s" % (__file__, request.node.name)
+        out = subprocess.run([sys.executable, "-m", "pytest", "-x", "-q", "-m", "gpu", node], env=env, capture_output=True,
+                             text=True, timeout=600)
+        assert out.returncode == 0, out.stdout[-3000:] + out.stderr[-2000:]
+        return
     from oracle import optflow3 as o3
     g, r = _pair(lo, hi, F)
     _same_images(g, r)
@@ -70,6 +82,12 @@ def test_loops_against_the_oracle(F, lo, hi, oracle):
     g.smooth(hi, 2)
     r.smooth(hi, 2)
     _equal(g, r, hi, range(o3.FLOW, o3.FLOW + 3), "two sweeps")
+    g.smooth(hi, 1)  # an odd number: flow now lives in its second buffers
+    r.smooth(hi, 1)
+    _equal(g, r, hi, range(o3.FLOW, o3.FLOW + 3), "third sweep")
+    g.smooth_color(hi, 1)
+    r.smooth_color(hi, 1)
+    _equal(g, r, hi, range(o3.FLOW, o3.FLOW + 3), "a colour after the one-pass sweeps")
     ng, nr = g.update_residual_norm(hi), r.update_residual_norm(hi)
     _equal(g, r, hi, range(o3.RES, o3.RES + 3), "residual")
     assert abs(ng - nr) <= 1e-14 * nr
