@@ -1,7 +1,8 @@
 """The C++ host programs under host/ -- the code the generator back-end prints, calling the C ABI directly.
 
 CPU: they compile and link against libexamg.so.  GPU: their stdout equals the reference's golden .results files
-(Testing/Smoothers/RBGS.results, Testing/Application/OpticalFlow2D.results, Testing/BC/3D_Periodic.results)."""
+(Testing/Smoothers/RBGS.results, Testing/Application/OpticalFlow2D.results and OpticalFlow3D.results,
+Testing/BC/3D_Periodic.results)."""
 import os
 import subprocess
 
@@ -19,8 +20,8 @@ def _build():
 
 def test_host_programs_link():
     _build()
-    for name in ("Testing_Smoothers_RBGS", "Testing_Application_OpticalFlow2D", "Testing_BC_3D_Periodic",
-                 "Benchmark_Poisson3D"):
+    for name in ("Testing_Smoothers_RBGS", "Testing_Application_OpticalFlow2D", "Testing_Application_OpticalFlow3D",
+                 "Testing_BC_3D_Periodic", "Benchmark_Poisson3D"):
         exe = os.path.join(HOST, "_build", name)
         assert os.access(exe, os.X_OK)
         out = subprocess.run(["ldd", exe], capture_output=True, text=True).stdout
@@ -30,6 +31,7 @@ def test_host_programs_link():
 @pytest.mark.gpu
 @pytest.mark.parametrize("name,golden", [("Testing_Smoothers_RBGS", "Smoothers_RBGS"),
                                          ("Testing_Application_OpticalFlow2D", "Application_OpticalFlow2D"),
+                                         ("Testing_Application_OpticalFlow3D", "Application_OpticalFlow3D"),
                                          ("Testing_BC_3D_Periodic", "BC_3D_Periodic")])
 def test_host_program_golden_stdout(name, golden):
     _build()
