@@ -380,8 +380,8 @@ int examg_prolong_add_cell(examg_ctx *ctx, const int *coarse, const int *fine, i
 int examg_system2_cg_coarse(examg_ctx *ctx, int sys, const int *fields, int max_it, double rel_tol, int *iters_out);
 
 /* whole program: InitFields / mgCycle@all / doSolve@finest as one library object.  Several blocks: create it on
- * every rank BEFORE examg_comm_export (it allocates the staging of the coarsest level on rank 0); blocks must
- * start on even cells for the fused sweeps (otherwise the per-colour kernels run).                 */
+ * every rank BEFORE examg_comm_export (it allocates the staging of the coarsest level on rank 0; one such object per
+ * context); blocks must start on even cells for the fused sweeps (otherwise the per-colour kernels run). */
 typedef struct {
   double alpha;          /* Globals { Val alpha }              */
   double relax;          /* solve locally relax ...            */
