@@ -39,6 +39,10 @@ struct O3Level {
   double *f[O3_NF];
   double *alt[3];  // second buffers of flow for the one-pass sweeps (levels of >= 32 cells in x; else nullptr)
   bool flipped;    // f[0..2] and alt[] have been exchanged an odd number of times
+  // copies of the six gradContribution arrays with every row split into its even and its odd elements: a colour pass
+  // reads consecutive doubles (levels of >= 2^15 cells with an even row length; else nullptr).  Valid after InitFields.
+  double *gs[6];
+  bool gs_valid;
 };
 
 // by value to the kernels
@@ -48,6 +52,7 @@ struct O3Args {
   double L[7];
   double a2;
   double *f[O3_NF];
+  const double *gs[6];  // split-row copies of f[9..14] (nullptr: none)
 };
 
 __device__ __forceinline__ long long o3_idx(const O3Args &a, int i, int j, int k) {
@@ -80,10 +85,10 @@ __device__ __forceinline__ double o3_lap(const O3Args &a, const double *w, long 
   return acc;
 }
 
-// rhs - combinedOp * w at p, all three components
-__device__ __forceinline__ void o3_residual_at(const O3Args &a, const double *w0, const double *w1, const double *w2,
-                                               long long p, double (&r)[3]) {
-  const double gxx = a.f[9][p], gxy = a.f[10][p], gxz = a.f[11][p], gyy = a.f[12][p], gyz = a.f[13][p], gzz = a.f[14][p];
+// rhs - combinedOp * w at p, all three components; g6 = gradContribution xx, xy, xz, yy, yz, zz at the cell
+__device__ __forceinline__ void o3_residual_g(const O3Args &a, const double (&g6)[6], const double *w0, const double *w1,
+                                              const double *w2, long long p, double (&r)[3]) {
+  const double gxx = g6[0], gxy = g6[1], gxz = g6[2], gyy = g6[3], gyz = g6[4], gzz = g6[5];
   const double u = w0[p], v = w1[p], w = w2[p];
   double t = gxx * u;
   t = fma(gxy, v, t);
@@ -97,6 +102,21 @@ __device__ __forceinline__ void o3_residual_at(const O3Args &a, const double *w0
   t = fma(gyz, v, t);
   t = fma(gzz, w, t);
   r[2] = a.f[5][p] - fma(a.a2, o3_lap(a, w2, p), t);
+}
+
+__device__ __forceinline__ void o3_residual_at(const O3Args &a, const double *w0, const double *w1, const double *w2,
+                                               long long p, double (&r)[3]) {
+  const double g6[6] = {a.f[9][p], a.f[10][p], a.f[11][p], a.f[12][p], a.f[13][p], a.f[14][p]};
+  o3_residual_g(a, g6, w0, w1, w2, p, r);
+}
+
+// dst = src with every row of `row` doubles split into its even and its odd elements
+__global__ void __launch_bounds__(256) k3_split_rows(const double *__restrict__ src, double *__restrict__ dst, int row,
+                                                     long long total) {
+  for (long long t = blockIdx.x * (long long)blockDim.x + threadIdx.x; t < total; t += (long long)gridDim.x * blockDim.x) {
+    const int ip = (int)(t % row);
+    dst[t - ip + (ip & 1) * (row >> 1) + (ip >> 1)] = src[t];
+  }
 }
 
 // combinedOp * w at p
@@ -241,6 +261,8 @@ __device__ __forceinline__ void o3_block_solve(const O3Args &a, const double (&G
 
 // one colour: flow += inverse ( diag ( combinedOp ) ) * ( rhs - combinedOp * flow ) on the cells with
 // (i + j + k) % 2 == color; apply bc
+// SPLIT: gradContribution from the split-row copies (the lanes of a warp read consecutive doubles)
+template <bool SPLIT>
 __global__ void __launch_bounds__(256) k3_smooth_color(const O3Args a, int color) {
   const int tx = blockIdx.x * blockDim.x + threadIdx.x, j = blockIdx.y * blockDim.y + threadIdx.y;
   if (j >= a.ny) return;
@@ -248,9 +270,17 @@ __global__ void __launch_bounds__(256) k3_smooth_color(const O3Args a, int color
     const int i = 2 * tx + ((j + k + color) & 1);
     if (i >= a.nx) continue;
     const long long p = o3_idx(a, i, j, k);
-    double r[3], d[3];
-    o3_residual_at(a, a.f[0], a.f[1], a.f[2], p, r);
-    const double g6[6] = {a.f[9][p], a.f[10][p], a.f[11][p], a.f[12][p], a.f[13][p], a.f[14][p]};
+    double r[3], d[3], g6[6];
+    if (SPLIT) {
+      const int ip = i + 1;
+      const long long sp = p - ip + (ip & 1) * ((a.nx + 2) >> 1) + (ip >> 1);
+#pragma unroll
+      for (int q = 0; q < 6; ++q) g6[q] = a.gs[q][sp];
+    } else {
+#pragma unroll
+      for (int q = 0; q < 6; ++q) g6[q] = a.f[9 + q][p];
+    }
+    o3_residual_g(a, g6, a.f[0], a.f[1], a.f[2], p, r);
     o3_block_solve(a, g6, r, d);
     o3_store(a, a.f[0], i, j, k, a.f[0][p] + d[0]);
     o3_store(a, a.f[1], i, j, k, a.f[1][p] + d[1]);
@@ -525,6 +555,7 @@ O3Args o3_args(const examg_optflow3 *o, const O3Level &L) {
   for (int k = 0; k < 7; ++k) a.L[k] = L.L[k];
   a.a2 = o->desc.alpha * o->desc.alpha;  // alpha ** 2
   for (int k = 0; k < O3_NF; ++k) a.f[k] = L.f[k];
+  for (int k = 0; k < 6; ++k) a.gs[k] = L.gs_valid ? L.gs[k] : nullptr;
   return a;
 }
 
@@ -555,7 +586,11 @@ double *o3_array(examg_optflow3 *o, int level, int which, size_t *count) {
 
 int o3_smooth_color(examg_optflow3 *o, O3Level &L, int color) {
   examg_ctx *c = o->c;
-  k3_smooth_color<<<o3_shape((L.n[0] + 1) / 2, L.n[1], L.n[2]), dim3(64, 4), 0, c->stream>>>(o3_args(o, L), color);
+  const O3Args a = o3_args(o, L);
+  if (a.gs[0])
+    k3_smooth_color<true><<<o3_shape((L.n[0] + 1) / 2, L.n[1], L.n[2]), dim3(64, 4), 0, c->stream>>>(a, color);
+  else
+    k3_smooth_color<false><<<o3_shape((L.n[0] + 1) / 2, L.n[1], L.n[2]), dim3(64, 4), 0, c->stream>>>(a, color);
   EXAMG_LAUNCH_CHECK(c);
   return EXAMG_OK;
 }
@@ -739,6 +774,13 @@ examg_optflow3 *examg_optflow3_create(examg_ctx *c, const examg_optflow3_desc *d
       ok = ok && cudaMalloc(&L.f[k], sizeof(double) * L.vol) == cudaSuccess &&
            cudaMemsetAsync(L.f[k], 0, sizeof(double) * L.vol, c->stream) == cudaSuccess;
     }
+    L.gs_valid = false;
+    static const bool split_on = !(getenv("EXAMG_OF3_SPLIT") && getenv("EXAMG_OF3_SPLIT")[0] == '0');
+    for (int k = 0; k < 6; ++k) {
+      L.gs[k] = nullptr;
+      if (split_on && L.n[0] % 2 == 0 && (long long)L.n[0] * L.n[1] * L.n[2] >= (1 << 15))
+        ok = ok && cudaMalloc(&L.gs[k], sizeof(double) * L.vol) == cudaSuccess;
+    }
     L.flipped = false;
     for (int k = 0; k < 3; ++k) {
       L.alt[k] = nullptr;
@@ -779,6 +821,8 @@ int examg_optflow3_destroy(examg_optflow3 *o) {
       if (L.f[k]) cudaFree(L.f[k]);
     for (int k = 0; k < 3; ++k)
       if (L.alt[k]) cudaFree(L.alt[k]);
+    for (int k = 0; k < 6; ++k)
+      if (L.gs[k]) cudaFree(L.gs[k]);
   }
   for (double *p : o->img)
     if (p) cudaFree(p);
@@ -807,6 +851,16 @@ int examg_optflow3_upload(examg_optflow3 *o, int level, int which, const double 
   size_t count = 0;
   double *dev = o3_array(o, level, which, &count);
   if (!dev) return set_error(EXAMG_EINVAL, "examg_optflow3_upload: level %d field %d", level, which);
+  if (which >= EXAMG_OF3_G && which < EXAMG_OF3_G + 6) {  // the split-row copies follow at once (cycles may be graphs)
+    O3Level *L = o3_level(o, level);
+    EXAMG_CUDA(cudaMemcpyAsync(dev, host, sizeof(double) * count, cudaMemcpyHostToDevice, o->c->stream));
+    if (L->gs[which - EXAMG_OF3_G]) {
+      k3_split_rows<<<o3_grid((long long)L->vol), 256, 0, o->c->stream>>>(dev, L->gs[which - EXAMG_OF3_G], L->n[0] + 2, (long long)L->vol);
+      EXAMG_LAUNCH_CHECK(o->c);
+    }
+    EXAMG_CUDA(cudaStreamSynchronize(o->c->stream));
+    return EXAMG_OK;
+  }
   EXAMG_CUDA(cudaMemcpyAsync(dev, host, sizeof(double) * count, cudaMemcpyHostToDevice, o->c->stream));
   EXAMG_CUDA(cudaStreamSynchronize(o->c->stream));
   return EXAMG_OK;
@@ -839,6 +893,14 @@ int examg_optflow3_init_fields(examg_optflow3 *o) {
   for (int l = (int)o->lev.size() - 2; l >= 0; --l) {  // initGradients@(all but finest)
     const int rc = o3_restrict(o, o->lev[l + 1], o->lev[l], g, g, 6);
     if (rc) return rc;
+  }
+  for (O3Level &Lv : o->lev) {  // split-row copies for the colour passes
+    if (!Lv.gs[0]) continue;
+    for (int k = 0; k < 6; ++k) {
+      k3_split_rows<<<o3_grid((long long)Lv.vol), 256, 0, c->stream>>>(Lv.f[9 + k], Lv.gs[k], Lv.n[0] + 2, (long long)Lv.vol);
+      EXAMG_LAUNCH_CHECK(c);
+    }
+    Lv.gs_valid = true;
   }
   return EXAMG_OK;
 }

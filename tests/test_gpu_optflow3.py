@@ -66,6 +66,10 @@ def test_loops_against_the_oracle(F, lo, hi, fused, oracle, request):
     for lvl in range(lo, hi + 1):
         _equal(g, r, lvl, range(o3.G, o3.G + 6), "initGradients")
     _equal(g, r, hi, range(o3.RHS, o3.RHS + 3), "rhs")
+    # a coefficient array replaced after InitFields: the split-row copies the colour passes read must follow
+    gxx = r.field(hi, o3.G) + 0.25
+    r.field(hi, o3.G)[...] = gxx
+    g.set_field(hi, o3.G, gxx)
     # random state on two levels (ghost cells consistent: the oracle's smoother applies bc itself)
     rng = np.random.default_rng(5)
     for lvl in (hi, hi - 1):
