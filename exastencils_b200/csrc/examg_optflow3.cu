@@ -55,6 +55,10 @@ struct O3Args {
   const double *gs[6];  // split-row copies of f[9..14] (nullptr: none)
 };
 
+// planes [o3_z0, o3_z1) of thread block z among gridDim.z
+__device__ __forceinline__ int o3_z0(int nz) { return (int)((long long)nz * blockIdx.z / gridDim.z); }
+__device__ __forceinline__ int o3_z1(int nz) { return (int)((long long)nz * (blockIdx.z + 1) / gridDim.z); }
+
 __device__ __forceinline__ long long o3_idx(const O3Args &a, int i, int j, int k) {
   return (i + 1) + a.sy * (j + 1) + a.sz * (k + 1);
 }
@@ -203,7 +207,7 @@ __global__ void __launch_bounds__(256) k3_correct(const O3Args a, const double *
                                                   const double *__restrict__ c2, long long syc, long long szc) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x, j = blockIdx.y * blockDim.y + threadIdx.y;
   if (i >= a.nx || j >= a.ny) return;
-  for (int k = blockIdx.z; k < a.nz; k += gridDim.z) {
+  for (int k = o3_z0(a.nz), k1 = o3_z1(a.nz); k < k1; ++k) {  // a contiguous chunk of planes: z neighbours stay in L1
     const long long p = o3_idx(a, i, j, k), q = ((i >> 1) + 1) + syc * ((j >> 1) + 1) + szc * ((k >> 1) + 1);
     o3_store(a, a.f[0], i, j, k, a.f[0][p] + c0[q]);
     o3_store(a, a.f[1], i, j, k, a.f[1][p] + c1[q]);
@@ -218,7 +222,7 @@ __global__ void __launch_bounds__(256) k3_residual(const O3Args a, dd *__restric
   const int i = blockIdx.x * blockDim.x + threadIdx.x, j = blockIdx.y * blockDim.y + threadIdx.y;
   dd part = {0.0, 0.0};
   if (i < a.nx && j < a.ny)
-    for (int k = blockIdx.z; k < a.nz; k += gridDim.z) {
+    for (int k = o3_z0(a.nz), k1 = o3_z1(a.nz); k < k1; ++k) {  // a contiguous chunk of planes: z neighbours stay in L1
       const long long p = o3_idx(a, i, j, k);
       double r[3];
       o3_residual_at(a, a.f[0], a.f[1], a.f[2], p, r);
@@ -266,7 +270,7 @@ template <bool SPLIT>
 __global__ void __launch_bounds__(256) k3_smooth_color(const O3Args a, int color) {
   const int tx = blockIdx.x * blockDim.x + threadIdx.x, j = blockIdx.y * blockDim.y + threadIdx.y;
   if (j >= a.ny) return;
-  for (int k = blockIdx.z; k < a.nz; k += gridDim.z) {
+  for (int k = o3_z0(a.nz), k1 = o3_z1(a.nz); k < k1; ++k) {  // a contiguous chunk of planes: z neighbours stay in L1
     const int i = 2 * tx + ((j + k + color) & 1);
     if (i >= a.nx) continue;
     const long long p = o3_idx(a, i, j, k);
